@@ -1,0 +1,64 @@
+# Build of the B200-native PCCL: libpccl.so (C++20 core + sm_100a kernels), ccoip_master, C++ tests.
+# Everything lands in-tree (pccl_b200/lib, pccl_b200/bin, build/) so that the artefacts travel
+# with a snapshot of the repository.
+CXX      ?= g++
+NVCC     ?= /usr/local/cuda/bin/nvcc
+CUDA_HOME ?= /usr/local/cuda
+BUILD    := build
+LIBDIR   := pccl_b200/lib
+BINDIR   := pccl_b200/bin
+
+CXXFLAGS := -std=c++20 -O3 -g1 -fPIC -fvisibility=hidden -Wall -Wextra -Iinclude -Icsrc -pthread
+NVFLAGS  := -std=c++20 -O3 -lineinfo -gencode arch=compute_100a,code=sm_100a -Xcompiler -fPIC,-fvisibility=hidden \
+            -Iinclude -Icsrc --expt-relaxed-constexpr -Xptxas -v
+LDFLAGS  := -pthread -Wl,--no-undefined
+
+ifeq ($(NO_CUDA),1)
+CXXFLAGS += -DPCCL_NO_CUDA
+CU_SRCS  :=
+CUDA_LIBS :=
+else
+CXXFLAGS += -I$(CUDA_HOME)/include
+CU_SRCS  := $(wildcard csrc/kernels/cuda/*.cu) $(wildcard csrc/device/*.cu)
+CUDA_LIBS := -L$(CUDA_HOME)/lib64 -lcudart_static -ldl -lrt
+endif
+
+CPP_SRCS := $(wildcard csrc/util/*.cpp csrc/wire/*.cpp csrc/net/*.cpp csrc/topo/*.cpp csrc/master/*.cpp \
+              csrc/kernels/cpu/*.cpp csrc/client/*.cpp csrc/device/*.cpp csrc/api/*.cpp)
+CPP_OBJS := $(patsubst %.cpp,$(BUILD)/%.o,$(CPP_SRCS))
+CU_OBJS  := $(patsubst %.cu,$(BUILD)/%.cu.o,$(CU_SRCS))
+
+TEST_SRCS := $(wildcard tests/cpp/test_*.cpp)
+TEST_BINS := $(patsubst tests/cpp/%.cpp,$(BUILD)/tests/%,$(TEST_SRCS))
+
+.PHONY: all lib master tests clean
+all: lib master tests
+lib: $(LIBDIR)/libpccl.so
+master: $(BINDIR)/ccoip_master
+tests: $(TEST_BINS)
+
+$(BUILD)/%.o: %.cpp
+	@mkdir -p $(dir $@)
+	$(CXX) $(CXXFLAGS) -MMD -MP -c $< -o $@
+
+$(BUILD)/%.cu.o: %.cu
+	@mkdir -p $(dir $@)
+	$(NVCC) $(NVFLAGS) -c $< -o $@ 2> $@.ptxas.log || (cat $@.ptxas.log; false)
+
+$(LIBDIR)/libpccl.so: $(CPP_OBJS) $(CU_OBJS)
+	@mkdir -p $(LIBDIR)
+	$(CXX) -shared -o $@ $^ $(LDFLAGS) $(CUDA_LIBS)
+
+$(BINDIR)/ccoip_master: tools/ccoip_master.cpp $(LIBDIR)/libpccl.so
+	@mkdir -p $(BINDIR)
+	$(CXX) $(CXXFLAGS) -fvisibility=default $< -o $@ -L$(LIBDIR) -lpccl -Wl,-rpath,'$$ORIGIN/../lib' -pthread
+
+# C++ tests link the objects directly so they can reach internal classes
+$(BUILD)/tests/%: tests/cpp/%.cpp $(CPP_OBJS) $(CU_OBJS)
+	@mkdir -p $(dir $@)
+	$(CXX) $(CXXFLAGS) -Itests/cpp $< $(CPP_OBJS) $(CU_OBJS) -o $@ $(LDFLAGS) $(CUDA_LIBS)
+
+clean:
+	rm -rf $(BUILD) $(LIBDIR)/libpccl.so $(BINDIR)/ccoip_master
+
+-include $(CPP_OBJS:.o=.d)

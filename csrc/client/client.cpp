@@ -1,0 +1,806 @@
+#include "client.hpp"
+
+#include <algorithm>
+#include <chrono>
+#include <cstring>
+#include <random>
+#include <thread>
+
+#include "../kernels/cpu/hash.hpp"
+#include "../kernels/cpu/reduce.hpp"
+#include "../net/sockutil.hpp"
+#include "../util/env.hpp"
+#include "../util/log.hpp"
+#include "ring_reduce.hpp"
+
+namespace pccl::client {
+
+using namespace pccl::wire;
+using clock_type = std::chrono::steady_clock;
+
+namespace {
+size_t frame_bytes_from_env() {
+    // reference knob: PCCL_MULTIPLEX_CHUNK_SIZE (ccoip/src/cpp/reduce.cpp:20-41); smaller default
+    // here because received frames are reduced while the next one is in flight
+    return static_cast<size_t>(env_u64("PCCL_MULTIPLEX_CHUNK_SIZE", 2u << 20));
+}
+} // namespace
+
+Client::Client(const ClientConfig &cfg)
+    : cfg_(cfg), master_(cfg.master), p2p_listener_(net::any_v4(cfg.p2p_port), true),
+      ss_listener_(net::any_v4(cfg.ss_port), true), bm_listener_(net::any_v4(cfg.bm_port), true),
+      plane_(device::Plane::create()) {
+    if (cfg_.pool_size == 0) cfg_.pool_size = 1;
+    const size_t n_workers = static_cast<size_t>(env_u64("PCCL_MAX_CONCURRENT_COLLECTIVE_OPS", 16));
+    workers_ = std::make_unique<ThreadPool>(std::max<size_t>(1, n_workers), 64);
+    ss_workers_ = std::make_unique<ThreadPool>(2, 64);
+    bm_workers_ = std::make_unique<ThreadPool>(static_cast<size_t>(env_u64("PCCL_NUM_BENCHMARK_CONNECTIONS", 16)) + 1, 64);
+}
+
+Client::~Client() {
+    interrupt();
+    join();
+}
+
+// ------------------------------------------------------------------------------------------
+// connect / lifecycle
+// ------------------------------------------------------------------------------------------
+
+bool Client::connect() {
+    if (started_.exchange(true)) return false;
+    p2p_listener_.on_join([this](std::unique_ptr<net::BlockingSocket> s) { on_p2p_accept(std::move(s)); });
+    ss_listener_.on_join([this](std::unique_ptr<net::BlockingSocket> s) {
+        auto shared = std::shared_ptr<net::BlockingSocket>(std::move(s));
+        ss_workers_->submit([this, shared]() mutable {
+            on_shared_state_accept(std::make_unique<net::BlockingSocket>(shared->release(), shared->remote()));
+        });
+    });
+    bm_listener_.on_join([this](std::unique_ptr<net::BlockingSocket> s) {
+        auto shared = std::shared_ptr<net::BlockingSocket>(std::move(s));
+        bm_workers_->submit([this, shared]() mutable {
+            on_benchmark_accept(std::make_unique<net::BlockingSocket>(shared->release(), shared->remote()));
+        });
+    });
+    if (!p2p_listener_.listen() || !ss_listener_.listen() || !bm_listener_.listen()) return false;
+    if (!p2p_listener_.run_async() || !ss_listener_.run_async() || !bm_listener_.run_async()) return false;
+
+    if (!master_.connect()) {
+        PLOG(ERR) << "cannot reach master at " << net::to_string(cfg_.master);
+        return false;
+    }
+    master_.run();
+
+    C2MSessionRegistration reg;
+    reg.peer_group = cfg_.peer_group;
+    reg.explicit_addresses = cfg_.explicit_addresses;
+    if (cfg_.explicit_addresses) {
+        reg.adv_p2p = cfg_.adv_p2p;
+        reg.adv_ss = cfg_.adv_ss;
+        reg.adv_bm = cfg_.adv_bm;
+    } else {
+        reg.p2p_port = p2p_listener_.port();
+        reg.ss_port = ss_listener_.port();
+        reg.bm_port = bm_listener_.port();
+    }
+    if (!master_.send_packet(reg)) return false;
+    const auto resp = master_.recv_packet<M2CSessionRegistrationResponse>();
+    if (!resp || !resp->accepted) {
+        PLOG(ERR) << "master refused the registration";
+        return false;
+    }
+    uuid_ = resp->assigned_uuid;
+    plane_->start(uuid_);
+
+    // Blocks until the accepted peers vote to let us in.
+    const Establish first = establish_round();
+    if (first == Establish::Failed) return false;
+    accepted_ = true;
+    if (first == Establish::Retry) {
+        // We count as accepted even though the round has to be repeated (somebody dropped or was
+        // unreachable); take part in the repeat like everybody else.
+        if (!request_and_establish(true)) {
+            accepted_ = false;
+            return false;
+        }
+    } else {
+        connection_revision_++;
+    }
+    return true;
+}
+
+bool Client::interrupt() {
+    if (interrupted_.exchange(true)) return true;
+    master_.interrupt();
+    p2p_listener_.interrupt();
+    ss_listener_.interrupt();
+    bm_listener_.interrupt();
+    {
+        std::lock_guard<std::mutex> lock(tx_mu_);
+        for (auto &[u, pool] : tx_pools_)
+            for (auto &s : pool)
+                if (s) s->interrupt();
+    }
+    {
+        std::lock_guard<std::mutex> lock(rx_mu_);
+        for (auto &[u, pool] : rx_pools_)
+            for (auto &s : pool)
+                if (s) s->interrupt();
+    }
+    rx_cv_.notify_all();
+    return true;
+}
+
+bool Client::join() {
+    if (workers_) workers_->shutdown();
+    master_.join();
+    p2p_listener_.join();
+    ss_listener_.join();
+    bm_listener_.join();
+    if (ss_workers_) ss_workers_->shutdown();
+    if (bm_workers_) bm_workers_->shutdown();
+    {
+        std::lock_guard<std::mutex> lock(tx_mu_);
+        tx_pools_.clear();
+    }
+    {
+        std::lock_guard<std::mutex> lock(rx_mu_);
+        rx_pools_.clear();
+    }
+    plane_->stop();
+    return true;
+}
+
+// ------------------------------------------------------------------------------------------
+// P2P wiring
+// ------------------------------------------------------------------------------------------
+
+void Client::on_p2p_accept(std::unique_ptr<net::BlockingSocket> sock) {
+    const auto hello = sock->recv_packet<P2PHello>(5000);
+    if (!hello) return;
+    if (!sock->send_packet(P2PHelloAck{})) return;
+    const ccoip_socket_address_t remote = sock->remote();
+    auto mux = std::make_shared<net::MuxSocket>(sock->release(), remote, net::MuxSocket::Mode::Rx);
+    mux->run();
+    {
+        std::lock_guard<std::mutex> lock(rx_mu_);
+        Pool &pool = rx_pools_[hello->uuid];
+        if (pool.size() <= hello->connection_nr) pool.resize(hello->connection_nr + 1);
+        if (pool[hello->connection_nr]) pool[hello->connection_nr]->interrupt(); // replaced by a fresh link
+        pool[hello->connection_nr] = std::move(mux);
+    }
+    rx_cv_.notify_all();
+}
+
+bool Client::dial_peer(const PeerEndpoint &peer) {
+    Pool pool;
+    for (uint32_t nr = 0; nr < cfg_.pool_size; ++nr) {
+        net::BlockingSocket sock(peer.p2p_addr);
+        if (!sock.connect(5000)) return false;
+        P2PHello hello;
+        hello.uuid = uuid_;
+        hello.connection_nr = nr;
+        if (!sock.send_packet(hello)) return false;
+        if (!sock.recv_packet<P2PHelloAck>(5000)) return false;
+        auto mux = std::make_shared<net::MuxSocket>(sock.release(), peer.p2p_addr, net::MuxSocket::Mode::Tx);
+        mux->run();
+        pool.push_back(std::move(mux));
+    }
+    std::lock_guard<std::mutex> lock(tx_mu_);
+    tx_pools_[peer.uuid] = std::move(pool);
+    return true;
+}
+
+Client::Establish Client::establish_round() {
+    const auto info = master_.recv_packet<M2CP2PConnectionInfo>();
+    if (!info) return Establish::Failed;
+    global_world_ = info->global_world_size;
+    local_world_ = info->local_world_size;
+    num_groups_ = info->num_peer_groups;
+    largest_group_ = info->largest_group_size;
+
+    C2MP2PEstablished report;
+    report.success = true;
+    if (!info->unchanged) {
+        for (const auto &peer : info->peers) {
+            bool have = false;
+            {
+                std::lock_guard<std::mutex> lock(tx_mu_);
+                const auto it = tx_pools_.find(peer.uuid);
+                have = it != tx_pools_.end() && !it->second.empty() &&
+                       std::all_of(it->second.begin(), it->second.end(), [](const auto &s) { return s && s->is_open(); });
+            }
+            if (have) continue;
+            if (!dial_peer(peer)) {
+                PLOG(WARN) << "cannot reach peer " << peer.uuid.str() << " at " << net::to_string(peer.p2p_addr);
+                report.success = false;
+                report.failed_peers.push_back(peer.uuid);
+                break;
+            }
+        }
+        // links to peers that are no longer neighbours are closed
+        auto wanted = [&](const Uuid &u) {
+            return std::any_of(info->peers.begin(), info->peers.end(), [&](const PeerEndpoint &p) { return p.uuid == u; });
+        };
+        {
+            std::lock_guard<std::mutex> lock(tx_mu_);
+            for (auto it = tx_pools_.begin(); it != tx_pools_.end();) {
+                if (wanted(it->first)) {
+                    ++it;
+                    continue;
+                }
+                for (auto &s : it->second)
+                    if (s) s->interrupt();
+                it = tx_pools_.erase(it);
+            }
+        }
+        {
+            std::lock_guard<std::mutex> lock(rx_mu_);
+            for (auto it = rx_pools_.begin(); it != rx_pools_.end();) {
+                if (wanted(it->first)) {
+                    ++it;
+                    continue;
+                }
+                for (auto &s : it->second)
+                    if (s) s->interrupt();
+                it = rx_pools_.erase(it);
+            }
+        }
+    }
+    if (!master_.send_packet(report)) return Establish::Failed;
+    const auto verdict = master_.recv_packet<M2CP2PEstablished>();
+    if (!verdict) return Establish::Failed;
+    if (!report.success && verdict->success) return Establish::Failed;
+    if (!verdict->success) return Establish::Retry;
+    {
+        std::unique_lock<std::shared_mutex> lock(ring_mu_);
+        ring_ = verdict->ring_order;
+    }
+    local_world_ = verdict->ring_order.size();
+    plane_->on_ring_changed(verdict->ring_order);
+    return Establish::Success;
+}
+
+bool Client::request_and_establish(bool accept_new_peers) {
+    if (!accepted_ || !master_.is_open()) return false;
+    if (any_reduce_running()) return false;
+    Establish result;
+    do {
+        C2MEstablishP2P vote;
+        vote.accept_new_peers = accept_new_peers;
+        if (!master_.send_packet(vote)) return false;
+        result = establish_round();
+    } while (result == Establish::Retry);
+    if (result == Establish::Failed) return false;
+    connection_revision_++;
+    return true;
+}
+
+bool Client::update_topology() {
+    std::lock_guard<std::mutex> lock(joint_mu_);
+    return request_and_establish(true);
+}
+
+bool Client::are_peers_pending(bool &pending) {
+    if (!accepted_ || !master_.is_open()) return false;
+    if (!master_.send_packet(C2MCheckPeersPending{})) return false;
+    const auto resp = master_.recv_packet<M2CPeersPendingResponse>();
+    if (!resp) return false;
+    pending = resp->pending;
+    return true;
+}
+
+// ------------------------------------------------------------------------------------------
+// topology optimisation
+// ------------------------------------------------------------------------------------------
+
+void Client::on_benchmark_accept(std::unique_ptr<net::BlockingSocket> sock) {
+    const auto hello = sock->recv_packet<C2BHello>(5000);
+    if (!hello) return;
+    // One measuring peer at a time; the runner opens several connections, so further
+    // connections of the admitted peer are let in, everybody else is told to come back.
+    bool admitted = false;
+    {
+        std::lock_guard<std::mutex> lock(bm_mu_);
+        if (bm_active_ == 0 || bm_owner_ == hello->uuid) {
+            bm_owner_ = hello->uuid;
+            bm_active_++;
+            admitted = true;
+        }
+    }
+    B2CBusy reply;
+    reply.busy = !admitted;
+    sock->send_packet(reply);
+    if (!admitted) return;
+    std::vector<uint8_t> sink(1 << 20);
+    const auto deadline = clock_type::now() + std::chrono::seconds(18);
+    while (clock_type::now() < deadline && !interrupted_) {
+        const int rc = net::wait_readable(sock->fd(), 200);
+        if (rc < 0) break;
+        if (rc == 0) continue;
+        const ssize_t k = ::recv(sock->fd(), sink.data(), sink.size(), 0);
+        if (k <= 0) break;
+    }
+    std::lock_guard<std::mutex> lock(bm_mu_);
+    --bm_active_;
+}
+
+bool Client::run_benchmark(const BenchmarkRequest &req, double &mbits, bool &busy) {
+    busy = false;
+    const int n_conn = static_cast<int>(env_u64("PCCL_NUM_BENCHMARK_CONNECTIONS", 16));
+    const uint64_t millis = env_u64("PCCL_BENCHMARK_MILLIS", 10000);
+    std::vector<std::unique_ptr<net::BlockingSocket>> socks;
+    for (int i = 0; i < n_conn; ++i) {
+        auto s = std::make_unique<net::BlockingSocket>(req.endpoint);
+        if (!s->connect(3000)) return false;
+        C2BHello hello;
+        hello.uuid = uuid_;
+        if (!s->send_packet(hello)) return false;
+        const auto reply = s->recv_packet<B2CBusy>(5000);
+        if (!reply) return false;
+        if (reply->busy) {
+            busy = true;
+            return false;
+        }
+        socks.push_back(std::move(s));
+    }
+    std::vector<uint8_t> payload(8u << 20);
+    std::mt19937_64 rng(0xbeef);
+    for (size_t i = 0; i + 8 <= payload.size(); i += 8) {
+        const uint64_t v = rng();
+        std::memcpy(&payload[i], &v, 8);
+    }
+    std::atomic<uint64_t> total{0};
+    const auto start = clock_type::now();
+    const auto stop_at = start + std::chrono::milliseconds(millis);
+    std::vector<std::thread> threads;
+    for (auto &s : socks) {
+        threads.emplace_back([&, fd = s->fd()] {
+            net::set_send_timeout(fd, 2);
+            while (clock_type::now() < stop_at && !interrupted_) {
+                const ssize_t k = ::send(fd, payload.data(), std::min<size_t>(payload.size(), 1u << 20), MSG_NOSIGNAL);
+                if (k <= 0) break;
+                total += static_cast<uint64_t>(k);
+            }
+        });
+    }
+    for (auto &t : threads) t.join();
+    const double secs = std::chrono::duration<double>(clock_type::now() - start).count();
+    socks.clear();
+    mbits = secs > 0 ? static_cast<double>(total) * 8.0 / 1e6 / secs : 0.0;
+    return total > 0;
+}
+
+bool Client::optimize_topology() {
+    std::lock_guard<std::mutex> lock(joint_mu_);
+    if (!accepted_ || !master_.is_open()) return false;
+    if (any_reduce_running()) return false;
+    for (int round = 0; round < 64; ++round) {
+        if (!master_.send_packet(C2MOptimizeTopology{})) return false;
+        const auto work = master_.recv_packet<M2COptimizeTopologyResponse>();
+        if (!work) return false;
+        std::vector<BenchmarkRequest> todo = work->requests;
+        int attempts = 0;
+        while (!todo.empty() && attempts < 30 && !interrupted_) {
+            std::vector<BenchmarkRequest> later;
+            for (const auto &req : todo) {
+                double mbits = 0;
+                bool busy = false;
+                if (run_benchmark(req, mbits, busy)) {
+                    C2MReportBandwidth rep;
+                    rep.to_peer = req.to;
+                    rep.mbits_per_second = mbits;
+                    if (!master_.send_packet(rep)) return false;
+                    PLOG(DEBUG) << "bandwidth to " << req.to.str() << ": " << mbits << " Mbit/s";
+                } else if (busy) {
+                    later.push_back(req);
+                    std::this_thread::sleep_for(std::chrono::milliseconds(env_u64("PCCL_BENCHMARK_BACKOFF_MILLIS", 1000)));
+                } // unreachable endpoints are simply not reported; the master marks them
+            }
+            todo.swap(later);
+            ++attempts;
+        }
+        if (!master_.send_packet(C2MOptimizeWorkComplete{})) return false;
+        const auto done = master_.recv_packet<M2COptimizeTopologyComplete>();
+        if (!done) return false;
+        if (done->success) break;
+    }
+    // rewire to the neighbours of the new ring
+    return request_and_establish(false);
+}
+
+// ------------------------------------------------------------------------------------------
+// shared state
+// ------------------------------------------------------------------------------------------
+
+namespace {
+constexpr size_t kStageBytes = 8u << 20;
+}
+
+void Client::on_shared_state_accept(std::unique_ptr<net::BlockingSocket> sock) {
+    const auto req = sock->recv_packet<C2SRequestSharedState>(10000);
+    if (!req) return;
+    S2CSharedStateResponse resp;
+    std::vector<SharedEntry> serve;
+    {
+        std::lock_guard<std::mutex> lock(ss_mu_);
+        if (!ss_serving_) {
+            resp.status = SharedStateStatus::NotInDistributionMode;
+        } else {
+            resp.status = SharedStateStatus::Success;
+            resp.revision = ss_snapshot_.revision;
+            for (const auto &key : req->keys) {
+                const auto it = std::find_if(ss_snapshot_.entries.begin(), ss_snapshot_.entries.end(),
+                                             [&](const SharedEntry &e) { return e.key == key; });
+                if (it == ss_snapshot_.entries.end()) {
+                    resp.status = SharedStateStatus::NotDistributed;
+                    resp.entries.clear();
+                    serve.clear();
+                    break;
+                }
+                resp.entries.push_back({key, it->bytes()});
+                serve.push_back(*it);
+            }
+        }
+    }
+    if (!sock->send_packet(resp) || resp.status != SharedStateStatus::Success) return;
+    // Raw tensor bytes follow, unframed, in request order.  The buffers stay valid: the owner is
+    // blocked inside sync_shared_state until every peer has reported completion.
+    std::vector<uint8_t> stage;
+    for (const auto &e : serve) {
+        const size_t bytes = e.bytes();
+        if (!e.on_device) {
+            if (!sock->send_raw(e.data, bytes)) return;
+        } else {
+            if (stage.empty()) stage.resize(kStageBytes);
+            for (size_t off = 0; off < bytes; off += kStageBytes) {
+                const size_t n = std::min(kStageBytes, bytes - off);
+                if (!plane_->copy_to_host(stage.data(), static_cast<const uint8_t *>(e.data) + off, n)) return;
+                if (!sock->send_raw(stage.data(), n)) return;
+            }
+        }
+        ss_tx_bytes_ += bytes;
+    }
+}
+
+bool Client::sync_shared_state(SharedStateArgs &state, uint64_t &tx_bytes, uint64_t &rx_bytes) {
+    std::lock_guard<std::mutex> lock(joint_mu_);
+    tx_bytes = rx_bytes = 0;
+    if (!accepted_ || !master_.is_open()) return false;
+    if (any_reduce_running()) return false;
+
+    C2MSyncSharedState vote;
+    vote.revision = state.revision;
+    vote.strategy = state.strategy;
+    for (const auto &e : state.entries) {
+        SharedStateEntry w;
+        w.key = e.key;
+        w.hash_type = HashType::Simple;
+        w.num_elements = e.count;
+        w.dtype = e.dtype;
+        w.allow_content_inequality = e.allow_content_inequality;
+        if (!e.allow_content_inequality) {
+            if (e.on_device) {
+                if (!plane_->hash_device(e.data, e.bytes(), HashType::Simple, w.hash)) {
+                    PLOG(ERR) << "cannot hash device tensor '" << e.key << "'";
+                    return false;
+                }
+            } else {
+                w.hash = cpu::simplehash(e.data, e.bytes());
+            }
+        }
+        vote.entries.push_back(std::move(w));
+    }
+
+    // From here until completion the shared-state server may hand our tensors to other peers.
+    {
+        std::lock_guard<std::mutex> l(ss_mu_);
+        ss_snapshot_ = state;
+        ss_serving_ = true;
+        ss_tx_bytes_ = 0;
+    }
+    struct Guard {
+        Client *c;
+        ~Guard() {
+            std::lock_guard<std::mutex> l(c->ss_mu_);
+            c->ss_serving_ = false;
+        }
+    } guard{this};
+
+    if (!master_.send_packet(vote)) return false;
+    const auto verdict = master_.recv_packet<M2CSyncSharedState>();
+    if (!verdict) return false;
+
+    if (verdict->is_outdated) {
+        const auto &d = verdict->distributor;
+        const bool empty_v4 = d.inet.protocol == inetIPv4 && d.port == 0;
+        if (empty_v4) {
+            PLOG(ERR) << "shared state is outdated but nobody can distribute it";
+            return false;
+        }
+        net::BlockingSocket sock(verdict->distributor);
+        if (!sock.connect(10000)) {
+            PLOG(ERR) << "cannot reach shared-state distributor " << net::to_string(verdict->distributor);
+            return false;
+        }
+        C2SRequestSharedState req;
+        req.keys = verdict->outdated_keys;
+        if (!sock.send_packet(req)) return false;
+        const auto resp = sock.recv_packet<S2CSharedStateResponse>(60000);
+        if (!resp || resp->status != SharedStateStatus::Success) {
+            PLOG(ERR) << "distributor refused the shared-state request";
+            return false;
+        }
+        if (resp->entries.size() != verdict->outdated_keys.size()) return false;
+        state.revision = resp->revision; // adopt the distributor's revision even if no bytes move
+        std::vector<uint8_t> stage;
+        for (size_t i = 0; i < resp->entries.size(); ++i) {
+            const auto &slice = resp->entries[i];
+            const auto it = std::find_if(state.entries.begin(), state.entries.end(),
+                                         [&](const SharedEntry &e) { return e.key == slice.key; });
+            if (it == state.entries.end() || it->bytes() != slice.size_bytes) {
+                PLOG(ERR) << "distributor offered '" << slice.key << "' with an unexpected size";
+                return false;
+            }
+            if (!it->on_device) {
+                if (!sock.recv_raw(it->data, slice.size_bytes)) return false;
+            } else {
+                if (stage.empty()) stage.resize(kStageBytes);
+                for (size_t off = 0; off < slice.size_bytes; off += kStageBytes) {
+                    const size_t n = std::min<size_t>(kStageBytes, slice.size_bytes - off);
+                    if (!sock.recv_raw(stage.data(), n)) return false;
+                    if (!plane_->copy_to_device(static_cast<uint8_t *>(it->data) + off, stage.data(), n)) return false;
+                }
+            }
+            rx_bytes += slice.size_bytes;
+            // verify what arrived against what the master elected
+            if (!it->allow_content_inequality && i < verdict->expected_hashes.size()) {
+                uint64_t h = 0;
+                if (it->on_device) {
+                    if (!plane_->hash_device(it->data, it->bytes(), HashType::Simple, h)) return false;
+                } else {
+                    h = cpu::simplehash(it->data, it->bytes());
+                }
+                if (h != verdict->expected_hashes[i]) {
+                    PLOG(ERR) << "shared-state tensor '" << slice.key << "' does not match the elected hash after transfer";
+                    return false;
+                }
+            }
+        }
+    }
+
+    if (!master_.send_packet(C2MDistSharedStateComplete{})) return false;
+    if (!master_.recv_packet<M2CSyncSharedStateComplete>()) return false;
+    tx_bytes = ss_tx_bytes_;
+    return true;
+}
+
+// ------------------------------------------------------------------------------------------
+// all-reduce
+// ------------------------------------------------------------------------------------------
+
+bool Client::any_reduce_running() {
+    std::lock_guard<std::mutex> lock(ops_mu_);
+    return !ops_.empty();
+}
+
+bool Client::last_stats(uint64_t tag, pcclExtReduceStats_t &out) {
+    std::lock_guard<std::mutex> lock(ops_mu_);
+    const auto it = stats_.find(tag);
+    if (it == stats_.end()) return false;
+    out = it->second;
+    return true;
+}
+
+Client::Launch Client::all_reduce_async(const ReduceRequest &req) {
+    if (!accepted_ || !master_.is_open()) return Launch::NotConnected;
+    std::lock_guard<std::mutex> lock(ops_mu_);
+    if (ops_.count(req.tag)) return Launch::DuplicateTag;
+    Op op;
+    op.revision_at_launch = connection_revision_;
+    const uint64_t rev = op.revision_at_launch;
+    op.future = workers_->submit([this, req, rev] { return run_reduce(req, rev); });
+    ops_.emplace(req.tag, std::move(op));
+    return Launch::Ok;
+}
+
+bool Client::await_reduce(uint64_t tag, ReduceOutcome &out) {
+    Op op;
+    {
+        std::lock_guard<std::mutex> lock(ops_mu_);
+        const auto it = ops_.find(tag);
+        if (it == ops_.end()) return false;
+        op = std::move(it->second);
+    }
+    try {
+        out = op.future.get();
+    } catch (...) {
+        out = ReduceOutcome{};
+    }
+    bool others_running;
+    {
+        std::lock_guard<std::mutex> lock(ops_mu_);
+        ops_.erase(tag);
+        stats_[tag] = out.stats;
+        if (stats_.size() > 4096) stats_.erase(stats_.begin());
+        others_running = !ops_.empty();
+    }
+    if (!out.ok) {
+        // A peer dropped: fetch the new ring before the caller retries.  Only once per
+        // connection revision, and only when no other reduction is still in flight (those
+        // will fail too and the last one to be awaited does the rewiring).
+        std::lock_guard<std::mutex> lock(joint_mu_);
+        if (!others_running && connection_revision_ == op.revision_at_launch && master_.is_open())
+            request_and_establish(false);
+    }
+    return out.ok;
+}
+
+std::shared_ptr<net::MuxSocket> Client::pick_rx(const Uuid &peer, uint64_t seq, int timeout_ms) {
+    std::unique_lock<std::mutex> lock(rx_mu_);
+    const auto deadline = clock_type::now() + std::chrono::milliseconds(timeout_ms);
+    for (;;) {
+        const auto it = rx_pools_.find(peer);
+        if (it != rx_pools_.end() && it->second.size() >= cfg_.pool_size) {
+            auto &s = it->second[seq % cfg_.pool_size];
+            if (s && s->is_open()) return s;
+        }
+        if (interrupted_ || rx_cv_.wait_until(lock, deadline) == std::cv_status::timeout) return nullptr;
+    }
+}
+
+ReduceOutcome Client::run_reduce(const ReduceRequest &req, uint64_t) {
+    ReduceOutcome out;
+    const size_t esz = dtype_size(req.dtype);
+    const auto send_info = device::classify_pointer(req.send), recv_info = device::classify_pointer(req.recv);
+
+    std::vector<Uuid> ring;
+    {
+        std::shared_lock<std::shared_mutex> lock(ring_mu_);
+        ring = ring_;
+    }
+    const auto me = std::find(ring.begin(), ring.end(), uuid_);
+    if (me == ring.end()) return out;
+    const uint32_t world = static_cast<uint32_t>(ring.size()), rank = static_cast<uint32_t>(me - ring.begin());
+    out.world = world;
+
+    device::DeviceReduceArgs dargs;
+    dargs.src = req.send;
+    dargs.dst = req.recv;
+    dargs.count = req.count;
+    dargs.dtype = req.dtype;
+    dargs.op = req.op;
+    dargs.quant = req.quant;
+    dargs.quant_dtype = req.quant_dtype;
+    dargs.rank = rank;
+    dargs.world = world;
+    const bool device_capable = send_info.is_device && recv_info.is_device && plane_->can_reduce(dargs);
+
+    // ---- vote.  The spare top bit of the operator byte tells the master that this peer can
+    // run the operation on the device plane; the master answers with the top bit of the
+    // sequence number when EVERY peer of the group said so.  Masters and peers that do not
+    // know the convention never set either bit, so mixed runs fall back to the TCP ring.
+    C2MCollectiveInitiate vote;
+    vote.tag = req.tag;
+    vote.count = req.count;
+    vote.dtype = req.dtype;
+    vote.op = static_cast<RedOp>(static_cast<uint8_t>(req.op) | (device_capable ? 0x80u : 0u));
+    if (!master_.send_packet(vote)) return out;
+    const auto go = master_.recv_matching<M2CCollectiveCommence>([&](const M2CCollectiveCommence &p) { return p.tag == req.tag; });
+    if (!go) return out;
+    const bool use_device = (go->seq_nr >> 63) != 0;
+    const uint64_t seq = go->seq_nr & ~(1ull << 63);
+    out.stats.seq_nr = seq;
+
+    bool abort_seen = false, aborted = false;
+    auto abort_requested = [&]() {
+        if (abort_seen) return aborted;
+        const auto pkt = master_.recv_matching<M2CCollectiveAbort>([&](const M2CCollectiveAbort &p) { return p.tag == req.tag; }, true);
+        if (pkt) {
+            abort_seen = true;
+            aborted = pkt->aborted;
+        }
+        if (!master_.is_open()) return true;
+        return aborted;
+    };
+
+    bool local_ok = false;
+    std::vector<uint8_t> host_backup;            // in-place rollback for host buffers
+    std::vector<uint8_t> stage_send, stage_recv; // host staging for device buffers on the TCP plane
+    const bool in_place = req.send == req.recv;
+
+    if (use_device && device_capable) {
+        dargs.seq = seq;
+        const auto r = plane_->reduce(dargs, abort_requested);
+        local_ok = r.ok;
+        out.tx_bytes = r.tx_bytes;
+        out.rx_bytes = r.rx_bytes;
+        out.stats.plane = r.plane;
+        out.stats.device_ms = r.device_ms;
+    } else if (use_device) {
+        // cannot happen unless peers disagree about their own capability between vote and run
+        PLOG(ERR) << "device plane was agreed on but is not available locally";
+    } else {
+        out.stats.plane = pcclExtPlaneTcpRing;
+        RingContext ctx;
+        ctx.tag = req.tag;
+        ctx.seq = seq;
+        ctx.rank = rank;
+        ctx.world = world;
+        ctx.frame_bytes = frame_bytes_from_env();
+        ctx.abort_requested = abort_requested;
+        bool wired = true;
+        if (world >= 2) {
+            const Uuid &next = ring[(rank + 1) % world], &prev = ring[(rank + world - 1) % world];
+            {
+                std::lock_guard<std::mutex> lock(tx_mu_);
+                const auto it = tx_pools_.find(next);
+                if (it != tx_pools_.end() && !it->second.empty()) ctx.tx = it->second[seq % it->second.size()];
+            }
+            ctx.rx = pick_rx(prev, seq, 10000);
+            wired = ctx.tx && ctx.rx;
+            if (!wired) PLOG(WARN) << "no usable p2p link for tag " << req.tag;
+        }
+        if (wired) {
+            ReduceArgs a;
+            a.count = req.count;
+            a.dtype = req.dtype;
+            a.op = req.op;
+            a.quant = req.quant;
+            a.quant_dtype = req.quant_dtype;
+            bool staged_ok = true;
+            if (send_info.is_device || recv_info.is_device) {
+                // Device buffers on the TCP plane are staged through host memory, as users of the
+                // reference do by hand (python/examples/nanogpt_diloco/sync_diloco.py:494).
+                stage_recv.resize(req.count * esz);
+                if (send_info.is_device) {
+                    staged_ok = plane_->copy_to_host(stage_recv.data(), req.send, req.count * esz);
+                } else {
+                    std::memcpy(stage_recv.data(), req.send, req.count * esz);
+                }
+                a.src = a.dst = stage_recv.data();
+            } else {
+                a.src = req.send;
+                a.dst = req.recv;
+            }
+            if (staged_ok) {
+                const RingResult r = ring_allreduce(ctx, a, host_backup);
+                local_ok = r.ok;
+                out.tx_bytes = r.tx_bytes;
+                out.rx_bytes = r.rx_bytes;
+            }
+        }
+    }
+
+    // ---- completion handshake: our verdict, then exactly one Abort packet, then Complete
+    C2MCollectiveComplete done;
+    done.tag = req.tag;
+    done.was_aborted = !local_ok;
+    if (!master_.send_packet(done)) return out;
+    if (!abort_seen) {
+        const auto pkt = master_.recv_matching<M2CCollectiveAbort>([&](const M2CCollectiveAbort &p) { return p.tag == req.tag; });
+        if (!pkt) return out;
+        abort_seen = true;
+        aborted = pkt->aborted;
+    }
+    if (!master_.recv_matching<M2CCollectiveComplete>([&](const M2CCollectiveComplete &p) { return p.tag == req.tag; })) return out;
+
+    const bool success = local_ok && !aborted;
+    if (use_device && device_capable && !success && in_place) plane_->restore_input(dargs);
+    if (out.stats.plane == pcclExtPlaneTcpRing) {
+        if (success && !stage_recv.empty()) {
+            if (recv_info.is_device) {
+                if (!plane_->copy_to_device(req.recv, stage_recv.data(), req.count * esz)) return out;
+            } else {
+                std::memcpy(req.recv, stage_recv.data(), req.count * esz);
+            }
+        } else if (!success && stage_recv.empty() && in_place && local_ok && !host_backup.empty()) {
+            // finished locally but another peer aborted: the caller will retry with this
+            // buffer as input, so it must hold the original values again
+            std::memcpy(req.recv, host_backup.data(), host_backup.size());
+        }
+    }
+    out.ok = success;
+    return out;
+}
+
+} // namespace pccl::client

@@ -1,0 +1,163 @@
+// A peer of a CCoIP run: master link, P2P links to the ring neighbours, shared-state server,
+// bandwidth-benchmark server, asynchronous all-reduce engine and the device data plane.
+//
+// Behavioural specification: reference ccoip/src/cpp/ccoip_client_handler.cpp (connect :46-280,
+// P2P establishment :282-314,831-1002, shared state :344-638,1022-1164, topology optimisation :640-736,
+// all-reduce :1187-1396) and ccoip/src/cpp/ccoip_client_state.cpp:184-232.  The structure is new:
+// one class, condition-variable based waiting, posted zero-copy sends, a pluggable device plane.
+#pragma once
+#include <atomic>
+#include <condition_variable>
+#include <future>
+#include <map>
+#include <memory>
+#include <mutex>
+#include <optional>
+#include <shared_mutex>
+#include <unordered_map>
+#include <vector>
+
+#include "../device/plane.hpp"
+#include "../net/blocking_socket.hpp"
+#include "../net/mux_socket.hpp"
+#include "../net/queued_socket.hpp"
+#include "../util/threadpool.hpp"
+#include "../util/uuid.hpp"
+#include "../wire/packets.hpp"
+#include "pccl.h"
+
+namespace pccl::client {
+
+struct ClientConfig {
+    ccoip_socket_address_t master{};
+    uint32_t peer_group = 0;
+    uint32_t pool_size = 1;
+    bool explicit_addresses = false;
+    ccoip_socket_address_t adv_p2p{}, adv_ss{}, adv_bm{};
+    uint16_t p2p_port = CCOIP_PROTOCOL_PORT_P2P, ss_port = CCOIP_PROTOCOL_PORT_SHARED_STATE,
+             bm_port = CCOIP_PROTOCOL_PORT_BANDWIDTH_BENCHMARK;
+};
+
+struct SharedEntry {
+    std::string key;
+    void *data = nullptr;
+    uint64_t count = 0;
+    wire::DType dtype = wire::DType::U8;
+    bool on_device = false;
+    bool allow_content_inequality = false;
+    size_t bytes() const { return count * wire::dtype_size(dtype); }
+};
+
+struct SharedStateArgs {
+    uint64_t revision = 0;
+    std::vector<SharedEntry> entries;
+    wire::SyncStrategy strategy = wire::SyncStrategy::EnforcePopular;
+};
+
+struct ReduceRequest {
+    const void *send = nullptr;
+    void *recv = nullptr;
+    uint64_t count = 0;
+    wire::DType dtype = wire::DType::F32;
+    wire::RedOp op = wire::RedOp::Sum;
+    wire::QuantAlgo quant = wire::QuantAlgo::None;
+    wire::DType quant_dtype = wire::DType::U8;
+    uint64_t tag = 0;
+};
+
+struct ReduceOutcome {
+    bool ok = false;
+    uint32_t world = 0;
+    uint64_t tx_bytes = 0, rx_bytes = 0;
+    pcclExtReduceStats_t stats{};
+};
+
+class Client {
+public:
+    explicit Client(const ClientConfig &cfg);
+    ~Client();
+
+    bool connect();
+    bool interrupt();
+    bool join();
+    bool is_connected() const { return accepted_.load(); }
+
+    // joint operations (one caller thread at a time)
+    bool update_topology();                 // accept pending peers + rewire
+    bool are_peers_pending(bool &pending);
+    bool optimize_topology();
+    bool sync_shared_state(SharedStateArgs &state, uint64_t &tx_bytes, uint64_t &rx_bytes);
+
+    // asynchronous reductions (any thread)
+    enum class Launch { Ok, DuplicateTag, NotConnected };
+    Launch all_reduce_async(const ReduceRequest &req);
+    bool await_reduce(uint64_t tag, ReduceOutcome &out);
+    bool any_reduce_running();
+    bool last_stats(uint64_t tag, pcclExtReduceStats_t &out);
+
+    uint64_t global_world() const { return global_world_; }
+    uint64_t local_world() const { return local_world_; }
+    uint64_t num_groups() const { return num_groups_; }
+    uint64_t largest_group() const { return largest_group_; }
+    const Uuid &uuid() const { return uuid_; }
+    device::Plane &plane() { return *plane_; }
+
+private:
+    enum class Establish { Success, Retry, Failed };
+    using Pool = std::vector<std::shared_ptr<net::MuxSocket>>;
+
+    bool request_and_establish(bool accept_new_peers);
+    Establish establish_round();
+    bool dial_peer(const wire::PeerEndpoint &peer);
+    void on_p2p_accept(std::unique_ptr<net::BlockingSocket> sock);
+    void on_shared_state_accept(std::unique_ptr<net::BlockingSocket> sock);
+    void on_benchmark_accept(std::unique_ptr<net::BlockingSocket> sock);
+    ReduceOutcome run_reduce(const ReduceRequest &req, uint64_t revision_at_launch);
+    std::shared_ptr<net::MuxSocket> pick_rx(const Uuid &peer, uint64_t seq, int timeout_ms);
+    bool run_benchmark(const wire::BenchmarkRequest &req, double &mbits, bool &busy);
+
+    ClientConfig cfg_;
+    net::QueuedSocket master_;
+    net::Listener p2p_listener_, ss_listener_, bm_listener_;
+    std::unique_ptr<device::Plane> plane_;
+
+    Uuid uuid_;
+    std::atomic<bool> accepted_{false}, interrupted_{false}, started_{false};
+    std::atomic<uint64_t> global_world_{0}, local_world_{0}, num_groups_{0}, largest_group_{0};
+    std::atomic<uint64_t> connection_revision_{0};
+
+    std::mutex joint_mu_; // serialises joint (phase changing) calls and re-establishment
+
+    std::shared_mutex ring_mu_;
+    std::vector<Uuid> ring_;
+
+    std::mutex tx_mu_;
+    std::unordered_map<Uuid, Pool> tx_pools_;
+    std::mutex rx_mu_;
+    std::condition_variable rx_cv_;
+    std::unordered_map<Uuid, Pool> rx_pools_;
+
+    struct Op {
+        std::future<ReduceOutcome> future;
+        uint64_t revision_at_launch = 0;
+    };
+    std::mutex ops_mu_;
+    std::map<uint64_t, Op> ops_;
+    std::map<uint64_t, pcclExtReduceStats_t> stats_;
+    std::unique_ptr<ThreadPool> workers_;
+
+    // shared-state serving
+    std::mutex ss_mu_;
+    bool ss_serving_ = false;
+    SharedStateArgs ss_snapshot_;
+    std::atomic<uint64_t> ss_tx_bytes_{0};
+    std::unique_ptr<ThreadPool> ss_workers_;
+
+    // benchmark serving
+    std::mutex bm_mu_;
+    Uuid bm_owner_;
+    int bm_active_ = 0;
+    std::unique_ptr<ThreadPool> bm_workers_;
+};
+
+} // namespace pccl::client

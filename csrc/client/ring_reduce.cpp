@@ -1,0 +1,243 @@
+#include "ring_reduce.hpp"
+
+#include <cstring>
+
+#include "../kernels/cpu/reduce.hpp"
+#include "../util/log.hpp"
+
+namespace pccl::client {
+
+using wire::DType;
+using wire::QuantAlgo;
+using wire::RedOp;
+
+namespace {
+
+constexpr int kPollMs = 2;
+
+struct Stage {
+    const RingContext &ctx;
+    RingResult &res;
+    bool failed = false;
+
+    bool check_abort() {
+        if (ctx.abort_requested && ctx.abort_requested()) {
+            res.aborted_by_master = true;
+            failed = true;
+        }
+        if (!ctx.tx->is_open() || !ctx.rx->is_open()) failed = true;
+        return failed;
+    }
+
+    // Blocks until the ticket is done, polling for aborts.  After an abort the ticket is still
+    // awaited (the successor's RX thread keeps draining, or the socket dies) because the TX
+    // thread reads from caller memory.
+    bool finish_send(const std::shared_ptr<net::SendTicket> &ticket) {
+        for (;;) {
+            const int st = ticket->wait_for(kPollMs);
+            if (st == 1) return true;
+            if (st == -1) {
+                failed = true;
+                return false;
+            }
+            if (check_abort() && res.aborted_by_master) {
+                // keep waiting for the ticket, but bounded: a wedged link is cut
+                for (int i = 0; i < 5000; ++i) {
+                    const int s2 = ticket->wait_for(kPollMs);
+                    if (s2 != 0) return false;
+                }
+                ctx.tx->interrupt();
+                ticket->wait_for(1000);
+                return false;
+            }
+        }
+    }
+
+    // Receives exactly `bytes` payload bytes, handing every frame to `sink(offset, data, n)`.
+    template <typename Sink> bool receive(size_t bytes, Sink sink) {
+        size_t got = 0;
+        bool first = true;
+        while (got < bytes || (first && bytes == 0)) {
+            auto frame = ctx.rx->recv_frame(ctx.tag, ctx.seq, kPollMs);
+            if (!frame) {
+                if (check_abort()) return false;
+                // a frame may have arrived between the timeout and the liveness check
+                if (!ctx.rx->is_open()) {
+                    frame = ctx.rx->recv_frame(ctx.tag, ctx.seq, 0);
+                    if (!frame) {
+                        failed = true;
+                        return false;
+                    }
+                } else {
+                    continue;
+                }
+            }
+            first = false;
+            if (frame->size() > bytes - got) {
+                PLOG(ERR) << "peer sent more bytes than the chunk holds";
+                failed = true;
+                return false;
+            }
+            sink(got, frame->data(), frame->size());
+            got += frame->size();
+            res.rx_bytes += frame->size();
+        }
+        return true;
+    }
+
+    bool exchange_meta(const cpu::QuantParams &mine, cpu::QuantParams &theirs) {
+        const auto pkt = cpu::to_wire(mine, ctx.tag);
+        if (!ctx.tx->send_packet(ctx.tag, ctx.seq, pkt)) {
+            failed = true;
+            return false;
+        }
+        res.tx_bytes += 8 + 2 + pkt.wire_size();
+        for (;;) {
+            auto got = ctx.rx->recv_packet<wire::P2PDequantMeta>(ctx.tag, ctx.seq, kPollMs);
+            if (got) {
+                res.rx_bytes += 8 + 2 + got->wire_size();
+                if (!cpu::from_wire(*got, theirs)) {
+                    failed = true;
+                    return false;
+                }
+                return true;
+            }
+            if (check_abort()) return false;
+        }
+    }
+};
+
+} // namespace
+
+RingResult ring_allreduce(const RingContext &ctx, const ReduceArgs &a, std::vector<uint8_t> &backup) {
+    RingResult res;
+    const size_t esz = wire::dtype_size(a.dtype);
+    auto *dst = static_cast<uint8_t *>(a.dst);
+    const bool in_place = a.src == a.dst;
+
+    if (ctx.world < 2) {
+        if (!in_place) std::memcpy(dst, a.src, a.count * esz);
+        res.ok = true;
+        return res;
+    }
+
+    // In-place operation destroys the input while it runs; keep a copy to roll back to.
+    backup.clear();
+    if (in_place)
+        backup.assign(dst, dst + a.count * esz);
+    else
+        std::memcpy(dst, a.src, a.count * esz);
+    auto fail = [&]() {
+        if (in_place) std::memcpy(dst, backup.data(), backup.size());
+        res.ok = false;
+        return res;
+    };
+
+    const bool quantised = a.quant != QuantAlgo::None;
+    const bool block_format = a.quant == QuantAlgo::BlockMinMax || a.quant == QuantAlgo::BlockFp8;
+    cpu::QuantParams qp;
+    qp.algo = a.quant;
+    qp.value_dtype = a.dtype;
+    qp.code_dtype = a.quant_dtype;
+    const size_t qsz = quantised && !block_format ? wire::dtype_size(a.quant_dtype) : 1;
+    // frames must carry whole elements so they can be consumed as they arrive
+    size_t frame_bytes = ctx.frame_bytes;
+    frame_bytes -= frame_bytes % 64;
+    if (frame_bytes == 0) frame_bytes = 64;
+
+    Stage st{ctx, res};
+    const uint32_t W = ctx.world, r = ctx.rank;
+    std::vector<uint8_t> tx_codes, rx_codes;
+
+    // ---------------- reduce-scatter
+    for (uint32_t step = 0; step + 1 < W; ++step) {
+        const uint32_t tx_chunk = (r + W - step) % W, rx_chunk = (r + W - step - 1) % W;
+        uint64_t tb, te, rb, re;
+        chunk_bounds(a.count, W, tx_chunk, tb, te);
+        chunk_bounds(a.count, W, rx_chunk, rb, re);
+        const uint64_t tx_n = te - tb, rx_n = re - rb;
+
+        if (!quantised) {
+            auto ticket = ctx.tx->send_bytes(ctx.tag, ctx.seq, dst + tb * esz, tx_n * esz, frame_bytes);
+            res.tx_bytes += tx_n * esz;
+            const bool rx_ok = st.receive(rx_n * esz, [&](size_t off, const uint8_t *data, size_t n) {
+                cpu::reduce_inplace(dst + rb * esz + off, data, n / esz, a.dtype, a.op);
+            });
+            const bool tx_ok = st.finish_send(ticket);
+            if (!rx_ok || !tx_ok) return fail();
+            continue;
+        }
+
+        cpu::QuantParams mine = qp, theirs = qp;
+        cpu::quant_analyze(dst + tb * esz, tx_n, mine);
+        tx_codes.resize(cpu::quantized_size(mine, tx_n));
+        cpu::quantize(dst + tb * esz, tx_codes.data(), tx_n, mine);
+        if (!st.exchange_meta(mine, theirs)) return fail();
+        auto ticket = ctx.tx->send_bytes(ctx.tag, ctx.seq, tx_codes.data(), tx_codes.size(), frame_bytes);
+        res.tx_bytes += tx_codes.size();
+        const size_t rx_bytes = cpu::quantized_size(theirs, rx_n);
+        bool rx_ok;
+        if (block_format) {
+            rx_codes.resize(rx_bytes);
+            rx_ok = st.receive(rx_bytes, [&](size_t off, const uint8_t *data, size_t n) { std::memcpy(rx_codes.data() + off, data, n); });
+            if (rx_ok) cpu::dequantize_reduce(dst + rb * esz, rx_codes.data(), rx_n, theirs, a.op);
+        } else {
+            rx_ok = st.receive(rx_bytes, [&](size_t off, const uint8_t *data, size_t n) {
+                cpu::dequantize_reduce(dst + (rb + off / qsz) * esz, data, n / qsz, theirs, a.op);
+            });
+        }
+        const bool tx_ok = st.finish_send(ticket);
+        if (!rx_ok || !tx_ok) return fail();
+    }
+
+    // ---------------- all-gather
+    cpu::QuantParams forwarded = qp; // metadata that travels with the codes we forward
+    for (uint32_t step = 0; step + 1 < W; ++step) {
+        const uint32_t tx_chunk = (r + 1 + W - step) % W, rx_chunk = (r + W - step) % W;
+        uint64_t tb, te, rb, re;
+        chunk_bounds(a.count, W, tx_chunk, tb, te);
+        chunk_bounds(a.count, W, rx_chunk, rb, re);
+        const uint64_t tx_n = te - tb, rx_n = re - rb;
+
+        if (!quantised) {
+            auto ticket = ctx.tx->send_bytes(ctx.tag, ctx.seq, dst + tb * esz, tx_n * esz, frame_bytes);
+            res.tx_bytes += tx_n * esz;
+            const bool rx_ok = st.receive(rx_n * esz, [&](size_t off, const uint8_t *data, size_t n) {
+                std::memcpy(dst + rb * esz + off, data, n);
+            });
+            const bool tx_ok = st.finish_send(ticket);
+            if (!rx_ok || !tx_ok) return fail();
+            continue;
+        }
+
+        if (step == 0) {
+            // Quantise the chunk this peer owns exactly once and adopt the decoded values, so
+            // the owner holds what everybody else will decode.
+            forwarded = qp;
+            cpu::quant_analyze(dst + tb * esz, tx_n, forwarded);
+            tx_codes.resize(cpu::quantized_size(forwarded, tx_n));
+            cpu::quantize(dst + tb * esz, tx_codes.data(), tx_n, forwarded);
+            cpu::dequantize_reduce(dst + tb * esz, tx_codes.data(), tx_n, forwarded, RedOp::Set);
+        }
+        cpu::QuantParams theirs = qp;
+        if (!st.exchange_meta(forwarded, theirs)) return fail();
+        auto ticket = ctx.tx->send_bytes(ctx.tag, ctx.seq, tx_codes.data(), tx_codes.size(), frame_bytes);
+        res.tx_bytes += tx_codes.size();
+        const size_t rx_bytes = cpu::quantized_size(theirs, rx_n);
+        rx_codes.resize(rx_bytes);
+        const bool rx_ok =
+            st.receive(rx_bytes, [&](size_t off, const uint8_t *data, size_t n) { std::memcpy(rx_codes.data() + off, data, n); });
+        const bool tx_ok = st.finish_send(ticket);
+        if (!rx_ok || !tx_ok) return fail();
+        cpu::dequantize_reduce(dst + rb * esz, rx_codes.data(), rx_n, theirs, RedOp::Set);
+        // next step forwards the received codes and metadata unchanged (no second quantisation)
+        tx_codes.swap(rx_codes);
+        forwarded = theirs;
+    }
+
+    if (a.op == RedOp::Avg) cpu::finalize_avg(dst, a.count, a.dtype, W);
+    res.ok = true;
+    return res;
+}
+
+} // namespace pccl::client

@@ -1,0 +1,57 @@
+// Pipelined ring all-reduce over the multiplexed TCP links: reduce-scatter followed by all-gather,
+// W-1 steps each.  Algorithmic contract as in the reference (ccoip/src/cpp/reduce.cpp:51-67 chunking,
+// :609-662 reduce-scatter, :673-769 all-gather incl. the "owner adopts D(Q(x))" rule that keeps
+// all peers bit-identical under quantisation, :782 AVG finalisation, :572-580 source restore on
+// abort).  The implementation differs: sends are zero-copy tickets on the TX thread, received
+// frames are reduced straight out of the frame buffer, and waiting is done on condition
+// variables with a short timeout that doubles as the abort-poll interval.
+#pragma once
+#include <functional>
+#include <memory>
+#include <vector>
+
+#include "../kernels/cpu/quantize.hpp"
+#include "../net/mux_socket.hpp"
+#include "../wire/packets.hpp"
+
+namespace pccl::client {
+
+struct RingContext {
+    uint64_t tag = 0, seq = 0;
+    uint32_t rank = 0, world = 1;
+    std::shared_ptr<net::MuxSocket> tx; // to ring successor
+    std::shared_ptr<net::MuxSocket> rx; // from ring predecessor
+    size_t frame_bytes = 2u << 20;
+    // returns true when the master told us to abort this operation
+    std::function<bool()> abort_requested;
+};
+
+struct RingResult {
+    bool ok = false;
+    bool aborted_by_master = false;
+    uint64_t tx_bytes = 0, rx_bytes = 0;
+};
+
+struct ReduceArgs {
+    const void *src = nullptr;
+    void *dst = nullptr;
+    uint64_t count = 0;
+    wire::DType dtype = wire::DType::F32;
+    wire::RedOp op = wire::RedOp::Sum;
+    wire::QuantAlgo quant = wire::QuantAlgo::None;
+    wire::DType quant_dtype = wire::DType::U8;
+};
+
+// `backup` receives a copy of the input when the operation is in place (src == dst).  On a local
+// failure the input is restored from it before returning; on local success it is left filled so
+// the caller can still roll back if the master later reports that another peer aborted.
+RingResult ring_allreduce(const RingContext &ctx, const ReduceArgs &args, std::vector<uint8_t> &backup);
+
+// chunk i of `count` elements split over `world` owners: [begin, end)
+inline void chunk_bounds(uint64_t count, uint32_t world, uint32_t i, uint64_t &begin, uint64_t &end) {
+    const uint64_t base = count / world, rem = count % world;
+    begin = i * base + (i < rem ? i : rem);
+    end = begin + base + (i < rem ? 1 : 0);
+}
+
+} // namespace pccl::client

@@ -1,0 +1,92 @@
+// Device data plane of a communicator: everything that touches CUDA.
+//
+// The reference library has no device data plane (its all-reduce asserts host memory,
+// python/framework/pccl/_pccl.py:617; CUDA is only used to hash and stage shared-state tensors,
+// ccoip/src/cpp/ccoip_client_handler.cpp:537-550,1140-1155).  This class is what makes peers that share
+// one NVLink/NVSwitch domain reduce on the GPUs directly:
+//
+//   * every communicator owns an "arena": device memory created with the CUDA VMM API and
+//     exported as a POSIX file descriptor; peers on the same host fetch the descriptor over an
+//     abstract unix-domain socket named after the peer UUID (SCM_RIGHTS) and map it;
+//   * the arena starts with a flag page used for cross-GPU barriers (values are derived from the
+//     master-issued sequence number, so they only ever grow and stale values are harmless),
+//     followed by staging slots;
+//   * all-reduce = one kernel launch per rank (csrc/kernels/cuda/allreduce_p2p.cu).
+//
+// Everything here degrades gracefully: without a GPU, or with peers on other hosts, the
+// communicator uses the TCP ring and stages device buffers through pinned host memory.
+#pragma once
+#include <cstddef>
+#include <cstdint>
+#include <functional>
+#include <memory>
+#include <string>
+#include <vector>
+
+#include "../util/uuid.hpp"
+#include "../wire/packets.hpp"
+#include "pccl.h"
+
+namespace pccl::device {
+
+struct PointerInfo {
+    bool is_device = false;
+    int device = -1;
+};
+PointerInfo classify_pointer(const void *p);
+bool cuda_runtime_usable(); // a driver and at least one device are present
+
+struct DeviceReduceArgs {
+    const void *src = nullptr;
+    void *dst = nullptr;
+    uint64_t count = 0;
+    wire::DType dtype = wire::DType::F32;
+    wire::RedOp op = wire::RedOp::Sum;
+    wire::QuantAlgo quant = wire::QuantAlgo::None;
+    wire::DType quant_dtype = wire::DType::U8;
+    uint64_t seq = 0;
+    uint32_t rank = 0, world = 1;
+};
+
+struct DeviceReduceResult {
+    bool ok = false;
+    bool aborted = false;
+    pcclExtDataPlane_t plane = pcclExtPlaneNone;
+    float device_ms = 0;
+    uint64_t tx_bytes = 0, rx_bytes = 0;
+};
+
+class Plane {
+public:
+    static std::unique_ptr<Plane> create(); // never null; may be an inert object
+    virtual ~Plane() = default;
+
+    // Binds the plane to a peer identity and opens the rendezvous socket.
+    virtual void start(const Uuid &self) = 0;
+    virtual void stop() = 0;
+
+    // Called after every successful topology round with the new ring of the caller's group.
+    // Maps the arenas of all ring members that live on this host.
+    virtual void on_ring_changed(const std::vector<Uuid> &ring) = 0;
+
+    // True when this peer could run the described reduction on the device plane
+    // (buffers on a GPU, every ring member mapped, operator/type supported).
+    virtual bool can_reduce(const DeviceReduceArgs &args) = 0;
+
+    // Runs the reduction; `abort_requested` is polled while the kernel runs.
+    virtual DeviceReduceResult reduce(const DeviceReduceArgs &args, const std::function<bool()> &abort_requested) = 0;
+
+    // After a failed in-place reduction: puts the original input back into args.dst.
+    virtual bool restore_input(const DeviceReduceArgs &args) = 0;
+
+    // Stream-ordered staging helpers for the TCP fallback and for shared state.
+    virtual bool copy_to_host(void *host_dst, const void *dev_src, size_t bytes) = 0;
+    virtual bool copy_to_device(void *dev_dst, const void *host_src, size_t bytes) = 0;
+    // Content hash of a device buffer; hash_type as on the wire.
+    virtual bool hash_device(const void *dev_ptr, size_t bytes, wire::HashType type, uint64_t &out) = 0;
+
+    virtual void *symmetric_alloc(size_t bytes) = 0;
+    virtual bool symmetric_free(void *ptr) = 0;
+};
+
+} // namespace pccl::device

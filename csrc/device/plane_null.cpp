@@ -1,0 +1,29 @@
+// Inert device plane used when the library is built without CUDA (PCCL_NO_CUDA).
+#include "plane.hpp"
+
+namespace pccl::device {
+
+#ifdef PCCL_NO_CUDA
+namespace {
+class NullPlane final : public Plane {
+public:
+    void start(const Uuid &) override {}
+    void stop() override {}
+    void on_ring_changed(const std::vector<Uuid> &) override {}
+    bool can_reduce(const DeviceReduceArgs &) override { return false; }
+    DeviceReduceResult reduce(const DeviceReduceArgs &, const std::function<bool()> &) override { return {}; }
+    bool restore_input(const DeviceReduceArgs &) override { return false; }
+    bool copy_to_host(void *, const void *, size_t) override { return false; }
+    bool copy_to_device(void *, const void *, size_t) override { return false; }
+    bool hash_device(const void *, size_t, wire::HashType, uint64_t &) override { return false; }
+    void *symmetric_alloc(size_t) override { return nullptr; }
+    bool symmetric_free(void *) override { return false; }
+};
+} // namespace
+
+PointerInfo classify_pointer(const void *) { return {}; }
+bool cuda_runtime_usable() { return false; }
+std::unique_ptr<Plane> Plane::create() { return std::make_unique<NullPlane>(); }
+#endif
+
+} // namespace pccl::device

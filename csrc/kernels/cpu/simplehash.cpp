@@ -1,0 +1,109 @@
+#include <algorithm>
+#include <cstring>
+#include <thread>
+#include <vector>
+
+#include "hash.hpp"
+
+namespace pccl::cpu {
+
+namespace {
+
+// One shuffle tree over 32 lanes: lane i takes lane i+offset, lanes without a partner combine
+// with themselves (that is what __shfl_down_sync hands back); only lane 0 is read afterwards.
+uint32_t warp_fold(const uint32_t *lanes) {
+    uint32_t v[32];
+    std::memcpy(v, lanes, sizeof v);
+    for (int offset = 16; offset > 0; offset >>= 1) {
+        uint32_t next[32];
+        for (int i = 0; i < 32; ++i) next[i] = hash_combine(v[i], i + offset < 32 ? v[i + offset] : v[i]);
+        std::memcpy(v, next, sizeof v);
+    }
+    return v[0];
+}
+
+uint32_t block_partial(const uint32_t *words, uint64_t vec_begin, uint64_t vec_end) {
+    uint32_t per_thread[kSimpleHashThreads];
+    for (uint32_t t = 0; t < kSimpleHashThreads; ++t) {
+        uint32_t h = 0;
+        for (uint64_t i = vec_begin + t; i < vec_end; i += kSimpleHashThreads) {
+            const uint32_t *w = words + i * 4;
+            h = hash_combine(h, w[0]);
+            h = hash_combine(h, w[1]);
+            h = hash_combine(h, w[2]);
+            h = hash_combine(h, w[3]);
+        }
+        per_thread[t] = h;
+    }
+    return simplehash_block_fold(per_thread);
+}
+
+} // namespace
+
+uint32_t simplehash_block_fold(const uint32_t *thread_values) {
+    uint32_t warp_results[32] = {0};
+    for (int w = 0; w < static_cast<int>(kSimpleHashThreads / 32); ++w) warp_results[w] = warp_fold(thread_values + w * 32);
+    return warp_fold(warp_results);
+}
+
+uint64_t simplehash(const void *data, size_t n_bytes) {
+    if (n_bytes == 0) return 0;
+    const auto *bytes = static_cast<const uint8_t *>(data);
+    const size_t n_words = n_bytes / 4, n_vec = n_words / 4;
+    uint32_t result = 0;
+
+    // unaligned input is legal on the host: go through a word view only when it is aligned
+    std::vector<uint32_t> aligned_copy;
+    const uint32_t *words = reinterpret_cast<const uint32_t *>(bytes);
+    if (reinterpret_cast<uintptr_t>(bytes) % 4 != 0) {
+        aligned_copy.resize(n_words);
+        std::memcpy(aligned_copy.data(), bytes, n_words * 4);
+        words = aligned_copy.data();
+    }
+
+    if (n_vec > 0) {
+        const uint32_t grid = static_cast<uint32_t>(
+            std::min<uint64_t>((n_vec + kSimpleHashThreads - 1) / kSimpleHashThreads, kSimpleHashMaxBlocks));
+        // the device kernel does this arithmetic in 32 bits
+        const uint32_t total_vec = static_cast<uint32_t>(n_vec);
+        const uint32_t per_block = (total_vec + grid - 1) / grid;
+        std::vector<uint32_t> partial(grid, 0);
+        auto run_blocks = [&](uint32_t first, uint32_t last) {
+            for (uint32_t b = first; b < last; ++b) {
+                const uint64_t begin = static_cast<uint64_t>(b) * per_block;
+                const uint64_t end = std::min<uint64_t>(begin + per_block, total_vec);
+                partial[b] = begin < end ? block_partial(words, begin, end) : simplehash_block_fold(std::vector<uint32_t>(kSimpleHashThreads, 0).data());
+            }
+        };
+        unsigned n_threads = 1;
+        if (n_bytes >= (8u << 20)) n_threads = std::max(1u, std::min(16u, std::thread::hardware_concurrency() / 2));
+        if (n_threads <= 1 || grid < n_threads) {
+            run_blocks(0, grid);
+        } else {
+            std::vector<std::thread> pool;
+            for (unsigned t = 0; t < n_threads; ++t) {
+                const uint32_t first = static_cast<uint32_t>(static_cast<uint64_t>(grid) * t / n_threads);
+                const uint32_t last = static_cast<uint32_t>(static_cast<uint64_t>(grid) * (t + 1) / n_threads);
+                pool.emplace_back(run_blocks, first, last);
+            }
+            for (auto &th : pool) th.join();
+        }
+        // final pass: 256 threads stride over the partials
+        uint32_t per_thread[kSimpleHashThreads];
+        for (uint32_t t = 0; t < kSimpleHashThreads; ++t) {
+            uint32_t h = 0;
+            for (uint32_t i = t; i < grid; i += kSimpleHashThreads) h = hash_combine(h, partial[i]);
+            per_thread[t] = h;
+        }
+        result = simplehash_block_fold(per_thread);
+    }
+    for (size_t w = n_vec * 4; w < n_words; ++w) result = hash_combine(result, words[w]);
+    if (const size_t tail = n_bytes % 4) {
+        uint32_t last = 0;
+        for (size_t i = 0; i < tail; ++i) last |= static_cast<uint32_t>(bytes[n_words * 4 + i]) << (8 * i);
+        result = hash_combine(result, last);
+    }
+    return result;
+}
+
+} // namespace pccl::cpu

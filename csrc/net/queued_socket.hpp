@@ -1,0 +1,82 @@
+// Client side of the master link.  A receive thread parks complete frames in an ordered inbox;
+// any number of consumer threads pick frames by packet type and, optionally, by a predicate on
+// the decoded packet (for example "the Commence packet for MY tag") without disturbing the order
+// of the frames they skip.  Behaviour model: reference tinysockets QueuedSocket
+// (tinysockets/src/queued_client_socket.cpp:28-424).
+#pragma once
+#include <atomic>
+#include <condition_variable>
+#include <functional>
+#include <list>
+#include <mutex>
+#include <optional>
+#include <thread>
+#include <vector>
+
+#include "../wire/packets.hpp"
+#include "addr.hpp"
+
+namespace pccl::net {
+
+class QueuedSocket {
+public:
+    explicit QueuedSocket(const ccoip_socket_address_t &remote) : remote_(remote) {}
+    ~QueuedSocket();
+    QueuedSocket(const QueuedSocket &) = delete;
+    QueuedSocket &operator=(const QueuedSocket &) = delete;
+
+    bool connect();
+    bool run(); // starts the receive thread
+    bool interrupt();
+    void join();
+    bool is_open() const { return open_.load(); }
+
+    template <typename P> bool send_packet(const P &pkt) {
+        const auto frame = wire::encode_frame(pkt);
+        return send_frame(frame);
+    }
+
+    template <typename P> std::optional<P> recv_packet(bool no_wait = false) {
+        return recv_matching<P>([](const P &) { return true; }, no_wait);
+    }
+
+    // Returns the oldest queued packet of type P for which pred holds.  Blocks (unless no_wait)
+    // until one arrives or the connection dies.
+    template <typename P, typename Pred> std::optional<P> recv_matching(Pred pred, bool no_wait = false) {
+        std::unique_lock<std::mutex> lock(mu_);
+        for (;;) {
+            for (auto it = inbox_.begin(); it != inbox_.end(); ++it) {
+                if (it->id != P::id) continue;
+                wire::Reader r(it->payload.data(), it->payload.size());
+                P pkt;
+                if (!pkt.read(r)) {
+                    inbox_.erase(it); // undecodable frame: drop it, report failure
+                    return std::nullopt;
+                }
+                if (!pred(pkt)) continue;
+                inbox_.erase(it);
+                return pkt;
+            }
+            if (no_wait || !open_) return std::nullopt;
+            cv_.wait(lock);
+        }
+    }
+
+private:
+    struct Frame {
+        uint16_t id;
+        std::vector<uint8_t> payload;
+    };
+    bool send_frame(const std::vector<uint8_t> &frame);
+    void rx_loop();
+
+    ccoip_socket_address_t remote_;
+    int fd_ = -1;
+    std::atomic<bool> open_{false};
+    std::thread rx_thread_;
+    std::mutex mu_, send_mu_;
+    std::condition_variable cv_;
+    std::list<Frame> inbox_;
+};
+
+} // namespace pccl::net

@@ -1,0 +1,363 @@
+/*
+ * pccl.h -- public C99 interface of the B200-native PCCL build.
+ *
+ * The types, enumerator values and function signatures in the "core" part of this header are
+ * ABI-compatible with the reference library (reference: include/pccl.h:22-458 and
+ * ccoip/public_include/ccoip_inet.h:13-35), so a program written against the reference can be
+ * recompiled against this header unchanged.  Differences in behaviour:
+ *
+ *   - send/recv buffers and shared-state tensors may be CUDA device pointers.  Peers that share
+ *     one NVLink/NVSwitch domain then reduce with sm_100a kernels that read and write each
+ *     other's memory directly; everything else falls back to the CCoIP TCP ring.
+ *   - pcclFloat16 / pcclBFloat16 / pcclInt16 have their real element size (2 bytes) in
+ *     shared-state bookkeeping (the reference computes 0, reference: src/pccl.cpp:525-543).
+ *   - additional quantisation algorithms and a few extension entry points, all declared in the
+ *     "extensions" part at the bottom and all prefixed so they cannot collide.
+ */
+#ifndef PCCL_H_
+#define PCCL_H_
+
+#ifdef __cplusplus
+#include <cstddef>
+#include <cstdint>
+#else
+#include <stdbool.h>
+#include <stddef.h>
+#include <stdint.h>
+#endif
+
+#if defined(_MSC_VER)
+#define PCCL_EXPORT __declspec(dllexport)
+#else
+#define PCCL_EXPORT __attribute__((visibility("default")))
+#endif
+
+/* Marks pointer parameters that may be NULL. */
+#define PCCL_NULLABLE
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ------------------------------------------------------------------------------------------- */
+/* Network address types (layout identical to reference ccoip_inet.h)                           */
+/* ------------------------------------------------------------------------------------------- */
+
+typedef enum ccoip_inet_protocol_t { inetIPv4, inetIPv6 } ccoip_inet_protocol_t;
+
+typedef struct ccoip_ipv4_address_t {
+    uint8_t data[4];
+} ccoip_ipv4_address_t;
+
+typedef struct ccoip_ipv6_address_t {
+    uint8_t data[16];
+} ccoip_ipv6_address_t;
+
+typedef struct ccoip_inet_address_t {
+    ccoip_inet_protocol_t protocol;
+    ccoip_ipv4_address_t ipv4;
+    ccoip_ipv6_address_t ipv6;
+} ccoip_inet_address_t;
+
+typedef struct ccoip_socket_address_t {
+    ccoip_inet_address_t inet;
+    uint16_t port;
+} ccoip_socket_address_t;
+
+/* Default ports (reference: ccoip/public_include/ccoip.h:11-29). */
+#define CCOIP_PROTOCOL_PORT_MASTER 48148
+#define CCOIP_PROTOCOL_PORT_SHARED_STATE 48149
+#define CCOIP_PROTOCOL_PORT_P2P 48150
+#define CCOIP_PROTOCOL_PORT_BANDWIDTH_BENCHMARK 48151
+
+/* ------------------------------------------------------------------------------------------- */
+/* Core enums                                                                                   */
+/* ------------------------------------------------------------------------------------------- */
+
+typedef enum pcclResult_t {
+    pcclSuccess = 0,
+    pcclNotInitialized = 1,
+    pcclInternalError = 2,
+    pcclInvalidArgument = 3,
+    pcclInvalidUsage = 4,
+    pcclTooFewPeers = 5,
+    pcclMasterConnectionFailed = 6,
+    pcclRankConnectionFailed = 7,
+    pcclRankConnectionLost = 8,
+    pcclNoSharedStateAvailable = 9,
+    pcclPendingAsyncOps = 10,
+    pcclUpdateTopologyFailed = 11,
+    pcclTopologyOptimizationFailed = 12
+} pcclResult_t;
+
+typedef enum pcclDataType_t {
+    pcclUint8 = 0,
+    pcclInt8 = 1,
+    pcclInt16 = 2,
+    pcclUint16 = 3,
+    pcclUint32 = 4,
+    pcclInt32 = 5,
+    pcclUint64 = 6,
+    pcclInt64 = 7,
+    pcclFloat16 = 8,
+    pcclBFloat16 = 9,
+    pcclFloat = 10,
+    pcclDouble = 11,
+    /* extension: only legal as quantized_datatype together with pcclQuantBlockFp8 */
+    pcclFloat8E4M3 = 12
+} pcclDataType_t;
+
+typedef enum pcclDeviceType_t {
+    pcclDeviceCpu = 0,
+    pcclDeviceCuda = 1
+} pcclDeviceType_t;
+
+typedef enum pcclRedOp_t { pcclSum, pcclAvg, pcclProd, pcclMax, pcclMin } pcclRedOp_t;
+
+typedef enum pcclAttribute_t {
+    /* number of peers in the whole run, over all peer groups */
+    PCCL_ATTRIBUTE_GLOBAL_WORLD_SIZE = 1,
+    /* number of peers in the caller's peer group */
+    PCCL_ATTRIBUTE_PEER_GROUP_WORLD_SIZE = 2,
+    /* number of different peer groups in the run */
+    PCCL_ATTRIBUTE_NUM_DISTINCT_PEER_GROUPS = 3,
+    /* size of the largest peer group */
+    PCCL_ATTRIBUTE_LARGEST_PEER_GROUP_WORLD_SIZE = 4
+} pcclAttribute_t;
+
+/*
+ * How a peer takes part in a shared-state synchronisation.
+ *   ENFORCE_POPULAR  send or receive, whichever makes every peer hold the most popular content;
+ *                    if any peer of a group uses it, all peers of that group must.
+ *   RECEIVE_ONLY     never transmit; the caller's content does not take part in the election.
+ *   SEND_ONLY        never be overwritten; the caller's content must be the elected one, peers
+ *                    that declare SEND_ONLY with diverging content are kicked by the master.
+ */
+typedef enum pcclSharedStateSyncStrategy_t {
+    PCCL_SHARED_STATE_SYNC_STRATEGY_ENFORCE_POPULAR = 0,
+    PCCL_SHARED_STATE_SYNC_STRATEGY_RECEIVE_ONLY = 1,
+    PCCL_SHARED_STATE_SYNC_STRATEGY_SEND_ONLY = 2
+} pcclSharedStateSyncStrategy_t;
+
+typedef enum pcclDistributionHint_t {
+    pcclDistributionNone = 0,
+    pcclDistributionNormal = 1,
+    pcclDistributionUniform = 2
+} pcclDistributionHint_t;
+
+typedef enum pcclQuantizationAlgorithm_t {
+    pcclQuantNone = 0,
+    /* one (min,max) pair per transferred chunk, unsigned integer code words */
+    pcclQuantMinMax = 1,
+    /* one (zero point, scale) pair per transferred chunk, round-to-nearest */
+    pcclQuantZeroPointScale = 2,
+    /* extension: (min,max) per 128-element block, uint8 code words, fp32 accumulation */
+    pcclQuantBlockMinMax = 3,
+    /* extension: fp8-e4m3 code words with one fp32 scale per 128-element block */
+    pcclQuantBlockFp8 = 4
+} pcclQuantizationAlgorithm_t;
+
+/* ------------------------------------------------------------------------------------------- */
+/* Core structs                                                                                 */
+/* ------------------------------------------------------------------------------------------- */
+
+typedef struct {
+    ccoip_socket_address_t master_address;
+    uint32_t peer_group;
+    uint32_t p2p_connection_pool_size;
+
+    /* When true the three advertised_* addresses are handed to the master verbatim (NAT, port
+     * forwarding); otherwise the master combines the source IP it sees with the ports below. */
+    bool use_explicit_p2p_addresses;
+    ccoip_socket_address_t advertised_p2p_address;
+    ccoip_socket_address_t advertised_shared_state_address;
+    ccoip_socket_address_t advertised_benchmark_address;
+
+    /* Ports this peer binds locally.  A busy port is bumped upwards until one is free. */
+    uint16_t internal_p2p_listen_port;          /* default 48149 */
+    uint16_t internal_shared_state_listen_port; /* default 48150 */
+    uint16_t internal_benchmark_listen_port;    /* default 48151 */
+} pcclCommCreateParams_t;
+
+typedef struct pcclComm_t pcclComm_t;
+typedef struct pcclRankInfo_t pcclRankInfo_t;
+
+typedef struct pcclReduceInfo_t {
+    /* number of peers that took part in the (successful) operation */
+    uint32_t local_world_size;
+    uint64_t tx_bytes;
+    uint64_t rx_bytes;
+} pcclReduceInfo_t;
+
+typedef struct pcclReduceOperandDescriptor_t {
+    pcclDataType_t datatype;
+    pcclDistributionHint_t distribution_hint;
+} pcclReduceOperandDescriptor_t;
+
+typedef struct pcclQuantizationOptions_t {
+    pcclDataType_t quantized_datatype;
+    pcclQuantizationAlgorithm_t algorithm;
+} pcclQuantizationOptions_t;
+
+typedef struct pcclReduceDescriptor_t {
+    size_t count;
+    pcclRedOp_t op;
+    uint64_t tag;
+    pcclReduceOperandDescriptor_t src_descriptor;
+    pcclQuantizationOptions_t quantization_options;
+} pcclReduceDescriptor_t;
+
+typedef struct pcclReduceSingleDescriptor_t {
+    void *sendbuf;
+    void *recvbuf;
+    pcclReduceDescriptor_t descriptor;
+} pcclReduceOpDescriptor_t;
+
+typedef struct pcclAsyncReduceOp_t {
+    pcclComm_t *comm;
+    uint64_t tag;
+} pcclAsyncReduceOp_t;
+
+/* Identity of a rank; never reused within a run. */
+typedef struct pcclRankUuid_t {
+    uint8_t data[16];
+} pcclRankUuid_t;
+
+typedef struct pcclTensorInfo_t {
+    const char *name;
+    void *data;
+    size_t count;
+    pcclDataType_t datatype;
+    pcclDeviceType_t device_type;
+    bool allow_content_inequality;
+} pcclTensorInfo_t;
+
+typedef struct pcclSharedState_t {
+    uint64_t revision;
+    size_t count;
+    pcclTensorInfo_t *infos;
+} pcclSharedState_t;
+
+typedef struct pcclSharedStateSyncInfo_t {
+    uint64_t tx_bytes;
+    uint64_t rx_bytes;
+} pcclSharedStateSyncInfo_t;
+
+typedef struct pcclMasterInstanceState_t pcclMasterInstance_t;
+
+typedef struct pcclBuildInfo_t {
+    bool has_cuda_support;
+} pcclBuildInfo_t;
+
+/* ------------------------------------------------------------------------------------------- */
+/* Core functions (reference: include/pccl.h:225-458)                                           */
+/* ------------------------------------------------------------------------------------------- */
+
+/* Must be the first call into the library. */
+PCCL_EXPORT pcclResult_t pcclInit(void);
+
+/* Allocates a communicator; no network activity happens before pcclConnect. */
+PCCL_EXPORT pcclResult_t pcclCreateCommunicator(const pcclCommCreateParams_t *params, pcclComm_t **comm_out);
+
+/* World-size style attributes; values are those of the last completed topology update. */
+PCCL_EXPORT pcclResult_t pcclGetAttribute(const pcclComm_t *communicator, pcclAttribute_t attribute,
+                                          int *p_attribute_out);
+
+/* Closes all sockets, joins all threads, releases device resources. */
+PCCL_EXPORT pcclResult_t pcclDestroyCommunicator(pcclComm_t *communicator);
+
+/* Joins the run.  Blocks until the already accepted peers vote to admit this peer. */
+PCCL_EXPORT pcclResult_t pcclConnect(pcclComm_t *communicator);
+
+/* Joint vote of all accepted peers to admit pending peers and (re)wire P2P links.
+ * Fails with pcclPendingAsyncOps while async reductions are in flight. */
+PCCL_EXPORT pcclResult_t pcclUpdateTopology(pcclComm_t *communicator);
+
+/* Joint query whether peers wait for admission; legal while reductions are in flight. */
+PCCL_EXPORT pcclResult_t pcclArePeersPending(const pcclComm_t *communicator, bool *pending_out);
+
+/* Joint bandwidth measurement + ring re-ordering (ATSP over measured link speeds). */
+PCCL_EXPORT pcclResult_t pcclOptimizeTopology(const pcclComm_t *communicator);
+
+/* Blocking all-reduce.  sendbuff may equal recvbuff.  On failure the contents of sendbuff are
+ * what they were before the call. */
+PCCL_EXPORT pcclResult_t pcclAllReduce(const void *sendbuff, void *recvbuff, const pcclReduceDescriptor_t *descriptor,
+                                       const pcclComm_t *communicator, pcclReduceInfo_t *PCCL_NULLABLE reduce_info_out);
+
+/* Starts an all-reduce; completion is observed with pcclAwaitAsyncReduce.  A tag may only be in
+ * flight once. */
+PCCL_EXPORT pcclResult_t pcclAllReduceAsync(const void *sendbuff, void *recvbuff,
+                                            const pcclReduceDescriptor_t *descriptor, const pcclComm_t *communicator,
+                                            pcclAsyncReduceOp_t *reduce_handle_out);
+
+/* Runs a list of reductions with at most max_in_flight concurrently; failed ones are retried
+ * with the surviving peers until all succeeded or fewer than two peers are left. */
+PCCL_EXPORT pcclResult_t pcclAllReduceMultipleWithRetry(const pcclReduceOpDescriptor_t *descriptors, size_t count,
+                                                        const pcclComm_t *communicator,
+                                                        pcclReduceInfo_t *PCCL_NULLABLE reduce_info_out,
+                                                        int max_in_flight);
+
+PCCL_EXPORT pcclResult_t pcclAwaitAsyncReduce(const pcclAsyncReduceOp_t *reduce_handle,
+                                              pcclReduceInfo_t *PCCL_NULLABLE reduce_info_out);
+
+/* Brings every peer of the group to the elected ("most popular") shared-state content; only
+ * tensors whose hash differs are transferred.  shared_state->revision may be updated. */
+PCCL_EXPORT pcclResult_t pcclSynchronizeSharedState(const pcclComm_t *communicator, pcclSharedState_t *shared_state,
+                                                    pcclSharedStateSyncStrategy_t strategy,
+                                                    pcclSharedStateSyncInfo_t *PCCL_NULLABLE sync_info_out);
+
+PCCL_EXPORT pcclResult_t pcclCreateMaster(ccoip_socket_address_t listen_address,
+                                          pcclMasterInstance_t **p_master_handle_out);
+/* Non-blocking: the master runs on its own thread. */
+PCCL_EXPORT pcclResult_t pcclRunMaster(pcclMasterInstance_t *master_instance);
+PCCL_EXPORT pcclResult_t pcclInterruptMaster(pcclMasterInstance_t *master_instance);
+PCCL_EXPORT pcclResult_t pcclMasterAwaitTermination(pcclMasterInstance_t *master_instance);
+PCCL_EXPORT pcclResult_t pcclDestroyMaster(pcclMasterInstance_t *master_instance);
+
+PCCL_EXPORT pcclResult_t pcclGetBuildInfo(pcclBuildInfo_t *info);
+
+/* ------------------------------------------------------------------------------------------- */
+/* Extensions (no counterpart in the reference)                                                 */
+/* ------------------------------------------------------------------------------------------- */
+
+/* Which data plane an all-reduce used. */
+typedef enum pcclExtDataPlane_t {
+    pcclExtPlaneNone = 0,
+    pcclExtPlaneTcpRing = 1,     /* CCoIP ring over sockets (host memory, staged for device buffers) */
+    pcclExtPlaneP2POneShot = 2,  /* every GPU reads every peer, latency regime */
+    pcclExtPlaneP2PTwoShot = 3,  /* reduce-scatter + all-gather with direct peer loads */
+    pcclExtPlaneNvls = 4         /* NVSwitch multicast ld_reduce / st */
+} pcclExtDataPlane_t;
+
+typedef struct pcclExtReduceStats_t {
+    pcclExtDataPlane_t plane;
+    float device_ms;     /* CUDA-event time of the device part, 0 for host ops */
+    uint64_t seq_nr;     /* master-issued sequence number of the operation */
+} pcclExtReduceStats_t;
+
+/* Stats of the most recently completed reduction with the given tag. */
+PCCL_EXPORT pcclResult_t pcclExtGetLastReduceStats(const pcclComm_t *communicator, uint64_t tag,
+                                                   pcclExtReduceStats_t *stats_out);
+
+/* Port the master actually bound (useful with port 0 / bumped ports in tests). */
+PCCL_EXPORT pcclResult_t pcclExtMasterGetPort(const pcclMasterInstance_t *master_instance, uint16_t *port_out);
+
+/* Hash of a host or device buffer with the hash the shared-state protocol uses.
+ * hash_type: 0 = simplehash (reference-compatible value), 1 = CRC32C. */
+PCCL_EXPORT pcclResult_t pcclExtHashBuffer(const void *data, size_t n_bytes, pcclDeviceType_t device_type,
+                                           int hash_type, uint64_t *hash_out);
+
+/* Allocates `bytes` of device memory on the current CUDA device from the communicator's
+ * peer-visible arena.  Reductions whose send/recv buffers both come from here skip the
+ * staging copy.  Freed by pcclExtSymmetricFree or with the communicator. */
+PCCL_EXPORT pcclResult_t pcclExtSymmetricAlloc(pcclComm_t *communicator, size_t bytes, void **ptr_out);
+PCCL_EXPORT pcclResult_t pcclExtSymmetricFree(pcclComm_t *communicator, void *ptr);
+
+/* Size of one element of a data type in bytes, 0 for unknown values. */
+PCCL_EXPORT size_t pcclExtDataTypeSize(pcclDataType_t datatype);
+
+#ifdef __cplusplus
+}
+#endif
+
+#endif /* PCCL_H_ */

@@ -1,0 +1,268 @@
+// End-to-end all-reduce contracts (reference ccoip/tests/end_to_end/test_all_reduce.cpp).
+#include <cmath>
+#include <cstring>
+#include <numeric>
+
+#include "e2e_util.hpp"
+
+using namespace pccl;
+using client::ReduceOutcome;
+using client::ReduceRequest;
+
+template <typename T> constexpr wire::DType dtype_of();
+template <> constexpr wire::DType dtype_of<uint8_t>() { return wire::DType::U8; }
+template <> constexpr wire::DType dtype_of<int8_t>() { return wire::DType::I8; }
+template <> constexpr wire::DType dtype_of<uint16_t>() { return wire::DType::U16; }
+template <> constexpr wire::DType dtype_of<int16_t>() { return wire::DType::I16; }
+template <> constexpr wire::DType dtype_of<uint32_t>() { return wire::DType::U32; }
+template <> constexpr wire::DType dtype_of<int32_t>() { return wire::DType::I32; }
+template <> constexpr wire::DType dtype_of<uint64_t>() { return wire::DType::U64; }
+template <> constexpr wire::DType dtype_of<int64_t>() { return wire::DType::I64; }
+template <> constexpr wire::DType dtype_of<float>() { return wire::DType::F32; }
+template <> constexpr wire::DType dtype_of<double>() { return wire::DType::F64; }
+
+template <typename T> static T fold(T a, T b, wire::RedOp op) {
+    switch (op) {
+    case wire::RedOp::Sum:
+    case wire::RedOp::Avg: return static_cast<T>(a + b);
+    case wire::RedOp::Prod: return static_cast<T>(a * b);
+    case wire::RedOp::Max: return a > b ? a : b;
+    case wire::RedOp::Min: return a < b ? a : b;
+    default: return b;
+    }
+}
+
+template <typename T> static void run_case(int world, size_t count, wire::RedOp op, bool in_place) {
+    TestMaster tm;
+    auto peers = connect_peers(tm, world);
+    std::vector<std::vector<T>> inputs(world, std::vector<T>(count)), outputs(world, std::vector<T>(count));
+    for (int r = 0; r < world; ++r)
+        for (size_t i = 0; i < count; ++i) inputs[r][i] = static_cast<T>((i * 7 + r * 3 + 1) % 11 + (op == wire::RedOp::Prod ? 0 : r));
+    std::vector<T> expect(inputs[0]);
+    for (int r = 1; r < world; ++r)
+        for (size_t i = 0; i < count; ++i) expect[i] = fold(expect[i], inputs[r][i], op);
+    if (op == wire::RedOp::Avg)
+        for (auto &v : expect) v = static_cast<T>(v / static_cast<T>(world));
+
+    std::vector<std::thread> ts;
+    for (int r = 0; r < world; ++r) {
+        ts.emplace_back([&, r] {
+            ReduceRequest req;
+            std::vector<T> work = inputs[r];
+            req.send = in_place ? work.data() : inputs[r].data();
+            req.recv = in_place ? work.data() : outputs[r].data();
+            req.count = count;
+            req.dtype = dtype_of<T>();
+            req.op = op;
+            req.tag = 1;
+            CHECK(peers[r]->all_reduce_async(req) == client::Client::Launch::Ok);
+            ReduceOutcome out;
+            CHECK(peers[r]->await_reduce(1, out));
+            CHECK_EQ(out.world, static_cast<uint32_t>(world));
+            if (in_place) outputs[r] = work;
+        });
+    }
+    for (auto &t : ts) t.join();
+    for (int r = 0; r < world; ++r)
+        for (size_t i = 0; i < count; ++i) {
+            if constexpr (std::is_floating_point_v<T>)
+                CHECK(std::fabs(static_cast<double>(outputs[r][i]) - static_cast<double>(expect[i])) < 1e-5);
+            else
+                CHECK(outputs[r][i] == expect[i]);
+        }
+}
+
+template <typename T> static void typed_suite() {
+    run_case<T>(2, 203530, wire::RedOp::Sum, false);
+    run_case<T>(2, 203530, wire::RedOp::Sum, true);
+    for (size_t n : {size_t(2), size_t(3), size_t(1025)}) run_case<T>(3, n, wire::RedOp::Sum, false);
+    run_case<T>(4, 2, wire::RedOp::Sum, true); // some ranks own empty chunks
+    run_case<T>(2, 1000, wire::RedOp::Avg, false);
+    run_case<T>(3, 1000, wire::RedOp::Min, false);
+    run_case<T>(3, 1000, wire::RedOp::Max, true);
+}
+
+TEST(allreduce_u8) { typed_suite<uint8_t>(); }
+TEST(allreduce_i16) { typed_suite<int16_t>(); }
+TEST(allreduce_u32) { typed_suite<uint32_t>(); }
+TEST(allreduce_i64) { typed_suite<int64_t>(); }
+TEST(allreduce_f32) { typed_suite<float>(); }
+TEST(allreduce_f64) { typed_suite<double>(); }
+TEST(allreduce_other_ints) {
+    run_case<int8_t>(3, 1025, wire::RedOp::Sum, false);
+    run_case<uint16_t>(3, 1025, wire::RedOp::Max, false);
+    run_case<int32_t>(4, 4099, wire::RedOp::Sum, true);
+    run_case<uint64_t>(2, 77, wire::RedOp::Prod, false);
+}
+
+// 42 + 43 must come out as exactly 85 through uint8 zero-point/scale quantisation
+template <typename T> static void quantised_exact() {
+    TestMaster tm;
+    auto peers = connect_peers(tm, 2);
+    std::vector<std::thread> ts;
+    for (int r = 0; r < 2; ++r) {
+        ts.emplace_back([&, r] {
+            std::vector<T> in(1024, static_cast<T>(42 + r)), out(1024, 0);
+            ReduceRequest req;
+            req.send = in.data();
+            req.recv = out.data();
+            req.count = in.size();
+            req.dtype = dtype_of<T>();
+            req.op = wire::RedOp::Sum;
+            req.quant = wire::QuantAlgo::ZeroPointScale;
+            req.quant_dtype = wire::DType::U8;
+            req.tag = 1;
+            CHECK(peers[r]->all_reduce_async(req) == client::Client::Launch::Ok);
+            ReduceOutcome o;
+            CHECK(peers[r]->await_reduce(1, o));
+            for (auto v : out) CHECK(v == static_cast<T>(85));
+        });
+    }
+    for (auto &t : ts) t.join();
+}
+TEST(quantised_zps_exact_f32) { quantised_exact<float>(); }
+TEST(quantised_zps_exact_f64) { quantised_exact<double>(); }
+
+// min-max uint8 quantisation: every peer ends up with bit-identical results close to the truth
+TEST(quantised_minmax_bit_identical) {
+    for (int world : {2, 3, 4}) {
+        TestMaster tm;
+        auto peers = connect_peers(tm, world);
+        const size_t n = 10007;
+        std::vector<std::vector<float>> in(world, std::vector<float>(n)), out(world, std::vector<float>(n));
+        for (int r = 0; r < world; ++r)
+            for (size_t i = 0; i < n; ++i) in[r][i] = std::sin(0.001f * i + r) * 3.0f;
+        std::vector<std::thread> ts;
+        for (int r = 0; r < world; ++r)
+            ts.emplace_back([&, r] {
+                ReduceRequest req;
+                req.send = in[r].data();
+                req.recv = out[r].data();
+                req.count = n;
+                req.op = wire::RedOp::Sum;
+                req.quant = wire::QuantAlgo::MinMax;
+                req.quant_dtype = wire::DType::U8;
+                req.tag = 7;
+                CHECK(peers[r]->all_reduce_async(req) == client::Client::Launch::Ok);
+                ReduceOutcome o;
+                CHECK(peers[r]->await_reduce(7, o));
+                CHECK(o.tx_bytes > 0 && o.tx_bytes < n * sizeof(float) * 2); // less than unquantised traffic
+            });
+        for (auto &t : ts) t.join();
+        for (int r = 1; r < world; ++r) CHECK(std::memcmp(out[0].data(), out[r].data(), n * sizeof(float)) == 0);
+        for (size_t i = 0; i < n; ++i) {
+            float truth = 0;
+            for (int r = 0; r < world; ++r) truth += in[r][i];
+            CHECK(std::fabs(out[0][i] - truth) < 0.05f * world);
+        }
+    }
+}
+
+TEST(quantised_block_formats) {
+    for (auto algo : {wire::QuantAlgo::BlockMinMax, wire::QuantAlgo::BlockFp8}) {
+        TestMaster tm;
+        auto peers = connect_peers(tm, 3);
+        const size_t n = 5000;
+        std::vector<std::vector<float>> in(3, std::vector<float>(n)), out(3, std::vector<float>(n));
+        for (int r = 0; r < 3; ++r)
+            for (size_t i = 0; i < n; ++i) in[r][i] = std::cos(0.01f * i * (r + 1)) * (1.0f + 0.001f * i);
+        std::vector<std::thread> ts;
+        for (int r = 0; r < 3; ++r)
+            ts.emplace_back([&, r] {
+                ReduceRequest req;
+                req.send = in[r].data();
+                req.recv = out[r].data();
+                req.count = n;
+                req.op = wire::RedOp::Avg;
+                req.quant = algo;
+                req.quant_dtype = algo == wire::QuantAlgo::BlockFp8 ? wire::DType::F8E4M3 : wire::DType::U8;
+                req.tag = 3;
+                CHECK(peers[r]->all_reduce_async(req) == client::Client::Launch::Ok);
+                ReduceOutcome o;
+                CHECK(peers[r]->await_reduce(3, o));
+            });
+        for (auto &t : ts) t.join();
+        for (int r = 1; r < 3; ++r) CHECK(std::memcmp(out[0].data(), out[r].data(), n * sizeof(float)) == 0);
+        for (size_t i = 0; i < n; ++i) {
+            const float truth = (in[0][i] + in[1][i] + in[2][i]) / 3.0f;
+            // uint8 blocks resolve 1/255 of the block range; e4m3 keeps 3 mantissa bits (about 6%
+            // of the block maximum per hop)
+            const float tol = algo == wire::QuantAlgo::BlockFp8 ? 0.9f : 0.08f;
+            CHECK(std::fabs(out[0][i] - truth) < tol);
+        }
+    }
+}
+
+// two tags run concurrently with different operators
+TEST(concurrent_tags) {
+    TestMaster tm;
+    auto peers = connect_peers(tm, 2);
+    const size_t n = 1 << 16;
+    std::vector<std::thread> ts;
+    for (int r = 0; r < 2; ++r)
+        ts.emplace_back([&, r] {
+            std::vector<float> a(n, 1.0f + r), b(n, 10.0f * (r + 1)), ra(n), rb(n);
+            ReduceRequest q1, q2;
+            q1.send = a.data(), q1.recv = ra.data(), q1.count = n, q1.op = wire::RedOp::Sum, q1.tag = 1;
+            q2.send = b.data(), q2.recv = rb.data(), q2.count = n, q2.op = wire::RedOp::Max, q2.tag = 2;
+            CHECK(peers[r]->all_reduce_async(q1) == client::Client::Launch::Ok);
+            CHECK(peers[r]->all_reduce_async(q2) == client::Client::Launch::Ok);
+            // joint calls are refused while reductions are in flight
+            CHECK(!peers[r]->update_topology());
+            ReduceOutcome o;
+            CHECK(peers[r]->await_reduce(1, o));
+            CHECK(peers[r]->await_reduce(2, o));
+            for (size_t i = 0; i < n; ++i) {
+                CHECK(ra[i] == 3.0f);
+                CHECK(rb[i] == 20.0f);
+            }
+        });
+    for (auto &t : ts) t.join();
+}
+
+// a tag may only be in flight once; the first operation is unaffected
+TEST(duplicate_tag_rejected) {
+    TestMaster tm;
+    auto peers = connect_peers(tm, 2);
+    const size_t n = 1 << 18;
+    std::vector<std::thread> ts;
+    for (int r = 0; r < 2; ++r)
+        ts.emplace_back([&, r] {
+            std::vector<float> a(n, 1.0f), ra(n), rb(n);
+            ReduceRequest q;
+            q.send = a.data(), q.recv = ra.data(), q.count = n, q.tag = 5;
+            CHECK(peers[r]->all_reduce_async(q) == client::Client::Launch::Ok);
+            ReduceRequest dup = q;
+            dup.recv = rb.data();
+            CHECK(peers[r]->all_reduce_async(dup) == client::Client::Launch::DuplicateTag);
+            ReduceOutcome o;
+            CHECK(peers[r]->await_reduce(5, o));
+            for (auto v : ra) CHECK(v == 2.0f);
+            // tag can be reused afterwards
+            CHECK(peers[r]->all_reduce_async(q) == client::Client::Launch::Ok);
+            CHECK(peers[r]->await_reduce(5, o));
+        });
+    for (auto &t : ts) t.join();
+}
+
+// basic_reduce_test of BASELINE.json: 2 peers + master on localhost, fp32 sum of 4 elements
+TEST(basic_reduce_four_elements) {
+    TestMaster tm;
+    auto peers = connect_peers(tm, 2);
+    std::vector<std::thread> ts;
+    for (int r = 0; r < 2; ++r)
+        ts.emplace_back([&, r] {
+            float in[4] = {1, 2, 3, 4}, out[4] = {0};
+            for (int it = 0; it < 50; ++it) {
+                ReduceRequest q;
+                q.send = in, q.recv = out, q.count = 4, q.tag = 0;
+                CHECK(peers[r]->all_reduce_async(q) == client::Client::Launch::Ok);
+                ReduceOutcome o;
+                CHECK(peers[r]->await_reduce(0, o));
+                for (int i = 0; i < 4; ++i) CHECK(out[i] == 2.0f * (i + 1));
+            }
+        });
+    for (auto &t : ts) t.join();
+}
+
+TEST_MAIN()
