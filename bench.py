@@ -1,0 +1,271 @@
+#!/usr/bin/env python3
+"""Headline benchmark: fp32 AVG all-reduce of DiLoCo pseudo-gradients (150 M parameters by default)
+across N peers, one peer per GPU (BASELINE.json: "DiLoCo outer-step fp32 all-reduce of 150M-param
+pseudo-gradients", metric "all-reduce bus GB/s ...; DiLoCo outer-step sec").
+
+  python bench.py --gpus 1 --steps K --warmup W
+  python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P \
+         bench.py --gpus N --steps K --warmup W
+  ... --impl reference      runs the unmodified reference from baseline/_ref (host all-reduce, staged)
+
+What is timed (device time, CUDA events on the launching stream, max over ranks):
+  value      K back-to-back all-reduces through the public API (`Communicator.all_reduce` on device
+             tensors).  bus GB/s = bytes * 2(P-1)/P / t; with ONE peer the factor is undefined and
+             the algorithm bandwidth bytes/t of the one-rank fused kernel is reported instead.
+  e2e        the same, but every step first copies that step's pseudo-gradients host->device from
+             pinned memory and reads the first reduced element back device->host.
+  diloco_outer_step_ms   pseudo-gradient kernel + all-reduce + fused Nesterov update (+ hash)
+Inputs (600 MB) are far larger than the 126 MB L2, so no explicit L2 flush is needed between steps.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+REPO = Path(__file__).resolve().parent
+sys.path.insert(0, str(REPO))
+
+PUBLISHED_BASELINE_GBPS = 45.0 / 8.0  # reference docs: 45 Gbit/s sustained all-reduce (docs/md/01_Introduction.md:8)
+
+
+class ClockSampler:
+    """Samples SM clocks and throttle reasons with nvidia-smi while the timed region runs."""
+
+    def __init__(self, gpu_index: int):
+        self.gpu = gpu_index
+        self.samples = []
+        self.proc = None
+
+    def start(self):
+        q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+             "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={q}", "--format=csv,noheader,nounits", "-lms", "50", "-i", str(self.gpu)],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            parts = [p.strip() for p in line.split(",")]
+            if len(parts) >= 6:
+                self.samples.append(parts)
+
+    def stop(self) -> dict:
+        if self.proc:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=2)
+            except Exception:
+                self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        for p in self.samples:
+            try:
+                sm.append(float(p[0]))
+                mx.append(float(p[1]))
+            except ValueError:
+                continue
+            for name, v in zip(["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"], p[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--params", type=int, default=150_000_000, help="fp32 elements per peer")
+    ap.add_argument("--quant", default="none", choices=["none", "minmax_u8", "fp8"])
+    ap.add_argument("--sweep", action="store_true", help="also print a size sweep table to stderr")
+    return ap.parse_args()
+
+
+def bus_factor(peers: int) -> float:
+    return 2.0 * (peers - 1) / peers if peers > 1 else 1.0
+
+
+def run_ours(args) -> dict:
+    import torch
+
+    import pccl_b200 as pccl
+    from pccl_b200 import ops
+    from pccl_b200.parallel.diloco import LocalOuterStep, outer_nesterov_, pseudo_gradient
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    assert world == args.gpus, f"--gpus {args.gpus} but WORLD_SIZE={world}"
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    n = args.params
+    nbytes = n * 4
+    torch.manual_seed(1234 + rank)
+
+    dist = None
+    if world > 1:
+        import torch.distributed as dist_mod
+        dist = dist_mod
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        if dist:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(x: float) -> float:
+        if not dist:
+            return x
+        t = torch.tensor([x], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    grad = torch.randn(n, device=dev)
+    out = torch.empty_like(grad)
+    pinned = torch.randn(n).pin_memory()
+    quant = {"none": None,
+             "minmax_u8": pccl.QuantizationOptions(pccl.DataType.UINT8, pccl.QuantizationAlgorithm.MIN_MAX),
+             "fp8": pccl.QuantizationOptions(pccl.DataType.FLOAT8_E4M3, pccl.QuantizationAlgorithm.BLOCK_FP8)}[args.quant]
+
+    master = comm = None
+    planes = set()
+    launches = 0
+    if world > 1:
+        port_box = [0]
+        if rank == 0:
+            master = pccl.MasterNode("127.0.0.1:0")
+            master.run()
+            port_box[0] = master.port
+        dist.broadcast_object_list(port_box, src=0)
+        comm = pccl.Communicator(f"127.0.0.1:{port_box[0]}")
+        comm.connect(n_attempts=15)
+        while comm.get_attribute(pccl.Attribute.GLOBAL_WORLD_SIZE) < world:
+            comm.update_topology()
+
+        def reduce_step(src, dst):
+            nonlocal launches
+            comm.all_reduce(src, dst, op=pccl.ReduceOp.AVG, tag=0, quantization_options=quant)
+            st = comm.ext_last_reduce_stats(0)
+            planes.add(st["plane"])
+            launches += st["kernel_launches"]
+    else:
+        arena = ops.LocalArena(dev, nbytes)
+        qalgo = {"none": pccl.QuantizationAlgorithm.NONE, "minmax_u8": pccl.QuantizationAlgorithm.BLOCK_MIN_MAX,
+                 "fp8": pccl.QuantizationAlgorithm.BLOCK_FP8}[args.quant]
+
+        def reduce_step(src, dst):
+            nonlocal launches
+            ops.local_all_reduce(src, dst, arena, op=pccl.ReduceOp.AVG, quant=qalgo)
+            planes.add("p2p_two_shot(world=1)")
+            launches += 1
+
+    def timed(fn, steps):
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        ms = e0.elapsed_time(e1)
+        barrier()
+        return max_over_ranks(ms) / steps
+
+    # ---- kernel-level number -----------------------------------------------------------------
+    for _ in range(max(3, args.warmup)):
+        reduce_step(grad, out)
+    launches = 0
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    ms_step = timed(lambda: reduce_step(grad, out), args.steps)
+    timed_launches = launches
+
+    # ---- end to end: H2D of the step's input, all-reduce, D2H of a result scalar ------------------
+    def e2e_step():
+        grad.copy_(pinned, non_blocking=True)
+        reduce_step(grad, out)
+        return float(out[0].item())
+
+    for _ in range(3):
+        e2e_step()
+    ms_e2e = timed(e2e_step, max(3, args.steps // 2))
+    clocks = sampler.stop() if rank == 0 else {}  # sampled across both timed regions
+
+    # ---- DiLoCo outer step ------------------------------------------------------------------------
+    outer = torch.randn(n, device=dev)
+    inner = outer - 0.01 * torch.randn(n, device=dev)
+    buf = torch.zeros_like(outer)
+    pg = torch.empty_like(outer)
+    state = {"k": 0}
+
+    def outer_step():
+        pseudo_gradient(pg, outer, inner)
+        reduce_step(pg, pg if world > 1 else out)
+        outer_nesterov_(outer, buf, pg if world > 1 else out, inner, 0.7, 0.9, state["k"] == 0)
+        state["k"] += 1
+
+    for _ in range(3):
+        outer_step()
+    ms_outer = timed(outer_step, max(3, args.steps // 2))
+    ops.simplehash(outer)  # first call creates the per-device scratch and stream
+    t0 = time.perf_counter()
+    digest = ops.simplehash(outer)
+    ms_hash = (time.perf_counter() - t0) * 1e3
+
+    factor = bus_factor(world)
+    value = nbytes * factor / (ms_step * 1e-3) / 1e9
+    e2e_value = nbytes * factor / (ms_e2e * 1e-3) / 1e9
+    result = {
+        "metric": "allreduce_bus_GBps" if world > 1 else "allreduce_alg_GBps_single_peer",
+        "value": round(value, 3), "unit": "GB/s", "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
+        "ms_per_step": round(ms_step, 4), "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": round(value / PUBLISHED_BASELINE_GBPS, 2), "dtype": "fp32", "data": "synthetic",
+        "impl": "ours",
+        "config": {"model": "DiLoCo pseudo-gradients, GPT-2-class 150M params fp32", "params": n, "global_batch": None, "seq_len": None,
+                   "parallelism": f"dp{world}", "op": "avg", "quantization": args.quant, "planes": sorted(planes),
+                   "l2_policy": "inputs (600 MB) larger than L2 (126 MB); no explicit flush",
+                   "note": "one peer: bus factor undefined, value is bytes/time of the one-rank fused kernel" if world == 1 else
+                           "bus GB/s = bytes*2(P-1)/P/t, device time incl. control plane round trips"},
+        "e2e": {"value": round(e2e_value, 3), "unit": "GB/s", "ms_per_step": round(ms_e2e, 4), "h2d_bytes_per_step": nbytes, "d2h_bytes_per_step": 4},
+        "gpu_launches": timed_launches,
+        "diloco_outer_step_ms": round(ms_outer, 4), "shared_state_hash_ms": round(ms_hash, 3), "shared_state_hash": digest,
+        "clocks": clocks,
+    }
+    if comm is not None:
+        comm.destroy()
+    if dist:
+        barrier()
+        dist.destroy_process_group()
+    return result if rank == 0 else {}
+
+
+def run_reference(args) -> dict:
+    ref_dir = REPO / "baseline" / "_ref"
+    marker = ref_dir / "pccl"
+    if not marker.exists():
+        return {"impl": "reference", "unavailable": "reference is not installed in baseline/_ref (see DESIGN.md: build needs the missing piquant submodule)"}
+    from baseline.reference_arm import run as run_ref  # noqa: WPS433
+    return run_ref(args)
+
+
+def main():
+    args = parse_args()
+    out = run_reference(args) if args.impl == "reference" else run_ours(args)
+    if out:
+        print(json.dumps(out), flush=True)
+
+
+if __name__ == "__main__":
+    main()

@@ -716,6 +716,7 @@ ReduceOutcome Client::run_reduce(const ReduceRequest &req, uint64_t) {
         out.rx_bytes = r.rx_bytes;
         out.stats.plane = r.plane;
         out.stats.device_ms = r.device_ms;
+        out.stats.kernel_launches = r.kernel_launches;
     } else if (use_device) {
         // cannot happen unless peers disagree about their own capability between vote and run
         PLOG(ERR) << "device plane was agreed on but is not available locally";

@@ -53,6 +53,7 @@ struct DeviceReduceResult {
     bool aborted = false;
     pcclExtDataPlane_t plane = pcclExtPlaneNone;
     float device_ms = 0;
+    uint32_t kernel_launches = 0;
     uint64_t tx_bytes = 0, rx_bytes = 0;
 };
 

@@ -1,0 +1,734 @@
+// CUDA implementation of the device plane (see plane.hpp for the design).
+//
+// Driver-API entry points (virtual memory management, multicast) are resolved at run time through
+// cudaGetDriverEntryPoint, so libpccl.so has no link-time dependency on libcuda and loads on
+// machines without a GPU.
+#ifndef PCCL_NO_CUDA
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <poll.h>
+#include <sys/socket.h>
+#include <sys/un.h>
+#include <unistd.h>
+
+#include <algorithm>
+#include <atomic>
+#include <chrono>
+#include <cstring>
+#include <map>
+#include <mutex>
+#include <thread>
+#include <unordered_map>
+
+#include "../util/env.hpp"
+#include "../util/log.hpp"
+#include "pccl_kernels.h"
+#include "plane.hpp"
+
+namespace pccl::device {
+
+namespace {
+
+using clock_type = std::chrono::steady_clock;
+
+// ------------------------------------------------------------------------------------------ driver API
+struct Driver {
+    bool ok = false;
+    CUresult (*MemGetAllocationGranularity)(size_t *, const CUmemAllocationProp *, CUmemAllocationGranularity_flags) = nullptr;
+    CUresult (*MemCreate)(CUmemGenericAllocationHandle *, size_t, const CUmemAllocationProp *, unsigned long long) = nullptr;
+    CUresult (*MemRelease)(CUmemGenericAllocationHandle) = nullptr;
+    CUresult (*MemAddressReserve)(CUdeviceptr *, size_t, size_t, CUdeviceptr, unsigned long long) = nullptr;
+    CUresult (*MemAddressFree)(CUdeviceptr, size_t) = nullptr;
+    CUresult (*MemMap)(CUdeviceptr, size_t, size_t, CUmemGenericAllocationHandle, unsigned long long) = nullptr;
+    CUresult (*MemUnmap)(CUdeviceptr, size_t) = nullptr;
+    CUresult (*MemSetAccess)(CUdeviceptr, size_t, const CUmemAccessDesc *, size_t) = nullptr;
+    CUresult (*MemExportToShareableHandle)(void *, CUmemGenericAllocationHandle, CUmemAllocationHandleType, unsigned long long) = nullptr;
+    CUresult (*MemImportFromShareableHandle)(CUmemGenericAllocationHandle *, void *, CUmemAllocationHandleType) = nullptr;
+    CUresult (*DeviceGet)(CUdevice *, int) = nullptr;
+    CUresult (*DeviceGetAttribute)(int *, CUdevice_attribute, CUdevice) = nullptr;
+};
+
+const Driver &driver() {
+    static const Driver d = [] {
+        Driver x;
+        int count = 0;
+        if (cudaGetDeviceCount(&count) != cudaSuccess || count == 0) {
+            (void) cudaGetLastError();
+            return x;
+        }
+        bool all = true;
+        auto load = [&](const char *name, auto &fn) {
+            void *p = nullptr;
+            cudaDriverEntryPointQueryResult q;
+            if (cudaGetDriverEntryPoint(name, &p, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess || !p) {
+                (void) cudaGetLastError();
+                all = false;
+                return;
+            }
+            fn = reinterpret_cast<std::remove_reference_t<decltype(fn)>>(p);
+        };
+        load("cuMemGetAllocationGranularity", x.MemGetAllocationGranularity);
+        load("cuMemCreate", x.MemCreate);
+        load("cuMemRelease", x.MemRelease);
+        load("cuMemAddressReserve", x.MemAddressReserve);
+        load("cuMemAddressFree", x.MemAddressFree);
+        load("cuMemMap", x.MemMap);
+        load("cuMemUnmap", x.MemUnmap);
+        load("cuMemSetAccess", x.MemSetAccess);
+        load("cuMemExportToShareableHandle", x.MemExportToShareableHandle);
+        load("cuMemImportFromShareableHandle", x.MemImportFromShareableHandle);
+        load("cuDeviceGet", x.DeviceGet);
+        load("cuDeviceGetAttribute", x.DeviceGetAttribute);
+        x.ok = all;
+        return x;
+    }();
+    return d;
+}
+
+#define CU_TRY(expr)                                                                                                   \
+    do {                                                                                                               \
+        const CUresult rc_ = (expr);                                                                                   \
+        if (rc_ != CUDA_SUCCESS) {                                                                                     \
+            PLOG(WARN) << #expr << " failed with CUresult " << static_cast<int>(rc_);                                  \
+            return false;                                                                                              \
+        }                                                                                                              \
+    } while (0)
+#define RT_TRY(expr)                                                                                                   \
+    do {                                                                                                               \
+        const cudaError_t rc_ = (expr);                                                                                \
+        if (rc_ != cudaSuccess) {                                                                                      \
+            PLOG(WARN) << #expr << " failed: " << cudaGetErrorString(rc_);                                             \
+            (void) cudaGetLastError();                                                                                 \
+            return false;                                                                                              \
+        }                                                                                                              \
+    } while (0)
+
+// ------------------------------------------------------------------------------------------ unix rendezvous
+constexpr uint32_t kMagic = 0x50434231; // "PCB1"
+enum : uint32_t { kReqArena = 1 };
+
+struct RendezvousRequest {
+    uint32_t magic, kind;
+    uint8_t requester[16];
+};
+struct RendezvousReply {
+    uint32_t magic, status; // status 0 = ok
+    uint64_t arena_bytes, slot_bytes, sym_bytes;
+    uint32_t n_slots, pid;
+    uint8_t gpu_uuid[16];
+};
+
+sockaddr_un rendezvous_address(const Uuid &u, socklen_t &len) {
+    sockaddr_un sa{};
+    sa.sun_family = AF_UNIX;
+    const std::string name = "pccl-b200-" + u.hex();
+    sa.sun_path[0] = '\0'; // abstract namespace: no file system entry, vanishes with the process
+    std::memcpy(sa.sun_path + 1, name.data(), name.size());
+    len = static_cast<socklen_t>(offsetof(sockaddr_un, sun_path) + 1 + name.size());
+    return sa;
+}
+
+bool send_with_fd(int sock, const void *data, size_t n, int fd) {
+    msghdr msg{};
+    iovec iov{const_cast<void *>(data), n};
+    msg.msg_iov = &iov;
+    msg.msg_iovlen = 1;
+    alignas(cmsghdr) char ctrl[CMSG_SPACE(sizeof(int))] = {0};
+    if (fd >= 0) {
+        msg.msg_control = ctrl;
+        msg.msg_controllen = sizeof ctrl;
+        cmsghdr *c = CMSG_FIRSTHDR(&msg);
+        c->cmsg_level = SOL_SOCKET;
+        c->cmsg_type = SCM_RIGHTS;
+        c->cmsg_len = CMSG_LEN(sizeof(int));
+        std::memcpy(CMSG_DATA(c), &fd, sizeof(int));
+    }
+    return ::sendmsg(sock, &msg, MSG_NOSIGNAL) == static_cast<ssize_t>(n);
+}
+
+bool recv_with_fd(int sock, void *data, size_t n, int &fd, int timeout_ms) {
+    fd = -1;
+    pollfd p{sock, POLLIN, 0};
+    if (::poll(&p, 1, timeout_ms) <= 0) return false;
+    msghdr msg{};
+    iovec iov{data, n};
+    msg.msg_iov = &iov;
+    msg.msg_iovlen = 1;
+    alignas(cmsghdr) char ctrl[CMSG_SPACE(sizeof(int))] = {0};
+    msg.msg_control = ctrl;
+    msg.msg_controllen = sizeof ctrl;
+    if (::recvmsg(sock, &msg, MSG_CMSG_CLOEXEC) != static_cast<ssize_t>(n)) return false;
+    for (cmsghdr *c = CMSG_FIRSTHDR(&msg); c; c = CMSG_NXTHDR(&msg, c))
+        if (c->cmsg_level == SOL_SOCKET && c->cmsg_type == SCM_RIGHTS) std::memcpy(&fd, CMSG_DATA(c), sizeof(int));
+    return true;
+}
+
+size_t round_up(size_t v, size_t g) { return (v + g - 1) / g * g; }
+
+// ------------------------------------------------------------------------------------------ the plane
+class CudaPlane final : public Plane {
+public:
+    CudaPlane() {
+        usable_ = cuda_runtime_usable() && driver().ok && env_flag("PCCL_DEVICE_PLANE", true);
+        if (usable_ && cudaGetDevice(&device_) != cudaSuccess) usable_ = false;
+        if (usable_) {
+            cudaDeviceProp prop{};
+            if (cudaGetDeviceProperties(&prop, device_) == cudaSuccess) {
+                std::memcpy(gpu_uuid_, prop.uuid.bytes, 16);
+                clock_khz_ = prop.clockRate > 0 ? prop.clockRate : 1900000;
+            }
+        }
+        slot_bytes_ = round_up(env_u64("PCCL_ARENA_SLOT_MB", 256) << 20, 2u << 20);
+        n_slots_ = static_cast<uint32_t>(std::clamp<uint64_t>(env_u64("PCCL_ARENA_SLOTS", 4), 1, 15));
+        sym_bytes_ = round_up(env_u64("PCCL_SYMMETRIC_MB", 0) << 20, 2u << 20);
+        timeout_ms_ = env_u64("PCCL_DEVICE_TIMEOUT_MS", 30000);
+        max_blocks_ = static_cast<int>(env_u64("PCCL_DEVICE_MAX_BLOCKS", 0));
+    }
+    ~CudaPlane() override { stop(); }
+
+    void start(const Uuid &self) override {
+        self_ = self;
+        if (!usable_ || started_) return;
+        listen_fd_ = ::socket(AF_UNIX, SOCK_STREAM | SOCK_CLOEXEC, 0);
+        if (listen_fd_ < 0) return;
+        socklen_t len;
+        const sockaddr_un sa = rendezvous_address(self, len);
+        if (::bind(listen_fd_, reinterpret_cast<const sockaddr *>(&sa), len) != 0 || ::listen(listen_fd_, 64) != 0) {
+            ::close(listen_fd_);
+            listen_fd_ = -1;
+            return;
+        }
+        started_ = true;
+        server_ = std::thread([this] { serve(); });
+    }
+
+    void stop() override {
+        if (started_) {
+            stopping_ = true;
+            if (server_.joinable()) server_.join();
+            ::close(listen_fd_);
+            listen_fd_ = -1;
+            started_ = false;
+        }
+        std::lock_guard<std::mutex> lock(mu_);
+        if (!usable_) return;
+        cudaSetDevice(device_);
+        for (auto &[u, p] : peers_) unmap_peer(p);
+        peers_.clear();
+        for (auto &s : slots_) {
+            if (s.stream) cudaStreamSynchronize(s.stream);
+            if (s.stream) cudaStreamDestroy(s.stream);
+            if (s.start) cudaEventDestroy(s.start);
+            if (s.stop) cudaEventDestroy(s.stop);
+            if (s.host_words) cudaFreeHost(s.host_words);
+            if (s.backup) cudaFree(s.backup);
+        }
+        slots_.clear();
+        if (util_stream_) cudaStreamDestroy(util_stream_), util_stream_ = nullptr;
+        if (arena_ptr_) {
+            driver().MemUnmap(arena_ptr_, arena_bytes_);
+            driver().MemAddressFree(arena_ptr_, arena_bytes_);
+            driver().MemRelease(arena_handle_);
+            arena_ptr_ = 0;
+        }
+    }
+
+    void on_ring_changed(const std::vector<Uuid> &ring) override {
+        std::lock_guard<std::mutex> lock(mu_);
+        ring_ = ring;
+        ring_ready_ = false;
+        if (!usable_ || !started_ || ring.size() < 2 || ring.size() > PCCL_K_MAX_RANKS) return;
+        cudaSetDevice(device_);
+        if (!ensure_arena()) return;
+        // forget peers that left
+        for (auto it = peers_.begin(); it != peers_.end();) {
+            if (std::find(ring.begin(), ring.end(), it->first) == ring.end()) {
+                unmap_peer(it->second);
+                it = peers_.erase(it);
+            } else {
+                ++it;
+            }
+        }
+        bool all = true;
+        for (const auto &u : ring) {
+            if (u == self_ || peers_.count(u)) continue;
+            Peer p;
+            if (fetch_peer(u, p)) {
+                peers_.emplace(u, p);
+            } else {
+                all = false;
+                break; // a peer on another host / without a GPU: this ring uses the TCP plane
+            }
+        }
+        if (!all) return;
+        // same geometry everywhere, one GPU per peer (kernels of two ranks that wait for each
+        // other must never share a GPU)
+        std::vector<std::array<uint8_t, 16>> gpus;
+        std::array<uint8_t, 16> mine;
+        std::memcpy(mine.data(), gpu_uuid_, 16);
+        gpus.push_back(mine);
+        for (const auto &[u, p] : peers_) {
+            if (p.bytes != arena_bytes_ || p.slot_bytes != slot_bytes_ || p.n_slots != n_slots_) return;
+            std::array<uint8_t, 16> g;
+            std::memcpy(g.data(), p.gpu_uuid, 16);
+            if (std::find(gpus.begin(), gpus.end(), g) != gpus.end()) {
+                PLOG(INFO) << "two peers of the ring share one GPU: device plane disabled for this ring";
+                return;
+            }
+            gpus.push_back(g);
+        }
+        ring_ready_ = true;
+        PLOG(INFO) << "device plane ready: " << ring.size() << " peers mapped over NVLink";
+    }
+
+    bool can_reduce(const DeviceReduceArgs &a) override {
+        std::lock_guard<std::mutex> lock(mu_);
+        if (!ring_ready_ || a.world != ring_.size()) return false;
+        const PointerInfo s = classify_pointer(a.src), d = classify_pointer(a.dst);
+        if (!s.is_device || !d.is_device || s.device != device_ || d.device != device_) return false;
+        if (a.dtype == wire::DType::F8E4M3) return false;
+        switch (a.quant) {
+        case wire::QuantAlgo::None: return true;
+        // on the device plane uint8 min-max is block-scaled (128 elements per (min,max) pair)
+        case wire::QuantAlgo::MinMax:
+        case wire::QuantAlgo::BlockMinMax: return a.dtype == wire::DType::F32 && a.quant_dtype == wire::DType::U8;
+        case wire::QuantAlgo::BlockFp8: return a.dtype == wire::DType::F32 && a.quant_dtype == wire::DType::F8E4M3;
+        default: return false;
+        }
+    }
+
+    DeviceReduceResult reduce(const DeviceReduceArgs &a, const std::function<bool()> &abort_requested) override {
+        DeviceReduceResult res;
+        std::vector<void *> arenas;
+        {
+            std::lock_guard<std::mutex> lock(mu_);
+            if (!ring_ready_ || a.world != ring_.size()) return res;
+            for (const auto &u : ring_) arenas.push_back(u == self_ ? reinterpret_cast<void *>(arena_ptr_) : reinterpret_cast<void *>(peers_.at(u).ptr));
+        }
+        cudaSetDevice(device_);
+        Slot &slot = slots_[a.seq % n_slots_];
+        std::lock_guard<std::mutex> slot_lock(slot.mu); // one operation per slot at a time
+        const size_t esz = wire::dtype_size(a.dtype);
+        const int dtype = pccl_dtype(a.dtype), op = pccl_op(a.op), quant = kernel_quant(a.quant);
+        const bool in_place = a.src == a.dst;
+
+        // symmetric memory: the buffer itself is peer-visible, no staging copy
+        const auto base = static_cast<uintptr_t>(arena_ptr_);
+        const auto p = reinterpret_cast<uintptr_t>(a.src);
+        const bool symmetric = in_place && quant == 0 && sym_bytes_ > 0 && p >= base + sym_offset() && p + a.count * esz <= base + arena_bytes_;
+
+        // rounds: the staging slot bounds how much one launch can move
+        uint64_t per_round = a.count;
+        if (!symmetric) {
+            const size_t need = pcclKernelP2PStagingBytes(a.count, dtype, quant);
+            if (need > slot_bytes_) {
+                const uint64_t unit = 32 * 4 * a.world * 16; // keeps chunk and quantisation-block alignment
+                per_round = (slot_bytes_ - 4096) / (quant ? 2 : esz);
+                per_round = std::max<uint64_t>(unit, per_round / unit * unit);
+            }
+        }
+        const uint64_t n_rounds = (a.count + per_round - 1) / per_round;
+        if (n_rounds > 255) return res;
+
+        if (in_place && !symmetric) {
+            // keep the input for a rollback (the staging slot only holds the last round)
+            if (slot.backup_bytes < a.count * esz) {
+                if (slot.backup) cudaFree(slot.backup);
+                slot.backup = nullptr;
+                slot.backup_bytes = 0;
+                if (cudaMalloc(&slot.backup, a.count * esz) != cudaSuccess) {
+                    (void) cudaGetLastError();
+                    return res;
+                }
+                slot.backup_bytes = a.count * esz;
+            }
+        }
+
+        // inputs may still be in flight on the legacy default stream
+        cudaEventRecord(slot.ready, cudaStreamLegacy);
+        cudaStreamWaitEvent(slot.stream, slot.ready, 0);
+        slot.host_words[0] = 0; // abort flag
+        slot.host_words[1] = 0; // status
+        cudaEventRecord(slot.start, slot.stream);
+        if (in_place && !symmetric) cudaMemcpyAsync(slot.backup, a.src, a.count * esz, cudaMemcpyDeviceToDevice, slot.stream);
+        slot.backup_valid = in_place && !symmetric;
+
+        int algorithm = 0;
+        for (uint64_t r = 0; r < n_rounds; ++r) {
+            const uint64_t off = r * per_round, n = std::min(per_round, a.count - off);
+            pcclKernelP2PArgs_t k{};
+            for (size_t i = 0; i < arenas.size(); ++i) k.arena[i] = arenas[i];
+            k.rank = a.rank;
+            k.world = a.world;
+            k.flag_slot = static_cast<uint32_t>(a.seq % n_slots_);
+            k.flag_base = (a.seq + 1) * 1024 + r * 4;
+            k.data_offset = symmetric ? (p - base) + off * esz : slot_offset(a.seq % n_slots_);
+            k.data_capacity = symmetric ? n * esz + 512 : slot_bytes_;
+            k.src = static_cast<const uint8_t *>(a.src) + off * esz;
+            k.dst = static_cast<uint8_t *>(a.dst) + off * esz;
+            k.count = n;
+            k.dtype = dtype;
+            k.op = op;
+            k.quant_algorithm = quant;
+            k.algorithm = 0;
+            k.max_blocks = max_blocks_;
+            k.src_in_arena = symmetric ? 1 : 0;
+            k.abort_flag = reinterpret_cast<volatile uint32_t *>(slot.host_words);
+            k.status = slot.host_words + 1;
+            k.timeout_cycles = timeout_ms_ * static_cast<uint64_t>(clock_khz_);
+            const int rc = pcclKernelAllReduceP2P(&k, &algorithm, slot.stream);
+            if (rc != 0) {
+                PLOG(ERR) << "all-reduce kernel launch failed: " << cudaGetErrorString(static_cast<cudaError_t>(rc));
+                cudaStreamSynchronize(slot.stream);
+                return res;
+            }
+        }
+        cudaEventRecord(slot.stop, slot.stream);
+        res.kernel_launches = static_cast<uint32_t>(n_rounds);
+
+        // wait, relaying aborts from the control plane into the kernel
+        int polls = 0;
+        for (;;) {
+            const cudaError_t q = cudaEventQuery(slot.stop);
+            if (q == cudaSuccess) break;
+            if (q != cudaErrorNotReady) {
+                PLOG(ERR) << "device all-reduce failed: " << cudaGetErrorString(q);
+                (void) cudaGetLastError();
+                return res;
+            }
+            if ((++polls & 63) == 0 && abort_requested && abort_requested()) {
+                reinterpret_cast<volatile uint32_t *>(slot.host_words)[0] = 1;
+                res.aborted = true;
+            }
+            if (polls > 2000) std::this_thread::sleep_for(std::chrono::microseconds(50));
+        }
+        const uint32_t status = reinterpret_cast<volatile uint32_t *>(slot.host_words)[1];
+        cudaEventElapsedTime(&res.device_ms, slot.start, slot.stop);
+        res.plane = algorithm == 1 ? pcclExtPlaneP2POneShot : pcclExtPlaneP2PTwoShot;
+        const uint64_t wire_bytes = quant ? a.count : a.count * esz;
+        res.tx_bytes = res.rx_bytes = algorithm == 1 ? wire_bytes * (a.world - 1) : 2 * wire_bytes * (a.world - 1) / a.world;
+        res.ok = status == 0;
+        if (status == 2) PLOG(ERR) << "device all-reduce timed out waiting for a peer";
+        return res;
+    }
+
+    bool restore_input(const DeviceReduceArgs &a) override {
+        if (!usable_ || slots_.empty()) return false;
+        cudaSetDevice(device_);
+        Slot &slot = slots_[a.seq % n_slots_];
+        std::lock_guard<std::mutex> slot_lock(slot.mu);
+        if (!slot.backup_valid || !slot.backup) return false;
+        const size_t bytes = a.count * wire::dtype_size(a.dtype);
+        if (cudaMemcpyAsync(a.dst, slot.backup, bytes, cudaMemcpyDeviceToDevice, slot.stream) != cudaSuccess) return false;
+        return cudaStreamSynchronize(slot.stream) == cudaSuccess;
+    }
+
+    bool copy_to_host(void *host_dst, const void *dev_src, size_t bytes) override { return copy(host_dst, dev_src, bytes, cudaMemcpyDeviceToHost); }
+    bool copy_to_device(void *dev_dst, const void *host_src, size_t bytes) override { return copy(dev_dst, host_src, bytes, cudaMemcpyHostToDevice); }
+
+    bool hash_device(const void *dev_ptr, size_t bytes, wire::HashType type, uint64_t &out) override {
+        if (!cuda_runtime_usable()) return false;
+        const PointerInfo info = classify_pointer(dev_ptr);
+        int prev = -1;
+        cudaGetDevice(&prev);
+        if (info.is_device && info.device >= 0) cudaSetDevice(info.device);
+        const int rc = pcclKernelHashSync(dev_ptr, bytes, type == wire::HashType::Simple ? 0 : 1, &out);
+        if (prev >= 0) cudaSetDevice(prev);
+        if (rc != 0) PLOG(ERR) << "device hash failed: " << cudaGetErrorString(static_cast<cudaError_t>(rc));
+        return rc == 0;
+    }
+
+    void *symmetric_alloc(size_t bytes) override {
+        std::lock_guard<std::mutex> lock(mu_);
+        if (!usable_ || sym_bytes_ == 0) return nullptr;
+        cudaSetDevice(device_);
+        if (!ensure_arena()) return nullptr;
+        bytes = round_up(bytes, 512);
+        // first fit over the gaps between live allocations (same call order on every peer gives
+        // the same offsets, which is what makes the memory "symmetric")
+        size_t cursor = 0;
+        for (const auto &[off, len] : sym_allocs_) {
+            if (off - cursor >= bytes) break;
+            cursor = off + len;
+        }
+        if (cursor + bytes > sym_bytes_) return nullptr;
+        sym_allocs_[cursor] = bytes;
+        return reinterpret_cast<void *>(arena_ptr_ + sym_offset() + cursor);
+    }
+
+    bool symmetric_free(void *ptr) override {
+        std::lock_guard<std::mutex> lock(mu_);
+        if (!arena_ptr_) return false;
+        const auto off = reinterpret_cast<uintptr_t>(ptr) - (arena_ptr_ + sym_offset());
+        return sym_allocs_.erase(off) > 0;
+    }
+
+private:
+    struct Peer {
+        CUdeviceptr ptr = 0;
+        size_t bytes = 0, slot_bytes = 0;
+        uint32_t n_slots = 0;
+        CUmemGenericAllocationHandle handle = 0;
+        uint8_t gpu_uuid[16] = {0};
+    };
+    struct Slot {
+        std::mutex mu;
+        cudaStream_t stream = nullptr;
+        cudaEvent_t start = nullptr, stop = nullptr, ready = nullptr;
+        uint32_t *host_words = nullptr; // [0] abort flag, [1] status; host-mapped
+        void *backup = nullptr;
+        size_t backup_bytes = 0;
+        bool backup_valid = false;
+    };
+
+    size_t slot_offset(uint64_t slot) const { return pcclKernelP2PControlBytes() + slot * slot_bytes_; }
+    size_t sym_offset() const { return pcclKernelP2PControlBytes() + size_t(n_slots_) * slot_bytes_; }
+
+    static int pccl_dtype(wire::DType t) {
+        switch (t) {
+        case wire::DType::U8: return pcclUint8;
+        case wire::DType::I8: return pcclInt8;
+        case wire::DType::U16: return pcclUint16;
+        case wire::DType::I16: return pcclInt16;
+        case wire::DType::U32: return pcclUint32;
+        case wire::DType::I32: return pcclInt32;
+        case wire::DType::U64: return pcclUint64;
+        case wire::DType::I64: return pcclInt64;
+        case wire::DType::F16: return pcclFloat16;
+        case wire::DType::BF16: return pcclBFloat16;
+        case wire::DType::F32: return pcclFloat;
+        case wire::DType::F64: return pcclDouble;
+        default: return -1;
+        }
+    }
+    static int pccl_op(wire::RedOp op) {
+        switch (op) {
+        case wire::RedOp::Sum: return pcclSum;
+        case wire::RedOp::Avg: return pcclAvg;
+        case wire::RedOp::Prod: return pcclProd;
+        case wire::RedOp::Max: return pcclMax;
+        case wire::RedOp::Min: return pcclMin;
+        default: return -1;
+        }
+    }
+    static int kernel_quant(wire::QuantAlgo q) {
+        switch (q) {
+        case wire::QuantAlgo::MinMax:
+        case wire::QuantAlgo::BlockMinMax: return pcclQuantBlockMinMax;
+        case wire::QuantAlgo::BlockFp8: return pcclQuantBlockFp8;
+        default: return pcclQuantNone;
+        }
+    }
+
+    // mu_ held, device current
+    bool ensure_arena() {
+        if (arena_ptr_) return true;
+        const Driver &d = driver();
+        CUmemAllocationProp prop{};
+        prop.type = CU_MEM_ALLOCATION_TYPE_PINNED;
+        prop.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
+        prop.location.id = device_;
+        prop.requestedHandleTypes = CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR;
+        size_t gran = 2u << 20;
+        CU_TRY(d.MemGetAllocationGranularity(&gran, &prop, CU_MEM_ALLOC_GRANULARITY_RECOMMENDED));
+        arena_bytes_ = round_up(pcclKernelP2PControlBytes() + size_t(n_slots_) * slot_bytes_ + sym_bytes_, gran);
+        CU_TRY(d.MemCreate(&arena_handle_, arena_bytes_, &prop, 0));
+        CU_TRY(d.MemAddressReserve(&arena_ptr_, arena_bytes_, gran, 0, 0));
+        CU_TRY(d.MemMap(arena_ptr_, arena_bytes_, 0, arena_handle_, 0));
+        CUmemAccessDesc acc{};
+        acc.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
+        acc.location.id = device_;
+        acc.flags = CU_MEM_ACCESS_FLAGS_PROT_READWRITE;
+        CU_TRY(d.MemSetAccess(arena_ptr_, arena_bytes_, &acc, 1));
+        RT_TRY(cudaMemset(reinterpret_cast<void *>(arena_ptr_), 0, pcclKernelP2PControlBytes()));
+        RT_TRY(cudaDeviceSynchronize());
+        slots_ = std::vector<Slot>(n_slots_);
+        for (auto &s : slots_) {
+            RT_TRY(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
+            RT_TRY(cudaEventCreate(&s.start));
+            RT_TRY(cudaEventCreate(&s.stop));
+            RT_TRY(cudaEventCreateWithFlags(&s.ready, cudaEventDisableTiming));
+            RT_TRY(cudaHostAlloc(reinterpret_cast<void **>(&s.host_words), 64, cudaHostAllocMapped));
+            std::memset(s.host_words, 0, 64);
+        }
+        PLOG(INFO) << "device arena of " << (arena_bytes_ >> 20) << " MiB on GPU " << device_;
+        return true;
+    }
+
+    void unmap_peer(Peer &p) {
+        if (!p.ptr) return;
+        driver().MemUnmap(p.ptr, p.bytes);
+        driver().MemAddressFree(p.ptr, p.bytes);
+        driver().MemRelease(p.handle);
+        p.ptr = 0;
+    }
+
+    // mu_ held, device current
+    bool fetch_peer(const Uuid &who, Peer &out) {
+        const int sock = ::socket(AF_UNIX, SOCK_STREAM | SOCK_CLOEXEC, 0);
+        if (sock < 0) return false;
+        socklen_t len;
+        const sockaddr_un sa = rendezvous_address(who, len);
+        bool connected = false;
+        for (int attempt = 0; attempt < 40 && !connected; ++attempt) {
+            if (::connect(sock, reinterpret_cast<const sockaddr *>(&sa), len) == 0)
+                connected = true;
+            else if (attempt < 2 || errno != ECONNREFUSED)
+                std::this_thread::sleep_for(std::chrono::milliseconds(25));
+            else
+                break; // nobody listens under that name: the peer is not on this host
+        }
+        if (!connected) {
+            ::close(sock);
+            return false;
+        }
+        RendezvousRequest req{kMagic, kReqArena, {0}};
+        std::memcpy(req.requester, self_.data.data(), 16);
+        RendezvousReply rep{};
+        int fd = -1;
+        const bool ok = ::send(sock, &req, sizeof req, MSG_NOSIGNAL) == static_cast<ssize_t>(sizeof req) &&
+                        recv_with_fd(sock, &rep, sizeof rep, fd, 20000) && rep.magic == kMagic && rep.status == 0 && fd >= 0;
+        ::close(sock);
+        if (!ok) {
+            if (fd >= 0) ::close(fd);
+            return false;
+        }
+        const Driver &d = driver();
+        Peer p;
+        p.bytes = rep.arena_bytes;
+        p.slot_bytes = rep.slot_bytes;
+        p.n_slots = rep.n_slots;
+        std::memcpy(p.gpu_uuid, rep.gpu_uuid, 16);
+        const CUresult imp = d.MemImportFromShareableHandle(&p.handle, reinterpret_cast<void *>(static_cast<uintptr_t>(fd)), CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR);
+        ::close(fd);
+        if (imp != CUDA_SUCCESS) {
+            PLOG(WARN) << "cannot import the arena of peer " << who.str() << " (CUresult " << static_cast<int>(imp) << ")";
+            return false;
+        }
+        if (d.MemAddressReserve(&p.ptr, p.bytes, 2u << 20, 0, 0) != CUDA_SUCCESS) {
+            d.MemRelease(p.handle);
+            return false;
+        }
+        CUmemAccessDesc acc{};
+        acc.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
+        acc.location.id = device_;
+        acc.flags = CU_MEM_ACCESS_FLAGS_PROT_READWRITE;
+        if (d.MemMap(p.ptr, p.bytes, 0, p.handle, 0) != CUDA_SUCCESS || d.MemSetAccess(p.ptr, p.bytes, &acc, 1) != CUDA_SUCCESS) {
+            PLOG(WARN) << "cannot map the arena of peer " << who.str() << " (no peer access between the GPUs?)";
+            d.MemUnmap(p.ptr, p.bytes);
+            d.MemAddressFree(p.ptr, p.bytes);
+            d.MemRelease(p.handle);
+            return false;
+        }
+        out = p;
+        return true;
+    }
+
+    void serve() {
+        cudaSetDevice(device_);
+        while (!stopping_) {
+            pollfd p{listen_fd_, POLLIN, 0};
+            if (::poll(&p, 1, 100) <= 0) continue;
+            const int c = ::accept4(listen_fd_, nullptr, nullptr, SOCK_CLOEXEC);
+            if (c < 0) continue;
+            RendezvousRequest req{};
+            pollfd cp{c, POLLIN, 0};
+            RendezvousReply rep{};
+            rep.magic = kMagic;
+            rep.status = 1;
+            int fd = -1;
+            if (::poll(&cp, 1, 2000) > 0 && ::recv(c, &req, sizeof req, MSG_WAITALL) == static_cast<ssize_t>(sizeof req) &&
+                req.magic == kMagic && req.kind == kReqArena) {
+                std::lock_guard<std::mutex> lock(mu_);
+                if (ensure_arena() && driver().MemExportToShareableHandle(&fd, arena_handle_, CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR, 0) == CUDA_SUCCESS) {
+                    rep.status = 0;
+                    rep.arena_bytes = arena_bytes_;
+                    rep.slot_bytes = slot_bytes_;
+                    rep.sym_bytes = sym_bytes_;
+                    rep.n_slots = n_slots_;
+                    rep.pid = static_cast<uint32_t>(::getpid());
+                    std::memcpy(rep.gpu_uuid, gpu_uuid_, 16);
+                }
+            }
+            send_with_fd(c, &rep, sizeof rep, fd);
+            if (fd >= 0) ::close(fd);
+            ::close(c);
+        }
+    }
+
+    bool copy(void *dst, const void *src, size_t bytes, cudaMemcpyKind kind) {
+        if (!cuda_runtime_usable()) return false;
+        const PointerInfo info = classify_pointer(kind == cudaMemcpyDeviceToHost ? src : dst);
+        if (info.is_device && info.device >= 0) cudaSetDevice(info.device);
+        std::lock_guard<std::mutex> lock(copy_mu_);
+        if (!util_stream_) RT_TRY(cudaStreamCreateWithFlags(&util_stream_, cudaStreamNonBlocking));
+        if (kind == cudaMemcpyDeviceToHost) {
+            // the source may still be written by work queued on the legacy default stream
+            cudaEvent_t ready;
+            RT_TRY(cudaEventCreateWithFlags(&ready, cudaEventDisableTiming));
+            cudaEventRecord(ready, cudaStreamLegacy);
+            cudaStreamWaitEvent(util_stream_, ready, 0);
+            cudaEventDestroy(ready);
+        }
+        RT_TRY(cudaMemcpyAsync(dst, src, bytes, kind, util_stream_));
+        RT_TRY(cudaStreamSynchronize(util_stream_));
+        return true;
+    }
+
+    bool usable_ = false, started_ = false;
+    std::atomic<bool> stopping_{false};
+    int device_ = 0;
+    int clock_khz_ = 1900000;
+    uint8_t gpu_uuid_[16] = {0};
+    Uuid self_;
+    int listen_fd_ = -1;
+    std::thread server_;
+
+    std::mutex mu_;
+    size_t slot_bytes_ = 0, sym_bytes_ = 0, arena_bytes_ = 0;
+    uint32_t n_slots_ = 4;
+    uint64_t timeout_ms_ = 30000;
+    int max_blocks_ = 0;
+    CUdeviceptr arena_ptr_ = 0;
+    CUmemGenericAllocationHandle arena_handle_ = 0;
+    std::vector<Slot> slots_;
+    std::map<size_t, size_t> sym_allocs_;
+    std::unordered_map<Uuid, Peer> peers_;
+    std::vector<Uuid> ring_;
+    bool ring_ready_ = false;
+
+    std::mutex copy_mu_;
+    cudaStream_t util_stream_ = nullptr;
+};
+
+} // namespace
+
+bool cuda_runtime_usable() {
+    static const bool ok = [] {
+        int n = 0;
+        const cudaError_t rc = cudaGetDeviceCount(&n);
+        if (rc != cudaSuccess) (void) cudaGetLastError();
+        return rc == cudaSuccess && n > 0;
+    }();
+    return ok;
+}
+
+PointerInfo classify_pointer(const void *p) {
+    PointerInfo info;
+    if (!p || !cuda_runtime_usable()) return info;
+    cudaPointerAttributes attr{};
+    if (cudaPointerGetAttributes(&attr, p) != cudaSuccess) {
+        (void) cudaGetLastError();
+        return info;
+    }
+    if (attr.type == cudaMemoryTypeDevice || attr.type == cudaMemoryTypeManaged) {
+        info.is_device = true;
+        info.device = attr.device;
+    }
+    return info;
+}
+
+std::unique_ptr<Plane> Plane::create() { return std::make_unique<CudaPlane>(); }
+
+} // namespace pccl::device
+#endif // PCCL_NO_CUDA

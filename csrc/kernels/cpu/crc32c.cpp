@@ -1,6 +1,7 @@
 #include <atomic>
 #include <cstring>
 
+#include "../crc_gf.hpp"
 #include "hash.hpp"
 
 #if defined(__x86_64__)
@@ -11,7 +12,7 @@ namespace pccl::cpu {
 
 namespace {
 
-constexpr uint32_t kPoly = 0x82F63B78u; // reflected Castagnoli polynomial
+constexpr uint32_t kPoly = gf::kCrc32cPoly; // reflected Castagnoli polynomial
 
 struct Tables {
     uint32_t slice[8][256];
@@ -21,26 +22,9 @@ struct Tables {
 };
 constexpr size_t kLong = 8192, kShort = 256;
 
-// GF(2) helpers on 32-bit polynomials in reflected representation.
-uint32_t gf_mul(uint32_t a, uint32_t b) { // a*b mod P
-    uint32_t p = 0;
-    for (int i = 0; i < 32; ++i) {
-        if (a & 0x80000000u) p ^= b; // reflected: bit 31 is x^0
-        a <<= 1;
-        b = (b >> 1) ^ ((b & 1u) ? kPoly : 0u);
-    }
-    return p;
-}
-uint32_t gf_x_pow_bits(uint64_t bits) { // x^bits mod P
-    uint32_t result = 0x80000000u;      // 1
-    uint32_t base = 0x40000000u;        // x
-    while (bits) {
-        if (bits & 1) result = gf_mul(result, base);
-        base = gf_mul(base, base);
-        bits >>= 1;
-    }
-    return result;
-}
+using gf::mul;
+inline uint32_t gf_mul(uint32_t a, uint32_t b) { return gf::mul(a, b); }
+inline uint32_t gf_x_pow_bits(uint64_t bits) { return gf::x_pow(bits); }
 
 void build_shift_table(uint32_t table[4][256], size_t n_bytes) {
     const uint32_t factor = gf_x_pow_bits(static_cast<uint64_t>(n_bytes) * 8);

@@ -1,0 +1,500 @@
+// All-reduce between GPUs that can address each other's memory (NVLink 5 / NVSwitch).
+//
+// There is no counterpart in the reference: its all-reduce is a host-memory TCP ring
+// (ccoip/src/cpp/reduce.cpp:528-784, element kernels reduce_kernels.cpp:56-215, AVG :437-510, min-max
+// quantiser quantize_kernels.cpp:24-217).  This file replaces that whole path for peers in one
+// NVLink domain with a single kernel launch per rank that fuses staging, reduction, AVG
+// finalisation and (optionally) block-scaled quantise -> reduce -> dequantise.
+//
+// Memory model.  Every rank owns an "arena" that all ranks have mapped.  It starts with a
+// control page of barrier flags, staging data follows at `data_offset`.
+//   flags[slot][block][src_rank] : u64, written with st.release.sys by block `block` of rank
+//   `src_rank`, polled with ld.acquire.sys by the same block of the owner.
+// Flag values only grow (the caller derives them from the master's sequence number), so values
+// left behind by an aborted operation can never satisfy a later wait.
+//
+// Work partition.  Data is cut into tiles of THREADS 16-byte packets.  Tile t belongs to block
+// t % gridDim.x ON EVERY RANK AND IN EVERY PHASE.  A block therefore only ever consumes data that
+// the same-numbered block of a peer produced, which is what makes per-block barriers sufficient
+// (no grid-wide synchronisation, no cooperative launch) and lets blocks run ahead of each other.
+//
+// Two-shot algorithm (bandwidth regime):
+//   phase 0  copy own input into own arena                      (skipped for symmetric memory)
+//   barrier
+//   phase 1  rank r reduces chunk r: reads chunk r of every peer's arena, reduces in rank order,
+//            applies AVG, writes the result to its arena AND to its own output
+//   barrier
+//   phase 2  reads the reduced chunks of all other ranks from their arenas into the output
+//   barrier  (nobody may overwrite an arena a peer is still reading)
+// One-shot algorithm (latency regime): phase 0, barrier, every rank reduces everything, barrier.
+//
+// Every spin is bounded: it polls a host-mapped abort word (set by the control thread when the
+// master aborts the operation or a peer dies) and a cycle budget.
+#include <cstdio>
+
+#include "common.cuh"
+#include "pccl_kernels.h"
+#include "quant.cuh"
+
+namespace pccl::cuda {
+
+constexpr int kThreads = 512;
+constexpr size_t kFlagBankBytes = size_t(PCCL_K_MAX_BLOCKS) * 128; // one 128-byte line per block
+constexpr int kFlagBanks = 16;
+constexpr size_t kControlBytes = 1u << 20;
+static_assert(kFlagBanks * kFlagBankBytes <= kControlBytes, "control page too small");
+static_assert(PCCL_K_MAX_RANKS * 8 <= 128, "flag line too small");
+
+struct DevArgs {
+    uint8_t *arena[PCCL_K_MAX_RANKS];
+    uint32_t rank, world, flag_slot;
+    uint64_t flag_base, data_offset;
+    const void *src;
+    void *dst;
+    uint64_t count;
+    uint64_t avg_divisor; // 0: none
+    int src_in_arena;
+    volatile uint32_t *abort_flag;
+    uint32_t *status;
+    uint64_t timeout_cycles;
+};
+
+// Peer base pointers live in shared memory: they are indexed with run-time rank numbers, and
+// a run-time index into kernel parameters would be demoted to a per-thread stack copy.
+struct PeerTable {
+    uint8_t *base[PCCL_K_MAX_RANKS];
+};
+__device__ __forceinline__ void load_peer_table(PeerTable &t, const DevArgs &a) {
+    if (threadIdx.x < PCCL_K_MAX_RANKS) t.base[threadIdx.x] = threadIdx.x < a.world ? a.arena[threadIdx.x] + a.data_offset : nullptr;
+    __syncthreads();
+}
+constexpr int kPeerGroup = 8; // peers whose loads are kept in flight together
+
+__device__ __forceinline__ uint64_t *flag_ptr(const DevArgs &a, uint8_t *arena_base, uint32_t block, uint32_t writer) {
+    return reinterpret_cast<uint64_t *>(arena_base + a.flag_slot * kFlagBankBytes + size_t(block) * 128) + writer;
+}
+
+// Cross-GPU barrier among the same-numbered blocks of all ranks.  Returns false when the
+// operation was aborted or timed out (uniform across the block).
+__device__ bool peer_barrier(const DevArgs &a, const PeerTable &t, uint64_t value) {
+    __shared__ int s_fail;
+    if (threadIdx.x == 0) s_fail = 0;
+    __syncthreads(); // this block's earlier writes are ordered before the flag stores below
+    if (threadIdx.x < a.world) {
+        const uint32_t peer = threadIdx.x;
+        st_flag_release(flag_ptr(a, t.base[peer] - a.data_offset, blockIdx.x, a.rank), value);
+        const uint64_t *mine = flag_ptr(a, t.base[a.rank] - a.data_offset, blockIdx.x, peer);
+        const long long t0 = clock64();
+        uint32_t spins = 0;
+        while (ld_flag_acquire(mine) < value) {
+            if ((++spins & 0x3ffu) == 0) {
+                if (*a.abort_flag != 0) {
+                    atomicExch(&s_fail, 1);
+                    break;
+                }
+                if (static_cast<uint64_t>(clock64() - t0) > a.timeout_cycles) {
+                    atomicExch(&s_fail, 2);
+                    break;
+                }
+            }
+        }
+    }
+    __syncthreads();
+    const int fail = s_fail;
+    if (fail != 0 && threadIdx.x == 0) atomicMax(a.status, static_cast<uint32_t>(fail));
+    return fail == 0;
+}
+
+// Iterates over the packets of [lo, hi) that belong to this block, U tiles at a time.
+// fn(v[], n_valid) gets up to U packet indices (all < hi).
+template <int U, typename Fn> __device__ __forceinline__ void for_owned_packets(uint64_t lo, uint64_t hi, Fn fn) {
+    if (lo >= hi) return;
+    const uint64_t first_tile = lo / kThreads;
+    // smallest tile >= first_tile owned by this block
+    uint64_t tile = first_tile + ((blockIdx.x + gridDim.x - first_tile % gridDim.x) % gridDim.x);
+    const uint64_t stride = uint64_t(gridDim.x) * U;
+    for (; tile * kThreads < hi; tile += stride) {
+        uint64_t v[U];
+        bool ok[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            v[u] = (tile + uint64_t(u) * gridDim.x) * kThreads + threadIdx.x;
+            ok[u] = v[u] >= lo && v[u] < hi;
+        }
+        fn(v, ok);
+    }
+}
+
+template <typename T> __device__ __forceinline__ uint4 load_input(const T *src, uint64_t v, uint64_t count, bool aligned) {
+    constexpr int N = 16 / sizeof(T);
+    const uint64_t e = v * N;
+    if (aligned && e + N <= count) return ld_stream_16(src + e);
+    Pack<T> p;
+#pragma unroll
+    for (int i = 0; i < N; ++i) p.v[i] = e + i < count ? src[e + i] : T{};
+    return *reinterpret_cast<uint4 *>(&p);
+}
+
+template <typename T> __device__ __forceinline__ void store_output(T *dst, uint64_t v, uint64_t count, bool aligned, uint4 val) {
+    constexpr int N = 16 / sizeof(T);
+    const uint64_t e = v * N;
+    if (aligned && e + N <= count) {
+        st_stream_16(dst + e, val);
+        return;
+    }
+    const Pack<T> p = *reinterpret_cast<Pack<T> *>(&val);
+#pragma unroll
+    for (int i = 0; i < N; ++i)
+        if (e + i < count) dst[e + i] = p.v[i];
+}
+
+template <typename T, int OP> __device__ __forceinline__ void accumulate(typename Elem<T>::acc_t (&acc)[16 / sizeof(T)], uint4 raw, bool first) {
+    constexpr int N = 16 / sizeof(T);
+    const Pack<T> p = *reinterpret_cast<const Pack<T> *>(&raw);
+#pragma unroll
+    for (int i = 0; i < N; ++i) {
+        const auto x = Elem<T>::load(p.v[i]);
+        acc[i] = first ? x : combine<OP>(acc[i], x);
+    }
+}
+
+template <typename T> __device__ __forceinline__ uint4 finish(typename Elem<T>::acc_t (&acc)[16 / sizeof(T)], uint64_t avg_divisor) {
+    constexpr int N = 16 / sizeof(T);
+    using A = typename Elem<T>::acc_t;
+    Pack<T> p;
+#pragma unroll
+    for (int i = 0; i < N; ++i) {
+        A x = acc[i];
+        if (avg_divisor) x = x / static_cast<A>(avg_divisor);
+        p.v[i] = Elem<T>::store(x);
+    }
+    return *reinterpret_cast<uint4 *>(&p);
+}
+
+// -----------------------------------------------------------------------------------------
+// two-shot, unquantised
+// -----------------------------------------------------------------------------------------
+template <typename T, int OP> __global__ void __launch_bounds__(kThreads, 1) allreduce_two_shot_kernel(const DevArgs a) {
+    constexpr int N = 16 / sizeof(T);
+    __shared__ PeerTable tbl;
+    load_peer_table(tbl, a);
+    const uint64_t n_pack = (a.count + N - 1) / N;
+    const uint64_t per = (n_pack + a.world - 1) / a.world; // packets per chunk
+    const T *src = static_cast<const T *>(a.src);
+    T *dst = static_cast<T *>(a.dst);
+    const bool src_aligned = (reinterpret_cast<uintptr_t>(src) & 15) == 0, dst_aligned = (reinterpret_cast<uintptr_t>(dst) & 15) == 0;
+    uint4 *mine = reinterpret_cast<uint4 *>(tbl.base[a.rank]);
+
+    // phase 0: stage the input where the peers can read it
+    if (!a.src_in_arena) {
+        for_owned_packets<4>(0, n_pack, [&](const uint64_t(&v)[4], const bool(&ok)[4]) {
+            uint4 tmp[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+                if (ok[u]) tmp[u] = load_input(src, v[u], a.count, src_aligned);
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+                if (ok[u]) mine[v[u]] = tmp[u];
+        });
+    }
+    if (!peer_barrier(a, tbl, a.flag_base + 1)) return;
+
+    // phase 1: reduce the chunk this rank owns, peers in rank order (deterministic result)
+    {
+        const uint64_t lo = min(uint64_t(a.rank) * per, n_pack), hi = min(lo + per, n_pack);
+        for_owned_packets<2>(lo, hi, [&](const uint64_t(&v)[2], const bool(&ok)[2]) {
+            typename Elem<T>::acc_t acc[2][N];
+            for (uint32_t r0 = 0; r0 < a.world; r0 += kPeerGroup) {
+                uint4 raw[2][kPeerGroup];
+#pragma unroll
+                for (int u = 0; u < 2; ++u)
+#pragma unroll
+                    for (int g = 0; g < kPeerGroup; ++g)
+                        if (r0 + g < a.world && ok[u]) raw[u][g] = ld_peer_16(reinterpret_cast<const uint4 *>(tbl.base[r0 + g]) + v[u]);
+#pragma unroll
+                for (int u = 0; u < 2; ++u)
+#pragma unroll
+                    for (int g = 0; g < kPeerGroup; ++g)
+                        if (r0 + g < a.world && ok[u]) accumulate<T, OP>(acc[u], raw[u][g], r0 + g == 0);
+            }
+#pragma unroll
+            for (int u = 0; u < 2; ++u) {
+                if (!ok[u]) continue;
+                const uint4 out = finish<T>(acc[u], a.avg_divisor);
+                mine[v[u]] = out;
+                store_output(dst, v[u], a.count, dst_aligned, out);
+            }
+        });
+    }
+    if (!peer_barrier(a, tbl, a.flag_base + 2)) return;
+
+    // phase 2: collect the other ranks' reduced chunks, starting with the right-hand neighbour
+    // so that at any moment the ranks pull from different peers
+    for (uint32_t k = 1; k < a.world; ++k) {
+        const uint32_t peer = (a.rank + k) % a.world;
+        const uint4 *from = reinterpret_cast<const uint4 *>(tbl.base[peer]);
+        const uint64_t lo = min(uint64_t(peer) * per, n_pack), hi = min(lo + per, n_pack);
+        for_owned_packets<4>(lo, hi, [&](const uint64_t(&v)[4], const bool(&ok)[4]) {
+            uint4 tmp[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+                if (ok[u]) tmp[u] = ld_peer_16(from + v[u]);
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+                if (ok[u]) store_output(dst, v[u], a.count, dst_aligned, tmp[u]);
+        });
+    }
+    peer_barrier(a, tbl, a.flag_base + 3);
+}
+
+// -----------------------------------------------------------------------------------------
+// one-shot, unquantised
+// -----------------------------------------------------------------------------------------
+template <typename T, int OP> __global__ void __launch_bounds__(kThreads, 1) allreduce_one_shot_kernel(const DevArgs a) {
+    constexpr int N = 16 / sizeof(T);
+    __shared__ PeerTable tbl;
+    load_peer_table(tbl, a);
+    const uint64_t n_pack = (a.count + N - 1) / N;
+    const T *src = static_cast<const T *>(a.src);
+    T *dst = static_cast<T *>(a.dst);
+    const bool src_aligned = (reinterpret_cast<uintptr_t>(src) & 15) == 0, dst_aligned = (reinterpret_cast<uintptr_t>(dst) & 15) == 0;
+    uint4 *mine = reinterpret_cast<uint4 *>(tbl.base[a.rank]);
+    if (!a.src_in_arena) {
+        for_owned_packets<1>(0, n_pack, [&](const uint64_t(&v)[1], const bool(&ok)[1]) {
+            if (ok[0]) mine[v[0]] = load_input(src, v[0], a.count, src_aligned);
+        });
+    }
+    if (!peer_barrier(a, tbl, a.flag_base + 1)) return;
+    for_owned_packets<1>(0, n_pack, [&](const uint64_t(&v)[1], const bool(&ok)[1]) {
+        if (!ok[0]) return;
+        typename Elem<T>::acc_t acc[N];
+        for (uint32_t r0 = 0; r0 < a.world; r0 += kPeerGroup) { // fixed order: bit-identical on every rank
+            uint4 raw[kPeerGroup];
+#pragma unroll
+            for (int g = 0; g < kPeerGroup; ++g)
+                if (r0 + g < a.world) raw[g] = ld_peer_16(reinterpret_cast<const uint4 *>(tbl.base[r0 + g]) + v[0]);
+#pragma unroll
+            for (int g = 0; g < kPeerGroup; ++g)
+                if (r0 + g < a.world) accumulate<T, OP>(acc, raw[g], r0 + g == 0);
+        }
+        store_output(dst, v[0], a.count, dst_aligned, finish<T>(acc, a.avg_divisor));
+    });
+    peer_barrier(a, tbl, a.flag_base + 2);
+}
+
+// -----------------------------------------------------------------------------------------
+// two-shot with block-scaled wire format (fp32 in memory, 1 byte per element on NVLink)
+//   staging layout: [u32 codes, one per float4][block records, one per 32 float4]
+// -----------------------------------------------------------------------------------------
+template <int ALGO, int OP> __global__ void __launch_bounds__(kThreads, 1) allreduce_two_shot_quant_kernel(const DevArgs a) {
+    constexpr int MB = QuantMeta<ALGO>::kBytes;
+    const uint64_t n_pack = (a.count + 3) / 4;                 // float4 packets
+    const uint64_t n_pack_pad = (n_pack + 31) / 32 * 32;       // whole quantisation blocks
+    const uint64_t per = ((n_pack_pad / 32 + a.world - 1) / a.world) * 32; // chunk = whole blocks
+    const float *src = static_cast<const float *>(a.src);
+    float *dst = static_cast<float *>(a.dst);
+    const bool src_aligned = (reinterpret_cast<uintptr_t>(src) & 15) == 0, dst_aligned = (reinterpret_cast<uintptr_t>(dst) & 15) == 0;
+    const int lane = threadIdx.x & 31;
+    __shared__ PeerTable tbl;
+    load_peer_table(tbl, a);
+    auto codes = [&](uint32_t r) { return reinterpret_cast<uint32_t *>(tbl.base[r]); };
+    auto metas = [&](uint32_t r) { return tbl.base[r] + n_pack_pad * 4; };
+
+    auto load4 = [&](uint64_t v, float (&x)[4]) -> int {
+        const uint4 raw = load_input(src, v < n_pack ? v : 0, v < n_pack ? a.count : 0, src_aligned);
+        x[0] = __uint_as_float(raw.x), x[1] = __uint_as_float(raw.y), x[2] = __uint_as_float(raw.z), x[3] = __uint_as_float(raw.w);
+        if (v >= n_pack) return 0;
+        const uint64_t left = a.count - v * 4;
+        return left >= 4 ? 4 : static_cast<int>(left);
+    };
+
+    // phase 0: quantise own input into own arena
+    for_owned_packets<1>(0, n_pack_pad, [&](const uint64_t(&v)[1], const bool(&)[1]) {
+        float x[4];
+        const int valid = load4(v[0], x);
+        const uint32_t packed = quantize4<ALGO>(x, valid, metas(a.rank) + (v[0] / 32) * MB, lane);
+        codes(a.rank)[v[0]] = packed;
+    });
+    if (!peer_barrier(a, tbl, a.flag_base + 1)) return;
+
+    // phase 1: dequantise + reduce own chunk in fp32, re-quantise once, adopt the decoded value
+    {
+        const uint64_t lo = min(uint64_t(a.rank) * per, n_pack_pad), hi = min(lo + per, n_pack_pad);
+        for_owned_packets<1>(lo, hi, [&](const uint64_t(&v)[1], const bool(&)[1]) {
+            float acc[4];
+            for (uint32_t r0 = 0; r0 < a.world; r0 += kPeerGroup) {
+                uint32_t raw[kPeerGroup], mlo[kPeerGroup], mhi[kPeerGroup];
+#pragma unroll
+                for (int g = 0; g < kPeerGroup; ++g)
+                    if (r0 + g < a.world) {
+                        raw[g] = ld_peer_4(codes(r0 + g) + v[0]);
+                        if constexpr (MB == 8) {
+                            const uint2 m = ld_peer_8(metas(r0 + g) + (v[0] / 32) * MB);
+                            mlo[g] = m.x, mhi[g] = m.y;
+                        } else {
+                            mlo[g] = ld_peer_4(metas(r0 + g) + (v[0] / 32) * MB), mhi[g] = 0;
+                        }
+                    }
+#pragma unroll
+                for (int g = 0; g < kPeerGroup; ++g)
+                    if (r0 + g < a.world) {
+                        float x[4];
+                        dequantize4<ALGO>(raw[g], mlo[g], mhi[g], x);
+#pragma unroll
+                        for (int i = 0; i < 4; ++i) acc[i] = r0 + g == 0 ? x[i] : combine<OP>(acc[i], x[i]);
+                    }
+            }
+            if (a.avg_divisor)
+#pragma unroll
+                for (int i = 0; i < 4; ++i) acc[i] = acc[i] / static_cast<float>(a.avg_divisor);
+            const uint64_t e = v[0] * 4;
+            const int valid = e >= a.count ? 0 : (a.count - e >= 4 ? 4 : static_cast<int>(a.count - e));
+            uint8_t *my_meta = metas(a.rank) + (v[0] / 32) * MB;
+            const uint32_t packed = quantize4<ALGO>(acc, valid, my_meta, lane);
+            codes(a.rank)[v[0]] = packed;
+            // the owner keeps exactly what the others will decode
+            float2 rec;
+            if constexpr (MB == 8) {
+                float mn = 3.402823466e+38f, mx = -3.402823466e+38f;
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+                    if (i < valid) mn = fminf(mn, acc[i]), mx = fmaxf(mx, acc[i]);
+                rec = make_float2(warp_min(mn), warp_max(mx));
+            } else {
+                float amax = 0.0f;
+#pragma unroll
+                for (int i = 0; i < 4; ++i)
+                    if (i < valid) amax = fmaxf(amax, fabsf(acc[i]));
+                amax = warp_max(amax);
+                rec = make_float2(amax > 0.0f ? amax / 448.0f : 1.0f, 0.0f);
+            }
+            float y[4];
+            dequantize4<ALGO>(packed, __float_as_uint(rec.x), __float_as_uint(rec.y), y);
+            if (valid > 0) {
+                uint4 out = make_uint4(__float_as_uint(y[0]), __float_as_uint(y[1]), __float_as_uint(y[2]), __float_as_uint(y[3]));
+                store_output(dst, v[0], a.count, dst_aligned, out);
+            }
+        });
+    }
+    if (!peer_barrier(a, tbl, a.flag_base + 2)) return;
+
+    // phase 2: fetch the other chunks as codes, decode into the output
+    for (uint32_t k = 1; k < a.world; ++k) {
+        const uint32_t peer = (a.rank + k) % a.world;
+        const uint64_t lo = min(uint64_t(peer) * per, n_pack_pad), hi = min(lo + per, n_pack_pad);
+        for_owned_packets<4>(lo, hi, [&](const uint64_t(&v)[4], const bool(&ok)[4]) {
+            uint32_t raw[4], mlo[4], mhi[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                if (!ok[u] || v[u] >= n_pack) continue;
+                raw[u] = ld_peer_4(codes(peer) + v[u]);
+                if constexpr (MB == 8) {
+                    const uint2 m = ld_peer_8(metas(peer) + (v[u] / 32) * MB);
+                    mlo[u] = m.x, mhi[u] = m.y;
+                } else {
+                    mlo[u] = ld_peer_4(metas(peer) + (v[u] / 32) * MB), mhi[u] = 0;
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                if (!ok[u] || v[u] >= n_pack) continue;
+                float y[4];
+                dequantize4<ALGO>(raw[u], mlo[u], mhi[u], y);
+                uint4 out = make_uint4(__float_as_uint(y[0]), __float_as_uint(y[1]), __float_as_uint(y[2]), __float_as_uint(y[3]));
+                store_output(dst, v[u], a.count, dst_aligned, out);
+            }
+        });
+    }
+    peer_barrier(a, tbl, a.flag_base + 3);
+}
+
+} // namespace pccl::cuda
+
+using namespace pccl::cuda;
+
+extern "C" size_t pcclKernelP2PControlBytes(void) { return kControlBytes; }
+
+extern "C" size_t pcclKernelP2PStagingBytes(uint64_t count, int dtype, int quant_algorithm) {
+    if (quant_algorithm == QUANT_BLOCK_MINMAX || quant_algorithm == QUANT_BLOCK_FP8) {
+        const uint64_t n_pack_pad = ((count + 3) / 4 + 31) / 32 * 32;
+        const uint64_t mb = quant_algorithm == QUANT_BLOCK_MINMAX ? 8 : 4;
+        return n_pack_pad * 4 + (n_pack_pad / 32) * mb + 256;
+    }
+    const size_t esz = pcclExtDataTypeSize(static_cast<pcclDataType_t>(dtype));
+    return (count * esz + 15) / 16 * 16 + 256;
+}
+
+extern "C" int pcclKernelAllReduceP2P(const pcclKernelP2PArgs_t *args, int *algorithm_out, void *stream_v) {
+    if (!args || args->world < 1 || args->world > PCCL_K_MAX_RANKS || args->rank >= args->world) return cudaErrorInvalidValue;
+    if (args->flag_slot >= static_cast<uint32_t>(kFlagBanks)) return cudaErrorInvalidValue;
+    const auto stream = static_cast<cudaStream_t>(stream_v);
+    DevArgs d{};
+    for (uint32_t r = 0; r < args->world; ++r) d.arena[r] = static_cast<uint8_t *>(args->arena[r]);
+    d.rank = args->rank;
+    d.world = args->world;
+    d.flag_slot = args->flag_slot;
+    d.flag_base = args->flag_base;
+    d.data_offset = args->data_offset;
+    d.src = args->src;
+    d.dst = args->dst;
+    d.count = args->count;
+    d.src_in_arena = args->src_in_arena;
+    d.abort_flag = args->abort_flag;
+    d.status = args->status;
+    d.timeout_cycles = args->timeout_cycles ? args->timeout_cycles : ~0ull;
+    bool is_avg = false;
+    const int kop = kernel_op(args->op, is_avg);
+    if (kop < 0) return cudaErrorInvalidValue;
+    d.avg_divisor = is_avg ? args->world : 0;
+    if (pcclKernelP2PStagingBytes(args->count, args->dtype, args->quant_algorithm) > args->data_capacity) return cudaErrorInvalidValue;
+
+    const size_t esz = pcclExtDataTypeSize(static_cast<pcclDataType_t>(args->dtype));
+    if (esz == 0) return cudaErrorInvalidValue;
+    const uint64_t bytes = args->count * esz;
+    const uint64_t n_pack = (bytes + 15) / 16;
+    const uint64_t tiles = (n_pack + kThreads - 1) / kThreads;
+    int max_blocks = args->max_blocks > 0 ? args->max_blocks : 144;
+    if (max_blocks > PCCL_K_MAX_BLOCKS) max_blocks = PCCL_K_MAX_BLOCKS;
+
+    const bool quantised = args->quant_algorithm == QUANT_BLOCK_MINMAX || args->quant_algorithm == QUANT_BLOCK_FP8;
+    if (quantised && args->dtype != pcclFloat) return cudaErrorInvalidValue;
+    if (!quantised && args->quant_algorithm != QUANT_NONE) return cudaErrorInvalidValue;
+
+    int algorithm = args->algorithm;
+    if (algorithm == 0) algorithm = (bytes <= (256u << 10) && !quantised) ? 1 : 2;
+    if (quantised) algorithm = 2;
+    if (algorithm_out) *algorithm_out = algorithm;
+
+    bool launched = false;
+    if (quantised) {
+        // per-chunk tiles: work is spread over the chunk of one rank in phase 1
+        const uint64_t chunk_tiles = (tiles + args->world - 1) / args->world;
+        const int grid = static_cast<int>(std::max<uint64_t>(1, std::min<uint64_t>(max_blocks, chunk_tiles)));
+        dispatch_op(kop, [&](auto op_tag) {
+            constexpr int OP = decltype(op_tag)::value;
+            if (args->quant_algorithm == QUANT_BLOCK_MINMAX)
+                allreduce_two_shot_quant_kernel<QUANT_BLOCK_MINMAX, OP><<<grid, kThreads, 0, stream>>>(d);
+            else
+                allreduce_two_shot_quant_kernel<QUANT_BLOCK_FP8, OP><<<grid, kThreads, 0, stream>>>(d);
+            launched = true;
+        });
+    } else {
+        dispatch_dtype(args->dtype, [&](auto type_tag) {
+            using T = decltype(type_tag);
+            dispatch_op(kop, [&](auto op_tag) {
+                constexpr int OP = decltype(op_tag)::value;
+                if (algorithm == 1) {
+                    const int grid = static_cast<int>(std::max<uint64_t>(1, std::min<uint64_t>(max_blocks, tiles)));
+                    allreduce_one_shot_kernel<T, OP><<<grid, kThreads, 0, stream>>>(d);
+                } else {
+                    const uint64_t chunk_tiles = (tiles + args->world - 1) / args->world;
+                    const int grid = static_cast<int>(std::max<uint64_t>(1, std::min<uint64_t>(max_blocks, chunk_tiles)));
+                    allreduce_two_shot_kernel<T, OP><<<grid, kThreads, 0, stream>>>(d);
+                }
+                launched = true;
+            });
+        });
+    }
+    if (!launched) return cudaErrorInvalidValue;
+    return cudaGetLastError();
+}

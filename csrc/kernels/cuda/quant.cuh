@@ -1,0 +1,94 @@
+// Block-scaled quantisation on the device: 128 consecutive fp32 values share one scale record.
+// One warp handles one block: every lane owns 4 consecutive values (one float4 in, one packed
+// u32 of code bytes out), the block statistics come from warp shuffles.
+// Numerics are identical to the host oracle in csrc/kernels/cpu/quantize.cpp (block_minmax_* and
+// block_fp8_*), operation by operation.
+#pragma once
+#include "common.cuh"
+
+namespace pccl::cuda {
+
+enum : int { QUANT_NONE = 0, QUANT_BLOCK_MINMAX = 3, QUANT_BLOCK_FP8 = 4 }; // pcclQuantizationAlgorithm_t values
+
+template <int ALGO> struct QuantMeta;
+template <> struct QuantMeta<QUANT_BLOCK_MINMAX> {
+    static constexpr int kBytes = 8;
+};
+template <> struct QuantMeta<QUANT_BLOCK_FP8> {
+    static constexpr int kBytes = 4;
+};
+
+__device__ __forceinline__ float warp_min(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fminf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+
+__device__ __forceinline__ uint32_t fp8_encode(float x) {
+    return static_cast<uint32_t>(__nv_cvt_float_to_fp8(x, __NV_SATFINITE, __NV_E4M3));
+}
+__device__ __forceinline__ float fp8_decode(uint32_t c) {
+    const __half_raw h = __nv_cvt_fp8_to_halfraw(static_cast<__nv_fp8_storage_t>(c & 0xffu), __NV_E4M3);
+    return __half2float(*reinterpret_cast<const __half *>(&h));
+}
+
+// Quantises the 4 values of this lane; all 32 lanes of the warp must call together.  `valid`
+// tells how many of the 4 values exist (tail of the buffer); missing ones do not influence the
+// statistics.  Returns the packed codes, writes the block record through `meta` (lane 0 only).
+template <int ALGO> __device__ __forceinline__ uint32_t quantize4(const float (&x)[4], int valid, void *meta, int lane) {
+    if constexpr (ALGO == QUANT_BLOCK_MINMAX) {
+        float mn = 3.402823466e+38f, mx = -3.402823466e+38f;
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+            if (i < valid) {
+                mn = fminf(mn, x[i]);
+                mx = fmaxf(mx, x[i]);
+            }
+        mn = warp_min(mn);
+        mx = warp_max(mx);
+        if (lane == 0) *reinterpret_cast<float2 *>(meta) = make_float2(mn, mx);
+        const float inv = mx > mn ? 255.0f / (mx - mn) : 0.0f;
+        uint32_t packed = 0;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const float r = rintf((x[i] - mn) * inv);
+            const uint32_t c = i < valid ? static_cast<uint32_t>(fminf(255.0f, fmaxf(0.0f, r))) : 0u;
+            packed |= c << (8 * i);
+        }
+        return packed;
+    } else {
+        float amax = 0.0f;
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+            if (i < valid) amax = fmaxf(amax, fabsf(x[i]));
+        amax = warp_max(amax);
+        const float scale = amax > 0.0f ? amax / 448.0f : 1.0f;
+        if (lane == 0) *reinterpret_cast<float *>(meta) = scale;
+        const float inv = 1.0f / scale;
+        uint32_t packed = 0;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) packed |= (i < valid ? fp8_encode(x[i] * inv) : 0u) << (8 * i);
+        return packed;
+    }
+}
+
+// meta_lo / meta_hi: the raw 32-bit words of the block record (hi unused for fp8)
+template <int ALGO> __device__ __forceinline__ void dequantize4(uint32_t packed, uint32_t meta_lo, uint32_t meta_hi, float (&out)[4]) {
+    if constexpr (ALGO == QUANT_BLOCK_MINMAX) {
+        const float mn = __uint_as_float(meta_lo), mx = __uint_as_float(meta_hi);
+        const float step = (mx - mn) * (1.0f / 255.0f);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) out[i] = fmaf(static_cast<float>((packed >> (8 * i)) & 0xffu), step, mn);
+    } else {
+        const float scale = __uint_as_float(meta_lo);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) out[i] = fp8_decode(packed >> (8 * i)) * scale;
+    }
+}
+
+} // namespace pccl::cuda

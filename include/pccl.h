@@ -333,6 +333,7 @@ typedef struct pcclExtReduceStats_t {
     pcclExtDataPlane_t plane;
     float device_ms;     /* CUDA-event time of the device part, 0 for host ops */
     uint64_t seq_nr;     /* master-issued sequence number of the operation */
+    uint32_t kernel_launches; /* kernels of this library launched for the operation */
 } pcclExtReduceStats_t;
 
 /* Stats of the most recently completed reduction with the given tag. */

@@ -1,0 +1,98 @@
+/*
+ * pccl_kernels.h -- C ABI of the sm_100a kernels inside libpccl.so.
+ *
+ * These entry points are what the communicator itself calls; they are exported so that tests,
+ * benchmarks and other runtimes (PyTorch through ctypes, for example) can drive single kernels.
+ * Every launcher is asynchronous on the given stream (a cudaStream_t passed as void*) unless
+ * stated otherwise, and returns 0 on success or a cudaError_t value.
+ *
+ * Data type / operator numbering is that of pcclDataType_t / pcclRedOp_t in pccl.h.
+ */
+#ifndef PCCL_KERNELS_H_
+#define PCCL_KERNELS_H_
+
+#include "pccl.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define PCCL_K_MAX_RANKS 16      /* peers in one NVLink domain */
+#define PCCL_K_MAX_BLOCKS 256    /* thread blocks of one collective kernel */
+#define PCCL_K_QUANT_BLOCK 128   /* elements sharing one scale in the block formats */
+
+/* ---------------------------------------------------------------------------------------------
+ * Content hashes (reference kernels: ccoip/src/cuda/simplehash_cuda.cu:95-156, no GPU CRC in the
+ * reference).  `scratch` must point to pcclKernelHashScratchBytes() bytes of device memory that
+ * was zeroed once; the kernels leave it zeroed again.  The result is written to *out_device
+ * (device memory, 8 bytes).
+ * ------------------------------------------------------------------------------------------- */
+PCCL_EXPORT size_t pcclKernelHashScratchBytes(void);
+PCCL_EXPORT int pcclKernelSimpleHash(const void *data, size_t n_bytes, void *scratch, uint64_t *out_device, void *stream);
+PCCL_EXPORT int pcclKernelCrc32c(const void *data, size_t n_bytes, void *scratch, uint64_t *out_device, void *stream);
+
+/* Convenience: allocates nothing itself -- uses a per-device scratch the library keeps -- runs the
+ * hash on an internal stream and returns the value on the host (synchronous). */
+PCCL_EXPORT int pcclKernelHashSync(const void *data, size_t n_bytes, int hash_type, uint64_t *out_host);
+
+/* ---------------------------------------------------------------------------------------------
+ * Element-wise kernels of the TCP data plane on device buffers (reference CPU versions:
+ * ccoip/src/cpp/reduce_kernels.cpp:56-215,437-510; quantize_kernels.cpp:24-217).
+ * ------------------------------------------------------------------------------------------- */
+/* dst[i] = dst[i] (op) src[i] */
+PCCL_EXPORT int pcclKernelReduce(void *dst, const void *src, size_t count, int dtype, int op, void *stream);
+/* dst[i] /= divisor, in the element type */
+PCCL_EXPORT int pcclKernelScaleInv(void *dst, size_t count, int dtype, uint64_t divisor, void *stream);
+
+/* Block formats: out = [meta for ceil(count/128) blocks][count code bytes].
+ *   algorithm pcclQuantBlockMinMax: meta = (min,max) fp32 pairs, codes uint8
+ *   algorithm pcclQuantBlockFp8:    meta = fp32 scale,           codes e4m3        */
+PCCL_EXPORT size_t pcclKernelQuantizedBytes(size_t count, int algorithm);
+PCCL_EXPORT int pcclKernelQuantize(const float *src, void *out, size_t count, int algorithm, void *stream);
+/* dst[i] = dst[i] (op) dequant(in[i]); op = -1 stores the dequantised value */
+PCCL_EXPORT int pcclKernelDequantizeReduce(float *dst, const void *in, size_t count, int algorithm, int op, void *stream);
+
+/* ---------------------------------------------------------------------------------------------
+ * Peer-to-peer all-reduce over NVLink (no counterpart in the reference, which reduces on the
+ * host: ccoip/src/cpp/reduce.cpp:528-784).  One launch per rank; all ranks pass the same
+ * geometry.  arena[r] is rank r's arena as mapped into the calling process.
+ * ------------------------------------------------------------------------------------------- */
+typedef struct pcclKernelP2PArgs_t {
+    void *arena[PCCL_K_MAX_RANKS];
+    uint32_t rank, world;
+    uint32_t flag_slot;     /* which flag bank of the control page */
+    uint64_t flag_base;     /* barrier values are flag_base + 1.. ; must grow from call to call */
+    uint64_t data_offset;   /* byte offset of the staging region inside every arena */
+    uint64_t data_capacity; /* bytes available there */
+    const void *src;        /* local input */
+    void *dst;              /* local output */
+    uint64_t count;         /* elements */
+    int dtype, op;
+    int quant_algorithm;    /* pcclQuantNone, pcclQuantBlockMinMax, pcclQuantBlockFp8 */
+    int algorithm;          /* 0 = choose, 1 = one-shot, 2 = two-shot */
+    int max_blocks;         /* SM budget, 0 = default */
+    int src_in_arena;       /* src already is arena[rank]+data_offset (symmetric memory): skip the copy-in */
+    volatile uint32_t *abort_flag; /* host-mapped; non-zero makes the kernel give up */
+    uint32_t *status;       /* host-mapped; 0 ok, 1 aborted, 2 timed out */
+    uint64_t timeout_cycles;
+} pcclKernelP2PArgs_t;
+
+/* Returns which algorithm ran (1 or 2) in *algorithm_out. */
+PCCL_EXPORT int pcclKernelAllReduceP2P(const pcclKernelP2PArgs_t *args, int *algorithm_out, void *stream);
+/* Bytes of arena staging needed for `count` elements. */
+PCCL_EXPORT size_t pcclKernelP2PStagingBytes(uint64_t count, int dtype, int quant_algorithm);
+/* Size of the control page at the start of every arena. */
+PCCL_EXPORT size_t pcclKernelP2PControlBytes(void);
+
+/* NVSwitch multicast variant: mc_base is the multicast mapping of all arenas.  Only
+ * sum/min/max/avg on f32, f16, bf16 (what multimem.ld_reduce offers). */
+typedef struct pcclKernelNvlsArgs_t {
+    pcclKernelP2PArgs_t p2p;
+    void *mc_arena; /* multicast view */
+} pcclKernelNvlsArgs_t;
+PCCL_EXPORT int pcclKernelAllReduceNvls(const pcclKernelNvlsArgs_t *args, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PCCL_KERNELS_H_ */

@@ -1,0 +1,154 @@
+"""Single-kernel operations on torch tensors.
+
+Every function here launches hand-written sm_100a kernels from libpccl.so through the C ABI in
+include/pccl_kernels.h.  There is no PyTorch fallback: on a CUDA tensor a missing library or a
+failed launch raises.  Host tensors go to the C++ host kernels (the oracles).
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional
+
+import torch
+
+from .. import _lib
+from .._lib import lib
+from .._pccl import DataType, QuantizationAlgorithm, ReduceOp
+
+
+def _check(rc: int, what: str) -> None:
+    if rc != 0:
+        raise RuntimeError(f"{what} failed with CUDA error {rc}")
+
+
+def _stream_ptr(t: torch.Tensor) -> int:
+    return torch.cuda.current_stream(t.device).cuda_stream
+
+
+def _hash(t: torch.Tensor, hash_type: int) -> int:
+    assert t.is_contiguous()
+    out = C.c_uint64()
+    nbytes = t.numel() * t.element_size()
+    if t.is_cuda:
+        with torch.cuda.device(t.device):
+            torch.cuda.current_stream().synchronize()
+            _check(lib().pcclKernelHashSync(t.data_ptr(), nbytes, hash_type, C.byref(out)), "pcclKernelHashSync")
+    else:
+        _check(lib().pcclExtHashBuffer(t.data_ptr(), nbytes, 0, hash_type, C.byref(out)), "pcclExtHashBuffer")
+    return out.value
+
+
+def simplehash(t: torch.Tensor) -> int:
+    """Shared-state content hash (value-compatible with the reference's simplehash)."""
+    return _hash(t, 0)
+
+
+def crc32c(t: torch.Tensor) -> int:
+    """CRC32C (Castagnoli) of the tensor's bytes."""
+    return _hash(t, 1)
+
+
+def reduce_(dst: torch.Tensor, src: torch.Tensor, op: ReduceOp = ReduceOp.SUM) -> torch.Tensor:
+    """dst (op)= src, element-wise, in place."""
+    assert dst.is_contiguous() and src.is_contiguous() and dst.dtype == src.dtype and dst.numel() == src.numel()
+    dt = DataType.from_torch_dtype(dst.dtype).value
+    if dst.is_cuda:
+        with torch.cuda.device(dst.device):
+            _check(lib().pcclKernelReduce(dst.data_ptr(), src.data_ptr(), dst.numel(), dt, op.value, _stream_ptr(dst)), "pcclKernelReduce")
+    else:
+        fn = lib().pcclHostReduce
+        fn.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_int]
+        _check(fn(dst.data_ptr(), src.data_ptr(), dst.numel(), dt, op.value), "pcclHostReduce")
+    return dst
+
+
+def scale_inv_(dst: torch.Tensor, divisor: int) -> torch.Tensor:
+    """dst /= divisor in the element type (AVG finalisation)."""
+    dt = DataType.from_torch_dtype(dst.dtype).value
+    if dst.is_cuda:
+        with torch.cuda.device(dst.device):
+            _check(lib().pcclKernelScaleInv(dst.data_ptr(), dst.numel(), dt, divisor, _stream_ptr(dst)), "pcclKernelScaleInv")
+    else:
+        fn = lib().pcclHostScaleInv
+        fn.argtypes = [C.c_void_p, C.c_size_t, C.c_int, C.c_uint64]
+        _check(fn(dst.data_ptr(), dst.numel(), dt, divisor), "pcclHostScaleInv")
+    return dst
+
+
+def _code_dtype(algo: QuantizationAlgorithm) -> int:
+    return DataType.FLOAT8_E4M3.value if algo == QuantizationAlgorithm.BLOCK_FP8 else DataType.UINT8.value
+
+
+def block_quantize(x: torch.Tensor, algo: QuantizationAlgorithm) -> torch.Tensor:
+    """fp32 -> [per-128-element records][1 byte per element].  Returns a uint8 tensor."""
+    assert x.dtype == torch.float32 and x.is_contiguous()
+    assert algo in (QuantizationAlgorithm.BLOCK_MIN_MAX, QuantizationAlgorithm.BLOCK_FP8)
+    n = x.numel()
+    nbytes = lib().pcclKernelQuantizedBytes(n, algo.value)
+    out = torch.empty(nbytes, dtype=torch.uint8, device=x.device)
+    if x.is_cuda:
+        with torch.cuda.device(x.device):
+            _check(lib().pcclKernelQuantize(x.data_ptr(), out.data_ptr(), n, algo.value, _stream_ptr(x)), "pcclKernelQuantize")
+    else:
+        fn = lib().pcclHostQuantize
+        fn.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_int, C.c_void_p]
+        _check(fn(x.data_ptr(), out.data_ptr(), n, algo.value, _code_dtype(algo), None), "pcclHostQuantize")
+    return out
+
+
+def block_dequantize_reduce(dst: torch.Tensor, q: torch.Tensor, algo: QuantizationAlgorithm, op: Optional[ReduceOp] = None) -> torch.Tensor:
+    """dst (op)= dequant(q); op None stores."""
+    assert dst.dtype == torch.float32 and dst.is_contiguous() and q.dtype == torch.uint8
+    opv = -1 if op is None else op.value
+    if dst.is_cuda:
+        with torch.cuda.device(dst.device):
+            _check(lib().pcclKernelDequantizeReduce(dst.data_ptr(), q.data_ptr(), dst.numel(), algo.value, opv, _stream_ptr(dst)),
+                   "pcclKernelDequantizeReduce")
+    else:
+        fn = lib().pcclHostDequantizeReduce
+        fn.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t, C.c_int, C.c_int, C.c_void_p, C.c_int]
+        _check(fn(dst.data_ptr(), q.data_ptr(), dst.numel(), algo.value, _code_dtype(algo), None, opv), "pcclHostDequantizeReduce")
+    return dst
+
+
+class LocalArena:
+    """A one-rank arena: control page + staging area in ordinary device memory.  Lets the
+    all-reduce kernels run with world size 1 (single GPU tests, the one-peer DiLoCo step)."""
+
+    def __init__(self, device: torch.device, staging_bytes: int):
+        self.control = int(lib().pcclKernelP2PControlBytes())
+        self.capacity = (staging_bytes + 4095) // 4096 * 4096 + 4096
+        self.buf = torch.zeros(self.control + self.capacity, dtype=torch.uint8, device=device)
+        self.words = torch.zeros(16, dtype=torch.int32).pin_memory()  # [0] abort flag, [1] status
+        self.epoch = 0
+
+
+def local_all_reduce(src: torch.Tensor, dst: torch.Tensor, arena: LocalArena, op: ReduceOp = ReduceOp.SUM,
+                     quant: QuantizationAlgorithm = QuantizationAlgorithm.NONE, algorithm: int = 0, max_blocks: int = 0) -> int:
+    """Runs the fused all-reduce kernel with world size 1 on the current stream.  Returns the
+    algorithm that ran (1 one-shot, 2 two-shot).  With one rank SUM/AVG/MIN/MAX return the input
+    (through the quantiser when one is selected)."""
+    assert src.is_cuda and dst.is_cuda and src.is_contiguous() and dst.is_contiguous()
+    args = _lib.KernelP2PArgs()
+    args.arena[0] = arena.buf.data_ptr()
+    args.rank, args.world = 0, 1
+    args.flag_slot = 0
+    arena.epoch += 1
+    args.flag_base = arena.epoch * 16
+    args.data_offset = arena.control
+    args.data_capacity = arena.capacity
+    args.src, args.dst = src.data_ptr(), dst.data_ptr()
+    args.count = src.numel()
+    args.dtype = DataType.from_torch_dtype(src.dtype).value
+    args.op = op.value
+    args.quant_algorithm = quant.value
+    args.algorithm = algorithm
+    args.max_blocks = max_blocks
+    args.src_in_arena = 0
+    args.abort_flag = arena.words.data_ptr()
+    args.status = arena.words.data_ptr() + 4
+    args.timeout_cycles = 20_000_000_000
+    ran = C.c_int()
+    with torch.cuda.device(src.device):
+        _check(lib().pcclKernelAllReduceP2P(C.byref(args), C.byref(ran), _stream_ptr(src)), "pcclKernelAllReduceP2P")
+    return ran.value
