@@ -1,7 +1,9 @@
 # Build of the B200-native PCCL: libpccl.so (C++20 core + sm_100a kernels), ccoip_master, C++ tests.
 # Everything lands in-tree (pccl_b200/lib, pccl_b200/bin, build/) so that the artefacts travel
 # with a snapshot of the repository.
-CXX      ?= g++
+# the image exports CXX=/opt/gcc/bin/g++, a toolchain that links libstdc++ statically; a second copy of
+# libstdc++ inside a Python process that already loaded the shared one crashes in iostream code
+CXX      := $(shell command -v /usr/bin/g++ || echo g++)
 NVCC     ?= /usr/local/cuda/bin/nvcc
 CUDA_HOME ?= /usr/local/cuda
 BUILD    := build

@@ -520,8 +520,11 @@ private:
         }
     }
 
-    // mu_ held, device current
+    // Device current.  Has its own lock: the rendezvous server thread must be able to create and
+    // export the arena while the main thread sits in on_ring_changed() waiting for a PEER's server
+    // (two peers fetching each other's arenas would otherwise deadlock until the timeout).
     bool ensure_arena() {
+        std::lock_guard<std::mutex> arena_lock(arena_mu_);
         if (arena_ptr_) return true;
         const Driver &d = driver();
         CUmemAllocationProp prop{};
@@ -639,7 +642,6 @@ private:
             int fd = -1;
             if (::poll(&cp, 1, 2000) > 0 && ::recv(c, &req, sizeof req, MSG_WAITALL) == static_cast<ssize_t>(sizeof req) &&
                 req.magic == kMagic && req.kind == kReqArena) {
-                std::lock_guard<std::mutex> lock(mu_);
                 if (ensure_arena() && driver().MemExportToShareableHandle(&fd, arena_handle_, CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR, 0) == CUDA_SUCCESS) {
                     rep.status = 0;
                     rep.arena_bytes = arena_bytes_;
@@ -685,6 +687,7 @@ private:
     std::thread server_;
 
     std::mutex mu_;
+    std::mutex arena_mu_; // guards arena creation only; never held while waiting for a peer
     size_t slot_bytes_ = 0, sym_bytes_ = 0, arena_bytes_ = 0;
     uint32_t n_slots_ = 4;
     uint64_t timeout_ms_ = 30000;

@@ -309,7 +309,10 @@ template <int ALGO, int OP> __global__ void __launch_bounds__(kThreads, 1) allre
     };
 
     // phase 0: quantise own input into own arena
-    for_owned_packets<1>(0, n_pack_pad, [&](const uint64_t(&v)[1], const bool(&)[1]) {
+    // ranges are multiples of 32 packets, so `ok` is uniform across a warp and the shuffles inside
+    // quantize4 always see complete warps
+    for_owned_packets<1>(0, n_pack_pad, [&](const uint64_t(&v)[1], const bool(&ok)[1]) {
+        if (!ok[0]) return;
         float x[4];
         const int valid = load4(v[0], x);
         const uint32_t packed = quantize4<ALGO>(x, valid, metas(a.rank) + (v[0] / 32) * MB, lane);
@@ -320,7 +323,8 @@ template <int ALGO, int OP> __global__ void __launch_bounds__(kThreads, 1) allre
     // phase 1: dequantise + reduce own chunk in fp32, re-quantise once, adopt the decoded value
     {
         const uint64_t lo = min(uint64_t(a.rank) * per, n_pack_pad), hi = min(lo + per, n_pack_pad);
-        for_owned_packets<1>(lo, hi, [&](const uint64_t(&v)[1], const bool(&)[1]) {
+        for_owned_packets<1>(lo, hi, [&](const uint64_t(&v)[1], const bool(&ok)[1]) {
+            if (!ok[0]) return;
             float acc[4];
             for (uint32_t r0 = 0; r0 < a.world; r0 += kPeerGroup) {
                 uint32_t raw[kPeerGroup], mlo[kPeerGroup], mhi[kPeerGroup];

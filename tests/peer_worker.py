@@ -1,0 +1,147 @@
+#!/usr/bin/env python3
+"""One peer of a multi-process test.  Usage: peer_worker.py <master_port> <rank> <world> <device|cpu> <scenario>
+
+Prints one JSON line with per-case results; exit code 0 when every case matched its expectation."""
+import json
+import sys
+import time
+from pathlib import Path
+
+import torch
+
+sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
+import pccl_b200 as pccl  # noqa: E402
+from pccl_b200 import ops  # noqa: E402
+
+
+def make_input(case_id: int, rank: int, n: int, dtype: torch.dtype) -> torch.Tensor:
+    g = torch.Generator().manual_seed(1000 * case_id + rank)
+    if dtype.is_floating_point:
+        return (torch.randn(n, generator=g) * 2).to(dtype)
+    return torch.randint(-50, 50, (n,), generator=g).to(dtype)
+
+
+def expected(case_id: int, world: int, n: int, dtype: torch.dtype, op: pccl.ReduceOp) -> torch.Tensor:
+    acc_dtype = torch.float64 if dtype == torch.float64 else (torch.float32 if dtype.is_floating_point else torch.int64)
+    acc = make_input(case_id, 0, n, dtype).to(acc_dtype)
+    for r in range(1, world):
+        x = make_input(case_id, r, n, dtype).to(acc_dtype)
+        if op in (pccl.ReduceOp.SUM, pccl.ReduceOp.AVG):
+            acc = acc + x
+        elif op == pccl.ReduceOp.MAX:
+            acc = torch.maximum(acc, x)
+        elif op == pccl.ReduceOp.MIN:
+            acc = torch.minimum(acc, x)
+        else:
+            acc = acc * x
+    if op == pccl.ReduceOp.AVG:
+        acc = acc / world if dtype.is_floating_point else torch.div(acc, world, rounding_mode="trunc")
+    return acc
+
+
+CASES = [
+    # id, n, dtype, op, quant, in_place, unaligned
+    (1, 1000, torch.float32, pccl.ReduceOp.SUM, None, False, False),
+    (2, 10_000_019, torch.float32, pccl.ReduceOp.AVG, None, False, False),
+    (3, 1_000_003, torch.bfloat16, pccl.ReduceOp.SUM, None, False, False),
+    (4, 70_001, torch.int32, pccl.ReduceOp.MAX, None, False, False),
+    (5, 500_000, torch.float64, pccl.ReduceOp.MIN, None, False, False),
+    (6, 3_000_000, torch.float32, pccl.ReduceOp.SUM, None, True, False),
+    (7, 2_000_000, torch.float32, pccl.ReduceOp.SUM, "u8", False, False),
+    (8, 2_000_001, torch.float32, pccl.ReduceOp.AVG, "fp8", False, False),
+    (9, 400_005, torch.float16, pccl.ReduceOp.SUM, None, False, True),
+    (10, 3, torch.float32, pccl.ReduceOp.SUM, None, False, False),
+    (11, 90_000_000, torch.float32, pccl.ReduceOp.AVG, None, True, False),  # 360 MB: more than one staging round
+    (12, 1_000_000, torch.int64, pccl.ReduceOp.AVG, None, False, False),
+]
+
+
+def main():
+    port, rank, world, device, scenario = int(sys.argv[1]), int(sys.argv[2]), int(sys.argv[3]), sys.argv[4], sys.argv[5]
+    dev = torch.device(device)
+    if dev.type == "cuda":
+        torch.cuda.set_device(dev)
+    comm = pccl.Communicator(f"127.0.0.1:{port}")
+    comm.connect(n_attempts=20)
+    while comm.get_attribute(pccl.Attribute.GLOBAL_WORLD_SIZE) < world:
+        comm.update_topology()
+    results = {"rank": rank, "cases": []}
+    ok_all = True
+    if scenario == "allreduce":
+        for cid, n, dtype, op, quant, in_place, unaligned in CASES:
+            x = make_input(cid, rank, n + (1 if unaligned else 0), dtype)
+            if unaligned:
+                # a view that starts one element into the allocation (not 16-byte aligned)
+                x = make_input(cid, rank, n, dtype)
+                store = torch.empty(n + 1, dtype=dtype, device=dev)
+                send = store[1:]
+                send.copy_(x)
+                recv_store = torch.empty(n + 1, dtype=dtype, device=dev)
+                recv = recv_store[1:]
+            else:
+                send = x.to(dev)
+                recv = send if in_place else torch.empty_like(send)
+            qopt = None
+            if quant == "u8":
+                qopt = pccl.QuantizationOptions(pccl.DataType.UINT8, pccl.QuantizationAlgorithm.MIN_MAX)
+            elif quant == "fp8":
+                qopt = pccl.QuantizationOptions(pccl.DataType.FLOAT8_E4M3, pccl.QuantizationAlgorithm.BLOCK_FP8)
+            info = comm.all_reduce(send, recv, op=op, tag=cid, quantization_options=qopt)
+            st = comm.ext_last_reduce_stats(cid)
+            want = expected(cid, world, n, dtype, op)
+            got = recv.cpu()
+            if quant:
+                scale = want.abs().max().item()
+                tol = (0.03 if quant == "u8" else 0.12) * scale * (1 + 0.3 * world)
+                ok = (got.double() - want.double()).abs().max().item() <= tol
+            elif dtype.is_floating_point:
+                rtol = {torch.float32: 1e-5, torch.float64: 1e-12, torch.bfloat16: 3e-2, torch.float16: 5e-3}[dtype]
+                ok = torch.allclose(got.double(), want.double(), rtol=rtol, atol=rtol * 8)
+            else:
+                ok = torch.equal(got.to(torch.int64), want)
+            digest = ops.simplehash(recv if not unaligned else recv.clone())
+            ok = ok and info.world_size == world
+            ok_all = ok_all and ok
+            results["cases"].append({"id": cid, "ok": bool(ok), "plane": st["plane"], "ms": round(st["device_ms"], 4), "hash": digest,
+                                     "launches": st["kernel_launches"]})
+    elif scenario == "concurrent":
+        n = 4_000_000
+        a = make_input(101, rank, n, torch.float32).to(dev)
+        b = make_input(102, rank, n, torch.float32).to(dev)
+        ra, rb = torch.empty_like(a), torch.empty_like(b)
+        h1 = comm.all_reduce_async(a, ra, op=pccl.ReduceOp.SUM, tag=1)
+        h2 = comm.all_reduce_async(b, rb, op=pccl.ReduceOp.MAX, tag=2)
+        ok1, _, _ = h1.wait()
+        ok2, _, _ = h2.wait()
+        wa = expected(101, world, n, torch.float32, pccl.ReduceOp.SUM)
+        wb = expected(102, world, n, torch.float32, pccl.ReduceOp.MAX)
+        ok_all = ok1 and ok2 and torch.allclose(ra.cpu(), wa, rtol=1e-5, atol=1e-5) and torch.equal(rb.cpu(), wb)
+        results["cases"].append({"id": "concurrent", "ok": bool(ok_all), "plane": comm.ext_last_reduce_stats(1)["plane"]})
+    elif scenario == "shared_state":
+        # rank 0 holds the truth; the others start from garbage and must end up identical
+        n = 5_000_003
+        w = make_input(201, 0 if rank == 0 else 7 + rank, n, torch.bfloat16).to(dev)
+        m = make_input(202, 0 if rank == 0 else 9 + rank, 1000, torch.float32).to(dev)
+        state = pccl.SharedState([pccl.TensorInfo.from_torch(w, "weights"), pccl.TensorInfo.from_torch(m, "momentum")])
+        state.revision = 1
+        strategy = pccl.SharedStateSyncStrategy.SEND_ONLY if rank == 0 else pccl.SharedStateSyncStrategy.RECEIVE_ONLY
+        info = comm.sync_shared_state(state, strategy)
+        want_w = make_input(201, 0, n, torch.bfloat16)
+        ok_all = torch.equal(w.cpu(), want_w) and torch.equal(m.cpu(), make_input(202, 0, 1000, torch.float32))
+        if rank == 0:
+            ok_all = ok_all and info.rx_bytes == 0 and info.tx_bytes == (world - 1) * (n * 2 + 4000)
+        else:
+            ok_all = ok_all and info.rx_bytes == n * 2 + 4000
+        # second sync: identical content, nothing moves
+        state.revision += 1
+        info2 = comm.sync_shared_state(state, pccl.SharedStateSyncStrategy.ENFORCE_POPULAR)
+        ok_all = ok_all and info2.tx_bytes == 0 and info2.rx_bytes == 0
+        results["cases"].append({"id": "shared_state", "ok": bool(ok_all), "tx": info.tx_bytes, "rx": info.rx_bytes})
+    results["ok"] = bool(ok_all)
+    print(json.dumps(results), flush=True)
+    comm.destroy()
+    sys.exit(0 if ok_all else 1)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,69 @@
+"""Multi-process peers, one per GPU, through the whole stack (master, control plane, NVLink kernels).
+Needs at least two GPUs; skipped otherwise."""
+import json
+import subprocess
+import sys
+from pathlib import Path
+
+import pytest
+
+import pccl_b200 as pccl
+from conftest import gpu_count
+
+pytestmark = [pytest.mark.gpu, pytest.mark.multigpu]
+HERE = Path(__file__).resolve().parent
+
+
+def run_peers(world: int, scenario: str, devices=None, timeout=600):
+    master = pccl.MasterNode("127.0.0.1:0")
+    master.run()
+    port = master.port
+    devices = devices or [f"cuda:{i}" for i in range(world)]
+    procs = [subprocess.Popen([sys.executable, str(HERE / "peer_worker.py"), str(port), str(r), str(world), devices[r], scenario],
+                              stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True) for r in range(world)]
+    outs = []
+    for p in procs:
+        try:
+            o, e = p.communicate(timeout=timeout)
+        except subprocess.TimeoutExpired:
+            for q in procs:
+                q.kill()
+            raise
+        outs.append((p.returncode, o, e))
+    master.interrupt()
+    results = []
+    for rc, o, e in outs:
+        assert rc == 0, f"peer failed rc={rc}\nstdout:{o[-3000:]}\nstderr:{e[-3000:]}"
+        results.append(json.loads(o.strip().splitlines()[-1]))
+    return results
+
+
+def worlds():
+    n = gpu_count()
+    return [w for w in (2, 4, 8) if w <= n]
+
+
+@pytest.mark.parametrize("world", worlds() or [pytest.param(2, marks=pytest.mark.skip(reason="needs >= 2 GPUs"))])
+def test_allreduce_over_nvlink(world):
+    results = run_peers(world, "allreduce")
+    by_case = {}
+    for r in results:
+        for c in r["cases"]:
+            assert c["ok"], c
+            assert c["plane"].startswith("p2p"), f"case {c['id']} ran on {c['plane']}, expected the NVLink plane"
+            by_case.setdefault(c["id"], set()).add(c["hash"])
+    # every peer must hold bit-identical results
+    for cid, hashes in by_case.items():
+        assert len(hashes) == 1, f"case {cid}: peers disagree bit-wise"
+
+
+@pytest.mark.parametrize("world", worlds()[:1] or [pytest.param(2, marks=pytest.mark.skip(reason="needs >= 2 GPUs"))])
+def test_concurrent_tags_over_nvlink(world):
+    for r in run_peers(world, "concurrent"):
+        assert r["ok"]
+
+
+@pytest.mark.parametrize("world", worlds()[:2] or [pytest.param(2, marks=pytest.mark.skip(reason="needs >= 2 GPUs"))])
+def test_shared_state_device_tensors(world):
+    for r in run_peers(world, "shared_state"):
+        assert r["ok"], r
