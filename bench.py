@@ -89,6 +89,8 @@ def parse_args():
     ap.add_argument("--params", type=int, default=150_000_000, help="fp32 elements per peer")
     ap.add_argument("--quant", default="none", choices=["none", "minmax_u8", "fp8"])
     ap.add_argument("--sweep", action="store_true", help="also print a size sweep table to stderr")
+    ap.add_argument("--buffers", default="symmetric", choices=["symmetric", "regular"],
+                    help="symmetric: tensors from Communicator.ext_symmetric_empty (zero-copy); regular: plain torch tensors (staged)")
     return ap.parse_args()
 
 
@@ -139,8 +141,10 @@ def run_ours(args) -> dict:
              "fp8": pccl.QuantizationOptions(pccl.DataType.FLOAT8_E4M3, pccl.QuantizationAlgorithm.BLOCK_FP8)}[args.quant]
 
     master = comm = None
+    sym = None
     planes = set()
     launches = 0
+    dev_ms = [0.0]
     if world > 1:
         port_box = [0]
         if rank == 0:
@@ -159,6 +163,14 @@ def run_ours(args) -> dict:
             st = comm.ext_last_reduce_stats(0)
             planes.add(st["plane"])
             launches += st["kernel_launches"]
+            dev_ms[0] += st["device_ms"]
+
+        if args.buffers == "symmetric" and quant is None:
+            # Peer-visible ("symmetric") buffers from the communicator's arena: the reduction runs in
+            # place on them with no staging copy.  This is the registered-buffer path; the plain
+            # torch-tensor path is measured as well and reported as `regular_buffers`.
+            sym = comm.ext_symmetric_empty(n, torch.float32)
+            sym.copy_(grad)
     else:
         arena = ops.LocalArena(dev, nbytes)
         qalgo = {"none": pccl.QuantizationAlgorithm.NONE, "minmax_u8": pccl.QuantizationAlgorithm.BLOCK_MIN_MAX,
@@ -183,20 +195,24 @@ def run_ours(args) -> dict:
         return max_over_ranks(ms) / steps
 
     # ---- kernel-level number -----------------------------------------------------------------
+    main_src, main_dst = (sym, sym) if sym is not None else (grad, out)
     for _ in range(max(3, args.warmup)):
-        reduce_step(grad, out)
+        reduce_step(main_src, main_dst)
     launches = 0
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
-    ms_step = timed(lambda: reduce_step(grad, out), args.steps)
+    dev_ms[0] = 0.0
+    ms_step = timed(lambda: reduce_step(main_src, main_dst), args.steps)
+    main_planes = sorted(planes)
+    kernel_ms = max_over_ranks(dev_ms[0] / args.steps) if dev_ms[0] else None
     timed_launches = launches
 
     # ---- end to end: H2D of the step's input, all-reduce, D2H of a result scalar ------------------
     def e2e_step():
-        grad.copy_(pinned, non_blocking=True)
-        reduce_step(grad, out)
-        return float(out[0].item())
+        main_src.copy_(pinned, non_blocking=True)
+        reduce_step(main_src, main_dst)
+        return float(main_dst[0].item())
 
     for _ in range(3):
         e2e_step()
@@ -207,7 +223,7 @@ def run_ours(args) -> dict:
     outer = torch.randn(n, device=dev)
     inner = outer - 0.01 * torch.randn(n, device=dev)
     buf = torch.zeros_like(outer)
-    pg = torch.empty_like(outer)
+    pg = sym if sym is not None else torch.empty_like(outer)
     state = {"k": 0}
 
     def outer_step():
@@ -224,6 +240,25 @@ def run_ours(args) -> dict:
     digest = ops.simplehash(outer)
     ms_hash = (time.perf_counter() - t0) * 1e3
 
+    # ---- the same reduction on plain torch tensors (staged through the arena) ----------------------
+    regular = None
+    if sym is not None:
+        planes.clear()
+        for _ in range(3):
+            reduce_step(grad, out)
+        dev_ms[0] = 0.0
+        ms_reg = timed(lambda: reduce_step(grad, out), args.steps)
+        regular = {"ms_per_step": round(ms_reg, 4), "bus_GBps": round(nbytes * bus_factor(world) / (ms_reg * 1e-3) / 1e9, 2),
+                   "kernel_ms_per_step": round(max_over_ranks(dev_ms[0] / args.steps), 4), "planes": sorted(planes)}
+
+    # ---- NCCL on the same tensors, same timing (the baseline the reference's own examples use) ----
+    nccl = None
+    if dist:
+        for _ in range(3):
+            dist.all_reduce(grad, op=dist.ReduceOp.AVG)
+        ms_nccl = timed(lambda: dist.all_reduce(grad, op=dist.ReduceOp.AVG), args.steps)
+        nccl = {"ms_per_step": round(ms_nccl, 4), "bus_GBps": round(nbytes * bus_factor(world) / (ms_nccl * 1e-3) / 1e9, 2)}
+
     factor = bus_factor(world)
     value = nbytes * factor / (ms_step * 1e-3) / 1e9
     e2e_value = nbytes * factor / (ms_e2e * 1e-3) / 1e9
@@ -234,7 +269,8 @@ def run_ours(args) -> dict:
         "vs_baseline": round(value / PUBLISHED_BASELINE_GBPS, 2), "dtype": "fp32", "data": "synthetic",
         "impl": "ours",
         "config": {"model": "DiLoCo pseudo-gradients, GPT-2-class 150M params fp32", "params": n, "global_batch": None, "seq_len": None,
-                   "parallelism": f"dp{world}", "op": "avg", "quantization": args.quant, "planes": sorted(planes),
+                   "parallelism": f"dp{world}", "op": "avg", "quantization": args.quant, "planes": main_planes,
+                   "buffers": "symmetric (Communicator.ext_symmetric_empty, in place)" if sym is not None else "regular torch tensors",
                    "l2_policy": "inputs (600 MB) larger than L2 (126 MB); no explicit flush",
                    "note": "one peer: bus factor undefined, value is bytes/time of the one-rank fused kernel" if world == 1 else
                            "bus GB/s = bytes*2(P-1)/P/t, device time incl. control plane round trips"},
@@ -242,6 +278,9 @@ def run_ours(args) -> dict:
         "gpu_launches": timed_launches,
         "diloco_outer_step_ms": round(ms_outer, 4), "shared_state_hash_ms": round(ms_hash, 3), "shared_state_hash": digest,
         "clocks": clocks,
+        "kernel_ms_per_step": round(kernel_ms, 4) if kernel_ms else None,
+        "regular_buffers": regular,
+        "nccl_same_run": nccl,
     }
     if comm is not None:
         comm.destroy()

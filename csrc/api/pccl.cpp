@@ -235,10 +235,24 @@ pcclResult_t pcclAwaitAsyncReduce(const pcclAsyncReduceOp_t *handle, pcclReduceI
 
 pcclResult_t pcclAllReduce(const void *sendbuff, void *recvbuff, const pcclReduceDescriptor_t *descriptor,
                            const pcclComm_t *c, pcclReduceInfo_t *info_out) {
-    pcclAsyncReduceOp_t handle{};
-    if (const pcclResult_t rc = pcclAllReduceAsync(sendbuff, recvbuff, descriptor, c, &handle); rc != pcclSuccess)
-        return rc;
-    return pcclAwaitAsyncReduce(&handle, info_out);
+    PCCL_REQUIRE_INIT();
+    PCCL_REQUIRE(c, pcclInvalidArgument);
+    PCCL_REQUIRE(c->client, pcclInvalidUsage);
+    client::ReduceRequest req;
+    if (const pcclResult_t rc = build_request(sendbuff, recvbuff, descriptor, req); rc != pcclSuccess) return rc;
+    PCCL_REQUIRE(c->client->local_world() >= 2, pcclTooFewPeers);
+    client::ReduceOutcome out;
+    switch (c->client->all_reduce_sync(req, out)) {
+    case client::Client::Launch::Ok: break;
+    case client::Client::Launch::DuplicateTag: return pcclInvalidArgument;
+    case client::Client::Launch::NotConnected: return pcclInvalidUsage;
+    }
+    if (info_out) {
+        info_out->local_world_size = out.world;
+        info_out->tx_bytes = out.tx_bytes;
+        info_out->rx_bytes = out.rx_bytes;
+    }
+    return out.ok ? pcclSuccess : pcclRankConnectionLost;
 }
 
 // Scheduler: keep up to max_in_flight reductions running; when any fails, drain everything

@@ -263,6 +263,7 @@ Client::Establish Client::establish_round() {
 bool Client::request_and_establish(bool accept_new_peers) {
     if (!accepted_ || !master_.is_open()) return false;
     if (any_reduce_running()) return false;
+    drain_deferred(); // the master must see this peer idle before it may vote
     Establish result;
     do {
         C2MEstablishP2P vote;
@@ -374,6 +375,7 @@ bool Client::optimize_topology() {
     std::lock_guard<std::mutex> lock(joint_mu_);
     if (!accepted_ || !master_.is_open()) return false;
     if (any_reduce_running()) return false;
+    drain_deferred();
     for (int round = 0; round < 64; ++round) {
         if (!master_.send_packet(C2MOptimizeTopology{})) return false;
         const auto work = master_.recv_packet<M2COptimizeTopologyResponse>();
@@ -467,6 +469,7 @@ bool Client::sync_shared_state(SharedStateArgs &state, uint64_t &tx_bytes, uint6
     tx_bytes = rx_bytes = 0;
     if (!accepted_ || !master_.is_open()) return false;
     if (any_reduce_running()) return false;
+    drain_deferred();
 
     C2MSyncSharedState vote;
     vote.revision = state.revision;
@@ -608,7 +611,7 @@ bool Client::await_reduce(uint64_t tag, ReduceOutcome &out) {
     {
         std::lock_guard<std::mutex> lock(ops_mu_);
         const auto it = ops_.find(tag);
-        if (it == ops_.end()) return false;
+        if (it == ops_.end() || !it->second.future.valid()) return false;
         op = std::move(it->second);
     }
     try {
@@ -616,6 +619,25 @@ bool Client::await_reduce(uint64_t tag, ReduceOutcome &out) {
     } catch (...) {
         out = ReduceOutcome{};
     }
+    return conclude(tag, op.revision_at_launch, out);
+}
+
+Client::Launch Client::all_reduce_sync(const ReduceRequest &req, ReduceOutcome &out) {
+    if (!accepted_ || !master_.is_open()) return Launch::NotConnected;
+    uint64_t rev;
+    {
+        std::lock_guard<std::mutex> lock(ops_mu_);
+        if (ops_.count(req.tag)) return Launch::DuplicateTag;
+        Op op;
+        op.revision_at_launch = rev = connection_revision_;
+        ops_.emplace(req.tag, std::move(op));
+    }
+    out = run_reduce(req, rev);
+    conclude(req.tag, rev, out);
+    return Launch::Ok;
+}
+
+bool Client::conclude(uint64_t tag, uint64_t revision_at_launch, ReduceOutcome &out) {
     bool others_running;
     {
         std::lock_guard<std::mutex> lock(ops_mu_);
@@ -629,10 +651,33 @@ bool Client::await_reduce(uint64_t tag, ReduceOutcome &out) {
         // connection revision, and only when no other reduction is still in flight (those
         // will fail too and the last one to be awaited does the rewiring).
         std::lock_guard<std::mutex> lock(joint_mu_);
-        if (!others_running && connection_revision_ == op.revision_at_launch && master_.is_open())
+        if (!others_running && connection_revision_ == revision_at_launch && master_.is_open())
             request_and_establish(false);
     }
     return out.ok;
+}
+
+// Consumes what the master still owes for an operation whose Complete vote was already sent:
+// exactly one Abort packet, then the Complete packet.
+bool Client::finish_deferred(uint64_t tag, Deferred &d) {
+    if (!d.abort_seen) {
+        const auto pkt = master_.recv_matching<M2CCollectiveAbort>([&](const M2CCollectiveAbort &p) { return p.tag == tag; });
+        if (!pkt) return false;
+        d.abort_seen = true;
+        d.aborted = pkt->aborted;
+    }
+    return master_.recv_matching<M2CCollectiveComplete>([&](const M2CCollectiveComplete &p) { return p.tag == tag; }).has_value();
+}
+
+bool Client::drain_deferred() {
+    std::map<uint64_t, Deferred> pending;
+    {
+        std::lock_guard<std::mutex> lock(deferred_mu_);
+        pending.swap(deferred_);
+    }
+    bool ok = true;
+    for (auto &[tag, d] : pending) ok = finish_deferred(tag, d) && ok;
+    return ok;
 }
 
 std::shared_ptr<net::MuxSocket> Client::pick_rx(const Uuid &peer, uint64_t seq, int timeout_ms) {
@@ -673,7 +718,8 @@ ReduceOutcome Client::run_reduce(const ReduceRequest &req, uint64_t) {
     dargs.quant_dtype = req.quant_dtype;
     dargs.rank = rank;
     dargs.world = world;
-    const bool device_capable = send_info.is_device && recv_info.is_device && plane_->can_reduce(dargs);
+    const uint32_t caps = send_info.is_device && recv_info.is_device ? plane_->capabilities(dargs) : 0;
+    const bool device_capable = (caps & device::Plane::kCapP2P) != 0;
 
     // ---- vote.  The spare top bit of the operator byte tells the master that this peer can
     // run the operation on the device plane; the master answers with the top bit of the
@@ -683,13 +729,37 @@ ReduceOutcome Client::run_reduce(const ReduceRequest &req, uint64_t) {
     vote.tag = req.tag;
     vote.count = req.count;
     vote.dtype = req.dtype;
-    vote.op = static_cast<RedOp>(static_cast<uint8_t>(req.op) | (device_capable ? 0x80u : 0u));
+    // (bit 6 / bit 62 do the same for the NVSwitch multicast variant)
+    vote.op = static_cast<RedOp>(static_cast<uint8_t>(req.op) | (device_capable ? 0x80u : 0u) |
+                                 ((caps & device::Plane::kCapNvls) ? 0x40u : 0u));
+    // The previous operation on this tag may have returned before its completion handshake was
+    // consumed (device plane, see below).  A master of this build queues the new vote behind
+    // it, so the vote goes out first and both answers arrive in one round trip; towards any
+    // other master the handshake is finished before voting again.
+    Deferred prev;
+    bool have_prev = false;
+    {
+        std::lock_guard<std::mutex> lock(deferred_mu_);
+        const auto it = deferred_.find(req.tag);
+        if (it != deferred_.end()) {
+            prev = it->second;
+            have_prev = true;
+            deferred_.erase(it);
+        }
+    }
+    if (have_prev && !master_pipelines_ && !finish_deferred(req.tag, prev)) return out;
     if (!master_.send_packet(vote)) return out;
+    if (have_prev && master_pipelines_ && !finish_deferred(req.tag, prev)) return out;
     const auto go = master_.recv_matching<M2CCollectiveCommence>([&](const M2CCollectiveCommence &p) { return p.tag == req.tag; });
     if (!go) return out;
+    // the earlier operation finished here, but a peer vanished before everybody had voted: the
+    // ring this peer knows is stale, so this operation is reported as failed without running
+    const bool poisoned = have_prev && prev.aborted;
     const bool use_device = (go->seq_nr >> 63) != 0;
-    const uint64_t seq = go->seq_nr & ~(1ull << 63);
+    const bool use_nvls = use_device && ((go->seq_nr >> 62) & 1) != 0;
+    const uint64_t seq = go->seq_nr & ~(3ull << 62);
     out.stats.seq_nr = seq;
+    if (use_device) master_pipelines_ = true; // only a master of this build ever sets that bit
 
     bool abort_seen = false, aborted = false;
     auto abort_requested = [&]() {
@@ -708,8 +778,11 @@ ReduceOutcome Client::run_reduce(const ReduceRequest &req, uint64_t) {
     std::vector<uint8_t> stage_send, stage_recv; // host staging for device buffers on the TCP plane
     const bool in_place = req.send == req.recv;
 
-    if (use_device && device_capable) {
+    if (poisoned) {
+        PLOG(INFO) << "previous reduction on tag " << req.tag << " was aborted after it finished locally; failing this one";
+    } else if (use_device && device_capable) {
         dargs.seq = seq;
+        dargs.use_nvls = use_nvls;
         const auto r = plane_->reduce(dargs, abort_requested);
         local_ok = r.ok;
         out.tx_bytes = r.tx_bytes;
@@ -777,6 +850,15 @@ ReduceOutcome Client::run_reduce(const ReduceRequest &req, uint64_t) {
     done.tag = req.tag;
     done.was_aborted = !local_ok;
     if (!master_.send_packet(done)) return out;
+    if (use_device && device_capable && local_ok && !aborted) {
+        // The kernel's closing barrier is only passed once EVERY peer has its complete result, so
+        // the outcome of the completion vote is already known.  Return now; the Abort/Complete
+        // packets are consumed by the next operation on this tag or by the next joint call.
+        std::lock_guard<std::mutex> lock(deferred_mu_);
+        deferred_[req.tag] = Deferred{abort_seen, aborted};
+        out.ok = true;
+        return out;
+    }
     if (!abort_seen) {
         const auto pkt = master_.recv_matching<M2CCollectiveAbort>([&](const M2CCollectiveAbort &p) { return p.tag == req.tag; });
         if (!pkt) return out;

@@ -92,6 +92,8 @@ public:
     enum class Launch { Ok, DuplicateTag, NotConnected };
     Launch all_reduce_async(const ReduceRequest &req);
     bool await_reduce(uint64_t tag, ReduceOutcome &out);
+    // Blocking variant that runs on the calling thread (no hand-over to the worker pool).
+    Launch all_reduce_sync(const ReduceRequest &req, ReduceOutcome &out);
     bool any_reduce_running();
     bool last_stats(uint64_t tag, pcclExtReduceStats_t &out);
 
@@ -113,6 +115,13 @@ private:
     void on_shared_state_accept(std::unique_ptr<net::BlockingSocket> sock);
     void on_benchmark_accept(std::unique_ptr<net::BlockingSocket> sock);
     ReduceOutcome run_reduce(const ReduceRequest &req, uint64_t revision_at_launch);
+    bool conclude(uint64_t tag, uint64_t revision_at_launch, ReduceOutcome &out);
+    // Completion handshakes that were left pending after a device-plane reduction returned early.
+    struct Deferred {
+        bool abort_seen = false, aborted = false;
+    };
+    bool finish_deferred(uint64_t tag, Deferred &d);
+    bool drain_deferred();
     std::shared_ptr<net::MuxSocket> pick_rx(const Uuid &peer, uint64_t seq, int timeout_ms);
     bool run_benchmark(const wire::BenchmarkRequest &req, double &mbits, bool &busy);
 
@@ -141,6 +150,9 @@ private:
         std::future<ReduceOutcome> future;
         uint64_t revision_at_launch = 0;
     };
+    std::mutex deferred_mu_;
+    std::map<uint64_t, Deferred> deferred_;
+    std::atomic<bool> master_pipelines_{false}; // the master queues an Initiate behind a pending Complete
     std::mutex ops_mu_;
     std::map<uint64_t, Op> ops_;
     std::map<uint64_t, pcclExtReduceStats_t> stats_;

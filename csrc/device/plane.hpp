@@ -46,6 +46,7 @@ struct DeviceReduceArgs {
     wire::DType quant_dtype = wire::DType::U8;
     uint64_t seq = 0;
     uint32_t rank = 0, world = 1;
+    bool use_nvls = false; // all peers agreed (through the master) to run this one over NVSwitch multicast
 };
 
 struct DeviceReduceResult {
@@ -70,9 +71,11 @@ public:
     // Maps the arenas of all ring members that live on this host.
     virtual void on_ring_changed(const std::vector<Uuid> &ring) = 0;
 
-    // True when this peer could run the described reduction on the device plane
-    // (buffers on a GPU, every ring member mapped, operator/type supported).
-    virtual bool can_reduce(const DeviceReduceArgs &args) = 0;
+    // What this peer could do for the described reduction: kCapP2P when the buffers are on the
+    // GPU, every ring member is mapped and the operator/type is supported by the peer-to-peer
+    // kernels; additionally kCapNvls when the multicast view exists and multimem can reduce it.
+    static constexpr uint32_t kCapP2P = 1, kCapNvls = 2;
+    virtual uint32_t capabilities(const DeviceReduceArgs &args) = 0;
 
     // Runs the reduction; `abort_requested` is polled while the kernel runs.
     virtual DeviceReduceResult reduce(const DeviceReduceArgs &args, const std::function<bool()> &abort_requested) = 0;

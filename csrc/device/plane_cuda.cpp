@@ -46,6 +46,13 @@ struct Driver {
     CUresult (*MemImportFromShareableHandle)(CUmemGenericAllocationHandle *, void *, CUmemAllocationHandleType) = nullptr;
     CUresult (*DeviceGet)(CUdevice *, int) = nullptr;
     CUresult (*DeviceGetAttribute)(int *, CUdevice_attribute, CUdevice) = nullptr;
+    // NVSwitch multicast (optional: absence only disables the NVLS path)
+    bool multicast = false;
+    CUresult (*MulticastCreate)(CUmemGenericAllocationHandle *, const CUmulticastObjectProp *) = nullptr;
+    CUresult (*MulticastAddDevice)(CUmemGenericAllocationHandle, CUdevice) = nullptr;
+    CUresult (*MulticastBindMem)(CUmemGenericAllocationHandle, size_t, CUmemGenericAllocationHandle, size_t, size_t, unsigned long long) = nullptr;
+    CUresult (*MulticastUnbind)(CUmemGenericAllocationHandle, CUdevice, size_t, size_t) = nullptr;
+    CUresult (*MulticastGetGranularity)(size_t *, const CUmulticastObjectProp *, CUmulticastGranularity_flags) = nullptr;
 };
 
 const Driver &driver() {
@@ -80,6 +87,13 @@ const Driver &driver() {
         load("cuDeviceGet", x.DeviceGet);
         load("cuDeviceGetAttribute", x.DeviceGetAttribute);
         x.ok = all;
+        all = true;
+        load("cuMulticastCreate", x.MulticastCreate);
+        load("cuMulticastAddDevice", x.MulticastAddDevice);
+        load("cuMulticastBindMem", x.MulticastBindMem);
+        load("cuMulticastUnbind", x.MulticastUnbind);
+        load("cuMulticastGetGranularity", x.MulticastGetGranularity);
+        x.multicast = all;
         return x;
     }();
     return d;
@@ -105,17 +119,19 @@ const Driver &driver() {
 
 // ------------------------------------------------------------------------------------------ unix rendezvous
 constexpr uint32_t kMagic = 0x50434231; // "PCB1"
-enum : uint32_t { kReqArena = 1 };
+enum : uint32_t { kReqArena = 1, kReqMulticast = 2, kReqMulticastAdded = 3, kReqMulticastReady = 4 };
 
 struct RendezvousRequest {
     uint32_t magic, kind;
     uint8_t requester[16];
+    uint64_t ring_key; // identifies the membership epoch a multicast object belongs to
 };
 struct RendezvousReply {
     uint32_t magic, status; // status 0 = ok
     uint64_t arena_bytes, slot_bytes, sym_bytes;
     uint32_t n_slots, pid;
     uint8_t gpu_uuid[16];
+    uint32_t multicast_ok, added_count;
 };
 
 sockaddr_un rendezvous_address(const Uuid &u, socklen_t &len) {
@@ -178,11 +194,13 @@ public:
                 clock_khz_ = prop.clockRate > 0 ? prop.clockRate : 1900000;
             }
         }
-        slot_bytes_ = round_up(env_u64("PCCL_ARENA_SLOT_MB", 256) << 20, 2u << 20);
-        n_slots_ = static_cast<uint32_t>(std::clamp<uint64_t>(env_u64("PCCL_ARENA_SLOTS", 4), 1, 15));
-        sym_bytes_ = round_up(env_u64("PCCL_SYMMETRIC_MB", 0) << 20, 2u << 20);
+        slot_bytes_ = round_up(env_u64("PCCL_ARENA_SLOT_MB", 768) << 20, 2u << 20);
+        n_slots_ = static_cast<uint32_t>(std::clamp<uint64_t>(env_u64("PCCL_ARENA_SLOTS", 2), 1, 15));
+        sym_bytes_ = round_up(env_u64("PCCL_SYMMETRIC_MB", 1024) << 20, 2u << 20);
         timeout_ms_ = env_u64("PCCL_DEVICE_TIMEOUT_MS", 30000);
         max_blocks_ = static_cast<int>(env_u64("PCCL_DEVICE_MAX_BLOCKS", 0));
+        nvls_min_world_ = static_cast<uint32_t>(env_u64("PCCL_NVLS_MIN_WORLD", 4));
+        nvls_min_bytes_ = env_u64("PCCL_NVLS_MIN_BYTES", 1u << 20);
     }
     ~CudaPlane() override { stop(); }
 
@@ -213,6 +231,7 @@ public:
         std::lock_guard<std::mutex> lock(mu_);
         if (!usable_) return;
         cudaSetDevice(device_);
+        if (arena_ptr_) teardown_multicast();
         for (auto &[u, p] : peers_) unmap_peer(p);
         peers_.clear();
         for (auto &s : slots_) {
@@ -237,6 +256,10 @@ public:
         std::lock_guard<std::mutex> lock(mu_);
         ring_ = ring;
         ring_ready_ = false;
+        if (usable_ && arena_ptr_) {
+            cudaSetDevice(device_);
+            teardown_multicast();
+        }
         if (!usable_ || !started_ || ring.size() < 2 || ring.size() > PCCL_K_MAX_RANKS) return;
         cudaSetDevice(device_);
         if (!ensure_arena()) return;
@@ -279,30 +302,42 @@ public:
         }
         ring_ready_ = true;
         PLOG(INFO) << "device plane ready: " << ring.size() << " peers mapped over NVLink";
+        setup_multicast(ring);
     }
 
-    bool can_reduce(const DeviceReduceArgs &a) override {
+    uint32_t capabilities(const DeviceReduceArgs &a) override {
         std::lock_guard<std::mutex> lock(mu_);
-        if (!ring_ready_ || a.world != ring_.size()) return false;
+        if (!ring_ready_ || a.world != ring_.size()) return 0;
         const PointerInfo s = classify_pointer(a.src), d = classify_pointer(a.dst);
-        if (!s.is_device || !d.is_device || s.device != device_ || d.device != device_) return false;
-        if (a.dtype == wire::DType::F8E4M3) return false;
+        if (!s.is_device || !d.is_device || s.device != device_ || d.device != device_) return 0;
+        if (a.dtype == wire::DType::F8E4M3) return 0;
         switch (a.quant) {
-        case wire::QuantAlgo::None: return true;
+        case wire::QuantAlgo::None:
+            // Through the switch every GPU moves about N(1+1/P) bytes per direction (its own stores
+            // are echoed back), peer-to-peer two-shot moves 2N(P-1)/P: multicast pays off from 4 peers.
+            return kCapP2P | (mc_ready_ && a.world >= nvls_min_world_ && a.count * wire::dtype_size(a.dtype) >= nvls_min_bytes_ &&
+                                      pcclKernelNvlsSupported(pccl_dtype(a.dtype), pccl_op(a.op))
+                                  ? kCapNvls
+                                  : 0u);
         // on the device plane uint8 min-max is block-scaled (128 elements per (min,max) pair)
         case wire::QuantAlgo::MinMax:
-        case wire::QuantAlgo::BlockMinMax: return a.dtype == wire::DType::F32 && a.quant_dtype == wire::DType::U8;
-        case wire::QuantAlgo::BlockFp8: return a.dtype == wire::DType::F32 && a.quant_dtype == wire::DType::F8E4M3;
-        default: return false;
+        case wire::QuantAlgo::BlockMinMax: return a.dtype == wire::DType::F32 && a.quant_dtype == wire::DType::U8 ? kCapP2P : 0u;
+        case wire::QuantAlgo::BlockFp8: return a.dtype == wire::DType::F32 && a.quant_dtype == wire::DType::F8E4M3 ? kCapP2P : 0u;
+        default: return 0;
         }
     }
 
     DeviceReduceResult reduce(const DeviceReduceArgs &a, const std::function<bool()> &abort_requested) override {
         DeviceReduceResult res;
         std::vector<void *> arenas;
+        void *mc_view = nullptr;
         {
             std::lock_guard<std::mutex> lock(mu_);
             if (!ring_ready_ || a.world != ring_.size()) return res;
+            if (a.use_nvls) {
+                if (!mc_ready_) return res;
+                mc_view = reinterpret_cast<void *>(mc_.ptr);
+            }
             for (const auto &u : ring_) arenas.push_back(u == self_ ? reinterpret_cast<void *>(arena_ptr_) : reinterpret_cast<void *>(peers_.at(u).ptr));
         }
         cudaSetDevice(device_);
@@ -376,7 +411,16 @@ public:
             k.abort_flag = reinterpret_cast<volatile uint32_t *>(slot.host_words);
             k.status = slot.host_words + 1;
             k.timeout_cycles = timeout_ms_ * static_cast<uint64_t>(clock_khz_);
-            const int rc = pcclKernelAllReduceP2P(&k, &algorithm, slot.stream);
+            int rc;
+            if (mc_view) {
+                pcclKernelNvlsArgs_t nk{};
+                nk.p2p = k;
+                nk.mc_arena = mc_view;
+                rc = pcclKernelAllReduceNvls(&nk, slot.stream);
+                algorithm = 3;
+            } else {
+                rc = pcclKernelAllReduceP2P(&k, &algorithm, slot.stream);
+            }
             if (rc != 0) {
                 PLOG(ERR) << "all-reduce kernel launch failed: " << cudaGetErrorString(static_cast<cudaError_t>(rc));
                 cudaStreamSynchronize(slot.stream);
@@ -404,9 +448,11 @@ public:
         }
         const uint32_t status = reinterpret_cast<volatile uint32_t *>(slot.host_words)[1];
         cudaEventElapsedTime(&res.device_ms, slot.start, slot.stop);
-        res.plane = algorithm == 1 ? pcclExtPlaneP2POneShot : pcclExtPlaneP2PTwoShot;
+        res.plane = algorithm == 1 ? pcclExtPlaneP2POneShot : (algorithm == 3 ? pcclExtPlaneNvls : pcclExtPlaneP2PTwoShot);
         const uint64_t wire_bytes = quant ? a.count : a.count * esz;
-        res.tx_bytes = res.rx_bytes = algorithm == 1 ? wire_bytes * (a.world - 1) : 2 * wire_bytes * (a.world - 1) / a.world;
+        res.tx_bytes = res.rx_bytes = algorithm == 1   ? wire_bytes * (a.world - 1)
+                                      : algorithm == 3 ? wire_bytes + wire_bytes / a.world
+                                                       : 2 * wire_bytes * (a.world - 1) / a.world;
         res.ok = status == 0;
         if (status == 2) PLOG(ERR) << "device all-reduce timed out waiting for a peer";
         return res;
@@ -534,6 +580,17 @@ private:
         prop.requestedHandleTypes = CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR;
         size_t gran = 2u << 20;
         CU_TRY(d.MemGetAllocationGranularity(&gran, &prop, CU_MEM_ALLOC_GRANULARITY_RECOMMENDED));
+        if (d.multicast) {
+            CUmulticastObjectProp mprop{};
+            mprop.numDevices = 2;
+            mprop.size = gran;
+            mprop.handleTypes = CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR;
+            size_t mg = 0;
+            if (d.MulticastGetGranularity(&mg, &mprop, CU_MULTICAST_GRANULARITY_RECOMMENDED) == CUDA_SUCCESS && mg > 0) {
+                mc_gran_ = mg;
+                gran = std::max(gran, mg);
+            }
+        }
         arena_bytes_ = round_up(pcclKernelP2PControlBytes() + size_t(n_slots_) * slot_bytes_ + sym_bytes_, gran);
         CU_TRY(d.MemCreate(&arena_handle_, arena_bytes_, &prop, 0));
         CU_TRY(d.MemAddressReserve(&arena_ptr_, arena_bytes_, gran, 0, 0));
@@ -585,7 +642,7 @@ private:
             ::close(sock);
             return false;
         }
-        RendezvousRequest req{kMagic, kReqArena, {0}};
+        RendezvousRequest req{kMagic, kReqArena, {0}, 0};
         std::memcpy(req.requester, self_.data.data(), 16);
         RendezvousReply rep{};
         int fd = -1;
@@ -627,6 +684,162 @@ private:
         return true;
     }
 
+    static uint64_t ring_key_of(const std::vector<Uuid> &ring) {
+        uint64_t h = 1469598103934665603ull;
+        for (const auto &u : ring)
+            for (uint8_t b : u.data) h = (h ^ b) * 1099511628211ull;
+        return h ? h : 1;
+    }
+
+    // One request/reply with a peer's rendezvous server.  Returns false when unreachable.
+    bool ask(const Uuid &who, uint32_t kind, uint64_t ring_key, RendezvousReply &rep, int &fd) {
+        fd = -1;
+        const int sock = ::socket(AF_UNIX, SOCK_STREAM | SOCK_CLOEXEC, 0);
+        if (sock < 0) return false;
+        socklen_t len;
+        const sockaddr_un sa = rendezvous_address(who, len);
+        if (::connect(sock, reinterpret_cast<const sockaddr *>(&sa), len) != 0) {
+            ::close(sock);
+            return false;
+        }
+        RendezvousRequest req{kMagic, kind, {0}, ring_key};
+        std::memcpy(req.requester, self_.data.data(), 16);
+        const bool ok = ::send(sock, &req, sizeof req, MSG_NOSIGNAL) == static_cast<ssize_t>(sizeof req) &&
+                        recv_with_fd(sock, &rep, sizeof rep, fd, 10000) && rep.magic == kMagic;
+        ::close(sock);
+        return ok;
+    }
+
+    // mu_ held, device current
+    void teardown_multicast() {
+        mc_ready_ = false;
+        std::lock_guard<std::mutex> lock(mc_mu_);
+        if (mc_.ptr) {
+            driver().MemUnmap(mc_.ptr, arena_bytes_);
+            driver().MemAddressFree(mc_.ptr, arena_bytes_);
+        }
+        if (mc_.bound) {
+            CUdevice dev;
+            if (driver().DeviceGet(&dev, device_) == CUDA_SUCCESS) driver().MulticastUnbind(mc_.handle, dev, 0, arena_bytes_);
+        }
+        if (mc_.have) driver().MemRelease(mc_.handle);
+        mc_ = Multicast{};
+    }
+
+    // Builds the multicast view of all arenas of the ring (NVSwitch multimem path).  Every member
+    // runs this after the unicast mappings exist: the first member of the ring creates the
+    // object, everybody adds its device, and only when all devices are in does anybody bind
+    // memory (a CUDA requirement).  Failure just leaves the NVLS path off; whether it is used is
+    // agreed per operation through the master, so a member without it cannot diverge.
+    // mu_ held, device current
+    void setup_multicast(const std::vector<Uuid> &ring) {
+        const Driver &d = driver();
+        if (!d.multicast || !env_flag("PCCL_NVLS", true)) return;
+        CUdevice dev;
+        int supported = 0;
+        if (d.DeviceGet(&dev, device_) != CUDA_SUCCESS ||
+            d.DeviceGetAttribute(&supported, CU_DEVICE_ATTRIBUTE_MULTICAST_SUPPORTED, dev) != CUDA_SUCCESS || !supported) {
+            PLOG(INFO) << "multicast is not supported on this device: NVLS path off";
+            return;
+        }
+        if (mc_gran_ == 0 || arena_bytes_ % mc_gran_ != 0) return;
+        const uint64_t key = ring_key_of(ring);
+        const Uuid &leader = ring[0];
+        const uint32_t world = static_cast<uint32_t>(ring.size());
+        CUmulticastObjectProp prop{};
+        prop.numDevices = world;
+        prop.size = arena_bytes_;
+        prop.handleTypes = CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR;
+        const auto deadline = clock_type::now() + std::chrono::seconds(15);
+        CUmemGenericAllocationHandle handle = 0;
+        if (leader == self_) {
+            const CUresult rc = d.MulticastCreate(&handle, &prop);
+            if (rc != CUDA_SUCCESS) {
+                PLOG(INFO) << "cuMulticastCreate failed (" << static_cast<int>(rc) << "): NVLS path off";
+                return;
+            }
+            std::lock_guard<std::mutex> lock(mc_mu_);
+            mc_.ring_key = key;
+            mc_.handle = handle;
+            mc_.created = mc_.have = true;
+        } else {
+            bool got = false;
+            while (!got && clock_type::now() < deadline) {
+                RendezvousReply rep{};
+                int fd = -1;
+                if (ask(leader, kReqMulticast, key, rep, fd) && rep.status == 0 && fd >= 0) {
+                    const CUresult rc = d.MemImportFromShareableHandle(&handle, reinterpret_cast<void *>(static_cast<uintptr_t>(fd)),
+                                                                       CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR);
+                    ::close(fd);
+                    if (rc != CUDA_SUCCESS) return;
+                    got = true;
+                } else {
+                    if (fd >= 0) ::close(fd);
+                    if (rep.status == 1) return; // leader cannot do multicast
+                    std::this_thread::sleep_for(std::chrono::milliseconds(5));
+                }
+            }
+            if (!got) return;
+            std::lock_guard<std::mutex> lock(mc_mu_);
+            mc_.ring_key = key;
+            mc_.handle = handle;
+            mc_.have = true;
+        }
+        if (d.MulticastAddDevice(handle, dev) != CUDA_SUCCESS) {
+            PLOG(INFO) << "cuMulticastAddDevice failed: NVLS path off";
+            return;
+        }
+        // tell the leader, then wait until every member has added its device
+        if (leader == self_) {
+            std::lock_guard<std::mutex> lock(mc_mu_);
+            mc_.added++;
+        } else {
+            RendezvousReply rep{};
+            int fd = -1;
+            if (!ask(leader, kReqMulticastAdded, key, rep, fd) || rep.status != 0) return;
+        }
+        for (;;) {
+            uint32_t added = 0;
+            if (leader == self_) {
+                std::lock_guard<std::mutex> lock(mc_mu_);
+                added = mc_.added;
+            } else {
+                RendezvousReply rep{};
+                int fd = -1;
+                if (!ask(leader, kReqMulticastReady, key, rep, fd) || rep.status != 0) return;
+                added = rep.added_count;
+            }
+            if (added >= world) break;
+            if (clock_type::now() > deadline) {
+                PLOG(WARN) << "multicast setup timed out (" << added << "/" << world << " devices): NVLS path off";
+                return;
+            }
+            std::this_thread::sleep_for(std::chrono::milliseconds(2));
+        }
+        CUresult rc = d.MulticastBindMem(handle, 0, arena_handle_, 0, arena_bytes_, 0);
+        if (rc != CUDA_SUCCESS) {
+            PLOG(INFO) << "cuMulticastBindMem failed (" << static_cast<int>(rc) << "): NVLS path off";
+            return;
+        }
+        CUdeviceptr ptr = 0;
+        CUmemAccessDesc acc{};
+        acc.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
+        acc.location.id = device_;
+        acc.flags = CU_MEM_ACCESS_FLAGS_PROT_READWRITE;
+        if (d.MemAddressReserve(&ptr, arena_bytes_, mc_gran_, 0, 0) != CUDA_SUCCESS) return;
+        if (d.MemMap(ptr, arena_bytes_, 0, handle, 0) != CUDA_SUCCESS || d.MemSetAccess(ptr, arena_bytes_, &acc, 1) != CUDA_SUCCESS) {
+            d.MemAddressFree(ptr, arena_bytes_);
+            return;
+        }
+        {
+            std::lock_guard<std::mutex> lock(mc_mu_);
+            mc_.bound = true;
+            mc_.ptr = ptr;
+        }
+        mc_ready_ = true;
+        PLOG(INFO) << "NVSwitch multicast view of " << world << " arenas mapped: NVLS path on";
+    }
+
     void serve() {
         cudaSetDevice(device_);
         while (!stopping_) {
@@ -640,8 +853,9 @@ private:
             rep.magic = kMagic;
             rep.status = 1;
             int fd = -1;
-            if (::poll(&cp, 1, 2000) > 0 && ::recv(c, &req, sizeof req, MSG_WAITALL) == static_cast<ssize_t>(sizeof req) &&
-                req.magic == kMagic && req.kind == kReqArena) {
+            const bool got = ::poll(&cp, 1, 2000) > 0 && ::recv(c, &req, sizeof req, MSG_WAITALL) == static_cast<ssize_t>(sizeof req) &&
+                             req.magic == kMagic;
+            if (got && req.kind == kReqArena) {
                 if (ensure_arena() && driver().MemExportToShareableHandle(&fd, arena_handle_, CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR, 0) == CUDA_SUCCESS) {
                     rep.status = 0;
                     rep.arena_bytes = arena_bytes_;
@@ -650,6 +864,22 @@ private:
                     rep.n_slots = n_slots_;
                     rep.pid = static_cast<uint32_t>(::getpid());
                     std::memcpy(rep.gpu_uuid, gpu_uuid_, 16);
+                }
+            } else if (got) {
+                // multicast bookkeeping; this peer answers as the leader (first member of the ring)
+                std::lock_guard<std::mutex> lock(mc_mu_);
+                if (mc_.created && mc_.ring_key == req.ring_key) {
+                    if (req.kind == kReqMulticast) {
+                        if (driver().MemExportToShareableHandle(&fd, mc_.handle, CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR, 0) == CUDA_SUCCESS) rep.status = 0;
+                    } else if (req.kind == kReqMulticastAdded) {
+                        mc_.added++;
+                        rep.status = 0;
+                    } else if (req.kind == kReqMulticastReady) {
+                        rep.status = 0;
+                    }
+                    rep.added_count = mc_.added;
+                } else {
+                    rep.status = 2; // not (yet) the leader of that epoch: ask again
                 }
             }
             send_with_fd(c, &rep, sizeof rep, fd);
@@ -688,10 +918,24 @@ private:
 
     std::mutex mu_;
     std::mutex arena_mu_; // guards arena creation only; never held while waiting for a peer
+    struct Multicast {
+        uint64_t ring_key = 0;
+        CUmemGenericAllocationHandle handle = 0;
+        bool created = false; // this peer created the object (leader)
+        bool have = false, bound = false;
+        uint32_t added = 0;
+        CUdeviceptr ptr = 0;
+    };
+    std::mutex mc_mu_; // leader-side multicast bookkeeping, shared with the server thread
+    Multicast mc_;
+    bool mc_ready_ = false;
+    size_t mc_gran_ = 0;
     size_t slot_bytes_ = 0, sym_bytes_ = 0, arena_bytes_ = 0;
     uint32_t n_slots_ = 4;
     uint64_t timeout_ms_ = 30000;
     int max_blocks_ = 0;
+    uint32_t nvls_min_world_ = 4;
+    uint64_t nvls_min_bytes_ = 1u << 20;
     CUdeviceptr arena_ptr_ = 0;
     CUmemGenericAllocationHandle arena_handle_ = 0;
     std::vector<Slot> slots_;

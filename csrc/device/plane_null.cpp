@@ -10,7 +10,7 @@ public:
     void start(const Uuid &) override {}
     void stop() override {}
     void on_ring_changed(const std::vector<Uuid> &) override {}
-    bool can_reduce(const DeviceReduceArgs &) override { return false; }
+    uint32_t capabilities(const DeviceReduceArgs &) override { return 0; }
     DeviceReduceResult reduce(const DeviceReduceArgs &, const std::function<bool()> &) override { return {}; }
     bool restore_input(const DeviceReduceArgs &) override { return false; }
     bool copy_to_host(void *, const void *, size_t) override { return false; }

@@ -1,0 +1,291 @@
+// All-reduce through NVSwitch multicast ("NVLS"): the switch performs the reduction
+// (multimem.ld_reduce pulls one packet from every GPU's arena and returns the reduced value) and
+// the broadcast (multimem.st writes one packet into every GPU's arena).  Per GPU and direction
+// about N(1 + 1/P) bytes cross NVLink instead of 2N(P-1)/P for the peer-to-peer two-shot.
+//
+// No counterpart in the reference (host TCP ring only, ccoip/src/cpp/reduce.cpp:528-784).
+//
+// Same arena, flag and work-partition scheme as allreduce_p2p.cu.  `mc` is the multicast mapping
+// of ALL ranks' arenas (same offsets).  Phases:
+//   0  copy the input into the own arena            (skipped for symmetric memory)
+//   barrier
+//   1  rank r, for the packets of chunk r: ld_reduce over all arenas, AVG scaling, multimem.st
+//      of the result back into every arena (in place: only rank r ever touches chunk r here)
+//   barrier
+//   2  copy the own arena into the output            (skipped for symmetric memory, in place)
+// No trailing barrier is needed: a peer can only touch this arena again after the first barrier
+// of the NEXT operation, which this rank enters after its copy-out.
+#include "common.cuh"
+#include "pccl_kernels.h"
+
+namespace pccl::cuda {
+
+constexpr int kNvlsThreads = 512;
+constexpr size_t kNvlsFlagBankBytes = size_t(PCCL_K_MAX_BLOCKS) * 128;
+
+struct NvlsArgs {
+    uint8_t *arena[PCCL_K_MAX_RANKS]; // unicast mappings, for the flags
+    uint8_t *mc;                      // multicast mapping of the arenas
+    uint32_t rank, world, flag_slot;
+    uint64_t flag_base, data_offset;
+    const void *src;
+    void *dst;
+    uint64_t count;
+    uint64_t avg_divisor;
+    int src_in_arena;
+    volatile uint32_t *abort_flag;
+    uint32_t *status;
+    uint64_t timeout_cycles;
+};
+
+__device__ bool nvls_barrier(const NvlsArgs &a, uint8_t *const *arena, uint64_t value) {
+    __shared__ int s_fail;
+    if (threadIdx.x == 0) s_fail = 0;
+    __threadfence_system(); // multimem stores of this thread are performed before the flag is raised
+    __syncthreads();
+    if (threadIdx.x < a.world) {
+        const uint32_t peer = threadIdx.x;
+        uint64_t *theirs = reinterpret_cast<uint64_t *>(arena[peer] + a.flag_slot * kNvlsFlagBankBytes + size_t(blockIdx.x) * 128) + a.rank;
+        st_flag_release(theirs, value);
+        const uint64_t *mine = reinterpret_cast<const uint64_t *>(arena[a.rank] + a.flag_slot * kNvlsFlagBankBytes + size_t(blockIdx.x) * 128) + peer;
+        const long long t0 = clock64();
+        uint32_t spins = 0;
+        while (ld_flag_acquire(mine) < value) {
+            if ((++spins & 0x3ffu) == 0) {
+                if (*a.abort_flag != 0) {
+                    atomicExch(&s_fail, 1);
+                    break;
+                }
+                if (static_cast<uint64_t>(clock64() - t0) > a.timeout_cycles) {
+                    atomicExch(&s_fail, 2);
+                    break;
+                }
+            }
+        }
+    }
+    __syncthreads();
+    const int fail = s_fail;
+    if (fail != 0 && threadIdx.x == 0) atomicMax(a.status, static_cast<uint32_t>(fail));
+    return fail == 0;
+}
+
+enum : int { NV_F32 = 0, NV_BF16 = 1, NV_F16 = 2 };
+
+template <int TYPE, int OP> __device__ __forceinline__ uint4 mc_ld_reduce(const void *p) {
+    uint4 v;
+    if constexpr (TYPE == NV_F32) {
+        static_assert(OP == OP_SUM, "multimem.ld_reduce on f32 only adds");
+        asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+                     : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+    } else if constexpr (TYPE == NV_BF16) {
+        if constexpr (OP == OP_SUM)
+            asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0,%1,%2,%3}, [%4];"
+                         : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+        else if constexpr (OP == OP_MAX)
+            asm volatile("multimem.ld_reduce.relaxed.sys.global.max.v4.bf16x2 {%0,%1,%2,%3}, [%4];"
+                         : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+        else
+            asm volatile("multimem.ld_reduce.relaxed.sys.global.min.v4.bf16x2 {%0,%1,%2,%3}, [%4];"
+                         : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+    } else {
+        if constexpr (OP == OP_SUM)
+            asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.f16x2 {%0,%1,%2,%3}, [%4];"
+                         : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+        else if constexpr (OP == OP_MAX)
+            asm volatile("multimem.ld_reduce.relaxed.sys.global.max.v4.f16x2 {%0,%1,%2,%3}, [%4];"
+                         : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+        else
+            asm volatile("multimem.ld_reduce.relaxed.sys.global.min.v4.f16x2 {%0,%1,%2,%3}, [%4];"
+                         : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p) : "memory");
+    }
+    return v;
+}
+
+__device__ __forceinline__ void mc_store(void *p, uint4 v) {
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+
+template <int TYPE> __device__ __forceinline__ uint4 scale_packet(uint4 v, float inv) {
+    if constexpr (TYPE == NV_F32) {
+        v.x = __float_as_uint(__uint_as_float(v.x) * inv);
+        v.y = __float_as_uint(__uint_as_float(v.y) * inv);
+        v.z = __float_as_uint(__uint_as_float(v.z) * inv);
+        v.w = __float_as_uint(__uint_as_float(v.w) * inv);
+    } else if constexpr (TYPE == NV_BF16) {
+        uint32_t *w = &v.x;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            __nv_bfloat162 h = *reinterpret_cast<__nv_bfloat162 *>(&w[i]);
+            float2 f = __bfloat1622float2(h);
+            h = __floats2bfloat162_rn(f.x * inv, f.y * inv);
+            w[i] = *reinterpret_cast<uint32_t *>(&h);
+        }
+    } else {
+        uint32_t *w = &v.x;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            __half2 h = *reinterpret_cast<__half2 *>(&w[i]);
+            float2 f = __half22float2(h);
+            h = __floats2half2_rn(f.x * inv, f.y * inv);
+            w[i] = *reinterpret_cast<uint32_t *>(&h);
+        }
+    }
+    return v;
+}
+
+// Byte-granular slow paths for unaligned buffers and the last partial packet.  Not inlined on
+// purpose: their byte arrays must not drag the callers' packet registers into local memory.
+__device__ __noinline__ uint4 load_partial(const uint8_t *src, uint64_t lo, uint64_t hi) {
+    alignas(16) uint8_t bytes[16] = {0};
+    for (uint64_t b = lo; b < hi; ++b) bytes[b - lo] = src[b];
+    return *reinterpret_cast<uint4 *>(bytes);
+}
+__device__ __noinline__ void store_partial(uint8_t *dst, uint64_t lo, uint64_t hi, uint4 val) {
+    alignas(16) uint8_t bytes[16];
+    *reinterpret_cast<uint4 *>(bytes) = val;
+    for (uint64_t b = lo; b < hi; ++b) dst[b] = bytes[b - lo];
+}
+
+template <int U, typename Fn> __device__ __forceinline__ void nvls_owned_packets(uint64_t lo, uint64_t hi, Fn fn) {
+    if (lo >= hi) return;
+    const uint64_t first_tile = lo / kNvlsThreads;
+    uint64_t tile = first_tile + ((blockIdx.x + gridDim.x - first_tile % gridDim.x) % gridDim.x);
+    const uint64_t stride = uint64_t(gridDim.x) * U;
+    for (; tile * kNvlsThreads < hi; tile += stride) {
+        uint64_t v[U];
+        bool ok[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            v[u] = (tile + uint64_t(u) * gridDim.x) * kNvlsThreads + threadIdx.x;
+            ok[u] = v[u] >= lo && v[u] < hi;
+        }
+        fn(v, ok);
+    }
+}
+
+template <int TYPE, int OP> __global__ void __launch_bounds__(kNvlsThreads, 1) allreduce_nvls_kernel(const NvlsArgs a) {
+    constexpr int ESZ = TYPE == NV_F32 ? 4 : 2;
+    constexpr int N = 16 / ESZ;
+    __shared__ uint8_t *s_arena[PCCL_K_MAX_RANKS];
+    if (threadIdx.x < PCCL_K_MAX_RANKS) s_arena[threadIdx.x] = threadIdx.x < a.world ? a.arena[threadIdx.x] : nullptr;
+    __syncthreads();
+    const uint64_t n_pack = (a.count + N - 1) / N;
+    const uint64_t per = (n_pack + a.world - 1) / a.world;
+    const uint8_t *src = static_cast<const uint8_t *>(a.src);
+    uint8_t *dst = static_cast<uint8_t *>(a.dst);
+    uint4 *mine = reinterpret_cast<uint4 *>(s_arena[a.rank] + a.data_offset);
+    uint4 *mc = reinterpret_cast<uint4 *>(a.mc + a.data_offset);
+    const uint64_t full_packets = a.count / N; // packets completely inside the user buffers
+    const bool aligned = ((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst)) & 15) == 0;
+
+    if (!a.src_in_arena) {
+        nvls_owned_packets<4>(0, n_pack, [&](const uint64_t(&v)[4], const bool(&ok)[4]) {
+            uint4 tmp[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                if (!ok[u]) continue;
+                if (aligned && v[u] < full_packets) {
+                    tmp[u] = ld_stream_16(src + v[u] * 16);
+                } else {
+                    tmp[u] = load_partial(src, v[u] * 16, min(v[u] * 16 + 16, uint64_t(a.count * ESZ)));
+                }
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+                if (ok[u]) mine[v[u]] = tmp[u];
+        });
+    }
+    if (!nvls_barrier(a, s_arena, a.flag_base + 1)) return;
+
+    {
+        const uint64_t lo = min(uint64_t(a.rank) * per, n_pack), hi = min(lo + per, n_pack);
+        const float inv = a.avg_divisor ? 1.0f / static_cast<float>(a.avg_divisor) : 1.0f;
+        nvls_owned_packets<4>(lo, hi, [&](const uint64_t(&v)[4], const bool(&ok)[4]) {
+            uint4 val[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+                if (ok[u]) val[u] = mc_ld_reduce<TYPE, OP>(mc + v[u]);
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                if (!ok[u]) continue;
+                if (a.avg_divisor) val[u] = scale_packet<TYPE>(val[u], inv);
+                mc_store(mc + v[u], val[u]);
+            }
+        });
+    }
+    if (!nvls_barrier(a, s_arena, a.flag_base + 2)) return;
+
+    if (!a.src_in_arena) {
+        nvls_owned_packets<4>(0, n_pack, [&](const uint64_t(&v)[4], const bool(&ok)[4]) {
+            uint4 tmp[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+                if (ok[u]) tmp[u] = ld_peer_16(mine + v[u]); // written through the switch: do not trust L1
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                if (!ok[u]) continue;
+                if (aligned && v[u] < full_packets) {
+                    st_stream_16(dst + v[u] * 16, tmp[u]);
+                } else {
+                    store_partial(dst, v[u] * 16, min(v[u] * 16 + 16, uint64_t(a.count * ESZ)), tmp[u]);
+                }
+            }
+        });
+    }
+}
+
+} // namespace pccl::cuda
+
+using namespace pccl::cuda;
+
+extern "C" int pcclKernelNvlsSupported(int dtype, int op) {
+    if (dtype == pcclFloat) return op == pcclSum || op == pcclAvg;
+    if (dtype == pcclBFloat16 || dtype == pcclFloat16) return op == pcclSum || op == pcclAvg || op == pcclMax || op == pcclMin;
+    return 0;
+}
+
+extern "C" int pcclKernelAllReduceNvls(const pcclKernelNvlsArgs_t *args, void *stream_v) {
+    if (!args || !args->mc_arena) return cudaErrorInvalidValue;
+    const pcclKernelP2PArgs_t &p = args->p2p;
+    if (p.world < 2 || p.world > PCCL_K_MAX_RANKS || p.rank >= p.world) return cudaErrorInvalidValue;
+    if (!pcclKernelNvlsSupported(p.dtype, p.op)) return cudaErrorInvalidValue;
+    NvlsArgs d{};
+    for (uint32_t r = 0; r < p.world; ++r) d.arena[r] = static_cast<uint8_t *>(p.arena[r]);
+    d.mc = static_cast<uint8_t *>(args->mc_arena);
+    d.rank = p.rank;
+    d.world = p.world;
+    d.flag_slot = p.flag_slot;
+    d.flag_base = p.flag_base;
+    d.data_offset = p.data_offset;
+    d.src = p.src;
+    d.dst = p.dst;
+    d.count = p.count;
+    d.avg_divisor = p.op == pcclAvg ? p.world : 0;
+    d.src_in_arena = p.src_in_arena;
+    d.abort_flag = p.abort_flag;
+    d.status = p.status;
+    d.timeout_cycles = p.timeout_cycles ? p.timeout_cycles : ~0ull;
+    const size_t esz = p.dtype == pcclFloat ? 4 : 2;
+    if ((p.count * esz + 15) / 16 * 16 + 256 > p.data_capacity) return cudaErrorInvalidValue;
+    if (p.data_offset % 16 != 0) return cudaErrorInvalidValue;
+    const uint64_t n_pack = (p.count * esz + 15) / 16;
+    const uint64_t tiles = (n_pack + kNvlsThreads - 1) / kNvlsThreads;
+    int max_blocks = p.max_blocks > 0 ? p.max_blocks : 144;
+    if (max_blocks > PCCL_K_MAX_BLOCKS) max_blocks = PCCL_K_MAX_BLOCKS;
+    const uint64_t chunk_tiles = (tiles + p.world - 1) / p.world;
+    const int grid = static_cast<int>(std::max<uint64_t>(1, std::min<uint64_t>(max_blocks, chunk_tiles)));
+    const auto stream = static_cast<cudaStream_t>(stream_v);
+    const int op = p.op == pcclMax ? OP_MAX : (p.op == pcclMin ? OP_MIN : OP_SUM);
+    if (p.dtype == pcclFloat) {
+        allreduce_nvls_kernel<NV_F32, OP_SUM><<<grid, kNvlsThreads, 0, stream>>>(d);
+    } else if (p.dtype == pcclBFloat16) {
+        if (op == OP_SUM) allreduce_nvls_kernel<NV_BF16, OP_SUM><<<grid, kNvlsThreads, 0, stream>>>(d);
+        else if (op == OP_MAX) allreduce_nvls_kernel<NV_BF16, OP_MAX><<<grid, kNvlsThreads, 0, stream>>>(d);
+        else allreduce_nvls_kernel<NV_BF16, OP_MIN><<<grid, kNvlsThreads, 0, stream>>>(d);
+    } else {
+        if (op == OP_SUM) allreduce_nvls_kernel<NV_F16, OP_SUM><<<grid, kNvlsThreads, 0, stream>>>(d);
+        else if (op == OP_MAX) allreduce_nvls_kernel<NV_F16, OP_MAX><<<grid, kNvlsThreads, 0, stream>>>(d);
+        else allreduce_nvls_kernel<NV_F16, OP_MIN><<<grid, kNvlsThreads, 0, stream>>>(d);
+    }
+    return cudaGetLastError();
+}

@@ -747,11 +747,19 @@ void Master::eval_sync_complete(uint32_t group) {
 void Master::handle_collective_initiate(Client &c, const C2MCollectiveInitiate &p) {
     if (c.phase != Phase::Accepted || (c.state != State::Idle && c.state != State::CollectiveCommunicationsRunning))
         return kick(c.link, "collective-initiate vote in illegal state");
-    if (c.collectives.count(p.tag)) return kick(c.link, "collective tag already in flight");
+    if (const auto it = c.collectives.find(p.tag); it != c.collectives.end()) {
+        // extension: a peer that already voted Complete may vote for the NEXT operation on the
+        // same tag right away; the vote takes effect when the current one is finished
+        if (it->second != CollectiveState::VoteComplete || c.queued_initiate.count(p.tag))
+            return kick(c.link, "collective tag already in flight");
+        c.queued_initiate[p.tag] = static_cast<uint8_t>(p.op) & 0xc0u;
+        return;
+    }
     c.state = State::CollectiveCommunicationsRunning;
     c.collectives[p.tag] = CollectiveState::VoteInitiate;
     // extension: top bit of the operator byte = "I can run this one on the device plane"
-    c.device_capable[p.tag] = (static_cast<uint8_t>(p.op) & 0x80u) != 0;
+    // bit 6: "... and over NVSwitch multicast"
+    c.device_capable[p.tag] = static_cast<uint8_t>(p.op) & 0xc0u;
     eval_collective_initiate(c.group, p.tag);
 }
 
@@ -766,14 +774,15 @@ void Master::eval_collective_initiate(uint32_t group, uint64_t tag) {
     if (voting == 0 || voting != accepted) return;
     uint64_t seq = next_seq_nr_++;
     // the device plane is used only if every single peer of the group offered it
-    bool all_device = true;
+    uint8_t common = 0xc0u;
     for (auto &[u, c] : clients_) {
         if (c.group != group || c.phase != Phase::Accepted) continue;
         const auto it = c.device_capable.find(tag);
-        all_device = all_device && it != c.device_capable.end() && it->second;
+        common &= it != c.device_capable.end() ? it->second : 0;
         c.device_capable.erase(tag);
     }
-    if (all_device) seq |= 1ull << 63;
+    if (common & 0x80u) seq |= 1ull << 63;
+    if ((common & 0xc0u) == 0xc0u) seq |= 1ull << 62;
     for (Client *c : ordered_clients()) {
         if (c->group != group || c->phase != Phase::Accepted) continue;
         c->collectives[tag] = CollectiveState::Perform;
@@ -825,6 +834,7 @@ void Master::eval_collective_complete(uint32_t group, uint64_t tag) {
     // ran, or this "not aborted" notice at the end.  Peers can therefore always consume one.
     if (!g.aborted[tag]) broadcast_abort(group, tag, false);
     g.aborted.erase(tag);
+    bool requeued = false;
     for (Client *c : ordered_clients()) {
         if (c->group != group || c->phase != Phase::Accepted) continue;
         c->collectives.erase(tag);
@@ -832,7 +842,15 @@ void Master::eval_collective_complete(uint32_t group, uint64_t tag) {
         M2CCollectiveComplete out;
         out.tag = tag;
         send(*c, out);
+        if (const auto q = c->queued_initiate.find(tag); q != c->queued_initiate.end()) {
+            c->state = State::CollectiveCommunicationsRunning;
+            c->collectives[tag] = CollectiveState::VoteInitiate;
+            c->device_capable[tag] = q->second;
+            c->queued_initiate.erase(q);
+            requeued = true;
+        }
     }
+    if (requeued) eval_collective_initiate(group, tag);
 }
 
 // ------------------------------------------------------------------------------------------

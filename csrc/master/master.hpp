@@ -69,7 +69,8 @@ struct Client {
     ccoip_socket_address_t p2p_addr{}, ss_addr{}, bm_addr{};
     bool voted_peers_pending = false;
     std::map<uint64_t, CollectiveState> collectives;
-    std::map<uint64_t, bool> device_capable; // per tag, between vote and commence
+    std::map<uint64_t, uint8_t> device_capable; // per tag, between vote and commence (capability bits)
+    std::map<uint64_t, uint8_t> queued_initiate; // next vote on a tag whose current operation is completing
 };
 
 class Master {

@@ -91,6 +91,8 @@ typedef struct pcclKernelNvlsArgs_t {
     void *mc_arena; /* multicast view */
 } pcclKernelNvlsArgs_t;
 PCCL_EXPORT int pcclKernelAllReduceNvls(const pcclKernelNvlsArgs_t *args, void *stream);
+/* 1 when multimem.ld_reduce can do (dtype, op). */
+PCCL_EXPORT int pcclKernelNvlsSupported(int dtype, int op);
 
 #ifdef __cplusplus
 }
