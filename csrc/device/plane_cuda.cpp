@@ -200,6 +200,7 @@ public:
         timeout_ms_ = env_u64("PCCL_DEVICE_TIMEOUT_MS", 30000);
         max_blocks_ = static_cast<int>(env_u64("PCCL_DEVICE_MAX_BLOCKS", 0));
         nvls_min_world_ = static_cast<uint32_t>(env_u64("PCCL_NVLS_MIN_WORLD", 4));
+        tune_ = env_flag("PCCL_DEVICE_TUNE", false);
         nvls_min_bytes_ = env_u64("PCCL_NVLS_MIN_BYTES", 1u << 20);
     }
     ~CudaPlane() override { stop(); }
@@ -407,6 +408,10 @@ public:
             k.quant_algorithm = quant;
             k.algorithm = 0;
             k.max_blocks = max_blocks_;
+            if (tune_) { // re-read the tuning knobs on every call (benchmark sweeps)
+                k.max_blocks = static_cast<int>(env_u64("PCCL_DEVICE_MAX_BLOCKS", 0));
+                k.algorithm = static_cast<int>(env_u64("PCCL_DEVICE_VARIANT", 0));
+            }
             k.src_in_arena = symmetric ? 1 : 0;
             k.abort_flag = reinterpret_cast<volatile uint32_t *>(slot.host_words);
             k.status = slot.host_words + 1;
@@ -935,6 +940,7 @@ private:
     uint64_t timeout_ms_ = 30000;
     int max_blocks_ = 0;
     uint32_t nvls_min_world_ = 4;
+    bool tune_ = false;
     uint64_t nvls_min_bytes_ = 1u << 20;
     CUdeviceptr arena_ptr_ = 0;
     CUmemGenericAllocationHandle arena_handle_ = 0;

@@ -163,7 +163,7 @@ template <int U, typename Fn> __device__ __forceinline__ void nvls_owned_packets
     }
 }
 
-template <int TYPE, int OP> __global__ void __launch_bounds__(kNvlsThreads, 1) allreduce_nvls_kernel(const NvlsArgs a) {
+template <int TYPE, int OP, int U, bool PIPELINED> __global__ void __launch_bounds__(kNvlsThreads, 1) allreduce_nvls_kernel(const NvlsArgs a) {
     constexpr int ESZ = TYPE == NV_F32 ? 4 : 2;
     constexpr int N = 16 / ESZ;
     __shared__ uint8_t *s_arena[PCCL_K_MAX_RANKS];
@@ -200,18 +200,61 @@ template <int TYPE, int OP> __global__ void __launch_bounds__(kNvlsThreads, 1) a
     {
         const uint64_t lo = min(uint64_t(a.rank) * per, n_pack), hi = min(lo + per, n_pack);
         const float inv = a.avg_divisor ? 1.0f / static_cast<float>(a.avg_divisor) : 1.0f;
-        nvls_owned_packets<4>(lo, hi, [&](const uint64_t(&v)[4], const bool(&ok)[4]) {
-            uint4 val[4];
+        if constexpr (!PIPELINED) {
+            nvls_owned_packets<U>(lo, hi, [&](const uint64_t(&v)[U], const bool(&ok)[U]) {
+                uint4 val[U];
 #pragma unroll
-            for (int u = 0; u < 4; ++u)
-                if (ok[u]) val[u] = mc_ld_reduce<TYPE, OP>(mc + v[u]);
+                for (int u = 0; u < U; ++u)
+                    if (ok[u]) val[u] = mc_ld_reduce<TYPE, OP>(mc + v[u]);
 #pragma unroll
-            for (int u = 0; u < 4; ++u) {
-                if (!ok[u]) continue;
-                if (a.avg_divisor) val[u] = scale_packet<TYPE>(val[u], inv);
-                mc_store(mc + v[u], val[u]);
+                for (int u = 0; u < U; ++u) {
+                    if (!ok[u]) continue;
+                    if (a.avg_divisor) val[u] = scale_packet<TYPE>(val[u], inv);
+                    mc_store(mc + v[u], val[u]);
+                }
+            });
+        } else {
+            // software pipeline: the loads of the next batch are in flight while the current batch
+            // is scaled and stored
+            const uint64_t first_tile = lo / kNvlsThreads;
+            uint64_t tile = first_tile + ((blockIdx.x + gridDim.x - first_tile % gridDim.x) % gridDim.x);
+            const uint64_t stride = uint64_t(gridDim.x) * U;
+            uint4 cur[U], nxt[U];
+            uint64_t cv[U];
+            bool cok[U];
+            auto issue = [&](uint64_t t, uint4(&val)[U], uint64_t(&v)[U], bool(&ok)[U]) {
+#pragma unroll
+                for (int u = 0; u < U; ++u) {
+                    v[u] = (t + uint64_t(u) * gridDim.x) * kNvlsThreads + threadIdx.x;
+                    ok[u] = v[u] >= lo && v[u] < hi;
+                    if (ok[u]) val[u] = mc_ld_reduce<TYPE, OP>(mc + v[u]);
+                }
+            };
+            if (lo < hi && tile * kNvlsThreads < hi) {
+                issue(tile, cur, cv, cok);
+                for (;;) {
+                    const uint64_t next_tile = tile + stride;
+                    const bool more = next_tile * kNvlsThreads < hi;
+                    uint64_t nv[U];
+                    bool nok[U];
+                    if (more) issue(next_tile, nxt, nv, nok);
+#pragma unroll
+                    for (int u = 0; u < U; ++u) {
+                        if (!cok[u]) continue;
+                        if (a.avg_divisor) cur[u] = scale_packet<TYPE>(cur[u], inv);
+                        mc_store(mc + cv[u], cur[u]);
+                    }
+                    if (!more) break;
+#pragma unroll
+                    for (int u = 0; u < U; ++u) {
+                        cur[u] = nxt[u];
+                        cv[u] = nv[u];
+                        cok[u] = nok[u];
+                    }
+                    tile = next_tile;
+                }
             }
-        });
+        }
     }
     if (!nvls_barrier(a, s_arena, a.flag_base + 2)) return;
 
@@ -276,16 +319,28 @@ extern "C" int pcclKernelAllReduceNvls(const pcclKernelNvlsArgs_t *args, void *s
     const int grid = static_cast<int>(std::max<uint64_t>(1, std::min<uint64_t>(max_blocks, chunk_tiles)));
     const auto stream = static_cast<cudaStream_t>(stream_v);
     const int op = p.op == pcclMax ? OP_MAX : (p.op == pcclMin ? OP_MIN : OP_SUM);
+    // p.algorithm selects a tuning variant: 0/1 = 4 packets per batch, 2 = 8 packets, 3 = 4 pipelined, 4 = 8 pipelined
+    auto launch = [&](auto type_tag, auto op_tag) {
+        constexpr int TYPE = decltype(type_tag)::value;
+        constexpr int OPV = decltype(op_tag)::value;
+        switch (p.algorithm) {
+        case 2: allreduce_nvls_kernel<TYPE, OPV, 8, false><<<grid, kNvlsThreads, 0, stream>>>(d); break;
+        case 3: allreduce_nvls_kernel<TYPE, OPV, 4, true><<<grid, kNvlsThreads, 0, stream>>>(d); break;
+        case 4: allreduce_nvls_kernel<TYPE, OPV, 8, true><<<grid, kNvlsThreads, 0, stream>>>(d); break;
+        default: allreduce_nvls_kernel<TYPE, OPV, 4, false><<<grid, kNvlsThreads, 0, stream>>>(d); break;
+        }
+    };
+    using std::integral_constant;
     if (p.dtype == pcclFloat) {
-        allreduce_nvls_kernel<NV_F32, OP_SUM><<<grid, kNvlsThreads, 0, stream>>>(d);
+        launch(integral_constant<int, NV_F32>{}, integral_constant<int, OP_SUM>{});
     } else if (p.dtype == pcclBFloat16) {
-        if (op == OP_SUM) allreduce_nvls_kernel<NV_BF16, OP_SUM><<<grid, kNvlsThreads, 0, stream>>>(d);
-        else if (op == OP_MAX) allreduce_nvls_kernel<NV_BF16, OP_MAX><<<grid, kNvlsThreads, 0, stream>>>(d);
-        else allreduce_nvls_kernel<NV_BF16, OP_MIN><<<grid, kNvlsThreads, 0, stream>>>(d);
+        if (op == OP_SUM) launch(integral_constant<int, NV_BF16>{}, integral_constant<int, OP_SUM>{});
+        else if (op == OP_MAX) launch(integral_constant<int, NV_BF16>{}, integral_constant<int, OP_MAX>{});
+        else launch(integral_constant<int, NV_BF16>{}, integral_constant<int, OP_MIN>{});
     } else {
-        if (op == OP_SUM) allreduce_nvls_kernel<NV_F16, OP_SUM><<<grid, kNvlsThreads, 0, stream>>>(d);
-        else if (op == OP_MAX) allreduce_nvls_kernel<NV_F16, OP_MAX><<<grid, kNvlsThreads, 0, stream>>>(d);
-        else allreduce_nvls_kernel<NV_F16, OP_MIN><<<grid, kNvlsThreads, 0, stream>>>(d);
+        if (op == OP_SUM) launch(integral_constant<int, NV_F16>{}, integral_constant<int, OP_SUM>{});
+        else if (op == OP_MAX) launch(integral_constant<int, NV_F16>{}, integral_constant<int, OP_MAX>{});
+        else launch(integral_constant<int, NV_F16>{}, integral_constant<int, OP_MIN>{});
     }
     return cudaGetLastError();
 }

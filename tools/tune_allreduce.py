@@ -1,0 +1,59 @@
+#!/usr/bin/env python3
+"""Sweeps kernel tuning knobs of the device all-reduce under torchrun (one communicator, many configs).
+Prints one JSON line per config from rank 0."""
+import json
+import os
+import sys
+from pathlib import Path
+
+import torch
+import torch.distributed as dist
+
+sys.path.insert(0, str(Path(__file__).resolve().parent.parent))
+os.environ["PCCL_DEVICE_TUNE"] = "1"
+import pccl_b200 as pccl  # noqa: E402
+
+rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
+torch.cuda.set_device(local)
+dev = torch.device("cuda", local)
+dist.init_process_group("nccl", device_id=dev)
+box = [0]
+master = None
+if rank == 0:
+    master = pccl.MasterNode("127.0.0.1:0")
+    master.run()
+    box[0] = master.port
+dist.broadcast_object_list(box, src=0)
+comm = pccl.Communicator(f"127.0.0.1:{box[0]}")
+comm.connect(n_attempts=15)
+while comm.get_attribute(pccl.Attribute.GLOBAL_WORLD_SIZE) < world:
+    comm.update_topology()
+n = int(sys.argv[1]) if len(sys.argv) > 1 else 150_000_000
+sym = comm.ext_symmetric_empty(n, torch.float32)
+sym.normal_()
+reg = torch.randn(n, device=dev)
+out = torch.empty_like(reg)
+configs = [(v, b) for v in (1, 2, 3, 4) for b in (96, 144, 216)]
+for buffers in ("symmetric", "regular"):
+    for variant, blocks in configs:
+        os.environ["PCCL_DEVICE_VARIANT"] = str(variant)
+        os.environ["PCCL_DEVICE_MAX_BLOCKS"] = str(blocks)
+        ms = []
+        for it in range(8):
+            if buffers == "symmetric":
+                comm.all_reduce(sym, sym, op=pccl.ReduceOp.AVG, tag=0)
+            else:
+                comm.all_reduce(reg, out, op=pccl.ReduceOp.AVG, tag=0)
+            st = comm.ext_last_reduce_stats(0)
+            if it >= 3:
+                ms.append(st["device_ms"])
+        t = torch.tensor([sum(ms) / len(ms)], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        if rank == 0:
+            print(json.dumps({"buffers": buffers, "variant": variant, "blocks": blocks, "plane": st["plane"], "kernel_ms": round(float(t.item()), 4),
+                              "bus_GBps": round(n * 4 * 2 * (world - 1) / world / float(t.item()) / 1e6, 1)}), flush=True)
+    if buffers == "symmetric" and world < 4:
+        pass
+comm.destroy()
+dist.barrier()
+dist.destroy_process_group()
