@@ -294,7 +294,7 @@ def run_reference(args) -> dict:
     ref_dir = REPO / "baseline" / "_ref"
     marker = ref_dir / "pccl"
     if not marker.exists():
-        return {"impl": "reference", "unavailable": "reference is not installed in baseline/_ref (see DESIGN.md: build needs the missing piquant submodule)"}
+        return {"impl": "reference", "unavailable": "reference is not installed in baseline/_ref (see baseline/README.md for the install recipe)"}
     from baseline.reference_arm import run as run_ref  # noqa: WPS433
     return run_ref(args)
 
