@@ -335,3 +335,83 @@ extern "C" int pcclKernelHashSync(const void *data, size_t n_bytes, int hash_typ
     *out_host = host;
     return 0;
 }
+
+// ---------------------------------------------------------------------------------------------
+// pcclKernelSimpleHashNoAlloc -- the same hash for callers that must not allocate.
+//
+// Who that is: code that runs while a CUDA stream capture is open on the thread, code that runs
+// when the framework's caching allocator already owns all device memory (a fresh cudaMalloc would
+// fail or force the allocator to release and synchronise), and latency-sensitive paths where the
+// device-wide synchronisation inside cudaMalloc/cudaFree would stall every other stream.  The
+// regular entry points above either take a caller-provided scratch buffer or create one lazily
+// with cudaMalloc; this one owns its scratch as a static device array instead, so every GPU that
+// loads libpccl.so gives up kNoAllocScratchBytes until the process exits.
+//
+// The scratch holds one 32-bit partial per thread block (at most 960) and the ticket counter the
+// last block uses to detect that it is last.  The hash is defined for inputs of up to 2^32 - 1
+// sixteen-byte packets (the kernel, like the reference, counts packets in 32 bits), so that is the
+// size limit; anything larger is refused.
+//
+// Rules for callers:
+//   * the first call on each device looks up the device address of the scratch array
+//     (cudaGetSymbolAddress).  Make that first call before any stream capture begins.
+//   * all calls on one device share the one scratch array.  The ticket counter is cleared on the
+//     stream before every launch (a failed earlier launch could have left it dirty), the partials
+//     need no clearing because every block overwrites its own before the fold.  Two calls whose
+//     kernels overlap on the GPU (different streams, no ordering) race on the array and return
+//     garbage: order them.
+//   * no cudaMalloc, cudaFree or other allocating call is made, on any path.
+// ---------------------------------------------------------------------------------------------
+namespace pccl::cuda {
+
+constexpr size_t kNoAllocScratchBytes = 4096; // 960 partials + ticket, rounded up
+constexpr uint64_t kNoAllocMaxBytes = (uint64_t(1) << 32) * 16 - 16;
+static_assert((kHashMaxBlocks + 1) * sizeof(uint32_t) <= kNoAllocScratchBytes, "static scratch too small");
+
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocScratchBytes];
+
+// In host code the array's name is only a handle for the runtime, not a device address; the real
+// address is fetched once per device with that device current.
+static int noalloc_scratch_address(uint32_t **out) {
+    static std::mutex mu;
+    static uint32_t *address[64] = {nullptr};
+    int dev = 0;
+    cudaError_t rc = cudaGetDevice(&dev);
+    if (rc != cudaSuccess) return rc;
+    if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
+    std::lock_guard<std::mutex> lock(mu);
+    if (!address[dev]) {
+        void *p = nullptr;
+        rc = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+        if (rc != cudaSuccess) return rc;
+        address[dev] = static_cast<uint32_t *>(p);
+    }
+    *out = address[dev];
+    return 0;
+}
+
+} // namespace pccl::cuda
+
+extern "C" PCCL_EXPORT size_t pcclKernelSimpleHashNoAllocMaxBytes(void) { return static_cast<size_t>(kNoAllocMaxBytes); }
+
+extern "C" PCCL_EXPORT int pcclKernelSimpleHashNoAlloc(const void *data, size_t n_bytes, uint64_t *out_device, void *stream_v) {
+    if (!out_device || (!data && n_bytes > 0)) return cudaErrorInvalidValue;
+    if (static_cast<uint64_t>(n_bytes) > kNoAllocMaxBytes) {
+        fprintf(stderr, "pcclKernelSimpleHashNoAlloc: %zu bytes exceed the supported maximum of %llu bytes\n", n_bytes,
+                static_cast<unsigned long long>(kNoAllocMaxBytes));
+        return cudaErrorInvalidValue;
+    }
+    const auto stream = static_cast<cudaStream_t>(stream_v);
+    if (n_bytes == 0) return cudaMemsetAsync(out_device, 0, sizeof(uint64_t), stream);
+    if (reinterpret_cast<uintptr_t>(data) % 16 != 0) return cudaErrorMisalignedAddress;
+    uint32_t *scratch = nullptr;
+    if (const int rc = noalloc_scratch_address(&scratch)) return rc;
+    // the ticket must be zero when the kernel starts
+    cudaError_t rc = cudaMemsetAsync(scratch + kHashMaxBlocks, 0, sizeof(uint32_t), stream);
+    if (rc != cudaSuccess) return rc;
+    const size_t n_vec = n_bytes / 16;
+    uint32_t grid = static_cast<uint32_t>(std::min<size_t>((n_vec + kHashThreads - 1) / kHashThreads, kHashMaxBlocks));
+    if (grid == 0) grid = 1;
+    simplehash_kernel<<<grid, kHashThreads, 0, stream>>>(static_cast<const uint8_t *>(data), n_bytes, scratch, out_device);
+    return cudaGetLastError();
+}

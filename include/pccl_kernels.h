@@ -35,6 +35,17 @@ PCCL_EXPORT int pcclKernelCrc32c(const void *data, size_t n_bytes, void *scratch
  * hash on an internal stream and returns the value on the host (synchronous). */
 PCCL_EXPORT int pcclKernelHashSync(const void *data, size_t n_bytes, int hash_type, uint64_t *out_host);
 
+/* Same hash, for callers that may not allocate device memory (open stream capture, allocator that already
+ * owns the whole GPU, paths that cannot afford cudaMalloc's device-wide synchronisation).  Has no
+ * counterpart in the reference.  The scratch is a 4 KiB static device array inside the library, shared
+ * by all calls on a device: calls whose kernels overlap on the GPU race, so order them.  The first
+ * call on each device resolves the array's address and should happen before any stream capture.
+ * Inputs larger than pcclKernelSimpleHashNoAllocMaxBytes() (2^32 - 1 sixteen-byte packets) are refused
+ * with cudaErrorInvalidValue and a message on stderr.  Asynchronous on `stream`; the 8-byte result
+ * lands in *out_device (device memory supplied by the caller). */
+PCCL_EXPORT int pcclKernelSimpleHashNoAlloc(const void *data, size_t n_bytes, uint64_t *out_device, void *stream);
+PCCL_EXPORT size_t pcclKernelSimpleHashNoAllocMaxBytes(void);
+
 /* ---------------------------------------------------------------------------------------------
  * Element-wise kernels of the TCP data plane on device buffers (reference CPU versions:
  * ccoip/src/cpp/reduce_kernels.cpp:56-215,437-510; quantize_kernels.cpp:24-217).
