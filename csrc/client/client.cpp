@@ -146,6 +146,11 @@ bool Client::join() {
         std::lock_guard<std::mutex> lock(rx_mu_);
         rx_pools_.clear();
     }
+    {
+        std::lock_guard<std::mutex> lock(stage_mu_);
+        for (auto &[tag, b] : stage_cache_) plane_->host_free(b.ptr);
+        stage_cache_.clear();
+    }
     plane_->stop();
     return true;
 }
@@ -680,17 +685,29 @@ bool Client::drain_deferred() {
     return ok;
 }
 
-std::shared_ptr<net::MuxSocket> Client::pick_rx(const Uuid &peer, uint64_t seq, int timeout_ms) {
+Client::Pool Client::pick_rx_pool(const Uuid &peer, int timeout_ms) {
     std::unique_lock<std::mutex> lock(rx_mu_);
     const auto deadline = clock_type::now() + std::chrono::milliseconds(timeout_ms);
     for (;;) {
         const auto it = rx_pools_.find(peer);
         if (it != rx_pools_.end() && it->second.size() >= cfg_.pool_size) {
-            auto &s = it->second[seq % cfg_.pool_size];
-            if (s && s->is_open()) return s;
+            bool all = true;
+            for (uint32_t i = 0; i < cfg_.pool_size; ++i) all = all && it->second[i] && it->second[i]->is_open();
+            if (all) return Pool(it->second.begin(), it->second.begin() + cfg_.pool_size);
         }
-        if (interrupted_ || rx_cv_.wait_until(lock, deadline) == std::cv_status::timeout) return nullptr;
+        if (interrupted_ || rx_cv_.wait_until(lock, deadline) == std::cv_status::timeout) return {};
     }
+}
+
+uint8_t *Client::staging_for(uint64_t tag, size_t bytes) {
+    std::lock_guard<std::mutex> lock(stage_mu_);
+    StageBuf &b = stage_cache_[tag];
+    if (b.bytes < bytes) {
+        if (b.ptr) plane_->host_free(b.ptr);
+        b.ptr = static_cast<uint8_t *>(plane_->host_alloc(bytes));
+        b.bytes = b.ptr ? bytes : 0;
+    }
+    return b.ptr;
 }
 
 ReduceOutcome Client::run_reduce(const ReduceRequest &req, uint64_t) {
@@ -774,8 +791,8 @@ ReduceOutcome Client::run_reduce(const ReduceRequest &req, uint64_t) {
     };
 
     bool local_ok = false;
-    std::vector<uint8_t> host_backup;            // in-place rollback for host buffers
-    std::vector<uint8_t> stage_send, stage_recv; // host staging for device buffers on the TCP plane
+    std::vector<uint8_t> host_backup; // in-place rollback for host buffers
+    uint8_t *stage = nullptr;         // host staging for device buffers on the TCP plane
     const bool in_place = req.send == req.recv;
 
     if (poisoned) {
@@ -808,10 +825,10 @@ ReduceOutcome Client::run_reduce(const ReduceRequest &req, uint64_t) {
             {
                 std::lock_guard<std::mutex> lock(tx_mu_);
                 const auto it = tx_pools_.find(next);
-                if (it != tx_pools_.end() && !it->second.empty()) ctx.tx = it->second[seq % it->second.size()];
+                if (it != tx_pools_.end()) ctx.tx = it->second;
             }
-            ctx.rx = pick_rx(prev, seq, 10000);
-            wired = ctx.tx && ctx.rx;
+            ctx.rx = pick_rx_pool(prev, 10000);
+            wired = !ctx.tx.empty() && ctx.tx.size() == ctx.rx.size();
             if (!wired) PLOG(WARN) << "no usable p2p link for tag " << req.tag;
         }
         if (wired) {
@@ -823,21 +840,23 @@ ReduceOutcome Client::run_reduce(const ReduceRequest &req, uint64_t) {
             a.quant_dtype = req.quant_dtype;
             bool staged_ok = true;
             if (send_info.is_device || recv_info.is_device) {
-                // Device buffers on the TCP plane are staged through host memory, as users of the
-                // reference do by hand (python/examples/nanogpt_diloco/sync_diloco.py:494).
-                stage_recv.resize(req.count * esz);
-                if (send_info.is_device) {
-                    staged_ok = plane_->copy_to_host(stage_recv.data(), req.send, req.count * esz);
-                } else {
-                    std::memcpy(stage_recv.data(), req.send, req.count * esz);
+                // Device buffers on the TCP plane are staged through page-locked host memory, as
+                // users of the reference do by hand (python/examples/nanogpt_diloco/sync_diloco.py:494).
+                // The user's buffers stay untouched until the verdict is known, so no backup copy.
+                stage = staging_for(req.tag, req.count * esz);
+                staged_ok = stage != nullptr;
+                if (staged_ok && send_info.is_device) {
+                    staged_ok = plane_->copy_to_host(stage, req.send, req.count * esz);
+                } else if (staged_ok) {
+                    std::memcpy(stage, req.send, req.count * esz);
                 }
-                a.src = a.dst = stage_recv.data();
+                a.src = a.dst = stage;
             } else {
                 a.src = req.send;
                 a.dst = req.recv;
             }
             if (staged_ok) {
-                const RingResult r = ring_allreduce(ctx, a, host_backup);
+                const RingResult r = ring_allreduce(ctx, a, stage ? nullptr : &host_backup);
                 local_ok = r.ok;
                 out.tx_bytes = r.tx_bytes;
                 out.rx_bytes = r.rx_bytes;
@@ -870,13 +889,13 @@ ReduceOutcome Client::run_reduce(const ReduceRequest &req, uint64_t) {
     const bool success = local_ok && !aborted;
     if (use_device && device_capable && !success && in_place) plane_->restore_input(dargs);
     if (out.stats.plane == pcclExtPlaneTcpRing) {
-        if (success && !stage_recv.empty()) {
+        if (success && stage) {
             if (recv_info.is_device) {
-                if (!plane_->copy_to_device(req.recv, stage_recv.data(), req.count * esz)) return out;
+                if (!plane_->copy_to_device(req.recv, stage, req.count * esz)) return out;
             } else {
-                std::memcpy(req.recv, stage_recv.data(), req.count * esz);
+                std::memcpy(req.recv, stage, req.count * esz);
             }
-        } else if (!success && stage_recv.empty() && in_place && local_ok && !host_backup.empty()) {
+        } else if (!success && !stage && in_place && local_ok && !host_backup.empty()) {
             // finished locally but another peer aborted: the caller will retry with this
             // buffer as input, so it must hold the original values again
             std::memcpy(req.recv, host_backup.data(), host_backup.size());

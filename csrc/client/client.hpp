@@ -122,7 +122,8 @@ private:
     };
     bool finish_deferred(uint64_t tag, Deferred &d);
     bool drain_deferred();
-    std::shared_ptr<net::MuxSocket> pick_rx(const Uuid &peer, uint64_t seq, int timeout_ms);
+    Pool pick_rx_pool(const Uuid &peer, int timeout_ms);
+    uint8_t *staging_for(uint64_t tag, size_t bytes);
     bool run_benchmark(const wire::BenchmarkRequest &req, double &mbits, bool &busy);
 
     ClientConfig cfg_;
@@ -150,6 +151,13 @@ private:
         std::future<ReduceOutcome> future;
         uint64_t revision_at_launch = 0;
     };
+    // page-locked host buffers for device tensors that travel over the TCP plane, one per tag
+    struct StageBuf {
+        uint8_t *ptr = nullptr;
+        size_t bytes = 0;
+    };
+    std::mutex stage_mu_;
+    std::map<uint64_t, StageBuf> stage_cache_;
     std::mutex deferred_mu_;
     std::map<uint64_t, Deferred> deferred_;
     std::atomic<bool> master_pipelines_{false}; // the master queues an Initiate behind a pending Complete

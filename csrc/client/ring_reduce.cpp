@@ -19,81 +19,119 @@ struct Stage {
     const RingContext &ctx;
     RingResult &res;
     bool failed = false;
+    size_t lane; // connection used for metadata and small transfers
+
+    Stage(const RingContext &c, RingResult &r) : ctx(c), res(r), lane(c.tx.empty() ? 0 : c.seq % c.tx.size()) {}
+
+    bool links_open() const {
+        for (const auto &s : ctx.tx)
+            if (!s->is_open()) return false;
+        for (const auto &s : ctx.rx)
+            if (!s->is_open()) return false;
+        return true;
+    }
 
     bool check_abort() {
         if (ctx.abort_requested && ctx.abort_requested()) {
             res.aborted_by_master = true;
             failed = true;
         }
-        if (!ctx.tx->is_open() || !ctx.rx->is_open()) failed = true;
+        if (!links_open()) failed = true;
         return failed;
     }
 
-    // Blocks until the ticket is done, polling for aborts.  After an abort the ticket is still
-    // awaited (the successor's RX thread keeps draining, or the socket dies) because the TX
-    // thread reads from caller memory.
-    bool finish_send(const std::shared_ptr<net::SendTicket> &ticket) {
-        for (;;) {
-            const int st = ticket->wait_for(kPollMs);
-            if (st == 1) return true;
-            if (st == -1) {
-                failed = true;
-                return false;
-            }
-            if (check_abort() && res.aborted_by_master) {
-                // keep waiting for the ticket, but bounded: a wedged link is cut
-                for (int i = 0; i < 5000; ++i) {
-                    const int s2 = ticket->wait_for(kPollMs);
-                    if (s2 != 0) return false;
+    // How a transfer of `bytes` is spread over the pool: part i covers [begin_i, end_i).
+    size_t parts(size_t bytes) const { return bytes >= ctx.stripe_threshold && ctx.tx.size() > 1 ? ctx.tx.size() : 1; }
+    static void part_bounds(size_t bytes, size_t n_parts, size_t i, size_t &begin, size_t &end) {
+        // 64-byte aligned cuts keep whole elements of every type together
+        const size_t per = ((bytes + n_parts - 1) / n_parts + 63) / 64 * 64;
+        begin = std::min(bytes, i * per);
+        end = std::min(bytes, begin + per);
+    }
+
+    using Tickets = std::vector<std::shared_ptr<net::SendTicket>>;
+
+    Tickets send(const uint8_t *data, size_t bytes) {
+        Tickets tickets;
+        const size_t n = parts(bytes);
+        for (size_t i = 0; i < n; ++i) {
+            size_t b, e;
+            part_bounds(bytes, n, i, b, e);
+            const size_t sock = n == 1 ? lane : i;
+            tickets.push_back(ctx.tx[sock]->send_bytes(ctx.tag, ctx.seq, data + b, e - b, ctx.frame_bytes));
+        }
+        res.tx_bytes += bytes;
+        return tickets;
+    }
+
+    // Blocks until every ticket is done, polling for aborts.  After an abort the tickets are still
+    // awaited (the successor's RX threads keep draining, or the socket dies) because the TX
+    // threads read from caller memory.
+    bool finish_send(const Tickets &tickets) {
+        bool ok = true;
+        for (const auto &ticket : tickets) {
+            for (;;) {
+                const int st = ticket->wait_for(kPollMs);
+                if (st == 1) break;
+                if (st == -1) {
+                    failed = true;
+                    ok = false;
+                    break;
                 }
-                ctx.tx->interrupt();
-                ticket->wait_for(1000);
-                return false;
+                if (check_abort() && res.aborted_by_master) {
+                    bool done = false;
+                    for (int i = 0; i < 5000 && !done; ++i) done = ticket->wait_for(kPollMs) != 0;
+                    if (!done) { // a wedged link is cut so the TX thread lets go of the buffer
+                        for (const auto &s : ctx.tx) s->interrupt();
+                        ticket->wait_for(1000);
+                    }
+                    ok = false;
+                    break;
+                }
             }
         }
+        return ok;
     }
 
     // Receives exactly `bytes` payload bytes, handing every frame to `sink(offset, data, n)`.
     template <typename Sink> bool receive(size_t bytes, Sink sink) {
-        size_t got = 0;
-        bool first = true;
-        while (got < bytes || (first && bytes == 0)) {
-            auto frame = ctx.rx->recv_frame(ctx.tag, ctx.seq, kPollMs);
-            if (!frame) {
-                if (check_abort()) return false;
-                // a frame may have arrived between the timeout and the liveness check
-                if (!ctx.rx->is_open()) {
-                    frame = ctx.rx->recv_frame(ctx.tag, ctx.seq, 0);
-                    if (!frame) {
-                        failed = true;
-                        return false;
-                    }
-                } else {
+        const size_t n = parts(bytes);
+        for (size_t i = 0; i < n; ++i) {
+            size_t b, e;
+            part_bounds(bytes, n, i, b, e);
+            net::MuxSocket &sock = *ctx.rx[n == 1 ? lane : i];
+            size_t got = 0;
+            const size_t want = e - b;
+            bool first = true;
+            while (got < want || (first && want == 0)) {
+                auto frame = sock.recv_frame(ctx.tag, ctx.seq, kPollMs);
+                if (!frame) {
+                    if (check_abort()) return false;
                     continue;
                 }
+                first = false;
+                if (frame->size() > want - got) {
+                    PLOG(ERR) << "peer sent more bytes than the chunk holds";
+                    failed = true;
+                    return false;
+                }
+                sink(b + got, frame->data(), frame->size());
+                got += frame->size();
+                res.rx_bytes += frame->size();
             }
-            first = false;
-            if (frame->size() > bytes - got) {
-                PLOG(ERR) << "peer sent more bytes than the chunk holds";
-                failed = true;
-                return false;
-            }
-            sink(got, frame->data(), frame->size());
-            got += frame->size();
-            res.rx_bytes += frame->size();
         }
         return true;
     }
 
     bool exchange_meta(const cpu::QuantParams &mine, cpu::QuantParams &theirs) {
         const auto pkt = cpu::to_wire(mine, ctx.tag);
-        if (!ctx.tx->send_packet(ctx.tag, ctx.seq, pkt)) {
+        if (!ctx.tx[lane]->send_packet(ctx.tag, ctx.seq, pkt)) {
             failed = true;
             return false;
         }
         res.tx_bytes += 8 + 2 + pkt.wire_size();
         for (;;) {
-            auto got = ctx.rx->recv_packet<wire::P2PDequantMeta>(ctx.tag, ctx.seq, kPollMs);
+            auto got = ctx.rx[lane]->recv_packet<wire::P2PDequantMeta>(ctx.tag, ctx.seq, kPollMs);
             if (got) {
                 res.rx_bytes += 8 + 2 + got->wire_size();
                 if (!cpu::from_wire(*got, theirs)) {
@@ -109,26 +147,28 @@ struct Stage {
 
 } // namespace
 
-RingResult ring_allreduce(const RingContext &ctx, const ReduceArgs &a, std::vector<uint8_t> &backup) {
+RingResult ring_allreduce(const RingContext &ctx, const ReduceArgs &a, std::vector<uint8_t> *backup) {
     RingResult res;
     const size_t esz = wire::dtype_size(a.dtype);
     auto *dst = static_cast<uint8_t *>(a.dst);
     const bool in_place = a.src == a.dst;
+    if (backup) backup->clear();
 
     if (ctx.world < 2) {
         if (!in_place) std::memcpy(dst, a.src, a.count * esz);
         res.ok = true;
         return res;
     }
+    if (ctx.tx.empty() || ctx.rx.empty() || ctx.tx.size() != ctx.rx.size()) return res;
 
     // In-place operation destroys the input while it runs; keep a copy to roll back to.
-    backup.clear();
-    if (in_place)
-        backup.assign(dst, dst + a.count * esz);
-    else
+    if (in_place) {
+        if (backup) backup->assign(dst, dst + a.count * esz);
+    } else {
         std::memcpy(dst, a.src, a.count * esz);
+    }
     auto fail = [&]() {
-        if (in_place) std::memcpy(dst, backup.data(), backup.size());
+        if (in_place && backup && !backup->empty()) std::memcpy(dst, backup->data(), backup->size());
         res.ok = false;
         return res;
     };
@@ -140,12 +180,8 @@ RingResult ring_allreduce(const RingContext &ctx, const ReduceArgs &a, std::vect
     qp.value_dtype = a.dtype;
     qp.code_dtype = a.quant_dtype;
     const size_t qsz = quantised && !block_format ? wire::dtype_size(a.quant_dtype) : 1;
-    // frames must carry whole elements so they can be consumed as they arrive
-    size_t frame_bytes = ctx.frame_bytes;
-    frame_bytes -= frame_bytes % 64;
-    if (frame_bytes == 0) frame_bytes = 64;
 
-    Stage st{ctx, res};
+    Stage st(ctx, res);
     const uint32_t W = ctx.world, r = ctx.rank;
     std::vector<uint8_t> tx_codes, rx_codes;
 
@@ -158,12 +194,11 @@ RingResult ring_allreduce(const RingContext &ctx, const ReduceArgs &a, std::vect
         const uint64_t tx_n = te - tb, rx_n = re - rb;
 
         if (!quantised) {
-            auto ticket = ctx.tx->send_bytes(ctx.tag, ctx.seq, dst + tb * esz, tx_n * esz, frame_bytes);
-            res.tx_bytes += tx_n * esz;
+            const auto tickets = st.send(dst + tb * esz, tx_n * esz);
             const bool rx_ok = st.receive(rx_n * esz, [&](size_t off, const uint8_t *data, size_t n) {
                 cpu::reduce_inplace(dst + rb * esz + off, data, n / esz, a.dtype, a.op);
             });
-            const bool tx_ok = st.finish_send(ticket);
+            const bool tx_ok = st.finish_send(tickets);
             if (!rx_ok || !tx_ok) return fail();
             continue;
         }
@@ -173,8 +208,7 @@ RingResult ring_allreduce(const RingContext &ctx, const ReduceArgs &a, std::vect
         tx_codes.resize(cpu::quantized_size(mine, tx_n));
         cpu::quantize(dst + tb * esz, tx_codes.data(), tx_n, mine);
         if (!st.exchange_meta(mine, theirs)) return fail();
-        auto ticket = ctx.tx->send_bytes(ctx.tag, ctx.seq, tx_codes.data(), tx_codes.size(), frame_bytes);
-        res.tx_bytes += tx_codes.size();
+        const auto tickets = st.send(tx_codes.data(), tx_codes.size());
         const size_t rx_bytes = cpu::quantized_size(theirs, rx_n);
         bool rx_ok;
         if (block_format) {
@@ -186,7 +220,7 @@ RingResult ring_allreduce(const RingContext &ctx, const ReduceArgs &a, std::vect
                 cpu::dequantize_reduce(dst + (rb + off / qsz) * esz, data, n / qsz, theirs, a.op);
             });
         }
-        const bool tx_ok = st.finish_send(ticket);
+        const bool tx_ok = st.finish_send(tickets);
         if (!rx_ok || !tx_ok) return fail();
     }
 
@@ -200,12 +234,11 @@ RingResult ring_allreduce(const RingContext &ctx, const ReduceArgs &a, std::vect
         const uint64_t tx_n = te - tb, rx_n = re - rb;
 
         if (!quantised) {
-            auto ticket = ctx.tx->send_bytes(ctx.tag, ctx.seq, dst + tb * esz, tx_n * esz, frame_bytes);
-            res.tx_bytes += tx_n * esz;
+            const auto tickets = st.send(dst + tb * esz, tx_n * esz);
             const bool rx_ok = st.receive(rx_n * esz, [&](size_t off, const uint8_t *data, size_t n) {
                 std::memcpy(dst + rb * esz + off, data, n);
             });
-            const bool tx_ok = st.finish_send(ticket);
+            const bool tx_ok = st.finish_send(tickets);
             if (!rx_ok || !tx_ok) return fail();
             continue;
         }
@@ -221,13 +254,12 @@ RingResult ring_allreduce(const RingContext &ctx, const ReduceArgs &a, std::vect
         }
         cpu::QuantParams theirs = qp;
         if (!st.exchange_meta(forwarded, theirs)) return fail();
-        auto ticket = ctx.tx->send_bytes(ctx.tag, ctx.seq, tx_codes.data(), tx_codes.size(), frame_bytes);
-        res.tx_bytes += tx_codes.size();
+        const auto tickets = st.send(tx_codes.data(), tx_codes.size());
         const size_t rx_bytes = cpu::quantized_size(theirs, rx_n);
         rx_codes.resize(rx_bytes);
         const bool rx_ok =
             st.receive(rx_bytes, [&](size_t off, const uint8_t *data, size_t n) { std::memcpy(rx_codes.data() + off, data, n); });
-        const bool tx_ok = st.finish_send(ticket);
+        const bool tx_ok = st.finish_send(tickets);
         if (!rx_ok || !tx_ok) return fail();
         cpu::dequantize_reduce(dst + rb * esz, rx_codes.data(), rx_n, theirs, RedOp::Set);
         // next step forwards the received codes and metadata unchanged (no second quantisation)

@@ -19,9 +19,12 @@ namespace pccl::client {
 struct RingContext {
     uint64_t tag = 0, seq = 0;
     uint32_t rank = 0, world = 1;
-    std::shared_ptr<net::MuxSocket> tx; // to ring successor
-    std::shared_ptr<net::MuxSocket> rx; // from ring predecessor
+    // Connection pools to the ring successor / from the predecessor (same size on both ends).
+    // Small transfers use connection seq % pool; large ones are striped over all of them so that
+    // several kernel socket queues (and RX/TX threads) work on one operation.
+    std::vector<std::shared_ptr<net::MuxSocket>> tx, rx;
     size_t frame_bytes = 2u << 20;
+    size_t stripe_threshold = 512u << 10;
     // returns true when the master told us to abort this operation
     std::function<bool()> abort_requested;
 };
@@ -42,10 +45,11 @@ struct ReduceArgs {
     wire::DType quant_dtype = wire::DType::U8;
 };
 
-// `backup` receives a copy of the input when the operation is in place (src == dst).  On a local
-// failure the input is restored from it before returning; on local success it is left filled so
-// the caller can still roll back if the master later reports that another peer aborted.
-RingResult ring_allreduce(const RingContext &ctx, const ReduceArgs &args, std::vector<uint8_t> &backup);
+// `backup`, when given, receives a copy of the input if the operation is in place (src == dst).
+// On a local failure the input is restored from it before returning; on local success it is left
+// filled so the caller can still roll back if the master later reports that another peer
+// aborted.  Callers that reduce a private staging copy pass nullptr and skip that pass over memory.
+RingResult ring_allreduce(const RingContext &ctx, const ReduceArgs &args, std::vector<uint8_t> *backup);
 
 // chunk i of `count` elements split over `world` owners: [begin, end)
 inline void chunk_bounds(uint64_t count, uint32_t world, uint32_t i, uint64_t &begin, uint64_t &end) {

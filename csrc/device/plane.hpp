@@ -89,6 +89,10 @@ public:
     // Content hash of a device buffer; hash_type as on the wire.
     virtual bool hash_device(const void *dev_ptr, size_t bytes, wire::HashType type, uint64_t &out) = 0;
 
+    // Page-locked host memory for staging (plain malloc when there is no GPU).
+    virtual void *host_alloc(size_t bytes) = 0;
+    virtual void host_free(void *ptr) = 0;
+
     virtual void *symmetric_alloc(size_t bytes) = 0;
     virtual bool symmetric_free(void *ptr) = 0;
 };

@@ -489,6 +489,23 @@ public:
         return rc == 0;
     }
 
+    void *host_alloc(size_t bytes) override {
+        if (cuda_runtime_usable()) {
+            void *p = nullptr;
+            if (cudaHostAlloc(&p, bytes, cudaHostAllocPortable) == cudaSuccess) return p;
+            (void) cudaGetLastError();
+            return nullptr;
+        }
+        return std::malloc(bytes);
+    }
+    void host_free(void *ptr) override {
+        if (!ptr) return;
+        if (cuda_runtime_usable())
+            cudaFreeHost(ptr);
+        else
+            std::free(ptr);
+    }
+
     void *symmetric_alloc(size_t bytes) override {
         std::lock_guard<std::mutex> lock(mu_);
         if (!usable_ || sym_bytes_ == 0) return nullptr;

@@ -1,4 +1,6 @@
 // Inert device plane used when the library is built without CUDA (PCCL_NO_CUDA).
+#include <cstdlib>
+
 #include "plane.hpp"
 
 namespace pccl::device {
@@ -16,6 +18,8 @@ public:
     bool copy_to_host(void *, const void *, size_t) override { return false; }
     bool copy_to_device(void *, const void *, size_t) override { return false; }
     bool hash_device(const void *, size_t, wire::HashType, uint64_t &) override { return false; }
+    void *host_alloc(size_t bytes) override { return std::malloc(bytes); }
+    void host_free(void *ptr) override { std::free(ptr); }
     void *symmetric_alloc(size_t) override { return nullptr; }
     bool symmetric_free(void *) override { return false; }
 };

@@ -158,8 +158,9 @@ void MuxSocket::rx_loop() {
         RxFrame frame;
         const uint64_t tag = get_be64(head + 8);
         frame.seq = get_be64(head + 16);
-        frame.data.resize(len - 16);
-        if (!frame.data.empty() && !recv_all(fd_, frame.data.data(), frame.data.size())) break;
+        frame.data.n = len - 16;
+        frame.data.bytes.reset(new uint8_t[frame.data.n ? frame.data.n : 1]);
+        if (frame.data.n && !recv_all(fd_, frame.data.bytes.get(), frame.data.n)) break;
         {
             std::lock_guard<std::mutex> lock(rx_mu_);
             rx_streams_[tag].push_back(std::move(frame));
@@ -170,7 +171,7 @@ void MuxSocket::rx_loop() {
     rx_cv_.notify_all();
 }
 
-std::optional<std::vector<uint8_t>> MuxSocket::recv_frame(uint64_t tag, uint64_t seq, int timeout_ms) {
+std::optional<MuxSocket::Frame> MuxSocket::recv_frame(uint64_t tag, uint64_t seq, int timeout_ms) {
     std::unique_lock<std::mutex> lock(rx_mu_);
     const auto deadline = std::chrono::steady_clock::now() + std::chrono::milliseconds(timeout_ms);
     for (;;) {

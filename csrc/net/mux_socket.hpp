@@ -69,9 +69,17 @@ public:
     }
     bool send_owned(uint64_t tag, uint64_t seq, std::vector<uint8_t> bytes);
 
+    // A received frame.  The buffer is deliberately NOT value-initialised (a std::vector would
+    // zero every byte before the socket overwrites it).
+    struct Frame {
+        std::unique_ptr<uint8_t[]> bytes;
+        size_t n = 0;
+        const uint8_t *data() const { return bytes.get(); }
+        size_t size() const { return n; }
+    };
     // ---- RX side.  Pops the oldest frame of `tag` whose sequence number equals `seq`; frames
     // with another sequence number are dropped on the way.  timeout_ms == 0 polls.
-    std::optional<std::vector<uint8_t>> recv_frame(uint64_t tag, uint64_t seq, int timeout_ms);
+    std::optional<Frame> recv_frame(uint64_t tag, uint64_t seq, int timeout_ms);
     template <typename P> std::optional<P> recv_packet(uint64_t tag, uint64_t seq, int timeout_ms) {
         auto frame = recv_frame(tag, seq, timeout_ms);
         if (!frame || frame->size() < 2) return std::nullopt;
@@ -93,7 +101,7 @@ private:
     };
     struct RxFrame {
         uint64_t seq;
-        std::vector<uint8_t> data;
+        Frame data;
     };
     void tx_loop();
     void rx_loop();

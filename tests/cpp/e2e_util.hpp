@@ -27,6 +27,7 @@ struct TestMaster {
         m->interrupt();
         m->join();
     }
+    uint32_t pool_size = 1;
     pccl::client::ClientConfig config(uint32_t group = 0) const {
         pccl::client::ClientConfig c;
         c.master.inet.protocol = inetIPv4;
@@ -34,6 +35,7 @@ struct TestMaster {
         c.master.inet.ipv4.data[3] = 1;
         c.master.port = port;
         c.peer_group = group;
+        c.pool_size = pool_size;
         return c;
     }
 };

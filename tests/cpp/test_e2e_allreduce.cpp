@@ -265,4 +265,30 @@ TEST(basic_reduce_four_elements) {
     for (auto &t : ts) t.join();
 }
 
+// connection pool of 4: large transfers are striped over all connections, small ones use one
+TEST(striped_over_connection_pool) {
+    TestMaster tm;
+    tm.pool_size = 4;
+    auto peers = connect_peers(tm, 3);
+    for (size_t n : {size_t(5), size_t(3'000'017)}) {
+        std::vector<std::vector<float>> in(3, std::vector<float>(n)), out(3, std::vector<float>(n));
+        for (int r = 0; r < 3; ++r)
+            for (size_t i = 0; i < n; ++i) in[r][i] = static_cast<float>((i * 13 + r) % 97);
+        std::vector<std::thread> ts;
+        for (int r = 0; r < 3; ++r)
+            ts.emplace_back([&, r] {
+                for (int rep = 0; rep < 3; ++rep) {
+                    ReduceRequest q;
+                    q.send = in[r].data(), q.recv = out[r].data(), q.count = n, q.op = wire::RedOp::Sum, q.tag = 9;
+                    CHECK(peers[r]->all_reduce_async(q) == client::Client::Launch::Ok);
+                    ReduceOutcome o;
+                    CHECK(peers[r]->await_reduce(9, o));
+                }
+            });
+        for (auto &t : ts) t.join();
+        for (int r = 0; r < 3; ++r)
+            for (size_t i = 0; i < n; ++i) CHECK(out[r][i] == in[0][i] + in[1][i] + in[2][i]);
+    }
+}
+
 TEST_MAIN()
