@@ -1,0 +1,294 @@
+// Shared-state synchronisation contracts (reference
+// ccoip/tests/end_to_end/test_shared_state_distribution.cpp:45-3073).
+#include <cstring>
+#include <numeric>
+
+#include "e2e_util.hpp"
+
+using namespace pccl;
+using client::SharedEntry;
+using client::SharedStateArgs;
+using wire::SyncStrategy;
+
+struct PeerState {
+    std::vector<std::vector<uint8_t>> buffers;
+    SharedStateArgs args;
+    bool ok = false;
+    uint64_t tx = 0, rx = 0;
+    void add(const std::string &key, size_t n, uint8_t fill, wire::DType dtype = wire::DType::U8, bool allow_ineq = false) {
+        buffers.emplace_back(n * wire::dtype_size(dtype), fill);
+        SharedEntry e;
+        e.key = key;
+        e.count = n;
+        e.dtype = dtype;
+        e.allow_content_inequality = allow_ineq;
+        args.entries.push_back(e);
+        for (size_t i = 0; i < buffers.size(); ++i) args.entries[i].data = buffers[i].data();
+    }
+};
+
+static void sync_all(std::vector<std::unique_ptr<client::Client>> &peers, std::vector<PeerState> &st, const std::vector<int> &who = {}) {
+    std::vector<std::thread> ts;
+    for (size_t i = 0; i < peers.size(); ++i) {
+        if (!who.empty() && std::find(who.begin(), who.end(), static_cast<int>(i)) == who.end()) continue;
+        ts.emplace_back([&, i] { st[i].ok = peers[i]->sync_shared_state(st[i].args, st[i].tx, st[i].rx); });
+    }
+    for (auto &t : ts) t.join();
+}
+
+// two peers, different content: exactly one direction transfers `size` bytes; afterwards equal
+TEST(basic_two_peers_differ) {
+    TestMaster tm;
+    auto peers = connect_peers(tm, 2);
+    std::vector<PeerState> st(2);
+    st[0].add("w", 1024, 7);
+    st[1].add("w", 1024, 9);
+    sync_all(peers, st);
+    CHECK(st[0].ok && st[1].ok);
+    CHECK(st[0].buffers[0] == st[1].buffers[0]);
+    CHECK_EQ(st[0].tx + st[1].tx, 1024u);
+    CHECK_EQ(st[0].rx + st[1].rx, 1024u);
+    CHECK((st[0].tx == 1024 && st[1].rx == 1024) || (st[1].tx == 1024 && st[0].rx == 1024));
+}
+
+TEST(identical_content_moves_nothing) {
+    TestMaster tm;
+    auto peers = connect_peers(tm, 3);
+    std::vector<PeerState> st(3);
+    for (auto &s : st) s.add("w", 4096, 3, wire::DType::F32);
+    sync_all(peers, st);
+    for (auto &s : st) CHECK(s.ok && s.tx == 0 && s.rx == 0);
+}
+
+// only keys whose hash differs are transferred
+TEST(only_dirty_keys_move) {
+    TestMaster tm;
+    auto peers = connect_peers(tm, 2);
+    std::vector<PeerState> st(2);
+    for (int p = 0; p < 2; ++p) {
+        st[p].add("a", 1000, 1);
+        st[p].add("b", 2000, p == 0 ? 2 : 5);
+        st[p].add("c", 3000, 3, wire::DType::BF16);
+    }
+    sync_all(peers, st);
+    CHECK(st[0].ok && st[1].ok);
+    CHECK_EQ(st[0].tx + st[1].tx, 2000u);
+    CHECK(st[0].buffers[1] == st[1].buffers[1]);
+}
+
+// popularity beats arrival order: 2 of 3 peers agree, the odd one receives
+TEST(popular_content_wins) {
+    TestMaster tm;
+    auto peers = connect_peers(tm, 3);
+    std::vector<PeerState> st(3);
+    st[0].add("w", 512, 42);
+    st[1].add("w", 512, 11);
+    st[2].add("w", 512, 11);
+    // the minority peer votes first
+    std::thread first([&] { st[0].ok = peers[0]->sync_shared_state(st[0].args, st[0].tx, st[0].rx); });
+    std::this_thread::sleep_for(std::chrono::milliseconds(100));
+    sync_all(peers, st, {1, 2});
+    first.join();
+    CHECK(st[0].ok && st[1].ok && st[2].ok);
+    CHECK_EQ(st[0].rx, 512u);
+    CHECK(st[0].buffers[0] == std::vector<uint8_t>(512, 11));
+    CHECK_EQ(st[1].rx + st[2].rx, 0u);
+}
+
+// peer groups are isolated: different content and key sets across groups, no traffic, no kicks
+TEST(peer_groups_are_isolated) {
+    TestMaster tm;
+    auto peers = connect_peers(tm, 4, {0, 0, 1, 1});
+    std::vector<PeerState> st(4);
+    st[0].add("w", 256, 1);
+    st[1].add("w", 256, 1);
+    st[2].add("other", 100, 2);
+    st[2].add("w", 256, 9); // same key name as in group 0, different content: no conflict
+    st[3].add("other", 100, 2);
+    st[3].add("w", 256, 9);
+    sync_all(peers, st);
+    for (auto &s : st) CHECK(s.ok && s.tx == 0 && s.rx == 0);
+    CHECK_EQ(peers[0]->local_world(), 2u);
+    CHECK_EQ(peers[0]->global_world(), 4u);
+    CHECK_EQ(peers[0]->num_groups(), 2u);
+}
+
+// multi-step: everybody advances content identically and bumps the revision by one
+TEST(multi_step_revisions) {
+    TestMaster tm;
+    auto peers = connect_peers(tm, 2);
+    std::vector<PeerState> st(2);
+    for (auto &s : st) s.add("w", 2048, 0);
+    for (int step = 0; step < 5; ++step) {
+        for (auto &s : st) {
+            std::fill(s.buffers[0].begin(), s.buffers[0].end(), static_cast<uint8_t>(step));
+            s.args.revision = 10 + step; // the first revision of a group may be anything (resume)
+        }
+        sync_all(peers, st);
+        for (auto &s : st) CHECK(s.ok && s.tx == 0 && s.rx == 0);
+    }
+}
+
+// drag-along: a peer that never bumps its revision is outdated; it adopts the distributor's
+// revision even when no bytes move
+TEST(outdated_revision_is_dragged_along) {
+    TestMaster tm;
+    auto peers = connect_peers(tm, 2);
+    std::vector<PeerState> st(2);
+    for (auto &s : st) s.add("w", 1024, 5);
+    st[0].args.revision = st[1].args.revision = 1;
+    sync_all(peers, st);
+    CHECK(st[0].ok && st[1].ok);
+    st[0].args.revision = 2; // leader moves on, laggard stays at 1 with equal content
+    sync_all(peers, st);
+    CHECK(st[0].ok && st[1].ok);
+    CHECK_EQ(st[1].args.revision, 2u);
+    CHECK_EQ(st[1].rx, 0u);
+    // now the leader also changes content: the laggard receives it
+    st[0].args.revision = 3;
+    std::fill(st[0].buffers[0].begin(), st[0].buffers[0].end(), uint8_t(77));
+    sync_all(peers, st);
+    CHECK(st[0].ok && st[1].ok);
+    CHECK_EQ(st[1].args.revision, 3u);
+    CHECK_EQ(st[1].rx, 1024u);
+    CHECK(st[1].buffers[0] == st[0].buffers[0]);
+}
+
+// revision may only grow by one: the violator is kicked; the lone outdated peer then fails too
+TEST(one_increment_rule) {
+    TestMaster tm;
+    auto peers = connect_peers(tm, 2);
+    std::vector<PeerState> st(2);
+    for (auto &s : st) s.add("w", 64, 1);
+    st[0].args.revision = st[1].args.revision = 1;
+    sync_all(peers, st);
+    CHECK(st[0].ok && st[1].ok);
+    st[0].args.revision = 4; // expected 2
+    st[1].args.revision = 1; // outdated
+    sync_all(peers, st);
+    CHECK(!st[0].ok);
+    CHECK(!st[1].ok);
+}
+
+// key set / dtype mismatch against the elected mask: the offender is kicked, the others go on
+TEST(key_set_mismatch_is_kicked) {
+    TestMaster tm;
+    auto peers = connect_peers(tm, 3);
+    std::vector<PeerState> st(3);
+    st[0].add("w", 128, 1);
+    st[1].add("w", 128, 1);
+    st[2].add("different_key", 128, 1);
+    sync_all(peers, st);
+    CHECK(st[0].ok && st[1].ok);
+    CHECK(!st[2].ok);
+    // survivors keep working
+    st[0].args.revision = st[1].args.revision = 1;
+    sync_all(peers, st, {0, 1});
+    CHECK(st[0].ok && st[1].ok);
+    // the kicked peer's later calls fail
+    CHECK(!peers[2]->sync_shared_state(st[2].args, st[2].tx, st[2].rx));
+}
+
+TEST(send_only_and_receive_only) {
+    TestMaster tm;
+    auto peers = connect_peers(tm, 3);
+    std::vector<PeerState> st(3);
+    st[0].add("w", 300, 8);
+    st[1].add("w", 300, 1);
+    st[2].add("w", 300, 2);
+    st[0].args.strategy = SyncStrategy::TxOnly;
+    st[1].args.strategy = st[2].args.strategy = SyncStrategy::RxOnly;
+    sync_all(peers, st);
+    for (auto &s : st) CHECK(s.ok);
+    CHECK_EQ(st[0].tx, 600u);
+    CHECK_EQ(st[0].rx, 0u);
+    CHECK(st[1].buffers[0] == st[0].buffers[0] && st[2].buffers[0] == st[0].buffers[0]);
+}
+
+// both SEND_ONLY with different content: at least one is kicked
+TEST(conflicting_send_only) {
+    TestMaster tm;
+    auto peers = connect_peers(tm, 2);
+    std::vector<PeerState> st(2);
+    st[0].add("w", 64, 1);
+    st[1].add("w", 64, 2);
+    st[0].args.strategy = st[1].args.strategy = SyncStrategy::TxOnly;
+    sync_all(peers, st);
+    CHECK(!st[0].ok || !st[1].ok);
+}
+
+// everybody RECEIVE_ONLY: nobody offers content, the whole group is kicked
+TEST(all_receive_only_kicks_group) {
+    TestMaster tm;
+    auto peers = connect_peers(tm, 2);
+    std::vector<PeerState> st(2);
+    st[0].add("w", 64, 1);
+    st[1].add("w", 64, 1);
+    st[0].args.strategy = st[1].args.strategy = SyncStrategy::RxOnly;
+    sync_all(peers, st);
+    CHECK(!st[0].ok && !st[1].ok);
+}
+
+// ENFORCE_POPULAR may not be mixed with other strategies: the others are kicked, the enforcer succeeds
+TEST(enforce_popular_cannot_be_mixed) {
+    TestMaster tm;
+    auto peers = connect_peers(tm, 2);
+    std::vector<PeerState> st(2);
+    st[0].add("w", 64, 1);
+    st[1].add("w", 64, 1);
+    st[0].args.strategy = SyncStrategy::EnforcePopular;
+    st[1].args.strategy = SyncStrategy::TxOnly;
+    sync_all(peers, st);
+    CHECK(st[0].ok);
+    CHECK(!st[1].ok);
+}
+
+// a peer that joins between two syncs takes part from the next one
+TEST(late_joiner_participates) {
+    TestMaster tm;
+    auto peers = connect_peers(tm, 2);
+    std::vector<PeerState> st(3);
+    for (auto &s : st) s.add("w", 777, 4, wire::DType::F16);
+    st[0].args.revision = st[1].args.revision = 1;
+    sync_all(peers, st, {0, 1});
+    CHECK(st[0].ok && st[1].ok);
+    // third peer connects while the others admit it
+    auto late = std::make_unique<client::Client>(tm.config());
+    std::atomic<bool> joined{false};
+    std::thread joiner([&] {
+        CHECK(late->connect());
+        joined = true;
+    });
+    // keep admitting until the newcomer is in (once it is accepted it has to vote as well, so the
+    // two old peers must stop voting on their own)
+    while (peers[0]->global_world() < 3) {
+        std::vector<std::thread> ts;
+        for (auto &p : peers) ts.emplace_back([&p] { CHECK(p->update_topology()); });
+        for (auto &t : ts) t.join();
+    }
+    joiner.join();
+    CHECK(joined);
+    peers.push_back(std::move(late));
+    st[0].args.revision = st[1].args.revision = 2;
+    st[2].args.revision = 2;
+    std::fill(st[2].buffers[0].begin(), st[2].buffers[0].end(), uint8_t(99)); // newcomer holds garbage
+    sync_all(peers, st);
+    for (auto &s : st) CHECK(s.ok);
+    CHECK_EQ(st[2].rx, 777u * 2);
+    CHECK(st[2].buffers[0] == st[0].buffers[0]);
+}
+
+// tensors with allow_content_inequality are never hashed or transferred
+TEST(content_inequality_allowed) {
+    TestMaster tm;
+    auto peers = connect_peers(tm, 2);
+    std::vector<PeerState> st(2);
+    st[0].add("rng_state", 100, 1, wire::DType::U8, true);
+    st[1].add("rng_state", 100, 2, wire::DType::U8, true);
+    sync_all(peers, st);
+    CHECK(st[0].ok && st[1].ok);
+    CHECK_EQ(st[0].tx + st[1].tx, 0u);
+    CHECK(st[0].buffers[0] != st[1].buffers[0]);
+}
+
+TEST_MAIN()

@@ -1,0 +1,384 @@
+// Unit tests of the host-side building blocks: wire codec (golden bytes hand-derived from the
+// reference serialisers, ccoip/src/cpp/ccoip_packets.cpp), ATSP solver, bandwidth store, hashes,
+// quantisers, 16-bit float conversions.
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+#include <numeric>
+#include <random>
+
+#include "harness.hpp"
+#include "kernels/cpu/half.hpp"
+#include "kernels/cpu/hash.hpp"
+#include "kernels/cpu/quantize.hpp"
+#include "kernels/cpu/reduce.hpp"
+#include "topo/atsp.hpp"
+#include "topo/bandwidth_store.hpp"
+#include "topo/optimizer.hpp"
+#include "wire/packets.hpp"
+
+using namespace pccl;
+using namespace pccl::wire;
+
+static std::vector<uint8_t> bytes_of(std::initializer_list<int> v) {
+    std::vector<uint8_t> out;
+    for (int x : v) out.push_back(static_cast<uint8_t>(x));
+    return out;
+}
+
+TEST(wire_primitives_are_big_endian) {
+    Writer w;
+    w.put<uint16_t>(0x1234);
+    w.put<uint32_t>(0xdeadbeef);
+    w.put<uint64_t>(1);
+    w.put<bool>(true);
+    w.put<float>(1.0f);
+    w.put_string("ab");
+    CHECK(w.bytes() == bytes_of({0x12, 0x34, 0xde, 0xad, 0xbe, 0xef, 0, 0, 0, 0, 0, 0, 0, 1, 1, 0x3f, 0x80, 0, 0, 0, 0, 0, 0, 0, 0, 0, 2, 'a', 'b'}));
+    Reader r(w.bytes().data(), w.size());
+    CHECK_EQ(r.get<uint16_t>(), 0x1234);
+    CHECK_EQ(r.get<uint32_t>(), 0xdeadbeefu);
+    CHECK_EQ(r.get<uint64_t>(), 1u);
+    CHECK(r.get<bool>());
+    CHECK(r.get<float>() == 1.0f);
+    CHECK(r.get_string() == "ab");
+    CHECK(r.ok() && r.remaining() == 0);
+    r.get<uint32_t>(); // reading past the end is an error, not a crash
+    CHECK(!r.ok());
+}
+
+TEST(wire_session_registration_golden) {
+    C2MSessionRegistration p;
+    p.peer_group = 7;
+    p.p2p_port = 48149, p.ss_port = 48150, p.bm_port = 48151;
+    const auto frame = encode_frame(p);
+    // [u64 len = 2 + 11][u16 id = 1][u32 group][bool explicit = 0][3 x u16 port]
+    CHECK(frame == bytes_of({0, 0, 0, 0, 0, 0, 0, 13, 0, 1, 0, 0, 0, 7, 0, 0xbc, 0x15, 0xbc, 0x16, 0xbc, 0x17}));
+    C2MSessionRegistration q;
+    Reader r(frame.data() + 10, frame.size() - 10);
+    CHECK(q.read(r));
+    CHECK_EQ(q.peer_group, 7u);
+    CHECK_EQ(q.ss_port, 48150);
+    // explicit addresses: three socket addresses instead of ports
+    p.explicit_addresses = true;
+    p.adv_p2p.inet.protocol = inetIPv4;
+    p.adv_p2p.inet.ipv4 = {{10, 1, 2, 3}};
+    p.adv_p2p.port = 5000;
+    p.adv_ss = p.adv_bm = p.adv_p2p;
+    Writer w;
+    p.write(w);
+    CHECK_EQ(w.size(), size_t(4 + 1 + 3 * (1 + 4 + 2)));
+    CHECK(std::vector<uint8_t>(w.bytes().begin() + 5, w.bytes().begin() + 12) == bytes_of({1, 10, 1, 2, 3, 0x13, 0x88}));
+}
+
+TEST(wire_collective_packets_golden) {
+    C2MCollectiveInitiate p;
+    p.tag = 0x0102030405060708ull;
+    p.count = 4;
+    p.dtype = DType::F32;
+    p.op = RedOp::Sum;
+    Writer w;
+    p.write(w);
+    CHECK(w.bytes() == bytes_of({1, 2, 3, 4, 5, 6, 7, 8, 0, 0, 0, 0, 0, 0, 0, 4, 10, 1}));
+    M2CCollectiveCommence c;
+    c.tag = 5, c.seq_nr = 9;
+    Writer w2;
+    c.write(w2);
+    CHECK(w2.bytes() == bytes_of({0, 0, 0, 0, 0, 0, 0, 5, 0, 0, 0, 0, 0, 0, 0, 9}));
+    CHECK_EQ(C2MCollectiveInitiate::id, 10);
+    CHECK_EQ(C2MCollectiveComplete::id, 11);
+    CHECK_EQ(M2CCollectiveCommence::id, 9);
+    CHECK_EQ(M2CCollectiveAbort::id, 11);
+}
+
+TEST(wire_round_trips) {
+    std::mt19937_64 rng(1);
+    M2CP2PConnectionInfo info;
+    info.global_world_size = 8, info.local_world_size = 4, info.num_peer_groups = 2, info.largest_group_size = 4;
+    for (int i = 0; i < 3; ++i) {
+        PeerEndpoint e;
+        e.uuid = Uuid::random_v4();
+        e.p2p_addr.inet.protocol = i == 1 ? inetIPv6 : inetIPv4;
+        e.p2p_addr.port = static_cast<uint16_t>(1000 + i);
+        info.peers.push_back(e);
+    }
+    Writer w;
+    info.write(w);
+    M2CP2PConnectionInfo back;
+    Reader r(w.bytes().data(), w.size());
+    CHECK(back.read(r) && r.remaining() == 0);
+    CHECK_EQ(back.peers.size(), size_t(3));
+    CHECK(back.peers[1].uuid == info.peers[1].uuid && back.peers[1].p2p_addr.inet.protocol == inetIPv6);
+    info.unchanged = true; // the peer list is not on the wire then
+    Writer w2;
+    info.write(w2);
+    CHECK_EQ(w2.size(), size_t(1 + 4 * 8));
+
+    C2MSyncSharedState s;
+    s.revision = 12;
+    s.strategy = SyncStrategy::TxOnly;
+    s.entries.push_back({"layer.0.weight", 0xabcdef, HashType::Simple, 1024, DType::BF16, false});
+    s.entries.push_back({"step", 0, HashType::Simple, 1, DType::I64, true});
+    Writer w3;
+    s.write(w3);
+    C2MSyncSharedState s2;
+    Reader r3(w3.bytes().data(), w3.size());
+    CHECK(s2.read(r3) && s2.entries == s.entries && s2.revision == 12 && s2.strategy == SyncStrategy::TxOnly);
+
+    // truncated input must be rejected, never read out of bounds
+    for (size_t cut = 0; cut + 1 < w3.size(); cut += 3) {
+        C2MSyncSharedState bad;
+        Reader rb(w3.bytes().data(), cut);
+        CHECK(!bad.read(rb));
+    }
+    // absurd element counts are refused before allocating
+    Writer evil;
+    evil.put<uint64_t>(1), evil.put<uint8_t>(0), evil.put<uint64_t>(~0ull);
+    C2MSyncSharedState bad;
+    Reader re(evil.bytes().data(), evil.size());
+    CHECK(!bad.read(re));
+
+    P2PDequantMeta m;
+    m.tag = 3;
+    m.meta_type = DequantMetaType::ZeroPointScale;
+    m.dtype_a = DType::I64, m.blob_a = bytes_of({0, 0, 0, 0, 0, 0, 0, 9});
+    m.dtype_b = DType::F32, m.blob_b = bytes_of({1, 2, 3, 4});
+    Writer w4;
+    m.write(w4);
+    P2PDequantMeta m2;
+    Reader r4(w4.bytes().data(), w4.size());
+    CHECK(m2.read(r4) && m2.blob_a == m.blob_a && m2.blob_b == m.blob_b && m2.dtype_b == DType::F32);
+}
+
+static double brute_force(const std::vector<double> &cost, int n) {
+    std::vector<int> perm(n - 1);
+    std::iota(perm.begin(), perm.end(), 1);
+    double best = topo::kNoEdge;
+    do {
+        std::vector<int> tour{0};
+        tour.insert(tour.end(), perm.begin(), perm.end());
+        best = std::min(best, topo::atsp_tour_cost(cost, n, tour));
+    } while (std::next_permutation(perm.begin(), perm.end()));
+    return best;
+}
+
+TEST(atsp_exact_matches_brute_force) {
+    std::mt19937 rng(7);
+    std::uniform_real_distribution<double> d(0.1, 10.0);
+    for (int n = 2; n <= 8; ++n)
+        for (int rep = 0; rep < 5; ++rep) {
+            std::vector<double> cost(n * n);
+            for (auto &c : cost) c = d(rng);
+            if (rep == 4 && n > 3) cost[1 * n + 2] = cost[2 * n + 1] = topo::kNoEdge; // missing link
+            const auto r = topo::atsp_solve_exact(cost, n);
+            const double want = brute_force(cost, n);
+            CHECK(r.feasible && r.optimal);
+            CHECK(std::fabs(r.cost - want) < 1e-9);
+            CHECK(std::fabs(topo::atsp_tour_cost(cost, n, r.tour) - r.cost) < 1e-9);
+            std::vector<int> sorted = r.tour;
+            std::sort(sorted.begin(), sorted.end());
+            for (int i = 0; i < n; ++i) CHECK_EQ(sorted[i], i);
+        }
+}
+
+TEST(atsp_heuristic_is_close_and_respects_missing_edges) {
+    std::mt19937 rng(11);
+    std::uniform_real_distribution<double> d(0.1, 10.0);
+    for (int n : {9, 12, 24}) {
+        std::vector<double> cost(n * n);
+        for (auto &c : cost) c = d(rng);
+        const auto h = topo::atsp_solve_heuristic(cost, n, 500, 4 * n, 3);
+        CHECK(h.feasible);
+        if (n <= 12) {
+            const auto e = topo::atsp_solve_exact(cost, n);
+            CHECK(h.cost <= e.cost * 1.25 + 1e-9);
+        }
+    }
+    // only one Hamiltonian cycle exists: 0->1->2->3->4->0
+    const int n = 5;
+    std::vector<double> cost(n * n, topo::kNoEdge);
+    for (int i = 0; i < n; ++i) cost[i * n + (i + 1) % n] = 1.0;
+    const auto h = topo::atsp_solve_heuristic(cost, n, 200, 20, 5);
+    CHECK(h.feasible && std::fabs(h.cost - 5.0) < 1e-9);
+}
+
+TEST(bandwidth_store_and_ring_optimiser) {
+    topo::BandwidthStore store;
+    std::vector<Uuid> peers;
+    for (int i = 0; i < 4; ++i) {
+        peers.push_back(Uuid::random_v4());
+        CHECK(store.register_peer(peers.back()));
+    }
+    CHECK(!store.register_peer(peers[0]));
+    CHECK_EQ(store.missing_edges(peers[0]).size(), size_t(6));
+    CHECK(!store.fully_populated());
+    // fast ring 0->2->1->3->0, everything else slow
+    auto fast = [&](int a, int b) { return (a == 0 && b == 2) || (a == 2 && b == 1) || (a == 1 && b == 3) || (a == 3 && b == 0); };
+    for (int a = 0; a < 4; ++a)
+        for (int b = 0; b < 4; ++b)
+            if (a != b) CHECK(store.store(peers[a], peers[b], fast(a, b) ? 40000.0 : 100.0));
+    CHECK(store.fully_populated());
+    CHECK(!store.store(peers[0], peers[0], 1.0));
+    std::vector<Uuid> ring = peers;
+    bool optimal = false;
+    CHECK(topo::optimize_ring(store, ring, optimal));
+    CHECK(optimal);
+    // the ring must follow the fast edges
+    for (size_t i = 0; i < ring.size(); ++i) {
+        const int a = static_cast<int>(std::find(peers.begin(), peers.end(), ring[i]) - peers.begin());
+        const int b = static_cast<int>(std::find(peers.begin(), peers.end(), ring[(i + 1) % 4]) - peers.begin());
+        CHECK(fast(a, b));
+    }
+    CHECK(store.unregister_peer(peers[3]));
+    CHECK(!store.get(peers[0], peers[3]));
+    CHECK(store.debug_matrix().find("Gbit/s") != std::string::npos);
+}
+
+static uint32_t lcg(uint32_t &s) {
+    s = 1664525u * s + 1013904223u;
+    return s % 256u;
+}
+
+TEST(simplehash_golden_values) {
+    // reference golden values: ccoip/tests/unit_tests/simple_hash/simplehash_cuda_test.cpp:58,104,150
+    for (auto [n, want] : {std::pair<size_t, uint64_t>{1, 344386053ull}, {4, 3765247898ull}, {25, 3651434421ull}}) {
+        std::vector<uint8_t> d(n);
+        uint32_t s = 42;
+        for (auto &b : d) b = static_cast<uint8_t>(lcg(s));
+        CHECK_EQ(cpu::simplehash(d.data(), n), want);
+    }
+    CHECK_EQ(cpu::simplehash(nullptr, 0), 0u);
+    // unaligned host pointers are fine
+    std::vector<uint8_t> d(4099);
+    uint32_t s = 1;
+    for (auto &b : d) b = static_cast<uint8_t>(lcg(s));
+    std::vector<uint8_t> shifted(d.size() + 1);
+    std::memcpy(shifted.data() + 1, d.data(), d.size());
+    CHECK_EQ(cpu::simplehash(d.data(), d.size()), cpu::simplehash(shifted.data() + 1, d.size()));
+}
+
+TEST(simplehash_golden_147MiB) {
+    // reference golden value: simplehash_cuda_test.cpp:195 (154 533 888 bytes of the seed-42 LCG)
+    const size_t n = 154533888;
+    std::vector<uint8_t> d(n);
+    uint32_t s = 42;
+    for (auto &b : d) b = static_cast<uint8_t>(lcg(s));
+    CHECK_EQ(cpu::simplehash(d.data(), n), 3391090508ull);
+}
+
+TEST(crc32c_all_paths_agree) {
+    CHECK_EQ(cpu::crc32c("123456789", 9), 0xE3069283u); // standard check value
+    std::vector<uint8_t> d(8u << 20);
+    uint32_t s = 3;
+    for (auto &b : d) b = static_cast<uint8_t>(lcg(s));
+    for (size_t n : {size_t(0), size_t(1), size_t(7), size_t(8), size_t(255), size_t(256 * 3), size_t(8192 * 3 + 5), d.size() - 3, d.size()}) {
+        for (size_t off : {size_t(0), size_t(1), size_t(5)}) {
+            if (off + n > d.size()) continue;
+            const uint32_t hw = cpu::crc32c(d.data() + off, n);
+            cpu::crc32c_force_generic(true); // what the reference calls "spoofing" CPU features
+            const uint32_t sw = cpu::crc32c(d.data() + off, n);
+            cpu::crc32c_force_generic(false);
+            CHECK_EQ(hw, sw);
+            CHECK_EQ(sw, cpu::crc32c_generic(d.data() + off, n));
+        }
+    }
+    const uint32_t a = cpu::crc32c(d.data(), 1000), b = cpu::crc32c(d.data() + 1000, 5000);
+    CHECK_EQ(cpu::crc32c_combine(a, b, 5000), cpu::crc32c(d.data(), 6000));
+}
+
+TEST(half_conversions) {
+    for (uint32_t h = 0; h < 65536; ++h) {
+        const float f = cpu::f16_to_f32(static_cast<uint16_t>(h));
+        if (std::isnan(f)) continue;
+        CHECK_EQ(cpu::f32_to_f16(f), static_cast<uint16_t>(h));
+        const float g = cpu::bf16_to_f32(static_cast<uint16_t>(h));
+        if (std::isnan(g)) continue;
+        CHECK_EQ(cpu::f32_to_bf16(g), static_cast<uint16_t>(h));
+    }
+    CHECK_EQ(cpu::f32_to_f16(65520.0f), 0x7c00); // rounds to infinity
+    CHECK_EQ(cpu::f32_to_f16(1.0f + 1.0f / 2048.0f), 0x3c00); // tie to even
+    CHECK_EQ(cpu::f32_to_bf16(1.0f + 1.0f / 256.0f), 0x3f80);
+}
+
+TEST(minmax_quantiser_matches_reference_formula) {
+    std::vector<float> x(1000);
+    for (size_t i = 0; i < x.size(); ++i) x[i] = -3.0f + 0.007f * static_cast<float>(i); // also covers all-negative sub-ranges
+    cpu::QuantParams p;
+    p.algo = QuantAlgo::MinMax;
+    p.code_dtype = DType::U8;
+    cpu::quant_analyze(x.data(), x.size(), p);
+    CHECK(p.min == x.front() && p.max == x.back());
+    std::vector<uint8_t> q(x.size());
+    cpu::quantize(x.data(), q.data(), x.size(), p);
+    for (size_t i = 0; i < x.size(); ++i) {
+        const double v = (double(x[i]) - double(x.front())) * (1.0 / double(x.back() - x.front())) * 255.0;
+        CHECK_EQ(q[i], static_cast<uint8_t>(v)); // truncating, in double
+    }
+    std::vector<float> y(x.size(), 0.0f);
+    cpu::dequantize_reduce(y.data(), q.data(), x.size(), p, RedOp::Set);
+    for (size_t i = 0; i < x.size(); ++i) CHECK(std::fabs(y[i] - x[i]) <= (x.back() - x.front()) / 255.0f + 1e-6f);
+    // all-negative chunk keeps a sane maximum (the reference seeds its max scan with FLT_MIN)
+    std::vector<float> neg{-5.0f, -4.0f, -4.5f};
+    cpu::quant_analyze(neg.data(), neg.size(), p);
+    CHECK(p.max == -4.0f && p.min == -5.0f);
+    // metadata survives the wire
+    cpu::QuantParams back = p;
+    back.min = back.max = 0;
+    CHECK(cpu::from_wire(cpu::to_wire(p, 1), back));
+    CHECK(back.min == p.min && back.max == p.max);
+}
+
+TEST(zero_point_scale_quantiser) {
+    std::vector<float> x(512);
+    for (size_t i = 0; i < x.size(); ++i) x[i] = std::sin(0.05f * static_cast<float>(i)) * 4.0f + 1.0f;
+    for (DType code : {DType::U8, DType::I8, DType::U16, DType::I16}) {
+        cpu::QuantParams p;
+        p.algo = QuantAlgo::ZeroPointScale;
+        p.code_dtype = code;
+        cpu::quant_analyze(x.data(), x.size(), p);
+        std::vector<uint8_t> q(cpu::quantized_size(p, x.size()));
+        cpu::quantize(x.data(), q.data(), x.size(), p);
+        std::vector<float> y(x.size(), 0.0f);
+        cpu::dequantize_reduce(y.data(), q.data(), x.size(), p, RedOp::Set);
+        const float step = static_cast<float>(p.scale);
+        for (size_t i = 0; i < x.size(); ++i) CHECK(std::fabs(y[i] - x[i]) <= 0.51f * step + 1e-6f);
+        cpu::QuantParams back = p;
+        back.scale = 0, back.zero_point = 0;
+        CHECK(cpu::from_wire(cpu::to_wire(p, 1), back));
+        CHECK(back.zero_point == p.zero_point && std::fabs(back.scale - p.scale) < 1e-12);
+    }
+    // constants survive exactly (the contract behind "42 + 43 == 85")
+    for (float c : {42.0f, -7.25f, 0.0f}) {
+        std::vector<float> k(100, c), y(100, 1.0f);
+        cpu::QuantParams p;
+        p.algo = QuantAlgo::ZeroPointScale;
+        p.code_dtype = DType::U8;
+        cpu::quant_analyze(k.data(), k.size(), p);
+        std::vector<uint8_t> q(k.size());
+        cpu::quantize(k.data(), q.data(), k.size(), p);
+        cpu::dequantize_reduce(y.data(), q.data(), k.size(), p, RedOp::Sum);
+        for (float v : y) CHECK(v == c + 1.0f);
+    }
+}
+
+TEST(reduce_kernels_all_types) {
+    std::vector<int16_t> a{1, -2, 30000}, b{5, 7, 2767};
+    cpu::reduce_inplace(a.data(), b.data(), 3, DType::I16, RedOp::Sum);
+    CHECK(a[0] == 6 && a[1] == 5 && a[2] == static_cast<int16_t>(32767));
+    std::vector<uint64_t> u{10, 20}, v{3, 40};
+    cpu::reduce_inplace(u.data(), v.data(), 2, DType::U64, RedOp::Max);
+    CHECK(u[0] == 10 && u[1] == 40);
+    cpu::reduce_inplace(u.data(), v.data(), 2, DType::U64, RedOp::Prod);
+    CHECK(u[0] == 30 && u[1] == 1600);
+    std::vector<int32_t> avg{7, -7, 9};
+    cpu::finalize_avg(avg.data(), 3, DType::I32, 2);
+    CHECK(avg[0] == 3 && avg[1] == -3 && avg[2] == 4); // integer division truncates
+    std::vector<uint16_t> h{cpu::f32_to_bf16(1.5f)}, g{cpu::f32_to_bf16(2.25f)};
+    cpu::reduce_inplace(h.data(), g.data(), 1, DType::BF16, RedOp::Sum);
+    CHECK(cpu::bf16_to_f32(h[0]) == 3.75f);
+    CHECK_EQ(wire::dtype_size(DType::BF16), size_t(2)); // the reference reports 0 here (src/pccl.cpp:525-543)
+    CHECK_EQ(wire::dtype_size(DType::I16), size_t(2));
+    CHECK_EQ(wire::dtype_size(DType::F16), size_t(2));
+}
+
+TEST_MAIN()
