@@ -1,0 +1,290 @@
+// Membership, topology and failure contracts (reference
+// ccoip/tests/end_to_end/test_accept_new_peers.cpp, test_peer_groups.cpp, and the SIGKILL stress
+// orchestrator python/tests/stress_tests/basic_stress_test/stresstest_orchestrator.py).
+#include <atomic>
+#include <chrono>
+#include <cstdlib>
+
+#include "e2e_util.hpp"
+#include "pccl.h"
+
+using namespace pccl;
+using namespace std::chrono_literals;
+using client::ReduceOutcome;
+using client::ReduceRequest;
+
+// connect() of the second peer blocks until the first one votes to accept it
+TEST(join_blocks_until_accepted) {
+    TestMaster tm;
+    client::Client first(tm.config());
+    CHECK(first.connect());
+    CHECK_EQ(first.global_world(), 1u);
+    client::Client second(tm.config(1)); // a different peer group: accept votes are global
+    std::atomic<bool> joined{false};
+    std::thread t([&] {
+        CHECK(second.connect());
+        joined = true;
+    });
+    std::this_thread::sleep_for(300ms);
+    CHECK(!joined);
+    bool pending = false;
+    CHECK(first.are_peers_pending(pending));
+    CHECK(pending);
+    CHECK(first.update_topology());
+    t.join();
+    CHECK(joined);
+    CHECK_EQ(first.global_world(), 2u);
+    CHECK_EQ(second.global_world(), 2u);
+    CHECK_EQ(first.local_world(), 1u);
+    CHECK_EQ(first.num_groups(), 2u);
+    CHECK_EQ(first.largest_group(), 1u);
+    // nothing pending any more; the query is a joint call of all accepted peers
+    std::thread q([&] {
+        bool p2 = true;
+        CHECK(second.are_peers_pending(p2));
+        CHECK(!p2);
+    });
+    CHECK(first.are_peers_pending(pending));
+    CHECK(!pending);
+    q.join();
+}
+
+TEST(calls_before_connect_fail) {
+    TestMaster tm;
+    client::Client c(tm.config());
+    CHECK(!c.update_topology());
+    bool pending;
+    CHECK(!c.are_peers_pending(pending));
+    ReduceRequest r;
+    float x = 1;
+    r.send = r.recv = &x;
+    r.count = 1;
+    CHECK(c.all_reduce_async(r) == client::Client::Launch::NotConnected);
+    // no master at all
+    auto cfg = tm.config();
+    cfg.master.port = 1;
+    client::Client nowhere(cfg);
+    CHECK(!nowhere.connect());
+}
+
+TEST(c_api_argument_checks) {
+    CHECK_EQ(pcclInit(), pcclSuccess);
+    pcclComm_t *comm = nullptr;
+    CHECK_EQ(pcclCreateCommunicator(nullptr, &comm), pcclInvalidArgument);
+    TestMaster tm;
+    pcclCommCreateParams_t params{};
+    params.master_address = tm.config().master;
+    CHECK_EQ(pcclCreateCommunicator(&params, &comm), pcclSuccess);
+    int v = 0;
+    CHECK_EQ(pcclGetAttribute(comm, PCCL_ATTRIBUTE_GLOBAL_WORLD_SIZE, &v), pcclInvalidUsage); // not connected
+    CHECK_EQ(pcclUpdateTopology(comm), pcclInvalidUsage);
+    CHECK_EQ(pcclConnect(comm), pcclSuccess);
+    CHECK_EQ(pcclConnect(comm), pcclInvalidUsage); // twice
+    CHECK_EQ(pcclGetAttribute(comm, PCCL_ATTRIBUTE_GLOBAL_WORLD_SIZE, &v), pcclSuccess);
+    CHECK_EQ(v, 1);
+    CHECK_EQ(pcclGetAttribute(comm, static_cast<pcclAttribute_t>(77), &v), pcclInvalidArgument);
+    float buf[4] = {1, 2, 3, 4};
+    pcclReduceDescriptor_t d{};
+    d.count = 4;
+    d.op = pcclSum;
+    d.src_descriptor.datatype = pcclFloat;
+    CHECK_EQ(pcclAllReduce(buf, buf, &d, comm, nullptr), pcclTooFewPeers); // alone
+    d.count = 0;
+    CHECK_EQ(pcclAllReduce(buf, buf, &d, comm, nullptr), pcclInvalidArgument);
+    d.count = 4;
+    d.quantization_options.algorithm = pcclQuantMinMax;
+    d.quantization_options.quantized_datatype = pcclInt8; // min-max needs an unsigned code type
+    CHECK_EQ(pcclAllReduce(buf, buf, &d, comm, nullptr), pcclInvalidArgument);
+    CHECK_EQ(pcclOptimizeTopology(comm), pcclInvalidUsage); // world of one
+    CHECK_EQ(pcclExtDataTypeSize(pcclBFloat16), size_t(2));
+    pcclBuildInfo_t info{};
+    CHECK_EQ(pcclGetBuildInfo(&info), pcclSuccess);
+    uint64_t h = 0;
+    CHECK_EQ(pcclExtHashBuffer(buf, sizeof buf, pcclDeviceCpu, 0, &h), pcclSuccess);
+    CHECK(h != 0);
+    CHECK_EQ(pcclDestroyCommunicator(comm), pcclSuccess);
+    // master handle life cycle
+    pcclMasterInstance_t *m = nullptr;
+    CHECK_EQ(pcclCreateMaster(tm.config().master, &m), pcclSuccess); // port is taken by `tm`
+    CHECK(pcclRunMaster(m) != pcclSuccess);
+    CHECK_EQ(pcclDestroyMaster(m), pcclSuccess);
+}
+
+// bandwidth measurement, ring optimisation, rewiring; reductions still work afterwards
+TEST(optimize_topology_end_to_end) {
+    setenv("PCCL_BENCHMARK_MILLIS", "120", 1);
+    setenv("PCCL_NUM_BENCHMARK_CONNECTIONS", "2", 1);
+    setenv("PCCL_BENCHMARK_BACKOFF_MILLIS", "30", 1);
+    TestMaster tm;
+    auto peers = connect_peers(tm, 4);
+    for (int round = 0; round < 2; ++round) { // second round: every edge is known, nothing to measure
+        std::vector<std::thread> ts;
+        std::atomic<int> ok{0};
+        for (auto &p : peers) ts.emplace_back([&] { ok += p->optimize_topology() ? 1 : 0; });
+        for (auto &t : ts) t.join();
+        CHECK_EQ(ok.load(), 4);
+    }
+    std::vector<std::thread> ts;
+    for (int r = 0; r < 4; ++r)
+        ts.emplace_back([&, r] {
+            std::vector<double> in(10001, r + 1.0), out(10001);
+            ReduceRequest q;
+            q.send = in.data(), q.recv = out.data(), q.count = in.size(), q.dtype = wire::DType::F64, q.tag = 4;
+            CHECK(peers[r]->all_reduce_async(q) == client::Client::Launch::Ok);
+            ReduceOutcome o;
+            CHECK(peers[r]->await_reduce(4, o));
+            for (double v : out) CHECK(v == 10.0);
+        });
+    for (auto &t : ts) t.join();
+}
+
+// A peer disappears in the middle of a reduction: the survivors' operation fails with the
+// input intact, the ring is rebuilt, and the retry succeeds with the smaller world.
+TEST(peer_loss_during_reduce_then_retry) {
+    TestMaster tm;
+    auto peers = connect_peers(tm, 3);
+    const size_t n = 6'000'000;
+    std::atomic<bool> victim_started{false};
+    std::vector<std::thread> ts;
+    std::atomic<int> survivors_ok{0};
+    for (int r = 0; r < 2; ++r)
+        ts.emplace_back([&, r] {
+            std::vector<float> buf(n, static_cast<float>(r + 1));
+            int attempts = 0;
+            for (;;) {
+                ++attempts;
+                ReduceRequest q;
+                q.send = q.recv = buf.data(); // in place: a failed attempt must leave the input untouched
+                q.count = n, q.op = wire::RedOp::Sum, q.tag = 1;
+                CHECK(peers[r]->all_reduce_async(q) == client::Client::Launch::Ok);
+                ReduceOutcome o;
+                if (peers[r]->await_reduce(1, o)) {
+                    // whichever world the successful attempt saw, the values must match it
+                    const float want = o.world == 3 ? 6.0f : 3.0f;
+                    for (size_t i = 0; i < n; i += 997) CHECK(buf[i] == want);
+                    CHECK(o.world == 2 || o.world == 3);
+                    break;
+                }
+                for (size_t i = 0; i < n; i += 997) CHECK(buf[i] == static_cast<float>(r + 1)); // rolled back
+                CHECK(attempts < 10);
+            }
+            survivors_ok++;
+        });
+    std::thread victim([&] {
+        std::vector<float> buf(n, 3.0f);
+        ReduceRequest q;
+        q.send = q.recv = buf.data();
+        q.count = n, q.tag = 1;
+        CHECK(peers[2]->all_reduce_async(q) == client::Client::Launch::Ok);
+        victim_started = true;
+        std::this_thread::sleep_for(3ms);
+        peers[2]->interrupt(); // as good as a SIGKILL from the others' point of view
+        ReduceOutcome o;
+        peers[2]->await_reduce(1, o);
+    });
+    victim.join();
+    for (auto &t : ts) t.join();
+    CHECK_EQ(survivors_ok.load(), 2);
+    // the survivors carry on as a group of two
+    CHECK_EQ(peers[0]->local_world(), 2u);
+    std::vector<std::thread> again;
+    for (int r = 0; r < 2; ++r)
+        again.emplace_back([&, r] {
+            std::vector<int32_t> in(1000, r + 1), out(1000);
+            ReduceRequest q;
+            q.send = in.data(), q.recv = out.data(), q.count = 1000, q.dtype = wire::DType::I32, q.tag = 2;
+            CHECK(peers[r]->all_reduce_async(q) == client::Client::Launch::Ok);
+            ReduceOutcome o;
+            CHECK(peers[r]->await_reduce(2, o));
+            CHECK_EQ(o.world, 2u);
+            for (auto v : out) CHECK_EQ(v, 3);
+        });
+    for (auto &t : again) t.join();
+}
+
+// pcclAllReduceMultipleWithRetry keeps going when a peer vanishes
+TEST(multiple_with_retry_survives_peer_loss) {
+    CHECK_EQ(pcclInit(), pcclSuccess);
+    TestMaster tm;
+    pcclCommCreateParams_t params{};
+    params.master_address = tm.config().master;
+    constexpr int W = 3, kOps = 12;
+    constexpr size_t n = 300'000;
+    pcclComm_t *comms[W] = {};
+    // peers join one after the other, the earlier ones admit the later ones
+    for (int i = 0; i < W; ++i) {
+        CHECK_EQ(pcclCreateCommunicator(&params, &comms[i]), pcclSuccess);
+        std::atomic<bool> joined{false};
+        std::thread j([&] {
+            CHECK_EQ(pcclConnect(comms[i]), pcclSuccess);
+            joined = true;
+        });
+        while (!joined) {
+            int world = 0;
+            if (i > 0 && pcclGetAttribute(comms[0], PCCL_ATTRIBUTE_GLOBAL_WORLD_SIZE, &world) == pcclSuccess && world < i + 1) {
+                std::vector<std::thread> ts;
+                for (int k = 0; k < i; ++k) ts.emplace_back([&, k] { CHECK_EQ(pcclUpdateTopology(comms[k]), pcclSuccess); });
+                for (auto &t : ts) t.join();
+            } else {
+                std::this_thread::sleep_for(2ms);
+            }
+        }
+        j.join();
+    }
+    std::vector<std::thread> ts;
+    std::atomic<int> done{0};
+    for (int r = 0; r < W; ++r)
+        ts.emplace_back([&, r] {
+            std::vector<std::vector<float>> in(kOps, std::vector<float>(n, 1.0f)), out(kOps, std::vector<float>(n, 0.0f));
+            std::vector<pcclReduceOpDescriptor_t> descs(kOps);
+            for (int k = 0; k < kOps; ++k) {
+                descs[k].sendbuf = in[k].data();
+                descs[k].recvbuf = out[k].data();
+                descs[k].descriptor.count = n;
+                descs[k].descriptor.op = pcclSum;
+                descs[k].descriptor.tag = 100 + k;
+                descs[k].descriptor.src_descriptor.datatype = pcclFloat;
+                descs[k].descriptor.quantization_options.algorithm = pcclQuantNone;
+            }
+            if (r == 2) { // the victim starts and dies
+                pcclAsyncReduceOp_t h{};
+                pcclAllReduceAsync(in[0].data(), out[0].data(), &descs[0].descriptor, comms[r], &h);
+                std::this_thread::sleep_for(2ms);
+                pcclDestroyCommunicator(comms[r]);
+                comms[r] = nullptr;
+                return;
+            }
+            pcclReduceInfo_t info{};
+            CHECK_EQ(pcclAllReduceMultipleWithRetry(descs.data(), kOps, comms[r], &info, 4), pcclSuccess);
+            for (int k = 0; k < kOps; ++k) {
+                const float v = out[k][n / 2];
+                CHECK(v == 2.0f || v == 3.0f); // done either before or after the loss
+            }
+            CHECK(info.tx_bytes > 0);
+            done++;
+        });
+    for (auto &t : ts) t.join();
+    CHECK_EQ(done.load(), 2);
+    for (auto *c : comms)
+        if (c) CHECK_EQ(pcclDestroyCommunicator(c), pcclSuccess);
+}
+
+TEST(master_loss_fails_cleanly) {
+    auto tm = std::make_unique<TestMaster>();
+    auto peers = connect_peers(*tm, 2);
+    tm.reset(); // master gone
+    std::this_thread::sleep_for(100ms);
+    for (auto &p : peers) {
+        CHECK(!p->update_topology());
+        ReduceRequest q;
+        float x = 1, y = 0;
+        q.send = &x, q.recv = &y, q.count = 1;
+        const auto l = p->all_reduce_async(q);
+        if (l == client::Client::Launch::Ok) {
+            ReduceOutcome o;
+            CHECK(!p->await_reduce(0, o));
+        }
+    }
+}
+
+TEST_MAIN()
