@@ -1,0 +1,200 @@
+"""Python surface on the CPU (reference: python/tests/unit_tests/pccl_test.py, numpy_only_tests, pytorch_only_tests,
+end_to_end/basic_reduce_test)."""
+import threading
+
+import numpy as np
+import pytest
+import torch
+
+import pccl_b200 as pccl
+from test_gpu_multi import run_peers
+
+
+def start_master():
+    m = pccl.MasterNode("127.0.0.1:0")
+    m.run()
+    return m, m.port
+
+
+def join(port, world, **kw):
+    c = pccl.Communicator(f"127.0.0.1:{port}", **kw)
+    c.connect(n_attempts=10)
+    while c.get_attribute(pccl.Attribute.GLOBAL_WORLD_SIZE) < world:
+        c.update_topology()
+    return c
+
+
+def run_threads(world, fn):
+    m, port = start_master()
+    errors, results = [], {}
+
+    def body(r):
+        try:
+            c = join(port, world)
+            results[r] = fn(r, c)
+            c.destroy()
+        except Exception as e:  # noqa: BLE001
+            errors.append((r, repr(e)))
+
+    ts = [threading.Thread(target=body, args=(r,)) for r in range(world)]
+    [t.start() for t in ts]
+    [t.join(timeout=120) for t in ts]
+    m.interrupt()
+    assert not errors, errors
+    return results
+
+
+def test_import_surface():
+    for name in ["Communicator", "MasterNode", "SharedState", "TensorInfo", "ReduceOp", "DataType", "QuantizationOptions",
+                 "ReduceDescriptor", "ReduceOpDescriptor", "AsyncReduceHandle", "PCCLError", "Attribute", "SharedStateSyncStrategy",
+                 "DistributionHint", "QuantizationAlgorithm", "ReduceOperandDescriptor", "ReduceInfo", "SharedStateSyncInfo"]:
+        assert hasattr(pccl, name), name
+    assert isinstance(pccl.cuda.is_available(), bool)
+    assert pccl.DataType.from_torch_dtype(torch.bfloat16) == pccl.DataType.BFLOAT16
+    assert pccl.DataType.from_numpy_dtype(np.float32) == pccl.DataType.FLOAT
+    assert pccl.DataType.FLOAT.to_torch_dtype() == torch.float32
+    assert pccl.DataType.BFLOAT16.itemsize == 2
+
+
+def test_master_lifecycle():
+    m, port = start_master()
+    assert port > 0
+    m.interrupt()
+    del m
+    m2 = pccl.MasterNode("127.0.0.1:0")  # never run: must still be destroyable
+    del m2
+
+
+def test_communicator_lifecycle_and_errors():
+    c = pccl.Communicator("127.0.0.1:1")
+    with pytest.raises(pccl.PCCLError) as e:
+        c.update_topology()  # before connect
+    assert e.value.result == pccl.Result.INVALID_USAGE
+    with pytest.raises(pccl.PCCLError) as e:
+        c.connect(n_attempts=1)  # nobody listens there
+    assert e.value.result == pccl.Result.MASTER_CONNECTION_FAILED
+    c.destroy()
+    c.destroy()  # idempotent
+    m, port = start_master()
+    solo = pccl.Communicator(f"127.0.0.1:{port}")
+    solo.connect()
+    assert solo.get_attribute(pccl.Attribute.GLOBAL_WORLD_SIZE) == 1
+    x = np.ones(8, dtype=np.float32)
+    with pytest.raises(pccl.PCCLError) as e:
+        solo.all_reduce(x, x, op=pccl.ReduceOp.SUM)
+    assert e.value.result == pccl.Result.TOO_FEW_PEERS
+    with pytest.raises(ValueError):
+        solo.all_reduce([1, 2], [3, 4], op=pccl.ReduceOp.SUM)
+    with pytest.raises(ValueError):
+        pccl.TensorInfo.from_torch(torch.ones(4, 4).t(), "non_contiguous")
+    solo.destroy()
+    m.interrupt()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_numpy_and_torch_all_reduce(world):
+    def body(r, c):
+        a = np.full(1000, r + 1, dtype=np.float32)
+        out = np.zeros_like(a)
+        info = c.all_reduce(a, out, op=pccl.ReduceOp.SUM, tag=0)
+        assert info.world_size == world and info.tx_bytes > 0
+        t = torch.full((333,), float(r), dtype=torch.bfloat16)
+        c.all_reduce(t, t, op=pccl.ReduceOp.MAX, tag=1)
+        i = torch.arange(10, dtype=torch.int64) * (r + 1)
+        c.all_reduce(i, i, op=pccl.ReduceOp.AVG, tag=2)
+        h = c.all_reduce_async(a, out, op=pccl.ReduceOp.MIN, tag=3)
+        ok, status, _ = h.wait()
+        assert ok and status == 0 and h.wait()[0]  # wait() is repeatable
+        return out.copy(), t.float().numpy().copy(), i.numpy().copy(), c.ext_last_reduce_stats(0)["plane"]
+
+    res = run_threads(world, body)
+    total = sum(range(1, world + 1))
+    for r in range(world):
+        out, t, i, plane = res[r]
+        assert plane == "tcp_ring"
+        assert (out == 1).all()  # MIN of (r+1) over ranks
+        assert (t == world - 1).all()
+        assert (i == (np.arange(10) * total) // world).all()
+
+
+def test_quantised_uint8_minmax_1000_revisions_style():
+    """the reference's python e2e: 2 peers, 1024-element uint8 min-max quantised reductions in a loop"""
+    def body(r, c):
+        q = pccl.QuantizationOptions(pccl.DataType.UINT8, pccl.QuantizationAlgorithm.MIN_MAX)
+        outs = []
+        for it in range(30):
+            x = torch.linspace(-1, 1, 1024) * (it + 1) + r
+            y = torch.empty_like(x)
+            c.all_reduce(x, y, op=pccl.ReduceOp.SUM, tag=0, quantization_options=q)
+            want = torch.linspace(-1, 1, 1024) * (it + 1) * 2 + 1
+            assert (y - want).abs().max() < 0.05 * (it + 1) + 0.05
+            outs.append(y.clone())
+        return torch.stack(outs)
+
+    res = run_threads(2, body)
+    assert torch.equal(res[0], res[1])  # bit-identical on both peers
+
+
+def test_all_reduce_multiple_with_retry():
+    def body(r, c):
+        tensors = [torch.full((n,), float(r + 1)) for n in (10, 1000, 100_000, 7)]
+        descs = []
+        for k, t in enumerate(tensors):
+            d = pccl.ReduceDescriptor(t.numel(), pccl.ReduceOp.SUM, k, pccl.ReduceOperandDescriptor(pccl.DataType.FLOAT))
+            descs.append(pccl.ReduceOpDescriptor.from_torch(t, t, d))
+        info = c.all_reduce_multiple_with_retry(descs, max_in_flight=3)
+        assert info.world_size == 3
+        return [float(t[0]) for t in tensors]
+
+    for r, vals in run_threads(3, body).items():
+        assert vals == [6.0] * 4
+
+
+def test_shared_state_revisions_and_strategies():
+    def body(r, c):
+        w = torch.full((5000,), 1.0 if r == 0 else 0.0)
+        step = torch.tensor([0], dtype=torch.int64)
+        state = pccl.SharedState([pccl.TensorInfo.from_torch(w, "w"), pccl.TensorInfo.from_torch(step, "step")])
+        state.revision = 5
+        info = c.sync_shared_state(state, pccl.SharedStateSyncStrategy.SEND_ONLY if r == 0 else pccl.SharedStateSyncStrategy.RECEIVE_ONLY)
+        first = (info.tx_bytes, info.rx_bytes)
+        assert (w == 1.0).all()
+        for it in range(3):
+            w += 1
+            step += 1
+            state.push_revision()
+            info = c.sync_shared_state(state)
+            assert info.tx_bytes == 0 and info.rx_bytes == 0
+        return first, state.revision
+
+    res = run_threads(2, body)
+    assert res[0][0] == (20000, 0) and res[1][0] == (0, 20000)
+    assert res[0][1] == res[1][1] == 8
+
+
+@pytest.mark.parametrize("scenario", ["allreduce", "concurrent", "shared_state"])
+def test_multi_process_peers_on_cpu(scenario):
+    for r in run_peers(3, scenario, devices=["cpu"] * 3):
+        assert r["ok"], r
+
+
+def test_diloco_cpu_matches_torch_sgd():
+    from pccl_b200.parallel import DiLoCo
+
+    def body(r, c):
+        torch.manual_seed(0)
+        params = torch.randn(2000)
+        ref = params.clone().requires_grad_(True)
+        opt = torch.optim.SGD([ref], lr=0.7, momentum=0.9, nesterov=True)
+        d = DiLoCo(c, params, lr=0.7, momentum=0.9)
+        for step in range(3):
+            inner = params - 0.01 * (step + 1) * (r + 1)   # what this peer's inner optimiser produced
+            d.outer_step(inner)
+            # plain PyTorch reference: averaged pseudo-gradient = 0.01*(step+1)*mean(r+1) = 0.015*(step+1) for two peers
+            ref.grad = torch.full_like(ref, 0.015 * (step + 1))
+            opt.step()
+            torch.testing.assert_close(params, ref.detach(), rtol=1e-5, atol=1e-6)
+            assert torch.equal(inner, params)  # the inner copy restarts from the new outer parameters
+        return True
+
+    assert all(run_threads(2, body).values())
