@@ -68,6 +68,13 @@ bool Client::connect() {
         PLOG(ERR) << "cannot reach master at " << net::to_string(cfg_.master);
         return false;
     }
+    // device-plane operations are queued per staging slot in the order their Commence packets arrive
+    master_.set_observer([this](uint16_t id, const std::vector<uint8_t> &payload) {
+        if (id != M2CCollectiveCommence::id) return;
+        Reader r(payload.data(), payload.size());
+        M2CCollectiveCommence c;
+        if (c.read(r) && (c.seq_nr >> 63)) plane_->announce(c.seq_nr & ~(3ull << 62));
+    });
     master_.run();
 
     C2MSessionRegistration reg;
@@ -795,6 +802,7 @@ ReduceOutcome Client::run_reduce(const ReduceRequest &req, uint64_t) {
     uint8_t *stage = nullptr;         // host staging for device buffers on the TCP plane
     const bool in_place = req.send == req.recv;
 
+    if (use_device && (poisoned || !device_capable)) plane_->cancel(seq); // announced, but it will not run
     if (poisoned) {
         PLOG(INFO) << "previous reduction on tag " << req.tag << " was aborted after it finished locally; failing this one";
     } else if (use_device && device_capable) {

@@ -77,6 +77,14 @@ public:
     static constexpr uint32_t kCapP2P = 1, kCapNvls = 2;
     virtual uint32_t capabilities(const DeviceReduceArgs &args) = 0;
 
+    // Operations that share a staging slot must run in the same order on every peer, otherwise two
+    // peers can each hold the slot for a different operation and wait for each other forever.
+    // The order everybody agrees on is the order in which the master's Commence packets arrive:
+    // `announce` is called for every device-plane Commence, in arrival order; `reduce` then waits
+    // for its turn; an announced operation that is not going to run must be `cancel`led.
+    virtual void announce(uint64_t seq) = 0;
+    virtual void cancel(uint64_t seq) = 0;
+
     // Runs the reduction; `abort_requested` is polled while the kernel runs.
     virtual DeviceReduceResult reduce(const DeviceReduceArgs &args, const std::function<bool()> &abort_requested) = 0;
 

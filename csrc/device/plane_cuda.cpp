@@ -14,7 +14,9 @@
 #include <algorithm>
 #include <atomic>
 #include <chrono>
+#include <condition_variable>
 #include <cstring>
+#include <deque>
 #include <map>
 #include <mutex>
 #include <thread>
@@ -328,8 +330,33 @@ public:
         }
     }
 
+    void announce(uint64_t seq) override {
+        std::lock_guard<std::mutex> lock(order_mu_);
+        order_[seq % n_slots_].push_back(seq);
+    }
+
+    void cancel(uint64_t seq) override {
+        {
+            std::lock_guard<std::mutex> lock(order_mu_);
+            auto &q = order_[seq % n_slots_];
+            q.erase(std::remove(q.begin(), q.end(), seq), q.end());
+        }
+        order_cv_.notify_all();
+    }
+
     DeviceReduceResult reduce(const DeviceReduceArgs &a, const std::function<bool()> &abort_requested) override {
         DeviceReduceResult res;
+        // wait for this operation's turn on its slot (see announce()); leave the queue on every exit
+        struct Turn {
+            CudaPlane *p;
+            uint64_t seq;
+            ~Turn() { p->cancel(seq); }
+        } turn{this, a.seq};
+        {
+            std::unique_lock<std::mutex> lock(order_mu_);
+            auto &q = order_[a.seq % n_slots_];
+            order_cv_.wait(lock, [&] { return q.empty() || q.front() == a.seq || std::find(q.begin(), q.end(), a.seq) == q.end(); });
+        }
         std::vector<void *> arenas;
         void *mc_view = nullptr;
         {
@@ -966,6 +993,10 @@ private:
     std::unordered_map<Uuid, Peer> peers_;
     std::vector<Uuid> ring_;
     bool ring_ready_ = false;
+
+    std::mutex order_mu_;
+    std::condition_variable order_cv_;
+    std::map<uint64_t, std::deque<uint64_t>> order_; // per slot: announced operations in arrival order
 
     std::mutex copy_mu_;
     cudaStream_t util_stream_ = nullptr;

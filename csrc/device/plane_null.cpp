@@ -13,6 +13,8 @@ public:
     void stop() override {}
     void on_ring_changed(const std::vector<Uuid> &) override {}
     uint32_t capabilities(const DeviceReduceArgs &) override { return 0; }
+    void announce(uint64_t) override {}
+    void cancel(uint64_t) override {}
     DeviceReduceResult reduce(const DeviceReduceArgs &, const std::function<bool()> &) override { return {}; }
     bool restore_input(const DeviceReduceArgs &) override { return false; }
     bool copy_to_host(void *, const void *, size_t) override { return false; }

@@ -61,6 +61,7 @@ void QueuedSocket::rx_loop() {
         f.id = static_cast<uint16_t>(head[8] << 8 | head[9]);
         f.payload.resize(len - 2);
         if (!f.payload.empty() && !recv_all(fd_, f.payload.data(), f.payload.size())) break;
+        if (observer_) observer_(f.id, f.payload);
         {
             std::lock_guard<std::mutex> lock(mu_);
             inbox_.push_back(std::move(f));

@@ -27,6 +27,9 @@ public:
 
     bool connect();
     bool run(); // starts the receive thread
+    // Called on the receive thread for every frame, in arrival order, before the frame is queued.
+    using Observer = std::function<void(uint16_t id, const std::vector<uint8_t> &payload)>;
+    void set_observer(Observer fn) { observer_ = std::move(fn); }
     bool interrupt();
     void join();
     bool is_open() const { return open_.load(); }
@@ -77,6 +80,7 @@ private:
     std::mutex mu_, send_mu_;
     std::condition_variable cv_;
     std::list<Frame> inbox_;
+    Observer observer_;
 };
 
 } // namespace pccl::net

@@ -364,7 +364,10 @@ class Communicator:
     def destroy(self) -> None:
         comm, self._comm = getattr(self, "_comm", None), None
         if comm:
-            lib().pcclDestroyCommunicator(comm)
+            try:
+                lib().pcclDestroyCommunicator(comm)
+            except Exception:  # interpreter shutdown: module globals may already be gone
+                pass
 
     def get_attribute(self, attribute: Attribute) -> int:
         out = C.c_int()
@@ -521,10 +524,13 @@ class MasterNode:
         m, self._master = getattr(self, "_master", None), None
         if not m:
             return
-        if self._running:
-            lib().pcclInterruptMaster(m)
-            lib().pcclMasterAwaitTermination(m)
-        lib().pcclDestroyMaster(m)
+        try:
+            if self._running:
+                lib().pcclInterruptMaster(m)
+                lib().pcclMasterAwaitTermination(m)
+            lib().pcclDestroyMaster(m)
+        except Exception:  # interpreter shutdown
+            pass
 
 
 def get_build_info() -> Dict[str, bool]:
