@@ -1,5 +1,6 @@
 """Training-loop level building blocks on top of the communicator: DiLoCo outer steps, DDP-style
 gradient averaging."""
-from .diloco import DiLoCo, LocalOuterStep
+from .ddp import GradientAverager
+from .diloco import AsyncDiLoCo, DiLoCo, LocalOuterStep
 
-__all__ = ["DiLoCo", "LocalOuterStep"]
+__all__ = ["DiLoCo", "AsyncDiLoCo", "LocalOuterStep", "GradientAverager"]

@@ -110,3 +110,73 @@ class DiLoCo:
             self.params.sub_(self.lr * (self.grad + self.mu * self.buf))
             inner.copy_(self.params)
         self.steps += 1
+
+
+class AsyncDiLoCo:
+    """One-step-delayed ("streaming") DiLoCo: the all-reduce of outer step t runs while the inner
+    phase of step t+1 computes; its result is applied at the end of step t+1.
+    Reference: python/examples/nanogpt_diloco/async_diloco.py:405-640 (reduction on a background thread,
+    `are_peers_pending` gate before `update_topology`)."""
+
+    def __init__(self, comm: Communicator, params: torch.Tensor, lr: float = 0.7, momentum: float = 0.9,
+                 quantization: Optional[QuantizationOptions] = None):
+        assert params.dtype == torch.float32 and params.is_contiguous()
+        self.comm = comm
+        self.params = params
+        self.lr, self.mu = lr, momentum
+        self.quantization = quantization
+        self.buf = torch.zeros_like(params)
+        self.grads = [torch.empty_like(params), torch.empty_like(params)]  # double buffer
+        self.in_flight = None  # (handle, buffer index)
+        self.steps = 0
+        self.applied = 0
+
+    def _apply(self, grad: torch.Tensor, inner: Optional[torch.Tensor]) -> None:
+        if self.params.is_cuda:
+            outer_nesterov_(self.params, self.buf, grad, inner, self.lr, self.mu, self.applied == 0)
+        else:
+            if self.applied == 0:
+                self.buf.copy_(grad)
+            else:
+                self.buf.mul_(self.mu).add_(grad)
+            self.params.sub_(self.lr * (grad + self.mu * self.buf))
+            if inner is not None:
+                inner.copy_(self.params)
+        self.applied += 1
+
+    def outer_step(self, inner: torch.Tensor) -> bool:
+        """Launches the reduction of this step's pseudo-gradient and applies the previous one.
+        Returns False when the previous reduction was lost to a peer failure (it is skipped)."""
+        idx = self.steps % 2
+        grad = self.grads[idx]
+        if self.params.is_cuda:
+            pseudo_gradient(grad, self.params, inner)
+        else:
+            torch.sub(self.params, inner, out=grad)
+        ok = True
+        previous = self.in_flight
+        if previous is not None:
+            handle, pidx = previous
+            success, status, _ = handle.wait()
+            if success:
+                self._apply(self.grads[pidx], None)
+            else:
+                ok = False  # dropped: DiLoCo tolerates a skipped outer update
+        try:
+            self.in_flight = (self.comm.all_reduce_async(grad, grad, op=ReduceOp.AVG, tag=idx, quantization_options=self.quantization), idx)
+        except PCCLError as e:
+            if e.result != Result.TOO_FEW_PEERS:
+                raise
+            self.in_flight = None
+            self._apply(grad, None)  # alone: apply the local pseudo-gradient right away
+        inner.copy_(self.params)
+        self.steps += 1
+        return ok
+
+    def flush(self) -> None:
+        """Waits for the reduction in flight and applies it (call before checkpointing / topology changes)."""
+        if self.in_flight is not None:
+            handle, pidx = self.in_flight
+            if handle.wait()[0]:
+                self._apply(self.grads[pidx], None)
+            self.in_flight = None

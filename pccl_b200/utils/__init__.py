@@ -1,0 +1,3 @@
+from .profiler import Profiler
+
+__all__ = ["Profiler"]
