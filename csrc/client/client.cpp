@@ -431,9 +431,26 @@ constexpr size_t kStageBytes = 8u << 20;
 }
 
 void Client::on_shared_state_accept(std::unique_ptr<net::BlockingSocket> sock) {
-    const auto req = sock->recv_packet<C2SRequestSharedState>(10000);
-    if (!req) return;
-    S2CSharedStateResponse resp;
+    uint16_t id = 0;
+    std::vector<uint8_t> payload;
+    if (!sock->recv_frame(id, payload, 10000)) return;
+    Reader r(payload.data(), payload.size());
+    std::vector<std::string> keys;
+    Uuid requester;
+    const bool extended = id == C2SRequestSharedStateP2P::id;
+    if (extended) {
+        C2SRequestSharedStateP2P req;
+        if (!req.read(r)) return;
+        keys = std::move(req.keys);
+        requester = req.requester;
+    } else if (id == C2SRequestSharedState::id) {
+        C2SRequestSharedState req;
+        if (!req.read(r)) return;
+        keys = std::move(req.keys);
+    } else {
+        return;
+    }
+    S2CSharedStateResponseP2P resp;
     std::vector<SharedEntry> serve;
     {
         std::lock_guard<std::mutex> lock(ss_mu_);
@@ -442,7 +459,7 @@ void Client::on_shared_state_accept(std::unique_ptr<net::BlockingSocket> sock) {
         } else {
             resp.status = SharedStateStatus::Success;
             resp.revision = ss_snapshot_.revision;
-            for (const auto &key : req->keys) {
+            for (const auto &key : keys) {
                 const auto it = std::find_if(ss_snapshot_.entries.begin(), ss_snapshot_.entries.end(),
                                              [&](const SharedEntry &e) { return e.key == key; });
                 if (it == ss_snapshot_.entries.end()) {
@@ -456,9 +473,39 @@ void Client::on_shared_state_accept(std::unique_ptr<net::BlockingSocket> sock) {
             }
         }
     }
-    if (!sock->send_packet(resp) || resp.status != SharedStateStatus::Success) return;
-    // Raw tensor bytes follow, unframed, in request order.  The buffers stay valid: the owner is
-    // blocked inside sync_shared_state until every peer has reported completion.
+    // NVLink path: the requester lives in the same NVLink domain and has this peer's arena mapped
+    const size_t chunk = extended ? plane_->exchange_bytes() : 0;
+    resp.p2p = extended && chunk > 0 && plane_->peer_mapped(requester) && env_flag("PCCL_SHARED_STATE_P2P", true);
+    resp.distributor = uuid_;
+    resp.chunk_bytes = chunk;
+    if (extended) {
+        if (!sock->send_packet(resp)) return;
+    } else {
+        S2CSharedStateResponse base;
+        base.status = resp.status;
+        base.revision = resp.revision;
+        base.entries = resp.entries;
+        if (!sock->send_packet(base)) return;
+    }
+    if (resp.status != SharedStateStatus::Success) return;
+    // The buffers stay valid: the owner is blocked inside sync_shared_state until every peer has
+    // reported completion.
+    if (resp.p2p) {
+        auto staging = plane_->exchange_lock(); // one requester at a time uses the staging area
+        for (const auto &e : serve) {
+            const size_t bytes = e.bytes();
+            for (size_t off = 0; off < bytes || (bytes == 0 && off == 0); off += chunk) {
+                const size_t n = std::min(chunk, bytes - off);
+                if (n && !plane_->export_chunk(static_cast<const uint8_t *>(e.data) + off, e.on_device, n)) return;
+                if (!sock->send_packet(S2CChunkReady{})) return;
+                if (!sock->recv_packet<C2SChunkAck>(60000)) return;
+                if (bytes == 0) break;
+            }
+            ss_tx_bytes_ += bytes;
+        }
+        return;
+    }
+    // Base protocol: raw tensor bytes follow, unframed, in request order.
     std::vector<uint8_t> stage;
     for (const auto &e : serve) {
         const size_t bytes = e.bytes();
@@ -537,26 +584,60 @@ bool Client::sync_shared_state(SharedStateArgs &state, uint64_t &tx_bytes, uint6
             PLOG(ERR) << "cannot reach shared-state distributor " << net::to_string(verdict->distributor);
             return false;
         }
-        C2SRequestSharedState req;
-        req.keys = verdict->outdated_keys;
-        if (!sock.send_packet(req)) return false;
-        const auto resp = sock.recv_packet<S2CSharedStateResponse>(60000);
-        if (!resp || resp->status != SharedStateStatus::Success) {
-            PLOG(ERR) << "distributor refused the shared-state request";
-            return false;
+        // Ask with the extended request when this peer has a device plane that could take the data
+        // over NVLink; the distributor answers whether it can.
+        const bool try_p2p = plane_->exchange_bytes() > 0;
+        bool p2p = false;
+        Uuid distributor;
+        uint64_t chunk = 0;
+        std::vector<SharedStateSlice> offered;
+        if (try_p2p) {
+            C2SRequestSharedStateP2P req;
+            req.requester = uuid_;
+            req.keys = verdict->outdated_keys;
+            if (!sock.send_packet(req)) return false;
+            const auto resp = sock.recv_packet<S2CSharedStateResponseP2P>(60000);
+            if (!resp || resp->status != SharedStateStatus::Success) {
+                PLOG(ERR) << "distributor refused the shared-state request";
+                return false;
+            }
+            p2p = resp->p2p && resp->chunk_bytes > 0 && plane_->peer_mapped(resp->distributor);
+            if (resp->p2p && !p2p) return false; // the distributor will wait for acks we cannot give
+            distributor = resp->distributor;
+            chunk = resp->chunk_bytes;
+            offered = resp->entries;
+            state.revision = resp->revision;
+        } else {
+            C2SRequestSharedState req;
+            req.keys = verdict->outdated_keys;
+            if (!sock.send_packet(req)) return false;
+            const auto resp = sock.recv_packet<S2CSharedStateResponse>(60000);
+            if (!resp || resp->status != SharedStateStatus::Success) {
+                PLOG(ERR) << "distributor refused the shared-state request";
+                return false;
+            }
+            offered = resp->entries;
+            state.revision = resp->revision; // adopt the distributor's revision even if no bytes move
         }
-        if (resp->entries.size() != verdict->outdated_keys.size()) return false;
-        state.revision = resp->revision; // adopt the distributor's revision even if no bytes move
+        if (offered.size() != verdict->outdated_keys.size()) return false;
         std::vector<uint8_t> stage;
-        for (size_t i = 0; i < resp->entries.size(); ++i) {
-            const auto &slice = resp->entries[i];
+        for (size_t i = 0; i < offered.size(); ++i) {
+            const auto &slice = offered[i];
             const auto it = std::find_if(state.entries.begin(), state.entries.end(),
                                          [&](const SharedEntry &e) { return e.key == slice.key; });
             if (it == state.entries.end() || it->bytes() != slice.size_bytes) {
                 PLOG(ERR) << "distributor offered '" << slice.key << "' with an unexpected size";
                 return false;
             }
-            if (!it->on_device) {
+            if (p2p) {
+                for (size_t off = 0; off < slice.size_bytes || (slice.size_bytes == 0 && off == 0); off += chunk) {
+                    const size_t n = std::min<size_t>(chunk, slice.size_bytes - off);
+                    if (!sock.recv_packet<S2CChunkReady>(60000)) return false;
+                    if (n && !plane_->import_chunk(distributor, static_cast<uint8_t *>(it->data) + off, it->on_device, n)) return false;
+                    if (!sock.send_packet(C2SChunkAck{})) return false;
+                    if (slice.size_bytes == 0) break;
+                }
+            } else if (!it->on_device) {
                 if (!sock.recv_raw(it->data, slice.size_bytes)) return false;
             } else {
                 if (stage.empty()) stage.resize(kStageBytes);

@@ -20,6 +20,7 @@
 #include <cstdint>
 #include <functional>
 #include <memory>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -77,8 +78,9 @@ public:
     static constexpr uint32_t kCapP2P = 1, kCapNvls = 2;
     virtual uint32_t capabilities(const DeviceReduceArgs &args) = 0;
 
-    // Operations that share a staging slot must run in the same order on every peer, otherwise two
-    // peers can each hold the slot for a different operation and wait for each other forever.
+    // Device operations must run in the same order on every peer, otherwise two peers can each
+    // run a different operation first (holding the staging slot and the SMs) and wait for each
+    // other forever.
     // The order everybody agrees on is the order in which the master's Commence packets arrive:
     // `announce` is called for every device-plane Commence, in arrival order; `reduce` then waits
     // for its turn; an announced operation that is not going to run must be `cancel`led.
@@ -96,6 +98,16 @@ public:
     virtual bool copy_to_device(void *dev_dst, const void *host_src, size_t bytes) = 0;
     // Content hash of a device buffer; hash_type as on the wire.
     virtual bool hash_device(const void *dev_ptr, size_t bytes, wire::HashType type, uint64_t &out) = 0;
+
+    // Shared-state transfer between peers of one NVLink domain: the distributor stages a chunk in its
+    // arena (export), the requester copies it out of the mapped arena (import).  `exchange_bytes` is
+    // the chunk capacity, 0 when the plane has no arena; `exchange_lock` serialises users of the
+    // staging area on the distributor.
+    virtual bool peer_mapped(const Uuid &peer) = 0;
+    virtual size_t exchange_bytes() = 0;
+    virtual std::unique_lock<std::mutex> exchange_lock() = 0;
+    virtual bool export_chunk(const void *src, bool src_on_device, size_t bytes) = 0;
+    virtual bool import_chunk(const Uuid &from, void *dst, bool dst_on_device, size_t bytes) = 0;
 
     // Page-locked host memory for staging (plain malloc when there is no GPU).
     virtual void *host_alloc(size_t bytes) = 0;

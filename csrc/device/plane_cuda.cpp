@@ -332,21 +332,23 @@ public:
 
     void announce(uint64_t seq) override {
         std::lock_guard<std::mutex> lock(order_mu_);
-        order_[seq % n_slots_].push_back(seq);
+        order_.push_back(seq);
     }
 
     void cancel(uint64_t seq) override {
         {
             std::lock_guard<std::mutex> lock(order_mu_);
-            auto &q = order_[seq % n_slots_];
-            q.erase(std::remove(q.begin(), q.end(), seq), q.end());
+            order_.erase(std::remove(order_.begin(), order_.end(), seq), order_.end());
         }
         order_cv_.notify_all();
     }
 
     DeviceReduceResult reduce(const DeviceReduceArgs &a, const std::function<bool()> &abort_requested) override {
         DeviceReduceResult res;
-        // wait for this operation's turn on its slot (see announce()); leave the queue on every exit
+        // Wait for this operation's turn (see announce()); leave the queue on every exit.  Device
+        // operations run strictly one after the other, in the same order on every peer: two
+        // collective kernels that each want (nearly) every SM and each wait for their twin on the
+        // other GPUs would deadlock if two GPUs started them in different orders.
         struct Turn {
             CudaPlane *p;
             uint64_t seq;
@@ -354,7 +356,7 @@ public:
         } turn{this, a.seq};
         {
             std::unique_lock<std::mutex> lock(order_mu_);
-            auto &q = order_[a.seq % n_slots_];
+            auto &q = order_;
             order_cv_.wait(lock, [&] { return q.empty() || q.front() == a.seq || std::find(q.begin(), q.end(), a.seq) == q.end(); });
         }
         std::vector<void *> arenas;
@@ -514,6 +516,30 @@ public:
         if (prev >= 0) cudaSetDevice(prev);
         if (rc != 0) PLOG(ERR) << "device hash failed: " << cudaGetErrorString(static_cast<cudaError_t>(rc));
         return rc == 0;
+    }
+
+    bool peer_mapped(const Uuid &peer) override {
+        std::lock_guard<std::mutex> lock(mu_);
+        return ring_ready_ && peers_.count(peer) > 0;
+    }
+    size_t exchange_bytes() override {
+        std::lock_guard<std::mutex> lock(mu_);
+        return arena_ptr_ && !slots_.empty() ? slot_bytes_ : 0;
+    }
+    std::unique_lock<std::mutex> exchange_lock() override { return std::unique_lock<std::mutex>(slots_[0].mu); }
+    bool export_chunk(const void *src, bool, size_t bytes) override {
+        if (bytes > slot_bytes_) return false;
+        return copy(reinterpret_cast<void *>(arena_ptr_ + slot_offset(0)), src, bytes, cudaMemcpyDefault);
+    }
+    bool import_chunk(const Uuid &from, void *dst, bool, size_t bytes) override {
+        CUdeviceptr base = 0;
+        {
+            std::lock_guard<std::mutex> lock(mu_);
+            const auto it = peers_.find(from);
+            if (it == peers_.end() || bytes > slot_bytes_) return false;
+            base = it->second.ptr;
+        }
+        return copy(dst, reinterpret_cast<const void *>(base + slot_offset(0)), bytes, cudaMemcpyDefault);
     }
 
     void *host_alloc(size_t bytes) override {
@@ -939,11 +965,15 @@ private:
 
     bool copy(void *dst, const void *src, size_t bytes, cudaMemcpyKind kind) {
         if (!cuda_runtime_usable()) return false;
-        const PointerInfo info = classify_pointer(kind == cudaMemcpyDeviceToHost ? src : dst);
-        if (info.is_device && info.device >= 0) cudaSetDevice(info.device);
+        if (kind == cudaMemcpyDefault) {
+            cudaSetDevice(device_);
+        } else {
+            const PointerInfo info = classify_pointer(kind == cudaMemcpyDeviceToHost ? src : dst);
+            if (info.is_device && info.device >= 0) cudaSetDevice(info.device);
+        }
         std::lock_guard<std::mutex> lock(copy_mu_);
         if (!util_stream_) RT_TRY(cudaStreamCreateWithFlags(&util_stream_, cudaStreamNonBlocking));
-        if (kind == cudaMemcpyDeviceToHost) {
+        if (kind == cudaMemcpyDeviceToHost || kind == cudaMemcpyDefault) {
             // the source may still be written by work queued on the legacy default stream
             cudaEvent_t ready;
             RT_TRY(cudaEventCreateWithFlags(&ready, cudaEventDisableTiming));
@@ -996,7 +1026,7 @@ private:
 
     std::mutex order_mu_;
     std::condition_variable order_cv_;
-    std::map<uint64_t, std::deque<uint64_t>> order_; // per slot: announced operations in arrival order
+    std::deque<uint64_t> order_; // announced device operations in Commence arrival order
 
     std::mutex copy_mu_;
     cudaStream_t util_stream_ = nullptr;

@@ -8,6 +8,8 @@ namespace pccl::device {
 #ifdef PCCL_NO_CUDA
 namespace {
 class NullPlane final : public Plane {
+    std::mutex mu_;
+
 public:
     void start(const Uuid &) override {}
     void stop() override {}
@@ -20,6 +22,11 @@ public:
     bool copy_to_host(void *, const void *, size_t) override { return false; }
     bool copy_to_device(void *, const void *, size_t) override { return false; }
     bool hash_device(const void *, size_t, wire::HashType, uint64_t &) override { return false; }
+    bool peer_mapped(const Uuid &) override { return false; }
+    size_t exchange_bytes() override { return 0; }
+    std::unique_lock<std::mutex> exchange_lock() override { return std::unique_lock<std::mutex>(mu_); }
+    bool export_chunk(const void *, bool, size_t) override { return false; }
+    bool import_chunk(const Uuid &, void *, bool, size_t) override { return false; }
     void *host_alloc(size_t bytes) override { return std::malloc(bytes); }
     void host_free(void *ptr) override { std::free(ptr); }
     void *symmetric_alloc(size_t) override { return nullptr; }

@@ -287,97 +287,117 @@ template <typename T, int OP> __global__ void __launch_bounds__(kThreads, 1) all
 //   staging layout: [u32 codes, one per float4][block records, one per 32 float4]
 // -----------------------------------------------------------------------------------------
 template <int ALGO, int OP> __global__ void __launch_bounds__(kThreads, 1) allreduce_two_shot_quant_kernel(const DevArgs a) {
+    // Work unit = one 16-byte code packet = 16 fp32 values of one thread; 8 lanes share a block record.
     constexpr int MB = QuantMeta<ALGO>::kBytes;
-    const uint64_t n_pack = (a.count + 3) / 4;                 // float4 packets
-    const uint64_t n_pack_pad = (n_pack + 31) / 32 * 32;       // whole quantisation blocks
-    const uint64_t per = ((n_pack_pad / 32 + a.world - 1) / a.world) * 32; // chunk = whole blocks
+    const uint64_t n_blocks = (a.count + PCCL_K_QUANT_BLOCK - 1) / PCCL_K_QUANT_BLOCK;
+    const uint64_t n_pack = n_blocks * 8;                                     // code packets incl. padding
+    const uint64_t per = ((n_blocks + a.world - 1) / a.world) * 8;            // chunk = whole blocks
     const float *src = static_cast<const float *>(a.src);
     float *dst = static_cast<float *>(a.dst);
     const bool src_aligned = (reinterpret_cast<uintptr_t>(src) & 15) == 0, dst_aligned = (reinterpret_cast<uintptr_t>(dst) & 15) == 0;
     const int lane = threadIdx.x & 31;
     __shared__ PeerTable tbl;
     load_peer_table(tbl, a);
-    auto codes = [&](uint32_t r) { return reinterpret_cast<uint32_t *>(tbl.base[r]); };
-    auto metas = [&](uint32_t r) { return tbl.base[r] + n_pack_pad * 4; };
+    auto codes = [&](uint32_t r) { return reinterpret_cast<uint4 *>(tbl.base[r]); };
+    auto metas = [&](uint32_t r) { return tbl.base[r] + n_pack * 16; };
 
-    auto load4 = [&](uint64_t v, float (&x)[4]) -> int {
-        const uint4 raw = load_input(src, v < n_pack ? v : 0, v < n_pack ? a.count : 0, src_aligned);
-        x[0] = __uint_as_float(raw.x), x[1] = __uint_as_float(raw.y), x[2] = __uint_as_float(raw.z), x[3] = __uint_as_float(raw.w);
-        if (v >= n_pack) return 0;
-        const uint64_t left = a.count - v * 4;
-        return left >= 4 ? 4 : static_cast<int>(left);
+    auto valid_of = [&](uint64_t v) -> int {
+        const uint64_t e = v * 16;
+        return e >= a.count ? 0 : (a.count - e >= 16 ? 16 : static_cast<int>(a.count - e));
+    };
+    // The input is read with plain (L1-allocating) loads: a thread walks 64 contiguous bytes in
+    // four steps, the neighbouring lanes fill the rest of each 128-byte line.
+    auto load16 = [&](uint64_t v, float (&x)[16]) -> int {
+        const int valid = valid_of(v);
+        if (valid == 16 && src_aligned) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const float4 f = *reinterpret_cast<const float4 *>(src + v * 16 + j * 4);
+                x[4 * j] = f.x, x[4 * j + 1] = f.y, x[4 * j + 2] = f.z, x[4 * j + 3] = f.w;
+            }
+        } else {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) x[i] = i < valid ? src[v * 16 + i] : 0.0f;
+        }
+        return valid;
+    };
+    auto store16 = [&](uint64_t v, const float (&y)[16]) {
+        const int valid = valid_of(v);
+        if (valid == 16 && dst_aligned) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) *reinterpret_cast<float4 *>(dst + v * 16 + j * 4) = make_float4(y[4 * j], y[4 * j + 1], y[4 * j + 2], y[4 * j + 3]);
+        } else {
+#pragma unroll
+            for (int i = 0; i < 16; ++i)
+                if (i < valid) dst[v * 16 + i] = y[i];
+        }
+    };
+    auto store_record = [&](uint32_t r, uint64_t v, uint32_t lo, uint32_t hi) {
+        if ((lane & 7) != 0) return;
+        uint8_t *m = metas(r) + (v / 8) * MB;
+        if constexpr (MB == 8)
+            *reinterpret_cast<uint2 *>(m) = make_uint2(lo, hi);
+        else
+            *reinterpret_cast<uint32_t *>(m) = lo;
+    };
+    auto load_record = [&](uint32_t r, uint64_t v, uint32_t &lo, uint32_t &hi) {
+        const uint8_t *m = metas(r) + (v / 8) * MB;
+        if constexpr (MB == 8) {
+            const uint2 q = ld_peer_8(m);
+            lo = q.x, hi = q.y;
+        } else {
+            lo = ld_peer_4(m), hi = 0;
+        }
     };
 
+    // Ranges are multiples of 8 packets and tiles of 512, so `ok` is uniform over every 8-lane
+    // group (NOT over the warp): the shuffles inside quantize16 use a per-group mask.
     // phase 0: quantise own input into own arena
-    // ranges are multiples of 32 packets, so `ok` is uniform across a warp and the shuffles inside
-    // quantize4 always see complete warps
-    for_owned_packets<1>(0, n_pack_pad, [&](const uint64_t(&v)[1], const bool(&ok)[1]) {
+    for_owned_packets<1>(0, n_pack, [&](const uint64_t(&v)[1], const bool(&ok)[1]) {
         if (!ok[0]) return;
-        float x[4];
-        const int valid = load4(v[0], x);
-        const uint32_t packed = quantize4<ALGO>(x, valid, metas(a.rank) + (v[0] / 32) * MB, lane);
+        float x[16];
+        const int valid = load16(v[0], x);
+        uint32_t lo, hi;
+        const uint4 packed = quantize16<ALGO>(x, valid, lo, hi);
         codes(a.rank)[v[0]] = packed;
+        store_record(a.rank, v[0], lo, hi);
     });
     if (!peer_barrier(a, tbl, a.flag_base + 1)) return;
 
     // phase 1: dequantise + reduce own chunk in fp32, re-quantise once, adopt the decoded value
     {
-        const uint64_t lo = min(uint64_t(a.rank) * per, n_pack_pad), hi = min(lo + per, n_pack_pad);
-        for_owned_packets<1>(lo, hi, [&](const uint64_t(&v)[1], const bool(&ok)[1]) {
+        const uint64_t lo_p = min(uint64_t(a.rank) * per, n_pack), hi_p = min(lo_p + per, n_pack);
+        for_owned_packets<1>(lo_p, hi_p, [&](const uint64_t(&v)[1], const bool(&ok)[1]) {
             if (!ok[0]) return;
-            float acc[4];
+            float acc[16];
             for (uint32_t r0 = 0; r0 < a.world; r0 += kPeerGroup) {
-                uint32_t raw[kPeerGroup], mlo[kPeerGroup], mhi[kPeerGroup];
+                uint4 raw[kPeerGroup];
+                uint32_t mlo[kPeerGroup], mhi[kPeerGroup];
 #pragma unroll
                 for (int g = 0; g < kPeerGroup; ++g)
                     if (r0 + g < a.world) {
-                        raw[g] = ld_peer_4(codes(r0 + g) + v[0]);
-                        if constexpr (MB == 8) {
-                            const uint2 m = ld_peer_8(metas(r0 + g) + (v[0] / 32) * MB);
-                            mlo[g] = m.x, mhi[g] = m.y;
-                        } else {
-                            mlo[g] = ld_peer_4(metas(r0 + g) + (v[0] / 32) * MB), mhi[g] = 0;
-                        }
+                        raw[g] = ld_peer_16(codes(r0 + g) + v[0]);
+                        load_record(r0 + g, v[0], mlo[g], mhi[g]);
                     }
 #pragma unroll
                 for (int g = 0; g < kPeerGroup; ++g)
                     if (r0 + g < a.world) {
-                        float x[4];
-                        dequantize4<ALGO>(raw[g], mlo[g], mhi[g], x);
+                        float x[16];
+                        dequantize16<ALGO>(raw[g], mlo[g], mhi[g], x);
 #pragma unroll
-                        for (int i = 0; i < 4; ++i) acc[i] = r0 + g == 0 ? x[i] : combine<OP>(acc[i], x[i]);
+                        for (int i = 0; i < 16; ++i) acc[i] = r0 + g == 0 ? x[i] : combine<OP>(acc[i], x[i]);
                     }
             }
             if (a.avg_divisor)
 #pragma unroll
-                for (int i = 0; i < 4; ++i) acc[i] = acc[i] / static_cast<float>(a.avg_divisor);
-            const uint64_t e = v[0] * 4;
-            const int valid = e >= a.count ? 0 : (a.count - e >= 4 ? 4 : static_cast<int>(a.count - e));
-            uint8_t *my_meta = metas(a.rank) + (v[0] / 32) * MB;
-            const uint32_t packed = quantize4<ALGO>(acc, valid, my_meta, lane);
+                for (int i = 0; i < 16; ++i) acc[i] = acc[i] / static_cast<float>(a.avg_divisor);
+            uint32_t lo, hi;
+            const uint4 packed = quantize16<ALGO>(acc, valid_of(v[0]), lo, hi);
             codes(a.rank)[v[0]] = packed;
-            // the owner keeps exactly what the others will decode
-            float2 rec;
-            if constexpr (MB == 8) {
-                float mn = 3.402823466e+38f, mx = -3.402823466e+38f;
-#pragma unroll
-                for (int i = 0; i < 4; ++i)
-                    if (i < valid) mn = fminf(mn, acc[i]), mx = fmaxf(mx, acc[i]);
-                rec = make_float2(warp_min(mn), warp_max(mx));
-            } else {
-                float amax = 0.0f;
-#pragma unroll
-                for (int i = 0; i < 4; ++i)
-                    if (i < valid) amax = fmaxf(amax, fabsf(acc[i]));
-                amax = warp_max(amax);
-                rec = make_float2(amax > 0.0f ? amax / 448.0f : 1.0f, 0.0f);
-            }
-            float y[4];
-            dequantize4<ALGO>(packed, __float_as_uint(rec.x), __float_as_uint(rec.y), y);
-            if (valid > 0) {
-                uint4 out = make_uint4(__float_as_uint(y[0]), __float_as_uint(y[1]), __float_as_uint(y[2]), __float_as_uint(y[3]));
-                store_output(dst, v[0], a.count, dst_aligned, out);
-            }
+            store_record(a.rank, v[0], lo, hi);
+            float y[16]; // the owner keeps exactly what the others will decode
+            dequantize16<ALGO>(packed, lo, hi, y);
+            store16(v[0], y);
         });
     }
     if (!peer_barrier(a, tbl, a.flag_base + 2)) return;
@@ -385,28 +405,23 @@ template <int ALGO, int OP> __global__ void __launch_bounds__(kThreads, 1) allre
     // phase 2: fetch the other chunks as codes, decode into the output
     for (uint32_t k = 1; k < a.world; ++k) {
         const uint32_t peer = (a.rank + k) % a.world;
-        const uint64_t lo = min(uint64_t(peer) * per, n_pack_pad), hi = min(lo + per, n_pack_pad);
-        for_owned_packets<4>(lo, hi, [&](const uint64_t(&v)[4], const bool(&ok)[4]) {
-            uint32_t raw[4], mlo[4], mhi[4];
+        const uint64_t lo_p = min(uint64_t(peer) * per, n_pack), hi_p = min(lo_p + per, n_pack);
+        for_owned_packets<2>(lo_p, hi_p, [&](const uint64_t(&v)[2], const bool(&ok)[2]) {
+            uint4 raw[2];
+            uint32_t mlo[2], mhi[2];
 #pragma unroll
-            for (int u = 0; u < 4; ++u) {
-                if (!ok[u] || v[u] >= n_pack) continue;
-                raw[u] = ld_peer_4(codes(peer) + v[u]);
-                if constexpr (MB == 8) {
-                    const uint2 m = ld_peer_8(metas(peer) + (v[u] / 32) * MB);
-                    mlo[u] = m.x, mhi[u] = m.y;
-                } else {
-                    mlo[u] = ld_peer_4(metas(peer) + (v[u] / 32) * MB), mhi[u] = 0;
+            for (int u = 0; u < 2; ++u)
+                if (ok[u]) {
+                    raw[u] = ld_peer_16(codes(peer) + v[u]);
+                    load_record(peer, v[u], mlo[u], mhi[u]);
                 }
-            }
 #pragma unroll
-            for (int u = 0; u < 4; ++u) {
-                if (!ok[u] || v[u] >= n_pack) continue;
-                float y[4];
-                dequantize4<ALGO>(raw[u], mlo[u], mhi[u], y);
-                uint4 out = make_uint4(__float_as_uint(y[0]), __float_as_uint(y[1]), __float_as_uint(y[2]), __float_as_uint(y[3]));
-                store_output(dst, v[u], a.count, dst_aligned, out);
-            }
+            for (int u = 0; u < 2; ++u)
+                if (ok[u]) {
+                    float y[16];
+                    dequantize16<ALGO>(raw[u], mlo[u], mhi[u], y);
+                    store16(v[u], y);
+                }
         });
     }
     peer_barrier(a, tbl, a.flag_base + 3);
@@ -420,9 +435,9 @@ extern "C" size_t pcclKernelP2PControlBytes(void) { return kControlBytes; }
 
 extern "C" size_t pcclKernelP2PStagingBytes(uint64_t count, int dtype, int quant_algorithm) {
     if (quant_algorithm == QUANT_BLOCK_MINMAX || quant_algorithm == QUANT_BLOCK_FP8) {
-        const uint64_t n_pack_pad = ((count + 3) / 4 + 31) / 32 * 32;
+        const uint64_t n_blocks = (count + PCCL_K_QUANT_BLOCK - 1) / PCCL_K_QUANT_BLOCK;
         const uint64_t mb = quant_algorithm == QUANT_BLOCK_MINMAX ? 8 : 4;
-        return n_pack_pad * 4 + (n_pack_pad / 32) * mb + 256;
+        return n_blocks * PCCL_K_QUANT_BLOCK + n_blocks * mb + 256;
     }
     const size_t esz = pcclExtDataTypeSize(static_cast<pcclDataType_t>(dtype));
     return (count * esz + 15) / 16 * 16 + 256;
@@ -471,8 +486,9 @@ extern "C" int pcclKernelAllReduceP2P(const pcclKernelP2PArgs_t *args, int *algo
 
     bool launched = false;
     if (quantised) {
-        // per-chunk tiles: work is spread over the chunk of one rank in phase 1
-        const uint64_t chunk_tiles = (tiles + args->world - 1) / args->world;
+        // per-chunk tiles (a tile = 512 threads x 16 values): work is spread over the chunk of one rank in phase 1
+        const uint64_t q_tiles = (args->count + uint64_t(kThreads) * 16 - 1) / (uint64_t(kThreads) * 16);
+        const uint64_t chunk_tiles = (q_tiles + args->world - 1) / args->world;
         const int grid = static_cast<int>(std::max<uint64_t>(1, std::min<uint64_t>(max_blocks, chunk_tiles)));
         dispatch_op(kop, [&](auto op_tag) {
             constexpr int OP = decltype(op_tag)::value;

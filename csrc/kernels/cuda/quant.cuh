@@ -91,4 +91,73 @@ template <int ALGO> __device__ __forceinline__ void dequantize4(uint32_t packed,
     }
 }
 
+
+// ---- 16 elements per thread, 8 lanes per block -------------------------------------------------
+// Used by the fused all-reduce: one 16-byte code packet per thread keeps the peer loads wide, and
+// the block statistics need 3 shuffle steps per 16 elements instead of 5 per 4.
+// Only the 8 lanes of the caller's group take part (other groups of the warp may have left
+// because their packets lie beyond the end of the buffer), so the mask names exactly that group.
+__device__ __forceinline__ uint32_t group8_mask() { return 0xffu << ((threadIdx.x & 31u) & ~7u); }
+__device__ __forceinline__ float group8_min(float v) {
+    const uint32_t mask = group8_mask();
+#pragma unroll
+    for (int o = 4; o > 0; o >>= 1) v = fminf(v, __shfl_xor_sync(mask, v, o));
+    return v;
+}
+__device__ __forceinline__ float group8_max(float v) {
+    const uint32_t mask = group8_mask();
+#pragma unroll
+    for (int o = 4; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(mask, v, o));
+    return v;
+}
+
+// `valid` = how many of the 16 values exist.  All 8 lanes of a group must call together.
+// Returns the block record in (rec_lo, rec_hi) on every lane of the group.
+template <int ALGO>
+__device__ __forceinline__ uint4 quantize16(const float (&x)[16], int valid, uint32_t &rec_lo, uint32_t &rec_hi) {
+    uint32_t w[4] = {0, 0, 0, 0};
+    if constexpr (ALGO == QUANT_BLOCK_MINMAX) {
+        float mn = 3.402823466e+38f, mx = -3.402823466e+38f;
+#pragma unroll
+        for (int i = 0; i < 16; ++i)
+            if (i < valid) {
+                mn = fminf(mn, x[i]);
+                mx = fmaxf(mx, x[i]);
+            }
+        mn = group8_min(mn);
+        mx = group8_max(mx);
+        rec_lo = __float_as_uint(mn), rec_hi = __float_as_uint(mx);
+        const float inv = mx > mn ? 255.0f / (mx - mn) : 0.0f;
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+            const float r = rintf((x[i] - mn) * inv);
+            const uint32_t c = i < valid ? static_cast<uint32_t>(fminf(255.0f, fmaxf(0.0f, r))) : 0u;
+            w[i >> 2] |= c << (8 * (i & 3));
+        }
+    } else {
+        float amax = 0.0f;
+#pragma unroll
+        for (int i = 0; i < 16; ++i)
+            if (i < valid) amax = fmaxf(amax, fabsf(x[i]));
+        amax = group8_max(amax);
+        const float scale = amax > 0.0f ? amax / 448.0f : 1.0f;
+        rec_lo = __float_as_uint(scale), rec_hi = 0;
+        const float inv = 1.0f / scale;
+#pragma unroll
+        for (int i = 0; i < 16; ++i) w[i >> 2] |= (i < valid ? fp8_encode(x[i] * inv) : 0u) << (8 * (i & 3));
+    }
+    return make_uint4(w[0], w[1], w[2], w[3]);
+}
+
+template <int ALGO> __device__ __forceinline__ void dequantize16(uint4 packed, uint32_t rec_lo, uint32_t rec_hi, float (&out)[16]) {
+    const uint32_t w[4] = {packed.x, packed.y, packed.z, packed.w};
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        float y[4];
+        dequantize4<ALGO>(w[j], rec_lo, rec_hi, y);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) out[4 * j + i] = y[i];
+    }
+}
+
 } // namespace pccl::cuda

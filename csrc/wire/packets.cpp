@@ -411,6 +411,49 @@ bool S2CSharedStateResponse::read(Reader &r) {
     return r.ok();
 }
 
+void C2SRequestSharedStateP2P::write(Writer &w) const {
+    put_uuid(w, requester);
+    w.put<uint64_t>(keys.size());
+    for (const auto &k : keys) w.put_string(k);
+}
+bool C2SRequestSharedStateP2P::read(Reader &r) {
+    requester = get_uuid(r);
+    const uint64_t n = r.get<uint64_t>();
+    if (!r.plausible_count(n, 8)) return false;
+    keys.clear();
+    for (uint64_t i = 0; i < n && r.ok(); ++i) keys.push_back(r.get_string());
+    return r.ok();
+}
+void S2CSharedStateResponseP2P::write(Writer &w) const {
+    w.put<uint8_t>(static_cast<uint8_t>(status));
+    w.put<uint64_t>(revision);
+    w.put<bool>(p2p);
+    put_uuid(w, distributor);
+    w.put<uint64_t>(chunk_bytes);
+    w.put<uint64_t>(entries.size());
+    for (const auto &e : entries) {
+        w.put_string(e.key);
+        w.put<uint64_t>(e.size_bytes);
+    }
+}
+bool S2CSharedStateResponseP2P::read(Reader &r) {
+    status = static_cast<SharedStateStatus>(r.get<uint8_t>());
+    revision = r.get<uint64_t>();
+    p2p = r.get<bool>();
+    distributor = get_uuid(r);
+    chunk_bytes = r.get<uint64_t>();
+    const uint64_t n = r.get<uint64_t>();
+    if (!r.plausible_count(n, 16)) return false;
+    entries.clear();
+    for (uint64_t i = 0; i < n && r.ok(); ++i) {
+        SharedStateSlice s;
+        s.key = r.get_string();
+        s.size_bytes = r.get<uint64_t>();
+        entries.push_back(std::move(s));
+    }
+    return r.ok();
+}
+
 // ---- benchmark
 void C2BHello::write(Writer &w) const { put_uuid(w, uuid); }
 bool C2BHello::read(Reader &r) {

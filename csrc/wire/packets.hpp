@@ -210,6 +210,31 @@ struct S2CSharedStateResponse {
     std::vector<SharedStateSlice> entries; // raw tensor bytes follow the frame, in this order
 };
 
+// Extension (ids >= 2 do not exist in the reference): shared state over NVLink.  The requester
+// names itself; a distributor that has the requester's arena mapped answers with p2p = true and
+// then announces every staged chunk with S2CChunkReady, the requester copies it out of the
+// distributor's arena and answers C2SChunkAck.  Otherwise raw bytes follow as in the base protocol.
+struct C2SRequestSharedStateP2P {
+    PCCL_PACKET(2)
+    Uuid requester;
+    std::vector<std::string> keys;
+};
+struct S2CSharedStateResponseP2P {
+    PCCL_PACKET(2)
+    SharedStateStatus status = SharedStateStatus::Success;
+    uint64_t revision = 0;
+    bool p2p = false;
+    Uuid distributor;
+    uint64_t chunk_bytes = 0;
+    std::vector<SharedStateSlice> entries;
+};
+struct S2CChunkReady {
+    PCCL_EMPTY_PACKET(3)
+};
+struct C2SChunkAck {
+    PCCL_EMPTY_PACKET(3)
+};
+
 // ---------------------------------------------------------------- bandwidth benchmark
 struct C2BHello {
     PCCL_PACKET(1)

@@ -147,7 +147,7 @@ def local_all_reduce(src: torch.Tensor, dst: torch.Tensor, arena: LocalArena, op
     args.src_in_arena = 0
     args.abort_flag = arena.words.data_ptr()
     args.status = arena.words.data_ptr() + 4
-    args.timeout_cycles = 20_000_000_000
+    args.timeout_cycles = 4_000_000_000  # ~2 s: a lost peer or a kernel bug fails fast
     ran = C.c_int()
     with torch.cuda.device(src.device):
         _check(lib().pcclKernelAllReduceP2P(C.byref(args), C.byref(ran), _stream_ptr(src)), "pcclKernelAllReduceP2P")
