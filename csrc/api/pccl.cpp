@@ -4,6 +4,7 @@
 #include "pccl.h"
 
 #include <atomic>
+#include <cstdlib>
 #include <cstring>
 #include <memory>
 #include <unordered_set>
@@ -255,6 +256,84 @@ pcclResult_t pcclAllReduce(const void *sendbuff, void *recvbuff, const pcclReduc
     return out.ok ? pcclSuccess : pcclRankConnectionLost;
 }
 
+// Many small reductions with the same element type and operator (the per-parameter pattern of the
+// reference's DiLoCo example, sync_diloco.py:500-505) are fused: gathered into one buffer, reduced
+// by ONE operation, scattered back.  Every peer passes the same descriptor list, so every peer
+// takes the same decision.  Returns pcclInternalError when the list does not qualify (the caller
+// then runs the general scheduler).  PCCL_FUSE_MULTIPLE=0 switches this off.
+static pcclResult_t try_fused_multiple(const pcclReduceOpDescriptor_t *descriptors, size_t count, const pcclComm_t *c,
+                                       pcclReduceInfo_t *info_out) {
+    static const bool enabled = [] {
+        const char *v = std::getenv("PCCL_FUSE_MULTIPLE");
+        return !(v && v[0] == '0');
+    }();
+    if (!enabled || count < 2) return pcclInternalError;
+    const pcclReduceDescriptor_t &first = descriptors[0].descriptor;
+    wire::DType dtype;
+    if (!to_wire_dtype(first.src_descriptor.datatype, dtype) || dtype == wire::DType::F8E4M3) return pcclInternalError;
+    const size_t esz = wire::dtype_size(dtype);
+    size_t total_bytes = 0;
+    bool any_device = false, any_host = false;
+    for (size_t i = 0; i < count; ++i) {
+        const auto &d = descriptors[i];
+        if (!d.sendbuf || !d.recvbuf || d.descriptor.count == 0) return pcclInvalidArgument;
+        if (d.descriptor.src_descriptor.datatype != first.src_descriptor.datatype || d.descriptor.op != first.op ||
+            d.descriptor.quantization_options.algorithm != pcclQuantNone)
+            return pcclInternalError;
+        (device::classify_pointer(d.sendbuf).is_device ? any_device : any_host) = true;
+        (device::classify_pointer(d.recvbuf).is_device ? any_device : any_host) = true;
+        total_bytes += (d.descriptor.count * esz + 15) / 16 * 16;
+    }
+    if (any_device == any_host || total_bytes > (size_t(1) << 30)) return pcclInternalError;
+    device::Plane &plane = c->client->plane();
+    std::vector<uint8_t> host_fused;
+    uint8_t *fused = nullptr;
+    std::vector<device::Plane::Part> in_parts, out_parts;
+    for (size_t i = 0; i < count; ++i) {
+        in_parts.push_back({descriptors[i].sendbuf, descriptors[i].descriptor.count * esz});
+        out_parts.push_back({descriptors[i].recvbuf, descriptors[i].descriptor.count * esz});
+    }
+    if (any_device) {
+        fused = static_cast<uint8_t *>(plane.fuse_buffer(total_bytes));
+        if (!fused || !plane.gather(in_parts, fused, true)) return pcclInternalError;
+    } else {
+        host_fused.resize(total_bytes);
+        fused = host_fused.data();
+        size_t off = 0;
+        for (const auto &p : in_parts) {
+            std::memcpy(fused + off, p.ptr, p.bytes);
+            off += (p.bytes + 15) / 16 * 16;
+        }
+    }
+    // padding between the parts is reduced too; its contents are irrelevant but must be defined
+    pcclReduceDescriptor_t desc = first;
+    desc.count = total_bytes / esz;
+    client::ReduceRequest req;
+    if (const pcclResult_t rc = build_request(fused, fused, &desc, req); rc != pcclSuccess) return rc;
+    client::ReduceOutcome out;
+    for (;;) {
+        if (c->client->local_world() < 2) {
+            if (info_out) *info_out = {static_cast<uint32_t>(c->client->local_world()), 0, 0};
+            return pcclTooFewPeers;
+        }
+        const auto launch = c->client->all_reduce_sync(req, out);
+        if (launch == client::Client::Launch::NotConnected) return pcclInvalidUsage;
+        if (launch == client::Client::Launch::DuplicateTag) return pcclInvalidArgument;
+        if (out.ok) break; // a failed in-place attempt leaves the fused input intact: just go again
+    }
+    if (any_device) {
+        if (!plane.gather(out_parts, fused, false)) return pcclInternalError;
+    } else {
+        size_t off = 0;
+        for (const auto &p : out_parts) {
+            std::memcpy(p.ptr, fused + off, p.bytes);
+            off += (p.bytes + 15) / 16 * 16;
+        }
+    }
+    if (info_out) *info_out = {out.world, out.tx_bytes, out.rx_bytes};
+    return pcclSuccess;
+}
+
 // Scheduler: keep up to max_in_flight reductions running; when any fails, drain everything
 // that is in flight (they share the broken ring) and start the unfinished ones again on the
 // new ring.  Ends when all are done or the group shrank below two peers.
@@ -263,6 +342,7 @@ pcclResult_t pcclAllReduceMultipleWithRetry(const pcclReduceOpDescriptor_t *desc
     PCCL_REQUIRE_INIT();
     PCCL_REQUIRE(descriptors && count > 0 && c && max_in_flight > 0, pcclInvalidArgument);
     PCCL_REQUIRE(c->client, pcclInvalidUsage);
+    if (const pcclResult_t fused = try_fused_multiple(descriptors, count, c, info_out); fused != pcclInternalError) return fused;
     std::vector<bool> done(count, false);
     size_t n_done = 0;
     uint64_t tx = 0, rx = 0;

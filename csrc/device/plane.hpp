@@ -109,6 +109,15 @@ public:
     virtual bool export_chunk(const void *src, bool src_on_device, size_t bytes) = 0;
     virtual bool import_chunk(const Uuid &from, void *dst, bool dst_on_device, size_t bytes) = 0;
 
+    // Fusing many small reductions into one: a reusable device buffer (from the symmetric heap when
+    // it fits, so the fused reduction needs no staging) and batched device-to-device copies.
+    struct Part {
+        void *ptr;
+        size_t bytes;
+    };
+    virtual void *fuse_buffer(size_t bytes) = 0;
+    virtual bool gather(const std::vector<Part> &parts, void *fused, bool into_fused) = 0;
+
     // Page-locked host memory for staging (plain malloc when there is no GPU).
     virtual void *host_alloc(size_t bytes) = 0;
     virtual void host_free(void *ptr) = 0;

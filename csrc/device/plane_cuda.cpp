@@ -518,6 +518,54 @@ public:
         return rc == 0;
     }
 
+    void *fuse_buffer(size_t bytes) override {
+        if (!usable_) return nullptr;
+        cudaSetDevice(device_);
+        std::lock_guard<std::mutex> lock(fuse_mu_);
+        if (fuse_ptr_ && fuse_bytes_ >= bytes) return fuse_ptr_;
+        if (fuse_ptr_ && !fuse_symmetric_) cudaFree(fuse_ptr_);
+        if (fuse_ptr_ && fuse_symmetric_) symmetric_free(fuse_ptr_);
+        fuse_ptr_ = nullptr;
+        fuse_bytes_ = 0;
+        // grow generously: parameter lists do not change from step to step
+        const size_t want = round_up(bytes + bytes / 8, 2u << 20);
+        if (void *p = symmetric_alloc(want)) {
+            fuse_ptr_ = p;
+            fuse_symmetric_ = true;
+        } else if (cudaMalloc(&fuse_ptr_, want) == cudaSuccess) {
+            fuse_symmetric_ = false;
+        } else {
+            (void) cudaGetLastError();
+            fuse_ptr_ = nullptr;
+            return nullptr;
+        }
+        fuse_bytes_ = want;
+        return fuse_ptr_;
+    }
+
+    bool gather(const std::vector<Part> &parts, void *fused, bool into_fused) override {
+        if (!usable_) return false;
+        cudaSetDevice(device_);
+        std::lock_guard<std::mutex> lock(copy_mu_);
+        if (!util_stream_) RT_TRY(cudaStreamCreateWithFlags(&util_stream_, cudaStreamNonBlocking));
+        cudaEvent_t ready;
+        RT_TRY(cudaEventCreateWithFlags(&ready, cudaEventDisableTiming));
+        cudaEventRecord(ready, cudaStreamLegacy);
+        cudaStreamWaitEvent(util_stream_, ready, 0);
+        cudaEventDestroy(ready);
+        auto *base = static_cast<uint8_t *>(fused);
+        size_t off = 0;
+        for (const Part &p : parts) {
+            if (into_fused)
+                RT_TRY(cudaMemcpyAsync(base + off, p.ptr, p.bytes, cudaMemcpyDeviceToDevice, util_stream_));
+            else
+                RT_TRY(cudaMemcpyAsync(p.ptr, base + off, p.bytes, cudaMemcpyDeviceToDevice, util_stream_));
+            off += round_up(p.bytes, 16);
+        }
+        RT_TRY(cudaStreamSynchronize(util_stream_));
+        return true;
+    }
+
     bool peer_mapped(const Uuid &peer) override {
         std::lock_guard<std::mutex> lock(mu_);
         return ring_ready_ && peers_.count(peer) > 0;
@@ -1030,6 +1078,11 @@ private:
 
     std::mutex copy_mu_;
     cudaStream_t util_stream_ = nullptr;
+
+    std::mutex fuse_mu_;
+    void *fuse_ptr_ = nullptr;
+    size_t fuse_bytes_ = 0;
+    bool fuse_symmetric_ = false;
 };
 
 } // namespace

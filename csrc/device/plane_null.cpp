@@ -22,6 +22,8 @@ public:
     bool copy_to_host(void *, const void *, size_t) override { return false; }
     bool copy_to_device(void *, const void *, size_t) override { return false; }
     bool hash_device(const void *, size_t, wire::HashType, uint64_t &) override { return false; }
+    void *fuse_buffer(size_t) override { return nullptr; }
+    bool gather(const std::vector<Part> &, void *, bool) override { return false; }
     bool peer_mapped(const Uuid &) override { return false; }
     size_t exchange_bytes() override { return 0; }
     std::unique_lock<std::mutex> exchange_lock() override { return std::unique_lock<std::mutex>(mu_); }

@@ -117,6 +117,25 @@ def main():
         wb = expected(102, world, n, torch.float32, pccl.ReduceOp.MAX)
         ok_all = ok1 and ok2 and torch.allclose(ra.cpu(), wa, rtol=1e-5, atol=1e-5) and torch.equal(rb.cpu(), wb)
         results["cases"].append({"id": "concurrent", "ok": bool(ok_all), "plane": comm.ext_last_reduce_stats(1)["plane"]})
+    elif scenario == "multiple":
+        # the per-parameter pattern: many tensors of very different sizes in one call
+        sizes = [7, 768, 768 * 4, 50_000, 1, 2_359_296, 3 * 768, 590_000, 13, 768] * 3
+        tensors = [make_input(300 + k, rank, n, torch.float32).to(dev) for k, n in enumerate(sizes)]
+        descs = []
+        for k, t in enumerate(tensors):
+            d = pccl.ReduceDescriptor(t.numel(), pccl.ReduceOp.AVG, k, pccl.ReduceOperandDescriptor(pccl.DataType.FLOAT))
+            descs.append(pccl.ReduceOpDescriptor.from_torch(t, t, d))
+        t0 = time.perf_counter()
+        info = comm.all_reduce_multiple_with_retry(descs, max_in_flight=8)
+        if dev.type == "cuda":
+            torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        ok_all = info.world_size == world
+        for k, (t, n) in enumerate(zip(tensors, sizes)):
+            want = expected(300 + k, world, n, torch.float32, pccl.ReduceOp.AVG)
+            ok_all = ok_all and torch.allclose(t.cpu(), want, rtol=1e-5, atol=1e-5)
+        results["cases"].append({"id": "multiple", "ok": bool(ok_all), "ms": round(dt * 1e3, 3), "tensors": len(sizes),
+                                 "plane": comm.ext_last_reduce_stats(0)["plane"]})
     elif scenario == "shared_state":
         # rank 0 holds the truth; the others start from garbage and must end up identical
         n = 5_000_003

@@ -63,6 +63,13 @@ def test_concurrent_tags_over_nvlink(world):
         assert r["ok"]
 
 
+@pytest.mark.parametrize("world", worlds()[:1] or [pytest.param(2, marks=pytest.mark.skip(reason="needs >= 2 GPUs"))])
+def test_many_small_tensors_are_fused(world):
+    for r in run_peers(world, "multiple"):
+        assert r["ok"], r
+        assert r["cases"][0]["plane"].startswith("p2p") or r["cases"][0]["plane"] == "nvls"
+
+
 @pytest.mark.parametrize("world", worlds()[:2] or [pytest.param(2, marks=pytest.mark.skip(reason="needs >= 2 GPUs"))])
 def test_shared_state_device_tensors(world):
     for r in run_peers(world, "shared_state"):
