@@ -33,11 +33,12 @@ sym = comm.ext_symmetric_empty(n, torch.float32)
 sym.normal_()
 reg = torch.randn(n, device=dev)
 out = torch.empty_like(reg)
-configs = [(v, b) for v in (1, 2, 3, 4) for b in (96, 144, 216)]
+configs = [(1, 144, 64)] + [(1, b, seg) for b in (72, 144) for seg in (32, 64, 128, 256)]
 for buffers in ("symmetric", "regular"):
-    for variant, blocks in configs:
+    for variant, blocks, seg in (configs[:1] if buffers == "symmetric" else configs):
         os.environ["PCCL_DEVICE_VARIANT"] = str(variant)
         os.environ["PCCL_DEVICE_MAX_BLOCKS"] = str(blocks)
+        os.environ["PCCL_PIPELINE_SEGMENT_MB"] = str(seg)
         ms = []
         for it in range(8):
             if buffers == "symmetric":
@@ -50,7 +51,7 @@ for buffers in ("symmetric", "regular"):
         t = torch.tensor([sum(ms) / len(ms)], device=dev, dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         if rank == 0:
-            print(json.dumps({"buffers": buffers, "variant": variant, "blocks": blocks, "plane": st["plane"], "kernel_ms": round(float(t.item()), 4),
+            print(json.dumps({"buffers": buffers, "variant": variant, "blocks": blocks, "segment_mb": seg, "plane": st["plane"], "kernel_ms": round(float(t.item()), 4),
                               "bus_GBps": round(n * 4 * 2 * (world - 1) / world / float(t.item()) / 1e6, 1)}), flush=True)
     if buffers == "symmetric" and world < 4:
         pass
