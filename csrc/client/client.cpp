@@ -530,25 +530,30 @@ bool Client::sync_shared_state(SharedStateArgs &state, uint64_t &tx_bytes, uint6
     if (any_reduce_running()) return false;
     drain_deferred();
 
+    // simplehash, like the reference (ccoip_client_handler.cpp:391-394); PCCL_SHARED_STATE_HASH=crc32 switches
+    // the whole run to CRC32C (all peers must agree, the master compares the hash type too)
+    static const HashType hash_type = [] {
+        const char *v = std::getenv("PCCL_SHARED_STATE_HASH");
+        return v && (std::string(v) == "crc32" || std::string(v) == "crc32c") ? HashType::Crc32 : HashType::Simple;
+    }();
+    auto hash_of = [&](const SharedEntry &e, uint64_t &out) {
+        if (e.on_device) return plane_->hash_device(e.data, e.bytes(), hash_type, out);
+        out = hash_type == HashType::Simple ? cpu::simplehash(e.data, e.bytes()) : cpu::crc32c(e.data, e.bytes());
+        return true;
+    };
     C2MSyncSharedState vote;
     vote.revision = state.revision;
     vote.strategy = state.strategy;
     for (const auto &e : state.entries) {
         SharedStateEntry w;
         w.key = e.key;
-        w.hash_type = HashType::Simple;
+        w.hash_type = hash_type;
         w.num_elements = e.count;
         w.dtype = e.dtype;
         w.allow_content_inequality = e.allow_content_inequality;
-        if (!e.allow_content_inequality) {
-            if (e.on_device) {
-                if (!plane_->hash_device(e.data, e.bytes(), HashType::Simple, w.hash)) {
-                    PLOG(ERR) << "cannot hash device tensor '" << e.key << "'";
-                    return false;
-                }
-            } else {
-                w.hash = cpu::simplehash(e.data, e.bytes());
-            }
+        if (!e.allow_content_inequality && !hash_of(e, w.hash)) {
+            PLOG(ERR) << "cannot hash tensor '" << e.key << "'";
+            return false;
         }
         vote.entries.push_back(std::move(w));
     }
@@ -651,11 +656,7 @@ bool Client::sync_shared_state(SharedStateArgs &state, uint64_t &tx_bytes, uint6
             // verify what arrived against what the master elected
             if (!it->allow_content_inequality && i < verdict->expected_hashes.size()) {
                 uint64_t h = 0;
-                if (it->on_device) {
-                    if (!plane_->hash_device(it->data, it->bytes(), HashType::Simple, h)) return false;
-                } else {
-                    h = cpu::simplehash(it->data, it->bytes());
-                }
+                if (!hash_of(*it, h)) return false;
                 if (h != verdict->expected_hashes[i]) {
                     PLOG(ERR) << "shared-state tensor '" << slice.key << "' does not match the elected hash after transfer";
                     return false;
