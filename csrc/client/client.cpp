@@ -268,6 +268,7 @@ Client::Establish Client::establish_round() {
         ring_ = verdict->ring_order;
     }
     local_world_ = verdict->ring_order.size();
+    ring_stale_ = false;
     plane_->on_ring_changed(verdict->ring_order);
     return Establish::Success;
 }
@@ -770,7 +771,10 @@ bool Client::drain_deferred() {
         pending.swap(deferred_);
     }
     bool ok = true;
-    for (auto &[tag, d] : pending) ok = finish_deferred(tag, d) && ok;
+    for (auto &[tag, d] : pending) {
+        ok = finish_deferred(tag, d) && ok;
+        if (d.aborted) ring_stale_ = true;
+    }
     return ok;
 }
 
@@ -846,6 +850,27 @@ ReduceOutcome Client::run_reduce(const ReduceRequest &req, uint64_t) {
     bool have_prev = false;
     {
         std::lock_guard<std::mutex> lock(deferred_mu_);
+        // Handshakes of OTHER tags whose answers have arrived in the meantime are retired on the
+        // way (programs that use a fresh tag for every operation would otherwise pile them up).
+        for (auto it = deferred_.begin(); it != deferred_.end();) {
+            Deferred &d = it->second;
+            const uint64_t tag = it->first;
+            if (tag != req.tag) {
+                if (!d.abort_seen) {
+                    if (const auto pkt = master_.recv_matching<M2CCollectiveAbort>([&](const M2CCollectiveAbort &p) { return p.tag == tag; }, true)) {
+                        d.abort_seen = true;
+                        d.aborted = pkt->aborted;
+                    }
+                }
+                if (d.abort_seen &&
+                    master_.recv_matching<M2CCollectiveComplete>([&](const M2CCollectiveComplete &p) { return p.tag == tag; }, true)) {
+                    if (d.aborted) ring_stale_ = true;
+                    it = deferred_.erase(it);
+                    continue;
+                }
+            }
+            ++it;
+        }
         const auto it = deferred_.find(req.tag);
         if (it != deferred_.end()) {
             prev = it->second;
@@ -860,7 +885,8 @@ ReduceOutcome Client::run_reduce(const ReduceRequest &req, uint64_t) {
     if (!go) return out;
     // the earlier operation finished here, but a peer vanished before everybody had voted: the
     // ring this peer knows is stale, so this operation is reported as failed without running
-    const bool poisoned = have_prev && prev.aborted;
+    if (have_prev && prev.aborted) ring_stale_ = true;
+    const bool poisoned = ring_stale_.load();
     const bool use_device = (go->seq_nr >> 63) != 0;
     const bool use_nvls = use_device && ((go->seq_nr >> 62) & 1) != 0;
     const uint64_t seq = go->seq_nr & ~(3ull << 62);

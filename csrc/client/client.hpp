@@ -160,6 +160,7 @@ private:
     std::map<uint64_t, StageBuf> stage_cache_;
     std::mutex deferred_mu_;
     std::map<uint64_t, Deferred> deferred_;
+    std::atomic<bool> ring_stale_{false};       // a peer vanished after an operation had finished here: rewire before the next one
     std::atomic<bool> master_pipelines_{false}; // the master queues an Initiate behind a pending Complete
     std::mutex ops_mu_;
     std::map<uint64_t, Op> ops_;
