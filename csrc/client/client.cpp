@@ -205,6 +205,7 @@ bool Client::dial_peer(const PeerEndpoint &peer) {
 Client::Establish Client::establish_round() {
     const auto info = master_.recv_packet<M2CP2PConnectionInfo>();
     if (!info) return Establish::Failed;
+    PLOG(DEBUG) << "connection info: " << info->peers.size() << " neighbours, unchanged=" << info->unchanged;
     global_world_ = info->global_world_size;
     local_world_ = info->local_world_size;
     num_groups_ = info->num_peer_groups;
@@ -258,8 +259,10 @@ Client::Establish Client::establish_round() {
             }
         }
     }
+    PLOG(DEBUG) << "p2p links " << (report.success ? "established" : "FAILED") << ", reporting to the master";
     if (!master_.send_packet(report)) return Establish::Failed;
     const auto verdict = master_.recv_packet<M2CP2PEstablished>();
+    PLOG(DEBUG) << "master verdict on p2p establishment received";
     if (!verdict) return Establish::Failed;
     if (!report.success && verdict->success) return Establish::Failed;
     if (!verdict->success) return Establish::Retry;
@@ -742,6 +745,7 @@ bool Client::conclude(uint64_t tag, uint64_t revision_at_launch, ReduceOutcome &
         others_running = !ops_.empty();
     }
     if (!out.ok) {
+        PLOG(DEBUG) << "reduction on tag " << tag << " failed, re-establishing p2p links";
         // A peer dropped: fetch the new ring before the caller retries.  Only once per
         // connection revision, and only when no other reduction is still in flight (those
         // will fail too and the last one to be awaited does the rewiring).
@@ -780,13 +784,21 @@ bool Client::drain_deferred() {
 
 Client::Pool Client::pick_rx_pool(const Uuid &peer, int timeout_ms) {
     std::unique_lock<std::mutex> lock(rx_mu_);
-    const auto deadline = clock_type::now() + std::chrono::milliseconds(timeout_ms);
+    auto deadline = clock_type::now() + std::chrono::milliseconds(timeout_ms);
+    bool saw_dead_link = false;
     for (;;) {
         const auto it = rx_pools_.find(peer);
         if (it != rx_pools_.end() && it->second.size() >= cfg_.pool_size) {
             bool all = true;
             for (uint32_t i = 0; i < cfg_.pool_size; ++i) all = all && it->second[i] && it->second[i]->is_open();
             if (all) return Pool(it->second.begin(), it->second.begin() + cfg_.pool_size);
+            // Links that exist but are closed mean the predecessor died (or is re-dialling right
+            // now): give a re-dial a moment, but do not sit out the full timeout meant for links
+            // that have not been accepted yet.
+            if (!saw_dead_link) {
+                saw_dead_link = true;
+                deadline = std::min(deadline, clock_type::now() + std::chrono::milliseconds(250));
+            }
         }
         if (interrupted_ || rx_cv_.wait_until(lock, deadline) == std::cv_status::timeout) return {};
     }

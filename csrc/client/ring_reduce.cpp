@@ -79,6 +79,7 @@ struct Stage {
                     break;
                 }
                 if (check_abort() && res.aborted_by_master) {
+                    PLOG(DEBUG) << "abort while a send is in flight, waiting for the TX thread to let go";
                     bool done = false;
                     for (int i = 0; i < 5000 && !done; ++i) done = ticket->wait_for(kPollMs) != 0;
                     if (!done) { // a wedged link is cut so the TX thread lets go of the buffer
@@ -168,6 +169,7 @@ RingResult ring_allreduce(const RingContext &ctx, const ReduceArgs &a, std::vect
         std::memcpy(dst, a.src, a.count * esz);
     }
     auto fail = [&]() {
+        PLOG(DEBUG) << "ring all-reduce tag " << ctx.tag << " seq " << ctx.seq << " failed locally (aborted_by_master=" << res.aborted_by_master << ")";
         if (in_place && backup && !backup->empty()) std::memcpy(dst, backup->data(), backup->size());
         res.ok = false;
         return res;

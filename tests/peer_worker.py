@@ -65,6 +65,7 @@ def main():
     comm.connect(n_attempts=20)
     while comm.get_attribute(pccl.Attribute.GLOBAL_WORLD_SIZE) < world:
         comm.update_topology()
+        time.sleep(0.005)
     results = {"rank": rank, "cases": []}
     ok_all = True
     if scenario == "allreduce":
@@ -136,6 +137,34 @@ def main():
             ok_all = ok_all and torch.allclose(t.cpu(), want, rtol=1e-5, atol=1e-5)
         results["cases"].append({"id": "multiple", "ok": bool(ok_all), "ms": round(dt * 1e3, 3), "tensors": len(sizes),
                                  "plane": comm.ext_last_reduce_stats(0)["plane"]})
+    elif scenario == "kill":
+        # the last rank dies without saying goodbye while reductions are running; the others must
+        # notice quickly (master abort -> abort word -> kernel exit), keep their input, and go on
+        import os
+        n = 64_000_000
+        x = make_input(400, rank, n, torch.float32).to(dev)
+        keep = x.clone()
+        done, failures, t_fail = 0, 0, None
+        for it in range(400):
+            if rank == world - 1 and it == 5:
+                os._exit(0)
+            try:
+                t0 = time.perf_counter()
+                comm.all_reduce(x, x, op=pccl.ReduceOp.SUM, tag=0)
+                done += 1
+                x.copy_(keep)
+            except pccl.PCCLError as e:
+                failures += 1
+                t_fail = time.perf_counter() - t0
+                if e.result == pccl.Result.TOO_FEW_PEERS:
+                    break
+                assert e.result == pccl.Result.RANK_CONNECTION_LOST, e
+                assert torch.equal(x, keep), "a failed in-place reduction must leave the input intact"
+            if comm.get_attribute(pccl.Attribute.PEER_GROUP_WORLD_SIZE) == world - 1 and done > 20:
+                break
+        ok_all = failures >= 1 and comm.get_attribute(pccl.Attribute.PEER_GROUP_WORLD_SIZE) == world - 1
+        results["cases"].append({"id": "kill", "ok": bool(ok_all), "done": done, "failures": failures,
+                                 "seconds_to_fail": None if t_fail is None else round(t_fail, 3)})
     elif scenario == "shared_state":
         # rank 0 holds the truth; the others start from garbage and must end up identical
         n = 5_000_003

@@ -32,7 +32,9 @@ def run_peers(world: int, scenario: str, devices=None, timeout=600):
         outs.append((p.returncode, o, e))
     master.interrupt()
     results = []
-    for rc, o, e in outs:
+    for rank, (rc, o, e) in enumerate(outs):
+        if scenario == "kill" and rank == world - 1:
+            continue  # the victim exits without a report
         assert rc == 0, f"peer failed rc={rc}\nstdout:{o[-3000:]}\nstderr:{e[-3000:]}"
         results.append(json.loads(o.strip().splitlines()[-1]))
     return results
@@ -74,3 +76,11 @@ def test_many_small_tensors_are_fused(world):
 def test_shared_state_device_tensors(world):
     for r in run_peers(world, "shared_state"):
         assert r["ok"], r
+
+
+@pytest.mark.parametrize("world", [w for w in worlds() if w >= 3][:1] or [pytest.param(3, marks=pytest.mark.skip(reason="needs >= 3 GPUs"))])
+def test_peer_killed_mid_reduction_on_the_device_plane(world):
+    for r in run_peers(world, "kill", timeout=180):
+        c = r["cases"][0]
+        assert c["ok"], c
+        assert c["seconds_to_fail"] is not None and c["seconds_to_fail"] < 10, c

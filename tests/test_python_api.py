@@ -198,3 +198,11 @@ def test_diloco_cpu_matches_torch_sgd():
         return True
 
     assert all(run_threads(2, body).values())
+
+
+def test_peer_killed_mid_run_recovers_quickly():
+    """a peer exits without notice while reductions run (the reference's stress orchestrator SIGKILLs peers)"""
+    for r in run_peers(3, "kill", devices=["cpu"] * 3, timeout=150):
+        c = r["cases"][0]
+        assert c["ok"], c
+        assert c["seconds_to_fail"] < 5, c
