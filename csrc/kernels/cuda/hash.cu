@@ -27,7 +27,7 @@ constexpr uint32_t kHashThreads = 256;
 constexpr uint32_t kHashMaxBlocks = 960;
 constexpr size_t kSimpleScratchBytes = 4096; // 960 partials + ticket
 constexpr uint32_t kCrcWarpsPerBlock = 8;
-constexpr uint32_t kCrcMaxBlocks = 592; // 4 per SM on 148 SMs
+constexpr uint32_t kCrcMaxBlocks = 1184; // 8 per SM on 148 SMs
 constexpr size_t kCrcScratchBytes = (kCrcMaxBlocks * kCrcWarpsPerBlock + 16) * sizeof(uint32_t);
 constexpr size_t kScratchBytes = 64 * 1024;
 static_assert(kSimpleScratchBytes + kCrcScratchBytes <= kScratchBytes, "scratch layout");
@@ -188,13 +188,26 @@ __global__ void __launch_bounds__(kCrcWarpsPerBlock * 32) crc32c_kernel(const ui
     __syncthreads();
     if (!s_last) return;
     __threadfence();
-    // combine: value of warp w is followed by all bytes after its span
+    // combine: the value of warp w is followed by all bulk bytes after its span.  All spans but the
+    // last have the same length, so a thread walks a contiguous run of warps with a Horner step
+    // (one multiplication by X = x^(8*span) per warp) and pays a single x^n computation for the
+    // bytes that follow its run.
     uint32_t total = 0;
-    for (uint32_t w = threadIdx.x; w < n_warps; w += blockDim.x) {
-        const uint64_t lo = min(uint64_t(w) * rows_per_warp, rows), hi = min(lo + rows_per_warp, rows);
-        if (hi == lo) continue;
-        const uint64_t bytes_after = (rows - hi) * 512; // up to the end of the bulk part
-        total ^= gf::mul(__ldcg(partial + w), gf::x_pow(bytes_after * 8));
+    {
+        const uint32_t per_thread = (n_warps + blockDim.x - 1) / blockDim.x;
+        const uint32_t w_lo = min(threadIdx.x * per_thread, n_warps), w_hi = min(w_lo + per_thread, n_warps);
+        const uint32_t X = gf::x_pow(rows_per_warp * 512 * 8);
+        uint32_t run = 0;
+        uint64_t last_row_end = 0;
+        for (uint32_t w = w_lo; w < w_hi; ++w) {
+            const uint64_t lo = min(uint64_t(w) * rows_per_warp, rows), hi = min(lo + rows_per_warp, rows);
+            if (hi == lo) break; // spans are assigned in order: the rest is empty
+            // shift what we have by the length of THIS span, then append it
+            run = hi - lo == rows_per_warp ? gf::mul(run, X) : gf::mul(run, gf::x_pow((hi - lo) * 512 * 8));
+            run ^= __ldcg(partial + w);
+            last_row_end = hi;
+        }
+        if (last_row_end) total = gf::mul(run, gf::x_pow((rows - last_row_end) * 512 * 8));
     }
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) total ^= __shfl_xor_sync(0xffffffffu, total, o);
