@@ -65,6 +65,7 @@ void QueuedSocket::rx_loop() {
         {
             std::lock_guard<std::mutex> lock(mu_);
             inbox_.push_back(std::move(f));
+            arrivals_.fetch_add(1, std::memory_order_release);
         }
         cv_.notify_all();
     }

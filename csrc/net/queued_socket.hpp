@@ -5,7 +5,9 @@
 // (tinysockets/src/queued_client_socket.cpp:28-424).
 #pragma once
 #include <atomic>
+#include <chrono>
 #include <condition_variable>
+#include <cstdlib>
 #include <functional>
 #include <list>
 #include <mutex>
@@ -47,6 +49,9 @@ public:
     // until one arrives or the connection dies.
     template <typename P, typename Pred> std::optional<P> recv_matching(Pred pred, bool no_wait = false) {
         std::unique_lock<std::mutex> lock(mu_);
+        // Answers from the master usually arrive within tens of microseconds: poll for a short
+        // while before paying for a futex sleep and wake-up.
+        auto spin_until = std::chrono::steady_clock::now() + std::chrono::microseconds(no_wait ? 0 : spin_budget_us());
         for (;;) {
             for (auto it = inbox_.begin(); it != inbox_.end(); ++it) {
                 if (it->id != P::id) continue;
@@ -61,8 +66,29 @@ public:
                 return pkt;
             }
             if (no_wait || !open_) return std::nullopt;
+            if (std::chrono::steady_clock::now() < spin_until) {
+                const size_t seen = arrivals_;
+                lock.unlock();
+                while (arrivals_.load(std::memory_order_acquire) == seen && std::chrono::steady_clock::now() < spin_until) {
+#if defined(__x86_64__)
+                    __builtin_ia32_pause();
+#endif
+                }
+                lock.lock();
+                continue;
+            }
             cv_.wait(lock);
         }
+    }
+
+    // PCCL_SPIN_US overrides; by default only machines with cores to spare spin (on a small host
+    // the spinning thread takes the core away from the thread it is waiting for).
+    static int spin_budget_us() {
+        static const int us = [] {
+            if (const char *v = std::getenv("PCCL_SPIN_US")) return std::atoi(v);
+            return std::thread::hardware_concurrency() >= 32 ? 60 : 0;
+        }();
+        return us;
     }
 
 private:
@@ -80,6 +106,7 @@ private:
     std::mutex mu_, send_mu_;
     std::condition_variable cv_;
     std::list<Frame> inbox_;
+    std::atomic<size_t> arrivals_{0}; // bumped for every queued frame; lets waiters poll without the lock
     Observer observer_;
 };
 

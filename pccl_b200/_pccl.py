@@ -100,10 +100,10 @@ class DataType(Enum):
 
     @classmethod
     def from_torch_dtype(cls, dtype) -> "DataType":
-        for k, v in _torch_table().items():
-            if v == dtype:
-                return k
-        raise ValueError(f"unsupported torch dtype {dtype}")
+        try:
+            return _torch_reverse()[dtype]
+        except KeyError:
+            raise ValueError(f"unsupported torch dtype {dtype}") from None
 
     @classmethod
     def from_numpy_dtype(cls, dtype) -> "DataType":
@@ -118,7 +118,21 @@ class DataType(Enum):
         return int(lib().pcclExtDataTypeSize(self.value))
 
 
+_TORCH_TABLE = None
+_TORCH_REVERSE = None
+
+
+def _torch_reverse():
+    global _TORCH_REVERSE
+    if _TORCH_REVERSE is None:
+        _TORCH_REVERSE = {v: k for k, v in _torch_table().items()}
+    return _TORCH_REVERSE
+
+
 def _torch_table() -> Dict[DataType, "torch.dtype"]:
+    global _TORCH_TABLE
+    if _TORCH_TABLE is not None:
+        return _TORCH_TABLE
     t = {
         DataType.UINT8: torch.uint8, DataType.INT8: torch.int8, DataType.INT16: torch.int16,
         DataType.INT32: torch.int32, DataType.INT64: torch.int64, DataType.FLOAT16: torch.float16,
@@ -127,6 +141,7 @@ def _torch_table() -> Dict[DataType, "torch.dtype"]:
     for name, dt in (("uint16", DataType.UINT16), ("uint32", DataType.UINT32), ("uint64", DataType.UINT64)):
         if hasattr(torch, name):
             t[dt] = getattr(torch, name)
+    _TORCH_TABLE = t
     return t
 
 
@@ -494,7 +509,7 @@ def _sync_current_stream(objs) -> None:
     for t in walk(objs):
         if t.is_cuda:
             s = torch.cuda.current_stream(t.device)
-            if s != torch.cuda.default_stream(t.device):
+            if s.cuda_stream != 0:  # the legacy default stream is ordered by the library itself
                 s.synchronize()
             return
 
