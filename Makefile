@@ -37,7 +37,7 @@ TEST_BINS := $(patsubst tests/cpp/%.cpp,$(BUILD)/tests/%,$(TEST_SRCS))
 all: lib master tests
 lib: $(LIBDIR)/libpccl.so
 master: $(BINDIR)/ccoip_master
-tests: $(TEST_BINS)
+tests: $(TEST_BINS) $(BUILD)/tests/c99_compat
 
 $(BUILD)/%.o: %.cpp
 	@mkdir -p $(dir $@)
@@ -59,6 +59,11 @@ $(BINDIR)/ccoip_master: tools/ccoip_master.cpp $(LIBDIR)/libpccl.so
 $(BUILD)/tests/%: tests/cpp/%.cpp $(CPP_OBJS) $(CU_OBJS)
 	@mkdir -p $(dir $@)
 	$(CXX) $(CXXFLAGS) -Itests/cpp $< $(CPP_OBJS) $(CU_OBJS) -o $@ $(LDFLAGS) $(CUDA_LIBS)
+
+# the headers must compile as strict C99
+$(BUILD)/tests/c99_compat: tests/cpp/c99_compat.c include/pccl.h include/pccl_kernels.h $(LIBDIR)/libpccl.so
+	@mkdir -p $(dir $@)
+	gcc -std=c99 -pedantic -Wall -Wextra -Werror -Iinclude $< -o $@ -L$(LIBDIR) -lpccl -Wl,-rpath,'$$ORIGIN/../../$(LIBDIR)'
 
 clean:
 	rm -rf $(BUILD) $(LIBDIR)/libpccl.so $(BINDIR)/ccoip_master

@@ -81,12 +81,12 @@ public:
         }
     }
 
-    // PCCL_SPIN_US overrides; by default only machines with cores to spare spin (on a small host
+    // PCCL_SPIN_US overrides; by default only machines with cores to spare (16+) spin (on a small host
     // the spinning thread takes the core away from the thread it is waiting for).
     static int spin_budget_us() {
         static const int us = [] {
             if (const char *v = std::getenv("PCCL_SPIN_US")) return std::atoi(v);
-            return std::thread::hardware_concurrency() >= 32 ? 60 : 0;
+            return std::thread::hardware_concurrency() >= 16 ? 60 : 0;
         }();
         return us;
     }

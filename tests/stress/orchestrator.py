@@ -1,0 +1,83 @@
+#!/usr/bin/env python3
+"""Chaos orchestrator (reference: python/tests/stress_tests/basic_stress_test/stresstest_orchestrator.py): starts a master,
+then keeps spawning peers and killing them with SIGKILL at random.  Fails when no reduction completes anywhere
+for `--stall` seconds.
+
+  python tests/stress/orchestrator.py --seconds 60 --max-peers 5 [--device cpu]
+"""
+import argparse
+import os
+import random
+import signal
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+HERE = Path(__file__).resolve().parent
+sys.path.insert(0, str(HERE.parent.parent))
+import pccl_b200 as pccl  # noqa: E402
+
+
+def run(seconds: float, max_peers: int, stall: float, device: str, seed: int = 0) -> dict:
+    rng = random.Random(seed)
+    master = pccl.MasterNode("127.0.0.1:0")
+    master.run()
+    port = master.port
+    peers = []
+    last_progress = [time.time()]
+    counts = {"reductions": 0, "spawned": 0, "killed": 0}
+    lock = threading.Lock()
+
+    def watch(p):
+        for line in p.stdout:
+            if line.startswith("REDUCE"):
+                with lock:
+                    counts["reductions"] += 1
+                    last_progress[0] = time.time()
+            elif line.startswith("FATAL"):
+                counts.setdefault("fatal", []).append(line.strip())
+
+    def spawn():
+        p = subprocess.Popen([sys.executable, str(HERE / "chaos_peer.py"), str(port), device], stdout=subprocess.PIPE,
+                             stderr=subprocess.DEVNULL, text=True)
+        threading.Thread(target=watch, args=(p,), daemon=True).start()
+        peers.append(p)
+        counts["spawned"] += 1
+
+    spawn()
+    spawn()
+    t_end = time.time() + seconds
+    stalled = False
+    while time.time() < t_end:
+        time.sleep(rng.uniform(0.3, 1.2))
+        peers[:] = [p for p in peers if p.poll() is None]
+        if rng.random() < 0.6:
+            if len(peers) < max_peers:
+                spawn()
+        elif len(peers) > 2:
+            victim = rng.choice(peers)
+            os.kill(victim.pid, signal.SIGKILL)
+            peers.remove(victim)
+            counts["killed"] += 1
+        if time.time() - last_progress[0] > stall:
+            stalled = True
+            break
+    for p in peers:
+        p.kill()
+    master.interrupt()
+    counts["stalled"] = stalled
+    return counts
+
+
+if __name__ == "__main__":
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--seconds", type=float, default=60)
+    ap.add_argument("--max-peers", type=int, default=5)
+    ap.add_argument("--stall", type=float, default=20)
+    ap.add_argument("--device", default="cpu")
+    a = ap.parse_args()
+    out = run(a.seconds, a.max_peers, a.stall, a.device)
+    print(out)
+    sys.exit(1 if out["stalled"] or out.get("fatal") else 0)

@@ -25,3 +25,10 @@ def test_cpp(binary, case):
     assert exe.exists(), f"{exe} was not built"
     proc = subprocess.run([str(exe), case], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=600)
     assert proc.returncode == 0, proc.stdout[-4000:]
+
+
+def test_headers_are_c99():
+    exe = REPO / "build" / "tests" / "c99_compat"
+    assert exe.exists(), f"{exe} was not built"
+    proc = subprocess.run([str(exe)], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=60)
+    assert proc.returncode == 0 and "c99 ok" in proc.stdout, proc.stdout
