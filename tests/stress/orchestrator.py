@@ -39,9 +39,26 @@ def run(seconds: float, max_peers: int, stall: float, device: str, seed: int = 0
             elif line.startswith("FATAL"):
                 counts.setdefault("fatal", []).append(line.strip())
 
+    # device "cuda" = one peer per GPU (kernels of two peers that wait for each other must not share a GPU)
+    n_gpus = 0
+    if device == "cuda":
+        import torch
+        n_gpus = torch.cuda.device_count()
+        max_peers = min(max_peers, n_gpus)
+    gpu_of = {}
+
     def spawn():
-        p = subprocess.Popen([sys.executable, str(HERE / "chaos_peer.py"), str(port), device], stdout=subprocess.PIPE,
+        dev = device
+        if device == "cuda":
+            used = {gpu_of[q.pid] for q in peers if q.poll() is None}
+            free = [g for g in range(n_gpus) if g not in used]
+            if not free:
+                return
+            dev = f"cuda:{free[0]}"
+        p = subprocess.Popen([sys.executable, str(HERE / "chaos_peer.py"), str(port), dev], stdout=subprocess.PIPE,
                              stderr=subprocess.DEVNULL, text=True)
+        if device == "cuda":
+            gpu_of[p.pid] = int(dev.split(":")[1])
         threading.Thread(target=watch, args=(p,), daemon=True).start()
         peers.append(p)
         counts["spawned"] += 1
