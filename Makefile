@@ -15,6 +15,21 @@ NVFLAGS  := -std=c++20 -O3 -lineinfo -gencode arch=compute_100a,code=sm_100a -Xc
             -Iinclude -Icsrc --expt-relaxed-constexpr -Xptxas -v
 LDFLAGS  := -pthread -Wl,--no-undefined
 
+# make SANITIZE=address|thread NO_CUDA=1 tests   -> instrumented C++ tests under build-<kind>/ (the shipped
+# library and the normal build tree are left alone)
+ifneq ($(SANITIZE),)
+BUILD    := build-$(SANITIZE)
+LIBDIR   := $(BUILD)/lib
+BINDIR   := $(BUILD)/bin
+ifeq ($(SANITIZE),address)
+SANFLAGS := -fsanitize=address,undefined -fno-sanitize-recover=undefined
+else
+SANFLAGS := -fsanitize=$(SANITIZE)
+endif
+CXXFLAGS := $(subst -O3,-O1,$(CXXFLAGS)) -fno-omit-frame-pointer $(SANFLAGS)
+LDFLAGS  := -pthread $(SANFLAGS)
+endif
+
 ifeq ($(NO_CUDA),1)
 CXXFLAGS += -DPCCL_NO_CUDA
 CU_SRCS  :=

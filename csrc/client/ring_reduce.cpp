@@ -116,7 +116,7 @@ struct Stage {
                     failed = true;
                     return false;
                 }
-                sink(b + got, frame->data(), frame->size());
+                if (frame->size()) sink(b + got, frame->data(), frame->size()); // empty chunks travel as empty frames
                 got += frame->size();
                 res.rx_bytes += frame->size();
             }

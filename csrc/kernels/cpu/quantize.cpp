@@ -80,7 +80,7 @@ template <typename T> void minmax_scan(const T *x, size_t n, double &mn, double 
 
 template <typename T, typename Q> void minmax_quant(const T *x, Q *q, size_t n, T mn, T mx) {
     if (mx == mn) {
-        std::memset(q, 0, n * sizeof(Q));
+        if (n) std::memset(q, 0, n * sizeof(Q)); // empty ring chunks come with a null pointer
         return;
     }
     const double inv = 1.0 / static_cast<double>(mx - mn), top = qmax_d<Q>();

@@ -108,6 +108,7 @@ void Master::promote(Client &c) {
 template <typename P> static bool decode(Reader &r, P &pkt) { return pkt.read(r) && r.ok(); }
 
 void Master::on_frame(const ccoip_socket_address_t &from, std::span<const uint8_t> frame) {
+    state_owner_.check("master state machine");
     Reader r(frame.data(), frame.size());
     const PacketId id = r.get<uint16_t>();
     if (!r.ok()) return kick(from, "truncated frame");
@@ -858,6 +859,7 @@ void Master::eval_collective_complete(uint32_t group, uint64_t tag) {
 // ------------------------------------------------------------------------------------------
 
 void Master::on_disconnect(const ccoip_socket_address_t &from) {
+    state_owner_.check("master state machine");
     const auto ait = by_addr_.find(net::AddrKey(from));
     if (ait == by_addr_.end()) return; // never registered
     const Uuid uuid = ait->second;

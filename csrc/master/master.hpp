@@ -29,6 +29,7 @@
 
 #include "../net/epoll_server.hpp"
 #include "../topo/bandwidth_store.hpp"
+#include "../util/guard.hpp"
 #include "../util/log.hpp"
 #include "../util/threadpool.hpp"
 #include "../wire/packets.hpp"
@@ -159,6 +160,7 @@ private:
 
     net::EpollServer server_;
     std::atomic<bool> running_{false}, interrupted_{false};
+    ThreadGuard state_owner_; // everything below belongs to the server's event thread
 
     std::unordered_map<Uuid, Client> clients_;
     std::unordered_map<net::AddrKey, Uuid> by_addr_;

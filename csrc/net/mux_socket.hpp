@@ -19,27 +19,20 @@
 #include <unordered_map>
 #include <vector>
 
+#include "../util/park.hpp"
 #include "../wire/packets.hpp"
 #include "addr.hpp"
 
 namespace pccl::net {
 
+// Completion handle of one queued send: 0 in flight, 1 sent, 2 failed (reported as -1).
 struct SendTicket {
-    std::mutex mu;
-    std::condition_variable cv;
-    int state = 0; // 0 in flight, 1 sent, -1 failed
-    void finish(bool ok) {
-        {
-            std::lock_guard<std::mutex> lock(mu);
-            state = ok ? 1 : -1;
-        }
-        cv.notify_all();
-    }
-    // returns state; 0 on timeout
+    Parker word{0};
+    void finish(bool ok) { word.publish(ok ? 1u : 2u); }
+    // returns 1 sent, -1 failed, 0 on timeout
     int wait_for(int timeout_ms) {
-        std::unique_lock<std::mutex> lock(mu);
-        cv.wait_for(lock, std::chrono::milliseconds(timeout_ms), [this] { return state != 0; });
-        return state;
+        const uint32_t v = word.wait_while(0, timeout_ms);
+        return v == 0 ? 0 : (v == 1 ? 1 : -1);
     }
 };
 

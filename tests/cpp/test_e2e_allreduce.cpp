@@ -4,6 +4,7 @@
 #include <numeric>
 
 #include "e2e_util.hpp"
+#include "util/guarded_alloc.hpp"
 
 using namespace pccl;
 using client::ReduceOutcome;
@@ -288,6 +289,50 @@ TEST(striped_over_connection_pool) {
         for (auto &t : ts) t.join();
         for (int r = 0; r < 3; ++r)
             for (size_t i = 0; i < n; ++i) CHECK(out[r][i] == in[0][i] + in[1][i] + in[2][i]);
+    }
+}
+
+// User buffers end exactly at an inaccessible page: any read or write past `count` elements in the reduce,
+// quantise or receive paths faults here.  Counts are chosen to leave ragged chunks and ragged quant blocks.
+TEST(buffers_in_guarded_blocks) {
+    TestMaster tm;
+    auto peers = connect_peers(tm, 3);
+    uint64_t tag = 10;
+    for (auto algo : {wire::QuantAlgo::None, wire::QuantAlgo::MinMax, wire::QuantAlgo::ZeroPointScale, wire::QuantAlgo::BlockMinMax,
+                      wire::QuantAlgo::BlockFp8}) {
+        for (size_t n : {1u, 2u, 127u, 129u, 1000u, 4099u}) {
+            ++tag;
+            std::vector<float *> in(3), out(3);
+            for (int r = 0; r < 3; ++r) {
+                in[r] = static_cast<float *>(guarded_alloc(n * sizeof(float)));
+                out[r] = static_cast<float *>(guarded_alloc(n * sizeof(float)));
+                for (size_t i = 0; i < n; ++i) in[r][i] = static_cast<float>((i + r) % 5);
+            }
+            std::vector<std::thread> ts;
+            for (int r = 0; r < 3; ++r)
+                ts.emplace_back([&, r] {
+                    ReduceRequest req;
+                    req.send = in[r];
+                    req.recv = out[r];
+                    req.count = n;
+                    req.op = wire::RedOp::Sum;
+                    req.quant = algo;
+                    req.quant_dtype = algo == wire::QuantAlgo::BlockFp8 ? wire::DType::F8E4M3 : wire::DType::U8;
+                    req.tag = tag;
+                    CHECK(peers[r]->all_reduce_async(req) == client::Client::Launch::Ok);
+                    ReduceOutcome o;
+                    CHECK(peers[r]->await_reduce(tag, o));
+                });
+            for (auto &t : ts) t.join();
+            for (size_t i = 0; i < n; ++i) {
+                const float truth = static_cast<float>(i % 5 + (i + 1) % 5 + (i + 2) % 5);
+                CHECK(std::fabs(out[0][i] - truth) < (algo == wire::QuantAlgo::None ? 1e-6f : 0.8f));
+            }
+            for (int r = 0; r < 3; ++r) {
+                CHECK(guarded_free(in[r]));
+                CHECK(guarded_free(out[r]));
+            }
+        }
     }
 }
 

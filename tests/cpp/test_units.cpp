@@ -6,6 +6,10 @@
 #include <cstring>
 #include <numeric>
 #include <random>
+#include <thread>
+
+#include <sys/wait.h>
+#include <unistd.h>
 
 #include "harness.hpp"
 #include "kernels/cpu/half.hpp"
@@ -15,6 +19,9 @@
 #include "topo/atsp.hpp"
 #include "topo/bandwidth_store.hpp"
 #include "topo/optimizer.hpp"
+#include "util/guard.hpp"
+#include "util/guarded_alloc.hpp"
+#include "util/park.hpp"
 #include "wire/packets.hpp"
 
 using namespace pccl;
@@ -379,6 +386,79 @@ TEST(reduce_kernels_all_types) {
     CHECK_EQ(wire::dtype_size(DType::BF16), size_t(2)); // the reference reports 0 here (src/pccl.cpp:525-543)
     CHECK_EQ(wire::dtype_size(DType::I16), size_t(2));
     CHECK_EQ(wire::dtype_size(DType::F16), size_t(2));
+}
+
+TEST(parker_wakes_and_times_out) {
+    Parker p(0);
+    const auto t0 = std::chrono::steady_clock::now();
+    CHECK_EQ(p.wait_while(0, 30), 0u); // nobody publishes: times out with the old value
+    const auto waited = std::chrono::duration_cast<std::chrono::milliseconds>(std::chrono::steady_clock::now() - t0).count();
+    CHECK(waited >= 25 && waited < 2000);
+    for (int round = 0; round < 200; ++round) {
+        Parker q(0);
+        std::thread waker([&] { q.publish(7); });
+        CHECK_EQ(q.wait_while(0, 5000), 7u);
+        waker.join();
+    }
+    CHECK_EQ(p.wait_while(1, -1), 0u); // value already differs: returns at once even without a limit
+}
+
+TEST(phase_guard_is_exclusive) {
+    std::atomic<bool> flag{false};
+    {
+        PhaseGuard outer(flag);
+        CHECK(outer.entered());
+        PhaseGuard inner(flag);
+        CHECK(!inner.entered());
+        CHECK(flag.load());
+    }
+    CHECK(!flag.load());
+}
+
+TEST(thread_guard_adopts_first_thread) {
+    ThreadGuard g;
+    std::thread([&] { g.check("unit"); }).join();
+    g.release();
+    g.check("unit"); // adopted by this thread now
+    g.check("unit");
+    // a foreign thread is a fatal error: observe it in a child process
+    const pid_t pid = fork();
+    if (pid == 0) {
+        std::thread([&] { g.check("unit"); }).join();
+        _exit(0);
+    }
+    int status = 0;
+    waitpid(pid, &status, 0);
+    CHECK(!(WIFEXITED(status) && WEXITSTATUS(status) == 0));
+}
+
+TEST(guarded_blocks_fault_on_overrun) {
+    for (size_t n : {1u, 15u, 16u, 4096u, 4097u, 100000u}) {
+        auto *p = static_cast<uint8_t *>(guarded_alloc(n));
+        CHECK(p != nullptr);
+        CHECK_EQ(reinterpret_cast<uintptr_t>(p) % 16, 0u);
+        std::memset(p, 0x11, n);
+        CHECK(guarded_free(p));
+    }
+    CHECK_EQ(guarded_live_blocks(), 0u);
+    // one byte past a block whose size is a multiple of 16 must fault; so must the byte before a page-sized block
+    for (int which = 0; which < 2; ++which) {
+        const pid_t pid = fork();
+        if (pid == 0) {
+            auto *p = static_cast<volatile uint8_t *>(guarded_alloc(4096));
+            if (which == 0) p[4096] = 1;
+            else p[-1] = 1;
+            _exit(0);
+        }
+        int status = 0;
+        waitpid(pid, &status, 0);
+        // a plain build dies of SIGSEGV; a sanitizer build catches the fault and exits non-zero
+        CHECK(WIFSIGNALED(status) ? WTERMSIG(status) == SIGSEGV : WEXITSTATUS(status) != 0);
+    }
+    // an underrun into the alignment slack is caught by the canary
+    auto *p = static_cast<uint8_t *>(guarded_alloc(40));
+    p[-1] = 0;
+    CHECK(!guarded_free(p));
 }
 
 TEST_MAIN()
