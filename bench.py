@@ -235,6 +235,20 @@ def run_ours(args) -> dict:
     for _ in range(3):
         outer_step()
     ms_outer = timed(outer_step, max(3, args.steps // 2))
+
+    # the same step as ONE collective on plain torch tensors (one kernel per peer: pseudo-gradient while
+    # staging, reduction over NVLink, Nesterov update while writing out)
+    fused_planes = set()
+    if world > 1:
+        def fused_outer_step():
+            comm.ext_diloco_outer_step(outer, inner, buf, lr=0.7, mu=0.9, first=False, tag=0)
+            fused_planes.add(comm.ext_last_reduce_stats(0)["plane"])
+    else:
+        def fused_outer_step():
+            ops.local_outer_step(outer, inner, buf, arena, 0.7, 0.9, False)
+    for _ in range(3):
+        fused_outer_step()
+    ms_outer_fused = timed(fused_outer_step, max(3, args.steps // 2))
     ops.simplehash(outer)  # first call creates the per-device scratch and stream
     t0 = time.perf_counter()
     digest = ops.simplehash(outer)
@@ -258,6 +272,21 @@ def run_ours(args) -> dict:
             dist.all_reduce(grad, op=dist.ReduceOp.AVG)
         ms_nccl = timed(lambda: dist.all_reduce(grad, op=dist.ReduceOp.AVG), args.steps)
         nccl = {"ms_per_step": round(ms_nccl, 4), "bus_GBps": round(nbytes * bus_factor(world) / (ms_nccl * 1e-3) / 1e9, 2)}
+        # and the outer step the way a torch + NCCL program writes it (sync_diloco.py:480-530 with NCCL as the transport)
+        tmp = torch.empty_like(outer)
+
+        def nccl_outer_step():
+            torch.sub(outer, inner, out=grad)
+            dist.all_reduce(grad, op=dist.ReduceOp.AVG)
+            buf.mul_(0.9).add_(grad)
+            torch.add(grad, buf, alpha=0.9, out=tmp)
+            outer.add_(tmp, alpha=-0.7)
+            inner.copy_(outer)
+
+        for _ in range(3):
+            nccl_outer_step()
+        nccl["diloco_outer_step_ms"] = round(timed(nccl_outer_step, max(3, args.steps // 2)), 4)
+        del tmp
 
     factor = bus_factor(world)
     value = nbytes * factor / (ms_step * 1e-3) / 1e9
@@ -276,7 +305,8 @@ def run_ours(args) -> dict:
                            "bus GB/s = bytes*2(P-1)/P/t, device time incl. control plane round trips"},
         "e2e": {"value": round(e2e_value, 3), "unit": "GB/s", "ms_per_step": round(ms_e2e, 4), "h2d_bytes_per_step": nbytes, "d2h_bytes_per_step": 4},
         "gpu_launches": timed_launches,
-        "diloco_outer_step_ms": round(ms_outer, 4), "shared_state_hash_ms": round(ms_hash, 3), "shared_state_hash": digest,
+        "diloco_outer_step_ms": round(ms_outer, 4),
+        "diloco_outer_step_fused_ms": round(ms_outer_fused, 4), "diloco_outer_step_fused_planes": sorted(fused_planes), "shared_state_hash_ms": round(ms_hash, 3), "shared_state_hash": digest,
         "clocks": clocks,
         "kernel_ms_per_step": round(kernel_ms, 4) if kernel_ms else None,
         "regular_buffers": regular,

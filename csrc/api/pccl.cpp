@@ -256,6 +256,45 @@ pcclResult_t pcclAllReduce(const void *sendbuff, void *recvbuff, const pcclReduc
     return out.ok ? pcclSuccess : pcclRankConnectionLost;
 }
 
+pcclResult_t pcclExtDiLoCoOuterStep(const pcclExtOuterStepDescriptor_t *d, const pcclComm_t *c, pcclReduceInfo_t *info_out) {
+    PCCL_REQUIRE_INIT();
+    PCCL_REQUIRE(c && d, pcclInvalidArgument);
+    PCCL_REQUIRE(c->client, pcclInvalidUsage);
+    PCCL_REQUIRE(d->params && d->inner && d->momentum && d->count > 0, pcclInvalidArgument);
+    // all three tensors live in the same place
+    const auto where = device::classify_pointer(d->params);
+    for (const void *q : {static_cast<const void *>(d->inner), static_cast<const void *>(d->momentum)}) {
+        const auto w = device::classify_pointer(q);
+        PCCL_REQUIRE(w.is_device == where.is_device && w.device == where.device, pcclInvalidArgument);
+    }
+    PCCL_REQUIRE(c->client->local_world() >= 2, pcclTooFewPeers);
+    device::OuterStepArgs step;
+    step.params = static_cast<float *>(d->params);
+    step.inner = static_cast<float *>(d->inner);
+    step.momentum = static_cast<float *>(d->momentum);
+    step.lr = d->lr;
+    step.mu = d->mu;
+    step.first = d->first_step != 0;
+    client::ReduceRequest req;
+    req.count = d->count;
+    req.dtype = wire::DType::F32;
+    req.op = wire::RedOp::Avg;
+    req.tag = d->tag;
+    req.outer = &step; // outlives the call: the operation runs synchronously on this thread
+    client::ReduceOutcome out;
+    switch (c->client->all_reduce_sync(req, out)) {
+    case client::Client::Launch::Ok: break;
+    case client::Client::Launch::DuplicateTag: return pcclInvalidArgument;
+    case client::Client::Launch::NotConnected: return pcclInvalidUsage;
+    }
+    if (info_out) {
+        info_out->local_world_size = out.world;
+        info_out->tx_bytes = out.tx_bytes;
+        info_out->rx_bytes = out.rx_bytes;
+    }
+    return out.ok ? pcclSuccess : pcclRankConnectionLost;
+}
+
 // Many small reductions with the same element type and operator (the per-parameter pattern of the
 // reference's DiLoCo example, sync_diloco.py:500-505) are fused: gathered into one buffer, reduced
 // by ONE operation, scattered back.  Every peer passes the same descriptor list, so every peer

@@ -818,7 +818,11 @@ uint8_t *Client::staging_for(uint64_t tag, size_t bytes) {
 ReduceOutcome Client::run_reduce(const ReduceRequest &req, uint64_t) {
     ReduceOutcome out;
     const size_t esz = dtype_size(req.dtype);
-    const auto send_info = device::classify_pointer(req.send), recv_info = device::classify_pointer(req.recv);
+    // Buffers of the reduction proper.  For an outer step they are either unused (fused kernel) or a scratch
+    // buffer holding the pseudo-gradient (two-pass form).
+    const void *send = req.outer ? req.outer->params : req.send;
+    void *recv = req.outer ? req.outer->params : req.recv;
+    const auto send_info = device::classify_pointer(send), recv_info = device::classify_pointer(recv);
 
     std::vector<Uuid> ring;
     {
@@ -831,8 +835,8 @@ ReduceOutcome Client::run_reduce(const ReduceRequest &req, uint64_t) {
     out.world = world;
 
     device::DeviceReduceArgs dargs;
-    dargs.src = req.send;
-    dargs.dst = req.recv;
+    dargs.src = send;
+    dargs.dst = recv;
     dargs.count = req.count;
     dargs.dtype = req.dtype;
     dargs.op = req.op;
@@ -840,7 +844,49 @@ ReduceOutcome Client::run_reduce(const ReduceRequest &req, uint64_t) {
     dargs.quant_dtype = req.quant_dtype;
     dargs.rank = rank;
     dargs.world = world;
-    const uint32_t caps = send_info.is_device && recv_info.is_device ? plane_->capabilities(dargs) : 0;
+    dargs.outer = req.outer;
+    uint32_t caps = send_info.is_device && recv_info.is_device ? plane_->capabilities(dargs) : 0;
+    // Outer step that cannot run as one kernel (host tensors, no device plane, larger than a staging slot): the
+    // pseudo-gradient goes to a scratch buffer now, the scratch buffer is reduced like any tensor, and the
+    // update is applied once the verdict is in.  Every peer sees the same geometry and decides alike.
+    const bool outer_two_pass = req.outer && (caps & device::Plane::kCapP2P) == 0;
+    std::vector<float> outer_host_scratch;
+    std::unique_lock<std::mutex> scratch_lock;
+    if (outer_two_pass) {
+        dargs.outer = nullptr;
+        float *scratch = nullptr;
+        if (send_info.is_device) {
+            scratch_lock = std::unique_lock<std::mutex>(outer_scratch_mu_);
+            scratch = static_cast<float *>(plane_->fuse_buffer(req.count * sizeof(float)));
+            if (!scratch || !plane_->pseudo_grad(scratch, req.outer->params, req.outer->inner, req.count)) {
+                PLOG(ERR) << "outer step: cannot stage the pseudo-gradient on the device";
+                return out;
+            }
+        } else {
+            outer_host_scratch.resize(req.count);
+            for (uint64_t i = 0; i < req.count; ++i) outer_host_scratch[i] = req.outer->params[i] - req.outer->inner[i];
+            scratch = outer_host_scratch.data();
+        }
+        send = recv = scratch;
+        dargs.src = dargs.dst = scratch;
+        caps = send_info.is_device ? plane_->capabilities(dargs) : 0;
+    }
+    const bool outer_fused = req.outer && !outer_two_pass;
+    auto apply_outer_update = [&]() -> bool {
+        if (!outer_two_pass) return true;
+        const auto *avg = static_cast<const float *>(recv);
+        if (send_info.is_device) return plane_->outer_nesterov(*req.outer, avg, req.count);
+        const device::OuterStepArgs &o = *req.outer;
+        for (uint64_t i = 0; i < req.count; ++i) { // torch.optim.SGD(nesterov=True), as in the device kernels
+            const float g = avg[i];
+            const float m = o.first ? g : o.mu * o.momentum[i] + g;
+            const float p = o.params[i] - o.lr * (g + o.mu * m);
+            o.momentum[i] = m;
+            o.params[i] = p;
+            if (o.inner) o.inner[i] = p;
+        }
+        return true;
+    };
     const bool device_capable = (caps & device::Plane::kCapP2P) != 0;
 
     // ---- vote.  The spare top bit of the operator byte tells the master that this peer can
@@ -920,7 +966,7 @@ ReduceOutcome Client::run_reduce(const ReduceRequest &req, uint64_t) {
     bool local_ok = false;
     std::vector<uint8_t> host_backup; // in-place rollback for host buffers
     uint8_t *stage = nullptr;         // host staging for device buffers on the TCP plane
-    const bool in_place = req.send == req.recv;
+    const bool in_place = send == recv && !outer_fused;
 
     if (use_device && (poisoned || !device_capable)) plane_->cancel(seq); // announced, but it will not run
     if (poisoned) {
@@ -974,17 +1020,17 @@ ReduceOutcome Client::run_reduce(const ReduceRequest &req, uint64_t) {
                 stage = staging_for(req.tag, req.count * esz);
                 staged_ok = stage != nullptr;
                 if (staged_ok && send_info.is_device) {
-                    staged_ok = plane_->copy_to_host(stage, req.send, req.count * esz);
+                    staged_ok = plane_->copy_to_host(stage, send, req.count * esz);
                 } else if (staged_ok) {
-                    std::memcpy(stage, req.send, req.count * esz);
+                    std::memcpy(stage, send, req.count * esz);
                 }
                 a.src = a.dst = stage;
             } else {
-                a.src = req.send;
-                a.dst = req.recv;
+                a.src = send;
+                a.dst = recv;
             }
             if (staged_ok) {
-                const RingResult r = ring_allreduce(ctx, a, stage ? nullptr : &host_backup);
+                const RingResult r = ring_allreduce(ctx, a, stage || outer_two_pass ? nullptr : &host_backup);
                 local_ok = r.ok;
                 out.tx_bytes = r.tx_bytes;
                 out.rx_bytes = r.rx_bytes;
@@ -1001,9 +1047,11 @@ ReduceOutcome Client::run_reduce(const ReduceRequest &req, uint64_t) {
         // The kernel's closing barrier is only passed once EVERY peer has its complete result, so
         // the outcome of the completion vote is already known.  Return now; the Abort/Complete
         // packets are consumed by the next operation on this tag or by the next joint call.
-        std::lock_guard<std::mutex> lock(deferred_mu_);
-        deferred_[req.tag] = Deferred{abort_seen, aborted};
-        out.ok = true;
+        {
+            std::lock_guard<std::mutex> lock(deferred_mu_);
+            deferred_[req.tag] = Deferred{abort_seen, aborted};
+        }
+        out.ok = apply_outer_update();
         return out;
     }
     if (!abort_seen) {
@@ -1014,22 +1062,27 @@ ReduceOutcome Client::run_reduce(const ReduceRequest &req, uint64_t) {
     }
     if (!master_.recv_matching<M2CCollectiveComplete>([&](const M2CCollectiveComplete &p) { return p.tag == req.tag; })) return out;
 
-    const bool success = local_ok && !aborted;
+    // A fused outer step has updated the caller's tensors once its kernel reports success (every rank held the whole
+    // average at that point, so every surviving rank applied it): it stays a success even when the master aborted
+    // the operation afterwards because a peer vanished; the ring is rebuilt before the next operation instead.
+    const bool fused_applied = outer_fused && use_device && device_capable && local_ok;
+    if (fused_applied && aborted) ring_stale_ = true;
+    const bool success = fused_applied || (local_ok && !aborted);
     if (use_device && device_capable && !success && in_place) plane_->restore_input(dargs);
     if (out.stats.plane == pcclExtPlaneTcpRing) {
         if (success && stage) {
             if (recv_info.is_device) {
-                if (!plane_->copy_to_device(req.recv, stage, req.count * esz)) return out;
+                if (!plane_->copy_to_device(recv, stage, req.count * esz)) return out;
             } else {
-                std::memcpy(req.recv, stage, req.count * esz);
+                std::memcpy(recv, stage, req.count * esz);
             }
         } else if (!success && !stage && in_place && local_ok && !host_backup.empty()) {
             // finished locally but another peer aborted: the caller will retry with this
             // buffer as input, so it must hold the original values again
-            std::memcpy(req.recv, host_backup.data(), host_backup.size());
+            std::memcpy(recv, host_backup.data(), host_backup.size());
         }
     }
-    out.ok = success;
+    out.ok = success && apply_outer_update();
     return out;
 }
 

@@ -63,6 +63,9 @@ struct ReduceRequest {
     wire::QuantAlgo quant = wire::QuantAlgo::None;
     wire::DType quant_dtype = wire::DType::U8;
     uint64_t tag = 0;
+    // DiLoCo outer step: when set, send/recv are ignored; the reduction averages params - inner (fp32) and
+    // its result drives the Nesterov update of params/momentum/inner (see device::OuterStepArgs)
+    const device::OuterStepArgs *outer = nullptr;
 };
 
 struct ReduceOutcome {
@@ -160,6 +163,7 @@ private:
     std::map<uint64_t, StageBuf> stage_cache_;
     std::mutex deferred_mu_;
     std::map<uint64_t, Deferred> deferred_;
+    std::mutex outer_scratch_mu_;               // the plane's reusable device buffer holds one pseudo-gradient at a time
     std::atomic<bool> ring_stale_{false};       // a peer vanished after an operation had finished here: rewire before the next one
     std::atomic<bool> master_pipelines_{false}; // the master queues an Initiate behind a pending Complete
     std::mutex ops_mu_;

@@ -37,6 +37,16 @@ struct PointerInfo {
 PointerInfo classify_pointer(const void *p);
 bool cuda_runtime_usable(); // a driver and at least one device are present
 
+// Fused DiLoCo outer step (fp32, AVG): the reduction's input is params - inner, its output is consumed by the
+// Nesterov update of params/momentum, and inner receives the new parameters.
+struct OuterStepArgs {
+    float *params = nullptr;
+    float *inner = nullptr;
+    float *momentum = nullptr;
+    float lr = 0.7f, mu = 0.9f;
+    bool first = false; // the momentum buffer holds nothing yet
+};
+
 struct DeviceReduceArgs {
     const void *src = nullptr;
     void *dst = nullptr;
@@ -48,6 +58,7 @@ struct DeviceReduceArgs {
     uint64_t seq = 0;
     uint32_t rank = 0, world = 1;
     bool use_nvls = false; // all peers agreed (through the master) to run this one over NVSwitch multicast
+    const OuterStepArgs *outer = nullptr; // non-null: src/dst are ignored, see OuterStepArgs
 };
 
 struct DeviceReduceResult {
@@ -117,6 +128,11 @@ public:
     };
     virtual void *fuse_buffer(size_t bytes) = 0;
     virtual bool gather(const std::vector<Part> &parts, void *fused, bool into_fused) = 0;
+
+    // The two halves of the outer step as separate passes over device memory (used when the fused kernel cannot
+    // run: TCP plane, operands larger than a staging slot).  Synchronous.
+    virtual bool pseudo_grad(float *out, const float *params, const float *inner, size_t count) = 0;
+    virtual bool outer_nesterov(const OuterStepArgs &step, const float *grad, size_t count) = 0;
 
     // Page-locked host memory for staging (plain malloc when there is no GPU).
     virtual void *host_alloc(size_t bytes) = 0;

@@ -320,6 +320,17 @@ public:
         const PointerInfo s = classify_pointer(a.src), d = classify_pointer(a.dst);
         if (!s.is_device || !d.is_device || s.device != device_ || d.device != device_) return 0;
         if (a.dtype == wire::DType::F8E4M3) return 0;
+        if (a.outer) {
+            // fused outer step: fp32 average, all three tensors on this GPU, and the pseudo-gradient has to fit
+            // into one staging slot (with several launches an abort could leave a half-applied update behind)
+            if (a.dtype != wire::DType::F32 || a.op != wire::RedOp::Avg || a.quant != wire::QuantAlgo::None) return 0;
+            for (const void *q : {static_cast<const void *>(a.outer->params), static_cast<const void *>(a.outer->inner),
+                                  static_cast<const void *>(a.outer->momentum)}) {
+                const PointerInfo i = classify_pointer(q);
+                if (!i.is_device || i.device != device_) return 0;
+            }
+            if (pcclKernelP2PStagingBytes(a.count, pcclFloat, 0) > slot_bytes_) return 0;
+        }
         switch (a.quant) {
         case wire::QuantAlgo::None:
             // Through the switch every GPU moves about N(1+1/P) bytes per direction (its own stores
@@ -381,7 +392,7 @@ public:
         std::lock_guard<std::mutex> slot_lock(slot.mu); // one operation per slot at a time
         const size_t esz = wire::dtype_size(a.dtype);
         const int dtype = pccl_dtype(a.dtype), op = pccl_op(a.op), quant = kernel_quant(a.quant);
-        const bool in_place = a.src == a.dst;
+        const bool in_place = a.src == a.dst && !a.outer;
 
         // symmetric memory: the buffer itself is peer-visible, no staging copy
         const auto base = static_cast<uintptr_t>(arena_ptr_);
@@ -399,7 +410,7 @@ public:
             }
         }
         const uint64_t n_rounds = (a.count + per_round - 1) / per_round;
-        if (n_rounds > 255) return res;
+        if (n_rounds > 255 || (a.outer && n_rounds != 1)) return res;
 
         if (in_place && !symmetric) {
             // keep the input for a rollback (the staging slot only holds the last round)
@@ -433,7 +444,7 @@ public:
         // the arena and segment s-1 is copied out to the user buffer by the copy engines (HBM-bound).
         uint64_t seg_bytes = tune_ ? (std::max<uint64_t>(1, env_u64("PCCL_PIPELINE_SEGMENT_MB", 64)) << 20) : pipeline_seg_bytes_;
         seg_bytes = std::min<uint64_t>(seg_bytes, slot_bytes_ / 2) / 4096 * 4096;
-        const bool pipelined = mc_view && !symmetric && quant == 0 && a.count * esz >= pipeline_min_bytes_ && seg_bytes >= (1u << 20) &&
+        const bool pipelined = mc_view && !a.outer && !symmetric && quant == 0 && a.count * esz >= pipeline_min_bytes_ && seg_bytes >= (1u << 20) &&
                                (a.count * esz + seg_bytes - 1) / seg_bytes <= 250 && env_flag("PCCL_PIPELINE", false);
         if (pipelined) {
             const uint64_t bytes = a.count * esz;
@@ -519,7 +530,25 @@ public:
             k.status = slot.host_words + 1;
             k.timeout_cycles = timeout_ms_ * static_cast<uint64_t>(clock_khz_);
             int rc;
-            if (mc_view) {
+            if (a.outer) {
+                pcclKernelOuterStep_t step{};
+                step.inner_in = step.inner_out = a.outer->inner;
+                step.params = a.outer->params;
+                step.momentum = a.outer->momentum;
+                step.lr = a.outer->lr;
+                step.mu = a.outer->mu;
+                step.first = a.outer->first ? 1 : 0;
+                if (mc_view) {
+                    pcclKernelNvlsArgs_t nk{};
+                    nk.p2p = k;
+                    nk.mc_arena = mc_view;
+                    rc = pcclKernelOuterStepNvls(&nk, &step, slot.stream);
+                    algorithm = 3;
+                } else {
+                    rc = pcclKernelOuterStepP2P(&k, &step, slot.stream);
+                    algorithm = 2;
+                }
+            } else if (mc_view) {
                 pcclKernelNvlsArgs_t nk{};
                 nk.p2p = k;
                 nk.mc_arena = mc_view;
@@ -589,6 +618,15 @@ public:
         if (prev >= 0) cudaSetDevice(prev);
         if (rc != 0) PLOG(ERR) << "device hash failed: " << cudaGetErrorString(static_cast<cudaError_t>(rc));
         return rc == 0;
+    }
+
+    bool pseudo_grad(float *out, const float *params, const float *inner, size_t count) override {
+        return elementwise([&](cudaStream_t st) { return pcclKernelPseudoGrad(out, params, inner, count, st); });
+    }
+    bool outer_nesterov(const OuterStepArgs &step, const float *grad, size_t count) override {
+        return elementwise([&](cudaStream_t st) {
+            return pcclKernelOuterNesterov(step.params, step.momentum, grad, step.inner, count, step.lr, step.mu, step.first ? 1 : 0, st);
+        });
     }
 
     void *fuse_buffer(size_t bytes) override {
@@ -1086,6 +1124,22 @@ private:
             if (fd >= 0) ::close(fd);
             ::close(c);
         }
+    }
+
+    // One element-wise launch on the utility stream, ordered after the legacy default stream, waited for.
+    template <typename Launch> bool elementwise(Launch launch) {
+        if (!usable_) return false;
+        cudaSetDevice(device_);
+        std::lock_guard<std::mutex> lock(copy_mu_);
+        if (!util_stream_) RT_TRY(cudaStreamCreateWithFlags(&util_stream_, cudaStreamNonBlocking));
+        cudaEvent_t ready;
+        RT_TRY(cudaEventCreateWithFlags(&ready, cudaEventDisableTiming));
+        cudaEventRecord(ready, cudaStreamLegacy);
+        cudaStreamWaitEvent(util_stream_, ready, 0);
+        cudaEventDestroy(ready);
+        if (launch(util_stream_) != 0) return false;
+        RT_TRY(cudaStreamSynchronize(util_stream_));
+        return true;
     }
 
     bool copy(void *dst, const void *src, size_t bytes, cudaMemcpyKind kind) {

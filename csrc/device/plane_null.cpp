@@ -29,6 +29,8 @@ public:
     std::unique_lock<std::mutex> exchange_lock() override { return std::unique_lock<std::mutex>(mu_); }
     bool export_chunk(const void *, bool, size_t) override { return false; }
     bool import_chunk(const Uuid &, void *, bool, size_t) override { return false; }
+    bool pseudo_grad(float *, const float *, const float *, size_t) override { return false; }
+    bool outer_nesterov(const OuterStepArgs &, const float *, size_t) override { return false; }
     void *host_alloc(size_t bytes) override { return std::malloc(bytes); }
     void host_free(void *ptr) override { std::free(ptr); }
     void *symmetric_alloc(size_t) override { return nullptr; }

@@ -16,6 +16,7 @@
 // No trailing barrier is needed: a peer can only touch this arena again after the first barrier
 // of the NEXT operation, which this rank enters after its copy-out.
 #include "common.cuh"
+#include "outer_step.cuh"
 #include "pccl_kernels.h"
 
 namespace pccl::cuda {
@@ -38,7 +39,7 @@ struct NvlsArgs {
     uint64_t timeout_cycles;
 };
 
-__device__ bool nvls_barrier(const NvlsArgs &a, uint8_t *const *arena, uint64_t value) {
+__device__ bool nvls_barrier(const NvlsArgs &a, uint8_t *const *arena, uint64_t value, bool record_failure = true) {
     __shared__ int s_fail;
     if (threadIdx.x == 0) s_fail = 0;
     __threadfence_system(); // multimem stores of this thread are performed before the flag is raised
@@ -65,7 +66,7 @@ __device__ bool nvls_barrier(const NvlsArgs &a, uint8_t *const *arena, uint64_t 
     }
     __syncthreads();
     const int fail = s_fail;
-    if (fail != 0 && threadIdx.x == 0) atomicMax(a.status, static_cast<uint32_t>(fail));
+    if (fail != 0 && record_failure && threadIdx.x == 0) atomicMax(a.status, static_cast<uint32_t>(fail));
     return fail == 0;
 }
 
@@ -277,6 +278,61 @@ template <int TYPE, int OP, int U, bool PIPELINED> __global__ void __launch_boun
     }
 }
 
+// -----------------------------------------------------------------------------------------
+// DiLoCo outer step in one launch (fp32, AVG): the staging pass computes the pseudo-gradient, the
+// switch averages it, the write-out pass is the Nesterov update.  Nothing the caller owns is
+// written before the second barrier, i.e. before every rank holds the complete average.
+// -----------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kNvlsThreads, 1) outer_step_nvls_kernel(const NvlsArgs a, const OuterStepDev s) {
+    __shared__ uint8_t *s_arena[PCCL_K_MAX_RANKS];
+    if (threadIdx.x < PCCL_K_MAX_RANKS) s_arena[threadIdx.x] = threadIdx.x < a.world ? a.arena[threadIdx.x] : nullptr;
+    __syncthreads();
+    const uint64_t n_pack = (a.count + 3) / 4;
+    const uint64_t per = (n_pack + a.world - 1) / a.world;
+    uint4 *mine = reinterpret_cast<uint4 *>(s_arena[a.rank] + a.data_offset);
+    uint4 *mc = reinterpret_cast<uint4 *>(a.mc + a.data_offset);
+
+    nvls_owned_packets<4>(0, n_pack, [&](const uint64_t(&v)[4], const bool(&ok)[4]) {
+        uint4 d[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+            if (ok[u]) d[u] = outer_delta_packet(s, v[u], a.count);
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+            if (ok[u]) mine[v[u]] = d[u];
+    });
+    if (!nvls_barrier(a, s_arena, a.flag_base + 1)) return;
+
+    {
+        const uint64_t lo = min(uint64_t(a.rank) * per, n_pack), hi = min(lo + per, n_pack);
+        const float inv = 1.0f / static_cast<float>(a.world);
+        nvls_owned_packets<4>(lo, hi, [&](const uint64_t(&v)[4], const bool(&ok)[4]) {
+            uint4 val[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+                if (ok[u]) val[u] = mc_ld_reduce<NV_F32, OP_SUM>(mc + v[u]);
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+                if (ok[u]) mc_store(mc + v[u], scale_packet<NV_F32>(val[u], inv));
+        });
+    }
+    if (!nvls_barrier(a, s_arena, a.flag_base + 2)) return;
+
+    nvls_owned_packets<2>(0, n_pack, [&](const uint64_t(&v)[2], const bool(&ok)[2]) {
+        uint4 g[2];
+        OuterLoaded l[2];
+#pragma unroll
+        for (int u = 0; u < 2; ++u)
+            if (ok[u]) {
+                g[u] = ld_peer_16(mine + v[u]); // written through the switch: do not trust L1
+                l[u] = outer_load_packet(s, v[u], a.count);
+            }
+#pragma unroll
+        for (int u = 0; u < 2; ++u)
+            if (ok[u]) outer_apply_packet(s, v[u], a.count, g[u], l[u]);
+    });
+}
+
 } // namespace pccl::cuda
 
 using namespace pccl::cuda;
@@ -342,5 +398,43 @@ extern "C" int pcclKernelAllReduceNvls(const pcclKernelNvlsArgs_t *args, void *s
         else if (op == OP_MAX) launch(integral_constant<int, NV_F16>{}, integral_constant<int, OP_MAX>{});
         else launch(integral_constant<int, NV_F16>{}, integral_constant<int, OP_MIN>{});
     }
+    return cudaGetLastError();
+}
+
+extern "C" int pcclKernelOuterStepNvls(const pcclKernelNvlsArgs_t *args, const pcclKernelOuterStep_t *step, void *stream_v) {
+    if (!args || !args->mc_arena || !step || !step->params || !step->inner_in || !step->momentum) return cudaErrorInvalidValue;
+    const pcclKernelP2PArgs_t &p = args->p2p;
+    if (p.world < 2 || p.world > PCCL_K_MAX_RANKS || p.rank >= p.world || p.count == 0) return cudaErrorInvalidValue;
+    if ((p.count * 4 + 15) / 16 * 16 + 256 > p.data_capacity || p.data_offset % 16 != 0) return cudaErrorInvalidValue;
+    NvlsArgs d{};
+    for (uint32_t r = 0; r < p.world; ++r) d.arena[r] = static_cast<uint8_t *>(p.arena[r]);
+    d.mc = static_cast<uint8_t *>(args->mc_arena);
+    d.rank = p.rank;
+    d.world = p.world;
+    d.flag_slot = p.flag_slot;
+    d.flag_base = p.flag_base;
+    d.data_offset = p.data_offset;
+    d.count = p.count;
+    d.avg_divisor = p.world;
+    d.abort_flag = p.abort_flag;
+    d.status = p.status;
+    d.timeout_cycles = p.timeout_cycles ? p.timeout_cycles : ~0ull;
+    OuterStepDev s{};
+    s.inner_in = step->inner_in;
+    s.params = step->params;
+    s.momentum = step->momentum;
+    s.inner_out = step->inner_out;
+    s.lr = step->lr;
+    s.mu = step->mu;
+    s.first = step->first;
+    s.aligned = ((reinterpret_cast<uintptr_t>(s.inner_in) | reinterpret_cast<uintptr_t>(s.params) | reinterpret_cast<uintptr_t>(s.momentum) |
+                  reinterpret_cast<uintptr_t>(s.inner_out)) & 15) == 0;
+    const uint64_t n_pack = (p.count + 3) / 4;
+    const uint64_t tiles = (n_pack + kNvlsThreads - 1) / kNvlsThreads;
+    int max_blocks = p.max_blocks > 0 ? p.max_blocks : 144;
+    if (max_blocks > PCCL_K_MAX_BLOCKS) max_blocks = PCCL_K_MAX_BLOCKS;
+    const uint64_t chunk_tiles = (tiles + p.world - 1) / p.world;
+    const int grid = static_cast<int>(std::max<uint64_t>(1, std::min<uint64_t>(max_blocks, chunk_tiles)));
+    outer_step_nvls_kernel<<<grid, kNvlsThreads, 0, static_cast<cudaStream_t>(stream_v)>>>(d, s);
     return cudaGetLastError();
 }

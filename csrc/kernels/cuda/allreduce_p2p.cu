@@ -33,6 +33,7 @@
 #include <cstdio>
 
 #include "common.cuh"
+#include "outer_step.cuh"
 #include "pccl_kernels.h"
 #include "quant.cuh"
 
@@ -76,7 +77,7 @@ __device__ __forceinline__ uint64_t *flag_ptr(const DevArgs &a, uint8_t *arena_b
 
 // Cross-GPU barrier among the same-numbered blocks of all ranks.  Returns false when the
 // operation was aborted or timed out (uniform across the block).
-__device__ bool peer_barrier(const DevArgs &a, const PeerTable &t, uint64_t value) {
+__device__ bool peer_barrier(const DevArgs &a, const PeerTable &t, uint64_t value, bool record_failure = true) {
     __shared__ int s_fail;
     if (threadIdx.x == 0) s_fail = 0;
     __syncthreads(); // this block's earlier writes are ordered before the flag stores below
@@ -101,7 +102,7 @@ __device__ bool peer_barrier(const DevArgs &a, const PeerTable &t, uint64_t valu
     }
     __syncthreads();
     const int fail = s_fail;
-    if (fail != 0 && threadIdx.x == 0) atomicMax(a.status, static_cast<uint32_t>(fail));
+    if (fail != 0 && record_failure && threadIdx.x == 0) atomicMax(a.status, static_cast<uint32_t>(fail));
     return fail == 0;
 }
 
@@ -427,6 +428,78 @@ template <int ALGO, int OP> __global__ void __launch_bounds__(kThreads, 1) allre
     peer_barrier(a, tbl, a.flag_base + 3);
 }
 
+// -----------------------------------------------------------------------------------------
+// DiLoCo outer step in one launch (fp32, AVG), peer-to-peer flavour of outer_step_nvls_kernel:
+//   phase 0  arena = params - inner
+//   phase 1  owner of a chunk averages it over all arenas, result goes to its arena ONLY
+//   phase 2  every rank walks all chunks (its own included) and applies the Nesterov update
+// The caller's tensors are first written in phase 2, when every rank provably holds the whole
+// average; a failure of the closing barrier (a peer died after that point) is therefore not an
+// error of this operation and is not recorded.
+// -----------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kThreads, 1) outer_step_two_shot_kernel(const DevArgs a, const OuterStepDev s) {
+    __shared__ PeerTable tbl;
+    load_peer_table(tbl, a);
+    const uint64_t n_pack = (a.count + 3) / 4;
+    const uint64_t per = (n_pack + a.world - 1) / a.world;
+    uint4 *mine = reinterpret_cast<uint4 *>(tbl.base[a.rank]);
+
+    for_owned_packets<4>(0, n_pack, [&](const uint64_t(&v)[4], const bool(&ok)[4]) {
+        uint4 d[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+            if (ok[u]) d[u] = outer_delta_packet(s, v[u], a.count);
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+            if (ok[u]) mine[v[u]] = d[u];
+    });
+    if (!peer_barrier(a, tbl, a.flag_base + 1)) return;
+
+    {
+        const uint64_t lo = min(uint64_t(a.rank) * per, n_pack), hi = min(lo + per, n_pack);
+        for_owned_packets<2>(lo, hi, [&](const uint64_t(&v)[2], const bool(&ok)[2]) {
+            float acc[2][4];
+            for (uint32_t r0 = 0; r0 < a.world; r0 += kPeerGroup) {
+                uint4 raw[2][kPeerGroup];
+#pragma unroll
+                for (int u = 0; u < 2; ++u)
+#pragma unroll
+                    for (int g = 0; g < kPeerGroup; ++g)
+                        if (r0 + g < a.world && ok[u]) raw[u][g] = ld_peer_16(reinterpret_cast<const uint4 *>(tbl.base[r0 + g]) + v[u]);
+#pragma unroll
+                for (int u = 0; u < 2; ++u)
+#pragma unroll
+                    for (int g = 0; g < kPeerGroup; ++g)
+                        if (r0 + g < a.world && ok[u]) accumulate<float, OP_SUM>(acc[u], raw[u][g], r0 + g == 0);
+            }
+#pragma unroll
+            for (int u = 0; u < 2; ++u)
+                if (ok[u]) mine[v[u]] = finish<float>(acc[u], a.avg_divisor);
+        });
+    }
+    if (!peer_barrier(a, tbl, a.flag_base + 2)) return;
+
+    for (uint32_t k = 0; k < a.world; ++k) {
+        const uint32_t peer = (a.rank + k) % a.world;
+        const uint4 *from = reinterpret_cast<const uint4 *>(tbl.base[peer]);
+        const uint64_t lo = min(uint64_t(peer) * per, n_pack), hi = min(lo + per, n_pack);
+        for_owned_packets<2>(lo, hi, [&](const uint64_t(&v)[2], const bool(&ok)[2]) {
+            uint4 g[2];
+            OuterLoaded l[2];
+#pragma unroll
+            for (int u = 0; u < 2; ++u)
+                if (ok[u]) {
+                    g[u] = ld_peer_16(from + v[u]);
+                    l[u] = outer_load_packet(s, v[u], a.count);
+                }
+#pragma unroll
+            for (int u = 0; u < 2; ++u)
+                if (ok[u]) outer_apply_packet(s, v[u], a.count, g[u], l[u]);
+        });
+    }
+    peer_barrier(a, tbl, a.flag_base + 3, false);
+}
+
 } // namespace pccl::cuda
 
 using namespace pccl::cuda;
@@ -516,5 +589,42 @@ extern "C" int pcclKernelAllReduceP2P(const pcclKernelP2PArgs_t *args, int *algo
         });
     }
     if (!launched) return cudaErrorInvalidValue;
+    return cudaGetLastError();
+}
+
+extern "C" int pcclKernelOuterStepP2P(const pcclKernelP2PArgs_t *args, const pcclKernelOuterStep_t *step, void *stream_v) {
+    if (!args || args->world < 1 || args->world > PCCL_K_MAX_RANKS || args->rank >= args->world || args->count == 0) return cudaErrorInvalidValue;
+    if (!step || !step->params || !step->inner_in || !step->momentum) return cudaErrorInvalidValue;
+    if (args->flag_slot >= static_cast<uint32_t>(kFlagBanks)) return cudaErrorInvalidValue;
+    if (pcclKernelP2PStagingBytes(args->count, pcclFloat, QUANT_NONE) > args->data_capacity) return cudaErrorInvalidValue;
+    DevArgs d{};
+    for (uint32_t r = 0; r < args->world; ++r) d.arena[r] = static_cast<uint8_t *>(args->arena[r]);
+    d.rank = args->rank;
+    d.world = args->world;
+    d.flag_slot = args->flag_slot;
+    d.flag_base = args->flag_base;
+    d.data_offset = args->data_offset;
+    d.count = args->count;
+    d.avg_divisor = args->world;
+    d.abort_flag = args->abort_flag;
+    d.status = args->status;
+    d.timeout_cycles = args->timeout_cycles ? args->timeout_cycles : ~0ull;
+    OuterStepDev s{};
+    s.inner_in = step->inner_in;
+    s.params = step->params;
+    s.momentum = step->momentum;
+    s.inner_out = step->inner_out;
+    s.lr = step->lr;
+    s.mu = step->mu;
+    s.first = step->first;
+    s.aligned = ((reinterpret_cast<uintptr_t>(s.inner_in) | reinterpret_cast<uintptr_t>(s.params) | reinterpret_cast<uintptr_t>(s.momentum) |
+                  reinterpret_cast<uintptr_t>(s.inner_out)) & 15) == 0;
+    const uint64_t n_pack = (args->count + 3) / 4;
+    const uint64_t tiles = (n_pack + kThreads - 1) / kThreads;
+    int max_blocks = args->max_blocks > 0 ? args->max_blocks : 144;
+    if (max_blocks > PCCL_K_MAX_BLOCKS) max_blocks = PCCL_K_MAX_BLOCKS;
+    const uint64_t chunk_tiles = (tiles + args->world - 1) / args->world;
+    const int grid = static_cast<int>(std::max<uint64_t>(1, std::min<uint64_t>(max_blocks, chunk_tiles)));
+    outer_step_two_shot_kernel<<<grid, kThreads, 0, static_cast<cudaStream_t>(stream_v)>>>(d, s);
     return cudaGetLastError();
 }

@@ -357,6 +357,31 @@ PCCL_EXPORT pcclResult_t pcclExtSymmetricFree(pcclComm_t *communicator, void *pt
 /* Size of one element of a data type in bytes, 0 for unknown values. */
 PCCL_EXPORT size_t pcclExtDataTypeSize(pcclDataType_t datatype);
 
+/* DiLoCo outer step as one collective operation (no counterpart in the reference, whose example performs the
+ * three stages with torch ops on the host around pcclAllReduce: python/examples/nanogpt_diloco/sync_diloco.py:480-530):
+ *     g        = average over all peers of (params - inner)
+ *     momentum = first_step ? g : mu * momentum + g
+ *     params  -= lr * (g + mu * momentum)            (torch.optim.SGD with nesterov=True)
+ *     inner    = params
+ * All three tensors are float32[count], all on the host or all on one CUDA device.  Between GPUs of one NVLink
+ * domain the whole step is a single kernel per peer (pseudo-gradient while staging, reduction over NVLink /
+ * NVSwitch, update while writing out); otherwise -- TCP ring, or more elements than one staging slot holds --
+ * the library computes the pseudo-gradient into a scratch buffer, reduces that, and applies the update.
+ * Either way the tensors are untouched when the call fails (pcclRankConnectionLost: retry after
+ * pcclUpdateTopology, like pcclAllReduce).  Synchronous; one tag like any reduction. */
+typedef struct pcclExtOuterStepDescriptor_t {
+    void *params;
+    void *inner;
+    void *momentum;
+    uint64_t count;
+    float lr;
+    float mu;
+    int first_step; /* non-zero: momentum holds nothing yet */
+    uint64_t tag;
+} pcclExtOuterStepDescriptor_t;
+PCCL_EXPORT pcclResult_t pcclExtDiLoCoOuterStep(const pcclExtOuterStepDescriptor_t *descriptor, const pcclComm_t *communicator,
+                                                pcclReduceInfo_t *PCCL_NULLABLE reduce_info_out);
+
 #ifdef __cplusplus
 }
 #endif

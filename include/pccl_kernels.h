@@ -105,6 +105,35 @@ PCCL_EXPORT int pcclKernelAllReduceNvls(const pcclKernelNvlsArgs_t *args, void *
 /* 1 when multimem.ld_reduce can do (dtype, op). */
 PCCL_EXPORT int pcclKernelNvlsSupported(int dtype, int op);
 
+/* ---------------------------------------------------------------------------------------------
+ * DiLoCo outer step as ONE kernel per rank: pseudo-gradient, fp32 AVG all-reduce, Nesterov-SGD update
+ * (the reference's example does the three on the host with torch ops around pcclAllReduce:
+ * python/examples/nanogpt_diloco/sync_diloco.py:480-530).
+ *   staging   arena[v] = params[v] - inner_in[v]                (replaces the copy-in)
+ *   reduce    as in the plain kernels, result left in the arenas only
+ *   update    g = averaged pseudo-gradient; momentum = first ? g : mu*momentum + g;
+ *             params -= lr*(g + mu*momentum); inner_out = params (replaces the copy-out)
+ * params/momentum/inner_out are only written after the barrier that proves every rank holds the complete
+ * average, so an aborted operation leaves them untouched.  Geometry (arena, flags, count, rank, world,
+ * abort word, status, timeout, max_blocks) comes from the all-reduce argument block; its src, dst,
+ * dtype, op, quant_algorithm, algorithm and src_in_arena members are ignored.
+ * ------------------------------------------------------------------------------------------- */
+typedef struct pcclKernelOuterStep_t {
+    const float *inner_in;
+    float *params;
+    float *momentum;
+    float *inner_out; /* may be NULL */
+    float lr, mu;
+    int first; /* momentum holds nothing yet */
+} pcclKernelOuterStep_t;
+/* The two halves as separate element-wise passes (used when the fused kernel cannot run):
+ * out = params - inner, and the update above with `grad` in place of g. */
+PCCL_EXPORT int pcclKernelPseudoGrad(float *out, const float *params, const float *inner, size_t count, void *stream);
+PCCL_EXPORT int pcclKernelOuterNesterov(float *params, float *momentum, const float *grad, float *inner_out, size_t count, float lr, float mu,
+                                        int first, void *stream);
+PCCL_EXPORT int pcclKernelOuterStepP2P(const pcclKernelP2PArgs_t *args, const pcclKernelOuterStep_t *step, void *stream);
+PCCL_EXPORT int pcclKernelOuterStepNvls(const pcclKernelNvlsArgs_t *args, const pcclKernelOuterStep_t *step, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -118,6 +118,16 @@ class ExtReduceStatsC(C.Structure):
     _fields_ = [("plane", C.c_int), ("device_ms", C.c_float), ("seq_nr", C.c_uint64), ("kernel_launches", C.c_uint32)]
 
 
+class ExtOuterStepDescriptorC(C.Structure):
+    _fields_ = [("params", C.c_void_p), ("inner", C.c_void_p), ("momentum", C.c_void_p), ("count", C.c_uint64),
+                ("lr", C.c_float), ("mu", C.c_float), ("first_step", C.c_int), ("tag", C.c_uint64)]
+
+
+class KernelOuterStepC(C.Structure):
+    _fields_ = [("inner_in", C.c_void_p), ("params", C.c_void_p), ("momentum", C.c_void_p), ("inner_out", C.c_void_p),
+                ("lr", C.c_float), ("mu", C.c_float), ("first", C.c_int)]
+
+
 K_MAX_RANKS = 16
 
 
@@ -191,6 +201,7 @@ def lib() -> C.CDLL:
     sig("pcclExtSymmetricAlloc", i32, vp, sz, C.POINTER(vp))
     sig("pcclExtSymmetricFree", i32, vp, vp)
     sig("pcclExtDataTypeSize", sz, i32)
+    sig("pcclExtDiLoCoOuterStep", i32, C.POINTER(ExtOuterStepDescriptorC), vp, C.POINTER(ReduceInfoC))
     # kernels
     sig("pcclKernelHashScratchBytes", sz)
     sig("pcclKernelSimpleHash", i32, vp, sz, vp, vp, vp)
@@ -203,6 +214,9 @@ def lib() -> C.CDLL:
     sig("pcclKernelDequantizeReduce", i32, vp, vp, sz, i32, i32, vp)
     sig("pcclKernelAllReduceP2P", i32, C.POINTER(KernelP2PArgs), C.POINTER(i32), vp)
     sig("pcclKernelP2PStagingBytes", sz, u64, i32, i32)
+    sig("pcclKernelOuterStepP2P", i32, C.POINTER(KernelP2PArgs), C.POINTER(KernelOuterStepC), vp)
+    sig("pcclKernelPseudoGrad", i32, vp, vp, vp, sz, vp)
+    sig("pcclKernelOuterNesterov", i32, vp, vp, vp, vp, sz, C.c_float, C.c_float, i32, vp)
     sig("pcclKernelP2PControlBytes", sz)
     L.pcclInit()
     _lib = L

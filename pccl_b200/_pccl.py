@@ -465,6 +465,23 @@ class Communicator:
         return {"plane": names.get(st.plane, str(st.plane)), "device_ms": float(st.device_ms), "seq_nr": int(st.seq_nr),
                 "kernel_launches": int(st.kernel_launches)}
 
+    def ext_diloco_outer_step(self, params, inner, momentum, *, lr: float = 0.7, mu: float = 0.9, first: bool = False,
+                              tag: int = 0) -> ReduceInfo:
+        """DiLoCo outer step as ONE collective: g = mean over peers of (params - inner); momentum = g if `first` else
+        mu*momentum + g; params -= lr*(g + mu*momentum); inner = params  (torch.optim.SGD with nesterov=True).
+        float32, contiguous, all on the host or all on one GPU.  Between GPUs of one NVLink domain this is a single
+        kernel per peer; see pcclExtDiLoCoOuterStep in pccl.h.  Raises like `all_reduce`; tensors are untouched on failure."""
+        views = [_tensor_view(t) for t in (params, inner, momentum)]
+        n = views[0][1]
+        for _, cnt, dt, dev, _ in views:
+            assert cnt == n and dt == DataType.FLOAT and dev == views[0][3], "three float32 tensors of equal size on one device"
+        if views[0][3] == DeviceType.CUDA:
+            _sync_current_stream([params, inner, momentum])
+        d = _lib.ExtOuterStepDescriptorC(views[0][0], views[1][0], views[2][0], n, lr, mu, 1 if first else 0, tag)
+        info = _lib.ReduceInfoC()
+        PCCLError.check(lib().pcclExtDiLoCoOuterStep(C.byref(d), self._comm, C.byref(info)), "pcclExtDiLoCoOuterStep")
+        return ReduceInfo(info.local_world_size, info.tx_bytes, info.rx_bytes)
+
     def ext_symmetric_empty(self, numel: int, dtype) -> "torch.Tensor":
         """A CUDA tensor inside the communicator's peer-visible arena (needs PCCL_SYMMETRIC_MB).
         In-place reductions on such tensors skip the staging copy.  Every peer must allocate

@@ -152,3 +152,30 @@ def local_all_reduce(src: torch.Tensor, dst: torch.Tensor, arena: LocalArena, op
     with torch.cuda.device(src.device):
         _check(lib().pcclKernelAllReduceP2P(C.byref(args), C.byref(ran), _stream_ptr(src)), "pcclKernelAllReduceP2P")
     return ran.value
+
+
+def local_outer_step(params: torch.Tensor, inner: torch.Tensor, momentum: torch.Tensor, arena: LocalArena, lr: float, mu: float,
+                     first: bool, max_blocks: int = 0) -> None:
+    """The fused DiLoCo outer-step kernel (pseudo-gradient -> fp32 AVG all-reduce -> Nesterov update, ONE launch)
+    with world size 1 on the current stream.  With one rank the average is the local pseudo-gradient."""
+    for t in (params, inner, momentum):
+        assert t.is_cuda and t.is_contiguous() and t.dtype == torch.float32 and t.numel() == params.numel()
+    args = _lib.KernelP2PArgs()
+    args.arena[0] = arena.buf.data_ptr()
+    args.rank, args.world = 0, 1
+    args.flag_slot = 0
+    arena.epoch += 1
+    args.flag_base = arena.epoch * 16
+    args.data_offset = arena.control
+    args.data_capacity = arena.capacity
+    args.count = params.numel()
+    args.max_blocks = max_blocks
+    args.abort_flag = arena.words.data_ptr()
+    args.status = arena.words.data_ptr() + 4
+    args.timeout_cycles = 4_000_000_000
+    step = _lib.KernelOuterStepC()
+    step.inner_in = step.inner_out = inner.data_ptr()
+    step.params, step.momentum = params.data_ptr(), momentum.data_ptr()
+    step.lr, step.mu, step.first = lr, mu, 1 if first else 0
+    with torch.cuda.device(params.device):
+        _check(lib().pcclKernelOuterStepP2P(C.byref(args), C.byref(step), _stream_ptr(params)), "pcclKernelOuterStepP2P")

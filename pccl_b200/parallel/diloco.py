@@ -43,21 +43,30 @@ def outer_nesterov_(params: torch.Tensor, momentum: torch.Tensor, grad: torch.Te
 
 
 class LocalOuterStep:
-    """Outer step of a single peer (world size 1): the reduction runs through the same fused
-    kernel with one rank, so the numerics and the launch sequence match the multi-peer path."""
+    """Outer step of a single peer (world size 1) through the same kernels as the multi-peer path with one rank:
+    `step` is the fused kernel (pseudo-gradient, reduction, Nesterov update in ONE launch) plus the content hash,
+    `step_three_pass` the separate-kernels form it replaces (kept for comparison and as numerical cross-check)."""
 
     def __init__(self, params: torch.Tensor, lr: float = 0.7, momentum: float = 0.9):
         assert params.is_cuda and params.dtype == torch.float32 and params.is_contiguous()
         self.params = params
         self.lr, self.mu = lr, momentum
         self.buf = torch.zeros_like(params)
-        self.grad = torch.empty_like(params)
-        self.reduced = torch.empty_like(params)
+        self.grad = None  # scratch of the three-pass form, allocated on first use
+        self.reduced = None
         self.arena = ops.LocalArena(params.device, params.numel() * 4)
         self.steps = 0
-        self.launches_per_step = 4  # pseudo-grad, all-reduce, nesterov, hash
+        self.launches_per_step = 2  # fused outer step, hash
 
     def step(self, inner: torch.Tensor, want_hash: bool = True) -> int:
+        ops.local_outer_step(self.params, inner, self.buf, self.arena, self.lr, self.mu, self.steps == 0)
+        self.steps += 1
+        return ops.simplehash(self.params) if want_hash else 0
+
+    def step_three_pass(self, inner: torch.Tensor, want_hash: bool = True) -> int:
+        if self.grad is None:
+            self.grad = torch.empty_like(self.params)
+            self.reduced = torch.empty_like(self.params)
         pseudo_gradient(self.grad, self.params, inner)
         ops.local_all_reduce(self.grad, self.reduced, self.arena, op=ReduceOp.AVG)
         outer_nesterov_(self.params, self.buf, self.reduced, inner, self.lr, self.mu, self.steps == 0)
@@ -81,16 +90,33 @@ class DiLoCo:
         self.lr, self.mu = lr, momentum
         self.quantization = quantization
         self.buf = torch.zeros_like(params)
-        self.grad = torch.empty_like(params)
+        self.grad = None  # scratch for the quantised / single-peer path, allocated on first use
         self.steps = 0
         self.last_info = None
 
     def outer_step(self, inner: torch.Tensor, tag: int = 0) -> None:
+        """One collective call (`Communicator.ext_diloco_outer_step`): between GPUs of one NVLink domain the whole step
+        is a single kernel per peer.  With wire quantisation the three stages run separately (the quantised
+        reduction needs the pseudo-gradient in memory)."""
+        if self.quantization is None:
+            while True:
+                try:
+                    self.last_info = self.comm.ext_diloco_outer_step(self.params, inner, self.buf, lr=self.lr, mu=self.mu,
+                                                                     first=self.steps == 0, tag=tag)
+                    self.steps += 1
+                    return
+                except PCCLError as e:
+                    if e.result == Result.TOO_FEW_PEERS:
+                        break  # alone: apply the local pseudo-gradient below
+                    if e.result != Result.RANK_CONNECTION_LOST:
+                        raise
+        if self.grad is None:
+            self.grad = torch.empty_like(self.params)
         if self.params.is_cuda:
             pseudo_gradient(self.grad, self.params, inner)
         else:
             torch.sub(self.params, inner, out=self.grad)
-        while True:
+        while self.quantization is not None:
             try:
                 self.last_info = self.comm.all_reduce(self.grad, self.grad, op=ReduceOp.AVG, tag=tag,
                                                       quantization_options=self.quantization)

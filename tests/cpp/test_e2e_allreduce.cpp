@@ -336,4 +336,57 @@ TEST(buffers_in_guarded_blocks) {
     }
 }
 
+// DiLoCo outer step on host tensors (two-pass form over the TCP ring): two consecutive steps against a direct
+// evaluation of  g = mean(params - inner);  m = first ? g : mu*m + g;  params -= lr*(g + mu*m);  inner = params.
+TEST(outer_step_host_tensors) {
+    TestMaster tm;
+    const int world = 3;
+    auto peers = connect_peers(tm, world);
+    const size_t n = 1237;
+    const float lr = 0.7f, mu = 0.9f;
+    std::vector<std::vector<float>> params(world, std::vector<float>(n)), inner(world, std::vector<float>(n)), mom(world, std::vector<float>(n, 123.0f));
+    std::vector<float> ref_p(n), ref_m(n, 0.0f);
+    for (size_t i = 0; i < n; ++i) ref_p[i] = std::sin(0.01f * i);
+    for (int r = 0; r < world; ++r) params[r] = ref_p;
+    for (int step = 0; step < 2; ++step) {
+        // every peer drifted differently during its inner steps
+        for (int r = 0; r < world; ++r)
+            for (size_t i = 0; i < n; ++i) inner[r][i] = params[r][i] - 0.001f * static_cast<float>((i + 7 * r + step) % 13);
+        for (size_t i = 0; i < n; ++i) {
+            float g = 0;
+            for (int r = 0; r < world; ++r) g += ref_p[i] - inner[r][i];
+            g /= world;
+            ref_m[i] = step == 0 ? g : mu * ref_m[i] + g;
+            ref_p[i] -= lr * (g + mu * ref_m[i]);
+        }
+        std::vector<std::thread> ts;
+        for (int r = 0; r < world; ++r)
+            ts.emplace_back([&, r] {
+                device::OuterStepArgs o;
+                o.params = params[r].data();
+                o.inner = inner[r].data();
+                o.momentum = mom[r].data();
+                o.lr = lr;
+                o.mu = mu;
+                o.first = step == 0;
+                ReduceRequest req;
+                req.count = n;
+                req.op = wire::RedOp::Avg;
+                req.tag = 40;
+                req.outer = &o;
+                ReduceOutcome out;
+                CHECK(peers[r]->all_reduce_sync(req, out) == client::Client::Launch::Ok);
+                CHECK(out.ok);
+            });
+        for (auto &t : ts) t.join();
+        for (int r = 0; r < world; ++r)
+            for (size_t i = 0; i < n; ++i) {
+                CHECK(std::fabs(params[r][i] - ref_p[i]) < 1e-5f);
+                CHECK(std::fabs(mom[r][i] - ref_m[i]) < 1e-5f);
+                CHECK(inner[r][i] == params[r][i]);
+                CHECK(params[r][i] == params[0][i]); // bit-identical on all peers
+            }
+    }
+}
+
 TEST_MAIN()

@@ -185,6 +185,30 @@ def main():
         info2 = comm.sync_shared_state(state, pccl.SharedStateSyncStrategy.ENFORCE_POPULAR)
         ok_all = ok_all and info2.tx_bytes == 0 and info2.rx_bytes == 0
         results["cases"].append({"id": "shared_state", "ok": bool(ok_all), "tx": info.tx_bytes, "rx": info.rx_bytes})
+    elif scenario == "outer_step":
+        # DiLoCo outer step as one collective: every peer starts from the same parameters, drifts differently, and
+        # must end with the parameters a direct evaluation of the update gives (two steps: first and steady state)
+        n = 5_000_003
+        start = make_input(500, 0, n, torch.float32)
+        params = start.clone().to(dev)
+        inner = torch.empty_like(params)
+        mom = torch.full_like(params, 77.0)  # garbage: the first step must not read it
+        ref_p, ref_m = start.clone(), torch.zeros(n)
+        lr, mu = 0.7, 0.9
+        ok_all = True
+        for k in range(2):
+            drifts = [0.01 * make_input(510 + k, r, n, torch.float32) for r in range(world)]
+            inner.copy_((ref_p - drifts[rank]).to(dev))
+            g = sum((ref_p - (ref_p - d)) for d in drifts) / world
+            ref_m = g.clone() if k == 0 else mu * ref_m + g
+            ref_p = ref_p - lr * (g + mu * ref_m)
+            info = comm.ext_diloco_outer_step(params, inner, mom, lr=lr, mu=mu, first=k == 0, tag=7)
+            st = comm.ext_last_reduce_stats(7)
+            ok = (info.world_size == world and torch.allclose(params.cpu(), ref_p, rtol=1e-4, atol=1e-5) and
+                  torch.allclose(mom.cpu(), ref_m, rtol=1e-4, atol=1e-5) and torch.equal(inner, params))
+            ok_all = ok_all and ok
+            results["cases"].append({"id": f"outer_step_{k}", "ok": bool(ok), "plane": st["plane"], "ms": round(st["device_ms"], 4),
+                                     "launches": st["kernel_launches"], "hash": ops.simplehash(params)})
     results["ok"] = bool(ok_all)
     print(json.dumps(results), flush=True)
     comm.destroy()

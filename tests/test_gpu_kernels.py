@@ -182,3 +182,53 @@ def test_fused_quantised_allreduce_world1(algo, n):
     torch.testing.assert_close(out, twice, rtol=0, atol=1e-6)
     tol = 0.02 if algo == pccl.QuantizationAlgorithm.BLOCK_MIN_MAX else 0.08
     assert (out - x).abs().max().item() <= tol * x.abs().max().item() * 2
+
+
+# ---- fused DiLoCo outer step (one launch) against plain PyTorch fp32 -----------------------------
+@pytest.mark.parametrize("n", [1, 3, 4, 1000, 4099, 1 << 20, (1 << 22) + 5])
+@pytest.mark.parametrize("offset", [0, 1])
+def test_fused_outer_step_matches_torch(n, offset):
+    from pccl_b200.parallel.diloco import LocalOuterStep
+    dev = torch.device("cuda:0")
+    torch.manual_seed(n)
+
+    def place(t):  # offset 1: the tensor starts 4 bytes off a 16-byte boundary (scalar path of the kernel)
+        big = torch.empty(t.numel() + offset, device=dev)
+        view = big[offset:]
+        view.copy_(t)
+        return view
+
+    params = place(torch.randn(n, device=dev))
+    inner = place(params - 0.01 * torch.randn(n, device=dev))
+    step = LocalOuterStep(params, lr=0.7, momentum=0.9)
+    ref_p, ref_m = params.clone(), torch.zeros_like(params)
+    for k in range(3):
+        g = ref_p - inner
+        ref_m = g.clone() if k == 0 else 0.9 * ref_m + g
+        ref_p = ref_p - 0.7 * (g + 0.9 * ref_m)
+        step.step(inner, want_hash=False)
+        torch.cuda.synchronize()
+        torch.testing.assert_close(step.params, ref_p, rtol=1e-5, atol=1e-6)
+        torch.testing.assert_close(step.buf, ref_m, rtol=1e-5, atol=1e-6)
+        assert torch.equal(inner, step.params), "inner must receive the new parameters"
+        inner.sub_(0.003 * torch.randn_like(inner))  # next inner phase drifts again
+
+
+def test_fused_outer_step_equals_three_pass():
+    from pccl_b200.parallel.diloco import LocalOuterStep
+    dev = torch.device("cuda:0")
+    torch.manual_seed(5)
+    n = 3_000_001
+    outer = torch.randn(n, device=dev)
+    inner_a = outer - 0.02 * torch.randn(n, device=dev)
+    inner_b = inner_a.clone()
+    a, b = LocalOuterStep(outer.clone()), LocalOuterStep(outer.clone())
+    for _ in range(2):
+        a.step(inner_a, want_hash=False)
+        b.step_three_pass(inner_b, want_hash=False)
+        torch.cuda.synchronize()
+        torch.testing.assert_close(a.params, b.params, rtol=1e-6, atol=1e-7)
+        torch.testing.assert_close(a.buf, b.buf, rtol=1e-6, atol=1e-7)
+        torch.testing.assert_close(inner_a, inner_b, rtol=1e-6, atol=1e-7)
+        inner_a.sub_(0.01)
+        inner_b.sub_(0.01)

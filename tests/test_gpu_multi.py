@@ -14,13 +14,15 @@ pytestmark = [pytest.mark.gpu, pytest.mark.multigpu]
 HERE = Path(__file__).resolve().parent
 
 
-def run_peers(world: int, scenario: str, devices=None, timeout=600):
+def run_peers(world: int, scenario: str, devices=None, timeout=600, env=None):
+    import os
     master = pccl.MasterNode("127.0.0.1:0")
     master.run()
     port = master.port
     devices = devices or [f"cuda:{i}" for i in range(world)]
     procs = [subprocess.Popen([sys.executable, str(HERE / "peer_worker.py"), str(port), str(r), str(world), devices[r], scenario],
-                              stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True) for r in range(world)]
+                              stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, env=dict(os.environ, **(env or {})))
+             for r in range(world)]
     outs = []
     for p in procs:
         try:
@@ -84,3 +86,25 @@ def test_peer_killed_mid_reduction_on_the_device_plane(world):
         c = r["cases"][0]
         assert c["ok"], c
         assert c["seconds_to_fail"] is not None and c["seconds_to_fail"] < 10, c
+
+
+@pytest.mark.parametrize("world", worlds()[:2] or [pytest.param(2, marks=pytest.mark.skip(reason="needs >= 2 GPUs"))])
+def test_fused_diloco_outer_step(world):
+    """pseudo-gradient -> average -> Nesterov update as ONE kernel per peer (P2P two-shot at 2 GPUs, NVLS from 4)."""
+    results = run_peers(world, "outer_step")
+    for r in results:
+        assert r["ok"], r
+        for c in r["cases"]:
+            assert c["launches"] == 1 and (c["plane"] == "nvls" if world >= 4 else c["plane"] == "p2p_two_shot"), c
+    assert len({c["hash"] for r in results for c in r["cases"] if c["id"] == "outer_step_1"}) == 1, "peers must agree bit for bit"
+
+
+@pytest.mark.parametrize("world", worlds()[:1] or [pytest.param(2, marks=pytest.mark.skip(reason="needs >= 2 GPUs"))])
+def test_outer_step_larger_than_a_staging_slot(world):
+    """More elements than one staging slot holds: the library falls back to scratch buffer + plain reduction (several
+    launches on the device plane) + update, with the same result."""
+    results = run_peers(world, "outer_step", env={"PCCL_ARENA_SLOT_MB": "8", "PCCL_SYMMETRIC_MB": "0"})
+    for r in results:
+        assert r["ok"], r
+        assert all(c["launches"] > 1 for c in r["cases"]), r
+    assert len({c["hash"] for r in results for c in r["cases"] if c["id"] == "outer_step_1"}) == 1

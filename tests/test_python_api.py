@@ -172,7 +172,7 @@ def test_shared_state_revisions_and_strategies():
     assert res[0][1] == res[1][1] == 8
 
 
-@pytest.mark.parametrize("scenario", ["allreduce", "concurrent", "shared_state", "multiple"])
+@pytest.mark.parametrize("scenario", ["allreduce", "concurrent", "shared_state", "multiple", "outer_step"])
 def test_multi_process_peers_on_cpu(scenario):
     for r in run_peers(3, scenario, devices=["cpu"] * 3):
         assert r["ok"], r
