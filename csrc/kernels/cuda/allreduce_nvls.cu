@@ -318,17 +318,19 @@ __global__ void __launch_bounds__(kNvlsThreads, 1) outer_step_nvls_kernel(const 
     }
     if (!nvls_barrier(a, s_arena, a.flag_base + 2)) return;
 
-    nvls_owned_packets<2>(0, n_pack, [&](const uint64_t(&v)[2], const bool(&ok)[2]) {
-        uint4 g[2];
-        OuterLoaded l[2];
+    // 4 packets x 3 loads in flight per thread: with one 512-thread block per SM this phase needs ~45 KB
+    // outstanding per SM to keep HBM busy
+    nvls_owned_packets<4>(0, n_pack, [&](const uint64_t(&v)[4], const bool(&ok)[4]) {
+        uint4 g[4];
+        OuterLoaded l[4];
 #pragma unroll
-        for (int u = 0; u < 2; ++u)
+        for (int u = 0; u < 4; ++u)
             if (ok[u]) {
                 g[u] = ld_peer_16(mine + v[u]); // written through the switch: do not trust L1
                 l[u] = outer_load_packet(s, v[u], a.count);
             }
 #pragma unroll
-        for (int u = 0; u < 2; ++u)
+        for (int u = 0; u < 4; ++u)
             if (ok[u]) outer_apply_packet(s, v[u], a.count, g[u], l[u]);
     });
 }

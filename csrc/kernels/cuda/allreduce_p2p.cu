@@ -483,17 +483,17 @@ __global__ void __launch_bounds__(kThreads, 1) outer_step_two_shot_kernel(const 
         const uint32_t peer = (a.rank + k) % a.world;
         const uint4 *from = reinterpret_cast<const uint4 *>(tbl.base[peer]);
         const uint64_t lo = min(uint64_t(peer) * per, n_pack), hi = min(lo + per, n_pack);
-        for_owned_packets<2>(lo, hi, [&](const uint64_t(&v)[2], const bool(&ok)[2]) {
-            uint4 g[2];
-            OuterLoaded l[2];
+        for_owned_packets<4>(lo, hi, [&](const uint64_t(&v)[4], const bool(&ok)[4]) {
+            uint4 g[4];
+            OuterLoaded l[4];
 #pragma unroll
-            for (int u = 0; u < 2; ++u)
+            for (int u = 0; u < 4; ++u)
                 if (ok[u]) {
                     g[u] = ld_peer_16(from + v[u]);
                     l[u] = outer_load_packet(s, v[u], a.count);
                 }
 #pragma unroll
-            for (int u = 0; u < 2; ++u)
+            for (int u = 0; u < 4; ++u)
                 if (ok[u]) outer_apply_packet(s, v[u], a.count, g[u], l[u]);
         });
     }

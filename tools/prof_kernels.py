@@ -4,6 +4,7 @@
   python tools/prof_kernels.py hash      # simplehash + crc32c over 1 GiB
   python tools/prof_kernels.py allreduce # one-rank fused all-reduce over 600 MB
   python tools/prof_kernels.py quant     # block quantisers
+  python tools/prof_kernels.py outer     # DiLoCo outer step over 150 M parameters: fused kernel vs three kernels
 """
 import json
 import sys
@@ -66,6 +67,17 @@ def main():
         for q in (pccl.QuantizationAlgorithm.BLOCK_MIN_MAX, pccl.QuantizationAlgorithm.BLOCK_FP8):
             ms = timeit(lambda: ops.block_quantize(x, q))
             out[f"quantize_{q.name}_GBps_in"] = round(n * 4 / ms / 1e6, 1)
+    if what in ("outer", "all"):
+        from pccl_b200.parallel.diloco import LocalOuterStep
+        n = 150_000_000
+        outer = torch.randn(n, device=dev)
+        inner = outer - 0.01 * torch.randn(n, device=dev)
+        step = LocalOuterStep(outer)
+        step.step(inner, want_hash=False)
+        out["outer_step_fused_world1_ms"] = round(timeit(lambda: step.step(inner, want_hash=False)), 4)
+        # HBM traffic of the one-rank fused kernel: 2N+N staging, N+N reduce, 3N+3N update = 11N
+        out["outer_step_fused_world1_hbm_GBps"] = round(11 * n * 4 / out["outer_step_fused_world1_ms"] / 1e6, 1)
+        out["outer_step_three_kernels_world1_ms"] = round(timeit(lambda: step.step_three_pass(inner, want_hash=False)), 4)
     print(json.dumps(out))
 
 
