@@ -30,7 +30,7 @@ bool MuxSocket::interrupt() {
     stop_ = true;
     open_.store(false, std::memory_order_release);
     if (fd_ >= 0) ::shutdown(fd_, SHUT_RDWR);
-    tx_cv_.notify_all();
+    tx_signal_.bump();
     rx_cv_.notify_all();
     return true;
 }
@@ -59,45 +59,52 @@ std::shared_ptr<SendTicket> MuxSocket::send_bytes(uint64_t tag, uint64_t seq, co
         return ticket;
     }
     TxItem item{tag, seq, static_cast<const uint8_t *>(data), n, frame_bytes ? frame_bytes : n, {}, ticket};
-    {
-        std::lock_guard<std::mutex> lock(tx_mu_);
-        tx_queue_.push_back(std::move(item));
-    }
-    tx_cv_.notify_one();
+    if (!enqueue(std::move(item))) ticket->finish(false);
     return ticket;
+}
+
+// Blocks (politely) while the ring is full: the TX thread frees a cell with every request it finishes.
+bool MuxSocket::enqueue(TxItem &&item) {
+    for (int spins = 0; !tx_queue_.try_push(std::move(item)); ++spins) {
+        if (!is_open() || stop_) return false;
+        if (spins < 64)
+            std::this_thread::yield();
+        else
+            std::this_thread::sleep_for(std::chrono::microseconds(50));
+    }
+    tx_signal_.bump();
+    // The TX thread may have left for good between the is_open() check and the push; then the pusher takes over
+    // the consumer role (serialised by the mutex) so that no ticket is left waiting.
+    if (tx_exited_.load(std::memory_order_seq_cst)) {
+        std::lock_guard<std::mutex> lock(tx_drain_mu_);
+        fail_all_tx();
+    }
+    return true;
 }
 
 bool MuxSocket::send_owned(uint64_t tag, uint64_t seq, std::vector<uint8_t> bytes) {
     if (!is_open() || mode_ != Mode::Tx) return false;
     TxItem item{tag, seq, nullptr, bytes.size(), bytes.size(), std::move(bytes), nullptr};
-    {
-        std::lock_guard<std::mutex> lock(tx_mu_);
-        tx_queue_.push_back(std::move(item));
-    }
-    tx_cv_.notify_one();
-    return true;
+    return enqueue(std::move(item));
 }
 
+// the ring's single consumer: the TX thread, or -- after it has exited -- whoever holds tx_drain_mu_
 void MuxSocket::fail_all_tx() {
-    std::deque<TxItem> rest;
-    {
-        std::lock_guard<std::mutex> lock(tx_mu_);
-        rest.swap(tx_queue_);
-    }
-    for (auto &it : rest)
+    TxItem it;
+    while (tx_queue_.try_pop(it))
         if (it.ticket) it.ticket->finish(false);
 }
 
 void MuxSocket::tx_loop() {
     for (;;) {
         TxItem item;
-        {
-            std::unique_lock<std::mutex> lock(tx_mu_);
-            tx_cv_.wait(lock, [this] { return stop_ || !tx_queue_.empty(); });
-            if (stop_) break;
-            item = std::move(tx_queue_.front());
-            tx_queue_.pop_front();
+        bool have = false;
+        while (!stop_) {
+            const uint32_t seen = tx_signal_.load();
+            if ((have = tx_queue_.try_pop(item))) break;
+            tx_signal_.wait_while(seen, 200); // a push after the failed pop changes the word: no lost wake-up
         }
+        if (!have) break;
         const uint8_t *src = item.data ? item.data : item.owned.data();
         size_t left = item.n;
         bool ok = true;
@@ -143,6 +150,8 @@ void MuxSocket::tx_loop() {
         }
     }
     open_.store(false, std::memory_order_release);
+    tx_exited_.store(true, std::memory_order_seq_cst); // before the last drain: see enqueue()
+    std::lock_guard<std::mutex> lock(tx_drain_mu_);
     fail_all_tx();
 }
 

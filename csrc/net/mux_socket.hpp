@@ -20,6 +20,7 @@
 #include <vector>
 
 #include "../util/park.hpp"
+#include "../util/ring_queue.hpp"
 #include "../wire/packets.hpp"
 #include "addr.hpp"
 
@@ -106,9 +107,13 @@ private:
     std::atomic<bool> open_{true}, stop_{false};
     std::thread thread_;
 
-    std::mutex tx_mu_;
-    std::condition_variable tx_cv_;
-    std::deque<TxItem> tx_queue_;
+    // send requests: lock-free ring filled by any thread, drained by the TX thread, which sleeps on `tx_signal_`
+    static constexpr size_t kTxDepth = 1024;
+    MpscRing<TxItem> tx_queue_{kTxDepth};
+    Parker tx_signal_{0};
+    std::atomic<bool> tx_exited_{false};
+    std::mutex tx_drain_mu_;
+    bool enqueue(TxItem &&item);
 
     std::mutex rx_mu_;
     std::condition_variable rx_cv_;

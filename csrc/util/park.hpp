@@ -36,6 +36,12 @@ public:
         if (sleepers_.load(std::memory_order_seq_cst) != 0) futex(FUTEX_WAKE_PRIVATE, INT_MAX, nullptr);
     }
 
+    // Changes the word (by one) and wakes every sleeper: "something happened, look again".
+    void bump() {
+        word_.fetch_add(1, std::memory_order_seq_cst);
+        if (sleepers_.load(std::memory_order_seq_cst) != 0) futex(FUTEX_WAKE_PRIVATE, INT_MAX, nullptr);
+    }
+
     // Sleeps while the word equals `while_value`, at most `timeout_ms` (< 0: no limit).  Returns the word.
     uint32_t wait_while(uint32_t while_value, int timeout_ms) {
         uint32_t cur = load();

@@ -22,6 +22,7 @@
 #include "util/guard.hpp"
 #include "util/guarded_alloc.hpp"
 #include "util/park.hpp"
+#include "util/ring_queue.hpp"
 #include "wire/packets.hpp"
 
 using namespace pccl;
@@ -386,6 +387,47 @@ TEST(reduce_kernels_all_types) {
     CHECK_EQ(wire::dtype_size(DType::BF16), size_t(2)); // the reference reports 0 here (src/pccl.cpp:525-543)
     CHECK_EQ(wire::dtype_size(DType::I16), size_t(2));
     CHECK_EQ(wire::dtype_size(DType::F16), size_t(2));
+}
+
+TEST(mpsc_ring_keeps_per_producer_order) {
+    MpscRing<std::pair<int, int>> ring(64);
+    CHECK_EQ(ring.capacity(), 64u);
+    // full / empty behaviour
+    for (int i = 0; i < 64; ++i) CHECK(ring.try_push({0, i}));
+    std::pair<int, int> extra{9, 9}, got;
+    CHECK(!ring.try_push(std::move(extra)));
+    for (int i = 0; i < 64; ++i) CHECK(ring.try_pop(got) && got.second == i);
+    CHECK(!ring.try_pop(got));
+    // four producers, one consumer: nothing lost, nothing duplicated, each producer's items arrive in order
+    constexpr int kProducers = 4, kItems = 20000;
+    std::vector<std::thread> producers;
+    for (int p = 0; p < kProducers; ++p)
+        producers.emplace_back([&ring, p] {
+            for (int i = 0; i < kItems; ++i) {
+                std::pair<int, int> item{p, i};
+                while (!ring.try_push(std::move(item))) std::this_thread::yield();
+            }
+        });
+    int next[kProducers] = {0, 0, 0, 0};
+    for (int received = 0; received < kProducers * kItems;) {
+        if (!ring.try_pop(got)) {
+            std::this_thread::yield();
+            continue;
+        }
+        CHECK_EQ(got.second, next[got.first]);
+        ++next[got.first];
+        ++received;
+    }
+    for (auto &t : producers) t.join();
+    CHECK(!ring.try_pop(got));
+    // elements left inside are destroyed with the ring
+    auto counter = std::make_shared<int>(0);
+    {
+        MpscRing<std::shared_ptr<int>> owned(8);
+        for (int i = 0; i < 5; ++i) CHECK(owned.try_push(std::shared_ptr<int>(counter)));
+        CHECK_EQ(counter.use_count(), 6);
+    }
+    CHECK_EQ(counter.use_count(), 1);
 }
 
 TEST(parker_wakes_and_times_out) {
