@@ -564,14 +564,12 @@ void Master::handle_sync_shared_state(Client &c, const C2MSyncSharedState &p) {
             rs = RevisionStatus::Outdated;
         else if (p.revision > g.next_revision)
             return kick(c.link, "shared-state revision must grow by exactly one per synchronisation");
-    } else if (p.revision > 0) {
-        // the very first synchronisation of a group may start anywhere (resume from checkpoint)
-        g.next_revision = p.revision;
-        g.revision_initialised = true;
     }
+    // (The very first synchronisation of a group may start at any revision -- resume from a checkpoint.  Which one
+    // that is gets decided when all votes are in, see eval_sync_votes.)
     if (static_cast<uint8_t>(p.strategy) > 2) return kick(c.link, "unknown sync strategy");
     c.state = State::VoteSyncSharedState;
-    g.sync_votes.push_back({c.uuid, p.strategy, rs, p.entries});
+    g.sync_votes.push_back({c.uuid, p.strategy, rs, p.entries, p.revision});
     if (eval_sync_votes(c.group) == Verdict::Failed) {
         PLOG(WARN) << "shared-state synchronisation of group " << c.group << " cannot proceed, kicking the group";
         for (Client *peer : ordered_clients())
@@ -580,9 +578,17 @@ void Master::handle_sync_shared_state(Client &c, const C2MSyncSharedState &p) {
 }
 
 namespace {
+// Peers of the reference build leave num_elements at zero (ccoip_client_handler.cpp:411-415 never fills it in), so a
+// zero on either side means "not reported" rather than "empty tensor".
 bool same_shape(const SharedStateEntry &a, const SharedStateEntry &b) {
     return a.key == b.key && a.allow_content_inequality == b.allow_content_inequality && a.dtype == b.dtype &&
-           a.hash_type == b.hash_type && a.num_elements == b.num_elements;
+           a.hash_type == b.hash_type && (a.num_elements == b.num_elements || a.num_elements == 0 || b.num_elements == 0);
+}
+bool same_candidate(const std::vector<SharedStateEntry> &a, const std::vector<SharedStateEntry> &b) {
+    if (a.size() != b.size()) return false;
+    for (size_t i = 0; i < a.size(); ++i)
+        if (!same_shape(a[i], b[i]) || a[i].hash != b[i].hash) return false;
+    return true;
 }
 } // namespace
 
@@ -596,6 +602,17 @@ Master::Verdict Master::eval_sync_votes(uint32_t group) {
     }
     if (voting == 0 || voting != accepted || g.sync_votes.size() != voting) return Verdict::NotReady;
 
+    // First synchronisation of the group: the highest revision anybody brings is where the group starts, and peers
+    // below it are outdated.  (The reference fixes the starting revision to whatever the first non-zero VOTE carried,
+    // ccoip_master_state.cpp:1076-1086, so a resumed peer and fresh peers could end up either way round depending on
+    // packet arrival order; deciding with all votes on the table keeps the wire protocol and removes the race.)
+    if (!g.revision_initialised) {
+        uint64_t start = 0;
+        for (const auto &v : g.sync_votes) start = std::max(start, v.revision);
+        g.next_revision = start;
+        for (auto &v : g.sync_votes) v.rev_status = v.revision < start ? RevisionStatus::Outdated : RevisionStatus::Match;
+    }
+
     // ---- elect the reference content ("mask"): most votes among the candidates of the best
     // revision class; RECEIVE_ONLY peers do not stand for election.
     struct Tally {
@@ -607,7 +624,7 @@ Master::Verdict Master::eval_sync_votes(uint32_t group) {
     for (const auto &v : g.sync_votes) {
         if (v.strategy == SyncStrategy::RxOnly) continue;
         const int prio = v.rev_status == RevisionStatus::Match ? 1 : -2;
-        auto it = std::find_if(tallies.begin(), tallies.end(), [&](const Tally &t) { return *t.entries == v.entries; });
+        auto it = std::find_if(tallies.begin(), tallies.end(), [&](const Tally &t) { return same_candidate(*t.entries, v.entries); });
         if (it == tallies.end())
             tallies.push_back({&v.entries, 1, prio});
         else {

@@ -90,6 +90,7 @@ private:
         wire::SyncStrategy strategy;
         RevisionStatus rev_status;
         std::vector<wire::SharedStateEntry> entries;
+        uint64_t revision = 0;
     };
     struct Group {
         // shared-state sync

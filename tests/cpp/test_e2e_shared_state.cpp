@@ -291,4 +291,34 @@ TEST(content_inequality_allowed) {
     CHECK(st[0].buffers[0] != st[1].buffers[0]);
 }
 
+// First synchronisation of a group: the peer that resumes from a checkpoint (revision 5) wins over fresh peers
+// (revision 0) no matter whose vote reaches the master first, and the fresh peers adopt its revision.
+TEST(resumed_peer_wins_first_sync_in_any_vote_order) {
+    for (int late : {0, 1, 2}) {
+        TestMaster tm;
+        auto peers = connect_peers(tm, 3);
+        std::vector<PeerState> st(3);
+        st[0].add("w", 4096, 42);
+        st[0].args.revision = 5;
+        st[1].add("w", 4096, 1);
+        st[2].add("w", 4096, 1); // two fresh peers agree with each other: popularity alone would pick them
+        std::vector<std::thread> ts;
+        for (int i = 0; i < 3; ++i)
+            ts.emplace_back([&, i] {
+                if (i == late) std::this_thread::sleep_for(std::chrono::milliseconds(150));
+                st[i].ok = peers[i]->sync_shared_state(st[i].args, st[i].tx, st[i].rx);
+            });
+        for (auto &t : ts) t.join();
+        for (int i = 0; i < 3; ++i) {
+            CHECK(st[i].ok);
+            CHECK_EQ(st[i].buffers[0][0], 42);
+            CHECK_EQ(st[i].buffers[0][4095], 42);
+            CHECK_EQ(st[i].args.revision, 5u);
+        }
+        CHECK_EQ(st[0].rx, 0u);
+        CHECK_EQ(st[1].rx, 4096u);
+        CHECK_EQ(st[2].rx, 4096u);
+    }
+}
+
 TEST_MAIN()
