@@ -74,4 +74,10 @@ assert (info.rx_bytes == 0) == (rank == 0), (rank, info.tx_bytes, info.rx_bytes)
 state.revision = 2
 info = comm.sync_shared_state(state, pccl.SharedStateSyncStrategy.ENFORCE_POPULAR)
 assert info.rx_bytes == 0 and info.tx_bytes == 0, (info.tx_bytes, info.rx_bytes)
+# 5. (optional) topology optimisation: every peer measures its bandwidth to the others with the benchmark protocol
+if len(sys.argv) > 6 and sys.argv[6] == "topology":
+    comm.optimize_topology()
+    x = torch.ones(1000)
+    comm.all_reduce(x, x, op=pccl.ReduceOp.SUM, tag=77)
+    assert float(x[0]) == world
 print("PEER OK", flush=True)

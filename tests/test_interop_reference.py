@@ -13,7 +13,7 @@ pytestmark = pytest.mark.skipif(not (REPO / "baseline" / "_ref" / "pccl").exists
 PORT = [48790]
 
 
-def run_mix(master_impl, peer_impls):
+def run_mix(master_impl, peer_impls, extra=()):
     PORT[0] += 1
     port = PORT[0]
     master = subprocess.Popen([sys.executable, str(SCRIPT), "master", master_impl, str(port)], stdin=subprocess.PIPE, stdout=subprocess.PIPE,
@@ -21,7 +21,7 @@ def run_mix(master_impl, peer_impls):
     try:
         assert "MASTER UP" in master.stdout.readline()
         world = len(peer_impls)
-        peers = [subprocess.Popen([sys.executable, str(SCRIPT), "peer", impl, str(port), str(r), str(world)], stdout=subprocess.PIPE,
+        peers = [subprocess.Popen([sys.executable, str(SCRIPT), "peer", impl, str(port), str(r), str(world), *extra], stdout=subprocess.PIPE,
                                   stderr=subprocess.STDOUT, text=True) for r, impl in enumerate(peer_impls)]
         outs = []
         for p in peers:
@@ -52,3 +52,9 @@ def run_mix(master_impl, peer_impls):
 ], ids=["refmaster-ours", "ourmaster-ref", "ourmaster-mixed", "refmaster-mixed3"])
 def test_mixed_run(master_impl, peer_impls):
     run_mix(master_impl, peer_impls)
+
+
+def test_topology_optimisation_in_a_mixed_ring():
+    """The bandwidth-benchmark protocol (C2B hello, busy answer, timed blast) between the two implementations, followed by a
+    reduction on the re-ordered ring."""
+    run_mix("ours", ["ours", "ref"], extra=("topology",))
