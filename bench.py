@@ -98,6 +98,9 @@ def bus_factor(peers: int) -> float:
     return 2.0 * (peers - 1) / peers if peers > 1 else 1.0
 
 
+_MASTERS = []
+
+
 def run_ours(args) -> dict:
     import torch
 
@@ -149,6 +152,7 @@ def run_ours(args) -> dict:
         port_box = [0]
         if rank == 0:
             master = pccl.MasterNode("127.0.0.1:0")
+            _MASTERS.append(master)  # a running master that loses its last reference waits to be interrupted (reference semantics)
             master.run()
             port_box[0] = master.port
         dist.broadcast_object_list(port_box, src=0)
@@ -316,6 +320,9 @@ def run_ours(args) -> dict:
         comm.destroy()
     if dist:
         barrier()
+    if master is not None:
+        master.interrupt()
+    if dist:
         dist.destroy_process_group()
     return result if rank == 0 else {}
 

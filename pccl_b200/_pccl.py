@@ -10,6 +10,7 @@ after `import pccl_b200 as pccl` (reference: python/framework/pccl/_pccl.py:42-8
 from __future__ import annotations
 
 import ctypes as C
+import sys
 import time
 from enum import Enum
 from ipaddress import IPv4Address, IPv6Address, ip_address
@@ -532,10 +533,19 @@ def _sync_current_stream(objs) -> None:
 
 
 class MasterNode:
+    """A CCoIP master.  `run()` starts it on its own thread and returns; `interrupt()` stops it.
+
+    Like the reference's class (python/framework/pccl/_pccl.py:814-834), dropping the last reference to a master that runs
+    and was not interrupted BLOCKS until somebody interrupts it: the reference's master scripts consist of
+    `MasterNode(addr).run()` and rely on exactly that to stay alive.  Unlike the reference, the wait is interruptible
+    (Ctrl-C ends it and stops the master), and the object is a context manager whose exit interrupts:
+    `with MasterNode(addr) as m: m.run(); ...`."""
+
     def __init__(self, listen_address: str):
         host, port = _parse_host_port(listen_address)
         self._master = C.c_void_p()
         self._running = False
+        self._interrupted = False
         PCCLError.check(lib().pcclCreateMaster(_socket_address(host, port), C.byref(self._master)), "pcclCreateMaster")
 
     def run(self) -> None:
@@ -551,6 +561,14 @@ class MasterNode:
 
     def interrupt(self) -> None:
         PCCLError.check(lib().pcclInterruptMaster(self._master), "pcclInterruptMaster")
+        self._interrupted = True
+
+    def __enter__(self) -> "MasterNode":
+        return self
+
+    def __exit__(self, *exc) -> None:
+        if self._running and not self._interrupted and self._master:
+            self.interrupt()
 
     def __del__(self):
         m, self._master = getattr(self, "_master", None), None
@@ -558,8 +576,13 @@ class MasterNode:
             return
         try:
             if self._running:
-                lib().pcclInterruptMaster(m)
-                lib().pcclMasterAwaitTermination(m)
+                try:
+                    while not self._interrupted and not sys.is_finalizing():
+                        time.sleep(0.1)  # stays alive until interrupt(); a KeyboardInterrupt lands here
+                finally:
+                    if not self._interrupted:
+                        lib().pcclInterruptMaster(m)
+                    lib().pcclMasterAwaitTermination(m)
             lib().pcclDestroyMaster(m)
         except Exception:  # interpreter shutdown
             pass

@@ -21,9 +21,13 @@ import pccl_b200 as pccl  # noqa: E402
 
 
 def run(seconds: float, max_peers: int, stall: float, device: str, seed: int = 0) -> dict:
+    with pccl.MasterNode("127.0.0.1:0") as master:  # leaving the block interrupts the master
+        master.run()
+        return _run(master, seconds, max_peers, stall, device, seed)
+
+
+def _run(master, seconds: float, max_peers: int, stall: float, device: str, seed: int) -> dict:
     rng = random.Random(seed)
-    master = pccl.MasterNode("127.0.0.1:0")
-    master.run()
     port = master.port
     peers = []
     last_progress = [time.time()]

@@ -5,9 +5,18 @@ import subprocess
 import sys
 from pathlib import Path
 
+import pytest
+
 import pccl_b200 as pccl
 
 REPO = Path(__file__).resolve().parent.parent
+
+
+@pytest.fixture
+def master():
+    with pccl.MasterNode("127.0.0.1:0") as m:  # leaving the block interrupts the master, also when a check fails
+        m.run()
+        yield m
 
 
 def _env():
@@ -16,11 +25,9 @@ def _env():
     return env
 
 
-def test_fsdp_islands_share_shards_through_peer_groups():
+def test_fsdp_islands_share_shards_through_peer_groups(master):
     """Two islands of two FSDP ranks each: equal shard ranks form one PCCL peer group and must end every outer step
     with identical shard contents (reference: python/examples/nanogpt_diloco/sync_diloco_fsdp.py)."""
-    master = pccl.MasterNode("127.0.0.1:0")
-    master.run()
     procs = []
     for island in range(2):
         cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
@@ -32,7 +39,6 @@ def test_fsdp_islands_share_shards_through_peer_groups():
         out, _ = p.communicate(timeout=300)
         assert p.returncode == 0, out[-4000:]
         outs.append(out)
-    master.interrupt()
     digests = [dict(), dict()]
     for island, out in enumerate(outs):
         for m in re.finditer(r"\[island rank (\d+)\] outer step (\d+): .* islands (\d+) .* digest (\d+)", out):
@@ -43,9 +49,7 @@ def test_fsdp_islands_share_shards_through_peer_groups():
     assert digests[0][(0, 1)] != digests[0][(1, 1)]
 
 
-def test_diloco_example_two_peers_cpu():
-    master = pccl.MasterNode("127.0.0.1:0")
-    master.run()
+def test_diloco_example_two_peers_cpu(master):
     procs = [subprocess.Popen([sys.executable, str(REPO / "examples" / "diloco.py"), "--master", f"127.0.0.1:{master.port}", "--device", "cpu",
                                "--outer-steps", "2", "--inner-steps", "2", "--min-peers", "2"],
                               stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, env=_env()) for _ in range(2)]
@@ -53,20 +57,16 @@ def test_diloco_example_two_peers_cpu():
         out, _ = p.communicate(timeout=300)
         assert p.returncode == 0, out[-4000:]
         assert "outer step 1" in out and "world 2" in out, out[-2000:]
-    master.interrupt()
 
 
-def test_ddp_examples_cpu():
+def test_ddp_examples_cpu(master):
     """examples/ddp.py (two fault-tolerant peers) and the NCCL/gloo baseline examples/ddp_nccl.py both train."""
-    master = pccl.MasterNode("127.0.0.1:0")
-    master.run()
     procs = [subprocess.Popen([sys.executable, str(REPO / "examples" / "ddp.py"), "--master", f"127.0.0.1:{master.port}", "--device", "cpu",
                                "--steps", "3", "--min-peers", "2"], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, env=_env())
              for _ in range(2)]
     for p in procs:
         out, _ = p.communicate(timeout=300)
         assert p.returncode == 0, out[-4000:]
-    master.interrupt()
     base = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
                            "--master-port", "29640", str(REPO / "examples" / "ddp_nccl.py"), "--device", "cpu", "--steps", "3"],
                           stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, env=_env(), timeout=300)

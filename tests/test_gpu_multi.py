@@ -16,23 +16,22 @@ HERE = Path(__file__).resolve().parent
 
 def run_peers(world: int, scenario: str, devices=None, timeout=600, env=None):
     import os
-    master = pccl.MasterNode("127.0.0.1:0")
-    master.run()
-    port = master.port
-    devices = devices or [f"cuda:{i}" for i in range(world)]
-    procs = [subprocess.Popen([sys.executable, str(HERE / "peer_worker.py"), str(port), str(r), str(world), devices[r], scenario],
-                              stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, env=dict(os.environ, **(env or {})))
-             for r in range(world)]
-    outs = []
-    for p in procs:
-        try:
-            o, e = p.communicate(timeout=timeout)
-        except subprocess.TimeoutExpired:
-            for q in procs:
-                q.kill()
-            raise
-        outs.append((p.returncode, o, e))
-    master.interrupt()
+    with pccl.MasterNode("127.0.0.1:0") as master:  # leaving the block interrupts the master, also when a check fails
+        master.run()
+        port = master.port
+        devices = devices or [f"cuda:{i}" for i in range(world)]
+        procs = [subprocess.Popen([sys.executable, str(HERE / "peer_worker.py"), str(port), str(r), str(world), devices[r], scenario],
+                                  stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, env=dict(os.environ, **(env or {})))
+                 for r in range(world)]
+        outs = []
+        for p in procs:
+            try:
+                o, e = p.communicate(timeout=timeout)
+            except subprocess.TimeoutExpired:
+                for q in procs:
+                    q.kill()
+                raise
+            outs.append((p.returncode, o, e))
     results = []
     for rank, (rc, o, e) in enumerate(outs):
         if scenario == "kill" and rank == world - 1:

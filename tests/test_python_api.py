@@ -10,10 +10,26 @@ import pccl_b200 as pccl
 from test_gpu_multi import run_peers
 
 
+_MASTERS = []
+
+
 def start_master():
     m = pccl.MasterNode("127.0.0.1:0")
     m.run()
+    _MASTERS.append(m)
     return m, m.port
+
+
+@pytest.fixture(autouse=True)
+def _stop_masters():
+    # a running master that loses its last reference waits to be interrupted (reference semantics): a failing test
+    # must not leave one behind
+    yield
+    while _MASTERS:
+        try:
+            _MASTERS.pop().interrupt()
+        except Exception:
+            pass
 
 
 def join(port, world, **kw):
