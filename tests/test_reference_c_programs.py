@@ -1,0 +1,65 @@
+"""The reference's C / C++ API programs (tests/basic_reduce_test, tests/concurrent_reduce_test, tests/c99_compat), read
+in place from /root/reference and compiled UNMODIFIED against this repository's headers and library; the two
+all-reduce programs (endless loops by design) then run as two peers under `ccoip_master` until each has reported
+completed reductions.  Skipped where the reference tree is not mounted."""
+import os
+import select
+import subprocess
+import time
+from pathlib import Path
+
+import pytest
+
+REPO = Path(__file__).resolve().parent.parent
+REF = Path("/root/reference/tests")
+pytestmark = pytest.mark.skipif(not REF.exists(), reason="reference tree not mounted")
+
+
+def build(tmp_path, name: str) -> Path:
+    src = REF / name / ("enforce_c99_compat.c" if name == "c99_compat" else "main.cpp")
+    exe = tmp_path / name
+    lib = REPO / "pccl_b200" / "lib"
+    if src.suffix == ".c":
+        cmd = ["gcc", "-std=c99", "-pedantic"]
+    else:
+        cmd = ["/usr/bin/g++", "-std=c++20", "-O2", "-pthread"]
+    cmd += [f"-I{REPO / 'include'}", str(src), "-o", str(exe), f"-L{lib}", "-lpccl", f"-Wl,-rpath,{lib}"]
+    proc = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=300)
+    assert proc.returncode == 0, proc.stdout[-4000:]
+    return exe
+
+
+def test_c99_program(tmp_path):
+    assert subprocess.run([str(build(tmp_path, "c99_compat"))], timeout=60).returncode == 0
+
+
+@pytest.mark.parametrize("name,marker,wanted", [("concurrent_reduce_test", "All reduces finished sucessfully", 2),
+                                                ("basic_reduce_test", "All reduce finished", 1)])
+def test_reduce_program_runs_as_two_peers(tmp_path, name, marker, wanted):
+    exe = build(tmp_path, name)
+    master = subprocess.Popen([str(REPO / "pccl_b200" / "bin" / "ccoip_master")], stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+    peers = []
+    try:
+        time.sleep(0.5)
+        peers = [subprocess.Popen([str(exe)], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True) for _ in range(2)]
+        for p in peers:
+            os.set_blocking(p.stdout.fileno(), False)
+        seen, tail = [0, 0], ["", ""]
+        deadline = time.time() + 240
+        while time.time() < deadline and min(seen) < wanted:
+            ready, _, _ = select.select([p.stdout for p in peers], [], [], 1.0)
+            for i, p in enumerate(peers):
+                if p.stdout in ready:
+                    chunk = p.stdout.read() or ""
+                    tail[i] = (tail[i] + chunk)[-4000:]
+                    seen[i] += chunk.count(marker)
+                assert p.poll() is None, f"peer {i} exited with {p.returncode}:\n{tail[i]}"
+        assert min(seen) >= wanted, f"only {seen} completed rounds within the time limit\n{tail[0][-1500:]}\n{tail[1][-1500:]}"
+    finally:
+        for p in peers:
+            p.kill()
+        master.terminate()
+        try:
+            master.wait(timeout=20)
+        except subprocess.TimeoutExpired:
+            master.kill()
