@@ -68,6 +68,7 @@ class ReduceOp(Enum):
 class Attribute(Enum):
     GLOBAL_WORLD_SIZE = 1
     PEER_GROUP_WORLD_SIZE = 2
+    LOCAL_WORLD_SIZE = 2  # the name the reference's Python package uses for the same attribute (_pccl.py:106)
     NUM_DISTINCT_PEER_GROUPS = 3
     LARGEST_PEER_GROUP_WORLD_SIZE = 4
 

@@ -58,3 +58,52 @@ def test_topology_optimisation_in_a_mixed_ring():
     """The bandwidth-benchmark protocol (C2B hello, busy answer, timed blast) between the two implementations, followed by a
     reduction on the re-ordered ring."""
     run_mix("ours", ["ours", "ref"], extra=("topology",))
+
+
+def test_python_surface_is_a_superset_of_the_reference_package():
+    """Every public class, enum member, method and keyword argument of the reference's Python package exists here under
+    the same name (checked in a subprocess: the two packages each load a `libpccl.so`)."""
+    code = r'''
+import inspect, json, sys
+sys.path.insert(0, sys.argv[1] + "/baseline/_ref")
+import pccl as ref
+sys.path.pop(0)
+sys.path.insert(0, sys.argv[1])
+import pccl_b200 as ours
+internal = {"to_c", "ffi", "C", "load_native_module", "ModuleDummy", "PY_PCCL_DEBUG", "version", "pccl"}
+problems = []
+for name in dir(ref):
+    if name.startswith("_") or name in internal:
+        continue
+    r = getattr(ref, name)
+    if inspect.ismodule(r) and name != "cuda":
+        continue
+    if not inspect.isclass(r) and not inspect.ismodule(r):
+        continue
+    if getattr(r, "__module__", "pccl").split(".")[0] not in ("pccl",) and not inspect.ismodule(r):
+        continue  # re-exported typing / stdlib helpers
+    if not hasattr(ours, name):
+        problems.append(f"missing {name}")
+        continue
+    o = getattr(ours, name)
+    for member in dir(r):
+        if member.startswith("_") or member in internal:
+            continue
+        if not hasattr(o, member):
+            problems.append(f"missing {name}.{member}")
+            continue
+        rm, om = getattr(r, member), getattr(o, member)
+        if inspect.isfunction(rm) and inspect.isfunction(om):
+            rp, op = inspect.signature(rm).parameters, inspect.signature(om).parameters
+            for p in rp:
+                if p not in op:
+                    problems.append(f"{name}.{member}: parameter {p} missing")
+init_r, init_o = inspect.signature(ref.Communicator.__init__).parameters, inspect.signature(ours.Communicator.__init__).parameters
+problems += [f"Communicator(): parameter {p} missing" for p in init_r if p not in init_o]
+print(json.dumps(problems))
+'''
+    proc = subprocess.run([sys.executable, "-c", code, str(REPO)], stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, timeout=120)
+    assert proc.returncode == 0, proc.stderr[-3000:]
+    import json
+    problems = json.loads(proc.stdout.strip().splitlines()[-1])
+    assert problems == [], problems

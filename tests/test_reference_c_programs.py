@@ -63,3 +63,34 @@ def test_reduce_program_runs_as_two_peers(tmp_path, name, marker, wanted):
             master.wait(timeout=20)
         except subprocess.TimeoutExpired:
             master.kill()
+
+
+def test_public_header_declares_everything_the_reference_header_does():
+    """Function names, enumerator names/values/order and struct member order of include/pccl.h against the reference's
+    include/pccl.h (extensions may only be appended)."""
+    import re
+    ref_path = Path("/root/reference/include/pccl.h")
+    strip = lambda s: re.sub(r"/\*.*?\*/|//[^\n]*", "", s, flags=re.S)  # noqa: E731
+    ref, ours = strip(ref_path.read_text()), strip((REPO / "include" / "pccl.h").read_text())
+    functions = lambda s: set(re.findall(r"\b(pccl[A-Z]\w+)\s*\(", s))  # noqa: E731
+    assert functions(ref) <= functions(ours), sorted(functions(ref) - functions(ours))
+
+    def enums(s):
+        return {m.group(1): [re.sub(r"\s+", "", x) for x in m.group(2).split(",") if x.strip()]
+                for m in re.finditer(r"typedef\s+enum\s+(\w+)\s*\{(.*?)\}", s, flags=re.S)}
+
+    def structs(s):
+        out = {}
+        for m in re.finditer(r"typedef\s+struct\s+(\w+)\s*\{(.*?)\}\s*\w+\s*;", s, flags=re.S):
+            fields = [re.sub(r"\s+", " ", f.strip()) for f in m.group(2).split(";") if f.strip()]
+            out[m.group(1)] = [re.sub(r"PCCL_NULLABLE|const ", "", f).replace(" *", "*").split()[-1] for f in fields]
+        return out
+
+    ref_enums, our_enums = enums(ref), enums(ours)
+    assert len(ref_enums) >= 8
+    for name, members in ref_enums.items():
+        assert our_enums.get(name, [])[:len(members)] == members, (name, members, our_enums.get(name))
+    ref_structs, our_structs = structs(ref), structs(ours)
+    assert len(ref_structs) >= 10
+    for name, members in ref_structs.items():
+        assert our_structs.get(name, [])[:len(members)] == members, (name, members, our_structs.get(name))
