@@ -332,7 +332,9 @@ static pcclResult_t try_fused_multiple(const pcclReduceOpDescriptor_t *descripto
         in_parts.push_back({descriptors[i].sendbuf, descriptors[i].descriptor.count * esz});
         out_parts.push_back({descriptors[i].recvbuf, descriptors[i].descriptor.count * esz});
     }
+    std::unique_lock<std::mutex> scratch_guard;
     if (any_device) {
+        scratch_guard = plane.fuse_lock(); // one buffer per plane: held until the results are scattered back
         fused = static_cast<uint8_t *>(plane.fuse_buffer(total_bytes));
         if (!fused || !plane.gather(in_parts, fused, true)) return pcclInternalError;
     } else {

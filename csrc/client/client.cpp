@@ -856,7 +856,7 @@ ReduceOutcome Client::run_reduce(const ReduceRequest &req, uint64_t) {
         dargs.outer = nullptr;
         float *scratch = nullptr;
         if (send_info.is_device) {
-            scratch_lock = std::unique_lock<std::mutex>(outer_scratch_mu_);
+            scratch_lock = plane_->fuse_lock();
             scratch = static_cast<float *>(plane_->fuse_buffer(req.count * sizeof(float)));
             if (!scratch || !plane_->pseudo_grad(scratch, req.outer->params, req.outer->inner, req.count)) {
                 PLOG(ERR) << "outer step: cannot stage the pseudo-gradient on the device";

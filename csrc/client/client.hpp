@@ -163,7 +163,6 @@ private:
     std::map<uint64_t, StageBuf> stage_cache_;
     std::mutex deferred_mu_;
     std::map<uint64_t, Deferred> deferred_;
-    std::mutex outer_scratch_mu_;               // the plane's reusable device buffer holds one pseudo-gradient at a time
     std::atomic<bool> ring_stale_{false};       // a peer vanished after an operation had finished here: rewire before the next one
     std::atomic<bool> master_pipelines_{false}; // the master queues an Initiate behind a pending Complete
     std::mutex ops_mu_;

@@ -126,7 +126,9 @@ public:
         void *ptr;
         size_t bytes;
     };
+    // The buffer is one per plane: whoever uses it holds `fuse_lock()` from fuse_buffer() until it is done with the contents.
     virtual void *fuse_buffer(size_t bytes) = 0;
+    virtual std::unique_lock<std::mutex> fuse_lock() = 0;
     virtual bool gather(const std::vector<Part> &parts, void *fused, bool into_fused) = 0;
 
     // The two halves of the outer step as separate passes over device memory (used when the fused kernel cannot

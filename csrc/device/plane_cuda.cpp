@@ -198,7 +198,11 @@ public:
         }
         slot_bytes_ = round_up(env_u64("PCCL_ARENA_SLOT_MB", 768) << 20, 2u << 20);
         n_slots_ = static_cast<uint32_t>(std::clamp<uint64_t>(env_u64("PCCL_ARENA_SLOTS", 2), 1, 15));
-        sym_bytes_ = round_up(env_u64("PCCL_SYMMETRIC_MB", 1024) << 20, 2u << 20);
+        // symmetric heap = [caller's allocations][library scratch].  The scratch region has a FIXED offset, so peers
+        // with different allocation histories (late joiners, different tensor lists in the past) still agree on where
+        // an internally staged operand lives -- symmetric operands are addressed with one offset in every arena.
+        sym_bytes_ = round_up(env_u64("PCCL_SYMMETRIC_MB", 2048) << 20, 2u << 20);
+        internal_bytes_ = std::min<size_t>(sym_bytes_ / 2, round_up(env_u64("PCCL_INTERNAL_SCRATCH_MB", 1024) << 20, 2u << 20));
         timeout_ms_ = env_u64("PCCL_DEVICE_TIMEOUT_MS", 30000);
         max_blocks_ = static_cast<int>(env_u64("PCCL_DEVICE_MAX_BLOCKS", 0));
         nvls_min_world_ = static_cast<uint32_t>(env_u64("PCCL_NVLS_MIN_WORLD", 4));
@@ -633,19 +637,18 @@ public:
         if (!usable_) return nullptr;
         cudaSetDevice(device_);
         std::lock_guard<std::mutex> lock(fuse_mu_);
+        // the fixed scratch region of the symmetric heap when the operand fits: reduced in place, no staging
+        if (bytes <= internal_bytes_) {
+            std::lock_guard<std::mutex> arena_lock(mu_);
+            if (ensure_arena()) return reinterpret_cast<void *>(arena_ptr_ + sym_offset() + (sym_bytes_ - internal_bytes_));
+        }
         if (fuse_ptr_ && fuse_bytes_ >= bytes) return fuse_ptr_;
-        if (fuse_ptr_ && !fuse_symmetric_) cudaFree(fuse_ptr_);
-        if (fuse_ptr_ && fuse_symmetric_) symmetric_free(fuse_ptr_);
+        if (fuse_ptr_) cudaFree(fuse_ptr_);
         fuse_ptr_ = nullptr;
         fuse_bytes_ = 0;
         // grow generously: parameter lists do not change from step to step
         const size_t want = round_up(bytes + bytes / 8, 2u << 20);
-        if (void *p = symmetric_alloc(want)) {
-            fuse_ptr_ = p;
-            fuse_symmetric_ = true;
-        } else if (cudaMalloc(&fuse_ptr_, want) == cudaSuccess) {
-            fuse_symmetric_ = false;
-        } else {
+        if (cudaMalloc(&fuse_ptr_, want) != cudaSuccess) {
             (void) cudaGetLastError();
             fuse_ptr_ = nullptr;
             return nullptr;
@@ -653,6 +656,7 @@ public:
         fuse_bytes_ = want;
         return fuse_ptr_;
     }
+    std::unique_lock<std::mutex> fuse_lock() override { return std::unique_lock<std::mutex>(fuse_use_mu_); }
 
     bool gather(const std::vector<Part> &parts, void *fused, bool into_fused) override {
         if (!usable_) return false;
@@ -731,7 +735,7 @@ public:
             if (off - cursor >= bytes) break;
             cursor = off + len;
         }
-        if (cursor + bytes > sym_bytes_) return nullptr;
+        if (cursor + bytes > sym_bytes_ - internal_bytes_) return nullptr; // the tail belongs to fuse_buffer()
         sym_allocs_[cursor] = bytes;
         return reinterpret_cast<void *>(arena_ptr_ + sym_offset() + cursor);
     }
@@ -1188,7 +1192,7 @@ private:
     Multicast mc_;
     bool mc_ready_ = false;
     size_t mc_gran_ = 0;
-    size_t slot_bytes_ = 0, sym_bytes_ = 0, arena_bytes_ = 0;
+    size_t slot_bytes_ = 0, sym_bytes_ = 0, internal_bytes_ = 0, arena_bytes_ = 0;
     uint32_t n_slots_ = 4;
     uint64_t timeout_ms_ = 30000;
     int max_blocks_ = 0;
@@ -1211,10 +1215,9 @@ private:
     std::mutex copy_mu_;
     cudaStream_t util_stream_ = nullptr;
 
-    std::mutex fuse_mu_;
-    void *fuse_ptr_ = nullptr;
+    std::mutex fuse_mu_, fuse_use_mu_;
+    void *fuse_ptr_ = nullptr; // cudaMalloc'd fallback for operands beyond the scratch region
     size_t fuse_bytes_ = 0;
-    bool fuse_symmetric_ = false;
 };
 
 } // namespace

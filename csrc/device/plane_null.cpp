@@ -8,7 +8,7 @@ namespace pccl::device {
 #ifdef PCCL_NO_CUDA
 namespace {
 class NullPlane final : public Plane {
-    std::mutex mu_;
+    std::mutex mu_, fuse_use_mu_;
 
 public:
     void start(const Uuid &) override {}
@@ -23,6 +23,7 @@ public:
     bool copy_to_device(void *, const void *, size_t) override { return false; }
     bool hash_device(const void *, size_t, wire::HashType, uint64_t &) override { return false; }
     void *fuse_buffer(size_t) override { return nullptr; }
+    std::unique_lock<std::mutex> fuse_lock() override { return std::unique_lock<std::mutex>(fuse_use_mu_); }
     bool gather(const std::vector<Part> &, void *, bool) override { return false; }
     bool peer_mapped(const Uuid &) override { return false; }
     size_t exchange_bytes() override { return 0; }
