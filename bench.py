@@ -292,6 +292,34 @@ def run_ours(args) -> dict:
         nccl["diloco_outer_step_ms"] = round(timed(nccl_outer_step, max(3, args.steps // 2)), 4)
         del tmp
 
+    # ---- self-check (outside every timed region): our results against NCCL + torch on fresh random data -------------
+    verified = None
+    if dist and quant is None:
+        x = torch.randn(n, device=dev)
+        want = x.clone()
+        dist.all_reduce(want, op=dist.ReduceOp.AVG)
+        reduce_step(x, out)
+        ok = torch.allclose(out, want, rtol=1e-5, atol=1e-6)
+        if sym is not None:
+            sym.copy_(x)
+            reduce_step(sym, sym)
+            ok = ok and torch.allclose(sym, want, rtol=1e-5, atol=1e-6)
+        p = torch.randn(n, device=dev)
+        dist.broadcast(p, src=0)                       # outer parameters are replicated
+        q = p - 0.01 * torch.randn(n, device=dev)      # every peer drifted differently
+        m = torch.randn(n, device=dev)
+        dist.broadcast(m, src=0)
+        g = p - q
+        dist.all_reduce(g, op=dist.ReduceOp.AVG)
+        m_want = 0.9 * m + g
+        p_want = p - 0.7 * (g + 0.9 * m_want)
+        comm.ext_diloco_outer_step(p, q, m, lr=0.7, mu=0.9, first=False, tag=0)
+        ok = ok and torch.allclose(p, p_want, rtol=1e-4, atol=1e-5) and torch.allclose(m, m_want, rtol=1e-4, atol=1e-5) and torch.equal(p, q)
+        flag = torch.tensor([1.0 if ok else 0.0], device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        verified = bool(flag.item() == 1.0)
+        del x, want, p, q, m, g, m_want, p_want
+
     factor = bus_factor(world)
     value = nbytes * factor / (ms_step * 1e-3) / 1e9
     e2e_value = nbytes * factor / (ms_e2e * 1e-3) / 1e9
@@ -315,6 +343,7 @@ def run_ours(args) -> dict:
         "kernel_ms_per_step": round(kernel_ms, 4) if kernel_ms else None,
         "regular_buffers": regular,
         "nccl_same_run": nccl,
+        "verified_against_nccl": verified,
     }
     if comm is not None:
         comm.destroy()

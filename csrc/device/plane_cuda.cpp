@@ -207,7 +207,9 @@ public:
         max_blocks_ = static_cast<int>(env_u64("PCCL_DEVICE_MAX_BLOCKS", 0));
         nvls_min_world_ = static_cast<uint32_t>(env_u64("PCCL_NVLS_MIN_WORLD", 4));
         tune_ = env_flag("PCCL_DEVICE_TUNE", false);
-        pipeline_min_bytes_ = env_u64("PCCL_PIPELINE_MIN_MB", 48) << 20;
+        pipeline_min_bytes_ = env_u64("PCCL_PIPELINE_MIN_MB", 256) << 20; // below that the extra barriers eat the overlap
+        kernel_pipeline_ = env_flag("PCCL_KERNEL_PIPELINE", true);
+        pipeline_segments_ = env_u64("PCCL_PIPELINE_SEGMENTS", 0);
         pipeline_seg_bytes_ = std::max<uint64_t>(1, env_u64("PCCL_PIPELINE_SEGMENT_MB", 64)) << 20;
         nvls_min_bytes_ = env_u64("PCCL_NVLS_MIN_BYTES", 1u << 20);
     }
@@ -534,6 +536,10 @@ public:
             k.status = slot.host_words + 1;
             k.timeout_cycles = timeout_ms_ * static_cast<uint64_t>(clock_khz_);
             int rc;
+            // warp-specialised pipeline (copy-in || switch reduction || copy-out) for staged operands of one round
+            const bool kernel_pipeline = mc_view && !symmetric && quant == 0 && n_rounds == 1 && n * esz >= pipeline_min_bytes_ &&
+                                         (tune_ ? env_flag("PCCL_KERNEL_PIPELINE", kernel_pipeline_) : kernel_pipeline_);
+            const int segments = static_cast<int>(tune_ ? env_u64("PCCL_PIPELINE_SEGMENTS", 0) : pipeline_segments_);
             if (a.outer) {
                 pcclKernelOuterStep_t step{};
                 step.inner_in = step.inner_out = a.outer->inner;
@@ -546,7 +552,8 @@ public:
                     pcclKernelNvlsArgs_t nk{};
                     nk.p2p = k;
                     nk.mc_arena = mc_view;
-                    rc = pcclKernelOuterStepNvls(&nk, &step, slot.stream);
+                    rc = kernel_pipeline ? pcclKernelAllReduceNvlsPipelined(&nk, &step, segments, slot.stream)
+                                         : pcclKernelOuterStepNvls(&nk, &step, slot.stream);
                     algorithm = 3;
                 } else {
                     rc = pcclKernelOuterStepP2P(&k, &step, slot.stream);
@@ -556,7 +563,8 @@ public:
                 pcclKernelNvlsArgs_t nk{};
                 nk.p2p = k;
                 nk.mc_arena = mc_view;
-                rc = pcclKernelAllReduceNvls(&nk, slot.stream);
+                rc = kernel_pipeline ? pcclKernelAllReduceNvlsPipelined(&nk, nullptr, segments, slot.stream)
+                                     : pcclKernelAllReduceNvls(&nk, slot.stream);
                 algorithm = 3;
             } else {
                 rc = pcclKernelAllReduceP2P(&k, &algorithm, slot.stream);
@@ -1193,6 +1201,8 @@ private:
     bool mc_ready_ = false;
     size_t mc_gran_ = 0;
     size_t slot_bytes_ = 0, sym_bytes_ = 0, internal_bytes_ = 0, arena_bytes_ = 0;
+    bool kernel_pipeline_ = false;
+    uint64_t pipeline_segments_ = 0;
     uint32_t n_slots_ = 4;
     uint64_t timeout_ms_ = 30000;
     int max_blocks_ = 0;

@@ -15,6 +15,8 @@
 //   2  copy the own arena into the output            (skipped for symmetric memory, in place)
 // No trailing barrier is needed: a peer can only touch this arena again after the first barrier
 // of the NEXT operation, which this rank enters after its copy-out.
+#include <cmath>
+
 #include "common.cuh"
 #include "outer_step.cuh"
 #include "pccl_kernels.h"
@@ -335,6 +337,139 @@ __global__ void __launch_bounds__(kNvlsThreads, 1) outer_step_nvls_kernel(const 
     });
 }
 
+// -----------------------------------------------------------------------------------------
+// Software-pipelined variant for operands that are NOT in symmetric memory: the three phases of the staged
+// kernel above (copy-in / reduce through the switch / copy-out) run CONCURRENTLY on different segments.
+// The block is split into two warp groups: the "memory" group (HBM-bound: stages segment i into the arena and
+// writes segment i-2 out to the user buffer) and the "network" group (NVLink-bound: reduces segment i-1 through
+// the switch).  One cross-GPU barrier per segment keeps the three in step:
+//
+//   iteration i :   memory group  A(seg i)  [+ C(seg i-2)]   ||   network group  B(seg i-1)      ; barrier
+//
+// A(seg j) happens-before B(seg j) on every rank (barrier of iteration j), B(seg j) before C(seg j) (barrier of
+// iteration j+1), and the three touch disjoint arena regions within one iteration.
+// OUTER = true is the DiLoCo outer step: A computes the pseudo-gradient; the Nesterov update must not start before
+// the WHOLE average is known to be complete (a failed step may not leave a half-updated model behind), so there
+// C is not pipelined: it runs with all warps after the last barrier.
+// -----------------------------------------------------------------------------------------
+constexpr int kGroupThreads = kNvlsThreads / 2;
+
+template <int U, typename Fn> __device__ __forceinline__ void nvls_group_packets(uint64_t lo, uint64_t hi, int gtid, Fn fn) {
+    if (lo >= hi) return;
+    constexpr int SUB = kNvlsThreads / kGroupThreads; // a tile of 512 packets takes a 256-thread group two passes
+    const uint64_t first_tile = lo / kNvlsThreads;
+    const uint64_t t0 = first_tile + ((blockIdx.x + gridDim.x - first_tile % gridDim.x) % gridDim.x);
+    for (uint64_t q = 0;; q += U) {
+        if ((t0 + (q / SUB) * gridDim.x) * kNvlsThreads >= hi) break;
+        uint64_t v[U];
+        bool ok[U];
+#pragma unroll
+        for (int u = 0; u < U; ++u) {
+            const uint64_t qq = q + u;
+            v[u] = (t0 + (qq / SUB) * gridDim.x) * kNvlsThreads + (qq % SUB) * kGroupThreads + gtid;
+            ok[u] = v[u] >= lo && v[u] < hi;
+        }
+        fn(v, ok);
+    }
+}
+
+template <int TYPE, int OP, bool OUTER>
+__global__ void __launch_bounds__(kNvlsThreads, 1)
+    allreduce_nvls_pipelined_kernel(const NvlsArgs a, const OuterStepDev s, const uint32_t n_seg, const uint64_t seg_pack) {
+    constexpr int ESZ = TYPE == NV_F32 ? 4 : 2;
+    constexpr int N = 16 / ESZ;
+    __shared__ uint8_t *s_arena[PCCL_K_MAX_RANKS];
+    if (threadIdx.x < PCCL_K_MAX_RANKS) s_arena[threadIdx.x] = threadIdx.x < a.world ? a.arena[threadIdx.x] : nullptr;
+    __syncthreads();
+    const bool memory_group = threadIdx.x < kGroupThreads;
+    const int gtid = threadIdx.x % kGroupThreads;
+    const uint64_t n_pack = (a.count + N - 1) / N;
+    const uint8_t *src = static_cast<const uint8_t *>(a.src);
+    uint8_t *dst = static_cast<uint8_t *>(a.dst);
+    uint4 *mine = reinterpret_cast<uint4 *>(s_arena[a.rank] + a.data_offset);
+    uint4 *mc = reinterpret_cast<uint4 *>(a.mc + a.data_offset);
+    const uint64_t full_packets = a.count / N;
+    const bool aligned = OUTER || ((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst)) & 15) == 0;
+    const float inv = a.avg_divisor ? 1.0f / static_cast<float>(a.avg_divisor) : 1.0f;
+    const uint64_t per = seg_pack / a.world; // the launcher makes segments a multiple of world * tile
+    const uint32_t last_iter = OUTER ? n_seg : n_seg + 1;
+
+    for (uint32_t i = 0; i <= last_iter; ++i) {
+        if (memory_group) {
+            if (i < n_seg) { // A: stage segment i
+                const uint64_t lo = min(uint64_t(i) * seg_pack, n_pack), hi = min(lo + seg_pack, n_pack);
+                nvls_group_packets<4>(lo, hi, gtid, [&](const uint64_t(&v)[4], const bool(&ok)[4]) {
+                    uint4 tmp[4];
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        if (!ok[u]) continue;
+                        if constexpr (OUTER) {
+                            tmp[u] = outer_delta_packet(s, v[u], a.count);
+                        } else {
+                            if (aligned && v[u] < full_packets)
+                                tmp[u] = ld_stream_16(src + v[u] * 16);
+                            else
+                                tmp[u] = load_partial(src, v[u] * 16, min(v[u] * 16 + 16, uint64_t(a.count * ESZ)));
+                        }
+                    }
+#pragma unroll
+                    for (int u = 0; u < 4; ++u)
+                        if (ok[u]) mine[v[u]] = tmp[u];
+                });
+            }
+            if (!OUTER && i >= 2) { // C: write segment i-2 out
+                const uint64_t lo = min(uint64_t(i - 2) * seg_pack, n_pack), hi = min(lo + seg_pack, n_pack);
+                nvls_group_packets<4>(lo, hi, gtid, [&](const uint64_t(&v)[4], const bool(&ok)[4]) {
+                    uint4 tmp[4];
+#pragma unroll
+                    for (int u = 0; u < 4; ++u)
+                        if (ok[u]) tmp[u] = ld_peer_16(mine + v[u]);
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        if (!ok[u]) continue;
+                        if (aligned && v[u] < full_packets)
+                            st_stream_16(dst + v[u] * 16, tmp[u]);
+                        else
+                            store_partial(dst, v[u] * 16, min(v[u] * 16 + 16, uint64_t(a.count * ESZ)), tmp[u]);
+                    }
+                });
+            }
+        } else if (i >= 1 && i <= n_seg) { // B: reduce this rank's share of segment i-1 through the switch
+            const uint64_t slo = min(uint64_t(i - 1) * seg_pack, n_pack), shi = min(slo + seg_pack, n_pack);
+            const uint64_t lo = min(slo + uint64_t(a.rank) * per, shi), hi = min(lo + per, shi);
+            nvls_group_packets<8>(lo, hi, gtid, [&](const uint64_t(&v)[8], const bool(&ok)[8]) {
+                uint4 val[8];
+#pragma unroll
+                for (int u = 0; u < 8; ++u)
+                    if (ok[u]) val[u] = mc_ld_reduce<TYPE, OP>(mc + v[u]);
+#pragma unroll
+                for (int u = 0; u < 8; ++u) {
+                    if (!ok[u]) continue;
+                    if (a.avg_divisor) val[u] = scale_packet<TYPE>(val[u], inv);
+                    mc_store(mc + v[u], val[u]);
+                }
+            });
+        }
+        if (OUTER || i < last_iter)
+            if (!nvls_barrier(a, s_arena, a.flag_base + 1 + i)) return;
+    }
+    if constexpr (OUTER) {
+        nvls_owned_packets<4>(0, n_pack, [&](const uint64_t(&v)[4], const bool(&ok)[4]) {
+            uint4 g[4];
+            OuterLoaded l[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+                if (ok[u]) {
+                    g[u] = ld_peer_16(mine + v[u]);
+                    l[u] = outer_load_packet(s, v[u], a.count);
+                }
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+                if (ok[u]) outer_apply_packet(s, v[u], a.count, g[u], l[u]);
+        });
+    }
+}
+
 } // namespace pccl::cuda
 
 using namespace pccl::cuda;
@@ -438,5 +573,84 @@ extern "C" int pcclKernelOuterStepNvls(const pcclKernelNvlsArgs_t *args, const p
     const uint64_t chunk_tiles = (tiles + p.world - 1) / p.world;
     const int grid = static_cast<int>(std::max<uint64_t>(1, std::min<uint64_t>(max_blocks, chunk_tiles)));
     outer_step_nvls_kernel<<<grid, kNvlsThreads, 0, static_cast<cudaStream_t>(stream_v)>>>(d, s);
+    return cudaGetLastError();
+}
+
+// Segments of the pipelined kernel.  With S segments the kernel takes about  T_reduce + (T_in + T_out)/S + (S+2)*b
+// (b = one cross-GPU barrier, measured ~15 us; T_in + T_out ~ 0.4 ms for 600 MB), minimal at S = sqrt((T_in+T_out)/b):
+// 5 for 600 MB, growing with the square root of the size (measured on 4xB200: 3:1.54  4:1.52  5:1.51  6:1.53  8:1.58
+// 12:1.71 ms against 1.73 ms unpipelined, profiles/tune4_kernel_pipeline.jsonl).  Segments are a whole number of
+// (world x tile) packets.
+static void pipeline_geometry(uint64_t n_pack, uint32_t world, int requested, uint32_t &n_seg, uint64_t &seg_pack) {
+    uint64_t want = requested > 0 ? static_cast<uint64_t>(requested)
+                                  : static_cast<uint64_t>(5.2 * std::sqrt(static_cast<double>(n_pack) * 16.0 / 6.0e8) + 0.5);
+    want = std::min<uint64_t>(24, std::max<uint64_t>(2, want));
+    const uint64_t unit = uint64_t(world) * kNvlsThreads;
+    seg_pack = ((n_pack + want - 1) / want + unit - 1) / unit * unit;
+    n_seg = static_cast<uint32_t>((n_pack + seg_pack - 1) / seg_pack);
+}
+
+extern "C" int pcclKernelAllReduceNvlsPipelined(const pcclKernelNvlsArgs_t *args, const pcclKernelOuterStep_t *step, int segments,
+                                                void *stream_v) {
+    if (!args || !args->mc_arena) return cudaErrorInvalidValue;
+    const pcclKernelP2PArgs_t &p = args->p2p;
+    if (p.world < 2 || p.world > PCCL_K_MAX_RANKS || p.rank >= p.world || p.count == 0) return cudaErrorInvalidValue;
+    const int dtype = step ? static_cast<int>(pcclFloat) : p.dtype;
+    const int rop = step ? static_cast<int>(pcclAvg) : p.op;
+    if (!pcclKernelNvlsSupported(dtype, rop)) return cudaErrorInvalidValue;
+    if (step && (!step->params || !step->inner_in || !step->momentum)) return cudaErrorInvalidValue;
+    NvlsArgs d{};
+    for (uint32_t r = 0; r < p.world; ++r) d.arena[r] = static_cast<uint8_t *>(p.arena[r]);
+    d.mc = static_cast<uint8_t *>(args->mc_arena);
+    d.rank = p.rank;
+    d.world = p.world;
+    d.flag_slot = p.flag_slot;
+    d.flag_base = p.flag_base;
+    d.data_offset = p.data_offset;
+    d.src = p.src;
+    d.dst = p.dst;
+    d.count = p.count;
+    d.avg_divisor = rop == pcclAvg ? p.world : 0;
+    d.abort_flag = p.abort_flag;
+    d.status = p.status;
+    d.timeout_cycles = p.timeout_cycles ? p.timeout_cycles : ~0ull;
+    const size_t esz = dtype == pcclFloat ? 4 : 2;
+    if ((p.count * esz + 15) / 16 * 16 + 256 > p.data_capacity || p.data_offset % 16 != 0) return cudaErrorInvalidValue;
+    OuterStepDev s{};
+    if (step) {
+        s.inner_in = step->inner_in;
+        s.params = step->params;
+        s.momentum = step->momentum;
+        s.inner_out = step->inner_out;
+        s.lr = step->lr;
+        s.mu = step->mu;
+        s.first = step->first;
+        s.aligned = ((reinterpret_cast<uintptr_t>(s.inner_in) | reinterpret_cast<uintptr_t>(s.params) | reinterpret_cast<uintptr_t>(s.momentum) |
+                      reinterpret_cast<uintptr_t>(s.inner_out)) & 15) == 0;
+    }
+    const uint64_t n_pack = (p.count * esz + 15) / 16;
+    uint32_t n_seg = 0;
+    uint64_t seg_pack = 0;
+    pipeline_geometry(n_pack, p.world, segments, n_seg, seg_pack);
+    int max_blocks = p.max_blocks > 0 ? p.max_blocks : 144;
+    if (max_blocks > PCCL_K_MAX_BLOCKS) max_blocks = PCCL_K_MAX_BLOCKS;
+    // the network group's share of one segment decides how many blocks have work in every iteration
+    const uint64_t chunk_tiles = std::max<uint64_t>(1, seg_pack / p.world / kNvlsThreads);
+    const int grid = static_cast<int>(std::max<uint64_t>(1, std::min<uint64_t>(max_blocks, chunk_tiles)));
+    const auto stream = static_cast<cudaStream_t>(stream_v);
+    const int op = rop == pcclMax ? OP_MAX : (rop == pcclMin ? OP_MIN : OP_SUM);
+    if (step) {
+        allreduce_nvls_pipelined_kernel<NV_F32, OP_SUM, true><<<grid, kNvlsThreads, 0, stream>>>(d, s, n_seg, seg_pack);
+    } else if (dtype == pcclFloat) {
+        allreduce_nvls_pipelined_kernel<NV_F32, OP_SUM, false><<<grid, kNvlsThreads, 0, stream>>>(d, s, n_seg, seg_pack);
+    } else if (dtype == pcclBFloat16) {
+        if (op == OP_SUM) allreduce_nvls_pipelined_kernel<NV_BF16, OP_SUM, false><<<grid, kNvlsThreads, 0, stream>>>(d, s, n_seg, seg_pack);
+        else if (op == OP_MAX) allreduce_nvls_pipelined_kernel<NV_BF16, OP_MAX, false><<<grid, kNvlsThreads, 0, stream>>>(d, s, n_seg, seg_pack);
+        else allreduce_nvls_pipelined_kernel<NV_BF16, OP_MIN, false><<<grid, kNvlsThreads, 0, stream>>>(d, s, n_seg, seg_pack);
+    } else {
+        if (op == OP_SUM) allreduce_nvls_pipelined_kernel<NV_F16, OP_SUM, false><<<grid, kNvlsThreads, 0, stream>>>(d, s, n_seg, seg_pack);
+        else if (op == OP_MAX) allreduce_nvls_pipelined_kernel<NV_F16, OP_MAX, false><<<grid, kNvlsThreads, 0, stream>>>(d, s, n_seg, seg_pack);
+        else allreduce_nvls_pipelined_kernel<NV_F16, OP_MIN, false><<<grid, kNvlsThreads, 0, stream>>>(d, s, n_seg, seg_pack);
+    }
     return cudaGetLastError();
 }

@@ -102,6 +102,14 @@ typedef struct pcclKernelNvlsArgs_t {
     void *mc_arena; /* multicast view */
 } pcclKernelNvlsArgs_t;
 PCCL_EXPORT int pcclKernelAllReduceNvls(const pcclKernelNvlsArgs_t *args, void *stream);
+/* Software-pipelined form for operands outside symmetric memory: copy-in of segment i, switch reduction of segment
+ * i-1 and copy-out of segment i-2 run concurrently on two warp groups of every block (one cross-GPU barrier per
+ * segment).  `step` non-NULL runs the DiLoCo outer step instead of a plain all-reduce (see pcclKernelOuterStepNvls
+ * below; its update phase is not pipelined so that a failed step leaves the tensors untouched).
+ * `segments` 0 = about 32 MiB each.  flag_base must leave room for segments + 2 barrier values. */
+struct pcclKernelOuterStep_t;
+PCCL_EXPORT int pcclKernelAllReduceNvlsPipelined(const pcclKernelNvlsArgs_t *args, const struct pcclKernelOuterStep_t *step, int segments,
+                                                 void *stream);
 /* 1 when multimem.ld_reduce can do (dtype, op). */
 PCCL_EXPORT int pcclKernelNvlsSupported(int dtype, int op);
 

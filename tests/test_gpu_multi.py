@@ -107,3 +107,18 @@ def test_outer_step_larger_than_a_staging_slot(world):
         assert r["ok"], r
         assert all(c["launches"] > 1 for c in r["cases"]), r
     assert len({c["hash"] for r in results for c in r["cases"] if c["id"] == "outer_step_1"}) == 1
+
+
+@pytest.mark.parametrize("world", [w for w in worlds() if w >= 4][:1] or [pytest.param(4, marks=pytest.mark.skip(reason="needs >= 4 GPUs (NVLS)"))])
+def test_pipelined_nvls_kernel(world):
+    """The warp-specialised pipeline (copy-in || switch reduction || copy-out) on every staged NVLS operation, including the
+    DiLoCo outer step, with the same expectations as the plain kernels."""
+    env = {"PCCL_KERNEL_PIPELINE": "1", "PCCL_PIPELINE_MIN_MB": "0"}
+    for r in run_peers(world, "allreduce", env=env):
+        assert r["ok"], r
+        assert any(c["plane"] == "nvls" for c in r["cases"]), r
+    results = run_peers(world, "outer_step", env=env)
+    for r in results:
+        assert r["ok"], r
+        assert all(c["launches"] == 1 and c["plane"] == "nvls" for c in r["cases"]), r
+    assert len({c["hash"] for r in results for c in r["cases"] if c["id"] == "outer_step_1"}) == 1
