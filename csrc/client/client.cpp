@@ -995,13 +995,13 @@ ReduceOutcome Client::run_reduce(const ReduceRequest &req, uint64_t) {
         ctx.abort_requested = abort_requested;
         bool wired = true;
         if (world >= 2) {
-            const Uuid &next = ring[(rank + 1) % world], &prev = ring[(rank + world - 1) % world];
+            const Uuid &next = ring[(rank + 1) % world], &before = ring[(rank + world - 1) % world];
             {
                 std::lock_guard<std::mutex> lock(tx_mu_);
                 const auto it = tx_pools_.find(next);
                 if (it != tx_pools_.end()) ctx.tx = it->second;
             }
-            ctx.rx = pick_rx_pool(prev, 10000);
+            ctx.rx = pick_rx_pool(before, 10000);
             wired = !ctx.tx.empty() && ctx.tx.size() == ctx.rx.size();
             if (!wired) PLOG(WARN) << "no usable p2p link for tag " << req.tag;
         }
