@@ -27,8 +27,8 @@ size_t frame_bytes_from_env() {
 } // namespace
 
 Client::Client(const ClientConfig &cfg)
-    : cfg_(cfg), master_(cfg.master), p2p_listener_(net::any_v4(cfg.p2p_port), true),
-      ss_listener_(net::any_v4(cfg.ss_port), true), bm_listener_(net::any_v4(cfg.bm_port), true),
+    : cfg_(cfg), master_(cfg.master), p2p_listener_(net::any_like(cfg.master, cfg.p2p_port), true),
+      ss_listener_(net::any_like(cfg.master, cfg.ss_port), true), bm_listener_(net::any_like(cfg.master, cfg.bm_port), true),
       plane_(device::Plane::create()) {
     if (cfg_.pool_size == 0) cfg_.pool_size = 1;
     const size_t n_workers = static_cast<size_t>(env_u64("PCCL_MAX_CONCURRENT_COLLECTIVE_OPS", 16));

@@ -97,4 +97,12 @@ ccoip_socket_address_t any_v4(uint16_t port) {
     return a;
 }
 
+ccoip_socket_address_t any_like(const ccoip_socket_address_t &like, uint16_t port) {
+    if (like.inet.protocol == inetIPv4) return any_v4(port);
+    ccoip_socket_address_t a{};
+    a.inet.protocol = inetIPv6; // all-zero address = "::"
+    a.port = port;
+    return a;
+}
+
 } // namespace pccl::net

@@ -20,6 +20,8 @@ std::string to_string(const ccoip_socket_address_t &a);
 bool parse_address(const std::string &text, ccoip_socket_address_t &out); // "1.2.3.4:80" or "[::1]:80"
 bool is_loopback(const ccoip_socket_address_t &a);
 ccoip_socket_address_t any_v4(uint16_t port);
+// Wildcard address of the same family as `like` ("::" listens dual-stack, see listen_tcp).
+ccoip_socket_address_t any_like(const ccoip_socket_address_t &like, uint16_t port);
 
 // Value type usable as map key.
 struct AddrKey {

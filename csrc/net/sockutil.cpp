@@ -20,6 +20,10 @@ int listen_tcp(const ccoip_socket_address_t &addr, bool bump, uint16_t &bound_po
         // No SO_REUSEADDR when bumping: two peers on one host must not share a port.
         int one = 1;
         if (!bump) setsockopt(fd, SOL_SOCKET, SO_REUSEADDR, &one, sizeof one);
+        if (family == AF_INET6) { // an IPv6 wildcard listener also takes IPv4 peers (mapped addresses)
+            int v6only = 0;
+            setsockopt(fd, IPPROTO_IPV6, IPV6_V6ONLY, &v6only, sizeof v6only);
+        }
         sockaddr_storage ss;
         const socklen_t len = to_sockaddr(a, ss);
         if (::bind(fd, reinterpret_cast<sockaddr *>(&ss), len) == 0 && ::listen(fd, 512) == 0) {

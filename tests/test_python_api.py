@@ -222,3 +222,50 @@ def test_peer_killed_mid_run_recovers_quickly():
         c = r["cases"][0]
         assert c["ok"], c
         assert c["seconds_to_fail"] < 5, c
+
+
+def _ipv6_available() -> bool:
+    import socket
+    try:
+        s = socket.socket(socket.AF_INET6, socket.SOCK_STREAM)
+        s.bind(("::1", 0))
+        s.close()
+        return True
+    except OSError:
+        return False
+
+
+@pytest.mark.skipif(not _ipv6_available(), reason="no IPv6 loopback")
+def test_everything_over_ipv6_loopback():
+    """Master, p2p ring, shared-state server: all reachable through [::1] when the master address is IPv6."""
+    with pccl.MasterNode("[::1]:0") as m:
+        m.run()
+        port = m.port
+        errors, results = [], {}
+
+        def body(rank):
+            try:
+                c = pccl.Communicator(f"[::1]:{port}", p2p_listen_port=48940 + 8 * rank, shared_state_listen_port=48941 + 8 * rank,
+                                      benchmark_listen_port=48942 + 8 * rank)
+                c.connect(n_attempts=10)
+                while c.get_attribute(pccl.Attribute.GLOBAL_WORLD_SIZE) < 2:
+                    c.update_topology()
+                x = torch.full((50_000,), float(rank + 1))
+                y = torch.empty_like(x)
+                c.all_reduce(x, y, op=pccl.ReduceOp.SUM)
+                w = torch.full((10_000,), 7.0 if rank == 0 else -1.0)
+                st = pccl.SharedState([pccl.TensorInfo.from_torch(w, "w")])
+                st.revision = 1
+                info = c.sync_shared_state(st, pccl.SharedStateSyncStrategy.SEND_ONLY if rank == 0 else pccl.SharedStateSyncStrategy.RECEIVE_ONLY)
+                results[rank] = (float(y[0]), float(w[-1]), info.rx_bytes)
+                c.destroy()
+            except Exception as e:  # noqa: BLE001
+                errors.append(e)
+
+        ts = [threading.Thread(target=body, args=(r,)) for r in range(2)]
+        for t in ts:
+            t.start()
+        for t in ts:
+            t.join(timeout=120)
+    assert not errors, errors
+    assert results[0] == (3.0, 7.0, 0) and results[1] == (3.0, 7.0, 40_000), results
