@@ -49,9 +49,10 @@ def test_fsdp_islands_share_shards_through_peer_groups(master):
     assert digests[0][(0, 1)] != digests[0][(1, 1)]
 
 
-def test_diloco_example_two_peers_cpu(master):
+@pytest.mark.parametrize("mode", ["sync", "async"])
+def test_diloco_example_two_peers_cpu(master, mode):
     procs = [subprocess.Popen([sys.executable, str(REPO / "examples" / "diloco.py"), "--master", f"127.0.0.1:{master.port}", "--device", "cpu",
-                               "--outer-steps", "2", "--inner-steps", "2", "--min-peers", "2"],
+                               "--outer-steps", "2", "--inner-steps", "2", "--min-peers", "2", "--mode", mode],
                               stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, env=_env()) for _ in range(2)]
     for p in procs:
         out, _ = p.communicate(timeout=300)

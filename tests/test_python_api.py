@@ -269,3 +269,54 @@ def test_everything_over_ipv6_loopback():
             t.join(timeout=120)
     assert not errors, errors
     assert results[0] == (3.0, 7.0, 0) and results[1] == (3.0, 7.0, 40_000), results
+
+
+def test_async_diloco_applies_each_average_one_step_late():
+    """AsyncDiLoCo: the reduction of step t overlaps the next inner phase and is applied at step t+1 (flush applies the last
+    one).  With pseudo-gradients that do not depend on the parameters the end result must equal plain Nesterov-SGD over the
+    same sequence of averages, and all peers must agree bit for bit."""
+    from pccl_b200.parallel import AsyncDiLoCo
+
+    def body(r, c):
+        params = torch.randn(3000, generator=torch.Generator().manual_seed(0))  # (the global generator is shared between threads)
+        ref = params.clone().requires_grad_(True)
+        opt = torch.optim.SGD([ref], lr=0.7, momentum=0.9, nesterov=True)
+        d = AsyncDiLoCo(c, params, lr=0.7, momentum=0.9)
+        applied_before = []
+        for step in range(4):
+            inner = params - 0.01 * (step + 1) * (r + 1)
+            assert d.outer_step(inner)
+            applied_before.append(d.applied)
+            assert torch.equal(inner, params)
+        assert applied_before == [0, 1, 2, 3]  # step t applies the average of step t-1
+        d.flush()
+        assert d.applied == 4
+        for step in range(4):
+            ref.grad = torch.full_like(ref, 0.015 * (step + 1))
+            opt.step()
+        torch.testing.assert_close(params, ref.detach(), rtol=1e-5, atol=1e-6)
+        return params.clone()
+
+    res = run_threads(2, body)
+    assert torch.equal(res[0], res[1])
+
+
+def test_gradient_averager_cpu():
+    """GradientAverager: flatten .grad, average over the group, scatter back; parameters without a gradient count as zero."""
+    from pccl_b200.parallel import GradientAverager
+
+    def body(r, c):
+        torch.manual_seed(1)
+        model = torch.nn.Sequential(torch.nn.Linear(8, 16), torch.nn.Linear(16, 4))
+        for i, p in enumerate(model.parameters()):
+            p.grad = torch.full_like(p, float((r + 1) * (i + 1)))
+        list(model.parameters())[-1].grad = None  # e.g. an unused head
+        avg = GradientAverager(c, model.parameters())
+        assert avg.average()
+        params = list(model.parameters())
+        for i, p in enumerate(params[:-1]):
+            assert torch.allclose(p.grad, torch.full_like(p, 1.5 * (i + 1)))
+        assert params[-1].grad is None
+        return True
+
+    assert all(run_threads(2, body).values())
