@@ -321,4 +321,80 @@ TEST(resumed_peer_wins_first_sync_in_any_vote_order) {
     }
 }
 
+// popularity with several keys: the peer that votes first holds the minority content of ONE key and receives only that key
+// (reference: test_shared_state_distribution.cpp:498)
+TEST(popularity_is_decided_per_candidate_and_moves_only_dirty_keys) {
+    TestMaster tm;
+    auto peers = connect_peers(tm, 3);
+    std::vector<PeerState> st(3);
+    for (int p = 0; p < 3; ++p) {
+        st[p].add("a", 300, 5);
+        st[p].add("b", 700, p == 0 ? 99 : 6);
+        st[p].add("c", 50, 7, wire::DType::F32);
+    }
+    std::thread first([&] { st[0].ok = peers[0]->sync_shared_state(st[0].args, st[0].tx, st[0].rx); });
+    std::this_thread::sleep_for(std::chrono::milliseconds(100));
+    sync_all(peers, st, {1, 2});
+    first.join();
+    CHECK(st[0].ok && st[1].ok && st[2].ok);
+    CHECK_EQ(st[0].rx, 700u);
+    CHECK(st[0].buffers[1] == std::vector<uint8_t>(700, 6));
+    CHECK_EQ(st[1].rx + st[2].rx, 0u);
+    CHECK_EQ(st[1].tx + st[2].tx, 700u);
+}
+
+// two groups synchronise at the same time, with the same key name meaning different things (size, content) in each:
+// traffic stays inside the groups, nobody is kicked (reference: :771, :885, :2082)
+TEST(groups_sync_concurrently_with_overlapping_key_names) {
+    TestMaster tm;
+    auto peers = connect_peers(tm, 4, {0, 0, 1, 1});
+    std::vector<PeerState> st(4);
+    st[0].add("w", 1000, 1);
+    st[1].add("w", 1000, 2);
+    st[2].add("w", 4000, 3, wire::DType::F32);
+    st[3].add("w", 4000, 4, wire::DType::F32);
+    for (int round = 0; round < 3; ++round) {
+        sync_all(peers, st);
+        for (auto &s : st) CHECK(s.ok);
+        CHECK(st[0].buffers[0] == st[1].buffers[0]);
+        CHECK(st[2].buffers[0] == st[3].buffers[0]);
+        CHECK(st[0].buffers[0].size() == 1000 && st[2].buffers[0].size() == 16000);
+        if (round == 0) {
+            CHECK_EQ(st[0].rx + st[1].rx, 1000u);
+            CHECK_EQ(st[2].rx + st[3].rx, 16000u);
+        } else {
+            for (auto &s : st) CHECK(s.tx == 0 && s.rx == 0);
+        }
+        for (auto &s : st) s.args.revision++;
+    }
+}
+
+// the strategy-mixing rule is applied per group: {SEND_ONLY, SEND_ONLY} with equal content is fine in group 0 while
+// group 1 = {ENFORCE_POPULAR, SEND_ONLY} loses its SEND_ONLY peer (reference: :3073); the kicked peer's later calls fail
+TEST(strategy_mixing_rule_is_per_group) {
+    TestMaster tm;
+    auto peers = connect_peers(tm, 4, {0, 0, 1, 1});
+    std::vector<PeerState> st(4);
+    for (auto &s : st) s.add("w", 128, 9);
+    st[0].args.strategy = SyncStrategy::TxOnly;
+    st[1].args.strategy = SyncStrategy::TxOnly;
+    st[2].args.strategy = SyncStrategy::EnforcePopular;
+    st[3].args.strategy = SyncStrategy::TxOnly;
+    sync_all(peers, st);
+    CHECK(st[0].ok && st[1].ok && st[2].ok);
+    CHECK(!st[3].ok);
+    // the kicked peer is out for good
+    uint64_t tx = 0, rx = 0;
+    CHECK(!peers[3]->sync_shared_state(st[3].args, tx, rx));
+    CHECK(!peers[3]->update_topology());
+    // the others go on: group 0 keeps synchronising, the global world has shrunk
+    for (int i = 0; i < 3; ++i) st[i].args.revision++;
+    std::vector<std::thread> ts;
+    for (int i = 0; i < 3; ++i) ts.emplace_back([&, i] { CHECK(peers[i]->update_topology()); });
+    for (auto &t : ts) t.join();
+    CHECK_EQ(peers[0]->global_world(), 3u);
+    sync_all(peers, st, {0, 1});
+    CHECK(st[0].ok && st[1].ok);
+}
+
 TEST_MAIN()
