@@ -14,7 +14,11 @@ What is timed (device time, CUDA events on the launching stream, max over ranks)
              the algorithm bandwidth bytes/t of the one-rank fused kernel is reported instead.
   e2e        the same, but every step first copies that step's pseudo-gradients host->device from
              pinned memory and reads the first reduced element back device->host.
-  diloco_outer_step_ms   pseudo-gradient kernel + all-reduce + fused Nesterov update (+ hash)
+  diloco_outer_step_ms         pseudo-gradient kernel + all-reduce + Nesterov kernel (three launches, symmetric scratch)
+  diloco_outer_step_fused_ms   the same step as ONE collective on ordinary tensors (`Communicator.ext_diloco_outer_step`)
+  regular_buffers              the headline all-reduce on ordinary torch tensors (staged through the arena)
+  nccl_same_run                NCCL all-reduce and the torch + NCCL formulation of the outer step, same process, same timing
+  verified_against_nccl        all of the above re-run once on fresh random data and compared with NCCL + torch (untimed)
 Inputs (600 MB) are far larger than the 126 MB L2, so no explicit L2 flush is needed between steps.
 """
 from __future__ import annotations
