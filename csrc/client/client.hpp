@@ -101,6 +101,10 @@ public:
     bool last_stats(uint64_t tag, pcclExtReduceStats_t &out);
 
     uint64_t global_world() const { return global_world_; }
+    // ports this peer listens on (after connect()): p2p, shared state, bandwidth benchmark
+    uint16_t p2p_port() const { return p2p_listener_.port(); }
+    uint16_t shared_state_port() const { return ss_listener_.port(); }
+    uint16_t benchmark_port() const { return bm_listener_.port(); }
     uint64_t local_world() const { return local_world_; }
     uint64_t num_groups() const { return num_groups_; }
     uint64_t largest_group() const { return largest_group_; }

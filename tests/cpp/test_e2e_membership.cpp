@@ -4,6 +4,7 @@
 #include <atomic>
 #include <chrono>
 #include <cstdlib>
+#include <random>
 
 #include "e2e_util.hpp"
 #include "pccl.h"
@@ -284,6 +285,125 @@ TEST(master_loss_fails_cleanly) {
             ReduceOutcome o;
             CHECK(!p->await_reduce(0, o));
         }
+    }
+}
+
+// The master is the one process every peer depends on: junk on its port (port scanners, peers of another version,
+// truncated or absurd frames, frames in the wrong state) may cost the sender its connection and nothing else.
+TEST(master_survives_garbage) {
+    TestMaster tm;
+    std::mt19937_64 rng(20240607);
+    auto target = tm.config().master;
+    auto random_bytes = [&](size_t n) {
+        std::vector<uint8_t> v(n);
+        for (auto &b : v) b = static_cast<uint8_t>(rng());
+        return v;
+    };
+    auto frame = [&](uint16_t id, const std::vector<uint8_t> &payload) {
+        std::vector<uint8_t> f;
+        const uint64_t len = 2 + payload.size();
+        for (int i = 7; i >= 0; --i) f.push_back(static_cast<uint8_t>(len >> (8 * i)));
+        f.push_back(static_cast<uint8_t>(id >> 8));
+        f.push_back(static_cast<uint8_t>(id));
+        f.insert(f.end(), payload.begin(), payload.end());
+        return f;
+    };
+    for (int round = 0; round < 200; ++round) {
+        net::BlockingSocket sock(target);
+        CHECK(sock.connect());
+        const int kind = static_cast<int>(rng() % 5);
+        if (kind == 0) { // no framing at all
+            const auto junk = random_bytes(1 + rng() % 300);
+            sock.send_raw(junk.data(), junk.size());
+        } else if (kind == 1) { // a length prefix that promises more than ever arrives
+            auto f = frame(static_cast<uint16_t>(rng() % 14), random_bytes(rng() % 64));
+            f[6] = 0x40;
+            sock.send_raw(f.data(), f.size());
+        } else {
+            if (kind >= 3) { // become a registered (the first: accepted) client, then misbehave
+                wire::C2MSessionRegistration reg;
+                reg.peer_group = static_cast<uint32_t>(rng() % 3);
+                reg.p2p_port = 1000;
+                reg.ss_port = 1001;
+                reg.bm_port = 1002;
+                sock.send_packet(reg);
+            }
+            const int n = 1 + static_cast<int>(rng() % 6);
+            for (int i = 0; i < n; ++i) {
+                // every known id with a random body, among them list counts of 2^63 and strings longer than the frame
+                auto body = random_bytes(rng() % 120);
+                if (!body.empty() && rng() % 3 == 0) std::fill(body.begin(), body.begin() + std::min<size_t>(8, body.size()), 0x7f);
+                const auto f = frame(static_cast<uint16_t>(rng() % 14), body);
+                if (!sock.send_raw(f.data(), f.size())) break;
+            }
+        }
+        if (rng() % 2) std::this_thread::sleep_for(std::chrono::milliseconds(1));
+    } // sockets close here
+    std::this_thread::sleep_for(200ms);
+    // the master still does its job
+    auto peers = connect_peers(tm, 2);
+    CHECK_EQ(peers[0]->global_world(), 2u);
+    std::vector<float> a(1000, 1.0f), b(1000, 2.0f), ra(1000), rb(1000);
+    std::thread t([&] {
+        ReduceRequest req;
+        req.send = b.data();
+        req.recv = rb.data();
+        req.count = 1000;
+        req.tag = 1;
+        ReduceOutcome out;
+        CHECK(peers[1]->all_reduce_sync(req, out) == client::Client::Launch::Ok && out.ok);
+    });
+    ReduceRequest req;
+    req.send = a.data();
+    req.recv = ra.data();
+    req.count = 1000;
+    req.tag = 1;
+    ReduceOutcome out;
+    CHECK(peers[0]->all_reduce_sync(req, out) == client::Client::Launch::Ok && out.ok);
+    t.join();
+    CHECK(ra[0] == 3.0f && rb[999] == 3.0f);
+}
+
+// The same for a peer's three listening ports (ring neighbours, shared-state requests, bandwidth probes).
+TEST(peer_listeners_survive_garbage) {
+    TestMaster tm;
+    auto peers = connect_peers(tm, 2);
+    std::mt19937_64 rng(77);
+    for (int round = 0; round < 150; ++round) {
+        auto target = tm.config().master; // 127.0.0.1, port replaced below
+        client::Client &victim = *peers[round % 2];
+        const uint16_t ports[3] = {victim.p2p_port(), victim.shared_state_port(), victim.benchmark_port()};
+        target.port = ports[rng() % 3];
+        net::BlockingSocket sock(target);
+        if (!sock.connect()) continue;
+        std::vector<uint8_t> junk(1 + rng() % 400);
+        for (auto &b : junk) b = static_cast<uint8_t>(rng());
+        if (junk.size() > 8 && rng() % 2) { // plausible framing: small length, then noise
+            for (int i = 0; i < 7; ++i) junk[i] = 0;
+            junk[7] = static_cast<uint8_t>(junk.size() - 8);
+        }
+        sock.send_raw(junk.data(), junk.size());
+    }
+    std::this_thread::sleep_for(200ms);
+    // both peers still reduce and synchronise
+    for (int tag = 0; tag < 3; ++tag) {
+        std::vector<float> a(5000, 1.0f), b(5000, 2.0f);
+        std::thread t([&] {
+            ReduceRequest req;
+            req.send = req.recv = b.data();
+            req.count = b.size();
+            req.tag = static_cast<uint64_t>(tag);
+            ReduceOutcome out;
+            CHECK(peers[1]->all_reduce_sync(req, out) == client::Client::Launch::Ok && out.ok);
+        });
+        ReduceRequest req;
+        req.send = req.recv = a.data();
+        req.count = a.size();
+        req.tag = static_cast<uint64_t>(tag);
+        ReduceOutcome out;
+        CHECK(peers[0]->all_reduce_sync(req, out) == client::Client::Launch::Ok && out.ok);
+        t.join();
+        CHECK(a[0] == 3.0f && b[4999] == 3.0f);
     }
 }
 
