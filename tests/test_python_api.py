@@ -1,6 +1,9 @@
 """Python surface on the CPU (reference: python/tests/unit_tests/pccl_test.py, numpy_only_tests, pytorch_only_tests,
 end_to_end/basic_reduce_test)."""
+import subprocess
+import sys
 import threading
+from pathlib import Path
 
 import numpy as np
 import pytest
@@ -8,6 +11,8 @@ import torch
 
 import pccl_b200 as pccl
 from test_gpu_multi import run_peers
+
+REPO = Path(__file__).resolve().parent.parent
 
 
 _MASTERS = []
@@ -320,3 +325,44 @@ def test_gradient_averager_cpu():
         return True
 
     assert all(run_threads(2, body).values())
+
+
+def test_package_works_without_torch():
+    """numpy-only installation (reference: python/tests/numpy_only_tests/numpy_only_test.py): importing, a master, a
+    communicator, the single-peer error and a two-peer numpy reduction, with `torch` made unimportable."""
+    code = r'''
+import sys, threading
+sys.modules["torch"] = None
+sys.path.insert(0, sys.argv[1])
+import numpy as np
+import pccl_b200 as pccl
+with pccl.MasterNode("127.0.0.1:0") as m:
+    m.run()
+    lone = pccl.Communicator(f"127.0.0.1:{m.port}", p2p_listen_port=48960, shared_state_listen_port=48961, benchmark_listen_port=48962)
+    lone.connect()
+    arr = np.random.rand(27)
+    try:
+        lone.all_reduce_async(arr, arr, op=pccl.ReduceOp.SUM)
+        raise SystemExit("a single peer must not be able to reduce")
+    except pccl.PCCLError:
+        pass
+    out = {}
+    def second():
+        c = pccl.Communicator(f"127.0.0.1:{m.port}", p2p_listen_port=48970, shared_state_listen_port=48971, benchmark_listen_port=48972)
+        c.connect(n_attempts=10)
+        x = np.full(1000, 2.0, dtype=np.float32); y = np.empty_like(x)
+        c.all_reduce(x, y, op=pccl.ReduceOp.SUM)
+        out[1] = float(y[0])
+        c.destroy()
+    t = threading.Thread(target=second); t.start()
+    while lone.get_attribute(pccl.Attribute.GLOBAL_WORLD_SIZE) < 2:
+        lone.update_topology()
+    x = np.full(1000, 1.0, dtype=np.float32); y = np.empty_like(x)
+    lone.all_reduce(x, y, op=pccl.ReduceOp.SUM)
+    t.join(timeout=60)
+    assert float(y[0]) == 3.0 and out[1] == 3.0, (y[0], out)
+    lone.destroy()
+print("NUMPY ONLY OK")
+'''
+    proc = subprocess.run([sys.executable, "-c", code, str(REPO)], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=180)
+    assert proc.returncode == 0 and "NUMPY ONLY OK" in proc.stdout, proc.stdout[-3000:]
