@@ -18,3 +18,13 @@ def test_two_peers_one_gpu_fall_back_to_tcp():
 def test_shared_state_two_peers_one_gpu():
     for r in run_peers(2, "shared_state", devices=["cuda:0", "cuda:0"]):
         assert r["ok"], r
+
+
+def test_outer_step_two_peers_one_gpu():
+    """Device tensors, TCP plane: the outer step takes its two-pass form (pseudo-gradient kernel into the library's scratch,
+    staged ring reduction, Nesterov kernel once the verdict is in)."""
+    results = run_peers(2, "outer_step", devices=["cuda:0", "cuda:0"], env={"PCCL_ARENA_SLOT_MB": "64", "PCCL_SYMMETRIC_MB": "128"})
+    for r in results:
+        assert r["ok"], r
+        assert all(c["plane"] == "tcp_ring" for c in r["cases"]), r
+    assert len({c["hash"] for r in results for c in r["cases"] if c["id"] == "outer_step_1"}) == 1
