@@ -1,5 +1,7 @@
 #include "epoll_server.hpp"
 
+#include <sys/uio.h>
+
 #include <sys/epoll.h>
 #include <sys/eventfd.h>
 #include <unistd.h>
@@ -11,6 +13,20 @@
 #include "sockutil.hpp"
 
 namespace pccl::net {
+
+// RAII for "a callback is running on the loop thread"
+struct EpollServer::Cork {
+    EpollServer &s;
+    explicit Cork(EpollServer &server) : s(server) {
+        std::lock_guard<std::recursive_mutex> lock(s.mu_);
+        ++s.cork_depth_;
+    }
+    ~Cork() {
+        std::lock_guard<std::recursive_mutex> lock(s.mu_);
+        if (--s.cork_depth_ == 0) s.uncork();
+    }
+};
+
 
 EpollServer::EpollServer(const ccoip_socket_address_t &listen_address, bool bump_port)
     : listen_addr_(listen_address), bump_(bump_port) {
@@ -99,6 +115,7 @@ void EpollServer::accept_ready() {
 }
 
 void EpollServer::client_readable(Client &c) {
+    Cork cork(*this);
     uint8_t buf[64 * 1024];
     for (;;) {
         const ssize_t k = ::recv(c.fd, buf, sizeof buf, 0);
@@ -143,24 +160,55 @@ void EpollServer::client_readable(Client &c) {
 
 void EpollServer::flush(Client &c) {
     while (!c.tx.empty()) {
-        auto &front = c.tx.front();
-        const ssize_t k = ::send(c.fd, front.data() + c.tx_off, front.size() - c.tx_off, MSG_NOSIGNAL);
+        iovec iov[16];
+        int n_iov = 0;
+        for (auto it = c.tx.begin(); it != c.tx.end() && n_iov < 16; ++it, ++n_iov) {
+            const size_t skip = n_iov == 0 ? c.tx_off : 0;
+            iov[n_iov].iov_base = it->data() + skip;
+            iov[n_iov].iov_len = it->size() - skip;
+        }
+        msghdr msg{};
+        msg.msg_iov = iov;
+        msg.msg_iovlen = static_cast<size_t>(n_iov);
+        const ssize_t k = ::sendmsg(c.fd, &msg, MSG_NOSIGNAL);
         if (k < 0) {
             if (errno == EINTR) continue;
             if (errno == EAGAIN || errno == EWOULDBLOCK) break;
             c.closing = true;
             return;
         }
-        c.tx_off += static_cast<size_t>(k);
-        if (c.tx_off == front.size()) {
-            c.tx.pop_front();
-            c.tx_off = 0;
+        size_t sent = static_cast<size_t>(k);
+        while (sent > 0 && !c.tx.empty()) {
+            const size_t left = c.tx.front().size() - c.tx_off;
+            if (sent >= left) {
+                sent -= left;
+                c.tx.pop_front();
+                c.tx_off = 0;
+            } else {
+                c.tx_off += sent;
+                sent = 0;
+            }
         }
     }
     const bool want = !c.tx.empty();
     if (want != c.want_write) {
         c.want_write = want;
         update_interest(c);
+    }
+}
+
+// mu_ held, loop thread
+void EpollServer::uncork() {
+    std::vector<int> todo;
+    todo.swap(corked_);
+    for (int fd : todo) {
+        auto it = clients_.find(fd);
+        if (it == clients_.end()) continue;
+        Client &c = it->second;
+        c.corked = false;
+        if (c.closing) continue;
+        flush(c);
+        if (c.closing) pending_close_.push_back(fd); // picked up by the loop's close pass of this iteration
     }
 }
 
@@ -172,6 +220,13 @@ bool EpollServer::send_raw(const ccoip_socket_address_t &client, std::vector<uin
     if (cit == clients_.end() || cit->second.closing) return false;
     Client &c = cit->second;
     c.tx.push_back(std::move(bytes));
+    if (cork_depth_ > 0 && std::this_thread::get_id() == loop_thread_.get_id()) {
+        if (!c.corked) {
+            c.corked = true;
+            corked_.push_back(c.fd);
+        }
+        return true;
+    }
     flush(c);
     if (c.closing) {
         pending_close_.push_back(c.fd);
@@ -209,6 +264,7 @@ void EpollServer::drop(int fd) {
         ::close(fd);
         clients_.erase(it);
     }
+    Cork cork(*this);
     if (close_cb_) close_cb_(addr);
 }
 

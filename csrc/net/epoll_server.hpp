@@ -57,6 +57,7 @@ private:
         size_t tx_off = 0;
         bool closing = false;
         bool want_write = false;
+        bool corked = false; // has frames whose flush is deferred to the end of the running callback
     };
 
     void loop();
@@ -77,6 +78,13 @@ private:
     std::unordered_map<int, Client> clients_;
     std::unordered_map<AddrKey, int> by_addr_;
     std::vector<int> pending_close_;
+    // Frames sent from inside a callback are written when the callback returns: a consensus that answers every
+    // client with two or three packets costs one writev per client instead of one send per packet, and the client
+    // wakes up once.  Only the loop thread touches these two (under mu_).
+    int cork_depth_ = 0;
+    std::vector<int> corked_;
+    void uncork();
+    struct Cork;
 
     ReadCallback read_cb_;
     AddrCallback join_cb_, close_cb_;
