@@ -127,6 +127,9 @@ public:
         size_t bytes;
     };
     // The buffer is one per plane: whoever uses it holds `fuse_lock()` from fuse_buffer() until it is done with the contents.
+    // The holders are synchronous collective calls (fused tensor lists, two-pass outer step) that keep the lock across
+    // their master vote; like all collectives they have to be issued in the same order on every peer -- two threads
+    // that start them in opposite orders on two peers would wait for each other's vote forever.
     virtual void *fuse_buffer(size_t bytes) = 0;
     virtual std::unique_lock<std::mutex> fuse_lock() = 0;
     virtual bool gather(const std::vector<Part> &parts, void *fused, bool into_fused) = 0;
