@@ -364,7 +364,17 @@ def run_reference(args) -> dict:
     ref_dir = REPO / "baseline" / "_ref"
     marker = ref_dir / "pccl"
     if not marker.exists():
-        return {"impl": "reference", "unavailable": "reference is not installed in baseline/_ref (see baseline/README.md for the install recipe)"}
+        # normally done by __graft_entry__.build(); try once here when the sources are on this machine
+        from baseline.install_reference import REF_SRC, install, installed
+        if REF_SRC.exists():
+            if int(os.environ.get("RANK", "0")) == 0:
+                install(verbose=False)
+            else:
+                deadline = time.time() + 300
+                while not installed() and time.time() < deadline:
+                    time.sleep(1)
+    if not marker.exists():
+        return {"impl": "reference", "unavailable": "reference is not installed in baseline/_ref and could not be built here (baseline/install_reference.py)"}
     from baseline.reference_arm import run as run_ref  # noqa: WPS433
     return run_ref(args)
 
