@@ -58,7 +58,9 @@ $(BUILD)/%.o: %.cpp
 	@mkdir -p $(dir $@)
 	$(CXX) $(CXXFLAGS) -MMD -MP -c $< -o $@
 
-$(BUILD)/%.cu.o: %.cu
+# nvcc writes no dependency files here: every CUDA object depends on every kernel header
+CU_HDRS := $(wildcard csrc/kernels/cuda/*.cuh csrc/kernels/*.hpp include/*.h)
+$(BUILD)/%.cu.o: %.cu $(CU_HDRS)
 	@mkdir -p $(dir $@)
 	$(NVCC) $(NVFLAGS) -c $< -o $@ 2> $@.ptxas.log || (cat $@.ptxas.log; false)
 

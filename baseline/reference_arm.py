@@ -121,7 +121,9 @@ def run(args) -> dict:
         "steps": steps, "warmup": max(3, warmup), "ms_per_step": round(ms, 3), "higher_is_better": True, "scaling": "weak",
         "vs_baseline": round(value / PUBLISHED_BASELINE_GBPS, 3), "dtype": "fp32", "data": "synthetic",
         "config": {"model": "DiLoCo pseudo-gradients, GPT-2-class 150M params fp32", "params": n, "parallelism": f"dp{peers}", "op": "avg",
-                   "peers": peers, "note": note, "build": "reference @ c488cabf, PCCL_BUILD_CUDA_SUPPORT=OFF, piquant stand-in header (not exercised)"},
+                   "peers": peers, "note": note,
+                   "e2e_note": "e2e: the step's input already sits in pinned host memory, so the reference skips the device-to-host half of its "
+                               "staging (all-reduce on host memory, then host-to-device copy of the result, then a 4-byte read)", "build": "reference @ c488cabf, PCCL_BUILD_CUDA_SUPPORT=OFF, piquant stand-in header (not exercised)"},
         "e2e": {"value": round(nbytes * factor / (ms_e2e * 1e-3) / 1e9, 4), "unit": "GB/s", "ms_per_step": round(ms_e2e, 3),
                 "h2d_bytes_per_step": nbytes, "d2h_bytes_per_step": 4},
         "gpu_launches": 0,

@@ -118,6 +118,9 @@ def run_ours(args) -> dict:
     assert world == args.gpus, f"--gpus {args.gpus} but WORLD_SIZE={world}"
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    # host threads and pinned buffers next to the GPU (matters for the end-to-end number with several peers per box)
+    from pccl_b200.utils import bind_to_device
+    numa = bind_to_device(local_rank) if os.environ.get("PCCL_BENCH_NUMA", "1") != "0" else {"bound": False, "reason": "disabled"}
     n = args.params
     nbytes = n * 4
     torch.manual_seed(1234 + rank)
@@ -169,7 +172,7 @@ def run_ours(args) -> dict:
             nonlocal launches
             comm.all_reduce(src, dst, op=pccl.ReduceOp.AVG, tag=0, quantization_options=quant)
             st = comm.ext_last_reduce_stats(0)
-            planes.add(st["plane"])
+            planes.add(st["plane"] + ("+lease" if st.get("leased") else ""))
             launches += st["kernel_launches"]
             dev_ms[0] += st["device_ms"]
 
@@ -190,17 +193,28 @@ def run_ours(args) -> dict:
             planes.add("p2p_two_shot(world=1)")
             launches += 1
 
+    last_timing = {}
+
     def timed(fn, steps):
+        """Every step between its own pair of CUDA events on the launching stream; the whole region bracketed by a
+        barrier + synchronize.  Returns the median step (max over ranks); mean, p95 and max are kept in last_timing
+        so that one stalled step shows up instead of silently shifting the number."""
         barrier()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        for _ in range(steps):
+        evs = [torch.cuda.Event(enable_timing=True) for _ in range(steps + 1)]
+        evs[0].record()
+        for i in range(steps):
             fn()
-        e1.record()
+            evs[i + 1].record()
         torch.cuda.synchronize()
-        ms = e0.elapsed_time(e1)
+        per = sorted(evs[i].elapsed_time(evs[i + 1]) for i in range(steps))
+        total = evs[0].elapsed_time(evs[steps])
         barrier()
-        return max_over_ranks(ms) / steps
+        med = per[len(per) // 2] if len(per) % 2 else 0.5 * (per[len(per) // 2 - 1] + per[len(per) // 2])
+        p95 = per[min(len(per) - 1, int(0.95 * len(per)))]
+        last_timing.clear()
+        last_timing.update({"median": max_over_ranks(med), "mean": max_over_ranks(total / steps), "p95": max_over_ranks(p95),
+                            "max": max_over_ranks(per[-1]), "min": max_over_ranks(per[0])})
+        return last_timing["median"]
 
     # ---- kernel-level number -----------------------------------------------------------------
     main_src, main_dst = (sym, sym) if sym is not None else (grad, out)
@@ -212,6 +226,7 @@ def run_ours(args) -> dict:
         sampler.start()
     dev_ms[0] = 0.0
     ms_step = timed(lambda: reduce_step(main_src, main_dst), args.steps)
+    main_timing = {k: round(v, 4) for k, v in last_timing.items()}
     main_planes = sorted(planes)
     kernel_ms = max_over_ranks(dev_ms[0] / args.steps) if dev_ms[0] else None
     timed_launches = launches
@@ -328,7 +343,7 @@ def run_ours(args) -> dict:
     value = nbytes * factor / (ms_step * 1e-3) / 1e9
     e2e_value = nbytes * factor / (ms_e2e * 1e-3) / 1e9
     result = {
-        "metric": "allreduce_bus_GBps" if world > 1 else "allreduce_alg_GBps_single_peer",
+        "metric": "allreduce_bus_GBps",
         "value": round(value, 3), "unit": "GB/s", "n_gpus": world, "steps": args.steps, "warmup": max(3, args.warmup),
         "ms_per_step": round(ms_step, 4), "higher_is_better": True, "scaling": "weak",
         "vs_baseline": round(value / PUBLISHED_BASELINE_GBPS, 2), "dtype": "fp32", "data": "synthetic",
@@ -337,10 +352,14 @@ def run_ours(args) -> dict:
                    "parallelism": f"dp{world}", "op": "avg", "quantization": args.quant, "planes": main_planes,
                    "buffers": "symmetric (Communicator.ext_symmetric_empty, in place)" if sym is not None else "regular torch tensors",
                    "l2_policy": "inputs (600 MB) larger than L2 (126 MB); no explicit flush",
-                   "note": "one peer: bus factor undefined, value is bytes/time of the one-rank fused kernel" if world == 1 else
-                           "bus GB/s = bytes*2(P-1)/P/t, device time incl. control plane round trips"},
+                   "bus_factor": factor, "numa": numa,
+                   "note": "one peer: the public API refuses to reduce alone (pcclTooFewPeers, as the reference), so the same fused kernel runs "
+                           "with world size 1 through ops.local_all_reduce; bus factor 1" if world == 1 else
+                           "bus GB/s = bytes*2(P-1)/P/t; t = median step (device time, max over ranks) incl. control plane"},
         "e2e": {"value": round(e2e_value, 3), "unit": "GB/s", "ms_per_step": round(ms_e2e, 4), "h2d_bytes_per_step": nbytes, "d2h_bytes_per_step": 4},
         "gpu_launches": timed_launches,
+        "step_ms": main_timing,
+        "call_overhead_ms": round(ms_step - kernel_ms, 4) if kernel_ms else None,
         "diloco_outer_step_ms": round(ms_outer, 4),
         "diloco_outer_step_fused_ms": round(ms_outer_fused, 4), "diloco_outer_step_fused_planes": sorted(fused_planes), "shared_state_hash_ms": round(ms_hash, 3), "shared_state_hash": digest,
         "clocks": clocks,

@@ -360,7 +360,18 @@ static pcclResult_t try_fused_multiple(const pcclReduceOpDescriptor_t *descripto
         const auto launch = c->client->all_reduce_sync(req, out);
         if (launch == client::Client::Launch::NotConnected) return pcclInvalidUsage;
         if (launch == client::Client::Launch::DuplicateTag) return pcclInvalidArgument;
-        if (out.ok) break; // a failed in-place attempt leaves the fused input intact: just go again
+        if (out.ok) break;
+        // The fused buffer may live in symmetric memory, where a failed in-place attempt can leave partly reduced
+        // values behind: bring the inputs in again before the next attempt.
+        if (any_device) {
+            if (!plane.gather(in_parts, fused, true)) return pcclInternalError;
+        } else {
+            size_t off = 0;
+            for (const auto &p : in_parts) {
+                std::memcpy(fused + off, p.ptr, p.bytes);
+                off += (p.bytes + 15) / 16 * 16;
+            }
+        }
     }
     if (any_device) {
         if (!plane.gather(out_parts, fused, false)) return pcclInternalError;
@@ -529,14 +540,14 @@ pcclResult_t pcclExtGetLastReduceStats(const pcclComm_t *c, uint64_t tag, pcclEx
 pcclResult_t pcclExtHashBuffer(const void *data, size_t n_bytes, pcclDeviceType_t device_type, int hash_type,
                                uint64_t *hash_out) {
     PCCL_REQUIRE(hash_out && (data || n_bytes == 0), pcclInvalidArgument);
-    PCCL_REQUIRE(hash_type == 0 || hash_type == 1, pcclInvalidArgument);
+    PCCL_REQUIRE(hash_type >= 0 && hash_type <= 2, pcclInvalidArgument);
     const bool on_device = device_type == pcclDeviceCuda || device::classify_pointer(data).is_device;
     if (on_device) {
         static std::unique_ptr<device::Plane> plane = device::Plane::create();
         return plane->hash_device(data, n_bytes, static_cast<wire::HashType>(hash_type), *hash_out) ? pcclSuccess
                                                                                                      : pcclInternalError;
     }
-    *hash_out = hash_type == 0 ? cpu::simplehash(data, n_bytes) : cpu::crc32c(data, n_bytes);
+    *hash_out = hash_type == 0 ? cpu::simplehash(data, n_bytes) : hash_type == 1 ? cpu::crc32c(data, n_bytes) : cpu::mset64(data, n_bytes);
     return pcclSuccess;
 }
 

@@ -35,6 +35,7 @@ Client::Client(const ClientConfig &cfg)
     workers_ = std::make_unique<ThreadPool>(std::max<size_t>(1, n_workers), 64);
     ss_workers_ = std::make_unique<ThreadPool>(2, 64);
     bm_workers_ = std::make_unique<ThreadPool>(static_cast<size_t>(env_u64("PCCL_NUM_BENCHMARK_CONNECTIONS", 16)) + 1, 64);
+    lease_enabled_ = env_flag("PCCL_LEASE", true);
 }
 
 Client::~Client() {
@@ -70,10 +71,26 @@ bool Client::connect() {
     }
     // device-plane operations are queued per staging slot in the order their Commence packets arrive
     master_.set_observer([this](uint16_t id, const std::vector<uint8_t> &payload) {
-        if (id != M2CCollectiveCommence::id) return;
         Reader r(payload.data(), payload.size());
+        if (id == M2CLeaseRevoked::id) {
+            // the lease of a tag (or of the whole group) ended: operations that run without a vote must stop waiting
+            // for peers that will not come, and later operations vote again
+            M2CLeaseRevoked rv;
+            if (!rv.read(r)) return;
+            {
+                std::lock_guard<std::mutex> lock(lease_mu_);
+                if (rv.all)
+                    lease_tags_.clear();
+                else
+                    lease_tags_.erase(rv.tag);
+            }
+            if (rv.peer_lost) ring_stale_ = true;
+            plane_->revoke_leased(rv.tag, rv.all);
+            return;
+        }
+        if (id != M2CCollectiveCommence::id) return;
         M2CCollectiveCommence c;
-        if (c.read(r) && (c.seq_nr >> 63)) plane_->announce(c.seq_nr & ~(3ull << 62));
+        if (c.read(r) && (c.seq_nr >> 63)) plane_->announce(c.seq_nr & ~(15ull << 60));
     });
     master_.run();
 
@@ -272,6 +289,11 @@ Client::Establish Client::establish_round() {
     }
     local_world_ = verdict->ring_order.size();
     ring_stale_ = false;
+    {
+        std::lock_guard<std::mutex> lock(lease_mu_); // leases belong to a ring
+        lease_tags_.clear();
+        lease_counts_.clear();
+    }
     plane_->on_ring_changed(verdict->ring_order);
     return Establish::Success;
 }
@@ -538,11 +560,15 @@ bool Client::sync_shared_state(SharedStateArgs &state, uint64_t &tx_bytes, uint6
     // the whole run to CRC32C (all peers must agree, the master compares the hash type too)
     static const HashType hash_type = [] {
         const char *v = std::getenv("PCCL_SHARED_STATE_HASH");
-        return v && (std::string(v) == "crc32" || std::string(v) == "crc32c") ? HashType::Crc32 : HashType::Simple;
+        if (v && (std::string(v) == "crc32" || std::string(v) == "crc32c")) return HashType::Crc32;
+        if (v && (std::string(v) == "mset" || std::string(v) == "mset64")) return HashType::Mset64;
+        return HashType::Simple;
     }();
     auto hash_of = [&](const SharedEntry &e, uint64_t &out) {
         if (e.on_device) return plane_->hash_device(e.data, e.bytes(), hash_type, out);
-        out = hash_type == HashType::Simple ? cpu::simplehash(e.data, e.bytes()) : cpu::crc32c(e.data, e.bytes());
+        out = hash_type == HashType::Simple  ? cpu::simplehash(e.data, e.bytes())
+              : hash_type == HashType::Crc32 ? cpu::crc32c(e.data, e.bytes())
+                                             : cpu::mset64(e.data, e.bytes());
         return true;
     };
     C2MSyncSharedState vote;
@@ -889,6 +915,55 @@ ReduceOutcome Client::run_reduce(const ReduceRequest &req, uint64_t) {
     };
     const bool device_capable = (caps & device::Plane::kCapP2P) != 0;
 
+    // ---- lease path.  An earlier operation on this tag was voted, ran on the device plane on every peer, and its
+    // Commence carried the lease bit: from then on the group runs this tag's collectives without the master.  Their
+    // order among concurrently issued operations comes from the same-box sequencer (device/sequencer.hpp), their
+    // failure detection from the master all the same: it revokes the lease when a member vanishes or when somebody
+    // votes on the tag after all (M2CLeaseRevoked, handled on the receive thread), which makes the kernels give up.
+    if (lease_enabled_) {
+        bool leased = false;
+        uint64_t k = 0;
+        {
+            std::lock_guard<std::mutex> lock(lease_mu_);
+            const auto it = lease_tags_.find(req.tag);
+            if (it != lease_tags_.end()) {
+                if (device_capable && !ring_stale_.load()) {
+                    leased = true;
+                    k = lease_counts_[req.tag]++;
+                } else {
+                    lease_tags_.erase(it); // host buffers, unsupported type...: vote; the master ends the lease for the others
+                }
+            }
+        }
+        if (leased) {
+            dargs.leased = true;
+            dargs.tag = req.tag;
+            dargs.lease_k = k;
+            dargs.use_nvls = lease_mc_all_.load() && (caps & device::Plane::kCapNvls) != 0;
+            const auto r = plane_->reduce(dargs, [&]() { return !master_.is_open() || interrupted_.load(); });
+            out.tx_bytes = r.tx_bytes;
+            out.rx_bytes = r.rx_bytes;
+            out.stats.plane = r.plane;
+            out.stats.device_ms = r.device_ms;
+            out.stats.kernel_launches = r.kernel_launches;
+            out.stats.seq_nr = k;
+            out.stats.leased = 1;
+            if (r.ok) {
+                out.ok = apply_outer_update();
+                return out;
+            }
+            {
+                std::lock_guard<std::mutex> lock(lease_mu_);
+                lease_tags_.erase(req.tag);
+            }
+            // The lease ended underneath the operation (not a data-plane failure) and the input is intact: vote like a
+            // peer that never had the lease.  Anything else is reported; the caller rewires and retries.
+            if (!(r.revoked && !r.input_destroyed && master_.is_open() && !ring_stale_.load())) return out;
+            dargs.leased = false;
+            out.stats = pcclExtReduceStats_t{};
+        }
+    }
+
     // ---- vote.  The spare top bit of the operator byte tells the master that this peer can
     // run the operation on the device plane; the master answers with the top bit of the
     // sequence number when EVERY peer of the group said so.  Masters and peers that do not
@@ -898,8 +973,11 @@ ReduceOutcome Client::run_reduce(const ReduceRequest &req, uint64_t) {
     vote.count = req.count;
     vote.dtype = req.dtype;
     // (bit 6 / bit 62 do the same for the NVSwitch multicast variant)
+    // (bit 5: this peer would run LATER operations on this tag under a lease; bit 4: it holds the multicast view)
+    const bool offer_lease = lease_enabled_ && device_capable && plane_->lease_ready();
     vote.op = static_cast<RedOp>(static_cast<uint8_t>(req.op) | (device_capable ? 0x80u : 0u) |
-                                 ((caps & device::Plane::kCapNvls) ? 0x40u : 0u));
+                                 ((caps & device::Plane::kCapNvls) ? 0x40u : 0u) | (offer_lease ? 0x20u : 0u) |
+                                 (offer_lease && plane_->multicast_ready() ? 0x10u : 0u));
     // The previous operation on this tag may have returned before its completion handshake was
     // consumed (device plane, see below).  A master of this build queues the new vote behind
     // it, so the vote goes out first and both answers arrive in one round trip; towards any
@@ -947,8 +1025,14 @@ ReduceOutcome Client::run_reduce(const ReduceRequest &req, uint64_t) {
     const bool poisoned = ring_stale_.load();
     const bool use_device = (go->seq_nr >> 63) != 0;
     const bool use_nvls = use_device && ((go->seq_nr >> 62) & 1) != 0;
-    const uint64_t seq = go->seq_nr & ~(3ull << 62);
+    const uint64_t seq = go->seq_nr & ~(15ull << 60);
     out.stats.seq_nr = seq;
+    if (use_device && offer_lease && ((go->seq_nr >> 61) & 1) != 0) {
+        // lease granted: the NEXT operation on this tag skips the vote (every peer decides so from this same packet)
+        lease_mc_all_ = ((go->seq_nr >> 60) & 1) != 0;
+        std::lock_guard<std::mutex> lock(lease_mu_);
+        lease_tags_.insert(req.tag);
+    }
     if (use_device) master_pipelines_ = true; // only a master of this build ever sets that bit
 
     bool abort_seen = false, aborted = false;
@@ -1068,7 +1152,8 @@ ReduceOutcome Client::run_reduce(const ReduceRequest &req, uint64_t) {
     const bool fused_applied = outer_fused && use_device && device_capable && local_ok;
     if (fused_applied && aborted) ring_stale_ = true;
     const bool success = fused_applied || (local_ok && !aborted);
-    if (use_device && device_capable && !success && in_place) plane_->restore_input(dargs);
+    // (A failed device-plane attempt leaves an ordinary in-place operand as it was: the kernels write the caller's
+    // memory only after every block of this rank knows the reduction completed everywhere.)
     if (out.stats.plane == pcclExtPlaneTcpRing) {
         if (success && stage) {
             if (recv_info.is_device) {

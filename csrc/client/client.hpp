@@ -13,6 +13,7 @@
 #include <memory>
 #include <mutex>
 #include <optional>
+#include <set>
 #include <shared_mutex>
 #include <unordered_map>
 #include <vector>
@@ -169,6 +170,14 @@ private:
     std::map<uint64_t, Deferred> deferred_;
     std::atomic<bool> ring_stale_{false};       // a peer vanished after an operation had finished here: rewire before the next one
     std::atomic<bool> master_pipelines_{false}; // the master queues an Initiate behind a pending Complete
+    // Leases: tags whose collectives run without a vote at the master (granted by the Commence of an earlier operation on
+    // that tag, see run_reduce), and how many leased operations each tag has seen on this ring (the operation's name in
+    // the same-box sequencer).  Everything here is reset when the ring changes.
+    std::mutex lease_mu_;
+    std::set<uint64_t> lease_tags_;
+    std::map<uint64_t, uint64_t> lease_counts_;
+    std::atomic<bool> lease_mc_all_{false}; // every peer of the ring holds the multicast view
+    bool lease_enabled_ = true;             // PCCL_LEASE=0 keeps every operation a vote
     std::mutex ops_mu_;
     std::map<uint64_t, Op> ops_;
     std::map<uint64_t, pcclExtReduceStats_t> stats_;

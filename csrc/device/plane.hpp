@@ -59,6 +59,12 @@ struct DeviceReduceArgs {
     uint32_t rank = 0, world = 1;
     bool use_nvls = false; // all peers agreed (through the master) to run this one over NVSwitch multicast
     const OuterStepArgs *outer = nullptr; // non-null: src/dst are ignored, see OuterStepArgs
+    // lease path (no vote at the master): the operation is identified by (tag, lease_k) in the same-box sequencer
+    bool leased = false;
+    uint64_t tag = 0, lease_k = 0;
+    bool want_hash = false; // produce the mset64 digest(s) of the output as a by-product
+    void *user_stream = nullptr; // non-null: order the operation after this CUDA stream instead of the legacy default stream
+    bool enqueue_only = false;   // return after the launch; the caller finishes with Plane::finish()
 };
 
 struct DeviceReduceResult {
@@ -68,6 +74,12 @@ struct DeviceReduceResult {
     float device_ms = 0;
     uint32_t kernel_launches = 0;
     uint64_t tx_bytes = 0, rx_bytes = 0;
+    bool revoked = false;         // gave up because the lease ended underneath it (not a data-plane failure)
+    bool input_destroyed = false; // in place on symmetric memory: a failed attempt may have overwritten the input
+    bool has_hash = false;
+    uint64_t hash[2] = {0, 0};    // mset64 of the output (outer step: [0] parameters, [1] momentum)
+    bool pending = false;         // enqueue_only: launched, not finished
+    uint64_t ticket = 0;          // identifies the pending operation for finish()
 };
 
 class Plane {
@@ -89,6 +101,18 @@ public:
     static constexpr uint32_t kCapP2P = 1, kCapNvls = 2;
     virtual uint32_t capabilities(const DeviceReduceArgs &args) = 0;
 
+    // Lease support: true when the same-box sequencer of the current ring is attached (operations can be ordered
+    // without the master); multicast_ready() tells whether the NVSwitch view of the current ring exists here.
+    virtual bool lease_ready() = 0;
+    virtual bool multicast_ready() = 0;
+    // Whether the multicast kernels can run this reduction (type, operator, size, ring size) -- the same answer on
+    // every peer; combined with "every peer has the multicast view" it decides the plane of a leased operation.
+    virtual bool nvls_eligible(const DeviceReduceArgs &args) = 0;
+    // The lease ended (tag, or everything when all is set): leased operations in flight give up.
+    virtual void revoke_leased(uint64_t tag, bool all) = 0;
+    // Second half of an enqueue_only reduction: waits for the kernel and reports its verdict.
+    virtual DeviceReduceResult finish(uint64_t ticket, const std::function<bool()> &abort_requested) = 0;
+
     // Device operations must run in the same order on every peer, otherwise two peers can each
     // run a different operation first (holding the staging slot and the SMs) and wait for each
     // other forever.
@@ -100,9 +124,6 @@ public:
 
     // Runs the reduction; `abort_requested` is polled while the kernel runs.
     virtual DeviceReduceResult reduce(const DeviceReduceArgs &args, const std::function<bool()> &abort_requested) = 0;
-
-    // After a failed in-place reduction: puts the original input back into args.dst.
-    virtual bool restore_input(const DeviceReduceArgs &args) = 0;
 
     // Stream-ordered staging helpers for the TCP fallback and for shared state.
     virtual bool copy_to_host(void *host_dst, const void *dev_src, size_t bytes) = 0;

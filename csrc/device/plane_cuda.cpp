@@ -7,6 +7,7 @@
 #include <cuda.h>
 #include <cuda_runtime.h>
 #include <poll.h>
+#include <sys/mman.h>
 #include <sys/socket.h>
 #include <sys/un.h>
 #include <unistd.h>
@@ -26,6 +27,7 @@
 #include "../util/log.hpp"
 #include "pccl_kernels.h"
 #include "plane.hpp"
+#include "sequencer.hpp"
 
 namespace pccl::device {
 
@@ -121,7 +123,7 @@ const Driver &driver() {
 
 // ------------------------------------------------------------------------------------------ unix rendezvous
 constexpr uint32_t kMagic = 0x50434231; // "PCB1"
-enum : uint32_t { kReqArena = 1, kReqMulticast = 2, kReqMulticastAdded = 3, kReqMulticastReady = 4 };
+enum : uint32_t { kReqArena = 1, kReqMulticast = 2, kReqMulticastAdded = 3, kReqMulticastReady = 4, kReqSequencer = 5 };
 
 struct RendezvousRequest {
     uint32_t magic, kind;
@@ -196,8 +198,10 @@ public:
                 clock_khz_ = prop.clockRate > 0 ? prop.clockRate : 1900000;
             }
         }
-        slot_bytes_ = round_up(env_u64("PCCL_ARENA_SLOT_MB", 768) << 20, 2u << 20);
+        slot_bytes_ = round_up(env_u64("PCCL_ARENA_SLOT_MB", 640) << 20, 2u << 20);
         n_slots_ = static_cast<uint32_t>(std::clamp<uint64_t>(env_u64("PCCL_ARENA_SLOTS", 2), 1, 15));
+        // every flag bank owns a small double-buffered staging area for latency-bound operations
+        small_half_ = round_up(std::clamp<uint64_t>(env_u64("PCCL_SMALL_STAGING_KB", 1024), 64, 16384) << 10, 4096);
         // symmetric heap = [caller's allocations][library scratch].  The scratch region has a FIXED offset, so peers
         // with different allocation histories (late joiners, different tensor lists in the past) still agree on where
         // an internally staged operand lives -- symmetric operands are addressed with one offset in every arena.
@@ -212,6 +216,8 @@ public:
         pipeline_segments_ = env_u64("PCCL_PIPELINE_SEGMENTS", 0);
         pipeline_seg_bytes_ = std::max<uint64_t>(1, env_u64("PCCL_PIPELINE_SEGMENT_MB", 64)) << 20;
         nvls_min_bytes_ = env_u64("PCCL_NVLS_MIN_BYTES", 1u << 20);
+        small_grid_ = static_cast<int>(std::clamp<uint64_t>(env_u64("PCCL_SMALL_OP_BLOCKS", 8), 1, 8));
+        use_sequencer_ = env_flag("PCCL_SEQUENCER", true);
     }
     ~CudaPlane() override { stop(); }
 
@@ -245,18 +251,18 @@ public:
         if (arena_ptr_) teardown_multicast();
         for (auto &[u, p] : peers_) unmap_peer(p);
         peers_.clear();
-        for (auto &s : slots_) {
-            if (s.stream) cudaStreamSynchronize(s.stream);
-            if (s.stream) cudaStreamDestroy(s.stream);
-            if (s.copy_in) cudaStreamDestroy(s.copy_in);
-            if (s.copy_out) cudaStreamDestroy(s.copy_out);
-            for (auto *v : {&s.ev_in, &s.ev_kernel, &s.ev_out})
-                for (cudaEvent_t e : *v) cudaEventDestroy(e);
-            if (s.start) cudaEventDestroy(s.start);
-            if (s.stop) cudaEventDestroy(s.stop);
-            if (s.host_words) cudaFreeHost(s.host_words);
-            if (s.backup) cudaFree(s.backup);
+        for (auto &b : banks_) {
+            if (b.stream) cudaStreamSynchronize(b.stream);
+            if (b.stream) cudaStreamDestroy(b.stream);
+            for (cudaEvent_t e : {b.start, b.stop, b.ready})
+                if (e) cudaEventDestroy(e);
+            if (b.host_words) cudaFreeHost(b.host_words);
+            if (b.hash_host) cudaFreeHost(b.hash_host);
+            if (b.hash_dev) cudaFree(b.hash_dev);
         }
+        banks_.clear();
+        for (auto &sl : slots_)
+            if (sl.last_use) cudaEventDestroy(sl.last_use);
         slots_.clear();
         if (util_stream_) cudaStreamDestroy(util_stream_), util_stream_ = nullptr;
         if (arena_ptr_) {
@@ -265,12 +271,21 @@ public:
             driver().MemRelease(arena_handle_);
             arena_ptr_ = 0;
         }
+        drop_sequencer();
     }
 
     void on_ring_changed(const std::vector<Uuid> &ring) override {
         std::lock_guard<std::mutex> lock(mu_);
         ring_ = ring;
         ring_ready_ = false;
+        {
+            std::lock_guard<std::mutex> l(launch_mu_);
+            drop_sequencer();
+            next_launch_ = 0;
+            big_count_ = 0;
+            last_big_bank_ = -1;
+        }
+        launch_cv_.notify_all();
         if (usable_ && arena_ptr_) {
             cudaSetDevice(device_);
             teardown_multicast();
@@ -318,6 +333,7 @@ public:
         ring_ready_ = true;
         PLOG(INFO) << "device plane ready: " << ring.size() << " peers mapped over NVLink";
         setup_multicast(ring);
+        if (use_sequencer_) setup_sequencer(ring);
     }
 
     uint32_t capabilities(const DeviceReduceArgs &a) override {
@@ -339,17 +355,34 @@ public:
         }
         switch (a.quant) {
         case wire::QuantAlgo::None:
-            // Through the switch every GPU moves about N(1+1/P) bytes per direction (its own stores
-            // are echoed back), peer-to-peer two-shot moves 2N(P-1)/P: multicast pays off from 4 peers.
-            return kCapP2P | (mc_ready_ && a.world >= nvls_min_world_ && a.count * wire::dtype_size(a.dtype) >= nvls_min_bytes_ &&
-                                      pcclKernelNvlsSupported(pccl_dtype(a.dtype), pccl_op(a.op))
-                                  ? kCapNvls
-                                  : 0u);
+            return kCapP2P | (mc_ready_ && nvls_eligible_locked(a) ? kCapNvls : 0u);
         // on the device plane uint8 min-max is block-scaled (128 elements per (min,max) pair)
         case wire::QuantAlgo::MinMax:
         case wire::QuantAlgo::BlockMinMax: return a.dtype == wire::DType::F32 && a.quant_dtype == wire::DType::U8 ? kCapP2P : 0u;
         case wire::QuantAlgo::BlockFp8: return a.dtype == wire::DType::F32 && a.quant_dtype == wire::DType::F8E4M3 ? kCapP2P : 0u;
         default: return 0;
+        }
+    }
+
+    bool lease_ready() override {
+        std::lock_guard<std::mutex> lock(launch_mu_);
+        return sequencer_.attached();
+    }
+    bool multicast_ready() override {
+        std::lock_guard<std::mutex> lock(mu_);
+        return mc_ready_;
+    }
+    bool nvls_eligible(const DeviceReduceArgs &a) override {
+        std::lock_guard<std::mutex> lock(mu_);
+        return nvls_eligible_locked(a);
+    }
+
+    void revoke_leased(uint64_t tag, bool all) override {
+        std::lock_guard<std::mutex> lock(inflight_mu_);
+        for (auto &[ticket, f] : inflight_) {
+            if (!f.leased || (!all && f.tag != tag)) continue;
+            f.revoked = true;
+            reinterpret_cast<volatile uint32_t *>(banks_[f.bank].host_words)[0] = 1;
         }
     }
 
@@ -366,179 +399,201 @@ public:
         order_cv_.notify_all();
     }
 
+    // Launches the kernel(s) of one reduction and (unless enqueue_only) waits for them.
+    //
+    // Order.  Collective kernels of different operations must start in the same order on every peer (each wants SMs and
+    // waits for its twins).  With the same-box sequencer attached, every operation -- voted at the master or leased --
+    // takes its place from the shared log and launches strictly in that order; without it, voted operations run one
+    // at a time in the order their Commence packets arrived (announce()).
+    // Resources.  Operation number i uses flag bank i % kSeqBanks with its own stream and status words.  Small operands
+    // are staged in the bank's own area (two halves, alternating between consecutive uses of the bank, which lets the
+    // one-shot kernel drop its closing barrier); large ones take a big staging slot in turn; symmetric operands none.
+    // Co-residency.  Small operations run with at most small_grid_ blocks, so a full set of banks fits on the GPU
+    // together; an operation that wants more waits (on the stream) for everything launched before it, and everything
+    // launched after it waits for it.  Those rules depend on the launch sequence only, hence are the same everywhere.
     DeviceReduceResult reduce(const DeviceReduceArgs &a, const std::function<bool()> &abort_requested) override {
         DeviceReduceResult res;
-        // Wait for this operation's turn (see announce()); leave the queue on every exit.  Device
-        // operations run strictly one after the other, in the same order on every peer: two
-        // collective kernels that each want (nearly) every SM and each wait for their twin on the
-        // other GPUs would deadlock if two GPUs started them in different orders.
-        struct Turn {
-            CudaPlane *p;
-            uint64_t seq;
-            ~Turn() { p->cancel(seq); }
-        } turn{this, a.seq};
+        std::vector<void *> arenas;
+        void *mc_view = nullptr;
+        bool ring_ok = false;
         {
+            std::lock_guard<std::mutex> lock(mu_);
+            ring_ok = ring_ready_ && a.world == ring_.size() && (!a.use_nvls || mc_ready_);
+            if (ring_ok) {
+                if (a.use_nvls) mc_view = reinterpret_cast<void *>(mc_.ptr);
+                for (const auto &u : ring_) arenas.push_back(u == self_ ? reinterpret_cast<void *>(arena_ptr_) : reinterpret_cast<void *>(peers_.at(u).ptr));
+            }
+        }
+        if (!ring_ok) {
+            if (!a.leased) cancel(a.seq);
+            return res;
+        }
+        cudaSetDevice(device_);
+
+        const size_t esz = wire::dtype_size(a.dtype);
+        const int dtype = pccl_dtype(a.dtype), op = pccl_op(a.op), quant = kernel_quant(a.quant);
+        const uint64_t bytes = a.count * esz;
+        const bool in_place = a.src == a.dst && !a.outer;
+
+        // symmetric memory: the buffer itself is peer-visible, no staging copy for that side
+        SymRef ssym, dsym;
+        if (!a.outer && quant == 0) {
+            std::lock_guard<std::mutex> lock(mu_);
+            ssym = symmetric_ref(a.src, bytes);
+            dsym = symmetric_ref(a.dst, bytes);
+        }
+        size_t need = pcclKernelP2PStagingBytes(a.count, dtype, quant);
+        if ((ssym.ok != dsym.ok) && need > slot_bytes_) ssym.ok = dsym.ok = false; // mixed and multi-round: stage both sides
+        const bool needs_staging = !(ssym.ok && dsym.ok);
+
+        // ---- place in the common order
+        std::unique_lock<std::mutex> launch(launch_mu_);
+        const bool sequenced = sequencer_.attached();
+        if (a.leased && !sequenced) return res;
+        uint64_t index = 0;
+        bool queue_turn = false;
+        if (sequenced) {
+            if (!a.leased) cancel(a.seq); // the Commence queue is not used while the sequencer orders everything
+            const bool got = a.leased ? sequencer_.order_of(a.tag, a.lease_k, index) : sequencer_.order_of(~0ull, a.seq, index);
+            if (!got) {
+                PLOG(ERR) << "same-box sequencer did not answer (a peer died while appending?)";
+                return res;
+            }
+            while (next_launch_ != index) {
+                launch_cv_.wait_for(launch, std::chrono::milliseconds(10));
+                if (next_launch_ != index && ((abort_requested && abort_requested()) || !sequencer_.attached() || next_launch_ > index)) {
+                    res.revoked = a.leased;
+                    return res;
+                }
+            }
+        } else {
+            launch.unlock();
             std::unique_lock<std::mutex> lock(order_mu_);
             auto &q = order_;
             order_cv_.wait(lock, [&] { return q.empty() || q.front() == a.seq || std::find(q.begin(), q.end(), a.seq) == q.end(); });
+            lock.unlock();
+            launch.lock();
+            queue_turn = true;
         }
-        std::vector<void *> arenas;
-        void *mc_view = nullptr;
-        {
-            std::lock_guard<std::mutex> lock(mu_);
-            if (!ring_ready_ || a.world != ring_.size()) return res;
-            if (a.use_nvls) {
-                if (!mc_ready_) return res;
-                mc_view = reinterpret_cast<void *>(mc_.ptr);
+        // from here on the turn must be passed on whatever happens
+        struct TurnGuard {
+            CudaPlane *p;
+            bool sequenced, queue_turn, keep_queue;
+            uint64_t index, seq;
+            std::unique_lock<std::mutex> &launch;
+            ~TurnGuard() {
+                if (sequenced) {
+                    if (!launch.owns_lock()) launch.lock();
+                    if (p->next_launch_ == index) p->next_launch_ = index + 1;
+                    launch.unlock();
+                    p->launch_cv_.notify_all();
+                } else if (queue_turn && !keep_queue) {
+                    if (launch.owns_lock()) launch.unlock();
+                    p->cancel(seq);
+                }
             }
-            for (const auto &u : ring_) arenas.push_back(u == self_ ? reinterpret_cast<void *>(arena_ptr_) : reinterpret_cast<void *>(peers_.at(u).ptr));
+        } turn{this, sequenced, queue_turn, false, index, a.seq, launch};
+
+        const int bank_id = sequenced ? static_cast<int>(index % kSeqBanks) : kSeqBanks + static_cast<int>(a.seq % n_slots_);
+        Bank &bank = banks_[bank_id];
+        while (bank.busy) {
+            retire_if_complete(bank_id);
+            if (!bank.busy) break;
+            launch_cv_.wait_for(launch, std::chrono::milliseconds(1));
+            if (abort_requested && abort_requested()) {
+                res.revoked = a.leased;
+                return res;
+            }
         }
-        cudaSetDevice(device_);
-        Slot &slot = slots_[a.seq % n_slots_];
-        std::lock_guard<std::mutex> slot_lock(slot.mu); // one operation per slot at a time
-        const size_t esz = wire::dtype_size(a.dtype);
-        const int dtype = pccl_dtype(a.dtype), op = pccl_op(a.op), quant = kernel_quant(a.quant);
-        const bool in_place = a.src == a.dst && !a.outer;
+        const uint64_t epoch_base = sequenced ? (sequencer_.flag_epoch(index) + 1) * 1024 : (a.seq + 1) * 1024;
 
-        // symmetric memory: the buffer itself is peer-visible, no staging copy
-        const auto base = static_cast<uintptr_t>(arena_ptr_);
-        const auto p = reinterpret_cast<uintptr_t>(a.src);
-        const bool symmetric = in_place && quant == 0 && sym_bytes_ > 0 && p >= base + sym_offset() && p + a.count * esz <= base + arena_bytes_;
-
+        // ---- staging
+        const bool small = need <= small_half_ && !a.outer;
+        uint64_t stage_off = 0, stage_cap = 0;
+        int slot_id = -1;
+        bool double_buffered = false;
+        if (needs_staging || a.outer) {
+            if (sequenced && small) {
+                const uint64_t parity = (index / kSeqBanks) & 1;
+                stage_off = small_offset(bank_id) + parity * small_half_;
+                stage_cap = small_half_;
+                double_buffered = true;
+            } else {
+                slot_id = static_cast<int>(sequenced ? big_count_++ % n_slots_ : a.seq % n_slots_);
+                stage_off = slot_offset(slot_id);
+                stage_cap = slot_bytes_;
+            }
+        }
         // rounds: the staging slot bounds how much one launch can move
         uint64_t per_round = a.count;
-        if (!symmetric) {
-            const size_t need = pcclKernelP2PStagingBytes(a.count, dtype, quant);
-            if (need > slot_bytes_) {
-                const uint64_t unit = 32 * 4 * a.world * 16; // keeps chunk and quantisation-block alignment
-                per_round = (slot_bytes_ - 4096) / (quant ? 2 : esz);
-                per_round = std::max<uint64_t>(unit, per_round / unit * unit);
-            }
+        if (needs_staging && need > stage_cap) {
+            const uint64_t unit = 32 * 4 * a.world * 16; // keeps chunk and quantisation-block alignment
+            per_round = (stage_cap - 4096) / (quant ? 2 : esz);
+            per_round = std::max<uint64_t>(unit, per_round / unit * unit);
         }
         const uint64_t n_rounds = (a.count + per_round - 1) / per_round;
         if (n_rounds > 255 || (a.outer && n_rounds != 1)) return res;
 
-        if (in_place && !symmetric) {
-            // keep the input for a rollback (the staging slot only holds the last round)
-            if (slot.backup_bytes < a.count * esz) {
-                if (slot.backup) cudaFree(slot.backup);
-                slot.backup = nullptr;
-                slot.backup_bytes = 0;
-                if (cudaMalloc(&slot.backup, a.count * esz) != cudaSuccess) {
-                    (void) cudaGetLastError();
-                    return res;
-                }
-                slot.backup_bytes = a.count * esz;
+        // ---- stream dependencies
+        bank.busy = true;
+        cudaStream_t stream = bank.stream;
+        cudaEventRecord(bank.ready, a.user_stream ? static_cast<cudaStream_t>(a.user_stream) : cudaStreamLegacy);
+        cudaStreamWaitEvent(stream, bank.ready, 0); // inputs may still be in flight where the caller produced them
+        const bool big = !small;
+        if (sequenced) {
+            if (big) {
+                for (int b = 0; b < kSeqBanks; ++b)
+                    if (b != bank_id && banks_[b].used) cudaStreamWaitEvent(stream, banks_[b].stop, 0);
+                last_big_bank_ = bank_id;
+            } else if (last_big_bank_ >= 0 && last_big_bank_ != bank_id) {
+                cudaStreamWaitEvent(stream, banks_[last_big_bank_].stop, 0);
             }
         }
-
-        // inputs may still be in flight on the legacy default stream
-        cudaEventRecord(slot.ready, cudaStreamLegacy);
-        cudaStreamWaitEvent(slot.stream, slot.ready, 0);
-        slot.host_words[0] = 0; // abort flag
-        slot.host_words[1] = 0; // status
-        cudaEventRecord(slot.start, slot.stream);
-        if (in_place && !symmetric) cudaMemcpyAsync(slot.backup, a.src, a.count * esz, cudaMemcpyDeviceToDevice, slot.stream);
-        slot.backup_valid = in_place && !symmetric;
+        if (slot_id >= 0 && slots_[slot_id].used) cudaStreamWaitEvent(stream, slots_[slot_id].last_use, 0);
+        volatile uint32_t *words = reinterpret_cast<volatile uint32_t *>(bank.host_words);
+        words[0] = 0; // abort flag
+        words[1] = 0; // status
+        for (int i = 0; i < 8; ++i) reinterpret_cast<volatile uint64_t *>(bank.host_words + 16)[i] = 0; // phase stamps
+        if (a.want_hash) cudaMemsetAsync(bank.hash_dev, 0, 2 * sizeof(uint64_t), stream);
+        cudaEventRecord(bank.start, stream);
 
         int algorithm = 0;
-        // (opt-in, PCCL_PIPELINE=1: measured on 4xB200 it is no faster than the plain staged kernel --
-        // 1.69-1.97 ms against 1.74 ms for 600 MB -- because the device-to-device copies compete with
-        // the collective kernel for SMs; kept for machines where the copy engines take them)
-        // Staged NVLS for ordinary device buffers, software-pipelined over segments: while segment s is
-        // reduced through the switch (NVLink-bound, in place in the arena), segment s+1 is copied into
-        // the arena and segment s-1 is copied out to the user buffer by the copy engines (HBM-bound).
-        uint64_t seg_bytes = tune_ ? (std::max<uint64_t>(1, env_u64("PCCL_PIPELINE_SEGMENT_MB", 64)) << 20) : pipeline_seg_bytes_;
-        seg_bytes = std::min<uint64_t>(seg_bytes, slot_bytes_ / 2) / 4096 * 4096;
-        const bool pipelined = mc_view && !a.outer && !symmetric && quant == 0 && a.count * esz >= pipeline_min_bytes_ && seg_bytes >= (1u << 20) &&
-                               (a.count * esz + seg_bytes - 1) / seg_bytes <= 250 && env_flag("PCCL_PIPELINE", false);
-        if (pipelined) {
-            const uint64_t bytes = a.count * esz;
-            const uint64_t n_seg = (bytes + seg_bytes - 1) / seg_bytes, ring = slot_bytes_ / seg_bytes;
-            for (auto *v : {&slot.ev_in, &slot.ev_kernel, &slot.ev_out})
-                while (v->size() < n_seg) {
-                    cudaEvent_t e;
-                    if (cudaEventCreateWithFlags(&e, cudaEventDisableTiming) != cudaSuccess) return res;
-                    v->push_back(e);
-                }
-            cudaStreamWaitEvent(slot.copy_in, slot.ready, 0);
-            // the copy-in of this operation may not overtake the copy-out of the previous one
-            cudaEventRecord(slot.ready, slot.stream);
-            cudaStreamWaitEvent(slot.copy_in, slot.ready, 0);
-            const auto *src8 = static_cast<const uint8_t *>(a.src);
-            auto *dst8 = static_cast<uint8_t *>(a.dst);
-            for (uint64_t sgm = 0; sgm < n_seg; ++sgm) {
-                const uint64_t off = sgm * seg_bytes, n = std::min(seg_bytes, bytes - off);
-                const uint64_t stage_off = slot_offset(a.seq % n_slots_) + (sgm % ring) * seg_bytes;
-                uint8_t *stage = reinterpret_cast<uint8_t *>(arena_ptr_) + stage_off;
-                if (sgm >= ring) cudaStreamWaitEvent(slot.copy_in, slot.ev_out[sgm - ring], 0);
-                cudaMemcpyAsync(stage, src8 + off, n, cudaMemcpyDeviceToDevice, slot.copy_in);
-                cudaEventRecord(slot.ev_in[sgm], slot.copy_in);
-                cudaStreamWaitEvent(slot.stream, slot.ev_in[sgm], 0);
-                pcclKernelNvlsArgs_t nk{};
-                pcclKernelP2PArgs_t &k = nk.p2p;
-                for (size_t i = 0; i < arenas.size(); ++i) k.arena[i] = arenas[i];
-                k.rank = a.rank;
-                k.world = a.world;
-                k.flag_slot = static_cast<uint32_t>(a.seq % n_slots_);
-                k.flag_base = (a.seq + 1) * 1024 + sgm * 4;
-                k.data_offset = stage_off;
-                k.data_capacity = seg_bytes + 512;
-                k.src = k.dst = stage;
-                k.count = n / esz;
-                k.dtype = dtype;
-                k.op = op;
-                k.max_blocks = tune_ ? static_cast<int>(env_u64("PCCL_DEVICE_MAX_BLOCKS", 0)) : max_blocks_;
-                k.src_in_arena = 1;
-                k.abort_flag = reinterpret_cast<volatile uint32_t *>(slot.host_words);
-                k.status = slot.host_words + 1;
-                k.timeout_cycles = timeout_ms_ * static_cast<uint64_t>(clock_khz_);
-                nk.mc_arena = mc_view;
-                const int rc = pcclKernelAllReduceNvls(&nk, slot.stream);
-                if (rc != 0) {
-                    PLOG(ERR) << "all-reduce kernel launch failed: " << cudaGetErrorString(static_cast<cudaError_t>(rc));
-                    cudaStreamSynchronize(slot.stream);
-                    return res;
-                }
-                cudaEventRecord(slot.ev_kernel[sgm], slot.stream);
-                cudaStreamWaitEvent(slot.copy_out, slot.ev_kernel[sgm], 0);
-                cudaMemcpyAsync(dst8 + off, stage, n, cudaMemcpyDeviceToDevice, slot.copy_out);
-                cudaEventRecord(slot.ev_out[sgm], slot.copy_out);
-            }
-            cudaStreamWaitEvent(slot.stream, slot.ev_out[n_seg - 1], 0);
-            algorithm = 3;
-            res.kernel_launches = static_cast<uint32_t>(n_seg);
-        }
-        for (uint64_t r = 0; r < (pipelined ? 0 : n_rounds); ++r) {
+        bool launch_failed = false;
+        for (uint64_t r = 0; r < n_rounds && !launch_failed; ++r) {
             const uint64_t off = r * per_round, n = std::min(per_round, a.count - off);
             pcclKernelP2PArgs_t k{};
             for (size_t i = 0; i < arenas.size(); ++i) k.arena[i] = arenas[i];
             k.rank = a.rank;
             k.world = a.world;
-            k.flag_slot = static_cast<uint32_t>(a.seq % n_slots_);
-            k.flag_base = (a.seq + 1) * 1024 + r * 4;
-            k.data_offset = symmetric ? (p - base) + off * esz : slot_offset(a.seq % n_slots_);
-            k.data_capacity = symmetric ? n * esz + 512 : slot_bytes_;
+            k.flag_slot = static_cast<uint32_t>(bank_id);
+            k.flag_base = epoch_base + r * 4;
             k.src = static_cast<const uint8_t *>(a.src) + off * esz;
             k.dst = static_cast<uint8_t *>(a.dst) + off * esz;
             k.count = n;
             k.dtype = dtype;
             k.op = op;
             k.quant_algorithm = quant;
-            k.algorithm = 0;
-            k.max_blocks = max_blocks_;
+            k.src_in_arena = ssym.ok ? 1 : 0;
+            k.dst_in_arena = dsym.ok ? 1 : 0;
+            k.data_offset = ssym.ok ? ssym.offset : stage_off;
+            k.red_offset = dsym.ok ? dsym.offset : stage_off;
+            k.data_capacity = needs_staging || a.outer ? stage_cap : n * esz + 512;
+            k.max_blocks = small && sequenced ? small_grid_ : max_blocks_;
+            k.no_trailing_barrier = double_buffered && !ssym.ok ? 1 : 0;
+            k.abort_flag = words;
+            k.status = bank.host_words + 1;
+            k.stamps = reinterpret_cast<uint64_t *>(bank.host_words + 16);
+            k.hash_out = a.want_hash && n_rounds == 1 ? bank.hash_dev : nullptr;
+            k.timeout_cycles = timeout_ms_ * static_cast<uint64_t>(clock_khz_);
             if (tune_) { // re-read the tuning knobs on every call (benchmark sweeps)
-                k.max_blocks = static_cast<int>(env_u64("PCCL_DEVICE_MAX_BLOCKS", 0));
+                if (!(small && sequenced)) k.max_blocks = static_cast<int>(env_u64("PCCL_DEVICE_MAX_BLOCKS", 0));
                 k.algorithm = static_cast<int>(env_u64("PCCL_DEVICE_VARIANT", 0));
             }
-            k.src_in_arena = symmetric ? 1 : 0;
-            k.abort_flag = reinterpret_cast<volatile uint32_t *>(slot.host_words);
-            k.status = slot.host_words + 1;
-            k.timeout_cycles = timeout_ms_ * static_cast<uint64_t>(clock_khz_);
             int rc;
-            // warp-specialised pipeline (copy-in || switch reduction || copy-out) for staged operands of one round
-            const bool kernel_pipeline = mc_view && !symmetric && quant == 0 && n_rounds == 1 && n * esz >= pipeline_min_bytes_ &&
-                                         (tune_ ? env_flag("PCCL_KERNEL_PIPELINE", kernel_pipeline_) : kernel_pipeline_);
+            // warp-specialised pipeline (copy-in || switch reduction || copy-out) for staged operands of one round; not for
+            // in-place operands, whose output may only be written once the whole reduction is known to be complete
+            const bool kernel_pipeline = mc_view && !ssym.ok && !dsym.ok && quant == 0 && n_rounds == 1 && !in_place &&
+                                         n * esz >= pipeline_min_bytes_ && (tune_ ? env_flag("PCCL_KERNEL_PIPELINE", kernel_pipeline_) : kernel_pipeline_);
             const int segments = static_cast<int>(tune_ ? env_u64("PCCL_PIPELINE_SEGMENTS", 0) : pipeline_segments_);
             if (a.outer) {
                 pcclKernelOuterStep_t step{};
@@ -552,69 +607,113 @@ public:
                     pcclKernelNvlsArgs_t nk{};
                     nk.p2p = k;
                     nk.mc_arena = mc_view;
-                    rc = kernel_pipeline ? pcclKernelAllReduceNvlsPipelined(&nk, &step, segments, slot.stream)
-                                         : pcclKernelOuterStepNvls(&nk, &step, slot.stream);
+                    rc = kernel_pipeline ? pcclKernelAllReduceNvlsPipelined(&nk, &step, segments, stream) : pcclKernelOuterStepNvls(&nk, &step, stream);
                     algorithm = 3;
                 } else {
-                    rc = pcclKernelOuterStepP2P(&k, &step, slot.stream);
+                    rc = pcclKernelOuterStepP2P(&k, &step, stream);
                     algorithm = 2;
                 }
             } else if (mc_view) {
                 pcclKernelNvlsArgs_t nk{};
                 nk.p2p = k;
                 nk.mc_arena = mc_view;
-                rc = kernel_pipeline ? pcclKernelAllReduceNvlsPipelined(&nk, nullptr, segments, slot.stream)
-                                     : pcclKernelAllReduceNvls(&nk, slot.stream);
+                rc = kernel_pipeline ? pcclKernelAllReduceNvlsPipelined(&nk, nullptr, segments, stream) : pcclKernelAllReduceNvls(&nk, stream);
                 algorithm = 3;
             } else {
-                rc = pcclKernelAllReduceP2P(&k, &algorithm, slot.stream);
+                rc = pcclKernelAllReduceP2P(&k, &algorithm, stream);
             }
             if (rc != 0) {
                 PLOG(ERR) << "all-reduce kernel launch failed: " << cudaGetErrorString(static_cast<cudaError_t>(rc));
-                cudaStreamSynchronize(slot.stream);
-                return res;
+                launch_failed = true;
             }
         }
-        cudaEventRecord(slot.stop, slot.stream);
-        if (!pipelined) res.kernel_launches = static_cast<uint32_t>(n_rounds);
+        if (a.want_hash && !launch_failed)
+            cudaMemcpyAsync(bank.hash_host, bank.hash_dev, 2 * sizeof(uint64_t), cudaMemcpyDeviceToHost, stream);
+        cudaEventRecord(bank.stop, stream);
+        bank.used = true;
+        if (slot_id >= 0) {
+            cudaEventRecord(slots_[slot_id].last_use, stream);
+            slots_[slot_id].used = true;
+        }
+        if (a.user_stream) cudaStreamWaitEvent(static_cast<cudaStream_t>(a.user_stream), bank.stop, 0);
 
+        Flight f;
+        f.bank = bank_id;
+        f.tag = a.tag;
+        f.leased = a.leased;
+        f.algorithm = algorithm;
+        f.launches = static_cast<uint32_t>(n_rounds);
+        f.wire_bytes = quant ? a.count : bytes;
+        f.world = a.world;
+        f.want_hash = a.want_hash && n_rounds == 1;
+        f.destroys_input = (in_place && ssym.ok) || (in_place && n_rounds > 1);
+        f.launch_failed = launch_failed;
+        f.queue_turn = queue_turn;
+        f.seq = a.seq;
+        const uint64_t ticket = ++ticket_counter_;
+        {
+            std::lock_guard<std::mutex> lock(inflight_mu_);
+            inflight_.emplace(ticket, f);
+        }
+        bank.ticket = ticket;
+        // pass the turn on: the next operation of the common order may launch now
+        if (sequenced) {
+            next_launch_ = index + 1;
+            launch.unlock();
+            launch_cv_.notify_all();
+        } else {
+            launch.unlock();
+            turn.keep_queue = true; // one at a time: the queue entry is removed when this operation has finished
+        }
+        if (a.enqueue_only && !launch_failed) {
+            res.pending = true;
+            res.ticket = ticket;
+            return res;
+        }
+        return finish(ticket, abort_requested);
+    }
+
+    DeviceReduceResult finish(uint64_t ticket, const std::function<bool()> &abort_requested) override {
+        DeviceReduceResult res;
+        Flight f;
+        {
+            std::lock_guard<std::mutex> launch(launch_mu_); // against retire_if_complete()
+            std::lock_guard<std::mutex> lock(inflight_mu_);
+            const auto it = inflight_.find(ticket);
+            if (it == inflight_.end()) return res;
+            f = it->second;
+            if (f.retired) { // the bank was needed again before the caller came back: the verdict was taken then
+                res = f.result;
+                inflight_.erase(it);
+                return res;
+            }
+            banks_[f.bank].collecting = true;
+        }
+        cudaSetDevice(device_);
+        Bank &bank = banks_[f.bank];
+        volatile uint32_t *words = reinterpret_cast<volatile uint32_t *>(bank.host_words);
         // wait, relaying aborts from the control plane into the kernel
         int polls = 0;
+        bool failed = f.launch_failed;
         for (;;) {
-            const cudaError_t q = cudaEventQuery(slot.stop);
+            const cudaError_t q = cudaEventQuery(bank.stop);
             if (q == cudaSuccess) break;
             if (q != cudaErrorNotReady) {
                 PLOG(ERR) << "device all-reduce failed: " << cudaGetErrorString(q);
                 (void) cudaGetLastError();
-                return res;
+                failed = true;
+                break;
             }
             if ((++polls & 63) == 0 && abort_requested && abort_requested()) {
-                reinterpret_cast<volatile uint32_t *>(slot.host_words)[0] = 1;
+                words[0] = 1;
                 res.aborted = true;
             }
             if (polls > 2000) std::this_thread::sleep_for(std::chrono::microseconds(50));
         }
-        const uint32_t status = reinterpret_cast<volatile uint32_t *>(slot.host_words)[1];
-        cudaEventElapsedTime(&res.device_ms, slot.start, slot.stop);
-        res.plane = algorithm == 1 ? pcclExtPlaneP2POneShot : (algorithm == 3 ? pcclExtPlaneNvls : pcclExtPlaneP2PTwoShot);
-        const uint64_t wire_bytes = quant ? a.count : a.count * esz;
-        res.tx_bytes = res.rx_bytes = algorithm == 1   ? wire_bytes * (a.world - 1)
-                                      : algorithm == 3 ? wire_bytes + wire_bytes / a.world
-                                                       : 2 * wire_bytes * (a.world - 1) / a.world;
-        res.ok = status == 0;
-        if (status == 2) PLOG(ERR) << "device all-reduce timed out waiting for a peer";
+        res = collect(ticket, f, failed, res.aborted);
+        release_bank(f.bank);
+        if (f.queue_turn) cancel(f.seq);
         return res;
-    }
-
-    bool restore_input(const DeviceReduceArgs &a) override {
-        if (!usable_ || slots_.empty()) return false;
-        cudaSetDevice(device_);
-        Slot &slot = slots_[a.seq % n_slots_];
-        std::lock_guard<std::mutex> slot_lock(slot.mu);
-        if (!slot.backup_valid || !slot.backup) return false;
-        const size_t bytes = a.count * wire::dtype_size(a.dtype);
-        if (cudaMemcpyAsync(a.dst, slot.backup, bytes, cudaMemcpyDeviceToDevice, slot.stream) != cudaSuccess) return false;
-        return cudaStreamSynchronize(slot.stream) == cudaSuccess;
     }
 
     bool copy_to_host(void *host_dst, const void *dev_src, size_t bytes) override { return copy(host_dst, dev_src, bytes, cudaMemcpyDeviceToHost); }
@@ -626,7 +725,7 @@ public:
         int prev = -1;
         cudaGetDevice(&prev);
         if (info.is_device && info.device >= 0) cudaSetDevice(info.device);
-        const int rc = pcclKernelHashSync(dev_ptr, bytes, type == wire::HashType::Simple ? 0 : 1, &out);
+        const int rc = pcclKernelHashSync(dev_ptr, bytes, static_cast<int>(type), &out);
         if (prev >= 0) cudaSetDevice(prev);
         if (rc != 0) PLOG(ERR) << "device hash failed: " << cudaGetErrorString(static_cast<cudaError_t>(rc));
         return rc == 0;
@@ -697,7 +796,7 @@ public:
         std::lock_guard<std::mutex> lock(mu_);
         return arena_ptr_ && !slots_.empty() ? slot_bytes_ : 0;
     }
-    std::unique_lock<std::mutex> exchange_lock() override { return std::unique_lock<std::mutex>(slots_[0].mu); }
+    std::unique_lock<std::mutex> exchange_lock() override { return std::unique_lock<std::mutex>(exchange_mu_); }
     bool export_chunk(const void *src, bool, size_t bytes) override {
         if (bytes > slot_bytes_) return false;
         return copy(reinterpret_cast<void *>(arena_ptr_ + slot_offset(0)), src, bytes, cudaMemcpyDefault);
@@ -763,20 +862,195 @@ private:
         CUmemGenericAllocationHandle handle = 0;
         uint8_t gpu_uuid[16] = {0};
     };
-    struct Slot {
-        std::mutex mu;
-        cudaStream_t stream = nullptr;
-        cudaEvent_t start = nullptr, stop = nullptr, ready = nullptr;
-        cudaStream_t copy_in = nullptr, copy_out = nullptr; // staged NVLS pipeline
-        std::vector<cudaEvent_t> ev_in, ev_kernel, ev_out;
-        uint32_t *host_words = nullptr; // [0] abort flag, [1] status; host-mapped
-        void *backup = nullptr;
-        size_t backup_bytes = 0;
-        bool backup_valid = false;
+    struct Slot { // a big staging area; consecutive users are ordered through last_use
+        cudaEvent_t last_use = nullptr;
+        bool used = false;
     };
 
-    size_t slot_offset(uint64_t slot) const { return pcclKernelP2PControlBytes() + slot * slot_bytes_; }
-    size_t sym_offset() const { return pcclKernelP2PControlBytes() + size_t(n_slots_) * slot_bytes_; }
+    size_t slot_offset(uint64_t slot) const { return pcclKernelP2PControlBytes() + small_region_bytes() + slot * slot_bytes_; }
+    size_t sym_offset() const { return pcclKernelP2PControlBytes() + small_region_bytes() + size_t(n_slots_) * slot_bytes_; }
+
+    // ---- per-operation bookkeeping -----------------------------------------------------------
+    static constexpr int kSeqBanks = 16; // flag banks handed out by position in the common order; the rest serve the Commence-queue order
+
+    struct Bank {
+        cudaStream_t stream = nullptr;
+        cudaEvent_t start = nullptr, stop = nullptr, ready = nullptr;
+        uint32_t *host_words = nullptr; // host-mapped: [0] abort flag, [1] status, [16..32) eight 64-bit phase stamps
+        uint64_t *hash_dev = nullptr;   // two raw mset64 sums
+        uint64_t *hash_host = nullptr;  // their page-locked landing place
+        bool busy = false, used = false, collecting = false; // guarded by launch_mu_
+        uint64_t ticket = 0;
+    };
+    struct Flight {
+        int bank = 0;
+        uint64_t tag = 0, seq = 0;
+        bool leased = false, revoked = false, want_hash = false, destroys_input = false, launch_failed = false, queue_turn = false;
+        int algorithm = 0;
+        uint32_t launches = 0, world = 1;
+        uint64_t wire_bytes = 0;
+        bool retired = false;
+        DeviceReduceResult result;
+    };
+    struct SymRef {
+        bool ok = false;
+        uint64_t offset = 0; // from the start of the arena
+    };
+
+    // mu_ held.  An operand counts as symmetric only when the kernels can treat it as such: 16-byte aligned, and its
+    // extent rounded up to whole 16-byte packets stays inside ONE allocation of the symmetric heap (the kernels read and
+    // write whole packets; a view into the middle of an allocation must not spill into its neighbour).
+    SymRef symmetric_ref(const void *ptr, uint64_t bytes) const {
+        SymRef r;
+        if (!arena_ptr_ || sym_bytes_ == 0 || !ptr) return r;
+        const auto p = reinterpret_cast<uintptr_t>(ptr), heap = static_cast<uintptr_t>(arena_ptr_) + sym_offset();
+        if (p < heap || p >= heap + sym_bytes_ || (p - static_cast<uintptr_t>(arena_ptr_)) % 16 != 0) return r;
+        const uint64_t begin = p - heap, end = begin + round_up(bytes, 16);
+        const uint64_t scratch = sym_bytes_ - internal_bytes_;
+        if (begin >= scratch) { // the library's own scratch region is one allocation
+            r.ok = end <= sym_bytes_;
+        } else {
+            auto it = sym_allocs_.upper_bound(begin);
+            if (it != sym_allocs_.begin()) {
+                --it;
+                r.ok = begin >= it->first && end <= it->first + it->second;
+            }
+        }
+        r.offset = p - static_cast<uintptr_t>(arena_ptr_);
+        return r;
+    }
+
+    // mu_ held.  Through the switch every GPU moves about N(1+1/P) bytes per direction (its own stores are echoed back),
+    // peer-to-peer two-shot moves 2N(P-1)/P: multicast pays off from nvls_min_world_ peers.
+    bool nvls_eligible_locked(const DeviceReduceArgs &a) const {
+        return a.quant == wire::QuantAlgo::None && a.world >= nvls_min_world_ && a.count * wire::dtype_size(a.dtype) >= nvls_min_bytes_ &&
+               pcclKernelNvlsSupported(pccl_dtype(a.dtype), pccl_op(a.op)) != 0;
+    }
+
+    DeviceReduceResult collect(uint64_t ticket, const Flight &f, bool failed, bool aborted) {
+        DeviceReduceResult res;
+        Bank &bank = banks_[f.bank];
+        const uint32_t status = reinterpret_cast<volatile uint32_t *>(bank.host_words)[1];
+        if (!failed) cudaEventElapsedTime(&res.device_ms, bank.start, bank.stop);
+        res.aborted = aborted;
+        res.kernel_launches = f.launches;
+        res.plane = f.algorithm == 1 ? pcclExtPlaneP2POneShot : (f.algorithm == 3 ? pcclExtPlaneNvls : pcclExtPlaneP2PTwoShot);
+        res.tx_bytes = res.rx_bytes = f.algorithm == 1   ? f.wire_bytes * (f.world - 1)
+                                      : f.algorithm == 3 ? f.wire_bytes + f.wire_bytes / f.world
+                                                         : 2 * f.wire_bytes * (f.world - 1) / f.world;
+        res.ok = !failed && status == 0;
+        if (status == 2) PLOG(ERR) << "device all-reduce timed out waiting for a peer";
+        if (res.ok && f.want_hash) {
+            res.has_hash = true;
+            res.hash[0] = bank.hash_host[0];
+            res.hash[1] = bank.hash_host[1];
+        }
+        {
+            std::lock_guard<std::mutex> lock(inflight_mu_);
+            const auto it = inflight_.find(ticket);
+            if (it != inflight_.end()) {
+                res.revoked = !res.ok && it->second.revoked;
+                inflight_.erase(it);
+            }
+        }
+        res.input_destroyed = !res.ok && f.destroys_input;
+        for (int i = 0; i < 8; ++i) last_stamps_[i] = reinterpret_cast<volatile uint64_t *>(bank.host_words + 16)[i];
+        return res;
+    }
+
+    void release_bank(int bank_id) {
+        {
+            std::lock_guard<std::mutex> lock(launch_mu_);
+            banks_[bank_id].busy = false;
+            banks_[bank_id].collecting = false;
+        }
+        launch_cv_.notify_all();
+    }
+
+    // launch_mu_ held.  A bank whose enqueue-only operation has finished on the GPU but was not collected yet is freed
+    // for the next operation; the verdict waits in the flight record.
+    void retire_if_complete(int bank_id) {
+        Bank &bank = banks_[bank_id];
+        if (!bank.busy || bank.collecting || cudaEventQuery(bank.stop) != cudaSuccess) return;
+        Flight f;
+        {
+            std::lock_guard<std::mutex> lock(inflight_mu_);
+            const auto it = inflight_.find(bank.ticket);
+            if (it == inflight_.end() || it->second.retired) return;
+            f = it->second;
+        }
+        const uint64_t ticket = bank.ticket;
+        DeviceReduceResult res = collect(ticket, f, f.launch_failed, false);
+        f.retired = true;
+        f.result = res;
+        {
+            std::lock_guard<std::mutex> lock(inflight_mu_);
+            inflight_[ticket] = f;
+        }
+        bank.busy = false;
+    }
+
+    size_t small_offset(int bank_id) const { return pcclKernelP2PControlBytes() + size_t(bank_id) * 2 * small_half_; }
+    size_t small_region_bytes() const { return round_up(size_t(PCCL_K_FLAG_BANKS) * 2 * small_half_, 2u << 20); }
+
+    // Same-box sequencer of the current ring (see sequencer.hpp): the first member of the ring creates the shared log,
+    // the others fetch its descriptor over the rendezvous socket.  Failure just means no leases and Commence-queue order.
+    // mu_ held.
+    void setup_sequencer(const std::vector<Uuid> &ring) {
+        const uint64_t key = ring_key_of(ring);
+        void *mem = nullptr;
+        int fd = -1;
+        if (ring[0] == self_) {
+            fd = ::memfd_create("pccl-sequencer", MFD_CLOEXEC);
+            if (fd < 0 || ::ftruncate(fd, static_cast<off_t>(Sequencer::bytes())) != 0) {
+                if (fd >= 0) ::close(fd);
+                return;
+            }
+            mem = ::mmap(nullptr, Sequencer::bytes(), PROT_READ | PROT_WRITE, MAP_SHARED, fd, 0);
+            if (mem == MAP_FAILED) {
+                ::close(fd);
+                return;
+            }
+            Sequencer::format(mem, Sequencer::fresh_base());
+            std::lock_guard<std::mutex> lock(seq_srv_mu_);
+            seq_fd_ = fd;
+            seq_key_ = key;
+        } else {
+            const auto deadline = clock_type::now() + std::chrono::seconds(10);
+            while (fd < 0 && clock_type::now() < deadline) {
+                RendezvousReply rep{};
+                if (ask(ring[0], kReqSequencer, key, rep, fd) && rep.status == 0 && fd >= 0) break;
+                if (fd >= 0) ::close(fd);
+                fd = -1;
+                if (rep.status == 1) return; // the leader has no sequencer
+                std::this_thread::sleep_for(std::chrono::milliseconds(2));
+            }
+            if (fd < 0) return;
+            mem = ::mmap(nullptr, Sequencer::bytes(), PROT_READ | PROT_WRITE, MAP_SHARED, fd, 0);
+            ::close(fd);
+            if (mem == MAP_FAILED) return;
+        }
+        std::lock_guard<std::mutex> lock(launch_mu_);
+        seq_mem_ = mem;
+        if (!sequencer_.attach(mem)) {
+            ::munmap(mem, Sequencer::bytes());
+            seq_mem_ = nullptr;
+            return;
+        }
+        next_launch_ = 0;
+        PLOG(INFO) << "same-box sequencer attached (flag epochs from " << sequencer_.base() << ")";
+    }
+
+    // launch_mu_ held
+    void drop_sequencer() {
+        sequencer_.detach();
+        if (seq_mem_) ::munmap(seq_mem_, Sequencer::bytes());
+        seq_mem_ = nullptr;
+        std::lock_guard<std::mutex> lock(seq_srv_mu_);
+        if (seq_fd_ >= 0) ::close(seq_fd_);
+        seq_fd_ = -1;
+        seq_key_ = 0;
+    }
 
     static int pccl_dtype(wire::DType t) {
         switch (t) {
@@ -839,7 +1113,7 @@ private:
                 gran = std::max(gran, mg);
             }
         }
-        arena_bytes_ = round_up(pcclKernelP2PControlBytes() + size_t(n_slots_) * slot_bytes_ + sym_bytes_, gran);
+        arena_bytes_ = round_up(pcclKernelP2PControlBytes() + small_region_bytes() + size_t(n_slots_) * slot_bytes_ + sym_bytes_, gran);
         CU_TRY(d.MemCreate(&arena_handle_, arena_bytes_, &prop, 0));
         CU_TRY(d.MemAddressReserve(&arena_ptr_, arena_bytes_, gran, 0, 0));
         CU_TRY(d.MemMap(arena_ptr_, arena_bytes_, 0, arena_handle_, 0));
@@ -851,15 +1125,17 @@ private:
         RT_TRY(cudaMemset(reinterpret_cast<void *>(arena_ptr_), 0, pcclKernelP2PControlBytes()));
         RT_TRY(cudaDeviceSynchronize());
         slots_ = std::vector<Slot>(n_slots_);
-        for (auto &s : slots_) {
-            RT_TRY(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking));
-            RT_TRY(cudaStreamCreateWithFlags(&s.copy_in, cudaStreamNonBlocking));
-            RT_TRY(cudaStreamCreateWithFlags(&s.copy_out, cudaStreamNonBlocking));
-            RT_TRY(cudaEventCreate(&s.start));
-            RT_TRY(cudaEventCreate(&s.stop));
-            RT_TRY(cudaEventCreateWithFlags(&s.ready, cudaEventDisableTiming));
-            RT_TRY(cudaHostAlloc(reinterpret_cast<void **>(&s.host_words), 64, cudaHostAllocMapped));
-            std::memset(s.host_words, 0, 64);
+        for (auto &sl : slots_) RT_TRY(cudaEventCreateWithFlags(&sl.last_use, cudaEventDisableTiming));
+        banks_ = std::vector<Bank>(kSeqBanks + n_slots_);
+        for (auto &b : banks_) {
+            RT_TRY(cudaStreamCreateWithFlags(&b.stream, cudaStreamNonBlocking));
+            RT_TRY(cudaEventCreate(&b.start));
+            RT_TRY(cudaEventCreate(&b.stop));
+            RT_TRY(cudaEventCreateWithFlags(&b.ready, cudaEventDisableTiming));
+            RT_TRY(cudaHostAlloc(reinterpret_cast<void **>(&b.host_words), 256, cudaHostAllocMapped));
+            std::memset(b.host_words, 0, 256);
+            RT_TRY(cudaMalloc(reinterpret_cast<void **>(&b.hash_dev), 2 * sizeof(uint64_t)));
+            RT_TRY(cudaHostAlloc(reinterpret_cast<void **>(&b.hash_host), 2 * sizeof(uint64_t), cudaHostAllocDefault));
         }
         PLOG(INFO) << "device arena of " << (arena_bytes_ >> 20) << " MiB on GPU " << device_;
         return true;
@@ -1115,6 +1391,16 @@ private:
                     rep.pid = static_cast<uint32_t>(::getpid());
                     std::memcpy(rep.gpu_uuid, gpu_uuid_, 16);
                 }
+            } else if (got && req.kind == kReqSequencer) {
+                std::lock_guard<std::mutex> lock(seq_srv_mu_);
+                if (!use_sequencer_) {
+                    rep.status = 1;
+                } else if (seq_fd_ >= 0 && seq_key_ == req.ring_key) {
+                    fd = ::dup(seq_fd_);
+                    rep.status = fd >= 0 ? 0 : 1;
+                } else {
+                    rep.status = 2; // not (yet) created for that ring: ask again
+                }
             } else if (got) {
                 // multicast bookkeeping; this peer answers as the leader (first member of the ring)
                 std::lock_guard<std::mutex> lock(mc_mu_);
@@ -1217,6 +1503,26 @@ private:
     std::unordered_map<Uuid, Peer> peers_;
     std::vector<Uuid> ring_;
     bool ring_ready_ = false;
+
+    // launch order, flag banks, operations in flight
+    std::mutex launch_mu_;
+    std::condition_variable launch_cv_;
+    Sequencer sequencer_;
+    void *seq_mem_ = nullptr;
+    std::mutex seq_srv_mu_; // descriptor of the log this peer created, shared with the server thread
+    int seq_fd_ = -1;
+    uint64_t seq_key_ = 0;
+    bool use_sequencer_ = true;
+    uint64_t next_launch_ = 0, big_count_ = 0;
+    int last_big_bank_ = -1;
+    int small_grid_ = 8;
+    size_t small_half_ = 1u << 20;
+    std::vector<Bank> banks_;
+    std::mutex inflight_mu_;
+    std::map<uint64_t, Flight> inflight_;
+    std::atomic<uint64_t> ticket_counter_{0};
+    uint64_t last_stamps_[8] = {0};
+    std::mutex exchange_mu_;
 
     std::mutex order_mu_;
     std::condition_variable order_cv_;

@@ -18,7 +18,11 @@ public:
     void announce(uint64_t) override {}
     void cancel(uint64_t) override {}
     DeviceReduceResult reduce(const DeviceReduceArgs &, const std::function<bool()> &) override { return {}; }
-    bool restore_input(const DeviceReduceArgs &) override { return false; }
+    bool lease_ready() override { return false; }
+    bool multicast_ready() override { return false; }
+    bool nvls_eligible(const DeviceReduceArgs &) override { return false; }
+    void revoke_leased(uint64_t, bool) override {}
+    DeviceReduceResult finish(uint64_t, const std::function<bool()> &) override { return {}; }
     bool copy_to_host(void *, const void *, size_t) override { return false; }
     bool copy_to_device(void *, const void *, size_t) override { return false; }
     bool hash_device(const void *, size_t, wire::HashType, uint64_t &) override { return false; }

@@ -29,6 +29,11 @@ uint64_t simplehash(const void *data, size_t n_bytes);
 // tree over the warp results padded with zeros).  Exposed for the GPU tests.
 uint32_t simplehash_block_fold(const uint32_t *thread_values);
 
+// mset64: order-independent sum of per-packet terms (csrc/kernels/mset_formula.hpp), the hash the collective kernels can
+// produce while they write their output.  mset64_raw: the unfinalised sum of a span whose first packet has the given index.
+uint64_t mset64(const void *data, size_t n_bytes);
+uint64_t mset64_raw(const void *data, size_t n_bytes, uint64_t first_packet);
+
 uint32_t crc32c(const void *data, size_t n_bytes);
 uint32_t crc32c_generic(const void *data, size_t n_bytes); // table driven, no special instructions
 // CRC of the concatenation A||B from crc(A), crc(B) and len(B)

@@ -17,60 +17,14 @@
 // of the NEXT operation, which this rank enters after its copy-out.
 #include <cmath>
 
-#include "common.cuh"
+#include "collective.cuh"
+#include "hash_mset.cuh"
 #include "outer_step.cuh"
 #include "pccl_kernels.h"
 
 namespace pccl::cuda {
 
-constexpr int kNvlsThreads = 512;
-constexpr size_t kNvlsFlagBankBytes = size_t(PCCL_K_MAX_BLOCKS) * 128;
-
-struct NvlsArgs {
-    uint8_t *arena[PCCL_K_MAX_RANKS]; // unicast mappings, for the flags
-    uint8_t *mc;                      // multicast mapping of the arenas
-    uint32_t rank, world, flag_slot;
-    uint64_t flag_base, data_offset;
-    const void *src;
-    void *dst;
-    uint64_t count;
-    uint64_t avg_divisor;
-    int src_in_arena;
-    volatile uint32_t *abort_flag;
-    uint32_t *status;
-    uint64_t timeout_cycles;
-};
-
-__device__ bool nvls_barrier(const NvlsArgs &a, uint8_t *const *arena, uint64_t value, bool record_failure = true) {
-    __shared__ int s_fail;
-    if (threadIdx.x == 0) s_fail = 0;
-    __threadfence_system(); // multimem stores of this thread are performed before the flag is raised
-    __syncthreads();
-    if (threadIdx.x < a.world) {
-        const uint32_t peer = threadIdx.x;
-        uint64_t *theirs = reinterpret_cast<uint64_t *>(arena[peer] + a.flag_slot * kNvlsFlagBankBytes + size_t(blockIdx.x) * 128) + a.rank;
-        st_flag_release(theirs, value);
-        const uint64_t *mine = reinterpret_cast<const uint64_t *>(arena[a.rank] + a.flag_slot * kNvlsFlagBankBytes + size_t(blockIdx.x) * 128) + peer;
-        const long long t0 = clock64();
-        uint32_t spins = 0;
-        while (ld_flag_acquire(mine) < value) {
-            if ((++spins & 0x3ffu) == 0) {
-                if (*a.abort_flag != 0) {
-                    atomicExch(&s_fail, 1);
-                    break;
-                }
-                if (static_cast<uint64_t>(clock64() - t0) > a.timeout_cycles) {
-                    atomicExch(&s_fail, 2);
-                    break;
-                }
-            }
-        }
-    }
-    __syncthreads();
-    const int fail = s_fail;
-    if (fail != 0 && record_failure && threadIdx.x == 0) atomicMax(a.status, static_cast<uint32_t>(fail));
-    return fail == 0;
-}
+constexpr int kNvlsThreads = kThreads;
 
 enum : int { NV_F32 = 0, NV_BF16 = 1, NV_F16 = 2 };
 
@@ -108,19 +62,21 @@ __device__ __forceinline__ void mc_store(void *p, uint4 v) {
     asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
 }
 
-template <int TYPE> __device__ __forceinline__ uint4 scale_packet(uint4 v, float inv) {
+// AVG finalisation: a true division, like the peer-to-peer kernels and the host kernels (x * (1/world) differs in the
+// last bit for world sizes that are not powers of two)
+template <int TYPE> __device__ __forceinline__ uint4 scale_packet(uint4 v, float div) {
     if constexpr (TYPE == NV_F32) {
-        v.x = __float_as_uint(__uint_as_float(v.x) * inv);
-        v.y = __float_as_uint(__uint_as_float(v.y) * inv);
-        v.z = __float_as_uint(__uint_as_float(v.z) * inv);
-        v.w = __float_as_uint(__uint_as_float(v.w) * inv);
+        v.x = __float_as_uint(__uint_as_float(v.x) / div);
+        v.y = __float_as_uint(__uint_as_float(v.y) / div);
+        v.z = __float_as_uint(__uint_as_float(v.z) / div);
+        v.w = __float_as_uint(__uint_as_float(v.w) / div);
     } else if constexpr (TYPE == NV_BF16) {
         uint32_t *w = &v.x;
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
             __nv_bfloat162 h = *reinterpret_cast<__nv_bfloat162 *>(&w[i]);
             float2 f = __bfloat1622float2(h);
-            h = __floats2bfloat162_rn(f.x * inv, f.y * inv);
+            h = __floats2bfloat162_rn(f.x / div, f.y / div);
             w[i] = *reinterpret_cast<uint32_t *>(&h);
         }
     } else {
@@ -129,7 +85,7 @@ template <int TYPE> __device__ __forceinline__ uint4 scale_packet(uint4 v, float
         for (int i = 0; i < 4; ++i) {
             __half2 h = *reinterpret_cast<__half2 *>(&w[i]);
             float2 f = __half22float2(h);
-            h = __floats2half2_rn(f.x * inv, f.y * inv);
+            h = __floats2half2_rn(f.x / div, f.y / div);
             w[i] = *reinterpret_cast<uint32_t *>(&h);
         }
     }
@@ -149,193 +105,178 @@ __device__ __noinline__ void store_partial(uint8_t *dst, uint64_t lo, uint64_t h
     for (uint64_t b = lo; b < hi; ++b) dst[b] = bytes[b - lo];
 }
 
-template <int U, typename Fn> __device__ __forceinline__ void nvls_owned_packets(uint64_t lo, uint64_t hi, Fn fn) {
-    if (lo >= hi) return;
-    const uint64_t first_tile = lo / kNvlsThreads;
-    uint64_t tile = first_tile + ((blockIdx.x + gridDim.x - first_tile % gridDim.x) % gridDim.x);
-    const uint64_t stride = uint64_t(gridDim.x) * U;
-    for (; tile * kNvlsThreads < hi; tile += stride) {
-        uint64_t v[U];
-        bool ok[U];
-#pragma unroll
-        for (int u = 0; u < U; ++u) {
-            v[u] = (tile + uint64_t(u) * gridDim.x) * kNvlsThreads + threadIdx.x;
-            ok[u] = v[u] >= lo && v[u] < hi;
-        }
-        fn(v, ok);
-    }
-}
+// -----------------------------------------------------------------------------------------
+// plain NVLS all-reduce.  Input region (data_offset) and result region (red_offset) may differ: symmetric out-of-place
+// operands keep their input, and so can be retried after a failure.
+// -----------------------------------------------------------------------------------------
+template <int TYPE, int OP, int U> struct NvlsAllReduce {
+    static __device__ void run(const DevArgs &a) {
+        constexpr int ESZ = TYPE == NV_F32 ? 4 : 2;
+        constexpr int N = 16 / ESZ;
+        __shared__ PeerTable tbl;
+        load_peer_table(tbl, a);
+        const uint64_t n_pack = (a.count + N - 1) / N;
+        const uint64_t per = (n_pack + a.world - 1) / a.world;
+        const uint8_t *src = static_cast<const uint8_t *>(a.src);
+        uint8_t *dst = static_cast<uint8_t *>(a.dst);
+        uint4 *mine = reinterpret_cast<uint4 *>(tbl.base[a.rank]);
+        const uint4 *mine_red = reinterpret_cast<const uint4 *>(tbl.red[a.rank]);
+        const uint4 *mc_in = reinterpret_cast<const uint4 *>(a.mc + a.data_offset);
+        uint4 *mc_out = reinterpret_cast<uint4 *>(a.mc + a.red_offset);
+        const uint64_t full_packets = a.count / N; // packets completely inside the user buffers
+        const bool aligned = ((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst)) & 15) == 0;
+        stamp(a, 0);
 
-template <int TYPE, int OP, int U, bool PIPELINED> __global__ void __launch_bounds__(kNvlsThreads, 1) allreduce_nvls_kernel(const NvlsArgs a) {
-    constexpr int ESZ = TYPE == NV_F32 ? 4 : 2;
-    constexpr int N = 16 / ESZ;
-    __shared__ uint8_t *s_arena[PCCL_K_MAX_RANKS];
-    if (threadIdx.x < PCCL_K_MAX_RANKS) s_arena[threadIdx.x] = threadIdx.x < a.world ? a.arena[threadIdx.x] : nullptr;
-    __syncthreads();
-    const uint64_t n_pack = (a.count + N - 1) / N;
-    const uint64_t per = (n_pack + a.world - 1) / a.world;
-    const uint8_t *src = static_cast<const uint8_t *>(a.src);
-    uint8_t *dst = static_cast<uint8_t *>(a.dst);
-    uint4 *mine = reinterpret_cast<uint4 *>(s_arena[a.rank] + a.data_offset);
-    uint4 *mc = reinterpret_cast<uint4 *>(a.mc + a.data_offset);
-    const uint64_t full_packets = a.count / N; // packets completely inside the user buffers
-    const bool aligned = ((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst)) & 15) == 0;
-
-    if (!a.src_in_arena) {
-        nvls_owned_packets<4>(0, n_pack, [&](const uint64_t(&v)[4], const bool(&ok)[4]) {
-            uint4 tmp[4];
+        if (!a.src_in_arena) {
+            for_owned_packets<4>(0, n_pack, [&](const uint64_t(&v)[4], const bool(&ok)[4]) {
+                uint4 tmp[4];
 #pragma unroll
-            for (int u = 0; u < 4; ++u) {
-                if (!ok[u]) continue;
-                if (aligned && v[u] < full_packets) {
-                    tmp[u] = ld_stream_16(src + v[u] * 16);
-                } else {
-                    tmp[u] = load_partial(src, v[u] * 16, min(v[u] * 16 + 16, uint64_t(a.count * ESZ)));
+                for (int u = 0; u < 4; ++u) {
+                    if (!ok[u]) continue;
+                    if (aligned && v[u] < full_packets) {
+                        tmp[u] = ld_stream_16(src + v[u] * 16);
+                    } else {
+                        tmp[u] = load_partial(src, v[u] * 16, min(v[u] * 16 + 16, uint64_t(a.count * ESZ)));
+                    }
                 }
-            }
 #pragma unroll
-            for (int u = 0; u < 4; ++u)
-                if (ok[u]) mine[v[u]] = tmp[u];
-        });
-    }
-    if (!nvls_barrier(a, s_arena, a.flag_base + 1)) return;
+                for (int u = 0; u < 4; ++u)
+                    if (ok[u]) mine[v[u]] = tmp[u];
+            });
+        }
+        stamp(a, 1);
+        if (!peer_barrier<true>(a, tbl, a.flag_base + 1)) {
+            if (a.commit_before_write) grid_commit(a, tbl.arena[a.rank], false);
+            return;
+        }
+        stamp(a, 2);
 
-    {
-        const uint64_t lo = min(uint64_t(a.rank) * per, n_pack), hi = min(lo + per, n_pack);
-        const float inv = a.avg_divisor ? 1.0f / static_cast<float>(a.avg_divisor) : 1.0f;
-        if constexpr (!PIPELINED) {
-            nvls_owned_packets<U>(lo, hi, [&](const uint64_t(&v)[U], const bool(&ok)[U]) {
+        MsetAcc digest;
+        {
+            const uint64_t lo = min(uint64_t(a.rank) * per, n_pack), hi = min(lo + per, n_pack);
+            const float div = static_cast<float>(a.avg_divisor);
+            for_owned_packets<U>(lo, hi, [&](const uint64_t(&v)[U], const bool(&ok)[U]) {
                 uint4 val[U];
 #pragma unroll
                 for (int u = 0; u < U; ++u)
-                    if (ok[u]) val[u] = mc_ld_reduce<TYPE, OP>(mc + v[u]);
+                    if (ok[u]) val[u] = mc_ld_reduce<TYPE, OP>(mc_in + v[u]);
 #pragma unroll
                 for (int u = 0; u < U; ++u) {
                     if (!ok[u]) continue;
-                    if (a.avg_divisor) val[u] = scale_packet<TYPE>(val[u], inv);
-                    mc_store(mc + v[u], val[u]);
+                    if (a.avg_divisor) val[u] = scale_packet<TYPE>(val[u], div);
+                    mc_store(mc_out + v[u], val[u]);
+                    if (a.hash_out) digest.add(v[u], val[u], a.count * ESZ);
                 }
             });
-        } else {
-            // software pipeline: the loads of the next batch are in flight while the current batch
-            // is scaled and stored
-            const uint64_t first_tile = lo / kNvlsThreads;
-            uint64_t tile = first_tile + ((blockIdx.x + gridDim.x - first_tile % gridDim.x) % gridDim.x);
-            const uint64_t stride = uint64_t(gridDim.x) * U;
-            uint4 cur[U], nxt[U];
-            uint64_t cv[U];
-            bool cok[U];
-            auto issue = [&](uint64_t t, uint4(&val)[U], uint64_t(&v)[U], bool(&ok)[U]) {
-#pragma unroll
-                for (int u = 0; u < U; ++u) {
-                    v[u] = (t + uint64_t(u) * gridDim.x) * kNvlsThreads + threadIdx.x;
-                    ok[u] = v[u] >= lo && v[u] < hi;
-                    if (ok[u]) val[u] = mc_ld_reduce<TYPE, OP>(mc + v[u]);
-                }
-            };
-            if (lo < hi && tile * kNvlsThreads < hi) {
-                issue(tile, cur, cv, cok);
-                for (;;) {
-                    const uint64_t next_tile = tile + stride;
-                    const bool more = next_tile * kNvlsThreads < hi;
-                    uint64_t nv[U];
-                    bool nok[U];
-                    if (more) issue(next_tile, nxt, nv, nok);
-#pragma unroll
-                    for (int u = 0; u < U; ++u) {
-                        if (!cok[u]) continue;
-                        if (a.avg_divisor) cur[u] = scale_packet<TYPE>(cur[u], inv);
-                        mc_store(mc + cv[u], cur[u]);
-                    }
-                    if (!more) break;
-#pragma unroll
-                    for (int u = 0; u < U; ++u) {
-                        cur[u] = nxt[u];
-                        cv[u] = nv[u];
-                        cok[u] = nok[u];
-                    }
-                    tile = next_tile;
-                }
-            }
         }
-    }
-    if (!nvls_barrier(a, s_arena, a.flag_base + 2)) return;
+        stamp(a, 3);
+        if (a.hash_out) digest_publish(a, tbl, digest.block_total());
+        if (a.commit_before_write) { // in place on an ordinary buffer: all blocks of this rank write the output, or none
+            const bool reduced_everywhere = peer_barrier<true>(a, tbl, a.flag_base + 2);
+            if (!grid_commit(a, tbl.arena[a.rank], reduced_everywhere)) return;
+        } else if (!peer_barrier<true>(a, tbl, a.flag_base + 2)) {
+            return;
+        }
+        if (a.hash_out) digest_collect(a, tbl, a.hash_out);
+        stamp(a, 4);
 
-    if (!a.src_in_arena) {
-        nvls_owned_packets<4>(0, n_pack, [&](const uint64_t(&v)[4], const bool(&ok)[4]) {
-            uint4 tmp[4];
+        if (!a.dst_in_arena) {
+            for_owned_packets<4>(0, n_pack, [&](const uint64_t(&v)[4], const bool(&ok)[4]) {
+                uint4 tmp[4];
 #pragma unroll
-            for (int u = 0; u < 4; ++u)
-                if (ok[u]) tmp[u] = ld_peer_16(mine + v[u]); // written through the switch: do not trust L1
+                for (int u = 0; u < 4; ++u)
+                    if (ok[u]) tmp[u] = ld_peer_16(mine_red + v[u]); // written through the switch: do not trust L1
 #pragma unroll
-            for (int u = 0; u < 4; ++u) {
-                if (!ok[u]) continue;
-                if (aligned && v[u] < full_packets) {
-                    st_stream_16(dst + v[u] * 16, tmp[u]);
-                } else {
-                    store_partial(dst, v[u] * 16, min(v[u] * 16 + 16, uint64_t(a.count * ESZ)), tmp[u]);
+                for (int u = 0; u < 4; ++u) {
+                    if (!ok[u]) continue;
+                    if (aligned && v[u] < full_packets) {
+                        st_stream_16(dst + v[u] * 16, tmp[u]);
+                    } else {
+                        store_partial(dst, v[u] * 16, min(v[u] * 16 + 16, uint64_t(a.count * ESZ)), tmp[u]);
+                    }
                 }
-            }
-        });
+            });
+        }
+        stamp(a, 5);
+        // No trailing barrier for staged operands: a peer can only touch this arena's staging area again after the first
+        // barrier of the NEXT operation on this flag bank, which this rank enters after its copy-out.  Symmetric operands
+        // belong to the caller, who may rewrite them as soon as this kernel ends -- but only the owner of a chunk reads
+        // the inputs of that chunk (through the switch), and it is done before it raises the second barrier.
     }
-}
+};
 
 // -----------------------------------------------------------------------------------------
-// DiLoCo outer step in one launch (fp32, AVG): the staging pass computes the pseudo-gradient, the
-// switch averages it, the write-out pass is the Nesterov update.  Nothing the caller owns is
-// written before the second barrier, i.e. before every rank holds the complete average.
+// DiLoCo outer step in one launch (fp32, AVG): the staging pass computes the pseudo-gradient, the switch averages
+// it, the write-out pass is the Nesterov update.  Nothing the caller owns is written before EVERY block of this rank
+// knows that every rank holds the complete average (second barrier + grid-wide commit).
 // -----------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kNvlsThreads, 1) outer_step_nvls_kernel(const NvlsArgs a, const OuterStepDev s) {
-    __shared__ uint8_t *s_arena[PCCL_K_MAX_RANKS];
-    if (threadIdx.x < PCCL_K_MAX_RANKS) s_arena[threadIdx.x] = threadIdx.x < a.world ? a.arena[threadIdx.x] : nullptr;
-    __syncthreads();
-    const uint64_t n_pack = (a.count + 3) / 4;
-    const uint64_t per = (n_pack + a.world - 1) / a.world;
-    uint4 *mine = reinterpret_cast<uint4 *>(s_arena[a.rank] + a.data_offset);
-    uint4 *mc = reinterpret_cast<uint4 *>(a.mc + a.data_offset);
+struct NvlsOuter {
+    static __device__ void run(const DevArgs &a, const OuterStepDev &s) {
+        __shared__ PeerTable tbl;
+        load_peer_table(tbl, a);
+        const uint64_t n_pack = (a.count + 3) / 4;
+        const uint64_t per = (n_pack + a.world - 1) / a.world;
+        uint4 *mine = reinterpret_cast<uint4 *>(tbl.base[a.rank]);
+        uint4 *mc = reinterpret_cast<uint4 *>(a.mc + a.data_offset);
+        stamp(a, 0);
 
-    nvls_owned_packets<4>(0, n_pack, [&](const uint64_t(&v)[4], const bool(&ok)[4]) {
-        uint4 d[4];
-#pragma unroll
-        for (int u = 0; u < 4; ++u)
-            if (ok[u]) d[u] = outer_delta_packet(s, v[u], a.count);
-#pragma unroll
-        for (int u = 0; u < 4; ++u)
-            if (ok[u]) mine[v[u]] = d[u];
-    });
-    if (!nvls_barrier(a, s_arena, a.flag_base + 1)) return;
-
-    {
-        const uint64_t lo = min(uint64_t(a.rank) * per, n_pack), hi = min(lo + per, n_pack);
-        const float inv = 1.0f / static_cast<float>(a.world);
-        nvls_owned_packets<4>(lo, hi, [&](const uint64_t(&v)[4], const bool(&ok)[4]) {
-            uint4 val[4];
+        for_owned_packets<4>(0, n_pack, [&](const uint64_t(&v)[4], const bool(&ok)[4]) {
+            uint4 d[4];
 #pragma unroll
             for (int u = 0; u < 4; ++u)
-                if (ok[u]) val[u] = mc_ld_reduce<NV_F32, OP_SUM>(mc + v[u]);
+                if (ok[u]) d[u] = outer_delta_packet(s, v[u], a.count);
 #pragma unroll
             for (int u = 0; u < 4; ++u)
-                if (ok[u]) mc_store(mc + v[u], scale_packet<NV_F32>(val[u], inv));
+                if (ok[u]) mine[v[u]] = d[u];
         });
-    }
-    if (!nvls_barrier(a, s_arena, a.flag_base + 2)) return;
+        stamp(a, 1);
+        if (!peer_barrier<true>(a, tbl, a.flag_base + 1)) {
+            grid_commit(a, tbl.arena[a.rank], false);
+            return;
+        }
+        stamp(a, 2);
 
-    // 4 packets x 3 loads in flight per thread: with one 512-thread block per SM this phase needs ~45 KB
-    // outstanding per SM to keep HBM busy
-    nvls_owned_packets<4>(0, n_pack, [&](const uint64_t(&v)[4], const bool(&ok)[4]) {
-        uint4 g[4];
-        OuterLoaded l[4];
+        {
+            const uint64_t lo = min(uint64_t(a.rank) * per, n_pack), hi = min(lo + per, n_pack);
+            const float div = static_cast<float>(a.world);
+            for_owned_packets<4>(lo, hi, [&](const uint64_t(&v)[4], const bool(&ok)[4]) {
+                uint4 val[4];
 #pragma unroll
-        for (int u = 0; u < 4; ++u)
-            if (ok[u]) {
-                g[u] = ld_peer_16(mine + v[u]); // written through the switch: do not trust L1
-                l[u] = outer_load_packet(s, v[u], a.count);
-            }
+                for (int u = 0; u < 4; ++u)
+                    if (ok[u]) val[u] = mc_ld_reduce<NV_F32, OP_SUM>(mc + v[u]);
 #pragma unroll
-        for (int u = 0; u < 4; ++u)
-            if (ok[u]) outer_apply_packet(s, v[u], a.count, g[u], l[u]);
-    });
-}
+                for (int u = 0; u < 4; ++u)
+                    if (ok[u]) mc_store(mc + v[u], scale_packet<NV_F32>(val[u], div));
+            });
+        }
+        stamp(a, 3);
+        const bool reduced_everywhere = peer_barrier<true>(a, tbl, a.flag_base + 2);
+        if (!grid_commit(a, tbl.arena[a.rank], reduced_everywhere)) return;
+        stamp(a, 4);
+
+        // 4 packets x 3 loads in flight per thread: with one 512-thread block per SM this phase needs ~45 KB
+        // outstanding per SM to keep HBM busy
+        MsetAcc dig_p, dig_m;
+        for_owned_packets<4>(0, n_pack, [&](const uint64_t(&v)[4], const bool(&ok)[4]) {
+            uint4 g[4];
+            OuterLoaded l[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+                if (ok[u]) {
+                    g[u] = ld_peer_16(mine + v[u]); // written through the switch: do not trust L1
+                    l[u] = outer_load_packet(s, v[u], a.count);
+                }
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+                if (ok[u]) outer_apply_packet(s, v[u], a.count, g[u], l[u], a.hash_out ? &dig_p : nullptr, a.hash_out ? &dig_m : nullptr);
+        });
+        if (a.hash_out) {
+            dig_p.flush(a.hash_out);
+            dig_m.flush(a.hash_out + 1);
+        }
+        stamp(a, 5);
+    }
+};
 
 // -----------------------------------------------------------------------------------------
 // Software-pipelined variant for operands that are NOT in symmetric memory: the three phases of the staged
@@ -350,7 +291,7 @@ __global__ void __launch_bounds__(kNvlsThreads, 1) outer_step_nvls_kernel(const 
 // iteration j+1), and the three touch disjoint arena regions within one iteration.
 // OUTER = true is the DiLoCo outer step: A computes the pseudo-gradient; the Nesterov update must not start before
 // the WHOLE average is known to be complete (a failed step may not leave a half-updated model behind), so there
-// C is not pipelined: it runs with all warps after the last barrier.
+// C is not pipelined: it runs with all warps after the last barrier and the grid-wide commit.
 // -----------------------------------------------------------------------------------------
 constexpr int kGroupThreads = kNvlsThreads / 2;
 
@@ -373,102 +314,130 @@ template <int U, typename Fn> __device__ __forceinline__ void nvls_group_packets
     }
 }
 
-template <int TYPE, int OP, bool OUTER>
-__global__ void __launch_bounds__(kNvlsThreads, 1)
-    allreduce_nvls_pipelined_kernel(const NvlsArgs a, const OuterStepDev s, const uint32_t n_seg, const uint64_t seg_pack) {
-    constexpr int ESZ = TYPE == NV_F32 ? 4 : 2;
-    constexpr int N = 16 / ESZ;
-    __shared__ uint8_t *s_arena[PCCL_K_MAX_RANKS];
-    if (threadIdx.x < PCCL_K_MAX_RANKS) s_arena[threadIdx.x] = threadIdx.x < a.world ? a.arena[threadIdx.x] : nullptr;
-    __syncthreads();
-    const bool memory_group = threadIdx.x < kGroupThreads;
-    const int gtid = threadIdx.x % kGroupThreads;
-    const uint64_t n_pack = (a.count + N - 1) / N;
-    const uint8_t *src = static_cast<const uint8_t *>(a.src);
-    uint8_t *dst = static_cast<uint8_t *>(a.dst);
-    uint4 *mine = reinterpret_cast<uint4 *>(s_arena[a.rank] + a.data_offset);
-    uint4 *mc = reinterpret_cast<uint4 *>(a.mc + a.data_offset);
-    const uint64_t full_packets = a.count / N;
-    const bool aligned = OUTER || ((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst)) & 15) == 0;
-    const float inv = a.avg_divisor ? 1.0f / static_cast<float>(a.avg_divisor) : 1.0f;
-    const uint64_t per = seg_pack / a.world; // the launcher makes segments a multiple of world * tile
-    const uint32_t last_iter = OUTER ? n_seg : n_seg + 1;
+struct PipelineGeometry {
+    uint32_t n_seg;
+    uint64_t seg_pack;
+};
 
-    for (uint32_t i = 0; i <= last_iter; ++i) {
-        if (memory_group) {
-            if (i < n_seg) { // A: stage segment i
-                const uint64_t lo = min(uint64_t(i) * seg_pack, n_pack), hi = min(lo + seg_pack, n_pack);
-                nvls_group_packets<4>(lo, hi, gtid, [&](const uint64_t(&v)[4], const bool(&ok)[4]) {
-                    uint4 tmp[4];
+template <int TYPE, int OP, bool OUTER> struct NvlsPipelined {
+    static __device__ void run(const DevArgs &a, const OuterStepDev &s, const PipelineGeometry &geo) {
+        constexpr int ESZ = TYPE == NV_F32 ? 4 : 2;
+        constexpr int N = 16 / ESZ;
+        __shared__ PeerTable tbl;
+        load_peer_table(tbl, a);
+        const uint32_t n_seg = geo.n_seg;
+        const uint64_t seg_pack = geo.seg_pack;
+        const bool memory_group = threadIdx.x < kGroupThreads;
+        const int gtid = threadIdx.x % kGroupThreads;
+        const uint64_t n_pack = (a.count + N - 1) / N;
+        const uint8_t *src = static_cast<const uint8_t *>(a.src);
+        uint8_t *dst = static_cast<uint8_t *>(a.dst);
+        uint4 *mine = reinterpret_cast<uint4 *>(tbl.base[a.rank]);
+        uint4 *mc = reinterpret_cast<uint4 *>(a.mc + a.data_offset);
+        const uint64_t full_packets = a.count / N;
+        const bool aligned = OUTER || ((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst)) & 15) == 0;
+        const float div = static_cast<float>(a.avg_divisor);
+        const uint64_t per = seg_pack / a.world; // the launcher makes segments a multiple of world * tile
+        const uint32_t last_iter = OUTER ? n_seg : n_seg + 1;
+        MsetAcc digest;
+        stamp(a, 0);
+
+        for (uint32_t i = 0; i <= last_iter; ++i) {
+            if (memory_group) {
+                if (i < n_seg) { // A: stage segment i
+                    const uint64_t lo = min(uint64_t(i) * seg_pack, n_pack), hi = min(lo + seg_pack, n_pack);
+                    nvls_group_packets<4>(lo, hi, gtid, [&](const uint64_t(&v)[4], const bool(&ok)[4]) {
+                        uint4 tmp[4];
 #pragma unroll
-                    for (int u = 0; u < 4; ++u) {
-                        if (!ok[u]) continue;
-                        if constexpr (OUTER) {
-                            tmp[u] = outer_delta_packet(s, v[u], a.count);
-                        } else {
-                            if (aligned && v[u] < full_packets)
-                                tmp[u] = ld_stream_16(src + v[u] * 16);
-                            else
-                                tmp[u] = load_partial(src, v[u] * 16, min(v[u] * 16 + 16, uint64_t(a.count * ESZ)));
+                        for (int u = 0; u < 4; ++u) {
+                            if (!ok[u]) continue;
+                            if constexpr (OUTER) {
+                                tmp[u] = outer_delta_packet(s, v[u], a.count);
+                            } else {
+                                if (aligned && v[u] < full_packets)
+                                    tmp[u] = ld_stream_16(src + v[u] * 16);
+                                else
+                                    tmp[u] = load_partial(src, v[u] * 16, min(v[u] * 16 + 16, uint64_t(a.count * ESZ)));
+                            }
                         }
-                    }
 #pragma unroll
-                    for (int u = 0; u < 4; ++u)
-                        if (ok[u]) mine[v[u]] = tmp[u];
-                });
-            }
-            if (!OUTER && i >= 2) { // C: write segment i-2 out
-                const uint64_t lo = min(uint64_t(i - 2) * seg_pack, n_pack), hi = min(lo + seg_pack, n_pack);
-                nvls_group_packets<4>(lo, hi, gtid, [&](const uint64_t(&v)[4], const bool(&ok)[4]) {
-                    uint4 tmp[4];
+                        for (int u = 0; u < 4; ++u)
+                            if (ok[u]) mine[v[u]] = tmp[u];
+                    });
+                }
+                if (!OUTER && i >= 2) { // C: write segment i-2 out
+                    const uint64_t lo = min(uint64_t(i - 2) * seg_pack, n_pack), hi = min(lo + seg_pack, n_pack);
+                    nvls_group_packets<4>(lo, hi, gtid, [&](const uint64_t(&v)[4], const bool(&ok)[4]) {
+                        uint4 tmp[4];
 #pragma unroll
-                    for (int u = 0; u < 4; ++u)
-                        if (ok[u]) tmp[u] = ld_peer_16(mine + v[u]);
+                        for (int u = 0; u < 4; ++u)
+                            if (ok[u]) tmp[u] = ld_peer_16(mine + v[u]);
 #pragma unroll
-                    for (int u = 0; u < 4; ++u) {
+                        for (int u = 0; u < 4; ++u) {
+                            if (!ok[u]) continue;
+                            if (aligned && v[u] < full_packets)
+                                st_stream_16(dst + v[u] * 16, tmp[u]);
+                            else
+                                store_partial(dst, v[u] * 16, min(v[u] * 16 + 16, uint64_t(a.count * ESZ)), tmp[u]);
+                            if (!OUTER && a.hash_out) digest.add(v[u], tmp[u], a.count * ESZ);
+                        }
+                    });
+                }
+            } else if (i >= 1 && i <= n_seg) { // B: reduce this rank's share of segment i-1 through the switch
+                const uint64_t slo = min(uint64_t(i - 1) * seg_pack, n_pack), shi = min(slo + seg_pack, n_pack);
+                const uint64_t lo = min(slo + uint64_t(a.rank) * per, shi), hi = min(lo + per, shi);
+                nvls_group_packets<8>(lo, hi, gtid, [&](const uint64_t(&v)[8], const bool(&ok)[8]) {
+                    uint4 val[8];
+#pragma unroll
+                    for (int u = 0; u < 8; ++u)
+                        if (ok[u]) val[u] = mc_ld_reduce<TYPE, OP>(mc + v[u]);
+#pragma unroll
+                    for (int u = 0; u < 8; ++u) {
                         if (!ok[u]) continue;
-                        if (aligned && v[u] < full_packets)
-                            st_stream_16(dst + v[u] * 16, tmp[u]);
-                        else
-                            store_partial(dst, v[u] * 16, min(v[u] * 16 + 16, uint64_t(a.count * ESZ)), tmp[u]);
+                        if (a.avg_divisor) val[u] = scale_packet<TYPE>(val[u], div);
+                        mc_store(mc + v[u], val[u]);
                     }
                 });
             }
-        } else if (i >= 1 && i <= n_seg) { // B: reduce this rank's share of segment i-1 through the switch
-            const uint64_t slo = min(uint64_t(i - 1) * seg_pack, n_pack), shi = min(slo + seg_pack, n_pack);
-            const uint64_t lo = min(slo + uint64_t(a.rank) * per, shi), hi = min(lo + per, shi);
-            nvls_group_packets<8>(lo, hi, gtid, [&](const uint64_t(&v)[8], const bool(&ok)[8]) {
-                uint4 val[8];
-#pragma unroll
-                for (int u = 0; u < 8; ++u)
-                    if (ok[u]) val[u] = mc_ld_reduce<TYPE, OP>(mc + v[u]);
-#pragma unroll
-                for (int u = 0; u < 8; ++u) {
-                    if (!ok[u]) continue;
-                    if (a.avg_divisor) val[u] = scale_packet<TYPE>(val[u], inv);
-                    mc_store(mc + v[u], val[u]);
+            if (OUTER || i < last_iter) {
+                const bool passed = peer_barrier<true>(a, tbl, a.flag_base + 1 + i);
+                if constexpr (OUTER) {
+                    if (i == last_iter) {
+                        if (!grid_commit(a, tbl.arena[a.rank], passed)) return;
+                    } else if (!passed) {
+                        grid_commit(a, tbl.arena[a.rank], false);
+                        return;
+                    }
+                } else if (!passed) {
+                    return;
                 }
-            });
+            }
         }
-        if (OUTER || i < last_iter)
-            if (!nvls_barrier(a, s_arena, a.flag_base + 1 + i)) return;
-    }
-    if constexpr (OUTER) {
-        nvls_owned_packets<4>(0, n_pack, [&](const uint64_t(&v)[4], const bool(&ok)[4]) {
-            uint4 g[4];
-            OuterLoaded l[4];
+        if constexpr (OUTER) {
+            MsetAcc dig_p, dig_m;
+            for_owned_packets<4>(0, n_pack, [&](const uint64_t(&v)[4], const bool(&ok)[4]) {
+                uint4 g[4];
+                OuterLoaded l[4];
 #pragma unroll
-            for (int u = 0; u < 4; ++u)
-                if (ok[u]) {
-                    g[u] = ld_peer_16(mine + v[u]);
-                    l[u] = outer_load_packet(s, v[u], a.count);
-                }
+                for (int u = 0; u < 4; ++u)
+                    if (ok[u]) {
+                        g[u] = ld_peer_16(mine + v[u]);
+                        l[u] = outer_load_packet(s, v[u], a.count);
+                    }
 #pragma unroll
-            for (int u = 0; u < 4; ++u)
-                if (ok[u]) outer_apply_packet(s, v[u], a.count, g[u], l[u]);
-        });
+                for (int u = 0; u < 4; ++u)
+                    if (ok[u]) outer_apply_packet(s, v[u], a.count, g[u], l[u], a.hash_out ? &dig_p : nullptr, a.hash_out ? &dig_m : nullptr);
+            });
+            if (a.hash_out) {
+                dig_p.flush(a.hash_out);
+                dig_m.flush(a.hash_out + 1);
+            }
+        } else if (a.hash_out) {
+            digest.flush(a.hash_out); // the write-out pass saw every packet of the result
+        }
+        stamp(a, 5);
     }
-}
+};
 
 } // namespace pccl::cuda
 
@@ -480,47 +449,44 @@ extern "C" int pcclKernelNvlsSupported(int dtype, int op) {
     return 0;
 }
 
-extern "C" int pcclKernelAllReduceNvls(const pcclKernelNvlsArgs_t *args, void *stream_v) {
-    if (!args || !args->mc_arena) return cudaErrorInvalidValue;
+namespace {
+bool fill_nvls_args(const pcclKernelNvlsArgs_t *args, int dtype, int rop, DevArgs &d) {
+    if (!args || !args->mc_arena) return false;
     const pcclKernelP2PArgs_t &p = args->p2p;
-    if (p.world < 2 || p.world > PCCL_K_MAX_RANKS || p.rank >= p.world) return cudaErrorInvalidValue;
-    if (!pcclKernelNvlsSupported(p.dtype, p.op)) return cudaErrorInvalidValue;
-    NvlsArgs d{};
-    for (uint32_t r = 0; r < p.world; ++r) d.arena[r] = static_cast<uint8_t *>(p.arena[r]);
+    if (p.world < 2 || p.count == 0 || !pcclKernelNvlsSupported(dtype, rop)) return false;
+    if (!fill_dev_args(p, d)) return false;
     d.mc = static_cast<uint8_t *>(args->mc_arena);
-    d.rank = p.rank;
-    d.world = p.world;
-    d.flag_slot = p.flag_slot;
-    d.flag_base = p.flag_base;
-    d.data_offset = p.data_offset;
-    d.src = p.src;
-    d.dst = p.dst;
-    d.count = p.count;
-    d.avg_divisor = p.op == pcclAvg ? p.world : 0;
-    d.src_in_arena = p.src_in_arena;
-    d.abort_flag = p.abort_flag;
-    d.status = p.status;
-    d.timeout_cycles = p.timeout_cycles ? p.timeout_cycles : ~0ull;
-    const size_t esz = p.dtype == pcclFloat ? 4 : 2;
-    if ((p.count * esz + 15) / 16 * 16 + 256 > p.data_capacity) return cudaErrorInvalidValue;
-    if (p.data_offset % 16 != 0) return cudaErrorInvalidValue;
-    const uint64_t n_pack = (p.count * esz + 15) / 16;
-    const uint64_t tiles = (n_pack + kNvlsThreads - 1) / kNvlsThreads;
+    d.avg_divisor = rop == pcclAvg ? p.world : 0;
+    const size_t esz = dtype == pcclFloat ? 4 : 2;
+    if ((p.count * esz + 15) / 16 * 16 + 256 > p.data_capacity) return false;
+    return true;
+}
+int grid_for(const pcclKernelP2PArgs_t &p, uint64_t chunk_tiles) {
     int max_blocks = p.max_blocks > 0 ? p.max_blocks : 144;
     if (max_blocks > PCCL_K_MAX_BLOCKS) max_blocks = PCCL_K_MAX_BLOCKS;
-    const uint64_t chunk_tiles = (tiles + p.world - 1) / p.world;
-    const int grid = static_cast<int>(std::max<uint64_t>(1, std::min<uint64_t>(max_blocks, chunk_tiles)));
+    return static_cast<int>(std::max<uint64_t>(1, std::min<uint64_t>(max_blocks, chunk_tiles)));
+}
+} // namespace
+
+extern "C" int pcclKernelAllReduceNvls(const pcclKernelNvlsArgs_t *args, void *stream_v) {
+    if (!args) return cudaErrorInvalidValue;
+    const pcclKernelP2PArgs_t &p = args->p2p;
+    DevArgs d{};
+    if (!fill_nvls_args(args, p.dtype, p.op, d)) return cudaErrorInvalidValue;
+    const size_t esz = p.dtype == pcclFloat ? 4 : 2;
+    const uint64_t n_pack = (p.count * esz + 15) / 16;
+    const uint64_t tiles = (n_pack + kNvlsThreads - 1) / kNvlsThreads;
+    const int grid = grid_for(p, (tiles + p.world - 1) / p.world);
     const auto stream = static_cast<cudaStream_t>(stream_v);
     const int op = p.op == pcclMax ? OP_MAX : (p.op == pcclMin ? OP_MIN : OP_SUM);
-    // p.algorithm selects a tuning variant: 0/1 = 4 packets per batch, 2 = 8 packets, 3 = 4 pipelined, 4 = 8 pipelined
+    // p.algorithm selects a tuning variant: packets kept in flight per thread (default 4; 2 -> 8; 5 -> 16)
     auto launch = [&](auto type_tag, auto op_tag) {
         constexpr int TYPE = decltype(type_tag)::value;
         constexpr int OPV = decltype(op_tag)::value;
         switch (p.algorithm) {
-        case 2: allreduce_nvls_kernel<TYPE, OPV, 8, false><<<grid, kNvlsThreads, 0, stream>>>(d); break;
-        case 3: allreduce_nvls_kernel<TYPE, OPV, 4, true><<<grid, kNvlsThreads, 0, stream>>>(d); break;
-        case 4: allreduce_nvls_kernel<TYPE, OPV, 8, true><<<grid, kNvlsThreads, 0, stream>>>(d); break;
-        default: allreduce_nvls_kernel<TYPE, OPV, 4, false><<<grid, kNvlsThreads, 0, stream>>>(d); break;
+        case 2: run_rank<NvlsAllReduce<TYPE, OPV, 8>><<<grid, kNvlsThreads, 0, stream>>>(d); break;
+        case 5: run_rank<NvlsAllReduce<TYPE, OPV, 16>><<<grid, kNvlsThreads, 0, stream>>>(d); break;
+        default: run_rank<NvlsAllReduce<TYPE, OPV, 4>><<<grid, kNvlsThreads, 0, stream>>>(d); break;
         }
     };
     using std::integral_constant;
@@ -539,40 +505,17 @@ extern "C" int pcclKernelAllReduceNvls(const pcclKernelNvlsArgs_t *args, void *s
 }
 
 extern "C" int pcclKernelOuterStepNvls(const pcclKernelNvlsArgs_t *args, const pcclKernelOuterStep_t *step, void *stream_v) {
-    if (!args || !args->mc_arena || !step || !step->params || !step->inner_in || !step->momentum) return cudaErrorInvalidValue;
+    if (!args || !step || !step->params || !step->inner_in || !step->momentum) return cudaErrorInvalidValue;
     const pcclKernelP2PArgs_t &p = args->p2p;
-    if (p.world < 2 || p.world > PCCL_K_MAX_RANKS || p.rank >= p.world || p.count == 0) return cudaErrorInvalidValue;
-    if ((p.count * 4 + 15) / 16 * 16 + 256 > p.data_capacity || p.data_offset % 16 != 0) return cudaErrorInvalidValue;
-    NvlsArgs d{};
-    for (uint32_t r = 0; r < p.world; ++r) d.arena[r] = static_cast<uint8_t *>(p.arena[r]);
-    d.mc = static_cast<uint8_t *>(args->mc_arena);
-    d.rank = p.rank;
-    d.world = p.world;
-    d.flag_slot = p.flag_slot;
-    d.flag_base = p.flag_base;
-    d.data_offset = p.data_offset;
-    d.count = p.count;
-    d.avg_divisor = p.world;
-    d.abort_flag = p.abort_flag;
-    d.status = p.status;
-    d.timeout_cycles = p.timeout_cycles ? p.timeout_cycles : ~0ull;
-    OuterStepDev s{};
-    s.inner_in = step->inner_in;
-    s.params = step->params;
-    s.momentum = step->momentum;
-    s.inner_out = step->inner_out;
-    s.lr = step->lr;
-    s.mu = step->mu;
-    s.first = step->first;
-    s.aligned = ((reinterpret_cast<uintptr_t>(s.inner_in) | reinterpret_cast<uintptr_t>(s.params) | reinterpret_cast<uintptr_t>(s.momentum) |
-                  reinterpret_cast<uintptr_t>(s.inner_out)) & 15) == 0;
+    DevArgs d{};
+    if (!fill_nvls_args(args, pcclFloat, pcclAvg, d)) return cudaErrorInvalidValue;
+    d.red_offset = d.data_offset;
+    d.src_in_arena = d.dst_in_arena = 0;
+    const OuterStepDev s = make_outer_step_dev(*step);
     const uint64_t n_pack = (p.count + 3) / 4;
     const uint64_t tiles = (n_pack + kNvlsThreads - 1) / kNvlsThreads;
-    int max_blocks = p.max_blocks > 0 ? p.max_blocks : 144;
-    if (max_blocks > PCCL_K_MAX_BLOCKS) max_blocks = PCCL_K_MAX_BLOCKS;
-    const uint64_t chunk_tiles = (tiles + p.world - 1) / p.world;
-    const int grid = static_cast<int>(std::max<uint64_t>(1, std::min<uint64_t>(max_blocks, chunk_tiles)));
-    outer_step_nvls_kernel<<<grid, kNvlsThreads, 0, static_cast<cudaStream_t>(stream_v)>>>(d, s);
+    const int grid = grid_for(p, (tiles + p.world - 1) / p.world);
+    run_rank<NvlsOuter, OuterStepDev><<<grid, kNvlsThreads, 0, static_cast<cudaStream_t>(stream_v)>>>(d, s);
     return cudaGetLastError();
 }
 
@@ -592,65 +535,41 @@ static void pipeline_geometry(uint64_t n_pack, uint32_t world, int requested, ui
 
 extern "C" int pcclKernelAllReduceNvlsPipelined(const pcclKernelNvlsArgs_t *args, const pcclKernelOuterStep_t *step, int segments,
                                                 void *stream_v) {
-    if (!args || !args->mc_arena) return cudaErrorInvalidValue;
+    if (!args) return cudaErrorInvalidValue;
     const pcclKernelP2PArgs_t &p = args->p2p;
-    if (p.world < 2 || p.world > PCCL_K_MAX_RANKS || p.rank >= p.world || p.count == 0) return cudaErrorInvalidValue;
     const int dtype = step ? static_cast<int>(pcclFloat) : p.dtype;
     const int rop = step ? static_cast<int>(pcclAvg) : p.op;
-    if (!pcclKernelNvlsSupported(dtype, rop)) return cudaErrorInvalidValue;
     if (step && (!step->params || !step->inner_in || !step->momentum)) return cudaErrorInvalidValue;
-    NvlsArgs d{};
-    for (uint32_t r = 0; r < p.world; ++r) d.arena[r] = static_cast<uint8_t *>(p.arena[r]);
-    d.mc = static_cast<uint8_t *>(args->mc_arena);
-    d.rank = p.rank;
-    d.world = p.world;
-    d.flag_slot = p.flag_slot;
-    d.flag_base = p.flag_base;
-    d.data_offset = p.data_offset;
-    d.src = p.src;
-    d.dst = p.dst;
-    d.count = p.count;
-    d.avg_divisor = rop == pcclAvg ? p.world : 0;
-    d.abort_flag = p.abort_flag;
-    d.status = p.status;
-    d.timeout_cycles = p.timeout_cycles ? p.timeout_cycles : ~0ull;
+    DevArgs d{};
+    if (!fill_nvls_args(args, dtype, rop, d)) return cudaErrorInvalidValue;
+    d.red_offset = d.data_offset; // staged: the segments are reduced in place in the arena
+    d.src_in_arena = d.dst_in_arena = 0;
     const size_t esz = dtype == pcclFloat ? 4 : 2;
-    if ((p.count * esz + 15) / 16 * 16 + 256 > p.data_capacity || p.data_offset % 16 != 0) return cudaErrorInvalidValue;
     OuterStepDev s{};
-    if (step) {
-        s.inner_in = step->inner_in;
-        s.params = step->params;
-        s.momentum = step->momentum;
-        s.inner_out = step->inner_out;
-        s.lr = step->lr;
-        s.mu = step->mu;
-        s.first = step->first;
-        s.aligned = ((reinterpret_cast<uintptr_t>(s.inner_in) | reinterpret_cast<uintptr_t>(s.params) | reinterpret_cast<uintptr_t>(s.momentum) |
-                      reinterpret_cast<uintptr_t>(s.inner_out)) & 15) == 0;
-    }
+    if (step) s = make_outer_step_dev(*step);
     const uint64_t n_pack = (p.count * esz + 15) / 16;
-    uint32_t n_seg = 0;
-    uint64_t seg_pack = 0;
-    pipeline_geometry(n_pack, p.world, segments, n_seg, seg_pack);
-    int max_blocks = p.max_blocks > 0 ? p.max_blocks : 144;
-    if (max_blocks > PCCL_K_MAX_BLOCKS) max_blocks = PCCL_K_MAX_BLOCKS;
+    PipelineGeometry geo{};
+    pipeline_geometry(n_pack, p.world, segments, geo.n_seg, geo.seg_pack);
     // the network group's share of one segment decides how many blocks have work in every iteration
-    const uint64_t chunk_tiles = std::max<uint64_t>(1, seg_pack / p.world / kNvlsThreads);
-    const int grid = static_cast<int>(std::max<uint64_t>(1, std::min<uint64_t>(max_blocks, chunk_tiles)));
+    const int grid = grid_for(p, std::max<uint64_t>(1, geo.seg_pack / p.world / kNvlsThreads));
     const auto stream = static_cast<cudaStream_t>(stream_v);
     const int op = rop == pcclMax ? OP_MAX : (rop == pcclMin ? OP_MIN : OP_SUM);
+    auto go = [&](auto body) {
+        using Body = decltype(body);
+        run_rank<Body, OuterStepDev, PipelineGeometry><<<grid, kNvlsThreads, 0, stream>>>(d, s, geo);
+    };
     if (step) {
-        allreduce_nvls_pipelined_kernel<NV_F32, OP_SUM, true><<<grid, kNvlsThreads, 0, stream>>>(d, s, n_seg, seg_pack);
+        go(NvlsPipelined<NV_F32, OP_SUM, true>{});
     } else if (dtype == pcclFloat) {
-        allreduce_nvls_pipelined_kernel<NV_F32, OP_SUM, false><<<grid, kNvlsThreads, 0, stream>>>(d, s, n_seg, seg_pack);
+        go(NvlsPipelined<NV_F32, OP_SUM, false>{});
     } else if (dtype == pcclBFloat16) {
-        if (op == OP_SUM) allreduce_nvls_pipelined_kernel<NV_BF16, OP_SUM, false><<<grid, kNvlsThreads, 0, stream>>>(d, s, n_seg, seg_pack);
-        else if (op == OP_MAX) allreduce_nvls_pipelined_kernel<NV_BF16, OP_MAX, false><<<grid, kNvlsThreads, 0, stream>>>(d, s, n_seg, seg_pack);
-        else allreduce_nvls_pipelined_kernel<NV_BF16, OP_MIN, false><<<grid, kNvlsThreads, 0, stream>>>(d, s, n_seg, seg_pack);
+        if (op == OP_SUM) go(NvlsPipelined<NV_BF16, OP_SUM, false>{});
+        else if (op == OP_MAX) go(NvlsPipelined<NV_BF16, OP_MAX, false>{});
+        else go(NvlsPipelined<NV_BF16, OP_MIN, false>{});
     } else {
-        if (op == OP_SUM) allreduce_nvls_pipelined_kernel<NV_F16, OP_SUM, false><<<grid, kNvlsThreads, 0, stream>>>(d, s, n_seg, seg_pack);
-        else if (op == OP_MAX) allreduce_nvls_pipelined_kernel<NV_F16, OP_MAX, false><<<grid, kNvlsThreads, 0, stream>>>(d, s, n_seg, seg_pack);
-        else allreduce_nvls_pipelined_kernel<NV_F16, OP_MIN, false><<<grid, kNvlsThreads, 0, stream>>>(d, s, n_seg, seg_pack);
+        if (op == OP_SUM) go(NvlsPipelined<NV_F16, OP_SUM, false>{});
+        else if (op == OP_MAX) go(NvlsPipelined<NV_F16, OP_MAX, false>{});
+        else go(NvlsPipelined<NV_F16, OP_MIN, false>{});
     }
     return cudaGetLastError();
 }

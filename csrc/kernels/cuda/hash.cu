@@ -19,12 +19,15 @@
 
 #include "../crc_gf.hpp"
 #include "common.cuh"
+#include "hash_mset.cuh"
 #include "pccl_kernels.h"
 
 namespace pccl::cuda {
 
 constexpr uint32_t kHashThreads = 256;
 constexpr uint32_t kHashMaxBlocks = 960;
+// largest input with a defined hash: the packet count must fit 32 bits (2^32 - 1 packets, then up to 15 tail bytes)
+constexpr uint64_t kSimpleHashMaxBytes = ((uint64_t(1) << 32) - 1) * 16 + 15;
 constexpr size_t kSimpleScratchBytes = 4096; // 960 partials + ticket
 constexpr uint32_t kCrcWarpsPerBlock = 8;
 constexpr uint32_t kCrcMaxBlocks = 1184; // 8 per SM on 148 SMs
@@ -72,12 +75,13 @@ __global__ void __launch_bounds__(kHashThreads) simplehash_kernel(const uint8_t 
 
     if (total_vec > 0) {
         const uint4 *d4 = reinterpret_cast<const uint4 *>(data);
-        const uint32_t per_block = (total_vec + gridDim.x - 1) / gridDim.x;
-        const uint32_t begin = blockIdx.x * per_block;
-        uint32_t end = begin + per_block;
-        if (end > total_vec || end < begin) end = total_vec;
+        // slab bounds and the running index are 64-bit: with up to 2^32 - 1 packets, `total_vec + gridDim.x - 1` and
+        // `i + 8 * kHashThreads` would wrap in 32 bits near the top of the range (the values themselves are unchanged)
+        const uint64_t per_block = (uint64_t(total_vec) + gridDim.x - 1) / gridDim.x;
+        const uint64_t begin = min(uint64_t(blockIdx.x) * per_block, uint64_t(total_vec));
+        const uint64_t end = min(begin + per_block, uint64_t(total_vec));
         uint32_t h = 0;
-        uint32_t i = begin + threadIdx.x;
+        uint64_t i = begin + threadIdx.x;
         // eight independent loads in flight, then the serial chain
         for (; i < end && end - i > 7 * kHashThreads; i += 8 * kHashThreads) {
             uint4 v[8];
@@ -122,6 +126,35 @@ __global__ void __launch_bounds__(kHashThreads) simplehash_kernel(const uint8_t 
         *out = result;
         *ticket = 0; // leave the scratch ready for the next call
     }
+}
+
+// ------------------------------------------------------------------------------------------ mset64
+// Stand-alone pass for the order-independent hash (csrc/kernels/mset_formula.hpp): used for the first hash of a tensor;
+// afterwards the collective kernels keep the digest up to date as a by-product of writing the tensor.
+__global__ void __launch_bounds__(512) mset64_kernel(const uint8_t *__restrict__ data, size_t n_bytes, unsigned long long *out) {
+    const uint64_t n_pack = (n_bytes + 15) / 16, full = n_bytes / 16;
+    const uint4 *d4 = reinterpret_cast<const uint4 *>(data);
+    MsetAcc acc;
+    const uint64_t stride = uint64_t(gridDim.x) * blockDim.x;
+    uint64_t i = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x;
+    for (; i + 3 * stride < full; i += 4 * stride) { // four independent loads in flight
+        uint4 v[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) v[k] = ld_stream_16(d4 + i + k * stride);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) acc.sum += mset::term(i + k * stride, v[k].x, v[k].y, v[k].z, v[k].w);
+    }
+    for (; i < n_pack; i += stride) {
+        if (i < full) {
+            const uint4 v = ld_stream_16(d4 + i);
+            acc.sum += mset::term(i, v.x, v.y, v.z, v.w);
+        } else { // the partial last packet, byte by byte
+            uint32_t w[4] = {0, 0, 0, 0};
+            for (uint64_t b = i * 16; b < n_bytes; ++b) w[(b - i * 16) / 4] |= static_cast<uint32_t>(data[b]) << (8 * ((b - i * 16) % 4));
+            acc.sum += mset::term(i, w[0], w[1], w[2], w[3]);
+        }
+    }
+    acc.flush(out);
 }
 
 // ------------------------------------------------------------------------------------------ CRC32C
@@ -276,6 +309,8 @@ extern "C" int pcclKernelSimpleHash(const void *data, size_t n_bytes, void *scra
     if (!scratch || !out_device) return cudaErrorInvalidValue;
     if (n_bytes == 0) return cudaMemsetAsync(out_device, 0, sizeof(uint64_t), static_cast<cudaStream_t>(stream));
     if (reinterpret_cast<uintptr_t>(data) % 16 != 0) return cudaErrorMisalignedAddress;
+    // the hash counts 16-byte packets in 32 bits (so does the reference kernel): larger inputs have no defined value
+    if (static_cast<uint64_t>(n_bytes) > kSimpleHashMaxBytes) return cudaErrorInvalidValue;
     const size_t n_vec = n_bytes / 16;
     uint32_t grid = static_cast<uint32_t>(std::min<size_t>((n_vec + kHashThreads - 1) / kHashThreads, kHashMaxBlocks));
     if (grid == 0) grid = 1;
@@ -283,6 +318,20 @@ extern "C" int pcclKernelSimpleHash(const void *data, size_t n_bytes, void *scra
                                                                                    static_cast<uint32_t *>(scratch), out_device);
     return cudaGetLastError();
 }
+
+extern "C" int pcclKernelMset64Raw(const void *data, size_t n_bytes, uint64_t *out_device, void *stream_v) {
+    if (!out_device || (!data && n_bytes > 0)) return cudaErrorInvalidValue;
+    const auto stream = static_cast<cudaStream_t>(stream_v);
+    cudaError_t rc = cudaMemsetAsync(out_device, 0, sizeof(uint64_t), stream);
+    if (rc != cudaSuccess || n_bytes == 0) return rc;
+    if (reinterpret_cast<uintptr_t>(data) % 16 != 0) return cudaErrorMisalignedAddress;
+    const uint64_t n_pack = (n_bytes + 15) / 16;
+    const int grid = static_cast<int>(std::min<uint64_t>(148 * 4, (n_pack + 2047) / 2048));
+    mset64_kernel<<<std::max(1, grid), 512, 0, stream>>>(static_cast<const uint8_t *>(data), n_bytes, reinterpret_cast<unsigned long long *>(out_device));
+    return cudaGetLastError();
+}
+
+extern "C" uint64_t pcclExtMsetFinalize(uint64_t raw_sum, uint64_t n_bytes) { return pccl::mset::finalize(raw_sum, n_bytes); }
 
 extern "C" int pcclKernelCrc32c(const void *data, size_t n_bytes, void *scratch, uint64_t *out_device, void *stream) {
     if (!scratch || !out_device) return cudaErrorInvalidValue;
@@ -304,6 +353,8 @@ struct HashContext {
     void *scratch = nullptr;
     uint64_t *out = nullptr;
     cudaStream_t stream = nullptr;
+    cudaEvent_t ready = nullptr; // orders the hash after work queued on the legacy default stream
+    uint64_t *host_out = nullptr; // pinned landing place of the result
 };
 HashContext *hash_context(int &rc) {
     static std::mutex mu;
@@ -321,6 +372,8 @@ HashContext *hash_context(int &rc) {
         if ((rc = cudaMemset(c.scratch, 0, kScratchBytes)) != cudaSuccess) return nullptr;
         if ((rc = cudaMalloc(&c.out, sizeof(uint64_t))) != cudaSuccess) return nullptr;
         if ((rc = cudaStreamCreateWithFlags(&c.stream, cudaStreamNonBlocking)) != cudaSuccess) return nullptr;
+        if ((rc = cudaEventCreateWithFlags(&c.ready, cudaEventDisableTiming)) != cudaSuccess) return nullptr;
+        if ((rc = cudaHostAlloc(reinterpret_cast<void **>(&c.host_out), sizeof(uint64_t), cudaHostAllocDefault)) != cudaSuccess) return nullptr;
     }
     return &c;
 }
@@ -334,18 +387,15 @@ extern "C" int pcclKernelHashSync(const void *data, size_t n_bytes, int hash_typ
     if (!c) return rc;
     std::lock_guard<std::mutex> lock(g_hash_call_mu);
     // the data may have been produced on the legacy default stream
-    cudaEvent_t ready;
-    if ((rc = cudaEventCreateWithFlags(&ready, cudaEventDisableTiming)) != cudaSuccess) return rc;
-    cudaEventRecord(ready, cudaStreamLegacy);
-    cudaStreamWaitEvent(c->stream, ready, 0);
-    cudaEventDestroy(ready);
-    rc = hash_type == 0 ? pcclKernelSimpleHash(data, n_bytes, c->scratch, c->out, c->stream)
-                        : pcclKernelCrc32c(data, n_bytes, c->scratch, c->out, c->stream);
+    cudaEventRecord(c->ready, cudaStreamLegacy);
+    cudaStreamWaitEvent(c->stream, c->ready, 0);
+    rc = hash_type == 0   ? pcclKernelSimpleHash(data, n_bytes, c->scratch, c->out, c->stream)
+         : hash_type == 1 ? pcclKernelCrc32c(data, n_bytes, c->scratch, c->out, c->stream)
+                          : pcclKernelMset64Raw(data, n_bytes, c->out, c->stream);
     if (rc != cudaSuccess) return rc;
-    uint64_t host = 0;
-    if ((rc = cudaMemcpyAsync(&host, c->out, sizeof host, cudaMemcpyDeviceToHost, c->stream)) != cudaSuccess) return rc;
+    if ((rc = cudaMemcpyAsync(c->host_out, c->out, sizeof(uint64_t), cudaMemcpyDeviceToHost, c->stream)) != cudaSuccess) return rc;
     if ((rc = cudaStreamSynchronize(c->stream)) != cudaSuccess) return rc;
-    *out_host = host;
+    *out_host = hash_type == 2 ? pccl::mset::finalize(*c->host_out, n_bytes) : *c->host_out;
     return 0;
 }
 
@@ -378,7 +428,7 @@ extern "C" int pcclKernelHashSync(const void *data, size_t n_bytes, int hash_typ
 namespace pccl::cuda {
 
 constexpr size_t kNoAllocScratchBytes = 4096; // 960 partials + ticket, rounded up
-constexpr uint64_t kNoAllocMaxBytes = (uint64_t(1) << 32) * 16 - 16;
+constexpr uint64_t kNoAllocMaxBytes = kSimpleHashMaxBytes; // 2^32 - 1 packets plus a tail of up to 15 bytes
 static_assert((kHashMaxBlocks + 1) * sizeof(uint32_t) <= kNoAllocScratchBytes, "static scratch too small");
 
 static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocScratchBytes];

@@ -7,6 +7,8 @@
 // (python/examples/nanogpt_diloco/sync_diloco.py:480-530).
 #pragma once
 #include "common.cuh"
+#include "hash_mset.cuh"
+#include "pccl_kernels.h"
 
 namespace pccl::cuda {
 
@@ -19,6 +21,20 @@ struct OuterStepDev {
     int first; // momentum buffer holds nothing yet
     int aligned; // all four pointers are 16-byte aligned
 };
+
+inline OuterStepDev make_outer_step_dev(const pcclKernelOuterStep_t &step) {
+    OuterStepDev s{};
+    s.inner_in = step.inner_in;
+    s.params = step.params;
+    s.momentum = step.momentum;
+    s.inner_out = step.inner_out;
+    s.lr = step.lr;
+    s.mu = step.mu;
+    s.first = step.first;
+    s.aligned = ((reinterpret_cast<uintptr_t>(s.inner_in) | reinterpret_cast<uintptr_t>(s.params) | reinterpret_cast<uintptr_t>(s.momentum) |
+                  reinterpret_cast<uintptr_t>(s.inner_out)) & 15) == 0;
+    return s;
+}
 
 __device__ __forceinline__ uint4 outer_delta_packet(const OuterStepDev &s, uint64_t v, uint64_t count) {
     const uint64_t e = v * 4;
@@ -56,7 +72,10 @@ __device__ __forceinline__ OuterLoaded outer_load_packet(const OuterStepDev &s, 
     return l;
 }
 
-__device__ __forceinline__ void outer_apply_packet(const OuterStepDev &s, uint64_t v, uint64_t count, uint4 g, const OuterLoaded &l) {
+// dig_p / dig_m (optional): mset64 accumulators of the new parameters and of the new momentum buffer, so that the content
+// hashes the next shared-state synchronisation needs are a by-product of this pass
+__device__ __forceinline__ void outer_apply_packet(const OuterStepDev &s, uint64_t v, uint64_t count, uint4 g, const OuterLoaded &l,
+                                                   MsetAcc *dig_p = nullptr, MsetAcc *dig_m = nullptr) {
     const uint64_t e = v * 4;
     if (s.aligned && e + 4 <= count) {
         float p[4], m[4];
@@ -65,12 +84,16 @@ __device__ __forceinline__ void outer_apply_packet(const OuterStepDev &s, uint64
         outer_update_one(s, __uint_as_float(g.z), __uint_as_float(l.p.z), __uint_as_float(l.m.z), p[2], m[2]);
         outer_update_one(s, __uint_as_float(g.w), __uint_as_float(l.p.w), __uint_as_float(l.m.w), p[3], m[3]);
         const uint4 pv = make_uint4(__float_as_uint(p[0]), __float_as_uint(p[1]), __float_as_uint(p[2]), __float_as_uint(p[3]));
-        st_stream_16(s.momentum + e, make_uint4(__float_as_uint(m[0]), __float_as_uint(m[1]), __float_as_uint(m[2]), __float_as_uint(m[3])));
+        const uint4 mv = make_uint4(__float_as_uint(m[0]), __float_as_uint(m[1]), __float_as_uint(m[2]), __float_as_uint(m[3]));
+        st_stream_16(s.momentum + e, mv);
         st_stream_16(s.params + e, pv);
         if (s.inner_out) st_stream_16(s.inner_out + e, pv);
+        if (dig_p) dig_p->add(v, pv, count * 4);
+        if (dig_m) dig_m->add(v, mv, count * 4);
         return;
     }
     const uint32_t gw[4] = {g.x, g.y, g.z, g.w};
+    uint32_t pw[4] = {0, 0, 0, 0}, mw[4] = {0, 0, 0, 0};
 #pragma unroll
     for (int i = 0; i < 4; ++i) {
         if (e + i >= count) break;
@@ -79,7 +102,11 @@ __device__ __forceinline__ void outer_apply_packet(const OuterStepDev &s, uint64
         s.momentum[e + i] = m;
         s.params[e + i] = p;
         if (s.inner_out) s.inner_out[e + i] = p;
+        pw[i] = __float_as_uint(p);
+        mw[i] = __float_as_uint(m);
     }
+    if (dig_p) dig_p->add(v, make_uint4(pw[0], pw[1], pw[2], pw[3]), count * 4);
+    if (dig_m) dig_m->add(v, make_uint4(mw[0], mw[1], mw[2], mw[3]), count * 4);
 }
 
 } // namespace pccl::cuda

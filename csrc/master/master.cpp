@@ -243,6 +243,8 @@ void Master::eval_establish_votes() {
 
 void Master::begin_establishment(bool accept_new_peers) {
     peer_dropped_ = false; // a fresh establishment round starts
+    // leases belong to a ring: every peer drops its lease state when the round ends (Client::establish_round)
+    for (auto &[id, g] : groups_) g.leased_tags.clear();
     for (auto &[u, c] : clients_)
         if (accept_new_peers || c.phase == Phase::Accepted) c.state = State::ConnectingToPeers;
     for (Client *c : ordered_clients())
@@ -770,14 +772,19 @@ void Master::handle_collective_initiate(Client &c, const C2MCollectiveInitiate &
         // same tag right away; the vote takes effect when the current one is finished
         if (it->second != CollectiveState::VoteComplete || c.queued_initiate.count(p.tag))
             return kick(c.link, "collective tag already in flight");
-        c.queued_initiate[p.tag] = static_cast<uint8_t>(p.op) & 0xc0u;
+        c.queued_initiate[p.tag] = static_cast<uint8_t>(p.op) & 0xf0u;
         return;
     }
+    // A vote for a tag the group runs under a lease: this peer cannot (or will not) take the lease path for this
+    // operation.  The lease of that tag ends for everybody; whoever already started the operation without a vote
+    // gives up and votes as well.
+    if (groups_[c.group].leased_tags.count(p.tag)) revoke_lease(c.group, p.tag, false, false);
     c.state = State::CollectiveCommunicationsRunning;
     c.collectives[p.tag] = CollectiveState::VoteInitiate;
     // extension: top bit of the operator byte = "I can run this one on the device plane"
-    // bit 6: "... and over NVSwitch multicast"
-    c.device_capable[p.tag] = static_cast<uint8_t>(p.op) & 0xc0u;
+    // bit 6: "... and over NVSwitch multicast", bit 5: "I would run later operations on this tag under a lease",
+    // bit 4: "the multicast view of the ring exists here" (independent of this operation)
+    c.device_capable[p.tag] = static_cast<uint8_t>(p.op) & 0xf0u;
     eval_collective_initiate(c.group, p.tag);
 }
 
@@ -792,7 +799,7 @@ void Master::eval_collective_initiate(uint32_t group, uint64_t tag) {
     if (voting == 0 || voting != accepted) return;
     uint64_t seq = next_seq_nr_++;
     // the device plane is used only if every single peer of the group offered it
-    uint8_t common = 0xc0u;
+    uint8_t common = 0xf0u;
     for (auto &[u, c] : clients_) {
         if (c.group != group || c.phase != Phase::Accepted) continue;
         const auto it = c.device_capable.find(tag);
@@ -801,6 +808,14 @@ void Master::eval_collective_initiate(uint32_t group, uint64_t tag) {
     }
     if (common & 0x80u) seq |= 1ull << 63;
     if ((common & 0xc0u) == 0xc0u) seq |= 1ull << 62;
+    // Lease: every peer ran this operation on the device plane and offers to run the following operations on this
+    // tag without voting.  From the next operation on, the group orders its collectives on this tag among itself
+    // (same-box sequencer) and the master only hears of them when something goes wrong.
+    if ((common & 0xa0u) == 0xa0u && accepted >= 2) {
+        seq |= 1ull << 61;
+        if (common & 0x10u) seq |= 1ull << 60;
+        groups_[group].leased_tags.insert(tag);
+    }
     for (Client *c : ordered_clients()) {
         if (c->group != group || c->phase != Phase::Accepted) continue;
         c->collectives[tag] = CollectiveState::Perform;
@@ -809,6 +824,21 @@ void Master::eval_collective_initiate(uint32_t group, uint64_t tag) {
         out.seq_nr = seq;
         send(*c, out);
     }
+}
+
+void Master::revoke_lease(uint32_t group, uint64_t tag, bool all, bool peer_lost) {
+    Group &g = groups_[group];
+    if (all ? g.leased_tags.empty() : !g.leased_tags.count(tag)) return;
+    if (all)
+        g.leased_tags.clear();
+    else
+        g.leased_tags.erase(tag);
+    M2CLeaseRevoked out;
+    out.tag = tag;
+    out.all = all;
+    out.peer_lost = peer_lost;
+    for (Client *c : ordered_clients())
+        if (c->group == group && c->phase == Phase::Accepted) send(*c, out);
 }
 
 bool Master::mark_aborted(uint32_t group, uint64_t tag) {
@@ -894,6 +924,7 @@ void Master::on_disconnect(const ccoip_socket_address_t &from) {
 
     Group &g = groups_[group];
     if (was_accepted) g.bandwidth.unregister_peer(uuid);
+    if (was_accepted) revoke_lease(group, 0, true, true); // peers may be inside a leased operation waiting for the one that left
     g.sync_votes.erase(std::remove_if(g.sync_votes.begin(), g.sync_votes.end(),
                                       [&](const SyncVote &v) { return v.uuid == uuid; }),
                        g.sync_votes.end());

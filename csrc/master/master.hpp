@@ -100,6 +100,8 @@ private:
         std::unordered_set<Uuid> sync_complete_votes;
         // collectives
         std::unordered_map<uint64_t, bool> aborted;
+        // tags whose collectives the group currently runs under a lease (no votes), see eval_collective_initiate
+        std::set<uint64_t> leased_tags;
         // topology
         topo::BandwidthStore bandwidth;
         std::vector<Uuid> ring;
@@ -139,6 +141,7 @@ private:
     void eval_collective_complete(uint32_t group, uint64_t tag);
     void broadcast_abort(uint32_t group, uint64_t tag, bool aborted);
     bool mark_aborted(uint32_t group, uint64_t tag);
+    void revoke_lease(uint32_t group, uint64_t tag, bool all, bool peer_lost);
 
     // ---- helpers
     Client *find(const ccoip_socket_address_t &addr);

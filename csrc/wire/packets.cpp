@@ -318,6 +318,18 @@ bool M2CCollectiveAbort::read(Reader &r) {
     return r.ok();
 }
 
+void M2CLeaseRevoked::write(Writer &w) const {
+    w.put<uint64_t>(tag);
+    w.put<bool>(all);
+    w.put<bool>(peer_lost);
+}
+bool M2CLeaseRevoked::read(Reader &r) {
+    tag = r.get<uint64_t>();
+    all = r.get<bool>();
+    peer_lost = r.get<bool>();
+    return r.ok();
+}
+
 // ---- P2P
 void P2PHello::write(Writer &w) const {
     put_uuid(w, uuid);

@@ -21,7 +21,7 @@ using PacketId = uint16_t;
 // from pcclDataType_t numbering.
 enum class DType : uint8_t { U8 = 0, I8 = 1, U16 = 2, U32 = 3, I16 = 4, I32 = 5, U64 = 6, I64 = 7, F16 = 8, BF16 = 9, F32 = 10, F64 = 11, F8E4M3 = 12 };
 enum class RedOp : uint8_t { Set = 0, Sum = 1, Avg = 2, Prod = 3, Max = 4, Min = 5 };
-enum class HashType : uint8_t { Simple = 0, Crc32 = 1 };
+enum class HashType : uint8_t { Simple = 0, Crc32 = 1, Mset64 = 2 }; // 2: extension, see kernels/mset_formula.hpp
 enum class SyncStrategy : uint8_t { EnforcePopular = 0, RxOnly = 1, TxOnly = 2 };
 enum class QuantAlgo : uint8_t { None = 0, MinMax = 1, ZeroPointScale = 2, BlockMinMax = 3, BlockFp8 = 4 };
 
@@ -170,6 +170,15 @@ struct M2CCollectiveAbort {
     PCCL_PACKET(11)
     uint64_t tag = 0;
     bool aborted = false;
+};
+// Extension (never sent to a group that contains a peer without lease support, so reference peers do not see it): the
+// lease under which a group ran the collectives of `tag` (or of every tag, `all`) without voting has ended.  `peer_lost`:
+// because a member of the group is gone -- the ring must be re-established before the next operation.
+struct M2CLeaseRevoked {
+    PCCL_PACKET(12)
+    uint64_t tag = 0;
+    bool all = false;
+    bool peer_lost = false;
 };
 
 // ---------------------------------------------------------------- peer <-> peer

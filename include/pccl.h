@@ -334,6 +334,7 @@ typedef struct pcclExtReduceStats_t {
     float device_ms;     /* CUDA-event time of the device part, 0 for host ops */
     uint64_t seq_nr;     /* master-issued sequence number of the operation */
     uint32_t kernel_launches; /* kernels of this library launched for the operation */
+    uint32_t leased;     /* 1: ran under a lease, without a vote at the master (seq_nr then counts leased operations of the tag) */
 } pcclExtReduceStats_t;
 
 /* Stats of the most recently completed reduction with the given tag. */

@@ -19,6 +19,7 @@ extern "C" {
 
 #define PCCL_K_MAX_RANKS 16      /* peers in one NVLink domain */
 #define PCCL_K_MAX_BLOCKS 256    /* thread blocks of one collective kernel */
+#define PCCL_K_FLAG_BANKS 32     /* independent barrier-flag banks in the control page (flag_slot < this) */
 #define PCCL_K_QUANT_BLOCK 128   /* elements sharing one scale in the block formats */
 
 /* ---------------------------------------------------------------------------------------------
@@ -31,9 +32,15 @@ PCCL_EXPORT size_t pcclKernelHashScratchBytes(void);
 PCCL_EXPORT int pcclKernelSimpleHash(const void *data, size_t n_bytes, void *scratch, uint64_t *out_device, void *stream);
 PCCL_EXPORT int pcclKernelCrc32c(const void *data, size_t n_bytes, void *scratch, uint64_t *out_device, void *stream);
 
+/* mset64, the order-independent hash type (no counterpart in the reference; definition in csrc/kernels/mset_formula.hpp):
+ * writes the RAW sum to *out_device; pcclExtMsetFinalize(raw, n_bytes) turns a raw sum into the hash value.  The collective
+ * kernels produce the same raw sums as a by-product (hash_out of pcclKernelP2PArgs_t). */
+PCCL_EXPORT int pcclKernelMset64Raw(const void *data, size_t n_bytes, uint64_t *out_device, void *stream);
+PCCL_EXPORT uint64_t pcclExtMsetFinalize(uint64_t raw_sum, uint64_t n_bytes);
+
 /* Convenience: allocates nothing itself -- uses a per-device scratch the library keeps -- runs the
  * hash on an internal stream and returns the value on the host (synchronous). */
-PCCL_EXPORT int pcclKernelHashSync(const void *data, size_t n_bytes, int hash_type, uint64_t *out_host);
+PCCL_EXPORT int pcclKernelHashSync(const void *data, size_t n_bytes, int hash_type, uint64_t *out_host); /* 0 simplehash, 1 CRC32C, 2 mset64 */
 
 /* Same hash, for callers that may not allocate device memory (open stream capture, allocator that already
  * owns the whole GPU, paths that cannot afford cudaMalloc's device-wide synchronisation).  Has no
@@ -86,10 +93,23 @@ typedef struct pcclKernelP2PArgs_t {
     volatile uint32_t *abort_flag; /* host-mapped; non-zero makes the kernel give up */
     uint32_t *status;       /* host-mapped; 0 ok, 1 aborted, 2 timed out */
     uint64_t timeout_cycles;
+    /* -- optional members; zero selects the classic behaviour -- */
+    uint64_t red_offset;     /* where chunk owners leave their reduced chunks in every arena; 0 = data_offset */
+    int dst_in_arena;        /* dst IS arena[rank]+red_offset (symmetric memory): results are written once, there */
+    int no_trailing_barrier; /* one-shot only: the caller alternates between two staging areas from call to call on this
+                                flag bank, so the closing "everybody has read" barrier is not needed */
+    uint64_t *stamps;        /* host-mapped, 8 words: %globaltimer (ns) at the phase boundaries, written by block 0 */
+    uint64_t *hash_out;      /* device memory, zeroed by the caller: raw mset64 sum of the output (two-shot, NVLS; the outer
+                                step writes two words: new parameters, new momentum).  Finalise with pcclExtMsetFinalize. */
 } pcclKernelP2PArgs_t;
 
 /* Returns which algorithm ran (1 or 2) in *algorithm_out. */
 PCCL_EXPORT int pcclKernelAllReduceP2P(const pcclKernelP2PArgs_t *args, int *algorithm_out, void *stream);
+/* Single-GPU emulation for tests: ranks[0..n_ranks) are the argument blocks of n_ranks = world ranks, each with its OWN
+ * arena[] table (all arenas in this GPU's memory).  Runs them as ONE cooperative kernel with grid (blocks, n_ranks) --
+ * kernels of ranks that wait for each other must not be separate launches on one GPU.  Synchronous; blocks * n_ranks must
+ * fit the GPU (keep max_blocks small). */
+PCCL_EXPORT int pcclKernelEmulatedAllReduceP2P(const pcclKernelP2PArgs_t *ranks, int n_ranks, int *algorithm_out, void *stream);
 /* Bytes of arena staging needed for `count` elements. */
 PCCL_EXPORT size_t pcclKernelP2PStagingBytes(uint64_t count, int dtype, int quant_algorithm);
 /* Size of the control page at the start of every arena. */
@@ -141,6 +161,8 @@ PCCL_EXPORT int pcclKernelOuterNesterov(float *params, float *momentum, const fl
                                         int first, void *stream);
 PCCL_EXPORT int pcclKernelOuterStepP2P(const pcclKernelP2PArgs_t *args, const pcclKernelOuterStep_t *step, void *stream);
 PCCL_EXPORT int pcclKernelOuterStepNvls(const pcclKernelNvlsArgs_t *args, const pcclKernelOuterStep_t *step, void *stream);
+/* Single-GPU emulation of pcclKernelOuterStepP2P, see pcclKernelEmulatedAllReduceP2P. */
+PCCL_EXPORT int pcclKernelEmulatedOuterStepP2P(const pcclKernelP2PArgs_t *ranks, const pcclKernelOuterStep_t *steps, int n_ranks, void *stream);
 
 #ifdef __cplusplus
 }

@@ -115,7 +115,8 @@ class BuildInfoC(C.Structure):
 
 
 class ExtReduceStatsC(C.Structure):
-    _fields_ = [("plane", C.c_int), ("device_ms", C.c_float), ("seq_nr", C.c_uint64), ("kernel_launches", C.c_uint32)]
+    _fields_ = [("plane", C.c_int), ("device_ms", C.c_float), ("seq_nr", C.c_uint64), ("kernel_launches", C.c_uint32),
+                ("leased", C.c_uint32)]
 
 
 class ExtOuterStepDescriptorC(C.Structure):
@@ -152,6 +153,11 @@ class KernelP2PArgs(C.Structure):
         ("abort_flag", C.c_void_p),
         ("status", C.c_void_p),
         ("timeout_cycles", C.c_uint64),
+        ("red_offset", C.c_uint64),
+        ("dst_in_arena", C.c_int),
+        ("no_trailing_barrier", C.c_int),
+        ("stamps", C.c_void_p),
+        ("hash_out", C.c_void_p),
     ]
 
 

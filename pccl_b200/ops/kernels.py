@@ -179,3 +179,115 @@ def local_outer_step(params: torch.Tensor, inner: torch.Tensor, momentum: torch.
     step.lr, step.mu, step.first = lr, mu, 1 if first else 0
     with torch.cuda.device(params.device):
         _check(lib().pcclKernelOuterStepP2P(C.byref(args), C.byref(step), _stream_ptr(params)), "pcclKernelOuterStepP2P")
+
+
+class EmulatedWorld:
+    """`world` ranks on ONE GPU, for tests: every rank has its own arena (control page + staging area) in this GPU's
+    memory, and a collective runs as ONE cooperative kernel whose grid is (blocks, world) -- kernels of ranks that wait
+    for each other must not be separate launches on one GPU.  The kernels are the production ones (same bodies, same
+    barriers and flags); only the launch differs.  Keep `max_blocks * world` below the SM count."""
+
+    def __init__(self, device: torch.device, world: int, staging_bytes: int):
+        assert 1 <= world <= _lib.K_MAX_RANKS
+        self.world = world
+        self.device = device
+        self.control = int(lib().pcclKernelP2PControlBytes())
+        self.capacity = (staging_bytes + 4095) // 4096 * 4096 + 4096
+        self.arenas = [torch.zeros(self.control + 2 * self.capacity, dtype=torch.uint8, device=device) for _ in range(world)]
+        self.words = [torch.zeros(64, dtype=torch.int32).pin_memory() for _ in range(world)]
+        self.epoch = 0
+
+    def symmetric_view(self, rank: int, numel: int, dtype: torch.dtype, second: bool = False) -> torch.Tensor:
+        """A tensor that lives in the rank's arena (the emulation of symmetric memory): first or second staging half."""
+        off = self.control + (self.capacity if second else 0)
+        nbytes = numel * torch.empty(0, dtype=dtype).element_size()
+        assert nbytes <= self.capacity
+        return self.arenas[rank][off:off + nbytes].view(dtype)
+
+    def _args(self, rank: int, count: int, dtype: torch.dtype, flag_slot: int):
+        a = _lib.KernelP2PArgs()
+        for i in range(self.world):
+            a.arena[i] = self.arenas[i].data_ptr()
+        a.rank, a.world = rank, self.world
+        a.flag_slot = flag_slot
+        a.flag_base = self.epoch * 1024
+        a.data_offset = self.control
+        a.data_capacity = self.capacity
+        a.count = count
+        a.abort_flag = self.words[rank].data_ptr()
+        a.status = self.words[rank].data_ptr() + 4
+        a.timeout_cycles = 6_000_000_000  # ~3 s: a kernel bug fails instead of hanging the box
+        return a
+
+    def status(self):
+        return [int(w[1]) for w in self.words]
+
+    def all_reduce(self, srcs, dsts, op: ReduceOp = ReduceOp.SUM, quant: QuantizationAlgorithm = QuantizationAlgorithm.NONE,
+                   algorithm: int = 0, max_blocks: int = 8, symmetric: str = "", no_trailing_barrier: bool = False,
+                   want_hash: bool = False, flag_slot: int = 0):
+        """symmetric: "" (ordinary buffers, staged), "in_place" (srcs[r] is symmetric_view(r) and is the output),
+        "out_of_place" (srcs[r] first half, dsts[r] second half of the arena).  Returns (algorithm, raw hash sums or None)."""
+        assert len(srcs) == len(dsts) == self.world and max_blocks * self.world <= 128
+        self.epoch += 1
+        for w in self.words:
+            w.zero_()
+        arr = (_lib.KernelP2PArgs * self.world)()
+        hashes = torch.zeros(self.world, 2, dtype=torch.int64, device=self.device) if want_hash else None
+        for r in range(self.world):
+            s, d = srcs[r], dsts[r]
+            a = self._args(r, s.numel(), s.dtype, flag_slot)
+            a.src, a.dst = s.data_ptr(), d.data_ptr()
+            a.dtype = DataType.from_torch_dtype(s.dtype).value
+            a.op = op.value
+            a.quant_algorithm = quant.value
+            a.algorithm = algorithm
+            a.max_blocks = max_blocks
+            a.no_trailing_barrier = 1 if no_trailing_barrier else 0
+            if symmetric:
+                assert s.data_ptr() == self.arenas[r].data_ptr() + self.control
+                a.src_in_arena = a.dst_in_arena = 1
+                a.red_offset = self.control + (self.capacity if symmetric == "out_of_place" else 0)
+                assert d.data_ptr() == self.arenas[r].data_ptr() + a.red_offset
+            if want_hash:
+                a.hash_out = hashes[r].data_ptr()
+            arr[r] = a
+        ran = C.c_int()
+        with torch.cuda.device(self.device):
+            _check(lib().pcclKernelEmulatedAllReduceP2P(arr, self.world, C.byref(ran), _stream_ptr(srcs[0])), "pcclKernelEmulatedAllReduceP2P")
+        return ran.value, hashes
+
+    def outer_step(self, params, inners, momenta, lr: float, mu: float, first: bool, max_blocks: int = 8, want_hash: bool = False):
+        assert max_blocks * self.world <= 128
+        self.epoch += 1
+        for w in self.words:
+            w.zero_()
+        arr = (_lib.KernelP2PArgs * self.world)()
+        steps = (_lib.KernelOuterStepC * self.world)()
+        hashes = torch.zeros(self.world, 2, dtype=torch.int64, device=self.device) if want_hash else None
+        for r in range(self.world):
+            a = self._args(r, params[r].numel(), torch.float32, 0)
+            a.max_blocks = max_blocks
+            if want_hash:
+                a.hash_out = hashes[r].data_ptr()
+            arr[r] = a
+            st = _lib.KernelOuterStepC()
+            st.inner_in = st.inner_out = inners[r].data_ptr()
+            st.params, st.momentum = params[r].data_ptr(), momenta[r].data_ptr()
+            st.lr, st.mu, st.first = lr, mu, 1 if first else 0
+            steps[r] = st
+        with torch.cuda.device(self.device):
+            _check(lib().pcclKernelEmulatedOuterStepP2P(arr, steps, self.world, _stream_ptr(params[0])), "pcclKernelEmulatedOuterStepP2P")
+        return hashes
+
+
+def mset64(t: torch.Tensor) -> int:
+    """Order-independent content hash (csrc/kernels/mset_formula.hpp), the hash type the collective kernels can produce
+    as a by-product."""
+    return _hash(t, 2)
+
+
+def mset64_finalize(raw: int, nbytes: int) -> int:
+    fn = lib().pcclExtMsetFinalize
+    fn.restype = C.c_uint64
+    fn.argtypes = [C.c_uint64, C.c_uint64]
+    return int(fn(raw & 0xFFFFFFFFFFFFFFFF, nbytes))

@@ -1,6 +1,12 @@
 // Unit tests of the host-side building blocks: wire codec (golden bytes hand-derived from the
 // reference serialisers, ccoip/src/cpp/ccoip_packets.cpp), ATSP solver, bandwidth store, hashes,
 // quantisers, 16-bit float conversions.
+#include "device/sequencer.hpp"
+#include "kernels/mset_formula.hpp"
+#include <sys/mman.h>
+#include <random>
+#include <algorithm>
+#include <thread>
 #include <algorithm>
 #include <cmath>
 #include <cstring>
@@ -472,6 +478,93 @@ TEST(thread_guard_adopts_first_thread) {
     int status = 0;
     waitpid(pid, &status, 0);
     CHECK(!(WIFEXITED(status) && WEXITSTATUS(status) == 0));
+}
+
+// ---- same-box sequencer: processes that ask for the same operations in different orders get ONE common order
+TEST(sequencer_gives_every_process_the_same_order) {
+    using pccl::device::Sequencer;
+    void *mem = mmap(nullptr, Sequencer::bytes(), PROT_READ | PROT_WRITE, MAP_SHARED | MAP_ANONYMOUS, -1, 0);
+    CHECK(mem != MAP_FAILED);
+    Sequencer::format(mem, Sequencer::fresh_base());
+    constexpr int kProcs = 4, kTags = 5, kOps = 200;
+    int pipes[kProcs][2];
+    std::vector<pid_t> kids;
+    for (int p = 0; p < kProcs; ++p) {
+        CHECK(pipe(pipes[p]) == 0);
+        const pid_t pid = fork();
+        if (pid == 0) {
+            Sequencer seq;
+            if (!seq.attach(mem)) _exit(2);
+            // every process issues the same (tag, k) set, each tag in order, tags interleaved differently per process
+            std::vector<uint64_t> next(kTags, 0), got(kTags * kOps);
+            std::mt19937 rng(1234 + p);
+            for (int done = 0; done < kTags * kOps;) {
+                const int t = static_cast<int>(rng() % kTags);
+                if (next[t] == kOps) continue;
+                uint64_t index = 0;
+                if (!seq.order_of(100 + t, next[t], index)) _exit(3);
+                got[t * kOps + next[t]] = index;
+                ++next[t];
+                ++done;
+            }
+            const ssize_t n = write(pipes[p][1], got.data(), got.size() * sizeof(uint64_t));
+            _exit(n == static_cast<ssize_t>(got.size() * sizeof(uint64_t)) ? 0 : 4);
+        }
+        kids.push_back(pid);
+    }
+    std::vector<std::vector<uint64_t>> all(kProcs, std::vector<uint64_t>(kTags * kOps));
+    for (int p = 0; p < kProcs; ++p) {
+        size_t off = 0;
+        while (off < all[p].size() * sizeof(uint64_t)) {
+            const ssize_t n = read(pipes[p][0], reinterpret_cast<uint8_t *>(all[p].data()) + off, all[p].size() * sizeof(uint64_t) - off);
+            CHECK(n > 0);
+            off += static_cast<size_t>(n);
+        }
+        int status = 0;
+        waitpid(kids[p], &status, 0);
+        CHECK(WIFEXITED(status) && WEXITSTATUS(status) == 0);
+    }
+    for (int p = 1; p < kProcs; ++p) CHECK(all[p] == all[0]); // same index for the same operation everywhere
+    std::vector<uint64_t> sorted = all[0];
+    std::sort(sorted.begin(), sorted.end());
+    for (size_t i = 0; i < sorted.size(); ++i) CHECK_EQ(sorted[i], i); // a permutation of 0..n-1: no gaps, no duplicates
+    for (int t = 0; t < kTags; ++t)
+        for (int k = 1; k < kOps; ++k) CHECK(all[0][t * kOps + k] > all[0][t * kOps + k - 1]); // per tag the order is the issue order
+    Sequencer a, b;
+    CHECK(a.attach(mem));
+    CHECK(a.flag_epoch(5) == a.base() + 5);
+    std::this_thread::sleep_for(std::chrono::milliseconds(3));
+    CHECK(Sequencer::fresh_base() > a.flag_epoch(kTags * kOps)); // a later log starts above everything this one handed out
+    munmap(mem, Sequencer::bytes());
+}
+
+TEST(mset64_is_order_independent_and_position_dependent) {
+    std::vector<uint8_t> data(1 << 20);
+    std::mt19937 rng(7);
+    for (auto &b : data) b = static_cast<uint8_t>(rng());
+    const uint64_t whole = pccl::cpu::mset64(data.data(), data.size());
+    // any split into spans of whole packets gives the same raw sum
+    uint64_t raw = 0;
+    size_t off = 0;
+    for (size_t len : {16u * 1000u, 16u * 1u, 16u * 40000u}) {
+        raw += pccl::cpu::mset64_raw(data.data() + off, len, off / 16);
+        off += len;
+    }
+    raw += pccl::cpu::mset64_raw(data.data() + off, data.size() - off, off / 16);
+    CHECK_EQ(pccl::mset::finalize(raw, data.size()), whole);
+    // a flipped bit, swapped packets and a different length all change the value
+    data[12345] ^= 1;
+    CHECK(pccl::cpu::mset64(data.data(), data.size()) != whole);
+    data[12345] ^= 1;
+    for (int i = 0; i < 16; ++i) std::swap(data[i], data[16 + i]);
+    CHECK(pccl::cpu::mset64(data.data(), data.size()) != whole);
+    for (int i = 0; i < 16; ++i) std::swap(data[i], data[16 + i]);
+    CHECK_EQ(pccl::cpu::mset64(data.data(), data.size()), whole);
+    CHECK(pccl::cpu::mset64(data.data(), data.size() - 1) != whole);
+    // tails: zero padding is not confused with real zeros because the length is part of the value
+    const uint8_t three[3] = {1, 2, 3}, four[4] = {1, 2, 3, 0};
+    CHECK(pccl::cpu::mset64(three, 3) != pccl::cpu::mset64(four, 4));
+    CHECK_EQ(pccl::cpu::mset64(nullptr, 0), pccl::mset::finalize(0, 0));
 }
 
 TEST(guarded_blocks_fault_on_overrun) {
