@@ -503,6 +503,11 @@ class Communicator:
         t = torch.as_tensor(holder, device="cuda")
         return t.view(dtype) if t.dtype != dtype else t
 
+    def ext_symmetric_free(self, tensor: "torch.Tensor") -> None:
+        """Gives a tensor from ext_symmetric_empty back to the arena (same order on every peer, like the allocation).
+        The tensor must not be used afterwards."""
+        PCCLError.check(lib().pcclExtSymmetricFree(self._comm, tensor.data_ptr()), "pcclExtSymmetricFree")
+
 
 def _typestr(dt: DataType) -> str:
     return {

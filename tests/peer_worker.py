@@ -137,6 +137,73 @@ def main():
             ok_all = ok_all and torch.allclose(t.cpu(), want, rtol=1e-5, atol=1e-5)
         results["cases"].append({"id": "multiple", "ok": bool(ok_all), "ms": round(dt * 1e3, 3), "tensors": len(sizes),
                                  "plane": comm.ext_last_reduce_stats(0)["plane"]})
+    elif scenario == "lease":
+        # After the first (voted) operation on a tag the group runs that tag without the master.  Checks: results stay
+        # right, the stats say "leased", symmetric and in-place operands of awkward sizes, many tags in flight at once,
+        # and a host-memory operation on a leased tag (the lease of that tag ends, the operation takes the TCP ring,
+        # and the next device operation is voted again).
+        def check(name, got, want, st, want_leased):
+            nonlocal ok_all
+            ok = torch.allclose(got.cpu().double(), want.double(), rtol=1e-5, atol=1e-5) and (want_leased is None or st["leased"] == want_leased)
+            ok_all = ok_all and ok
+            results["cases"].append({"id": name, "ok": bool(ok), "plane": st["plane"], "leased": st["leased"], "us": round(st["device_ms"] * 1e3, 1)})
+
+        for it, n in enumerate([256, 256, 1000, 70_001, 300_000, 2_000_003, 256]):
+            x = make_input(600 + it, rank, n, torch.float32).to(dev)
+            y = torch.empty_like(x)
+            comm.all_reduce(x, y, op=pccl.ReduceOp.SUM, tag=0)
+            check(f"tag0_{it}_{n}", y, expected(600 + it, world, n, torch.float32, pccl.ReduceOp.SUM), comm.ext_last_reduce_stats(0), it > 0)
+            comm.all_reduce(x, x, op=pccl.ReduceOp.AVG, tag=0)  # in place on an ordinary buffer
+            check(f"tag0_inplace_{it}", x, expected(600 + it, world, n, torch.float32, pccl.ReduceOp.AVG), comm.ext_last_reduce_stats(0), True)
+        # symmetric operands, in place: small (one-shot), around the switch-over sizes, counts that are no multiple of four
+        for it, n in enumerate([5, 4099, 65_536, 65_541, 262_147, 300_001]):
+            sym = comm.ext_symmetric_empty(n, torch.float32)
+            for rep in range(3):
+                sym.copy_(make_input(700 + it, rank, n, torch.float32))
+                comm.all_reduce(sym, sym, op=pccl.ReduceOp.SUM, tag=1)
+                check(f"sym_{n}_{rep}", sym, expected(700 + it, world, n, torch.float32, pccl.ReduceOp.SUM), comm.ext_last_reduce_stats(1), None)
+            comm.ext_symmetric_free(sym)
+        # a view into the middle of a symmetric tensor is not 16-byte aligned: it must be staged, not faulted on
+        sym = comm.ext_symmetric_empty(1001, torch.float32)
+        sym.copy_(make_input(720, rank, 1001, torch.float32))
+        view = sym[1:]
+        comm.all_reduce(view, view, op=pccl.ReduceOp.SUM, tag=1)
+        check("sym_view", view, expected(720, world, 1001, torch.float32, pccl.ReduceOp.SUM)[1:], comm.ext_last_reduce_stats(1), None)
+        ok_all = ok_all and abs(float(sym[0]) - float(make_input(720, rank, 1001, torch.float32)[0])) < 1e-6
+        # 16 tags in flight, twice (the second round is leased on every tag)
+        import time as _t
+        for rnd in range(3):
+            xs = [make_input(800 + t, rank, 256, torch.float32).to(dev) for t in range(16)]
+            ys = [torch.empty_like(x) for x in xs]
+            torch.cuda.synchronize()
+            t0 = _t.perf_counter()
+            hs = [comm.all_reduce_async(xs[t], ys[t], op=pccl.ReduceOp.SUM, tag=100 + t) for t in range(16)]
+            oks = [h.wait()[0] for h in hs]
+            dt = _t.perf_counter() - t0
+            ok = all(oks) and all(torch.allclose(ys[t].cpu(), expected(800 + t, world, 256, torch.float32, pccl.ReduceOp.SUM), rtol=1e-5, atol=1e-5) for t in range(16))
+            ok_all = ok_all and ok
+            results["cases"].append({"id": f"16tags_round{rnd}", "ok": bool(ok), "total_us": round(dt * 1e6, 1),
+                                     "leased": comm.ext_last_reduce_stats(100)["leased"]})
+        # latency of a leased 1 KB operation (host wall clock around the blocking call)
+        x = make_input(900, rank, 256, torch.float32).to(dev)
+        y = torch.empty_like(x)
+        for _ in range(20):
+            comm.all_reduce(x, y, op=pccl.ReduceOp.SUM, tag=0)
+        torch.cuda.synchronize()
+        t0 = _t.perf_counter()
+        for _ in range(200):
+            comm.all_reduce(x, y, op=pccl.ReduceOp.SUM, tag=0)
+        results["leased_1KB_us"] = round((_t.perf_counter() - t0) / 200 * 1e6, 2)
+        # host memory on a leased tag: ends the lease of the tag, runs on the TCP ring, then the device takes over again
+        h = make_input(910, rank, 5000, torch.float32)
+        comm.all_reduce(h, h, op=pccl.ReduceOp.SUM, tag=0)
+        st = comm.ext_last_reduce_stats(0)
+        ok = torch.allclose(h, expected(910, world, 5000, torch.float32, pccl.ReduceOp.SUM), rtol=1e-5, atol=1e-5) and st["plane"] == "tcp_ring"
+        ok_all = ok_all and ok
+        results["cases"].append({"id": "host_on_leased_tag", "ok": bool(ok), "plane": st["plane"]})
+        for it in range(3):
+            comm.all_reduce(x, y, op=pccl.ReduceOp.SUM, tag=0)
+            check(f"after_host_{it}", y, expected(900, world, 256, torch.float32, pccl.ReduceOp.SUM), comm.ext_last_reduce_stats(0), it > 0)
     elif scenario == "kill":
         # the last rank dies without saying goodbye while reductions are running; the others must
         # notice quickly (master abort -> abort word -> kernel exit), keep their input, and go on

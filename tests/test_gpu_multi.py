@@ -122,3 +122,20 @@ def test_pipelined_nvls_kernel(world):
         assert r["ok"], r
         assert all(c["launches"] == 1 and c["plane"] == "nvls" for c in r["cases"]), r
     assert len({c["hash"] for r in results for c in r["cases"] if c["id"] == "outer_step_1"}) == 1
+
+
+@pytest.mark.parametrize("world", worlds()[:2] or [pytest.param(2, marks=pytest.mark.skip(reason="needs >= 2 GPUs"))])
+def test_leased_operations(world):
+    """Operations after the first one on a tag run without the master (lease + same-box sequencer)."""
+    results = run_peers(world, "lease", timeout=300)
+    for r in results:
+        assert r["ok"], [c for c in r["cases"] if not c["ok"]]
+    print({"world": world, "leased_1KB_us": [r["leased_1KB_us"] for r in results],
+           "16tags_us": [c["total_us"] for c in results[0]["cases"] if str(c["id"]).startswith("16tags")]})
+
+
+@pytest.mark.parametrize("world", worlds()[:1] or [pytest.param(2, marks=pytest.mark.skip(reason="needs >= 2 GPUs"))])
+def test_everything_still_works_without_leases(world):
+    for r in run_peers(world, "lease", timeout=300, env={"PCCL_LEASE": "0"}):
+        bad = [c for c in r["cases"] if not c["ok"] and "leased" not in c]
+        assert not bad, bad

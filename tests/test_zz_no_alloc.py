@@ -77,9 +77,11 @@ def test_no_alloc_hash_matches_regular_entry_point_twice_in_a_row():
 def test_no_alloc_hash_refuses_oversized_input():
     L = _declare()
     limit = L.pcclKernelSimpleHashNoAllocMaxBytes()
-    assert limit == (1 << 32) * 16 - 16
+    # 2^32 - 1 whole packets (the hash counts packets in 32 bits) and a tail shorter than a packet; the kernel's slab and
+    # loop arithmetic is 64-bit, so the top of the range is hashed, not wrapped
+    assert limit == ((1 << 32) - 1) * 16 + 15
     x = torch.zeros(16, dtype=torch.uint8, device="cuda:0")
     out = torch.zeros(1, dtype=torch.int64, device="cuda:0")
     # only the size is looked at before the refusal, nothing is read
-    rc = L.pcclKernelSimpleHashNoAlloc(x.data_ptr(), limit + 16, out.data_ptr(), None)
+    rc = L.pcclKernelSimpleHashNoAlloc(x.data_ptr(), limit + 1, out.data_ptr(), None)
     assert rc == 1  # cudaErrorInvalidValue
