@@ -168,13 +168,24 @@ def run_ours(args) -> dict:
         while comm.get_attribute(pccl.Attribute.GLOBAL_WORLD_SIZE) < world:
             comm.update_topology()
 
-        def reduce_step(src, dst):
+        enqueue = os.environ.get("PCCL_BENCH_ENQUEUE", "1") != "0"
+
+        def collect_stats():
             nonlocal launches
-            comm.all_reduce(src, dst, op=pccl.ReduceOp.AVG, tag=0, quantization_options=quant)
+            comm.ext_wait_stream_ops()
             st = comm.ext_last_reduce_stats(0)
             planes.add(st["plane"] + ("+lease" if st.get("leased") else ""))
-            launches += st["kernel_launches"]
-            dev_ms[0] += st["device_ms"]
+            return st
+
+        def reduce_step(src, dst):
+            # Stream-ordered, like NCCL's all-reduce: the call returns after the launch (when no vote at the master is
+            # needed) and the next one queues up behind it; verdicts are taken in batches and at the end of the region.
+            nonlocal launches
+            comm.all_reduce(src, dst, op=pccl.ReduceOp.AVG, tag=0, quantization_options=quant, enqueue=enqueue)
+            launches += 1
+            if not enqueue:
+                st = collect_stats()
+                dev_ms[0] += st["device_ms"]
 
         if args.buffers == "symmetric" and quant is None:
             # Peer-visible ("symmetric") buffers from the communicator's arena: the reduction runs in
@@ -205,6 +216,8 @@ def run_ours(args) -> dict:
         for i in range(steps):
             fn()
             evs[i + 1].record()
+        if comm is not None:
+            comm.ext_wait_stream_ops()  # verdicts of everything enqueued in the region
         torch.cuda.synchronize()
         per = sorted(evs[i].elapsed_time(evs[i + 1]) for i in range(steps))
         total = evs[0].elapsed_time(evs[steps])
@@ -228,6 +241,10 @@ def run_ours(args) -> dict:
     ms_step = timed(lambda: reduce_step(main_src, main_dst), args.steps)
     main_timing = {k: round(v, 4) for k, v in last_timing.items()}
     main_planes = sorted(planes)
+    if comm is not None:
+        st_last = collect_stats()
+        if not dev_ms[0]:
+            dev_ms[0] = st_last["device_ms"] * args.steps  # enqueued operations: the last one's kernel time stands for all
     kernel_ms = max_over_ranks(dev_ms[0] / args.steps) if dev_ms[0] else None
     timed_launches = launches
 
@@ -235,7 +252,7 @@ def run_ours(args) -> dict:
     def e2e_step():
         main_src.copy_(pinned, non_blocking=True)
         reduce_step(main_src, main_dst)
-        return float(main_dst[0].item())
+        return float(main_dst[0].item())  # device-to-host read of the result: waits for the stream, i.e. for the reduction
 
     for _ in range(3):
         e2e_step()
@@ -285,6 +302,9 @@ def run_ours(args) -> dict:
             reduce_step(grad, out)
         dev_ms[0] = 0.0
         ms_reg = timed(lambda: reduce_step(grad, out), args.steps)
+        st_last = collect_stats()
+        if not dev_ms[0]:
+            dev_ms[0] = st_last["device_ms"] * args.steps
         regular = {"ms_per_step": round(ms_reg, 4), "bus_GBps": round(nbytes * bus_factor(world) / (ms_reg * 1e-3) / 1e9, 2),
                    "kernel_ms_per_step": round(max_over_ranks(dev_ms[0] / args.steps), 4), "planes": sorted(planes)}
 
@@ -357,7 +377,7 @@ def run_ours(args) -> dict:
                            "with world size 1 through ops.local_all_reduce; bus factor 1" if world == 1 else
                            "bus GB/s = bytes*2(P-1)/P/t; t = median step (device time, max over ranks) incl. control plane"},
         "e2e": {"value": round(e2e_value, 3), "unit": "GB/s", "ms_per_step": round(ms_e2e, 4), "h2d_bytes_per_step": nbytes, "d2h_bytes_per_step": 4},
-        "gpu_launches": timed_launches,
+        "gpu_launches": timed_launches, "api": "Communicator.all_reduce(..., enqueue=%s), stream-ordered" % (world > 1 and os.environ.get("PCCL_BENCH_ENQUEUE", "1") != "0"),
         "step_ms": main_timing,
         "call_overhead_ms": round(ms_step - kernel_ms, 4) if kernel_ms else None,
         "diloco_outer_step_ms": round(ms_outer, 4),

@@ -256,6 +256,37 @@ pcclResult_t pcclAllReduce(const void *sendbuff, void *recvbuff, const pcclReduc
     return out.ok ? pcclSuccess : pcclRankConnectionLost;
 }
 
+pcclResult_t pcclExtAllReduceOnStream(const void *sendbuff, void *recvbuff, const pcclReduceDescriptor_t *descriptor, const pcclComm_t *c,
+                                      void *cuda_stream, int enqueue, pcclReduceInfo_t *info_out) {
+    PCCL_REQUIRE_INIT();
+    PCCL_REQUIRE(c, pcclInvalidArgument);
+    PCCL_REQUIRE(c->client, pcclInvalidUsage);
+    client::ReduceRequest req;
+    if (const pcclResult_t rc = build_request(sendbuff, recvbuff, descriptor, req); rc != pcclSuccess) return rc;
+    PCCL_REQUIRE(device::classify_pointer(sendbuff).is_device && device::classify_pointer(recvbuff).is_device, pcclInvalidArgument);
+    PCCL_REQUIRE(c->client->local_world() >= 2, pcclTooFewPeers);
+    req.user_stream = cuda_stream ? cuda_stream : reinterpret_cast<void *>(uintptr_t(1)); // null = the legacy default stream (handle 1)
+    req.enqueue = enqueue != 0;
+    client::ReduceOutcome out;
+    switch (c->client->all_reduce_on_stream(req, out)) {
+    case client::Client::Launch::Ok: break;
+    case client::Client::Launch::DuplicateTag: return pcclInvalidArgument;
+    case client::Client::Launch::NotConnected: return pcclInvalidUsage;
+    }
+    if (info_out) *info_out = {out.world, out.tx_bytes, out.rx_bytes};
+    return out.ok ? pcclSuccess : pcclRankConnectionLost;
+}
+
+pcclResult_t pcclExtWaitStreamOps(const pcclComm_t *c, uint64_t tag, int all_tags, pcclReduceInfo_t *info_out) {
+    PCCL_REQUIRE_INIT();
+    PCCL_REQUIRE(c, pcclInvalidArgument);
+    PCCL_REQUIRE(c->client, pcclInvalidUsage);
+    client::ReduceOutcome out;
+    const bool ok = c->client->wait_stream_ops(tag, all_tags != 0, out);
+    if (info_out) *info_out = {out.world, out.tx_bytes, out.rx_bytes};
+    return ok ? pcclSuccess : pcclRankConnectionLost;
+}
+
 pcclResult_t pcclExtDiLoCoOuterStep(const pcclExtOuterStepDescriptor_t *d, const pcclComm_t *c, pcclReduceInfo_t *info_out) {
     PCCL_REQUIRE_INIT();
     PCCL_REQUIRE(c && d, pcclInvalidArgument);

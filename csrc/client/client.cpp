@@ -707,7 +707,7 @@ bool Client::sync_shared_state(SharedStateArgs &state, uint64_t &tx_bytes, uint6
 
 bool Client::any_reduce_running() {
     std::lock_guard<std::mutex> lock(ops_mu_);
-    return !ops_.empty();
+    return !ops_.empty() || !stream_ops_.empty();
 }
 
 bool Client::last_stats(uint64_t tag, pcclExtReduceStats_t &out) {
@@ -759,6 +759,100 @@ Client::Launch Client::all_reduce_sync(const ReduceRequest &req, ReduceOutcome &
     out = run_reduce(req, rev);
     conclude(req.tag, rev, out);
     return Launch::Ok;
+}
+
+Client::Launch Client::all_reduce_on_stream(const ReduceRequest &req, ReduceOutcome &out) {
+    if (!accepted_ || !master_.is_open()) return Launch::NotConnected;
+    // Verdicts of earlier enqueued operations are collected on the way: all of them when too many are in flight (each
+    // holds a flag bank), otherwise only while the oldest ones have already finished.  A failure among them is
+    // reported by this call.
+    constexpr size_t kMaxEnqueued = 8;
+    for (;;) {
+        StreamOp oldest;
+        uint64_t tag = 0;
+        {
+            std::lock_guard<std::mutex> lock(ops_mu_);
+            if (stream_ops_.size() < kMaxEnqueued) break;
+            tag = stream_ops_.front().first;
+            oldest = stream_ops_.front().second;
+            stream_ops_.pop_front();
+        }
+        ReduceOutcome prev;
+        if (!finish_stream_op(tag, oldest, prev)) {
+            out = prev;
+            out.ok = false;
+            return Launch::Ok;
+        }
+    }
+    uint64_t rev;
+    {
+        std::lock_guard<std::mutex> lock(ops_mu_);
+        if (ops_.count(req.tag)) return Launch::DuplicateTag;
+        Op op;
+        op.revision_at_launch = rev = connection_revision_;
+        ops_.emplace(req.tag, std::move(op));
+    }
+    out = run_reduce(req, rev);
+    if (out.pending) {
+        std::lock_guard<std::mutex> lock(ops_mu_);
+        ops_.erase(req.tag); // several enqueued operations may share a tag; they are tracked in stream_ops_
+        StreamOp so;
+        so.ticket = out.ticket;
+        so.revision_at_launch = rev;
+        so.partial = out;
+        stream_ops_.emplace_back(req.tag, so);
+        return Launch::Ok;
+    }
+    conclude(req.tag, rev, out);
+    return Launch::Ok;
+}
+
+bool Client::finish_stream_op(uint64_t tag, const StreamOp &so, ReduceOutcome &out) {
+    const auto r = plane_->finish(so.ticket, [&]() { return !master_.is_open() || interrupted_.load(); });
+    out = so.partial;
+    out.pending = false;
+    out.ok = r.ok;
+    out.tx_bytes = r.tx_bytes;
+    out.rx_bytes = r.rx_bytes;
+    out.stats.plane = r.plane;
+    out.stats.device_ms = r.device_ms;
+    out.stats.kernel_launches = r.kernel_launches;
+    out.has_hash = r.has_hash;
+    out.hash[0] = r.hash[0];
+    out.hash[1] = r.hash[1];
+    if (!r.ok) {
+        std::lock_guard<std::mutex> lock(lease_mu_);
+        lease_tags_.erase(tag);
+    }
+    bool others;
+    {
+        std::lock_guard<std::mutex> lock(ops_mu_);
+        stats_[tag] = out.stats;
+        others = !ops_.empty() || !stream_ops_.empty();
+    }
+    if (!out.ok && !others) {
+        std::lock_guard<std::mutex> lock(joint_mu_);
+        if (connection_revision_ == so.revision_at_launch && master_.is_open()) request_and_establish(false);
+    }
+    return out.ok;
+}
+
+bool Client::wait_stream_ops(uint64_t tag, bool all, ReduceOutcome &last) {
+    std::vector<std::pair<uint64_t, StreamOp>> todo;
+    {
+        std::lock_guard<std::mutex> lock(ops_mu_);
+        for (auto it = stream_ops_.begin(); it != stream_ops_.end();) {
+            if (all || it->first == tag) {
+                todo.push_back(*it);
+                it = stream_ops_.erase(it);
+            } else {
+                ++it;
+            }
+        }
+    }
+    bool ok = true;
+    for (auto &[t, so] : todo) ok = finish_stream_op(t, so, last) && ok;
+    return ok;
 }
 
 bool Client::conclude(uint64_t tag, uint64_t revision_at_launch, ReduceOutcome &out) {
@@ -871,6 +965,8 @@ ReduceOutcome Client::run_reduce(const ReduceRequest &req, uint64_t) {
     dargs.rank = rank;
     dargs.world = world;
     dargs.outer = req.outer;
+    dargs.user_stream = req.user_stream;
+    dargs.want_hash = req.want_hash;
     uint32_t caps = send_info.is_device && recv_info.is_device ? plane_->capabilities(dargs) : 0;
     // Outer step that cannot run as one kernel (host tensors, no device plane, larger than a staging slot): the
     // pseudo-gradient goes to a scratch buffer now, the scratch buffer is reduced like any tensor, and the
@@ -940,7 +1036,19 @@ ReduceOutcome Client::run_reduce(const ReduceRequest &req, uint64_t) {
             dargs.tag = req.tag;
             dargs.lease_k = k;
             dargs.use_nvls = lease_mc_all_.load() && (caps & device::Plane::kCapNvls) != 0;
+            dargs.enqueue_only = req.enqueue && req.user_stream != nullptr && !outer_two_pass;
             const auto r = plane_->reduce(dargs, [&]() { return !master_.is_open() || interrupted_.load(); });
+            if (r.pending) { // launched behind the caller's stream; the verdict is taken later (wait_stream_ops)
+                out.pending = true;
+                out.ticket = r.ticket;
+                out.stats.leased = 1;
+                out.stats.seq_nr = k;
+                out.ok = true;
+                return out;
+            }
+            out.has_hash = r.has_hash;
+            out.hash[0] = r.hash[0];
+            out.hash[1] = r.hash[1];
             out.tx_bytes = r.tx_bytes;
             out.rx_bytes = r.rx_bytes;
             out.stats.plane = r.plane;
@@ -1065,6 +1173,9 @@ ReduceOutcome Client::run_reduce(const ReduceRequest &req, uint64_t) {
         out.stats.plane = r.plane;
         out.stats.device_ms = r.device_ms;
         out.stats.kernel_launches = r.kernel_launches;
+        out.has_hash = r.has_hash;
+        out.hash[0] = r.hash[0];
+        out.hash[1] = r.hash[1];
     } else if (use_device) {
         // cannot happen unless peers disagree about their own capability between vote and run
         PLOG(ERR) << "device plane was agreed on but is not available locally";

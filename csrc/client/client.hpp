@@ -8,6 +8,7 @@
 #pragma once
 #include <atomic>
 #include <condition_variable>
+#include <deque>
 #include <future>
 #include <map>
 #include <memory>
@@ -67,6 +68,11 @@ struct ReduceRequest {
     // DiLoCo outer step: when set, send/recv are ignored; the reduction averages params - inner (fp32) and
     // its result drives the Nesterov update of params/momentum/inner (see device::OuterStepArgs)
     const device::OuterStepArgs *outer = nullptr;
+    // stream-ordered form (device buffers): the operation is ordered after the work already queued on this CUDA stream
+    // and the stream waits for its result; with `enqueue` the call returns after the launch when no vote is needed
+    void *user_stream = nullptr;
+    bool enqueue = false;
+    bool want_hash = false; // also produce the mset64 content hash(es) of the result (device plane, one launch)
 };
 
 struct ReduceOutcome {
@@ -74,6 +80,10 @@ struct ReduceOutcome {
     uint32_t world = 0;
     uint64_t tx_bytes = 0, rx_bytes = 0;
     pcclExtReduceStats_t stats{};
+    bool pending = false;  // enqueued on the device, verdict not taken yet (see Client::wait_stream_ops)
+    uint64_t ticket = 0;
+    bool has_hash = false;
+    uint64_t hash[2] = {0, 0};
 };
 
 class Client {
@@ -98,6 +108,12 @@ public:
     bool await_reduce(uint64_t tag, ReduceOutcome &out);
     // Blocking variant that runs on the calling thread (no hand-over to the worker pool).
     Launch all_reduce_sync(const ReduceRequest &req, ReduceOutcome &out);
+    // Stream-ordered reduction: like all_reduce_sync, but ordered after req.user_stream; when the operation runs under a
+    // lease the call returns right after the launch and the verdict is taken by the next operation on the same tag or
+    // by wait_stream_ops().  Several may be in flight, also on one tag (the stream orders them).
+    Launch all_reduce_on_stream(const ReduceRequest &req, ReduceOutcome &out);
+    // Takes the verdict of the enqueued operation on `tag` (all tags when `all`).  False when one of them failed.
+    bool wait_stream_ops(uint64_t tag, bool all, ReduceOutcome &last);
     bool any_reduce_running();
     bool last_stats(uint64_t tag, pcclExtReduceStats_t &out);
 
@@ -124,6 +140,8 @@ private:
     void on_benchmark_accept(std::unique_ptr<net::BlockingSocket> sock);
     ReduceOutcome run_reduce(const ReduceRequest &req, uint64_t revision_at_launch);
     bool conclude(uint64_t tag, uint64_t revision_at_launch, ReduceOutcome &out);
+    struct StreamOp;
+    bool finish_stream_op(uint64_t tag, const StreamOp &so, ReduceOutcome &out);
     // Completion handshakes that were left pending after a device-plane reduction returned early.
     struct Deferred {
         bool abort_seen = false, aborted = false;
@@ -178,6 +196,11 @@ private:
     std::map<uint64_t, uint64_t> lease_counts_;
     std::atomic<bool> lease_mc_all_{false}; // every peer of the ring holds the multicast view
     bool lease_enabled_ = true;             // PCCL_LEASE=0 keeps every operation a vote
+    struct StreamOp {
+        uint64_t ticket = 0, revision_at_launch = 0;
+        ReduceOutcome partial;
+    };
+    std::deque<std::pair<uint64_t, StreamOp>> stream_ops_; // (tag, operation) in launch order; guarded by ops_mu_
     std::mutex ops_mu_;
     std::map<uint64_t, Op> ops_;
     std::map<uint64_t, pcclExtReduceStats_t> stats_;

@@ -370,6 +370,22 @@ PCCL_EXPORT size_t pcclExtDataTypeSize(pcclDataType_t datatype);
  * the library computes the pseudo-gradient into a scratch buffer, reduces that, and applies the update.
  * Either way the tensors are untouched when the call fails (pcclRankConnectionLost: retry after
  * pcclUpdateTopology, like pcclAllReduce).  Synchronous; one tag like any reduction. */
+/* Stream-ordered all-reduce on device buffers (no counterpart in the reference, whose all-reduce takes host memory and
+ * blocks: src/pccl.cpp:301-313).  The operation is ordered after everything already queued on `cuda_stream`
+ * (a cudaStream_t; NULL = the legacy default stream) and that stream waits for the result, so the caller needs no
+ * stream or device synchronisation on either side and kernels on other streams keep running while peers exchange data.
+ * enqueue != 0: when the operation needs no vote at the master (it runs under a lease) the call
+ * returns right after the launch; its verdict is taken by the next stream-ordered operation on the same tag or by
+ * pcclExtWaitStreamOps, and until then the tag counts as in flight (pcclUpdateTopology and
+ * pcclSynchronizeSharedState answer pcclPendingAsyncOps).  A failure of an enqueued operation is reported by that
+ * later call as pcclRankConnectionLost. */
+PCCL_EXPORT pcclResult_t pcclExtAllReduceOnStream(const void *sendbuff, void *recvbuff, const pcclReduceDescriptor_t *descriptor,
+                                                  const pcclComm_t *communicator, void *cuda_stream, int enqueue,
+                                                  pcclReduceInfo_t *reduce_info_out);
+/* Takes the verdict of the enqueued operation on `tag` (of all tags when all_tags != 0); blocks until it has finished. */
+PCCL_EXPORT pcclResult_t pcclExtWaitStreamOps(const pcclComm_t *communicator, uint64_t tag, int all_tags,
+                                              pcclReduceInfo_t *reduce_info_out);
+
 typedef struct pcclExtOuterStepDescriptor_t {
     void *params;
     void *inner;

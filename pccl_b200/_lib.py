@@ -201,6 +201,8 @@ def lib() -> C.CDLL:
     sig("pcclMasterAwaitTermination", i32, vp)
     sig("pcclDestroyMaster", i32, vp)
     sig("pcclGetBuildInfo", i32, C.POINTER(BuildInfoC))
+    sig("pcclExtAllReduceOnStream", i32, vp, vp, C.POINTER(ReduceDescriptorC), vp, vp, i32, C.POINTER(ReduceInfoC))
+    sig("pcclExtWaitStreamOps", i32, vp, u64, i32, C.POINTER(ReduceInfoC))
     sig("pcclExtGetLastReduceStats", i32, vp, u64, C.POINTER(ExtReduceStatsC))
     sig("pcclExtMasterGetPort", i32, vp, C.POINTER(C.c_uint16))
     sig("pcclExtHashBuffer", i32, vp, sz, i32, i32, C.POINTER(u64))

@@ -421,7 +421,7 @@ class Communicator:
                         "pcclSynchronizeSharedState")
         return SharedStateSyncInfo(info.tx_bytes, info.rx_bytes)
 
-    def _descriptor(self, send, recv, op: ReduceOp, tag: int, operand_descriptor, quantization_options):
+    def _descriptor(self, send, recv, op: ReduceOp, tag: int, operand_descriptor, quantization_options, sync_stream: bool = True):
         sp, sn, sdt, sdev, _ = _tensor_view(send)
         rp, rn, rdt, rdev, _ = _tensor_view(recv)
         assert sn == rn, "send and recv must have the same number of elements"
@@ -429,16 +429,39 @@ class Communicator:
         assert sdev == rdev, "send and recv must live on the same kind of device"
         operand_descriptor = operand_descriptor or ReduceOperandDescriptor(sdt)
         desc = ReduceDescriptor(sn, op, tag, operand_descriptor, quantization_options)
-        if sdev == DeviceType.CUDA:
+        if sdev == DeviceType.CUDA and sync_stream:
             _sync_current_stream([send, recv])
         return sp, rp, desc.to_c()
 
     def all_reduce(self, send, recv, *, op: ReduceOp, tag: int = 0,
                    operand_descriptor: Optional[ReduceOperandDescriptor] = None,
-                   quantization_options: Optional[QuantizationOptions] = None) -> ReduceInfo:
-        sp, rp, desc = self._descriptor(send, recv, op, tag, operand_descriptor, quantization_options)
+                   quantization_options: Optional[QuantizationOptions] = None,
+                   stream=None, enqueue: bool = False) -> ReduceInfo:
+        """Reduces `send` over all peers of the group into `recv`.
+
+        CUDA tensors are reduced in stream order: the operation starts after the work queued on `stream` (default: torch's
+        current stream of the tensor's device) and that stream waits for the result -- no stream or device synchronisation
+        happens here, and kernels on other streams overlap with the reduction.  By default the call still returns only
+        when the reduction has finished (the reference's contract).  enqueue=True returns after the launch whenever the
+        operation needs no vote at the master (every operation on a tag after the first one, until membership changes);
+        a failure then surfaces at the next stream-ordered call or at ext_wait_stream_ops()."""
+        on_device = torch is not None and isinstance(send, torch.Tensor) and send.is_cuda
+        sp, rp, desc = self._descriptor(send, recv, op, tag, operand_descriptor, quantization_options, sync_stream=not on_device)
         info = _lib.ReduceInfoC()
-        PCCLError.check(lib().pcclAllReduce(sp, rp, C.byref(desc), self._comm, C.byref(info)), "pcclAllReduce")
+        if on_device:
+            handle = (stream if stream is not None else torch.cuda.current_stream(send.device)).cuda_stream
+            PCCLError.check(lib().pcclExtAllReduceOnStream(sp, rp, C.byref(desc), self._comm, C.c_void_p(handle), 1 if enqueue else 0, C.byref(info)),
+                            "pcclExtAllReduceOnStream")
+        else:
+            PCCLError.check(lib().pcclAllReduce(sp, rp, C.byref(desc), self._comm, C.byref(info)), "pcclAllReduce")
+        return ReduceInfo(info.local_world_size, info.tx_bytes, info.rx_bytes)
+
+    def ext_wait_stream_ops(self, tag: Optional[int] = None) -> ReduceInfo:
+        """Takes the verdict of the enqueued (all_reduce(..., enqueue=True)) operations on `tag`, or of all of them.
+        Raises PCCLError(RANK_CONNECTION_LOST) when one of them failed."""
+        info = _lib.ReduceInfoC()
+        PCCLError.check(lib().pcclExtWaitStreamOps(self._comm, 0 if tag is None else tag, 1 if tag is None else 0, C.byref(info)),
+                        "pcclExtWaitStreamOps")
         return ReduceInfo(info.local_world_size, info.tx_bytes, info.rx_bytes)
 
     def all_reduce_async(self, send, recv, *, op: ReduceOp, tag: int = 0,

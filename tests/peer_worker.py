@@ -142,8 +142,13 @@ def main():
         # right, the stats say "leased", symmetric and in-place operands of awkward sizes, many tags in flight at once,
         # and a host-memory operation on a leased tag (the lease of that tag ends, the operation takes the TCP ring,
         # and the next device operation is voted again).
+        import os as _os
+        lease_on = _os.environ.get("PCCL_LEASE", "1") != "0"
+
         def check(name, got, want, st, want_leased):
             nonlocal ok_all
+            if want_leased is not None:
+                want_leased = want_leased and lease_on
             ok = torch.allclose(got.cpu().double(), want.double(), rtol=1e-5, atol=1e-5) and (want_leased is None or st["leased"] == want_leased)
             ok_all = ok_all and ok
             results["cases"].append({"id": name, "ok": bool(ok), "plane": st["plane"], "leased": st["leased"], "us": round(st["device_ms"] * 1e3, 1)})
@@ -194,6 +199,50 @@ def main():
         for _ in range(200):
             comm.all_reduce(x, y, op=pccl.ReduceOp.SUM, tag=0)
         results["leased_1KB_us"] = round((_t.perf_counter() - t0) / 200 * 1e6, 2)
+        # enqueued (stream-ordered) operations: a chain on one tag whose every link depends on the one before
+        z = torch.ones(100_000, device=dev)
+        for _ in range(12):
+            comm.all_reduce(z, z, op=pccl.ReduceOp.SUM, tag=0, enqueue=True)
+            z.mul_(0.5)
+        comm.ext_wait_stream_ops()
+        ok = torch.allclose(z.cpu(), torch.full((100_000,), (world * 0.5) ** 12), rtol=1e-5)
+        ok_all = ok_all and ok
+        results["cases"].append({"id": "enqueued_chain", "ok": bool(ok), "leased": comm.ext_last_reduce_stats(0)["leased"]})
+        # overlap: a long local kernel on another stream runs WHILE a large reduction is in flight
+        big = make_input(930, rank, 64_000_000, torch.float32).to(dev)
+        a = torch.randn(6144, 6144, device=dev)
+        side = torch.cuda.Stream(device=dev)
+
+        def burn():
+            with torch.cuda.stream(side):
+                for _ in range(12):
+                    torch.mm(a, a)
+
+        def timed_ms(fn):
+            torch.cuda.synchronize()
+            t0 = _t.perf_counter()
+            fn()
+            torch.cuda.synchronize()
+            return (_t.perf_counter() - t0) * 1e3
+
+        comm.all_reduce(big, big, op=pccl.ReduceOp.AVG, tag=2)
+        comm.all_reduce(big, big, op=pccl.ReduceOp.AVG, tag=2)
+        burn()
+        t_burn = min(timed_ms(burn) for _ in range(2))
+        t_red = min(timed_ms(lambda: comm.all_reduce(big, big, op=pccl.ReduceOp.AVG, tag=2, enqueue=True)) for _ in range(2))
+        comm.ext_wait_stream_ops()
+
+        def both():
+            burn()
+            comm.all_reduce(big, big, op=pccl.ReduceOp.AVG, tag=2, enqueue=True)
+
+        t_both = min(timed_ms(both) for _ in range(2))
+        comm.ext_wait_stream_ops()
+        results["overlap_ms"] = {"compute": round(t_burn, 3), "reduce": round(t_red, 3), "both": round(t_both, 3)}
+        if lease_on:
+            ok = t_both < 0.9 * (t_burn + t_red)
+            ok_all = ok_all and ok
+            results["cases"].append({"id": "overlap", "ok": bool(ok)})
         # host memory on a leased tag: ends the lease of the tag, runs on the TCP ring, then the device takes over again
         h = make_input(910, rank, 5000, torch.float32)
         comm.all_reduce(h, h, op=pccl.ReduceOp.SUM, tag=0)
