@@ -817,6 +817,7 @@ bool Client::finish_stream_op(uint64_t tag, const StreamOp &so, ReduceOutcome &o
     out.stats.plane = r.plane;
     out.stats.device_ms = r.device_ms;
     out.stats.kernel_launches = r.kernel_launches;
+        std::copy(std::begin(r.phase_ns), std::end(r.phase_ns), std::begin(out.stats.phase_ns));
     out.has_hash = r.has_hash;
     out.hash[0] = r.hash[0];
     out.hash[1] = r.hash[1];
@@ -1054,6 +1055,7 @@ ReduceOutcome Client::run_reduce(const ReduceRequest &req, uint64_t) {
             out.stats.plane = r.plane;
             out.stats.device_ms = r.device_ms;
             out.stats.kernel_launches = r.kernel_launches;
+        std::copy(std::begin(r.phase_ns), std::end(r.phase_ns), std::begin(out.stats.phase_ns));
             out.stats.seq_nr = k;
             out.stats.leased = 1;
             if (r.ok) {
@@ -1173,6 +1175,7 @@ ReduceOutcome Client::run_reduce(const ReduceRequest &req, uint64_t) {
         out.stats.plane = r.plane;
         out.stats.device_ms = r.device_ms;
         out.stats.kernel_launches = r.kernel_launches;
+        std::copy(std::begin(r.phase_ns), std::end(r.phase_ns), std::begin(out.stats.phase_ns));
         out.has_hash = r.has_hash;
         out.hash[0] = r.hash[0];
         out.hash[1] = r.hash[1];

@@ -78,6 +78,7 @@ struct DeviceReduceResult {
     bool input_destroyed = false; // in place on symmetric memory: a failed attempt may have overwritten the input
     bool has_hash = false;
     uint64_t hash[2] = {0, 0};    // mset64 of the output (outer step: [0] parameters, [1] momentum)
+    uint64_t phase_ns[8] = {0};   // GPU global timer at the kernel's phase boundaries (block 0)
     bool pending = false;         // enqueue_only: launched, not finished
     uint64_t ticket = 0;          // identifies the pending operation for finish()
 };

@@ -954,7 +954,7 @@ private:
             }
         }
         res.input_destroyed = !res.ok && f.destroys_input;
-        for (int i = 0; i < 8; ++i) last_stamps_[i] = reinterpret_cast<volatile uint64_t *>(bank.host_words + 16)[i];
+        for (int i = 0; i < 8; ++i) res.phase_ns[i] = reinterpret_cast<volatile uint64_t *>(bank.host_words + 16)[i];
         return res;
     }
 
@@ -1521,7 +1521,6 @@ private:
     std::mutex inflight_mu_;
     std::map<uint64_t, Flight> inflight_;
     std::atomic<uint64_t> ticket_counter_{0};
-    uint64_t last_stamps_[8] = {0};
     std::mutex exchange_mu_;
 
     std::mutex order_mu_;
@@ -1551,6 +1550,21 @@ bool cuda_runtime_usable() {
 PointerInfo classify_pointer(const void *p) {
     PointerInfo info;
     if (!p || !cuda_runtime_usable()) return info;
+    // Hot path of small reductions: the same few pointers are asked about again and again.  Only positive answers are
+    // remembered (unified addressing keeps device and host ranges apart, so a device address stays a device address of
+    // that GPU for as long as it is valid at all).
+    struct Known {
+        const void *ptr;
+        int device;
+    };
+    thread_local Known known[8] = {};
+    thread_local unsigned next_slot = 0;
+    for (const Known &k : known)
+        if (k.ptr == p) {
+            info.is_device = true;
+            info.device = k.device;
+            return info;
+        }
     cudaPointerAttributes attr{};
     if (cudaPointerGetAttributes(&attr, p) != cudaSuccess) {
         (void) cudaGetLastError();
@@ -1559,6 +1573,7 @@ PointerInfo classify_pointer(const void *p) {
     if (attr.type == cudaMemoryTypeDevice || attr.type == cudaMemoryTypeManaged) {
         info.is_device = true;
         info.device = attr.device;
+        known[next_slot++ % 8] = Known{p, attr.device};
     }
     return info;
 }

@@ -335,6 +335,9 @@ typedef struct pcclExtReduceStats_t {
     uint64_t seq_nr;     /* master-issued sequence number of the operation */
     uint32_t kernel_launches; /* kernels of this library launched for the operation */
     uint32_t leased;     /* 1: ran under a lease, without a vote at the master (seq_nr then counts leased operations of the tag) */
+    uint64_t phase_ns[8]; /* device plane: GPU global timer (ns) when block 0 of the (last) kernel reached its phase boundaries:
+                             [0] start, [1] input staged, [2] first barrier passed, [3] own chunk reduced, [4] second barrier
+                             passed, [5] output written, [6] closing barrier passed; 0 = phase not present */
 } pcclExtReduceStats_t;
 
 /* Stats of the most recently completed reduction with the given tag. */

@@ -116,7 +116,7 @@ class BuildInfoC(C.Structure):
 
 class ExtReduceStatsC(C.Structure):
     _fields_ = [("plane", C.c_int), ("device_ms", C.c_float), ("seq_nr", C.c_uint64), ("kernel_launches", C.c_uint32),
-                ("leased", C.c_uint32)]
+                ("leased", C.c_uint32), ("phase_ns", C.c_uint64 * 8)]
 
 
 class ExtOuterStepDescriptorC(C.Structure):

@@ -488,7 +488,8 @@ class Communicator:
         PCCLError.check(lib().pcclExtGetLastReduceStats(self._comm, tag, C.byref(st)), "pcclExtGetLastReduceStats")
         names = {0: "none", 1: "tcp_ring", 2: "p2p_one_shot", 3: "p2p_two_shot", 4: "nvls"}
         return {"plane": names.get(st.plane, str(st.plane)), "device_ms": float(st.device_ms), "seq_nr": int(st.seq_nr),
-                "kernel_launches": int(st.kernel_launches), "leased": bool(st.leased)}
+                "kernel_launches": int(st.kernel_launches), "leased": bool(st.leased),
+                "phase_us": [round((int(st.phase_ns[i]) - int(st.phase_ns[0])) / 1e3, 2) if st.phase_ns[i] else None for i in range(7)]}
 
     def ext_diloco_outer_step(self, params, inner, momentum, *, lr: float = 0.7, mu: float = 0.9, first: bool = False,
                               tag: int = 0) -> ReduceInfo:

@@ -132,7 +132,7 @@ def test_leased_operations(world):
         assert r["ok"], [c for c in r["cases"] if not c["ok"]]
     print({"world": world, "leased_1KB_us": [r["leased_1KB_us"] for r in results],
            "16tags_us": [c["total_us"] for c in results[0]["cases"] if str(c["id"]).startswith("16tags")],
-           "overlap_ms": results[0].get("overlap_ms")})
+           })
 
 
 @pytest.mark.parametrize("world", worlds()[:1] or [pytest.param(2, marks=pytest.mark.skip(reason="needs >= 2 GPUs"))])
@@ -140,3 +140,11 @@ def test_everything_still_works_without_leases(world):
     for r in run_peers(world, "lease", timeout=300, env={"PCCL_LEASE": "0"}):
         assert r["ok"], [c for c in r["cases"] if not c["ok"]]
         assert not any(c.get("leased") for c in r["cases"])
+
+
+@pytest.mark.parametrize("world", worlds()[:1] or [pytest.param(2, marks=pytest.mark.skip(reason="needs >= 2 GPUs"))])
+def test_reduction_overlaps_with_compute_on_another_stream(world):
+    results = run_peers(world, "overlap", timeout=300, env={"PCCL_DEVICE_MAX_BLOCKS": "32"})
+    print({"overlap_ms": [r.get("overlap_ms") for r in results]})
+    for r in results:
+        assert r["ok"], r
