@@ -240,11 +240,11 @@ def run_ours(args) -> dict:
     dev_ms[0] = 0.0
     ms_step = timed(lambda: reduce_step(main_src, main_dst), args.steps)
     main_timing = {k: round(v, 4) for k, v in last_timing.items()}
-    main_planes = sorted(planes)
     if comm is not None:
         st_last = collect_stats()
         if not dev_ms[0]:
             dev_ms[0] = st_last["device_ms"] * args.steps  # enqueued operations: the last one's kernel time stands for all
+    main_planes = sorted(planes)
     kernel_ms = max_over_ranks(dev_ms[0] / args.steps) if dev_ms[0] else None
     timed_launches = launches
 

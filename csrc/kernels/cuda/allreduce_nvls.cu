@@ -152,23 +152,53 @@ template <int TYPE, int OP, int U> struct NvlsAllReduce {
         stamp(a, 2);
 
         MsetAcc digest;
-        {
-            const uint64_t lo = min(uint64_t(a.rank) * per, n_pack), hi = min(lo + per, n_pack);
-            const float div = static_cast<float>(a.avg_divisor);
-            for_owned_packets<U>(lo, hi, [&](const uint64_t(&v)[U], const bool(&ok)[U]) {
+        const uint64_t lo = min(uint64_t(a.rank) * per, n_pack), hi = min(lo + per, n_pack);
+        const float div = static_cast<float>(a.avg_divisor);
+        if (a.dynamic) {
+            // Large symmetric operands: SMs differ in how fast they get data through the switch (die, distance to the
+            // NVLink ports), and with a static split the whole kernel waits for the slowest block.  Here every warp takes
+            // units of 32 x U packets from a counter until the chunk is done; a barrier over all blocks of all ranks follows.
+            const int lane = threadIdx.x & 31;
+            constexpr uint64_t kUnit = 32ull * U;
+            const uint64_t n_units = (hi - lo + kUnit - 1) / kUnit;
+            for (;;) {
+                unsigned long long unit = 0;
+                if (lane == 0) unit = claim_units(a, tbl.arena[a.rank], 1);
+                unit = __shfl_sync(0xffffffffu, unit, 0);
+                if (unit >= n_units) break;
                 uint4 val[U];
-#pragma unroll
-                for (int u = 0; u < U; ++u)
-                    if (ok[u]) val[u] = mc_ld_reduce<TYPE, OP>(mc_in + v[u]);
+                uint64_t v[U];
 #pragma unroll
                 for (int u = 0; u < U; ++u) {
-                    if (!ok[u]) continue;
+                    v[u] = lo + unit * kUnit + uint64_t(u) * 32 + lane;
+                    if (v[u] < hi) val[u] = mc_ld_reduce<TYPE, OP>(mc_in + v[u]);
+                }
+#pragma unroll
+                for (int u = 0; u < U; ++u) {
+                    if (v[u] >= hi) continue;
                     if (a.avg_divisor) val[u] = scale_packet<TYPE>(val[u], div);
                     mc_store(mc_out + v[u], val[u]);
-                    if (a.hash_out) digest.add(v[u], val[u], a.count * ESZ);
                 }
-            });
+            }
+            stamp(a, 3);
+            if (!rank_barrier(a, tbl, a.flag_base + 2)) return;
+            stamp(a, 4);
+            stamp(a, 5);
+            return; // dynamic scheduling is only used for symmetric operands: nothing to copy out
         }
+        for_owned_packets<U>(lo, hi, [&](const uint64_t(&v)[U], const bool(&ok)[U]) {
+            uint4 val[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u)
+                if (ok[u]) val[u] = mc_ld_reduce<TYPE, OP>(mc_in + v[u]);
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                if (!ok[u]) continue;
+                if (a.avg_divisor) val[u] = scale_packet<TYPE>(val[u], div);
+                mc_store(mc_out + v[u], val[u]);
+                if (a.hash_out) digest.add(v[u], val[u], a.count * ESZ);
+            }
+        });
         stamp(a, 3);
         if (a.hash_out) digest_publish(a, tbl, digest.block_total());
         if (a.commit_before_write) { // in place on an ordinary buffer: all blocks of this rank write the output, or none
@@ -477,13 +507,17 @@ extern "C" int pcclKernelAllReduceNvls(const pcclKernelNvlsArgs_t *args, void *s
     const uint64_t n_pack = (p.count * esz + 15) / 16;
     const uint64_t tiles = (n_pack + kNvlsThreads - 1) / kNvlsThreads;
     const int grid = grid_for(p, (tiles + p.world - 1) / p.world);
+    // dynamic work distribution pays off once every block has many units to balance with; symmetric operands only (a staged
+    // input would need a barrier over all blocks before the reduction as well); bit 9 of `algorithm` switches it off
+    d.dynamic = d.src_in_arena && d.dst_in_arena && !d.hash_out && (p.algorithm & 0x200) == 0 &&
+                (tiles + p.world - 1) / p.world >= uint64_t(grid) * 8;
     const auto stream = static_cast<cudaStream_t>(stream_v);
     const int op = p.op == pcclMax ? OP_MAX : (p.op == pcclMin ? OP_MIN : OP_SUM);
     // p.algorithm selects a tuning variant: packets kept in flight per thread (default 4; 2 -> 8; 5 -> 16)
     auto launch = [&](auto type_tag, auto op_tag) {
         constexpr int TYPE = decltype(type_tag)::value;
         constexpr int OPV = decltype(op_tag)::value;
-        switch (p.algorithm) {
+        switch (p.algorithm & 0xff) {
         case 2: run_rank<NvlsAllReduce<TYPE, OPV, 8>><<<grid, kNvlsThreads, 0, stream>>>(d); break;
         case 5: run_rank<NvlsAllReduce<TYPE, OPV, 16>><<<grid, kNvlsThreads, 0, stream>>>(d); break;
         default: run_rank<NvlsAllReduce<TYPE, OPV, 4>><<<grid, kNvlsThreads, 0, stream>>>(d); break;

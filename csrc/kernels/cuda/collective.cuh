@@ -41,6 +41,8 @@ struct DevArgs {
     int src_in_arena;     // the input already is arena[rank] + data_offset (symmetric memory)
     int dst_in_arena;     // the output IS arena[rank] + red_offset (symmetric memory): no second store
     int trailing_barrier; // close with a barrier (nobody may reuse peer-visible memory a peer still reads)
+    int fence_system;     // barriers start with a block-wide system fence (tuning/diagnosis; the release stores suffice)
+    int dynamic;          // NVLS: warps take work units from a shared counter instead of a static tile assignment
     int commit_before_write; // the output aliases the (staged) input: write it only once every block of this rank knows
                              // that the reduction completed everywhere, so a failed operation leaves the input intact
     volatile uint32_t *abort_flag;
@@ -102,7 +104,12 @@ __device__ __forceinline__ unsigned long long ld_acquire_gpu_u64(const unsigned 
 template <bool FENCE_SYSTEM = false> __device__ bool peer_barrier(const DevArgs &a, const PeerTable &t, uint64_t value, bool record_failure = true) {
     __shared__ int s_fail;
     if (threadIdx.x == 0) s_fail = 0;
-    if constexpr (FENCE_SYSTEM) __threadfence_system();
+    // Stores of this block (plain or multimem) become visible to a peer that acquires the flag through the release stores
+    // below, which are cumulative over everything the block barrier orders before them.  A fence by every thread costs
+    // ~10 us per barrier on B200 and is only kept as a diagnostic switch.
+    if constexpr (FENCE_SYSTEM) {
+        if (a.fence_system) __threadfence_system();
+    }
     __syncthreads(); // this block's earlier writes are ordered before the flag stores below
     if (threadIdx.x < a.world) {
         const uint32_t peer = threadIdx.x;
@@ -127,6 +134,67 @@ template <bool FENCE_SYSTEM = false> __device__ bool peer_barrier(const DevArgs 
     const int fail = s_fail;
     if (fail != 0 && record_failure && threadIdx.x == 0) atomicMax(a.status, static_cast<uint32_t>(fail));
     return fail == 0;
+}
+
+// Barrier among ALL blocks of ALL ranks (the per-block barrier above only ties same-numbered blocks together): every
+// block arrives at a counter in its own rank's control page; the last one raises this rank's flag in line 0 of every
+// arena; everybody waits for all ranks' flags there.  Used where work is handed out dynamically, so that any block may
+// have produced what any other block consumes next.  words[2] = (serial << 32) | arrivals.
+static __device__ bool rank_barrier(const DevArgs &a, const PeerTable &t, uint64_t value) {
+    __shared__ int s_last, s_fail;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        s_fail = 0;
+        __threadfence_system(); // one thread: cumulative over the block's stores, multimem included
+        auto *word = reinterpret_cast<unsigned long long *>(t.arena[a.rank] + kGridSyncOffset + a.flag_slot * kGridSyncStride) + 2;
+        const unsigned long long mine = static_cast<unsigned long long>(a.serial) << 32;
+        unsigned long long old = ld_acquire_gpu_u64(word), now;
+        for (;;) {
+            now = (old >> 32) == a.serial ? old + 1 : (mine | 1ull);
+            const unsigned long long seen = atomicCAS(word, old, now);
+            if (seen == old) break;
+            old = seen;
+        }
+        s_last = (now & 0xffffffffull) == gridDim.x;
+    }
+    __syncthreads();
+    if (threadIdx.x < a.world) {
+        const uint32_t peer = threadIdx.x;
+        if (s_last) st_flag_release(flag_ptr(a, t.arena[peer], 0, a.rank), value);
+        const uint64_t *mine = flag_ptr(a, t.arena[a.rank], 0, peer);
+        const long long t0 = clock64();
+        uint32_t spins = 0;
+        while (ld_flag_acquire(mine) < value) {
+            if ((++spins & 0x3ffu) == 0) {
+                if (*a.abort_flag != 0) {
+                    atomicExch(&s_fail, 1);
+                    break;
+                }
+                if (static_cast<uint64_t>(clock64() - t0) > a.timeout_cycles) {
+                    atomicExch(&s_fail, 2);
+                    break;
+                }
+            }
+        }
+    }
+    __syncthreads();
+    const int fail = s_fail;
+    if (fail != 0 && threadIdx.x == 0) atomicMax(a.status, static_cast<uint32_t>(fail));
+    return fail == 0;
+}
+
+// Work counter for dynamically scheduled phases: returns the first of `n` units claimed for the caller.
+// words[3] = (serial << 32) | next unit.
+static __device__ __forceinline__ unsigned long long claim_units(const DevArgs &a, uint8_t *my_arena, uint32_t n) {
+    auto *word = reinterpret_cast<unsigned long long *>(my_arena + kGridSyncOffset + a.flag_slot * kGridSyncStride) + 3;
+    const unsigned long long mine = static_cast<unsigned long long>(a.serial) << 32;
+    unsigned long long old = *reinterpret_cast<volatile unsigned long long *>(word);
+    for (;;) {
+        const unsigned long long base = (old >> 32) == a.serial ? (old & 0xffffffffull) : 0ull;
+        const unsigned long long seen = atomicCAS(word, old, mine | (base + n));
+        if (seen == old) return base;
+        old = seen;
+    }
 }
 
 // Per-rank, grid-wide agreement: returns true in EVERY block of this rank's grid iff every block called with
@@ -259,6 +327,7 @@ inline bool fill_dev_args(const pcclKernelP2PArgs_t &p, DevArgs &d) {
     d.src_in_arena = p.src_in_arena;
     d.dst_in_arena = p.dst_in_arena;
     d.trailing_barrier = p.no_trailing_barrier ? 0 : 1;
+    d.fence_system = (p.algorithm & 0x100) ? 1 : 0;
     d.commit_before_write = (!p.src_in_arena && !p.dst_in_arena && p.src == p.dst && p.src != nullptr) ? 1 : 0;
     d.abort_flag = p.abort_flag;
     d.status = p.status;

@@ -446,7 +446,22 @@ class Communicator:
         operation needs no vote at the master (every operation on a tag after the first one, until membership changes);
         a failure then surfaces at the next stream-ordered call or at ext_wait_stream_ops()."""
         on_device = torch is not None and isinstance(send, torch.Tensor) and send.is_cuda
-        sp, rp, desc = self._descriptor(send, recv, op, tag, operand_descriptor, quantization_options, sync_stream=not on_device)
+        if on_device and operand_descriptor is None and type(recv) is type(send):
+            # hot path (small stream-ordered reductions are host-bound): no intermediate descriptor objects
+            if not (send.is_contiguous() and recv.is_contiguous()):
+                raise ValueError("tensor must be contiguous")
+            assert send.numel() == recv.numel() and send.dtype == recv.dtype and recv.is_cuda, "send and recv must match"
+            q = quantization_options
+            key = (send.dtype, op, tag, None if q is None else (q.quantized_datatype, q.algorithm))
+            cache = self.__dict__.setdefault("_desc_cache", {})
+            desc = cache.get(key)
+            if desc is None:
+                desc = ReduceDescriptor(0, op, tag, ReduceOperandDescriptor(DataType.from_torch_dtype(send.dtype)), q).to_c()
+                cache[key] = desc
+            desc.count = send.numel()
+            sp, rp = send.data_ptr(), recv.data_ptr()
+        else:
+            sp, rp, desc = self._descriptor(send, recv, op, tag, operand_descriptor, quantization_options, sync_stream=not on_device)
         info = _lib.ReduceInfoC()
         if on_device:
             handle = (stream if stream is not None else torch.cuda.current_stream(send.device)).cuda_stream
