@@ -508,10 +508,14 @@ extern "C" int pcclKernelAllReduceNvls(const pcclKernelNvlsArgs_t *args, void *s
     const uint64_t tiles = (n_pack + kNvlsThreads - 1) / kNvlsThreads;
     const int grid = grid_for(p, (tiles + p.world - 1) / p.world);
     // dynamic work distribution pays off once every block has many units to balance with; symmetric operands only (a staged
-    // input would need a barrier over all blocks before the reduction as well); bit 9 of `algorithm` switches it off
-    d.dynamic = d.src_in_arena && d.dst_in_arena && !d.hash_out && (p.algorithm & 0x200) == 0 &&
+    // input would need a barrier over all blocks before the reduction as well); bit 9 of `algorithm` switches it on (measured before it becomes the default)
+    d.dynamic = d.src_in_arena && d.dst_in_arena && !d.hash_out && (p.algorithm & 0x200) != 0 &&
                 (tiles + p.world - 1) / p.world >= uint64_t(grid) * 8;
     const auto stream = static_cast<cudaStream_t>(stream_v);
+    if (d.dynamic) {
+        const cudaError_t rc = cudaMemsetAsync(d.arena[d.rank] + claim_word_offset(d.flag_slot), 0, sizeof(unsigned long long), stream);
+        if (rc != cudaSuccess) return rc;
+    }
     const int op = p.op == pcclMax ? OP_MAX : (p.op == pcclMin ? OP_MIN : OP_SUM);
     // p.algorithm selects a tuning variant: packets kept in flight per thread (default 4; 2 -> 8; 5 -> 16)
     auto launch = [&](auto type_tag, auto op_tag) {

@@ -183,19 +183,13 @@ static __device__ bool rank_barrier(const DevArgs &a, const PeerTable &t, uint64
     return fail == 0;
 }
 
-// Work counter for dynamically scheduled phases: returns the first of `n` units claimed for the caller.
-// words[3] = (serial << 32) | next unit.
+// Work counter for dynamically scheduled phases (words[3], zeroed on the stream by the launcher before the kernel):
+// returns the first of `n` units claimed for the caller.
 static __device__ __forceinline__ unsigned long long claim_units(const DevArgs &a, uint8_t *my_arena, uint32_t n) {
     auto *word = reinterpret_cast<unsigned long long *>(my_arena + kGridSyncOffset + a.flag_slot * kGridSyncStride) + 3;
-    const unsigned long long mine = static_cast<unsigned long long>(a.serial) << 32;
-    unsigned long long old = *reinterpret_cast<volatile unsigned long long *>(word);
-    for (;;) {
-        const unsigned long long base = (old >> 32) == a.serial ? (old & 0xffffffffull) : 0ull;
-        const unsigned long long seen = atomicCAS(word, old, mine | (base + n));
-        if (seen == old) return base;
-        old = seen;
-    }
+    return atomicAdd(word, static_cast<unsigned long long>(n));
 }
+inline size_t claim_word_offset(uint32_t flag_slot) { return kGridSyncOffset + size_t(flag_slot) * kGridSyncStride + 24; }
 
 // Per-rank, grid-wide agreement: returns true in EVERY block of this rank's grid iff every block called with
 // ok == true; otherwise false everywhere.  Used where a kernel is about to write memory the caller owns and must

@@ -32,8 +32,8 @@ sizes = [int(a) for a in sys.argv[1:]] or [1 << 20, 1 << 24, 1 << 26, 600_000_00
 sym = comm.ext_symmetric_empty(max(sizes) // 4, torch.float32)
 sym.normal_()
 # (label, PCCL_DEVICE_VARIANT, PCCL_DEVICE_MAX_BLOCKS)
-configs = [("dyn_u4", 0, 0), ("static_u4", 0x200, 0), ("dyn_u8", 2, 0), ("static_u8", 0x202, 0), ("dyn_u16", 5, 0),
-           ("static_u4_fence", 0x300, 0), ("dyn_u8_b72", 2, 72), ("dyn_u8_b148", 2, 148), ("dyn_u4_b148", 0, 148)]
+configs = [("static_u4", 0, 0), ("dyn_u4", 0x200, 0), ("dyn_u8", 0x202, 0), ("dyn_u16", 0x205, 0), ("dyn_u8_b72", 0x202, 72),
+           ("dyn_u8_b148", 0x202, 148), ("static_u4_b148", 0, 148)]
 for nbytes in sizes:
     x = sym[:nbytes // 4]
     for label, variant, blocks in configs:
