@@ -17,6 +17,7 @@
 // of the NEXT operation, which this rank enters after its copy-out.
 #include <cmath>
 
+#include "bulk_copy.cuh"
 #include "collective.cuh"
 #include "hash_mset.cuh"
 #include "outer_step.cuh"
@@ -125,9 +126,14 @@ template <int TYPE, int OP, int U> struct NvlsAllReduce {
         uint4 *mc_out = reinterpret_cast<uint4 *>(a.mc + a.red_offset);
         const uint64_t full_packets = a.count / N; // packets completely inside the user buffers
         const bool aligned = ((reinterpret_cast<uintptr_t>(src) | reinterpret_cast<uintptr_t>(dst)) & 15) == 0;
+        extern __shared__ __align__(128) uint8_t dyn_smem[];
+        BulkRing ring;
+        if (a.bulk) bulk_ring_init(ring, dyn_smem, 0);
         stamp(a, 0);
 
-        if (!a.src_in_arena) {
+        if (!a.src_in_arena && a.bulk) {
+            bulk_copy_owned_tiles(ring, reinterpret_cast<uint8_t *>(mine), src, 0, n_pack, 0);
+        } else if (!a.src_in_arena) {
             for_owned_packets<4>(0, n_pack, [&](const uint64_t(&v)[4], const bool(&ok)[4]) {
                 uint4 tmp[4];
 #pragma unroll
@@ -210,7 +216,10 @@ template <int TYPE, int OP, int U> struct NvlsAllReduce {
         if (a.hash_out) digest_collect(a, tbl, a.hash_out);
         stamp(a, 4);
 
-        if (!a.dst_in_arena) {
+        if (!a.dst_in_arena && a.bulk) {
+            // (the bulk engine reads through L2, where the switch delivered the result; nothing stale in L1 to worry about)
+            bulk_copy_owned_tiles(ring, dst, reinterpret_cast<const uint8_t *>(mine_red), 0, n_pack, 0);
+        } else if (!a.dst_in_arena) {
             for_owned_packets<4>(0, n_pack, [&](const uint64_t(&v)[4], const bool(&ok)[4]) {
                 uint4 tmp[4];
 #pragma unroll
@@ -370,10 +379,24 @@ template <int TYPE, int OP, bool OUTER> struct NvlsPipelined {
         const uint64_t per = seg_pack / a.world; // the launcher makes segments a multiple of world * tile
         const uint32_t last_iter = OUTER ? n_seg : n_seg + 1;
         MsetAcc digest;
+        extern __shared__ __align__(128) uint8_t dyn_smem[];
+        BulkRing ring;
+        const bool bulk = a.bulk && !OUTER && !a.hash_out;
+        if (bulk) bulk_ring_init(ring, dyn_smem, 0);
         stamp(a, 0);
 
         for (uint32_t i = 0; i <= last_iter; ++i) {
-            if (memory_group) {
+            if (memory_group && bulk) {
+                // thread 0 of the memory group drives the copy engine: segment i in, segment i-2 out
+                if (i < n_seg) {
+                    const uint64_t lo = min(uint64_t(i) * seg_pack, n_pack), hi = min(lo + seg_pack, n_pack);
+                    bulk_copy_owned_tiles(ring, reinterpret_cast<uint8_t *>(mine), src, lo, hi, 0);
+                }
+                if (i >= 2) {
+                    const uint64_t lo = min(uint64_t(i - 2) * seg_pack, n_pack), hi = min(lo + seg_pack, n_pack);
+                    bulk_copy_owned_tiles(ring, dst, reinterpret_cast<const uint8_t *>(mine), lo, hi, 0);
+                }
+            } else if (memory_group) {
                 if (i < n_seg) { // A: stage segment i
                     const uint64_t lo = min(uint64_t(i) * seg_pack, n_pack), hi = min(lo + seg_pack, n_pack);
                     nvls_group_packets<4>(lo, hi, gtid, [&](const uint64_t(&v)[4], const bool(&ok)[4]) {
@@ -521,10 +544,16 @@ extern "C" int pcclKernelAllReduceNvls(const pcclKernelNvlsArgs_t *args, void *s
     auto launch = [&](auto type_tag, auto op_tag) {
         constexpr int TYPE = decltype(type_tag)::value;
         constexpr int OPV = decltype(op_tag)::value;
+        auto go = [&](auto body) {
+            using Body = decltype(body);
+            const size_t smem = bulk_smem_for(run_rank<Body>, d);
+            if (smem == 0) d.bulk = 0;
+            run_rank<Body><<<grid, kNvlsThreads, smem, stream>>>(d);
+        };
         switch (p.algorithm & 0xff) {
-        case 2: run_rank<NvlsAllReduce<TYPE, OPV, 8>><<<grid, kNvlsThreads, 0, stream>>>(d); break;
-        case 5: run_rank<NvlsAllReduce<TYPE, OPV, 16>><<<grid, kNvlsThreads, 0, stream>>>(d); break;
-        default: run_rank<NvlsAllReduce<TYPE, OPV, 4>><<<grid, kNvlsThreads, 0, stream>>>(d); break;
+        case 2: go(NvlsAllReduce<TYPE, OPV, 8>{}); break;
+        case 5: go(NvlsAllReduce<TYPE, OPV, 16>{}); break;
+        default: go(NvlsAllReduce<TYPE, OPV, 4>{}); break;
         }
     };
     using std::integral_constant;
@@ -553,7 +582,8 @@ extern "C" int pcclKernelOuterStepNvls(const pcclKernelNvlsArgs_t *args, const p
     const uint64_t n_pack = (p.count + 3) / 4;
     const uint64_t tiles = (n_pack + kNvlsThreads - 1) / kNvlsThreads;
     const int grid = grid_for(p, (tiles + p.world - 1) / p.world);
-    run_rank<NvlsOuter, OuterStepDev><<<grid, kNvlsThreads, 0, static_cast<cudaStream_t>(stream_v)>>>(d, s);
+    d.bulk = 0;
+    run_rank1<NvlsOuter, OuterStepDev><<<grid, kNvlsThreads, 0, static_cast<cudaStream_t>(stream_v)>>>(d, s);
     return cudaGetLastError();
 }
 
@@ -594,7 +624,9 @@ extern "C" int pcclKernelAllReduceNvlsPipelined(const pcclKernelNvlsArgs_t *args
     const int op = rop == pcclMax ? OP_MAX : (rop == pcclMin ? OP_MIN : OP_SUM);
     auto go = [&](auto body) {
         using Body = decltype(body);
-        run_rank<Body, OuterStepDev, PipelineGeometry><<<grid, kNvlsThreads, 0, stream>>>(d, s, geo);
+        const size_t smem = bulk_smem_for(run_rank2<Body, OuterStepDev, PipelineGeometry>, d);
+        if (smem == 0) d.bulk = 0;
+        run_rank2<Body, OuterStepDev, PipelineGeometry><<<grid, kNvlsThreads, smem, stream>>>(d, s, geo);
     };
     if (step) {
         go(NvlsPipelined<NV_F32, OP_SUM, true>{});

@@ -34,6 +34,7 @@
 #include <tuple>
 #include <type_traits>
 
+#include "bulk_copy.cuh"
 #include "collective.cuh"
 #include "hash_mset.cuh"
 #include "outer_step.cuh"
@@ -111,10 +112,15 @@ template <typename T, int OP> struct TwoShot {
         uint4 *mine = reinterpret_cast<uint4 *>(tbl.base[a.rank]);
         uint4 *mine_red = reinterpret_cast<uint4 *>(tbl.red[a.rank]);
         MsetAcc digest;
+        extern __shared__ __align__(128) uint8_t dyn_smem[];
+        BulkRing ring;
+        if (a.bulk) bulk_ring_init(ring, dyn_smem, 0);
         stamp(a, 0);
 
         // phase 0: stage the input where the peers can read it
-        if (!a.src_in_arena) {
+        if (!a.src_in_arena && a.bulk) {
+            bulk_copy_owned_tiles(ring, reinterpret_cast<uint8_t *>(mine), static_cast<const uint8_t *>(a.src), 0, n_pack, 0);
+        } else if (!a.src_in_arena) {
             for_owned_packets<4>(0, n_pack, [&](const uint64_t(&v)[4], const bool(&ok)[4]) {
                 uint4 tmp[4];
 #pragma unroll
@@ -552,7 +558,16 @@ namespace {
 template <typename Body, typename... Extra>
 int launch_body(const DevArgs *ranks, int n_ranks, bool emulated, int grid, cudaStream_t stream, const Extra *...extra) {
     if (!emulated) {
-        run_rank<Body, Extra...><<<grid, kThreads, 0, stream>>>(ranks[0], extra[0]...);
+        DevArgs d = ranks[0];
+        if constexpr (sizeof...(Extra) == 0) {
+            const size_t smem = bulk_smem_for(run_rank<Body>, d);
+            if (smem == 0) d.bulk = 0;
+            run_rank<Body><<<grid, kThreads, smem, stream>>>(d);
+        } else {
+            const size_t smem = bulk_smem_for(run_rank1<Body, Extra...>, d);
+            if (smem == 0) d.bulk = 0;
+            run_rank1<Body, Extra...><<<grid, kThreads, smem, stream>>>(d, extra[0]...);
+        }
         return cudaGetLastError();
     }
     DevArgs *d_ranks = nullptr;
@@ -565,7 +580,12 @@ int launch_body(const DevArgs *ranks, int n_ranks, bool emulated, int grid, cuda
         rc = cudaMalloc(&dev, sizeof(E) * n_ranks);
         if (rc == cudaSuccess) rc = cudaMemcpyAsync(dev, host, sizeof(E) * n_ranks, cudaMemcpyHostToDevice, stream);
     };
-    rc = cudaMemcpyAsync(d_ranks, ranks, sizeof(DevArgs) * n_ranks, cudaMemcpyHostToDevice, stream);
+    DevArgs no_bulk[PCCL_K_MAX_RANKS]; // the emulated (test) launch keeps the register copy loops
+    for (int i = 0; i < n_ranks; ++i) {
+        no_bulk[i] = ranks[i];
+        no_bulk[i].bulk = 0;
+    }
+    rc = cudaMemcpyAsync(d_ranks, no_bulk, sizeof(DevArgs) * n_ranks, cudaMemcpyHostToDevice, stream);
     std::apply([&](auto *&...dev) { (upload(dev, extra), ...); }, d_extra);
     if (rc == cudaSuccess) {
         std::apply(
@@ -672,6 +692,7 @@ int launch_outer_step(const pcclKernelP2PArgs_t *ranks, const pcclKernelOuterSte
         d[i].red_offset = d[i].data_offset;
         d[i].src_in_arena = d[i].dst_in_arena = 0;
         if (emulated) d[i].serial = d[0].serial;
+        d[i].bulk = 0; // the outer step's staging and update passes do arithmetic; no pure copy in it
         s[i] = make_outer_step_dev(step);
     }
     const uint64_t n_pack = (ranks[0].count + 3) / 4;

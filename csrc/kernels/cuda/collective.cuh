@@ -9,6 +9,7 @@
 // operation can never satisfy a later wait.
 #pragma once
 #include <atomic>
+#include <cstdlib>
 
 #include "common.cuh"
 #include "pccl_kernels.h"
@@ -42,6 +43,7 @@ struct DevArgs {
     int dst_in_arena;     // the output IS arena[rank] + red_offset (symmetric memory): no second store
     int trailing_barrier; // close with a barrier (nobody may reuse peer-visible memory a peer still reads)
     int fence_system;     // barriers start with a block-wide system fence (tuning/diagnosis; the release stores suffice)
+    int bulk;             // pure copy phases use the bulk asynchronous copy engine (bulk_copy.cuh); needs its dynamic shared memory
     int dynamic;          // NVLS: warps take work units from a shared counter instead of a static tile assignment
     int commit_before_write; // the output aliases the (staged) input: write it only once every block of this rank knows
                              // that the reduction completed everywhere, so a failed operation leaves the input intact
@@ -267,8 +269,12 @@ __device__ __forceinline__ void digest_collect(const DevArgs &a, const PeerTable
 // launch, ranks on different GPUs) and into the emulated form used by single-GPU tests: ONE cooperative launch whose
 // grid is (blocks, ranks), every y-slice playing one rank on its own arena.  (Ranks that wait for each other must
 // never be separate launches on one GPU -- nothing guarantees that they run at the same time.)
-template <typename Body, typename... Extra> __global__ void __launch_bounds__(kThreads, 1) run_rank(const DevArgs a, const Extra... extra) {
-    Body::run(a, extra...);
+// (fixed arities instead of a parameter pack: the address of a kernel is needed for cudaFuncSetAttribute, and a
+// specialisation whose trailing pack could still grow has no unique address)
+template <typename Body> __global__ void __launch_bounds__(kThreads, 1) run_rank(const DevArgs a) { Body::run(a); }
+template <typename Body, typename E1> __global__ void __launch_bounds__(kThreads, 1) run_rank1(const DevArgs a, const E1 e1) { Body::run(a, e1); }
+template <typename Body, typename E1, typename E2> __global__ void __launch_bounds__(kThreads, 1) run_rank2(const DevArgs a, const E1 e1, const E2 e2) {
+    Body::run(a, e1, e2);
 }
 template <typename Body, typename... Extra> __global__ void __launch_bounds__(kThreads, 1) run_emulated(const DevArgs *ranks, const Extra *...extra) {
     Body::run(ranks[blockIdx.y], extra[blockIdx.y]...);
@@ -322,6 +328,16 @@ inline bool fill_dev_args(const pcclKernelP2PArgs_t &p, DevArgs &d) {
     d.dst_in_arena = p.dst_in_arena;
     d.trailing_barrier = p.no_trailing_barrier ? 0 : 1;
     d.fence_system = (p.algorithm & 0x100) ? 1 : 0;
+    {
+        // bulk copies move whole 16-byte packets between 16-byte aligned addresses; small operands are latency-bound anyway
+        static const bool enabled = [] {
+            const char *v = std::getenv("PCCL_BULK_COPY");
+            return !(v && v[0] == '0');
+        }();
+        const uint64_t bytes = p.count * pcclExtDataTypeSize(static_cast<pcclDataType_t>(p.dtype));
+        const auto misaligned = (reinterpret_cast<uintptr_t>(p.src) | reinterpret_cast<uintptr_t>(p.dst)) & 15;
+        d.bulk = enabled && (p.algorithm & 0x400) == 0 && !misaligned && bytes % 16 == 0 && bytes >= (1u << 20) && p.quant_algorithm == 0;
+    }
     d.commit_before_write = (!p.src_in_arena && !p.dst_in_arena && p.src == p.dst && p.src != nullptr) ? 1 : 0;
     d.abort_flag = p.abort_flag;
     d.status = p.status;

@@ -232,3 +232,22 @@ def test_fused_outer_step_equals_three_pass():
         torch.testing.assert_close(inner_a, inner_b, rtol=1e-6, atol=1e-7)
         inner_a.sub_(0.01)
         inner_b.sub_(0.01)
+
+
+@pytest.mark.parametrize("n", [262_144, 262_148, 1_000_000, 16_000_004, 37_000_000])
+def test_staging_through_the_bulk_copy_engine(n):
+    """Operands of a megabyte and more are staged with cp.async.bulk (global -> shared -> global) instead of register
+    copies; sizes that end in a partial tile and both SUM and AVG go through it.  World size 1: the result is the input."""
+    dev = torch.device("cuda:0")
+    x = torch.randn(n, device=dev)
+    arena = ops.LocalArena(dev, n * 4)
+    for op in (pccl.ReduceOp.SUM, pccl.ReduceOp.AVG):
+        y = torch.zeros_like(x)
+        assert ops.local_all_reduce(x, y, arena, op=op) == 2
+        torch.cuda.synchronize()
+        assert int(arena.words[1]) == 0
+        assert torch.equal(x, y)
+    # in place as well (the output is written only after the commit point)
+    z = x.clone()
+    ops.local_all_reduce(z, z, arena, op=pccl.ReduceOp.SUM)
+    assert torch.equal(x, z)
