@@ -277,6 +277,20 @@ pcclResult_t pcclExtAllReduceOnStream(const void *sendbuff, void *recvbuff, cons
     return out.ok ? pcclSuccess : pcclRankConnectionLost;
 }
 
+pcclResult_t pcclExtTrustContentHashes(pcclComm_t *c, int on) {
+    PCCL_REQUIRE(c, pcclInvalidArgument);
+    PCCL_REQUIRE(c->client, pcclInvalidUsage);
+    c->client->trust_content_hashes(on != 0);
+    return pcclSuccess;
+}
+
+pcclResult_t pcclExtHashKernelsSkipped(const pcclComm_t *c, uint64_t *count_out) {
+    PCCL_REQUIRE(c && count_out, pcclInvalidArgument);
+    PCCL_REQUIRE(c->client, pcclInvalidUsage);
+    *count_out = c->client->hash_kernels_skipped();
+    return pcclSuccess;
+}
+
 pcclResult_t pcclExtWaitStreamOps(const pcclComm_t *c, uint64_t tag, int all_tags, pcclReduceInfo_t *info_out) {
     PCCL_REQUIRE_INIT();
     PCCL_REQUIRE(c, pcclInvalidArgument);

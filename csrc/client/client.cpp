@@ -8,6 +8,7 @@
 
 #include "../kernels/cpu/hash.hpp"
 #include "../kernels/cpu/reduce.hpp"
+#include "../kernels/mset_formula.hpp"
 #include "../net/sockutil.hpp"
 #include "../util/env.hpp"
 #include "../util/log.hpp"
@@ -565,6 +566,10 @@ bool Client::sync_shared_state(SharedStateArgs &state, uint64_t &tx_bytes, uint6
         return HashType::Simple;
     }();
     auto hash_of = [&](const SharedEntry &e, uint64_t &out) {
+        if (hash_type == HashType::Mset64 && trust_hashes_ && recall_hash(e.data, e.bytes(), out)) {
+            ++hash_skips_; // the kernel that last wrote this tensor hashed it on the way
+            return true;
+        }
         if (e.on_device) return plane_->hash_device(e.data, e.bytes(), hash_type, out);
         out = hash_type == HashType::Simple  ? cpu::simplehash(e.data, e.bytes())
               : hash_type == HashType::Crc32 ? cpu::crc32c(e.data, e.bytes())
@@ -683,6 +688,7 @@ bool Client::sync_shared_state(SharedStateArgs &state, uint64_t &tx_bytes, uint6
                 }
             }
             rx_bytes += slice.size_bytes;
+            forget_hashes(it->data, it->bytes());
             // verify what arrived against what the master elected
             if (!it->allow_content_inequality && i < verdict->expected_hashes.size()) {
                 uint64_t h = 0;
@@ -704,6 +710,31 @@ bool Client::sync_shared_state(SharedStateArgs &state, uint64_t &tx_bytes, uint6
 // ------------------------------------------------------------------------------------------
 // all-reduce
 // ------------------------------------------------------------------------------------------
+
+void Client::remember_hash(const void *ptr, size_t bytes, uint64_t value) {
+    std::lock_guard<std::mutex> lock(hash_mu_);
+    known_hashes_[reinterpret_cast<uintptr_t>(ptr)] = KnownHash{bytes, value};
+    if (known_hashes_.size() > 4096) known_hashes_.erase(known_hashes_.begin());
+}
+
+void Client::forget_hashes(const void *ptr, size_t bytes) {
+    const auto lo = reinterpret_cast<uintptr_t>(ptr), hi = lo + bytes;
+    std::lock_guard<std::mutex> lock(hash_mu_);
+    for (auto it = known_hashes_.begin(); it != known_hashes_.end();) {
+        if (it->first < hi && it->first + it->second.bytes > lo)
+            it = known_hashes_.erase(it);
+        else
+            ++it;
+    }
+}
+
+bool Client::recall_hash(const void *ptr, size_t bytes, uint64_t &value) {
+    std::lock_guard<std::mutex> lock(hash_mu_);
+    const auto it = known_hashes_.find(reinterpret_cast<uintptr_t>(ptr));
+    if (it == known_hashes_.end() || it->second.bytes != bytes) return false;
+    value = it->second.value;
+    return true;
+}
 
 bool Client::any_reduce_running() {
     std::lock_guard<std::mutex> lock(ops_mu_);
@@ -936,7 +967,29 @@ uint8_t *Client::staging_for(uint64_t tag, size_t bytes) {
     return b.ptr;
 }
 
-ReduceOutcome Client::run_reduce(const ReduceRequest &req, uint64_t) {
+ReduceOutcome Client::run_reduce(const ReduceRequest &req, uint64_t revision_at_launch) {
+    ReduceOutcome out = run_reduce_impl(req, revision_at_launch);
+    if (out.ok && !out.pending && out.has_hash) {
+        // the kernel hashed what it wrote: the next shared-state synchronisation can use it (see trust_content_hashes)
+        if (req.outer) {
+            const size_t bytes = req.count * sizeof(float);
+            const uint64_t hp = mset::finalize(out.hash[0], bytes), hm = mset::finalize(out.hash[1], bytes);
+            remember_hash(req.outer->params, bytes, hp);
+            remember_hash(req.outer->momentum, bytes, hm);
+            if (req.outer->inner) remember_hash(req.outer->inner, bytes, hp); // inner receives the new parameters
+            out.stats.content_hash[0] = hp;
+            out.stats.content_hash[1] = hm;
+        } else {
+            const size_t bytes = req.count * dtype_size(req.dtype);
+            out.stats.content_hash[0] = mset::finalize(out.hash[0], bytes);
+            remember_hash(req.recv, bytes, out.stats.content_hash[0]);
+        }
+        out.stats.has_content_hash = 1;
+    }
+    return out;
+}
+
+ReduceOutcome Client::run_reduce_impl(const ReduceRequest &req, uint64_t) {
     ReduceOutcome out;
     const size_t esz = dtype_size(req.dtype);
     // Buffers of the reduction proper.  For an outer step they are either unused (fused kernel) or a scratch
@@ -945,6 +998,14 @@ ReduceOutcome Client::run_reduce(const ReduceRequest &req, uint64_t) {
     void *recv = req.outer ? req.outer->params : req.recv;
     const auto send_info = device::classify_pointer(send), recv_info = device::classify_pointer(recv);
 
+    // whatever this operation writes no longer has a known content hash
+    if (req.outer) {
+        forget_hashes(req.outer->params, req.count * sizeof(float));
+        forget_hashes(req.outer->momentum, req.count * sizeof(float));
+        if (req.outer->inner) forget_hashes(req.outer->inner, req.count * sizeof(float));
+    } else {
+        forget_hashes(req.recv, req.count * esz);
+    }
     std::vector<Uuid> ring;
     {
         std::shared_lock<std::shared_mutex> lock(ring_mu_);
@@ -967,7 +1028,7 @@ ReduceOutcome Client::run_reduce(const ReduceRequest &req, uint64_t) {
     dargs.world = world;
     dargs.outer = req.outer;
     dargs.user_stream = req.user_stream;
-    dargs.want_hash = req.want_hash;
+    dargs.want_hash = req.want_hash || (trust_hashes_ && req.outer != nullptr);
     uint32_t caps = send_info.is_device && recv_info.is_device ? plane_->capabilities(dargs) : 0;
     // Outer step that cannot run as one kernel (host tensors, no device plane, larger than a staging slot): the
     // pseudo-gradient goes to a scratch buffer now, the scratch buffer is reduced like any tensor, and the
@@ -977,6 +1038,7 @@ ReduceOutcome Client::run_reduce(const ReduceRequest &req, uint64_t) {
     std::unique_lock<std::mutex> scratch_lock;
     if (outer_two_pass) {
         dargs.outer = nullptr;
+        dargs.want_hash = false; // the reduction's result is the averaged pseudo-gradient, not a tensor anybody synchronises
         float *scratch = nullptr;
         if (send_info.is_device) {
             scratch_lock = plane_->fuse_lock();

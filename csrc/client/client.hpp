@@ -117,6 +117,16 @@ public:
     bool any_reduce_running();
     bool last_stats(uint64_t tag, pcclExtReduceStats_t &out);
 
+    // Content hashes the collective kernels produced while writing a tensor (mset64).  With trust switched on, a shared-state
+    // synchronisation that uses the mset64 hash type takes a tensor's hash from here instead of launching a hash kernel --
+    // valid as long as nothing but this library wrote the tensor since (the caller's promise when switching it on).
+    void trust_content_hashes(bool on) { trust_hashes_ = on; }
+    bool trusts_content_hashes() const { return trust_hashes_; }
+    void remember_hash(const void *ptr, size_t bytes, uint64_t value);
+    void forget_hashes(const void *ptr, size_t bytes); // anything overlapping [ptr, ptr+bytes)
+    bool recall_hash(const void *ptr, size_t bytes, uint64_t &value);
+    uint64_t hash_kernels_skipped() const { return hash_skips_; }
+
     uint64_t global_world() const { return global_world_; }
     // ports this peer listens on (after connect()): p2p, shared state, bandwidth benchmark
     uint16_t p2p_port() const { return p2p_listener_.port(); }
@@ -139,6 +149,7 @@ private:
     void on_shared_state_accept(std::unique_ptr<net::BlockingSocket> sock);
     void on_benchmark_accept(std::unique_ptr<net::BlockingSocket> sock);
     ReduceOutcome run_reduce(const ReduceRequest &req, uint64_t revision_at_launch);
+    ReduceOutcome run_reduce_impl(const ReduceRequest &req, uint64_t revision_at_launch);
     bool conclude(uint64_t tag, uint64_t revision_at_launch, ReduceOutcome &out);
     struct StreamOp;
     bool finish_stream_op(uint64_t tag, const StreamOp &so, ReduceOutcome &out);
@@ -205,6 +216,15 @@ private:
     std::map<uint64_t, Op> ops_;
     std::map<uint64_t, pcclExtReduceStats_t> stats_;
     std::unique_ptr<ThreadPool> workers_;
+
+    struct KnownHash {
+        size_t bytes;
+        uint64_t value;
+    };
+    std::mutex hash_mu_;
+    std::map<uintptr_t, KnownHash> known_hashes_;
+    std::atomic<bool> trust_hashes_{false};
+    std::atomic<uint64_t> hash_skips_{0};
 
     // shared-state serving
     std::mutex ss_mu_;

@@ -338,6 +338,8 @@ typedef struct pcclExtReduceStats_t {
     uint64_t phase_ns[8]; /* device plane: GPU global timer (ns) when block 0 of the (last) kernel reached its phase boundaries:
                              [0] start, [1] input staged, [2] first barrier passed, [3] own chunk reduced, [4] second barrier
                              passed, [5] output written, [6] closing barrier passed; 0 = phase not present */
+    uint32_t has_content_hash; /* 1: the kernel produced the mset64 content hash of what it wrote as a by-product */
+    uint64_t content_hash[2];  /* all-reduce: [0] hash of the result; outer step: [0] new parameters, [1] new momentum */
 } pcclExtReduceStats_t;
 
 /* Stats of the most recently completed reduction with the given tag. */
@@ -388,6 +390,15 @@ PCCL_EXPORT pcclResult_t pcclExtAllReduceOnStream(const void *sendbuff, void *re
 /* Takes the verdict of the enqueued operation on `tag` (of all tags when all_tags != 0); blocks until it has finished. */
 PCCL_EXPORT pcclResult_t pcclExtWaitStreamOps(const pcclComm_t *communicator, uint64_t tag, int all_tags,
                                               pcclReduceInfo_t *reduce_info_out);
+
+/* Content hashes as a by-product (no counterpart in the reference, which hashes every shared-state tensor in a pass of its own
+ * before each synchronisation: ccoip_client_handler.cpp:383-416).  With trust switched on, the fused DiLoCo outer step hashes
+ * the parameters and the momentum buffer while it writes them (hash type mset64, PCCL_SHARED_STATE_HASH=mset), and the next
+ * pcclSynchronizeSharedState takes the hash of a tensor this library wrote last from that record instead of launching a hash
+ * kernel.  The caller promises not to modify such tensors behind the library's back; anything the library itself writes
+ * (reductions, received shared state) drops the record.  pcclExtHashKernelsSkipped counts the hashes that were saved. */
+PCCL_EXPORT pcclResult_t pcclExtTrustContentHashes(pcclComm_t *communicator, int on);
+PCCL_EXPORT pcclResult_t pcclExtHashKernelsSkipped(const pcclComm_t *communicator, uint64_t *count_out);
 
 typedef struct pcclExtOuterStepDescriptor_t {
     void *params;

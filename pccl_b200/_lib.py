@@ -116,7 +116,8 @@ class BuildInfoC(C.Structure):
 
 class ExtReduceStatsC(C.Structure):
     _fields_ = [("plane", C.c_int), ("device_ms", C.c_float), ("seq_nr", C.c_uint64), ("kernel_launches", C.c_uint32),
-                ("leased", C.c_uint32), ("phase_ns", C.c_uint64 * 8)]
+                ("leased", C.c_uint32), ("phase_ns", C.c_uint64 * 8),
+                ("has_content_hash", C.c_uint32), ("content_hash", C.c_uint64 * 2)]
 
 
 class ExtOuterStepDescriptorC(C.Structure):
@@ -202,6 +203,8 @@ def lib() -> C.CDLL:
     sig("pcclDestroyMaster", i32, vp)
     sig("pcclGetBuildInfo", i32, C.POINTER(BuildInfoC))
     sig("pcclExtAllReduceOnStream", i32, vp, vp, C.POINTER(ReduceDescriptorC), vp, vp, i32, C.POINTER(ReduceInfoC))
+    sig("pcclExtTrustContentHashes", i32, vp, i32)
+    sig("pcclExtHashKernelsSkipped", i32, vp, C.POINTER(u64))
     sig("pcclExtWaitStreamOps", i32, vp, u64, i32, C.POINTER(ReduceInfoC))
     sig("pcclExtGetLastReduceStats", i32, vp, u64, C.POINTER(ExtReduceStatsC))
     sig("pcclExtMasterGetPort", i32, vp, C.POINTER(C.c_uint16))

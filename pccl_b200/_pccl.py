@@ -504,7 +504,19 @@ class Communicator:
         names = {0: "none", 1: "tcp_ring", 2: "p2p_one_shot", 3: "p2p_two_shot", 4: "nvls"}
         return {"plane": names.get(st.plane, str(st.plane)), "device_ms": float(st.device_ms), "seq_nr": int(st.seq_nr),
                 "kernel_launches": int(st.kernel_launches), "leased": bool(st.leased),
-                "phase_us": [round((int(st.phase_ns[i]) - int(st.phase_ns[0])) / 1e3, 2) if st.phase_ns[i] else None for i in range(7)]}
+                "phase_us": [round((int(st.phase_ns[i]) - int(st.phase_ns[0])) / 1e3, 2) if st.phase_ns[i] else None for i in range(7)],
+                "content_hash": [int(st.content_hash[0]), int(st.content_hash[1])] if st.has_content_hash else None}
+
+    def ext_trust_content_hashes(self, on: bool = True) -> None:
+        """Lets shared-state synchronisation reuse the content hashes the collective kernels produce while they write a
+        tensor (hash type mset64: set PCCL_SHARED_STATE_HASH=mset on every peer).  You promise not to modify tensors the
+        library wrote last (outer-step parameters and momentum) except through the library."""
+        PCCLError.check(lib().pcclExtTrustContentHashes(self._comm, 1 if on else 0), "pcclExtTrustContentHashes")
+
+    def ext_hash_kernels_skipped(self) -> int:
+        out = C.c_uint64()
+        PCCLError.check(lib().pcclExtHashKernelsSkipped(self._comm, C.byref(out)), "pcclExtHashKernelsSkipped")
+        return int(out.value)
 
     def ext_diloco_outer_step(self, params, inner, momentum, *, lr: float = 0.7, mu: float = 0.9, first: bool = False,
                               tag: int = 0) -> ReduceInfo:

@@ -139,10 +139,19 @@ class DiLoCo:
 
 
 class AsyncDiLoCo:
-    """One-step-delayed ("streaming") DiLoCo: the all-reduce of outer step t runs while the inner
-    phase of step t+1 computes; its result is applied at the end of step t+1.
-    Reference: python/examples/nanogpt_diloco/async_diloco.py:405-640 (reduction on a background thread,
-    `are_peers_pending` gate before `update_topology`)."""
+    """One-step-delayed ("streaming") DiLoCo: the all-reduce of outer step t runs while the inner phase of step t+1
+    computes; its result is applied at the end of step t+1.
+
+    Follows the reference's protocol (python/examples/nanogpt_diloco/async_diloco.py):
+      * membership (:419-431): `admit_peers()` asks `are_peers_pending()`; only when somebody waits is the reduction in
+        flight awaited and `update_topology()` called, followed by an ordinary shared-state synchronisation;
+      * pipeline insertion of a late joiner (:551-580): in the step after a topology change the peers that hold a
+        reduction result apply it and THEN re-send the shared state (SEND_ONLY) while the joiner, which has no result to
+        apply, receives it (RECEIVE_ONLY) -- so the joiner starts its next inner phase from the state that includes the
+        update it could not take part in.
+    Different from the reference: on CUDA tensors nothing goes through the host and no thread is needed -- the reduction
+    is enqueued stream-ordered on a side stream (`all_reduce(..., enqueue=True)`) and overlaps with the inner phase's
+    kernels; the verdict is taken when the next outer step needs the result."""
 
     def __init__(self, comm: Communicator, params: torch.Tensor, lr: float = 0.7, momentum: float = 0.9,
                  quantization: Optional[QuantizationOptions] = None):
@@ -153,56 +162,135 @@ class AsyncDiLoCo:
         self.quantization = quantization
         self.buf = torch.zeros_like(params)
         self.grads = [torch.empty_like(params), torch.empty_like(params)]  # double buffer
-        self.in_flight = None  # (handle, buffer index)
+        self.in_flight = None  # (kind, handle or None, buffer index)
+        self.side = torch.cuda.Stream(device=params.device) if params.is_cuda else None
         self.steps = 0
         self.applied = 0
+        self.topology_updated = True  # a peer that has just connected went through a topology round
 
-    def _apply(self, grad: torch.Tensor, inner: Optional[torch.Tensor]) -> None:
+    # ---- pieces -------------------------------------------------------------------------------------------------
+    def _apply(self, grad: torch.Tensor) -> None:
         if self.params.is_cuda:
-            outer_nesterov_(self.params, self.buf, grad, inner, self.lr, self.mu, self.applied == 0)
+            outer_nesterov_(self.params, self.buf, grad, None, self.lr, self.mu, self.applied == 0)
         else:
             if self.applied == 0:
                 self.buf.copy_(grad)
             else:
                 self.buf.mul_(self.mu).add_(grad)
             self.params.sub_(self.lr * (grad + self.mu * self.buf))
-            if inner is not None:
-                inner.copy_(self.params)
         self.applied += 1
 
-    def outer_step(self, inner: torch.Tensor) -> bool:
-        """Launches the reduction of this step's pseudo-gradient and applies the previous one.
-        Returns False when the previous reduction was lost to a peer failure (it is skipped)."""
-        idx = self.steps % 2
+    def _launch(self, idx: int) -> None:
         grad = self.grads[idx]
+        try:
+            if grad.is_cuda:
+                self.side.wait_stream(torch.cuda.current_stream(grad.device))  # the pseudo-gradient was computed there
+                self.comm.all_reduce(grad, grad, op=ReduceOp.AVG, tag=idx, quantization_options=self.quantization, stream=self.side,
+                                     enqueue=True)
+                self.in_flight = ("stream", None, idx)
+            else:
+                h = self.comm.all_reduce_async(grad, grad, op=ReduceOp.AVG, tag=idx, quantization_options=self.quantization)
+                self.in_flight = ("async", h, idx)
+        except PCCLError as e:
+            if e.result == Result.TOO_FEW_PEERS:
+                self.in_flight = ("local", None, idx)  # alone: the local pseudo-gradient is the average
+            elif e.result == Result.RANK_CONNECTION_LOST:
+                self.in_flight = None  # a peer vanished right at the launch: this update is skipped
+            else:
+                raise
+
+    def _await(self) -> Optional[torch.Tensor]:
+        """Waits for the reduction in flight.  Returns the averaged pseudo-gradient, or None when there was none or it
+        was lost to a peer failure (DiLoCo tolerates a skipped outer update)."""
+        if self.in_flight is None:
+            return None
+        kind, handle, idx = self.in_flight
+        self.in_flight = None
+        if kind == "stream":
+            try:
+                self.comm.ext_wait_stream_ops(idx)
+            except PCCLError as e:
+                if e.result != Result.RANK_CONNECTION_LOST:
+                    raise
+                return None
+            torch.cuda.current_stream(self.params.device).wait_stream(self.side)
+        elif kind == "async":
+            if not handle.wait()[0]:
+                return None
+        return self.grads[idx]
+
+    # ---- the protocol ---------------------------------------------------------------------------------------------
+    def admit_peers(self, sync_shared_state=None) -> bool:
+        """Top of an outer iteration.  When peers wait to join: finish the reduction in flight (its result is applied by the
+        coming outer_step), accept them, and run the ordinary shared-state synchronisation `sync_shared_state(strategy)`.
+        Returns whether the topology changed."""
+        from .._pccl import Attribute, SharedStateSyncStrategy
+        changed = self.topology_updated
+        if self.steps > 0:
+            changed = False
+            if self.comm.get_attribute(Attribute.GLOBAL_WORLD_SIZE) > 1 and self.comm.are_peers_pending():
+                self._held = self._await_keep()
+                self.comm.update_topology()
+                changed = True
+            elif self.comm.get_attribute(Attribute.GLOBAL_WORLD_SIZE) < 2:
+                self._held = self._await_keep()
+                self.comm.update_topology()  # alone: let anybody in who knocks
+                changed = self.comm.get_attribute(Attribute.GLOBAL_WORLD_SIZE) > 1
+        if changed and sync_shared_state is not None and self.comm.get_attribute(Attribute.PEER_GROUP_WORLD_SIZE) > 1:
+            sync_shared_state(SharedStateSyncStrategy.ENFORCE_POPULAR)
+        self.topology_updated = changed
+        return changed
+
+    _held = None  # (result or None, True) of a reduction that had to be awaited before a topology change
+
+    def _await_keep(self):
+        had = self.in_flight is not None
+        return (self._await(), had)
+
+    def outer_step(self, inner: torch.Tensor, sync_shared_state=None, run_step: Optional[int] = None) -> bool:
+        """End of an outer iteration (after the inner phase).  Applies the PREVIOUS step's averaged pseudo-gradient, inserts
+        a late joiner when the topology changed (second synchronisation, SEND_ONLY / RECEIVE_ONLY), resets the inner
+        parameters to the outer ones and launches this step's reduction.  Returns False when the previous reduction was
+        lost to a peer failure (that update is skipped).
+        run_step: the RUN's outer-step counter (part of the shared state, so a late joiner has it too); it picks the tag
+        and the buffer of this step's reduction, which must be the same on every peer.  Default: this peer's own count."""
+        from .._pccl import Attribute, SharedStateSyncStrategy
+        idx = (self.steps if run_step is None else run_step) % 2
+        grad = self.grads[idx]
+        # this step's pseudo-gradient, against the outer state as it was during the inner phase
         if self.params.is_cuda:
             pseudo_gradient(grad, self.params, inner)
         else:
             torch.sub(self.params, inner, out=grad)
-        ok = True
-        previous = self.in_flight
-        if previous is not None:
-            handle, pidx = previous
-            success, status, _ = handle.wait()
-            if success:
-                self._apply(self.grads[pidx], None)
-            else:
-                ok = False  # dropped: DiLoCo tolerates a skipped outer update
-        try:
-            self.in_flight = (self.comm.all_reduce_async(grad, grad, op=ReduceOp.AVG, tag=idx, quantization_options=self.quantization), idx)
-        except PCCLError as e:
-            if e.result != Result.TOO_FEW_PEERS:
-                raise
-            self.in_flight = None
-            self._apply(grad, None)  # alone: apply the local pseudo-gradient right away
+        if self._held is not None:
+            result, had_previous = self._held
+            self._held = None
+        else:
+            had_previous = self.in_flight is not None
+            result = self._await()
+        ok = result is not None or not had_previous
+        multi = self.comm.get_attribute(Attribute.PEER_GROUP_WORLD_SIZE) > 1
+        if self.steps > 0:  # a member of the running pipeline
+            if result is not None:
+                self._apply(result)
+            if self.topology_updated and multi and sync_shared_state is not None:
+                sync_shared_state(SharedStateSyncStrategy.SEND_ONLY)  # the joiner eavesdrops on the update it missed
+        elif self.topology_updated and multi and sync_shared_state is not None and self._joined_running_group:
+            sync_shared_state(SharedStateSyncStrategy.RECEIVE_ONLY)  # we are the joiner: take the state after that update
         inner.copy_(self.params)
+        self._launch(idx)
         self.steps += 1
         return ok
 
+    _joined_running_group = False
+
+    def mark_joined_running_group(self, yes: bool = True) -> None:
+        """Tell a freshly connected peer that the group it joined is past its first outer step (its first shared-state
+        synchronisation received data): it then takes part in the insertion protocol as the receiving side."""
+        self._joined_running_group = yes
+
     def flush(self) -> None:
-        """Waits for the reduction in flight and applies it (call before checkpointing / topology changes)."""
-        if self.in_flight is not None:
-            handle, pidx = self.in_flight
-            if handle.wait()[0]:
-                self._apply(self.grads[pidx], None)
-            self.in_flight = None
+        """Waits for the reduction in flight and applies it (before a checkpoint or at the end of the run)."""
+        result = self._await()
+        if result is not None:
+            self._apply(result)

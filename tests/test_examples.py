@@ -72,3 +72,58 @@ def test_ddp_examples_cpu(master):
                            "--master-port", "29640", str(REPO / "examples" / "ddp_nccl.py"), "--device", "cpu", "--steps", "3"],
                           stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, env=_env(), timeout=300)
     assert base.returncode == 0 and "step 2: loss" in base.stdout, base.stdout[-4000:]
+
+
+def test_diloco_example_checkpoint_and_resume(master, tmp_path):
+    """Config file, evaluation, checkpoint, and a second run that resumes: the resumed peers bring their shared-state
+    revision along (the first synchronisation of a group may carry any revision) and continue the step count
+    (reference: sync_diloco.py:247-262,445-457)."""
+    cfg = tmp_path / "cfg.json"
+    cfg.write_text('{"model": "tiny", "inner_steps": 2, "outer_steps": 3, "batch_size": 2, "eval_interval": 1, "eval_iters": 1, '
+                   f'"checkpoint_dir": "{tmp_path}/ckpt_RANK"' + "}")
+
+    def run(extra):
+        procs = []
+        for r in range(2):
+            c = tmp_path / f"cfg{r}.json"
+            c.write_text(cfg.read_text().replace("ckpt_RANK", f"ckpt_{r}"))
+            procs.append(subprocess.Popen([sys.executable, str(REPO / "examples" / "diloco.py"), "--master", f"127.0.0.1:{master.port}", "--device", "cpu",
+                                           "--config", str(c), "--min-peers", "2"] + extra, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True,
+                                          env=_env()))
+        outs = []
+        for p in procs:
+            out, _ = p.communicate(timeout=300)
+            assert p.returncode == 0, out[-4000:]
+            outs.append(out)
+        return outs
+
+    first = run([])
+    assert all("val loss" in o and "run step 3" in o for o in first), first[0][-2000:]
+    assert (tmp_path / "ckpt_0" / "ckpt.pt").exists() and (tmp_path / "ckpt_1" / "ckpt.pt").exists()
+    second = run(["--resume"])
+    for o in second:
+        assert "resumed from" in o and "at outer step 3" in o, o[-2000:]
+        assert "run step 6" in o and "world 2" in o, o[-2000:]
+
+
+def test_async_diloco_late_joiner_is_inserted_into_the_pipeline(master):
+    """Two peers train in the one-step-delayed mode; a third joins mid-run.  The members apply the reduction the joiner
+    missed and re-send the shared state (SEND_ONLY), the joiner receives it (RECEIVE_ONLY) -- reference:
+    python/examples/nanogpt_diloco/async_diloco.py:551-580 -- and all three go on together."""
+    import time
+    base = [sys.executable, str(REPO / "examples" / "diloco.py"), "--master", f"127.0.0.1:{master.port}", "--device", "cpu", "--mode", "async",
+            "--inner-steps", "2", "--batch", "2"]
+    old = [subprocess.Popen(base + ["--outer-steps", "40", "--min-peers", "2"], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, env=_env())
+           for _ in range(2)]
+    time.sleep(6)
+    new = subprocess.Popen(base + ["--outer-steps", "12", "--min-peers", "3"], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, env=_env())
+    out_new, _ = new.communicate(timeout=400)
+    assert new.returncode == 0, out_new[-4000:]
+    assert "world 3" in out_new, out_new[-3000:]
+    # the joiner adopted the run's step counter: its first line is not "run step 1"
+    first = re.search(r"outer step 0: .* run step (\d+)", out_new)
+    assert first and int(first.group(1)) > 1, out_new[:2000]
+    for p in old:
+        out, _ = p.communicate(timeout=400)
+        assert p.returncode == 0, out[-4000:]
+        assert "world 3" in out, out[-3000:]
