@@ -243,6 +243,77 @@ TEST(enforce_popular_cannot_be_mixed) {
     CHECK(!st[1].ok);
 }
 
+// ENFORCE_POPULAR x RECEIVE_ONLY (reference test_shared_state_distribution.cpp:2766): the receiver is kicked, the enforcer succeeds
+TEST(enforce_popular_with_receive_only) {
+    TestMaster tm;
+    auto peers = connect_peers(tm, 2);
+    std::vector<PeerState> st(2);
+    st[0].add("w", 64, 1);
+    st[1].add("w", 64, 2);
+    st[0].args.strategy = SyncStrategy::EnforcePopular;
+    st[1].args.strategy = SyncStrategy::RxOnly;
+    sync_all(peers, st);
+    CHECK(st[0].ok);
+    CHECK(!st[1].ok);
+    CHECK_EQ(st[0].tx, 0u);
+}
+
+// three peers, two enforcers and one SEND_ONLY (reference :2848): only the odd one out is kicked, the enforcers agree
+TEST(enforce_popular_three_peers_one_send_only) {
+    TestMaster tm;
+    auto peers = connect_peers(tm, 3);
+    std::vector<PeerState> st(3);
+    st[0].add("w", 128, 5);
+    st[1].add("w", 128, 6); // unpopular among the enforcers
+    st[2].add("w", 128, 5);
+    st[0].args.strategy = st[1].args.strategy = SyncStrategy::EnforcePopular;
+    st[2].args.strategy = SyncStrategy::TxOnly;
+    sync_all(peers, st);
+    CHECK(st[0].ok && st[1].ok);
+    CHECK(!st[2].ok);
+    CHECK(st[0].buffers[0] == st[1].buffers[0]); // the survivors hold one state
+}
+
+// three peers, one enforcer among a SEND_ONLY and a RECEIVE_ONLY peer (reference :2960): both others are kicked
+TEST(enforce_popular_three_peers_mixed_others) {
+    TestMaster tm;
+    auto peers = connect_peers(tm, 3);
+    std::vector<PeerState> st(3);
+    for (int i = 0; i < 3; ++i) st[i].add("w", 32, static_cast<uint8_t>(10 + i));
+    st[0].args.strategy = SyncStrategy::EnforcePopular;
+    st[1].args.strategy = SyncStrategy::TxOnly;
+    st[2].args.strategy = SyncStrategy::RxOnly;
+    sync_all(peers, st);
+    CHECK(st[0].ok);
+    CHECK(!st[1].ok && !st[2].ok);
+    // the enforcer keeps working alone afterwards... with nobody left there is nothing to agree on, the call still succeeds
+    st[0].args.revision = 1;
+    uint64_t tx = 0, rx = 0;
+    CHECK(peers[0]->sync_shared_state(st[0].args, tx, rx));
+    CHECK_EQ(tx + rx, 0u);
+}
+
+// SEND_ONLY towards two receivers: one distributor serves both, each receiver gets the full state exactly once
+TEST(one_sender_two_receivers) {
+    TestMaster tm;
+    auto peers = connect_peers(tm, 3);
+    std::vector<PeerState> st(3);
+    st[0].add("a", 1000, 7);
+    st[0].add("b", 33, 9, wire::DType::F32);
+    for (int i = 1; i < 3; ++i) {
+        st[i].add("a", 1000, static_cast<uint8_t>(20 + i));
+        st[i].add("b", 33, static_cast<uint8_t>(30 + i), wire::DType::F32);
+    }
+    st[0].args.strategy = SyncStrategy::TxOnly;
+    st[1].args.strategy = st[2].args.strategy = SyncStrategy::RxOnly;
+    sync_all(peers, st);
+    CHECK(st[0].ok && st[1].ok && st[2].ok);
+    CHECK_EQ(st[0].tx, 2u * (1000 + 33 * 4));
+    CHECK_EQ(st[1].rx, 1000u + 33 * 4);
+    CHECK_EQ(st[2].rx, 1000u + 33 * 4);
+    CHECK(st[1].buffers == st[0].buffers && st[2].buffers == st[0].buffers);
+}
+
 // a peer that joins between two syncs takes part from the next one
 TEST(late_joiner_participates) {
     TestMaster tm;

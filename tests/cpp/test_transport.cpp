@@ -158,6 +158,59 @@ TEST(server_many_concurrent_clients) {
     s.join();
 }
 
+// many clients, each with several multi-megabyte frames in flight at once, interleaved on the wire: every frame is
+// reassembled intact and in per-connection order (reference tinysockets/tests/test_server_socket.cpp:1074-1186)
+TEST(server_many_concurrent_large_frames) {
+    EpollServer s(loopback(0));
+    std::mutex mu;
+    std::map<uint8_t, std::vector<uint32_t>> seen; // client id -> frame numbers in arrival order
+    std::atomic<int> bad{0};
+    s.on_read([&](const ccoip_socket_address_t &, std::span<const uint8_t> frame) {
+        // frame = [u16 id][client][frame number u32 LE][payload of a size that depends on both]
+        if (frame.size() < 7) {
+            ++bad;
+            return;
+        }
+        const uint8_t client = frame[2];
+        uint32_t number = 0;
+        std::memcpy(&number, frame.data() + 3, 4);
+        const size_t want = 7 + (3u << 20) + 4099u * client + 17u * number;
+        if (frame.size() != want) ++bad;
+        for (size_t i = 7; i < frame.size(); i += 997)
+            if (frame[i] != static_cast<uint8_t>(client * 31 + number + i)) ++bad;
+        std::lock_guard<std::mutex> lock(mu);
+        seen[client].push_back(number);
+    });
+    CHECK(s.listen() && s.run_async());
+    constexpr int kClients = 8, kFrames = 6;
+    std::vector<std::thread> ts;
+    for (int c = 0; c < kClients; ++c)
+        ts.emplace_back([&, c] {
+            BlockingSocket sock(loopback(s.port()));
+            CHECK(sock.connect());
+            for (uint32_t k = 0; k < kFrames; ++k) {
+                RawPacket p;
+                p.body.resize(5 + (3u << 20) + 4099u * c + 17u * k);
+                p.body[0] = static_cast<uint8_t>(c);
+                std::memcpy(p.body.data() + 1, &k, 4);
+                for (size_t i = 7; i < p.body.size() + 2; ++i) p.body[i - 2] = static_cast<uint8_t>(c * 31 + k + i);
+                CHECK(sock.send_packet(p)); // no acknowledgement in between: frames pile up behind each other
+            }
+        });
+    for (auto &t : ts) t.join();
+    CHECK(eventually([&] {
+        std::lock_guard<std::mutex> lock(mu);
+        size_t n = 0;
+        for (auto &[c, v] : seen) n += v.size();
+        return n == size_t(kClients) * kFrames;
+    }));
+    CHECK_EQ(bad.load(), 0);
+    for (auto &[c, v] : seen)
+        for (uint32_t k = 0; k < kFrames; ++k) CHECK_EQ(v[k], k);
+    s.interrupt();
+    s.join();
+}
+
 // predicate-matched receive never loses or reorders packets that do not match
 TEST(queued_socket_matching) {
     EpollServer s(loopback(0));
