@@ -360,6 +360,8 @@ public:
         case wire::QuantAlgo::MinMax:
         case wire::QuantAlgo::BlockMinMax: return a.dtype == wire::DType::F32 && a.quant_dtype == wire::DType::U8 ? kCapP2P : 0u;
         case wire::QuantAlgo::BlockFp8: return a.dtype == wire::DType::F32 && a.quant_dtype == wire::DType::F8E4M3 ? kCapP2P : 0u;
+        // zero-point/scale with uint8 codes runs block-wise on the device; other code types take the TCP ring
+        case wire::QuantAlgo::ZeroPointScale: return a.dtype == wire::DType::F32 && a.quant_dtype == wire::DType::U8 ? kCapP2P : 0u;
         default: return 0;
         }
     }
@@ -1084,6 +1086,7 @@ private:
         case wire::QuantAlgo::MinMax:
         case wire::QuantAlgo::BlockMinMax: return pcclQuantBlockMinMax;
         case wire::QuantAlgo::BlockFp8: return pcclQuantBlockFp8;
+        case wire::QuantAlgo::ZeroPointScale: return pcclQuantZeroPointScale;
         default: return pcclQuantNone;
         }
     }

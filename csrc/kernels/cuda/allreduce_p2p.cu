@@ -542,9 +542,9 @@ using namespace pccl::cuda;
 extern "C" size_t pcclKernelP2PControlBytes(void) { return kControlBytes; }
 
 extern "C" size_t pcclKernelP2PStagingBytes(uint64_t count, int dtype, int quant_algorithm) {
-    if (quant_algorithm == QUANT_BLOCK_MINMAX || quant_algorithm == QUANT_BLOCK_FP8) {
+    if (quant_algorithm == QUANT_BLOCK_MINMAX || quant_algorithm == QUANT_BLOCK_FP8 || quant_algorithm == QUANT_BLOCK_ZPS) {
         const uint64_t n_blocks = (count + PCCL_K_QUANT_BLOCK - 1) / PCCL_K_QUANT_BLOCK;
-        const uint64_t mb = quant_algorithm == QUANT_BLOCK_MINMAX ? 8 : 4;
+        const uint64_t mb = quant_algorithm == QUANT_BLOCK_FP8 ? 4 : 8;
         return n_blocks * PCCL_K_QUANT_BLOCK + n_blocks * mb + 256;
     }
     const size_t esz = pcclExtDataTypeSize(static_cast<pcclDataType_t>(dtype));
@@ -629,7 +629,8 @@ int launch_allreduce(const pcclKernelP2PArgs_t *ranks, int n_ranks, bool emulate
     int max_blocks = args->max_blocks > 0 ? args->max_blocks : 144;
     if (max_blocks > PCCL_K_MAX_BLOCKS) max_blocks = PCCL_K_MAX_BLOCKS;
 
-    const bool quantised = args->quant_algorithm == QUANT_BLOCK_MINMAX || args->quant_algorithm == QUANT_BLOCK_FP8;
+    const bool quantised = args->quant_algorithm == QUANT_BLOCK_MINMAX || args->quant_algorithm == QUANT_BLOCK_FP8 ||
+                           args->quant_algorithm == QUANT_BLOCK_ZPS;
     if (quantised && args->dtype != pcclFloat) return cudaErrorInvalidValue;
     if (!quantised && args->quant_algorithm != QUANT_NONE) return cudaErrorInvalidValue;
 
@@ -656,6 +657,8 @@ int launch_allreduce(const pcclKernelP2PArgs_t *ranks, int n_ranks, bool emulate
             constexpr int OP = decltype(op_tag)::value;
             if (args->quant_algorithm == QUANT_BLOCK_MINMAX)
                 rc = launch_body<TwoShotQuant<QUANT_BLOCK_MINMAX, OP>>(d, n_ranks, emulated, grid, stream);
+            else if (args->quant_algorithm == QUANT_BLOCK_ZPS)
+                rc = launch_body<TwoShotQuant<QUANT_BLOCK_ZPS, OP>>(d, n_ranks, emulated, grid, stream);
             else
                 rc = launch_body<TwoShotQuant<QUANT_BLOCK_FP8, OP>>(d, n_ranks, emulated, grid, stream);
         });

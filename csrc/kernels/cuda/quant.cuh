@@ -8,7 +8,12 @@
 
 namespace pccl::cuda {
 
-enum : int { QUANT_NONE = 0, QUANT_BLOCK_MINMAX = 3, QUANT_BLOCK_FP8 = 4 }; // pcclQuantizationAlgorithm_t values
+// pcclQuantizationAlgorithm_t values; QUANT_BLOCK_ZPS is how pcclQuantZeroPointScale (2) runs on the device plane: uint8 codes, one
+// (scale, zero point) record per 128 elements -- scale = (max-min)/255, zp = round(-min/scale), q = clamp(round(x/scale) + zp),
+// x' = (q - zp) * scale; a constant block is stored as scale = value, q = 1, so it survives exactly (the reference's anchor:
+// 42 + 43 must come out as exactly 85, ccoip/tests/end_to_end/test_all_reduce.cpp:326-399).  The reference takes these
+// formulas from the piquant library per ring chunk (ccoip/src/cpp/quantize.cpp:22-57); here they are per block.
+enum : int { QUANT_NONE = 0, QUANT_BLOCK_ZPS = 2, QUANT_BLOCK_MINMAX = 3, QUANT_BLOCK_FP8 = 4 };
 
 template <int ALGO> struct QuantMeta;
 template <> struct QuantMeta<QUANT_BLOCK_MINMAX> {
@@ -16,6 +21,9 @@ template <> struct QuantMeta<QUANT_BLOCK_MINMAX> {
 };
 template <> struct QuantMeta<QUANT_BLOCK_FP8> {
     static constexpr int kBytes = 4;
+};
+template <> struct QuantMeta<QUANT_BLOCK_ZPS> {
+    static constexpr int kBytes = 8;
 };
 
 __device__ __forceinline__ float warp_min(float v) {
@@ -84,6 +92,10 @@ template <int ALGO> __device__ __forceinline__ void dequantize4(uint32_t packed,
         const float step = (mx - mn) * (1.0f / 255.0f);
 #pragma unroll
         for (int i = 0; i < 4; ++i) out[i] = fmaf(static_cast<float>((packed >> (8 * i)) & 0xffu), step, mn);
+    } else if constexpr (ALGO == QUANT_BLOCK_ZPS) {
+        const float scale = __uint_as_float(meta_lo), zp = static_cast<float>(static_cast<int>(meta_hi));
+#pragma unroll
+        for (int i = 0; i < 4; ++i) out[i] = (static_cast<float>((packed >> (8 * i)) & 0xffu) - zp) * scale;
     } else {
         const float scale = __uint_as_float(meta_lo);
 #pragma unroll
@@ -131,6 +143,34 @@ __device__ __forceinline__ uint4 quantize16(const float (&x)[16], int valid, uin
 #pragma unroll
         for (int i = 0; i < 16; ++i) {
             const float r = rintf((x[i] - mn) * inv);
+            const uint32_t c = i < valid ? static_cast<uint32_t>(fminf(255.0f, fmaxf(0.0f, r))) : 0u;
+            w[i >> 2] |= c << (8 * (i & 3));
+        }
+    } else if constexpr (ALGO == QUANT_BLOCK_ZPS) {
+        float mn = 3.402823466e+38f, mx = -3.402823466e+38f;
+#pragma unroll
+        for (int i = 0; i < 16; ++i)
+            if (i < valid) {
+                mn = fminf(mn, x[i]);
+                mx = fmaxf(mx, x[i]);
+            }
+        mn = group8_min(mn);
+        mx = group8_max(mx);
+        float scale;
+        int zp;
+        if (!(mx > mn)) { // constant block: code 1 times scale = the value (code 0 for zeros)
+            scale = mn != 0.0f ? mn : 1.0f;
+            zp = 0;
+        } else {
+            scale = (mx - mn) * (1.0f / 255.0f);
+            if (!(scale > 0.0f) || !isfinite(scale)) scale = 1.0f;
+            zp = __float2int_rn(-mn / scale);
+        }
+        rec_lo = __float_as_uint(scale), rec_hi = static_cast<uint32_t>(zp);
+        const float inv = 1.0f / scale;
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+            const float r = rintf(x[i] * inv) + static_cast<float>(zp);
             const uint32_t c = i < valid ? static_cast<uint32_t>(fminf(255.0f, fmaxf(0.0f, r))) : 0u;
             w[i >> 2] |= c << (8 * (i & 3));
         }

@@ -192,3 +192,27 @@ def test_mset64_device_equals_host():
     x = torch.randint(0, 255, (64,), dtype=torch.uint8)
     y = torch.cat([x[16:32], x[:16], x[32:]])
     assert ops.mset64(x) != ops.mset64(y)
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_zero_point_scale_on_the_device(world):
+    """Zero-point/scale quantisation (uint8 codes, one record per 128 elements) in the fused kernel.  The reference's anchor
+    (ccoip/tests/end_to_end/test_all_reduce.cpp:326-399): constants 42 and 43 must come out as exactly 85."""
+    d = dev()
+    n = 70_003
+    w = ops.EmulatedWorld(d, world, n * 2 + 65536)
+    consts = [42.0, 43.0, 44.0][:world]
+    srcs = [torch.full((n,), c, device=d) for c in consts]
+    dsts = [torch.zeros_like(s) for s in srcs]
+    w.all_reduce(srcs, dsts, op=pccl.ReduceOp.SUM, quant=pccl.QuantizationAlgorithm.ZERO_POINT_SCALE, max_blocks=8)
+    assert w.status() == [0] * world
+    for out in dsts:
+        assert torch.equal(out, torch.full_like(out, sum(consts)))
+    xs = [torch.randn(n, generator=torch.Generator().manual_seed(90 + r)) * 3 + r for r in range(world)]
+    want = fold(xs, pccl.ReduceOp.SUM, torch.float32)
+    srcs = [x.to(d) for x in xs]
+    w.all_reduce(srcs, dsts, op=pccl.ReduceOp.SUM, quant=pccl.QuantizationAlgorithm.ZERO_POINT_SCALE, max_blocks=8)
+    tol = 0.03 * want.abs().max().item()
+    for out in dsts:
+        assert (out.cpu().double() - want).abs().max().item() <= tol
+        assert torch.equal(out, dsts[0])
