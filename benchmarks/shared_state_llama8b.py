@@ -82,6 +82,44 @@ tC, infoC = phase(pccl.SharedStateSyncStrategy.SEND_ONLY if rank == 0 else pccl.
 one = tensors["layers.0.down_proj"].numel() * 2
 if rank == 1:
     assert infoC.rx_bytes == one, (infoC.rx_bytes, one)
+# phase D: the last peer leaves the run and comes back with garbage in its weights (a restarted worker): the others admit it
+# and one synchronisation brings it up to date (popular content wins; only the joiner receives)
+tD = tD_sync = None
+infoD = None
+if world >= 2:
+    state.push_revision()
+    dist.barrier()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    if rank == world - 1:
+        comm.destroy()
+        for t in tensors.values():
+            t.normal_()
+        comm = pccl.Communicator(f"127.0.0.1:{box[0]}")
+        comm.connect(n_attempts=30)
+        state = pccl.SharedState([pccl.TensorInfo.from_torch(t, name) for name, t in tensors.items()])
+        state.revision = 0  # knows nothing: whatever the group holds is newer
+    else:
+        while comm.get_attribute(pccl.Attribute.GLOBAL_WORLD_SIZE) != world - 1:
+            time.sleep(0.001)  # the master has noticed the departure
+            comm.update_topology()
+        while comm.get_attribute(pccl.Attribute.GLOBAL_WORLD_SIZE) < world:
+            comm.update_topology()
+    t1 = time.perf_counter()
+    infoD = comm.sync_shared_state(state, pccl.SharedStateSyncStrategy.ENFORCE_POPULAR)
+    torch.cuda.synchronize()
+    t2 = time.perf_counter()
+    tt = torch.tensor([t1 - t0, t2 - t1], device=dev, dtype=torch.float64)
+    dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    tD, tD_sync = float(tt[0]), float(tt[1])
+    ref = tensors["layers.0.q_proj"].float().sum().item()
+    chk = torch.tensor([ref], device=dev, dtype=torch.float64)
+    dist.broadcast(chk, src=0)
+    assert abs(chk.item() - ref) < 1e-3, "the rejoined peer does not hold the group's weights"
+    if rank == world - 1:
+        assert infoD.rx_bytes == n_params * 2
+    out.update({"leave_and_rejoin_membership_s": round(tD, 4), "rejoin_sync_s": round(tD_sync, 4),
+                "rejoin_sync_GBps": round(n_params * 2 / tD_sync / 1e9, 1)})
 out.update({"full_transfer_s": round(tA, 4), "full_transfer_GBps_per_receiver": round(n_params * 2 / tA / 1e9, 1),
             "rank_rx_bytes_A": infoA.rx_bytes, "rank_tx_bytes_A": infoA.tx_bytes,
             "hash_only_s": round(tB, 4), "hash_only_GBps": round(n_params * 2 / tB / 1e9, 1),

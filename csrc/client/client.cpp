@@ -3,6 +3,7 @@
 #include <algorithm>
 #include <chrono>
 #include <cstring>
+#include <future>
 #include <random>
 #include <thread>
 
@@ -455,7 +456,27 @@ bool Client::optimize_topology() {
 
 namespace {
 constexpr size_t kStageBytes = 8u << 20;
-}
+
+// two page-locked staging buffers for the socket <-> GPU pipelines of the shared-state transfer
+class PinnedPair {
+public:
+    explicit PinnedPair(device::Plane &plane) : plane_(plane) {}
+    ~PinnedPair() {
+        for (void *p : bufs_)
+            if (p) plane_.host_free(p);
+    }
+    bool ok() {
+        for (void *&p : bufs_)
+            if (!p && !(p = plane_.host_alloc(kStageBytes))) return false;
+        return true;
+    }
+    uint8_t *buf(size_t i) { return static_cast<uint8_t *>(bufs_[i & 1]); }
+
+private:
+    device::Plane &plane_;
+    void *bufs_[2] = {nullptr, nullptr};
+};
+} // namespace
 
 void Client::on_shared_state_accept(std::unique_ptr<net::BlockingSocket> sock) {
     uint16_t id = 0;
@@ -519,31 +540,54 @@ void Client::on_shared_state_accept(std::unique_ptr<net::BlockingSocket> sock) {
     // reported completion.
     if (resp.p2p) {
         auto staging = plane_->exchange_lock(); // one requester at a time uses the staging area
+        // Chunk number c of the whole transfer goes through staging slot c % window; a slot is staged again only when the
+        // requester has acknowledged the chunk that used it last.  With two slots this peer stages chunk c+1 while the
+        // requester still copies chunk c out over NVLink.
+        const size_t window = std::max<size_t>(1, std::min<size_t>(plane_->exchange_slots(), 2));
+        uint64_t sent = 0, acked = 0;
+        auto take_ack = [&]() -> bool {
+            if (!sock->recv_packet<C2SChunkAck>(60000)) return false;
+            ++acked;
+            return true;
+        };
         for (const auto &e : serve) {
             const size_t bytes = e.bytes();
             for (size_t off = 0; off < bytes || (bytes == 0 && off == 0); off += chunk) {
                 const size_t n = std::min(chunk, bytes - off);
-                if (n && !plane_->export_chunk(static_cast<const uint8_t *>(e.data) + off, e.on_device, n)) return;
+                while (sent - acked >= window)
+                    if (!take_ack()) return;
+                if (n && !plane_->export_chunk(sent % window, static_cast<const uint8_t *>(e.data) + off, e.on_device, n)) return;
                 if (!sock->send_packet(S2CChunkReady{})) return;
-                if (!sock->recv_packet<C2SChunkAck>(60000)) return;
+                ++sent;
                 if (bytes == 0) break;
             }
             ss_tx_bytes_ += bytes;
         }
+        while (acked < sent)
+            if (!take_ack()) return;
         return;
     }
-    // Base protocol: raw tensor bytes follow, unframed, in request order.
-    std::vector<uint8_t> stage;
+    // Base protocol: raw tensor bytes follow, unframed, in request order.  Device tensors go through two page-locked buffers:
+    // while one is on its way into the socket, the next chunk is copied off the GPU into the other.
+    PinnedPair stage(*plane_);
     for (const auto &e : serve) {
         const size_t bytes = e.bytes();
         if (!e.on_device) {
             if (!sock->send_raw(e.data, bytes)) return;
         } else {
-            if (stage.empty()) stage.resize(kStageBytes);
-            for (size_t off = 0; off < bytes; off += kStageBytes) {
-                const size_t n = std::min(kStageBytes, bytes - off);
-                if (!plane_->copy_to_host(stage.data(), static_cast<const uint8_t *>(e.data) + off, n)) return;
-                if (!sock->send_raw(stage.data(), n)) return;
+            if (!stage.ok()) return;
+            const auto *src = static_cast<const uint8_t *>(e.data);
+            size_t filled = std::min(kStageBytes, bytes);
+            if (filled && !plane_->copy_to_host(stage.buf(0), src, filled)) return;
+            for (size_t off = 0, k = 0; off < bytes; ++k) {
+                const size_t n = filled, next_off = off + n, next_n = std::min(kStageBytes, bytes - next_off);
+                std::future<bool> next;
+                if (next_n) next = std::async(std::launch::async, [&, k, next_off, next_n] { return plane_->copy_to_host(stage.buf((k + 1) & 1), src + next_off, next_n); });
+                const bool sent = sock->send_raw(stage.buf(k & 1), n);
+                const bool copied = !next.valid() || next.get();
+                if (!sent || !copied) return;
+                off = next_off;
+                filled = next_n;
             }
         }
         ss_tx_bytes_ += bytes;
@@ -579,14 +623,41 @@ bool Client::sync_shared_state(SharedStateArgs &state, uint64_t &tx_bytes, uint6
     C2MSyncSharedState vote;
     vote.revision = state.revision;
     vote.strategy = state.strategy;
-    for (const auto &e : state.entries) {
+    // device tensors whose hash is not already known are hashed in one batch (one wait for all of them)
+    std::vector<device::Plane::HashJob> jobs;
+    std::vector<size_t> job_entry;
+    std::vector<uint64_t> hashes(state.entries.size(), 0);
+    std::vector<bool> have(state.entries.size(), false);
+    for (size_t i = 0; i < state.entries.size(); ++i) {
+        const auto &e = state.entries[i];
+        if (e.allow_content_inequality) continue;
+        if (hash_type == HashType::Mset64 && trust_hashes_ && recall_hash(e.data, e.bytes(), hashes[i])) {
+            ++hash_skips_;
+            have[i] = true;
+        } else if (e.on_device && state.entries.size() > 1) {
+            jobs.push_back({e.data, e.bytes(), 0});
+            job_entry.push_back(i);
+        }
+    }
+    if (!jobs.empty()) {
+        if (plane_->hash_device_many(jobs, hash_type)) {
+            for (size_t j = 0; j < jobs.size(); ++j) {
+                hashes[job_entry[j]] = jobs[j].result;
+                have[job_entry[j]] = true;
+            }
+        } // else: one by one below, which reports the tensor that fails
+    }
+    for (size_t i = 0; i < state.entries.size(); ++i) {
+        const auto &e = state.entries[i];
         SharedStateEntry w;
         w.key = e.key;
         w.hash_type = hash_type;
         w.num_elements = e.count;
         w.dtype = e.dtype;
         w.allow_content_inequality = e.allow_content_inequality;
-        if (!e.allow_content_inequality && !hash_of(e, w.hash)) {
+        if (have[i]) {
+            w.hash = hashes[i];
+        } else if (!e.allow_content_inequality && !hash_of(e, w.hash)) {
             PLOG(ERR) << "cannot hash tensor '" << e.key << "'";
             return false;
         }
@@ -660,7 +731,9 @@ bool Client::sync_shared_state(SharedStateArgs &state, uint64_t &tx_bytes, uint6
             state.revision = resp->revision; // adopt the distributor's revision even if no bytes move
         }
         if (offered.size() != verdict->outdated_keys.size()) return false;
-        std::vector<uint8_t> stage;
+        PinnedPair stage(*plane_);
+        const size_t window = std::max<size_t>(1, std::min<size_t>(plane_->exchange_slots(), 2));
+        uint64_t chunk_no = 0; // counts the chunks of the whole transfer, like the distributor does
         for (size_t i = 0; i < offered.size(); ++i) {
             const auto &slice = offered[i];
             const auto it = std::find_if(state.entries.begin(), state.entries.end(),
@@ -673,19 +746,27 @@ bool Client::sync_shared_state(SharedStateArgs &state, uint64_t &tx_bytes, uint6
                 for (size_t off = 0; off < slice.size_bytes || (slice.size_bytes == 0 && off == 0); off += chunk) {
                     const size_t n = std::min<size_t>(chunk, slice.size_bytes - off);
                     if (!sock.recv_packet<S2CChunkReady>(60000)) return false;
-                    if (n && !plane_->import_chunk(distributor, static_cast<uint8_t *>(it->data) + off, it->on_device, n)) return false;
+                    if (n && !plane_->import_chunk(chunk_no % window, distributor, static_cast<uint8_t *>(it->data) + off, it->on_device, n)) return false;
                     if (!sock.send_packet(C2SChunkAck{})) return false;
+                    ++chunk_no;
                     if (slice.size_bytes == 0) break;
                 }
             } else if (!it->on_device) {
                 if (!sock.recv_raw(it->data, slice.size_bytes)) return false;
             } else {
-                if (stage.empty()) stage.resize(kStageBytes);
-                for (size_t off = 0; off < slice.size_bytes; off += kStageBytes) {
+                // socket -> page-locked buffer -> GPU, the copy of chunk k overlapping the receive of chunk k+1
+                if (!stage.ok()) return false;
+                auto *dst = static_cast<uint8_t *>(it->data);
+                std::future<bool> pending;
+                size_t k = 0;
+                for (size_t off = 0; off < slice.size_bytes; off += kStageBytes, ++k) {
                     const size_t n = std::min<size_t>(kStageBytes, slice.size_bytes - off);
-                    if (!sock.recv_raw(stage.data(), n)) return false;
-                    if (!plane_->copy_to_device(static_cast<uint8_t *>(it->data) + off, stage.data(), n)) return false;
+                    const bool got = sock.recv_raw(stage.buf(k & 1), n);
+                    if (pending.valid() && !pending.get()) return false; // the buffer received into next is free again
+                    if (!got) return false;
+                    pending = std::async(std::launch::async, [&, k, off, n] { return plane_->copy_to_device(dst + off, stage.buf(k & 1), n); });
                 }
+                if (pending.valid() && !pending.get()) return false;
             }
             rx_bytes += slice.size_bytes;
             forget_hashes(it->data, it->bytes());

@@ -131,6 +131,14 @@ public:
     virtual bool copy_to_device(void *dev_dst, const void *host_src, size_t bytes) = 0;
     // Content hash of a device buffer; hash_type as on the wire.
     virtual bool hash_device(const void *dev_ptr, size_t bytes, wire::HashType type, uint64_t &out) = 0;
+    // Many buffers at once: the kernels are queued back to back and waited for once (a model's parameter list is hundreds
+    // of tensors; one synchronisation per tensor costs more than the hashing).
+    struct HashJob {
+        const void *ptr;
+        size_t bytes;
+        uint64_t result;
+    };
+    virtual bool hash_device_many(std::vector<HashJob> &jobs, wire::HashType type) = 0;
 
     // Shared-state transfer between peers of one NVLink domain: the distributor stages a chunk in its
     // arena (export), the requester copies it out of the mapped arena (import).  `exchange_bytes` is
@@ -139,8 +147,10 @@ public:
     virtual bool peer_mapped(const Uuid &peer) = 0;
     virtual size_t exchange_bytes() = 0;
     virtual std::unique_lock<std::mutex> exchange_lock() = 0;
-    virtual bool export_chunk(const void *src, bool src_on_device, size_t bytes) = 0;
-    virtual bool import_chunk(const Uuid &from, void *dst, bool dst_on_device, size_t bytes) = 0;
+    // `slot` < exchange_slots(): with two of them the distributor stages chunk i+1 while the requester still reads chunk i.
+    virtual size_t exchange_slots() = 0;
+    virtual bool export_chunk(size_t slot, const void *src, bool src_on_device, size_t bytes) = 0;
+    virtual bool import_chunk(size_t slot, const Uuid &from, void *dst, bool dst_on_device, size_t bytes) = 0;
 
     // Fusing many small reductions into one: a reusable device buffer (from the symmetric heap when
     // it fits, so the fused reduction needs no staging) and batched device-to-device copies.

@@ -733,6 +733,29 @@ public:
         return rc == 0;
     }
 
+    bool hash_device_many(std::vector<HashJob> &jobs, wire::HashType type) override {
+        if (!cuda_runtime_usable() || jobs.empty()) return jobs.empty();
+        const PointerInfo info = classify_pointer(jobs[0].ptr);
+        int prev = -1;
+        cudaGetDevice(&prev);
+        if (info.is_device && info.device >= 0) cudaSetDevice(info.device);
+        std::vector<const void *> ptrs;
+        std::vector<size_t> sizes;
+        std::vector<uint64_t> out(jobs.size());
+        for (const auto &j : jobs) {
+            ptrs.push_back(j.ptr);
+            sizes.push_back(j.bytes);
+        }
+        const int rc = pcclKernelHashManySync(ptrs.data(), sizes.data(), jobs.size(), static_cast<int>(type), out.data());
+        if (prev >= 0) cudaSetDevice(prev);
+        if (rc != 0) {
+            PLOG(ERR) << "device hash failed: " << cudaGetErrorString(static_cast<cudaError_t>(rc));
+            return false;
+        }
+        for (size_t i = 0; i < jobs.size(); ++i) jobs[i].result = out[i];
+        return true;
+    }
+
     bool pseudo_grad(float *out, const float *params, const float *inner, size_t count) override {
         return elementwise([&](cudaStream_t st) { return pcclKernelPseudoGrad(out, params, inner, count, st); });
     }
@@ -796,14 +819,17 @@ public:
     }
     size_t exchange_bytes() override {
         std::lock_guard<std::mutex> lock(mu_);
-        return arena_ptr_ && !slots_.empty() ? slot_bytes_ : 0;
+        // chunks well below the slot size: the two-slot pipeline (stage chunk i+1 while chunk i is read) fills and drains faster
+        return arena_ptr_ && !slots_.empty() ? std::min<size_t>(slot_bytes_, size_t(256) << 20) : 0;
     }
     std::unique_lock<std::mutex> exchange_lock() override { return std::unique_lock<std::mutex>(exchange_mu_); }
-    bool export_chunk(const void *src, bool, size_t bytes) override {
-        if (bytes > slot_bytes_) return false;
-        return copy(reinterpret_cast<void *>(arena_ptr_ + slot_offset(0)), src, bytes, cudaMemcpyDefault);
+    size_t exchange_slots() override { return n_slots_; }
+    bool export_chunk(size_t slot, const void *src, bool, size_t bytes) override {
+        if (bytes > slot_bytes_ || slot >= n_slots_) return false;
+        return copy(reinterpret_cast<void *>(arena_ptr_ + slot_offset(slot)), src, bytes, cudaMemcpyDefault);
     }
-    bool import_chunk(const Uuid &from, void *dst, bool, size_t bytes) override {
+    bool import_chunk(size_t slot, const Uuid &from, void *dst, bool, size_t bytes) override {
+        if (slot >= n_slots_) return false;
         CUdeviceptr base = 0;
         {
             std::lock_guard<std::mutex> lock(mu_);
@@ -811,7 +837,7 @@ public:
             if (it == peers_.end() || bytes > slot_bytes_) return false;
             base = it->second.ptr;
         }
-        return copy(dst, reinterpret_cast<const void *>(base + slot_offset(0)), bytes, cudaMemcpyDefault);
+        return copy(dst, reinterpret_cast<const void *>(base + slot_offset(slot)), bytes, cudaMemcpyDefault);
     }
 
     void *host_alloc(size_t bytes) override {

@@ -26,14 +26,16 @@ public:
     bool copy_to_host(void *, const void *, size_t) override { return false; }
     bool copy_to_device(void *, const void *, size_t) override { return false; }
     bool hash_device(const void *, size_t, wire::HashType, uint64_t &) override { return false; }
+    bool hash_device_many(std::vector<HashJob> &, wire::HashType) override { return false; }
+    size_t exchange_slots() override { return 0; }
     void *fuse_buffer(size_t) override { return nullptr; }
     std::unique_lock<std::mutex> fuse_lock() override { return std::unique_lock<std::mutex>(fuse_use_mu_); }
     bool gather(const std::vector<Part> &, void *, bool) override { return false; }
     bool peer_mapped(const Uuid &) override { return false; }
     size_t exchange_bytes() override { return 0; }
     std::unique_lock<std::mutex> exchange_lock() override { return std::unique_lock<std::mutex>(mu_); }
-    bool export_chunk(const void *, bool, size_t) override { return false; }
-    bool import_chunk(const Uuid &, void *, bool, size_t) override { return false; }
+    bool export_chunk(size_t, const void *, bool, size_t) override { return false; }
+    bool import_chunk(size_t, const Uuid &, void *, bool, size_t) override { return false; }
     bool pseudo_grad(float *, const float *, const float *, size_t) override { return false; }
     bool outer_nesterov(const OuterStepArgs &, const float *, size_t) override { return false; }
     void *host_alloc(size_t bytes) override { return std::malloc(bytes); }

@@ -399,6 +399,45 @@ extern "C" int pcclKernelHashSync(const void *data, size_t n_bytes, int hash_typ
     return 0;
 }
 
+// Many buffers, one wait: the kernels run back to back on the library's hash stream (they share the one scratch area, which
+// every kernel leaves ready for the next), each writes its own result word, one copy brings all results back.
+extern "C" int pcclKernelHashManySync(const void *const *data, const size_t *n_bytes, size_t count, int hash_type, uint64_t *out_host) {
+    if (!data || !n_bytes || !out_host) return cudaErrorInvalidValue;
+    if (count == 0) return 0;
+    int rc = 0;
+    HashContext *c = hash_context(rc);
+    if (!c) return rc;
+    std::lock_guard<std::mutex> lock(g_hash_call_mu);
+    static thread_local uint64_t *dev_out = nullptr, *host_out = nullptr;
+    static thread_local size_t capacity = 0;
+    static thread_local int owner_device = -1;
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (capacity < count || owner_device != dev) {
+        if (dev_out) cudaFree(dev_out);
+        if (host_out) cudaFreeHost(host_out);
+        dev_out = host_out = nullptr;
+        capacity = 0;
+        const size_t want = std::max<size_t>(count, 1024);
+        if ((rc = cudaMalloc(reinterpret_cast<void **>(&dev_out), want * sizeof(uint64_t))) != cudaSuccess) return rc;
+        if ((rc = cudaHostAlloc(reinterpret_cast<void **>(&host_out), want * sizeof(uint64_t), cudaHostAllocDefault)) != cudaSuccess) return rc;
+        capacity = want;
+        owner_device = dev;
+    }
+    cudaEventRecord(c->ready, cudaStreamLegacy);
+    cudaStreamWaitEvent(c->stream, c->ready, 0);
+    for (size_t i = 0; i < count; ++i) {
+        rc = hash_type == 0   ? pcclKernelSimpleHash(data[i], n_bytes[i], c->scratch, dev_out + i, c->stream)
+             : hash_type == 1 ? pcclKernelCrc32c(data[i], n_bytes[i], c->scratch, dev_out + i, c->stream)
+                              : pcclKernelMset64Raw(data[i], n_bytes[i], dev_out + i, c->stream);
+        if (rc != cudaSuccess) return rc;
+    }
+    if ((rc = cudaMemcpyAsync(host_out, dev_out, count * sizeof(uint64_t), cudaMemcpyDeviceToHost, c->stream)) != cudaSuccess) return rc;
+    if ((rc = cudaStreamSynchronize(c->stream)) != cudaSuccess) return rc;
+    for (size_t i = 0; i < count; ++i) out_host[i] = hash_type == 2 ? pccl::mset::finalize(host_out[i], n_bytes[i]) : host_out[i];
+    return 0;
+}
+
 // ---------------------------------------------------------------------------------------------
 // pcclKernelSimpleHashNoAlloc -- the same hash for callers that must not allocate.
 //

@@ -42,6 +42,9 @@ PCCL_EXPORT uint64_t pcclExtMsetFinalize(uint64_t raw_sum, uint64_t n_bytes);
  * hash on an internal stream and returns the value on the host (synchronous). */
 PCCL_EXPORT int pcclKernelHashSync(const void *data, size_t n_bytes, int hash_type, uint64_t *out_host); /* 0 simplehash, 1 CRC32C, 2 mset64 */
 
+/* The same for `count` buffers with ONE wait at the end (shared-state synchronisation of a parameter list). */
+PCCL_EXPORT int pcclKernelHashManySync(const void *const *data, const size_t *n_bytes, size_t count, int hash_type, uint64_t *out_host);
+
 /* Same hash, for callers that may not allocate device memory (open stream capture, allocator that already
  * owns the whole GPU, paths that cannot afford cudaMalloc's device-wide synchronisation).  Has no
  * counterpart in the reference.  The scratch is a 4 KiB static device array inside the library, shared
