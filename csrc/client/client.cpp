@@ -734,6 +734,8 @@ bool Client::sync_shared_state(SharedStateArgs &state, uint64_t &tx_bytes, uint6
         PinnedPair stage(*plane_);
         const size_t window = std::max<size_t>(1, std::min<size_t>(plane_->exchange_slots(), 2));
         uint64_t chunk_no = 0; // counts the chunks of the whole transfer, like the distributor does
+        unsigned imports_pending = 0, acks_owed = 0;
+        std::vector<std::pair<const SharedEntry *, uint64_t>> to_verify;
         for (size_t i = 0; i < offered.size(); ++i) {
             const auto &slice = offered[i];
             const auto it = std::find_if(state.entries.begin(), state.entries.end(),
@@ -743,14 +745,29 @@ bool Client::sync_shared_state(SharedStateArgs &state, uint64_t &tx_bytes, uint6
                 return false;
             }
             if (p2p) {
+                // The copy of a chunk is only enqueued when its Ready arrives; the acknowledgement (which lets the distributor
+                // reuse the slot) follows once the copy has finished -- one chunk later, so that consecutive copies run back
+                // to back on the stream while the next Ready is already on its way.
                 for (size_t off = 0; off < slice.size_bytes || (slice.size_bytes == 0 && off == 0); off += chunk) {
                     const size_t n = std::min<size_t>(chunk, slice.size_bytes - off);
                     if (!sock.recv_packet<S2CChunkReady>(60000)) return false;
-                    if (n && !plane_->import_chunk(chunk_no % window, distributor, static_cast<uint8_t *>(it->data) + off, it->on_device, n)) return false;
-                    if (!sock.send_packet(C2SChunkAck{})) return false;
+                    if (n) {
+                        if (!plane_->import_chunk_begin(chunk_no % window, distributor, static_cast<uint8_t *>(it->data) + off, it->on_device, n)) return false;
+                        ++imports_pending;
+                    } else {
+                        ++acks_owed; // an empty tensor: nothing to copy, acknowledged with the others
+                    }
+                    while (imports_pending > (window > 1 ? 1u : 0u)) {
+                        if (!plane_->import_chunk_finish_oldest()) return false;
+                        --imports_pending;
+                        ++acks_owed;
+                    }
+                    for (; acks_owed; --acks_owed)
+                        if (!sock.send_packet(C2SChunkAck{})) return false;
                     ++chunk_no;
                     if (slice.size_bytes == 0) break;
                 }
+
             } else if (!it->on_device) {
                 if (!sock.recv_raw(it->data, slice.size_bytes)) return false;
             } else {
@@ -770,15 +787,39 @@ bool Client::sync_shared_state(SharedStateArgs &state, uint64_t &tx_bytes, uint6
             }
             rx_bytes += slice.size_bytes;
             forget_hashes(it->data, it->bytes());
-            // verify what arrived against what the master elected
-            if (!it->allow_content_inequality && i < verdict->expected_hashes.size()) {
-                uint64_t h = 0;
-                if (!hash_of(*it, h)) return false;
-                if (h != verdict->expected_hashes[i]) {
-                    PLOG(ERR) << "shared-state tensor '" << slice.key << "' does not match the elected hash after transfer";
-                    return false;
-                }
+            if (!it->allow_content_inequality && i < verdict->expected_hashes.size()) to_verify.push_back({&*it, verdict->expected_hashes[i]});
+        }
+        // the last copies must have landed before anything is hashed
+        while (imports_pending) {
+            if (!plane_->import_chunk_finish_oldest()) return false;
+            --imports_pending;
+            ++acks_owed;
+        }
+        for (; acks_owed; --acks_owed)
+            if (!sock.send_packet(C2SChunkAck{})) return false;
+        // verify what arrived against what the master elected: device tensors in one batch
+        std::vector<device::Plane::HashJob> vjobs;
+        std::vector<size_t> vidx;
+        for (size_t k = 0; k < to_verify.size(); ++k)
+            if (to_verify[k].first->on_device && to_verify.size() > 1) {
+                vjobs.push_back({to_verify[k].first->data, to_verify[k].first->bytes(), 0});
+                vidx.push_back(k);
             }
+        std::vector<uint64_t> got(to_verify.size(), 0);
+        std::vector<bool> hashed(to_verify.size(), false);
+        if (!vjobs.empty() && plane_->hash_device_many(vjobs, hash_type))
+            for (size_t j = 0; j < vjobs.size(); ++j) {
+                got[vidx[j]] = vjobs[j].result;
+                hashed[vidx[j]] = true;
+            }
+        for (size_t k = 0; k < to_verify.size(); ++k) {
+            const SharedEntry &e = *to_verify[k].first;
+            if (!hashed[k] && !hash_of(e, got[k])) return false;
+            if (got[k] != to_verify[k].second) {
+                PLOG(ERR) << "shared-state tensor '" << e.key << "' does not match the elected hash after transfer";
+                return false;
+            }
+            if (hash_type == HashType::Mset64) remember_hash(e.data, e.bytes(), got[k]);
         }
     }
 

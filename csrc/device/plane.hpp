@@ -151,6 +151,10 @@ public:
     virtual size_t exchange_slots() = 0;
     virtual bool export_chunk(size_t slot, const void *src, bool src_on_device, size_t bytes) = 0;
     virtual bool import_chunk(size_t slot, const Uuid &from, void *dst, bool dst_on_device, size_t bytes) = 0;
+    // The same in two halves, so that the copies of consecutive chunks queue up back to back: begin() enqueues the copy,
+    // finish_oldest() waits for the oldest one still pending (false when none is, or on failure).
+    virtual bool import_chunk_begin(size_t slot, const Uuid &from, void *dst, bool dst_on_device, size_t bytes) = 0;
+    virtual bool import_chunk_finish_oldest() = 0;
 
     // Fusing many small reductions into one: a reusable device buffer (from the symmetric heap when
     // it fits, so the fused reduction needs no staging) and batched device-to-device copies.

@@ -840,6 +840,43 @@ public:
         return copy(dst, reinterpret_cast<const void *>(base + slot_offset(slot)), bytes, cudaMemcpyDefault);
     }
 
+    bool import_chunk_begin(size_t slot, const Uuid &from, void *dst, bool, size_t bytes) override {
+        if (slot >= n_slots_) return false;
+        CUdeviceptr base = 0;
+        {
+            std::lock_guard<std::mutex> lock(mu_);
+            const auto it = peers_.find(from);
+            if (it == peers_.end() || bytes > slot_bytes_) return false;
+            base = it->second.ptr;
+        }
+        cudaSetDevice(device_);
+        std::lock_guard<std::mutex> lock(copy_mu_);
+        if (!util_stream_) RT_TRY(cudaStreamCreateWithFlags(&util_stream_, cudaStreamNonBlocking));
+        cudaEvent_t done;
+        RT_TRY(cudaEventCreateWithFlags(&done, cudaEventDisableTiming));
+        if (cudaMemcpyAsync(dst, reinterpret_cast<const void *>(base + slot_offset(slot)), bytes, cudaMemcpyDefault, util_stream_) != cudaSuccess ||
+            cudaEventRecord(done, util_stream_) != cudaSuccess) {
+            (void) cudaGetLastError();
+            cudaEventDestroy(done);
+            return false;
+        }
+        pending_imports_.push_back(done);
+        return true;
+    }
+    bool import_chunk_finish_oldest() override {
+        cudaEvent_t done;
+        {
+            std::lock_guard<std::mutex> lock(copy_mu_);
+            if (pending_imports_.empty()) return false;
+            done = pending_imports_.front();
+            pending_imports_.pop_front();
+        }
+        const cudaError_t rc = cudaEventSynchronize(done);
+        cudaEventDestroy(done);
+        if (rc != cudaSuccess) (void) cudaGetLastError();
+        return rc == cudaSuccess;
+    }
+
     void *host_alloc(size_t bytes) override {
         if (cuda_runtime_usable()) {
             void *p = nullptr;
@@ -1558,6 +1595,7 @@ private:
 
     std::mutex copy_mu_;
     cudaStream_t util_stream_ = nullptr;
+    std::deque<cudaEvent_t> pending_imports_; // guarded by copy_mu_
 
     std::mutex fuse_mu_, fuse_use_mu_;
     void *fuse_ptr_ = nullptr; // cudaMalloc'd fallback for operands beyond the scratch region

@@ -28,6 +28,8 @@ public:
     bool hash_device(const void *, size_t, wire::HashType, uint64_t &) override { return false; }
     bool hash_device_many(std::vector<HashJob> &, wire::HashType) override { return false; }
     size_t exchange_slots() override { return 0; }
+    bool import_chunk_begin(size_t, const Uuid &, void *, bool, size_t) override { return false; }
+    bool import_chunk_finish_oldest() override { return false; }
     void *fuse_buffer(size_t) override { return nullptr; }
     std::unique_lock<std::mutex> fuse_lock() override { return std::unique_lock<std::mutex>(fuse_use_mu_); }
     bool gather(const std::vector<Part> &, void *, bool) override { return false; }
