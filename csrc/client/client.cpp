@@ -873,11 +873,42 @@ bool Client::last_stats(uint64_t tag, pcclExtReduceStats_t &out) {
 
 Client::Launch Client::all_reduce_async(const ReduceRequest &req) {
     if (!accepted_ || !master_.is_open()) return Launch::NotConnected;
-    std::lock_guard<std::mutex> lock(ops_mu_);
+    std::unique_lock<std::mutex> lock(ops_mu_);
     if (ops_.count(req.tag)) return Launch::DuplicateTag;
     Op op;
     op.revision_at_launch = connection_revision_;
     const uint64_t rev = op.revision_at_launch;
+    bool leased_device = false;
+    if (lease_enabled_ && !req.outer) {
+        {
+            std::lock_guard<std::mutex> l(lease_mu_);
+            leased_device = lease_tags_.count(req.tag) > 0;
+        }
+        leased_device = leased_device && device::classify_pointer(req.send).is_device && device::classify_pointer(req.recv).is_device;
+    }
+    if (leased_device) {
+        // no vote, no socket: the launch takes microseconds, do it here (ordered after the legacy default stream, like every
+        // operation that is not given a stream) and let await_reduce() take the verdict
+        ops_.emplace(req.tag, Op{});
+        ReduceRequest inline_req = req;
+        inline_req.user_stream = reinterpret_cast<void *>(uintptr_t(1)); // cudaStreamLegacy
+        inline_req.enqueue = true;
+        lock.unlock();
+        ReduceOutcome out = run_reduce(inline_req, rev);
+        lock.lock();
+        Op &slot = ops_[req.tag];
+        slot.revision_at_launch = rev;
+        if (out.pending) {
+            slot.launched_inline = true;
+            slot.ticket = out.ticket;
+            slot.partial = out;
+        } else { // the lease was gone after all and the operation ran (or failed) right here
+            std::promise<ReduceOutcome> done;
+            done.set_value(out);
+            slot.future = done.get_future();
+        }
+        return Launch::Ok;
+    }
     op.future = workers_->submit([this, req, rev] { return run_reduce(req, rev); });
     ops_.emplace(req.tag, std::move(op));
     return Launch::Ok;
@@ -888,8 +919,19 @@ bool Client::await_reduce(uint64_t tag, ReduceOutcome &out) {
     {
         std::lock_guard<std::mutex> lock(ops_mu_);
         const auto it = ops_.find(tag);
-        if (it == ops_.end() || !it->second.future.valid()) return false;
+        if (it == ops_.end() || (!it->second.future.valid() && !it->second.launched_inline)) return false;
         op = std::move(it->second);
+    }
+    if (op.launched_inline) {
+        StreamOp so;
+        so.ticket = op.ticket;
+        so.revision_at_launch = op.revision_at_launch;
+        so.partial = op.partial;
+        {
+            std::lock_guard<std::mutex> lock(ops_mu_);
+            ops_.erase(tag);
+        }
+        return finish_stream_op(tag, so, out);
     }
     try {
         out = op.future.get();

@@ -187,6 +187,11 @@ private:
     struct Op {
         std::future<ReduceOutcome> future;
         uint64_t revision_at_launch = 0;
+        // leased device operations are launched on the calling thread (no hand-over to a worker, whose wake-up costs more
+        // than the whole operation); await_reduce() then only collects the verdict
+        bool launched_inline = false;
+        uint64_t ticket = 0;
+        ReduceOutcome partial;
     };
     // page-locked host buffers for device tensors that travel over the TCP plane, one per tag
     struct StageBuf {

@@ -534,7 +534,9 @@ public:
             per_round = std::max<uint64_t>(unit, per_round / unit * unit);
         }
         const uint64_t n_rounds = (a.count + per_round - 1) / per_round;
-        if (n_rounds > 255 || (a.outer && n_rounds != 1)) return res;
+        // every round gets kRoundFlags barrier values of the operation's 1024 (the pipelined kernel uses one per segment + 2)
+        constexpr uint64_t kRoundFlags = 32;
+        if (n_rounds > 1024 / kRoundFlags - 1 || (a.outer && n_rounds != 1)) return res;
 
         // ---- stream dependencies
         bank.busy = true;
@@ -568,7 +570,7 @@ public:
             k.rank = a.rank;
             k.world = a.world;
             k.flag_slot = static_cast<uint32_t>(bank_id);
-            k.flag_base = epoch_base + r * 4;
+            k.flag_base = epoch_base + r * kRoundFlags;
             k.src = static_cast<const uint8_t *>(a.src) + off * esz;
             k.dst = static_cast<uint8_t *>(a.dst) + off * esz;
             k.count = n;
@@ -594,7 +596,7 @@ public:
             int rc;
             // warp-specialised pipeline (copy-in || switch reduction || copy-out) for staged operands of one round; not for
             // in-place operands, whose output may only be written once the whole reduction is known to be complete
-            const bool kernel_pipeline = mc_view && !ssym.ok && !dsym.ok && quant == 0 && n_rounds == 1 && !in_place &&
+            const bool kernel_pipeline = mc_view && !ssym.ok && !dsym.ok && quant == 0 && !in_place &&
                                          n * esz >= pipeline_min_bytes_ && (tune_ ? env_flag("PCCL_KERNEL_PIPELINE", kernel_pipeline_) : kernel_pipeline_);
             const int segments = static_cast<int>(tune_ ? env_u64("PCCL_PIPELINE_SEGMENTS", 0) : pipeline_segments_);
             if (a.outer) {

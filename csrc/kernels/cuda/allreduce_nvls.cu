@@ -595,7 +595,7 @@ extern "C" int pcclKernelOuterStepNvls(const pcclKernelNvlsArgs_t *args, const p
 static void pipeline_geometry(uint64_t n_pack, uint32_t world, int requested, uint32_t &n_seg, uint64_t &seg_pack) {
     uint64_t want = requested > 0 ? static_cast<uint64_t>(requested)
                                   : static_cast<uint64_t>(5.2 * std::sqrt(static_cast<double>(n_pack) * 16.0 / 6.0e8) + 0.5);
-    want = std::min<uint64_t>(24, std::max<uint64_t>(2, want));
+    want = std::min<uint64_t>(24, std::max<uint64_t>(2, want)); // segments + 2 barrier values must fit the caller's flag budget (32)
     const uint64_t unit = uint64_t(world) * kNvlsThreads;
     seg_pack = ((n_pack + want - 1) / want + unit - 1) / unit * unit;
     n_seg = static_cast<uint32_t>((n_pack + seg_pack - 1) / seg_pack);

@@ -33,11 +33,37 @@ def device_numa_node(device_index: int) -> int | None:
         return None
 
 
+def _affinity_from_nvidia_smi(device_index: int) -> set[int]:
+    """CPU affinity of a GPU as `nvidia-smi topo -m` reports it (containers often hide the sysfs NUMA node)."""
+    import re
+    import subprocess
+    try:
+        out = subprocess.run(["nvidia-smi", "topo", "-m"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True, timeout=20).stdout
+    except Exception:
+        return set()
+    for line in out.splitlines():
+        cells = [c for c in re.split(r"\t+|\s{2,}", re.sub(r"\x1b\[[0-9;]*m", "", line).strip()) if c]
+        if not cells or cells[0] != f"GPU{device_index}":
+            continue
+        for c in cells[1:]:
+            if re.fullmatch(r"\d+(-\d+)?(,\d+(-\d+)?)*", c) and ("-" in c or "," in c):
+                return _parse_cpulist(c)
+    return set()
+
+
 def bind_to_device(device_index: int) -> dict:
     """Restricts the calling process to the CPUs of the GPU's memory node (so later allocations, pinned ones included,
     are local to it).  Does nothing, and says why, when the topology is unknown.  Returns a small report."""
     node = device_numa_node(device_index)
     if node is None:
+        cpus = _affinity_from_nvidia_smi(device_index)
+        try:
+            target = cpus & os.sched_getaffinity(0)
+            if target and len(target) < len(os.sched_getaffinity(0)):
+                os.sched_setaffinity(0, target)
+                return {"bound": True, "source": "nvidia-smi topo", "cpus": len(target)}
+        except Exception as e:  # noqa: BLE001
+            return {"bound": False, "reason": str(e)}
         return {"bound": False, "reason": "no NUMA information for the device"}
     try:
         cpus = _parse_cpulist(Path(f"/sys/devices/system/node/node{node}/cpulist").read_text())
