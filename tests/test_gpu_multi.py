@@ -148,3 +148,40 @@ def test_reduction_overlaps_with_compute_on_another_stream(world):
     print({"overlap_ms": [r.get("overlap_ms") for r in results]})
     for r in results:
         assert r["ok"], r
+
+
+@pytest.mark.parametrize("mode", ["sync", "async"])
+def test_diloco_training_with_a_late_joiner_on_gpus(mode):
+    """Training-level check on the device plane (the reference's MNIST tier with a late joiner and CUDA shared state,
+    python/tests/end_to_end/mnist_ddp/mnist_ddp_e2e_test.py): two peers train a small GPT with DiLoCo on two GPUs, a third
+    process joins mid-run, everybody finishes, the loss goes down and the joiner took over the run's step counter."""
+    import os
+    import re
+    import time
+    if gpu_count() < 2:
+        pytest.skip("needs >= 2 GPUs")
+    n = gpu_count()
+    repo = HERE.parent
+    with pccl.MasterNode("127.0.0.1:0") as master:
+        master.run()
+        base = [sys.executable, str(repo / "examples" / "diloco.py"), "--master", f"127.0.0.1:{master.port}", "--mode", mode, "--inner-steps", "4",
+                "--batch", "4"]
+        env = dict(os.environ, PCCL_DEVICE_TIMEOUT_MS="8000")
+        old = [subprocess.Popen(base + ["--device", f"cuda:{i}", "--outer-steps", "60", "--min-peers", "2"], stdout=subprocess.PIPE,
+                                stderr=subprocess.STDOUT, text=True, env=env) for i in range(2)]
+        time.sleep(12)
+        new = subprocess.Popen(base + ["--device", f"cuda:{2 if n > 2 else 1}", "--outer-steps", "15", "--min-peers", "3"], stdout=subprocess.PIPE,
+                               stderr=subprocess.STDOUT, text=True, env=env)
+        out_new, _ = new.communicate(timeout=400)
+        outs = [p.communicate(timeout=400)[0] for p in old]
+    assert new.returncode == 0, out_new[-3000:]
+    assert "world 3" in out_new
+    first = re.search(r"outer step 0: .* run step (\d+)", out_new)
+    assert first and int(first.group(1)) > 1, out_new[:1500]
+    for p, out in zip(old, outs):
+        assert p.returncode == 0, out[-3000:]
+        losses = [float(m) for m in re.findall(r"outer step \d+: loss ([0-9.]+)", out)]
+        assert len(losses) == 60 and sum(losses[-5:]) / 5 < sum(losses[:5]) / 5 - 0.5, losses[:5] + losses[-5:]
+        assert "world 3" in out
+        if n > 2 and mode == "sync":
+            assert "plane p2p" in out or "plane nvls" in out, "peers on distinct GPUs must reduce on the device plane"
