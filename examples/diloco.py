@@ -148,7 +148,9 @@ def main():
                 # shared state is only synchronised when the topology changed (reference: async_diloco.py:419-431,448-451)
                 algo.admit_peers(sync)
             else:
-                if comm.get_attribute(pccl.Attribute.GLOBAL_WORLD_SIZE) < 2 or comm.are_peers_pending():
+                # not in the first iteration: a peer that has just been admitted went through the topology round already, and
+                # the others are waiting for it in the shared-state synchronisation (reference: sync_diloco.py, local_iter_num > 1)
+                if it > 0 and (comm.get_attribute(pccl.Attribute.GLOBAL_WORLD_SIZE) < 2 or comm.are_peers_pending()):
                     comm.update_topology()
                 if comm.get_attribute(pccl.Attribute.PEER_GROUP_WORLD_SIZE) > 1:
                     with prof.section("shared_state"):

@@ -218,6 +218,37 @@ def main():
         for it in range(3):
             comm.all_reduce(x, y, op=pccl.ReduceOp.SUM, tag=0)
             check(f"after_host_{it}", y, expected(900, world, 256, torch.float32, pccl.ReduceOp.SUM), comm.ext_last_reduce_stats(0), it > 0)
+    elif scenario == "trusted_hashes":
+        n = 3_000_001
+        comm.ext_trust_content_hashes(True)
+        start = make_input(500, 0, n, torch.float32)
+        params = start.clone().to(dev)
+        inner = (start - 0.01 * make_input(520, rank, n, torch.float32)).to(dev)
+        mom = torch.zeros(n, device=dev)
+        state = pccl.SharedState([pccl.TensorInfo.from_torch(params, "params"), pccl.TensorInfo.from_torch(mom, "momentum")])
+        state.revision = 1
+        info0 = comm.sync_shared_state(state)  # first check: hashes computed by the (batched) hash kernels
+        skipped0 = comm.ext_hash_kernels_skipped()
+        for k in range(2):
+            comm.ext_diloco_outer_step(params, inner, mom, lr=0.7, mu=0.9, first=k == 0, tag=3)
+            st = comm.ext_last_reduce_stats(3)
+            state.push_revision()
+            before = comm.ext_hash_kernels_skipped()
+            info = comm.sync_shared_state(state)
+            ok = (st["content_hash"] is not None and st["content_hash"][0] == ops.mset64(params) and st["content_hash"][1] == ops.mset64(mom)
+                  and comm.ext_hash_kernels_skipped() - before == 2 and info.tx_bytes == 0 and info.rx_bytes == 0 and st["kernel_launches"] == 1)
+            ok_all = ok_all and ok
+            results["cases"].append({"id": f"trusted_{k}", "ok": bool(ok), "skipped": comm.ext_hash_kernels_skipped() - before, "plane": st["plane"],
+                                     "leased": st["leased"]})
+            inner.sub_(0.001 * make_input(530 + k, rank, n, torch.float32).to(dev))
+        # a tensor the caller changed through the library's back is the caller's business; one the LIBRARY changed loses its record
+        comm.all_reduce(mom, mom, op=pccl.ReduceOp.AVG, tag=4)
+        before = comm.ext_hash_kernels_skipped()
+        state.push_revision()
+        comm.sync_shared_state(state)
+        ok = comm.ext_hash_kernels_skipped() - before == 1  # params still known, momentum hashed afresh
+        ok_all = ok_all and ok and skipped0 == 0 and info0.rx_bytes == 0
+        results["cases"].append({"id": "record_dropped_on_library_write", "ok": bool(ok)})
     elif scenario == "overlap":
         # A local compute kernel on another stream runs WHILE a large reduction is in flight: the reduction is stream
         # ordered (no host or device synchronisation) and, with an SM budget below the whole GPU (PCCL_DEVICE_MAX_BLOCKS),

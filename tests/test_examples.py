@@ -106,6 +106,26 @@ def test_diloco_example_checkpoint_and_resume(master, tmp_path):
         assert "run step 6" in o and "world 2" in o, o[-2000:]
 
 
+def test_sync_diloco_late_joiner(master):
+    """A peer that joins a synchronous run mid-way takes part from the next outer step with the run's parameters."""
+    import time
+    base = [sys.executable, str(REPO / "examples" / "diloco.py"), "--master", f"127.0.0.1:{master.port}", "--device", "cpu", "--mode", "sync",
+            "--inner-steps", "2", "--batch", "2"]
+    old = [subprocess.Popen(base + ["--outer-steps", "40", "--min-peers", "2"], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, env=_env())
+           for _ in range(2)]
+    time.sleep(6)
+    new = subprocess.Popen(base + ["--outer-steps", "12", "--min-peers", "3"], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, env=_env())
+    out_new, _ = new.communicate(timeout=300)
+    assert new.returncode == 0, out_new[-4000:]
+    assert "world 3" in out_new, out_new[-3000:]
+    first = re.search(r"outer step 0: .* run step (\d+)", out_new)
+    assert first and int(first.group(1)) > 1, out_new[:2000]
+    for p in old:
+        out, _ = p.communicate(timeout=300)
+        assert p.returncode == 0, out[-4000:]
+        assert "world 3" in out, out[-3000:]
+
+
 def test_async_diloco_late_joiner_is_inserted_into_the_pipeline(master):
     """Two peers train in the one-step-delayed mode; a third joins mid-run.  The members apply the reduction the joiner
     missed and re-send the shared state (SEND_ONLY), the joiner receives it (RECEIVE_ONLY) -- reference:

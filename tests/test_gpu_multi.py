@@ -172,8 +172,13 @@ def test_diloco_training_with_a_late_joiner_on_gpus(mode):
         time.sleep(12)
         new = subprocess.Popen(base + ["--device", f"cuda:{2 if n > 2 else 1}", "--outer-steps", "15", "--min-peers", "3"], stdout=subprocess.PIPE,
                                stderr=subprocess.STDOUT, text=True, env=env)
-        out_new, _ = new.communicate(timeout=400)
-        outs = [p.communicate(timeout=400)[0] for p in old]
+        try:
+            out_new, _ = new.communicate(timeout=120)
+            outs = [p.communicate(timeout=120)[0] for p in old]
+        finally:
+            for p in old + [new]:
+                if p.poll() is None:
+                    p.kill()
     assert new.returncode == 0, out_new[-3000:]
     assert "world 3" in out_new
     first = re.search(r"outer step 0: .* run step (\d+)", out_new)
@@ -185,3 +190,11 @@ def test_diloco_training_with_a_late_joiner_on_gpus(mode):
         assert "world 3" in out
         if n > 2 and mode == "sync":
             assert "plane p2p" in out or "plane nvls" in out, "peers on distinct GPUs must reduce on the device plane"
+
+
+@pytest.mark.parametrize("world", worlds()[:2] or [pytest.param(2, marks=pytest.mark.skip(reason="needs >= 2 GPUs"))])
+def test_outer_step_hashes_make_the_next_shared_state_check_free(world):
+    """With the mset64 hash type and trusted content hashes the fused outer step hashes parameters and momentum while it
+    writes them; the following shared-state synchronisation launches no hash kernel for them and moves nothing."""
+    for r in run_peers(world, "trusted_hashes", timeout=200, env={"PCCL_SHARED_STATE_HASH": "mset"}):
+        assert r["ok"], r
