@@ -1363,6 +1363,8 @@ ReduceOutcome Client::run_reduce_impl(const ReduceRequest &req, uint64_t) {
     const bool use_nvls = use_device && ((go->seq_nr >> 62) & 1) != 0;
     const uint64_t seq = go->seq_nr & ~(15ull << 60);
     out.stats.seq_nr = seq;
+    // bit 61 also says that every peer holds the same-box sequencer: the operation is ordered through it
+    dargs.sequenced = use_device && ((go->seq_nr >> 61) & 1) != 0;
     if (use_device && offer_lease && ((go->seq_nr >> 61) & 1) != 0) {
         // lease granted: the NEXT operation on this tag skips the vote (every peer decides so from this same packet)
         lease_mc_all_ = ((go->seq_nr >> 60) & 1) != 0;

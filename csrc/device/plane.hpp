@@ -62,6 +62,9 @@ struct DeviceReduceArgs {
     // lease path (no vote at the master): the operation is identified by (tag, lease_k) in the same-box sequencer
     bool leased = false;
     uint64_t tag = 0, lease_k = 0;
+    // voted operations: every peer of the group holds the same-box sequencer (agreed through the master, like the plane), so
+    // the operation takes its place and its resources from the common log; otherwise it runs in Commence order
+    bool sequenced = false;
     bool want_hash = false; // produce the mset64 digest(s) of the output as a by-product
     void *user_stream = nullptr; // non-null: order the operation after this CUDA stream instead of the legacy default stream
     bool enqueue_only = false;   // return after the launch; the caller finishes with Plane::finish()

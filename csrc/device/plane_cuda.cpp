@@ -450,8 +450,12 @@ public:
 
         // ---- place in the common order
         std::unique_lock<std::mutex> launch(launch_mu_);
-        const bool sequenced = sequencer_.attached();
-        if (a.leased && !sequenced) return res;
+        // (a peer whose sequencer set-up failed must not diverge from the others: whether the log is used is part of the vote)
+        const bool sequenced = sequencer_.attached() && (a.leased || a.sequenced);
+        if ((a.leased || a.sequenced) && !sequenced) {
+            if (!a.leased) cancel(a.seq);
+            return res;
+        }
         uint64_t index = 0;
         bool queue_turn = false;
         if (sequenced) {

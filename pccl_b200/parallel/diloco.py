@@ -99,7 +99,7 @@ class DiLoCo:
         is a single kernel per peer.  With wire quantisation the three stages run separately (the quantised
         reduction needs the pseudo-gradient in memory)."""
         if self.quantization is None:
-            while True:
+            for attempt in range(64):  # every failed attempt has re-established the ring; something is wrong if that never helps
                 try:
                     self.last_info = self.comm.ext_diloco_outer_step(self.params, inner, self.buf, lr=self.lr, mu=self.mu,
                                                                      first=self.steps == 0, tag=tag)
@@ -108,7 +108,7 @@ class DiLoCo:
                 except PCCLError as e:
                     if e.result == Result.TOO_FEW_PEERS:
                         break  # alone: apply the local pseudo-gradient below
-                    if e.result != Result.RANK_CONNECTION_LOST:
+                    if e.result != Result.RANK_CONNECTION_LOST or attempt == 63:
                         raise
         if self.grad is None:
             self.grad = torch.empty_like(self.params)

@@ -151,7 +151,7 @@ def test_reduction_overlaps_with_compute_on_another_stream(world):
 
 
 @pytest.mark.parametrize("mode", ["sync", "async"])
-def test_diloco_training_with_a_late_joiner_on_gpus(mode):
+def test_diloco_training_with_a_late_joiner_on_gpus(mode, tmp_path):
     """Training-level check on the device plane (the reference's MNIST tier with a late joiner and CUDA shared state,
     python/tests/end_to_end/mnist_ddp/mnist_ddp_e2e_test.py): two peers train a small GPT with DiLoCo on two GPUs, a third
     process joins mid-run, everybody finishes, the loss goes down and the joiner took over the run's step counter."""
@@ -162,29 +162,36 @@ def test_diloco_training_with_a_late_joiner_on_gpus(mode):
         pytest.skip("needs >= 2 GPUs")
     n = gpu_count()
     repo = HERE.parent
+    logs = [tmp_path / f"peer{i}.log" for i in range(3)]
     with pccl.MasterNode("127.0.0.1:0") as master:
         master.run()
-        base = [sys.executable, str(repo / "examples" / "diloco.py"), "--master", f"127.0.0.1:{master.port}", "--mode", mode, "--inner-steps", "4",
+        base = [sys.executable, "-u", str(repo / "examples" / "diloco.py"), "--master", f"127.0.0.1:{master.port}", "--mode", mode, "--inner-steps", "4",
                 "--batch", "4"]
-        env = dict(os.environ, PCCL_DEVICE_TIMEOUT_MS="8000")
-        old = [subprocess.Popen(base + ["--device", f"cuda:{i}", "--outer-steps", "60", "--min-peers", "2"], stdout=subprocess.PIPE,
-                                stderr=subprocess.STDOUT, text=True, env=env) for i in range(2)]
+        env = dict(os.environ, PCCL_DEVICE_TIMEOUT_MS="8000", PCCL_LOG_LEVEL="INFO")
+
+        def start(i, device, steps, min_peers):
+            return subprocess.Popen(base + ["--device", device, "--outer-steps", str(steps), "--min-peers", str(min_peers)], stdout=open(logs[i], "w"),
+                                    stderr=subprocess.STDOUT, env=env)
+
+        procs = [start(0, "cuda:0", 60, 2), start(1, "cuda:1", 60, 2)]
         time.sleep(12)
-        new = subprocess.Popen(base + ["--device", f"cuda:{2 if n > 2 else 1}", "--outer-steps", "15", "--min-peers", "3"], stdout=subprocess.PIPE,
-                               stderr=subprocess.STDOUT, text=True, env=env)
-        try:
-            out_new, _ = new.communicate(timeout=120)
-            outs = [p.communicate(timeout=120)[0] for p in old]
-        finally:
-            for p in old + [new]:
-                if p.poll() is None:
-                    p.kill()
-    assert new.returncode == 0, out_new[-3000:]
-    assert "world 3" in out_new
+        procs.append(start(2, f"cuda:{2 if n > 2 else 1}", 15, 3))
+        deadline = time.time() + 150
+        while time.time() < deadline and any(p.poll() is None for p in procs):
+            time.sleep(0.5)
+        hung = [i for i, p in enumerate(procs) if p.poll() is None]
+        for p in procs:
+            if p.poll() is None:
+                p.kill()
+    outs = [log.read_text() for log in logs]
+    tails = "\n".join(f"--- peer {i} (rc {procs[i].returncode}) ---\n{o[-1800:]}" for i, o in enumerate(outs))
+    assert not hung, f"peers {hung} did not finish\n{tails}"
+    assert all(p.returncode == 0 for p in procs), tails
+    out_new = outs[2]
+    assert "world 3" in out_new, tails
     first = re.search(r"outer step 0: .* run step (\d+)", out_new)
     assert first and int(first.group(1)) > 1, out_new[:1500]
-    for p, out in zip(old, outs):
-        assert p.returncode == 0, out[-3000:]
+    for out in outs[:2]:
         losses = [float(m) for m in re.findall(r"outer step \d+: loss ([0-9.]+)", out)]
         assert len(losses) == 60 and sum(losses[-5:]) / 5 < sum(losses[:5]) / 5 - 0.5, losses[:5] + losses[-5:]
         assert "world 3" in out
