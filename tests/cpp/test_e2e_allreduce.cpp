@@ -4,6 +4,7 @@
 #include <numeric>
 
 #include "e2e_util.hpp"
+#include "net/blocking_socket.hpp"
 #include "util/guarded_alloc.hpp"
 
 using namespace pccl;
@@ -387,6 +388,130 @@ TEST(outer_step_host_tensors) {
                 CHECK(params[r][i] == params[0][i]); // bit-identical on all peers
             }
     }
+}
+
+// ---- lease extension of the collective vote, spoken by hand: two scripted peers on raw sockets (a real peer only offers a
+// lease when it has a device plane, which this CPU test does not) -----------------------------------------------------
+namespace {
+ccoip_socket_address_t loopback(uint16_t port) {
+    ccoip_socket_address_t a{};
+    a.inet.protocol = inetIPv4;
+    a.inet.ipv4.data[0] = 127;
+    a.inet.ipv4.data[3] = 1;
+    a.port = port;
+    return a;
+}
+struct ScriptedPeer {
+    net::BlockingSocket sock;
+    Uuid uuid;
+    explicit ScriptedPeer(uint16_t master_port) : sock(loopback(master_port)) {
+        CHECK(sock.connect(5000));
+        wire::C2MSessionRegistration reg;
+        reg.p2p_port = 1;
+        reg.ss_port = 2;
+        reg.bm_port = 3;
+        CHECK(sock.send_packet(reg));
+        const auto resp = sock.recv_packet<wire::M2CSessionRegistrationResponse>(5000);
+        CHECK(resp && resp->accepted);
+        uuid = resp->assigned_uuid;
+    }
+    void finish_round() { // answer the connection info with "links established", take the verdict
+        CHECK(sock.recv_packet<wire::M2CP2PConnectionInfo>(5000).has_value());
+        wire::C2MP2PEstablished ok;
+        ok.success = true;
+        CHECK(sock.send_packet(ok));
+        const auto verdict = sock.recv_packet<wire::M2CP2PEstablished>(5000);
+        CHECK(verdict && verdict->success);
+    }
+    void vote(uint64_t tag, uint8_t bits) {
+        wire::C2MCollectiveInitiate v;
+        v.tag = tag;
+        v.count = 4;
+        v.op = static_cast<wire::RedOp>(static_cast<uint8_t>(wire::RedOp::Sum) | bits);
+        CHECK(sock.send_packet(v));
+    }
+    uint64_t commence(uint64_t tag) {
+        const auto go = sock.recv_packet<wire::M2CCollectiveCommence>(5000);
+        CHECK(go && go->tag == tag);
+        return go->seq_nr;
+    }
+    void complete(uint64_t tag) {
+        wire::C2MCollectiveComplete done;
+        done.tag = tag;
+        CHECK(sock.send_packet(done));
+    }
+    void finish(uint64_t tag) {
+        const auto ab = sock.recv_packet<wire::M2CCollectiveAbort>(5000);
+        CHECK(ab && ab->tag == tag && !ab->aborted);
+        const auto done = sock.recv_packet<wire::M2CCollectiveComplete>(5000);
+        CHECK(done && done->tag == tag);
+    }
+};
+} // namespace
+
+TEST(master_grants_and_revokes_leases) {
+    TestMaster tm;
+    ScriptedPeer a(tm.port);
+    a.finish_round(); // the first peer is admitted at once
+    std::unique_ptr<ScriptedPeer> b;
+    std::thread joiner([&] {
+        b = std::make_unique<ScriptedPeer>(tm.port);
+        b->finish_round();
+    });
+    std::this_thread::sleep_for(std::chrono::milliseconds(200));
+    wire::C2MEstablishP2P admit;
+    admit.accept_new_peers = true;
+    CHECK(a.sock.send_packet(admit));
+    a.finish_round();
+    joiner.join();
+
+    auto run_op = [&](uint64_t tag, uint8_t bits_a, uint8_t bits_b) {
+        a.vote(tag, bits_a);
+        b->vote(tag, bits_b);
+        const uint64_t sa = a.commence(tag), sb = b->commence(tag);
+        CHECK_EQ(sa, sb);
+        a.complete(tag);
+        b->complete(tag);
+        a.finish(tag);
+        b->finish(tag);
+        return sa;
+    };
+    // device plane + lease offer + multicast view from both: granted (bits 63, 61, 60; NVLS bit 62 was not offered)
+    uint64_t s = run_op(7, 0x80 | 0x20 | 0x10, 0x80 | 0x20 | 0x10);
+    CHECK((s >> 63) == 1 && ((s >> 62) & 1) == 0 && ((s >> 61) & 1) == 1 && ((s >> 60) & 1) == 1);
+    // one peer without the multicast view: lease yes, multicast no
+    s = run_op(8, 0x80 | 0x20 | 0x10, 0x80 | 0x20);
+    CHECK(((s >> 61) & 1) == 1 && ((s >> 60) & 1) == 0);
+    // one peer does not offer a lease (or cannot use the device plane): no lease, and a reference peer never sets any of the bits
+    s = run_op(9, 0x80 | 0x20, 0x80);
+    CHECK((s >> 63) == 1 && ((s >> 61) & 1) == 0);
+    s = run_op(10, 0x80 | 0x20, 0);
+    CHECK((s >> 60) == 0);
+
+    // a vote on a leased tag ends that tag's lease for everybody -- and only that tag's -- before the vote proceeds
+    a.vote(7, 0);
+    {
+        const auto rv = a.sock.recv_packet<wire::M2CLeaseRevoked>(5000);
+        CHECK(rv && rv->tag == 7 && !rv->all && !rv->peer_lost);
+        const auto rv2 = b->sock.recv_packet<wire::M2CLeaseRevoked>(5000);
+        CHECK(rv2 && rv2->tag == 7 && !rv2->all);
+    }
+    b->vote(7, 0);
+    s = a.commence(7);
+    CHECK_EQ(b->commence(7), s);
+    CHECK((s >> 60) == 0); // host buffers this time: no device plane, no new lease
+    a.complete(7);
+    b->complete(7);
+    a.finish(7);
+    b->finish(7);
+    // voting again on the now unleased tag revokes nothing
+    s = run_op(7, 0x80 | 0x20, 0x80 | 0x20);
+    CHECK(((s >> 61) & 1) == 1);
+
+    // a member vanishes: the survivor is told that every lease is gone and why
+    b.reset();
+    const auto lost = a.sock.recv_packet<wire::M2CLeaseRevoked>(5000);
+    CHECK(lost && lost->all && lost->peer_lost);
 }
 
 TEST_MAIN()
