@@ -199,6 +199,31 @@ def test_multi_process_peers_on_cpu(scenario):
         assert r["ok"], r
 
 
+@pytest.mark.parametrize("hash_type", ["mset", "crc32"])
+def test_shared_state_with_the_other_hash_types(hash_type):
+    """PCCL_SHARED_STATE_HASH switches the content hash of the whole run: mset64 (the order-independent hash the collective
+    kernels produce as a by-product; host twin here) and CRC32C decide "who is outdated" exactly like simplehash does."""
+    for r in run_peers(3, "shared_state", devices=["cpu"] * 3, env={"PCCL_SHARED_STATE_HASH": hash_type}):
+        assert r["ok"], r
+
+
+def test_stream_api_degrades_gracefully_on_host_tensors():
+    """all_reduce(enqueue=True) on host tensors is the ordinary blocking call; waiting for enqueued operations when there are
+    none succeeds."""
+    def body(r, c):
+        x = torch.full((1000,), float(r + 1))
+        c.all_reduce(x, x, op=pccl.ReduceOp.SUM, tag=3, enqueue=True)
+        c.ext_wait_stream_ops()
+        c.ext_wait_stream_ops(3)
+        c.ext_trust_content_hashes(True)
+        assert c.ext_hash_kernels_skipped() == 0
+        st = c.ext_last_reduce_stats(3)
+        assert st["plane"] == "tcp_ring" and not st["leased"] and st["content_hash"] is None
+        return float(x[0])
+
+    assert run_threads(2, body) == {0: 3.0, 1: 3.0}
+
+
 def test_diloco_cpu_matches_torch_sgd():
     from pccl_b200.parallel import DiLoCo
 
