@@ -6,6 +6,7 @@
 #include <future>
 #include <random>
 #include <thread>
+#include <unistd.h>
 
 #include "../kernels/cpu/hash.hpp"
 #include "../kernels/cpu/reduce.hpp"
@@ -38,6 +39,34 @@ Client::Client(const ClientConfig &cfg)
     ss_workers_ = std::make_unique<ThreadPool>(2, 64);
     bm_workers_ = std::make_unique<ThreadPool>(static_cast<size_t>(env_u64("PCCL_NUM_BENCHMARK_CONNECTIONS", 16)) + 1, 64);
     lease_enabled_ = env_flag("PCCL_LEASE", true);
+    // which host this peer runs on, for the two-level all-reduce of groups that span hosts
+    auto fnv = [](const std::string &text) {
+        uint64_t h = 1469598103934665603ull;
+        for (unsigned char c : text) h = (h ^ c) * 1099511628211ull;
+        return h ? h : 1;
+    };
+    const char *host_env = std::getenv("PCCL_HOST_ID");
+    if (cfg_.host_id) {
+        host_id_ = cfg_.host_id;
+    } else if (host_env && *host_env) {
+        host_id_ = fnv(host_env);
+    } else {
+        char name[256] = {0};
+        ::gethostname(name, sizeof name - 1);
+        std::string id = name;
+        if (FILE *f = std::fopen("/proc/sys/kernel/random/boot_id", "r")) {
+            char boot[64] = {0};
+            if (std::fgets(boot, sizeof boot, f)) id += boot;
+            std::fclose(f);
+        }
+        host_id_ = fnv(id);
+    }
+    if (cfg_.hierarchy >= 0)
+        hierarchy_enabled_ = cfg_.hierarchy != 0;
+    else if (const char *v = std::getenv("PCCL_HIERARCHY"))
+        hierarchy_enabled_ = v[0] != '0';
+    else
+        hierarchy_enabled_ = !net::is_loopback(cfg_.master) || cfg_.host_id != 0 || (host_env && *host_env);
 }
 
 Client::~Client() {
@@ -92,7 +121,7 @@ bool Client::connect() {
         }
         if (id != M2CCollectiveCommence::id) return;
         M2CCollectiveCommence c;
-        if (c.read(r) && (c.seq_nr >> 63)) plane_->announce(c.seq_nr & ~(15ull << 60));
+        if (c.read(r) && (c.seq_nr >> 63)) plane_->announce(c.seq_nr & ~(31ull << 59));
     });
     master_.run();
 
@@ -232,6 +261,7 @@ Client::Establish Client::establish_round() {
 
     C2MP2PEstablished report;
     report.success = true;
+    if (!info->unchanged) last_neighbours_ = info->peers;
     if (!info->unchanged) {
         for (const auto &peer : info->peers) {
             bool have = false;
@@ -297,7 +327,140 @@ Client::Establish Client::establish_round() {
         lease_counts_.clear();
     }
     plane_->on_ring_changed(verdict->ring_order);
+    build_hierarchy(verdict->ring_order);
     return Establish::Success;
+}
+
+// Two-level layout for rings that span hosts.  The peers first learn each other's host and address: a P2PDirectory packet
+// travels around the ring like an all-gather (world-1 hops), every peer contributing its own host identity and the endpoint
+// of its successor (the master only tells a peer about its neighbours).  If the ring turns out to be B >= 2 hosts with the
+// same number L >= 2 of peers each, links to the local successor and to the peer of equal local rank on the next host are
+// dialled.  Whether an operation then uses the hierarchy is agreed through the vote (bit 3 of the operator byte), so a peer
+// on which any of this failed -- or a reference peer, which does not forward the directory -- simply keeps the ring flat
+// for everybody.  The flat ring remains wired and is what quantised operations use.
+void Client::build_hierarchy(const std::vector<Uuid> &ring) {
+    {
+        std::unique_lock<std::shared_mutex> lock(ring_mu_);
+        hier_ = Hierarchy{};
+    }
+    const uint32_t W = static_cast<uint32_t>(ring.size());
+    if (!hierarchy_enabled_ || W < 4) return;
+    const auto me = std::find(ring.begin(), ring.end(), uuid_);
+    if (me == ring.end()) return;
+    const uint32_t r = static_cast<uint32_t>(me - ring.begin());
+    const Uuid &next = ring[(r + 1) % W], &prev = ring[(r + W - 1) % W];
+    Pool tx;
+    {
+        std::lock_guard<std::mutex> lock(tx_mu_);
+        const auto it = tx_pools_.find(next);
+        if (it != tx_pools_.end()) tx = it->second;
+    }
+    const Pool rx = pick_rx_pool(prev, 3000);
+    if (tx.empty() || rx.empty()) return;
+
+    constexpr uint64_t kDirectoryTag = 0xD17EC7027A6ull;
+    uint64_t seq = 1469598103934665603ull; // the same on every member of this ring, different for another ring
+    for (const auto &u : ring)
+        for (uint8_t b : u.data) seq = (seq ^ b) * 1099511628211ull;
+    seq &= (1ull << 59) - 1;
+
+    std::unordered_map<Uuid, DirectoryEntry> known;
+    auto merge = [&](const DirectoryEntry &e) {
+        DirectoryEntry &k = known[e.uuid];
+        k.uuid = e.uuid;
+        if (e.has_host) {
+            k.has_host = true;
+            k.host_id = e.host_id;
+        }
+        if (e.has_endpoint) {
+            k.has_endpoint = true;
+            k.endpoint = e.endpoint;
+        }
+    };
+    P2PDirectory mine;
+    {
+        DirectoryEntry self;
+        self.uuid = uuid_;
+        self.has_host = true;
+        self.host_id = host_id_;
+        mine.entries.push_back(self);
+        for (const auto &p : last_neighbours_)
+            if (p.uuid == next) {
+                DirectoryEntry succ;
+                succ.uuid = next;
+                succ.has_endpoint = true;
+                succ.endpoint = p.p2p_addr;
+                mine.entries.push_back(succ);
+            }
+    }
+    for (const auto &e : mine.entries) merge(e);
+    P2PDirectory cur = mine;
+    const auto deadline = clock_type::now() + std::chrono::seconds(3);
+    for (uint32_t step = 0; step + 1 < W; ++step) {
+        if (!tx[0]->send_packet(kDirectoryTag, seq, cur)) return;
+        std::optional<P2PDirectory> got;
+        while (!got) {
+            got = rx[0]->recv_packet<P2PDirectory>(kDirectoryTag, seq, 20);
+            if (!got && (clock_type::now() > deadline || interrupted_ || !rx[0]->is_open())) {
+                PLOG(INFO) << "peer directory did not come round (a peer of another build in the ring?): the ring stays flat";
+                return;
+            }
+        }
+        for (const auto &e : got->entries) merge(e);
+        cur = std::move(*got);
+    }
+
+    // hosts in the order in which the ring first visits them; every host must hold the same number of peers
+    std::vector<uint64_t> hosts;
+    std::unordered_map<uint64_t, std::vector<Uuid>> members;
+    for (const auto &u : ring) {
+        const auto it = known.find(u);
+        if (it == known.end() || !it->second.has_host) return;
+        if (!members.count(it->second.host_id)) hosts.push_back(it->second.host_id);
+        members[it->second.host_id].push_back(u);
+    }
+    const uint32_t B = static_cast<uint32_t>(hosts.size());
+    const uint32_t L = static_cast<uint32_t>(members[hosts[0]].size());
+    if (B < 2 || L < 2) return;
+    for (uint64_t h : hosts)
+        if (members[h].size() != L) {
+            PLOG(INFO) << "hosts hold different numbers of peers: the ring stays flat";
+            return;
+        }
+    Hierarchy h;
+    h.B = B;
+    h.L = L;
+    h.box = static_cast<uint32_t>(std::find(hosts.begin(), hosts.end(), host_id_) - hosts.begin());
+    if (h.box >= B) return;
+    const auto &local = members[host_id_];
+    h.local_rank = static_cast<uint32_t>(std::find(local.begin(), local.end(), uuid_) - local.begin());
+    h.local_next = local[(h.local_rank + 1) % L];
+    h.local_prev = local[(h.local_rank + L - 1) % L];
+    h.cross_next = members[hosts[(h.box + 1) % B]][h.local_rank];
+    h.cross_prev = members[hosts[(h.box + B - 1) % B]][h.local_rank];
+    for (const Uuid *target : {&h.local_next, &h.cross_next}) {
+        bool have;
+        {
+            std::lock_guard<std::mutex> lock(tx_mu_);
+            const auto it = tx_pools_.find(*target);
+            have = it != tx_pools_.end() && !it->second.empty() &&
+                   std::all_of(it->second.begin(), it->second.end(), [](const auto &s) { return s && s->is_open(); });
+        }
+        if (have) continue;
+        const auto it = known.find(*target);
+        if (it == known.end() || !it->second.has_endpoint) return;
+        PeerEndpoint ep;
+        ep.uuid = *target;
+        ep.p2p_addr = it->second.endpoint;
+        if (!dial_peer(ep)) {
+            PLOG(WARN) << "cannot reach " << target->str() << " for the two-level ring: the ring stays flat";
+            return;
+        }
+    }
+    h.ready = true;
+    PLOG(INFO) << "two-level ring: " << B << " hosts x " << L << " peers, this peer is (" << h.box << ", " << h.local_rank << ")";
+    std::unique_lock<std::shared_mutex> lock(ring_mu_);
+    hier_ = h;
 }
 
 bool Client::request_and_establish(bool accept_new_peers) {
@@ -1311,9 +1474,16 @@ ReduceOutcome Client::run_reduce_impl(const ReduceRequest &req, uint64_t) {
     // (bit 6 / bit 62 do the same for the NVSwitch multicast variant)
     // (bit 5: this peer would run LATER operations on this tag under a lease; bit 4: it holds the multicast view)
     const bool offer_lease = lease_enabled_ && device_capable && plane_->lease_ready();
+    // (bit 3: this peer has the two-level layout of a multi-host ring wired and would use it for this operation)
+    Hierarchy hier;
+    {
+        std::shared_lock<std::shared_mutex> lock(ring_mu_);
+        hier = hier_;
+    }
+    const bool offer_hierarchy = hier.ready && req.quant == QuantAlgo::None && hier.L * hier.B == world;
     vote.op = static_cast<RedOp>(static_cast<uint8_t>(req.op) | (device_capable ? 0x80u : 0u) |
                                  ((caps & device::Plane::kCapNvls) ? 0x40u : 0u) | (offer_lease ? 0x20u : 0u) |
-                                 (offer_lease && plane_->multicast_ready() ? 0x10u : 0u));
+                                 (offer_lease && plane_->multicast_ready() ? 0x10u : 0u) | (offer_hierarchy ? 0x08u : 0u));
     // The previous operation on this tag may have returned before its completion handshake was
     // consumed (device plane, see below).  A master of this build queues the new vote behind
     // it, so the vote goes out first and both answers arrive in one round trip; towards any
@@ -1361,8 +1531,9 @@ ReduceOutcome Client::run_reduce_impl(const ReduceRequest &req, uint64_t) {
     const bool poisoned = ring_stale_.load();
     const bool use_device = (go->seq_nr >> 63) != 0;
     const bool use_nvls = use_device && ((go->seq_nr >> 62) & 1) != 0;
-    const uint64_t seq = go->seq_nr & ~(15ull << 60);
+    const uint64_t seq = go->seq_nr & ~(31ull << 59);
     out.stats.seq_nr = seq;
+    const bool use_hierarchy = !use_device && offer_hierarchy && ((go->seq_nr >> 59) & 1) != 0; // every peer offered it
     // bit 61 also says that every peer holds the same-box sequencer: the operation is ordered through it
     dargs.sequenced = use_device && ((go->seq_nr >> 61) & 1) != 0;
     if (use_device && offer_lease && ((go->seq_nr >> 61) & 1) != 0) {
@@ -1420,7 +1591,24 @@ ReduceOutcome Client::run_reduce_impl(const ReduceRequest &req, uint64_t) {
         ctx.frame_bytes = frame_bytes_from_env();
         ctx.abort_requested = abort_requested;
         bool wired = true;
-        if (world >= 2) {
+        RingContext cross_ctx; // second level of the two-level ring
+        if (use_hierarchy) {
+            out.stats.plane = pcclExtPlaneTcpHierarchical;
+            ctx.rank = hier.local_rank;
+            ctx.world = hier.L;
+            cross_ctx = ctx;
+            cross_ctx.rank = hier.box;
+            cross_ctx.world = hier.B;
+            {
+                std::lock_guard<std::mutex> lock(tx_mu_);
+                if (const auto it = tx_pools_.find(hier.local_next); it != tx_pools_.end()) ctx.tx = it->second;
+                if (const auto it = tx_pools_.find(hier.cross_next); it != tx_pools_.end()) cross_ctx.tx = it->second;
+            }
+            ctx.rx = pick_rx_pool(hier.local_prev, 10000);
+            cross_ctx.rx = pick_rx_pool(hier.cross_prev, 10000);
+            wired = !ctx.tx.empty() && ctx.tx.size() == ctx.rx.size() && !cross_ctx.tx.empty() && cross_ctx.tx.size() == cross_ctx.rx.size();
+            if (!wired) PLOG(WARN) << "two-level ring is not fully wired for tag " << req.tag;
+        } else if (world >= 2) {
             const Uuid &next = ring[(rank + 1) % world], &before = ring[(rank + world - 1) % world];
             {
                 std::lock_guard<std::mutex> lock(tx_mu_);
@@ -1456,7 +1644,8 @@ ReduceOutcome Client::run_reduce_impl(const ReduceRequest &req, uint64_t) {
                 a.dst = recv;
             }
             if (staged_ok) {
-                const RingResult r = ring_allreduce(ctx, a, stage || outer_two_pass ? nullptr : &host_backup);
+                std::vector<uint8_t> *backup = stage || outer_two_pass ? nullptr : &host_backup;
+                const RingResult r = use_hierarchy ? hierarchical_allreduce(ctx, cross_ctx, a, backup) : ring_allreduce(ctx, a, backup);
                 local_ok = r.ok;
                 out.tx_bytes = r.tx_bytes;
                 out.rx_bytes = r.rx_bytes;
@@ -1496,7 +1685,7 @@ ReduceOutcome Client::run_reduce_impl(const ReduceRequest &req, uint64_t) {
     const bool success = fused_applied || (local_ok && !aborted);
     // (A failed device-plane attempt leaves an ordinary in-place operand as it was: the kernels write the caller's
     // memory only after every block of this rank knows the reduction completed everywhere.)
-    if (out.stats.plane == pcclExtPlaneTcpRing) {
+    if (out.stats.plane == pcclExtPlaneTcpRing || out.stats.plane == pcclExtPlaneTcpHierarchical) {
         if (success && stage) {
             if (recv_info.is_device) {
                 if (!plane_->copy_to_device(recv, stage, req.count * esz)) return out;

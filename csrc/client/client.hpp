@@ -38,6 +38,11 @@ struct ClientConfig {
     ccoip_socket_address_t adv_p2p{}, adv_ss{}, adv_bm{};
     uint16_t p2p_port = CCOIP_PROTOCOL_PORT_P2P, ss_port = CCOIP_PROTOCOL_PORT_SHARED_STATE,
              bm_port = CCOIP_PROTOCOL_PORT_BANDWIDTH_BENCHMARK;
+    // Two-level all-reduce for groups that span hosts (see Client::build_hierarchy).  host_id 0 = derive it (PCCL_HOST_ID, else
+    // host name + boot id); hierarchy -1 = automatic (PCCL_HIERARCHY, else on when the master is not on loopback or a host id
+    // was given), 0 = off, 1 = on.  Tests set these per client to emulate several hosts in one process.
+    uint64_t host_id = 0;
+    int hierarchy = -1;
 };
 
 struct SharedEntry {
@@ -135,6 +140,11 @@ public:
     uint64_t local_world() const { return local_world_; }
     uint64_t num_groups() const { return num_groups_; }
     uint64_t largest_group() const { return largest_group_; }
+    // (hosts, peers per host) of the two-level layout in use, (0, 0) when the ring is flat
+    std::pair<uint32_t, uint32_t> hierarchy_shape() {
+        std::shared_lock<std::shared_mutex> lock(ring_mu_);
+        return hier_.ready ? std::make_pair(hier_.B, hier_.L) : std::make_pair(0u, 0u);
+    }
     const Uuid &uuid() const { return uuid_; }
     device::Plane &plane() { return *plane_; }
 
@@ -177,6 +187,18 @@ private:
 
     std::shared_mutex ring_mu_;
     std::vector<Uuid> ring_;
+    // Two-level layout of the ring (guarded by ring_mu_): L peers on each of B hosts; the local ring links the peers of this
+    // host, the cross ring the peers of equal local rank on all hosts.
+    struct Hierarchy {
+        bool ready = false;
+        uint32_t L = 0, B = 0, local_rank = 0, box = 0;
+        Uuid local_next, local_prev, cross_next, cross_prev;
+    };
+    Hierarchy hier_;
+    std::vector<wire::PeerEndpoint> last_neighbours_; // endpoints of the ring neighbours, from the master's last full connection info
+    uint64_t host_id_ = 0;
+    bool hierarchy_enabled_ = false;
+    void build_hierarchy(const std::vector<Uuid> &ring);
 
     std::mutex tx_mu_;
     std::unordered_map<Uuid, Pool> tx_pools_;

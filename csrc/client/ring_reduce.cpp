@@ -274,4 +274,77 @@ RingResult ring_allreduce(const RingContext &ctx, const ReduceArgs &a, std::vect
     return res;
 }
 
+RingResult hierarchical_allreduce(const RingContext &local, const RingContext &cross, const ReduceArgs &a, std::vector<uint8_t> *backup) {
+    RingResult res;
+    const size_t esz = wire::dtype_size(a.dtype);
+    auto *dst = static_cast<uint8_t *>(a.dst);
+    const bool in_place = a.src == a.dst;
+    if (backup) backup->clear();
+    if (a.quant != QuantAlgo::None || local.world < 1 || cross.world < 1) return res;
+    const uint32_t L = local.world, B = cross.world, l = local.rank;
+    if ((L > 1 && (local.tx.empty() || local.tx.size() != local.rx.size())) || (B > 1 && (cross.tx.empty() || cross.tx.size() != cross.rx.size())))
+        return res;
+    if (in_place) {
+        if (backup) backup->assign(dst, dst + a.count * esz);
+    } else {
+        std::memcpy(dst, a.src, a.count * esz);
+    }
+    auto fail = [&]() {
+        if (in_place && backup && !backup->empty()) std::memcpy(dst, backup->data(), backup->size());
+        res.ok = false;
+        return res;
+    };
+    // AVG is a sum that is divided by the number of ALL peers at the very end
+    const RedOp op = a.op == RedOp::Avg ? RedOp::Sum : a.op;
+
+    // ---- 1. reduce-scatter among the peers of this host (same schedule as the flat ring)
+    Stage st(local, res);
+    for (uint32_t step = 0; step + 1 < L; ++step) {
+        const uint32_t tx_chunk = (l + L - step) % L, rx_chunk = (l + L - step - 1) % L;
+        uint64_t tb, te, rb, re;
+        chunk_bounds(a.count, L, tx_chunk, tb, te);
+        chunk_bounds(a.count, L, rx_chunk, rb, re);
+        const auto tickets = st.send(dst + tb * esz, (te - tb) * esz);
+        const bool rx_ok = st.receive((re - rb) * esz, [&](size_t off, const uint8_t *data, size_t n) {
+            cpu::reduce_inplace(dst + rb * esz + off, data, n / esz, a.dtype, op);
+        });
+        const bool tx_ok = st.finish_send(tickets);
+        if (!rx_ok || !tx_ok) return fail();
+    }
+
+    // ---- 2. the chunk this peer now owns, (l+1) mod L, is summed over the hosts by the peers of equal local rank
+    {
+        uint64_t ob, oe;
+        chunk_bounds(a.count, L, (l + 1) % L, ob, oe);
+        ReduceArgs sub = a;
+        sub.src = sub.dst = dst + ob * esz;
+        sub.count = oe - ob;
+        sub.op = op;
+        RingContext cx = cross;
+        cx.tag = local.tag;
+        cx.seq = local.seq;
+        cx.abort_requested = local.abort_requested;
+        const RingResult r = ring_allreduce(cx, sub, nullptr);
+        res.tx_bytes += r.tx_bytes;
+        res.rx_bytes += r.rx_bytes;
+        res.aborted_by_master = res.aborted_by_master || r.aborted_by_master;
+        if (!r.ok) return fail();
+    }
+
+    // ---- 3. all-gather among the peers of this host
+    for (uint32_t step = 0; step + 1 < L; ++step) {
+        const uint32_t tx_chunk = (l + 1 + L - step) % L, rx_chunk = (l + L - step) % L;
+        uint64_t tb, te, rb, re;
+        chunk_bounds(a.count, L, tx_chunk, tb, te);
+        chunk_bounds(a.count, L, rx_chunk, rb, re);
+        const auto tickets = st.send(dst + tb * esz, (te - tb) * esz);
+        const bool rx_ok = st.receive((re - rb) * esz, [&](size_t off, const uint8_t *data, size_t n) { std::memcpy(dst + rb * esz + off, data, n); });
+        const bool tx_ok = st.finish_send(tickets);
+        if (!rx_ok || !tx_ok) return fail();
+    }
+    if (a.op == RedOp::Avg) cpu::finalize_avg(dst, a.count, a.dtype, L * B);
+    res.ok = true;
+    return res;
+}
+
 } // namespace pccl::client

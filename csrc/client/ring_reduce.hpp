@@ -51,6 +51,16 @@ struct ReduceArgs {
 // aborted.  Callers that reduce a private staging copy pass nullptr and skip that pass over memory.
 RingResult ring_allreduce(const RingContext &ctx, const ReduceArgs &args, std::vector<uint8_t> *backup);
 
+// Two-level all-reduce for groups that span several hosts (no counterpart in the reference, whose ring is flat:
+// ccoip/src/cpp/reduce.cpp:528-784): L peers per host, B hosts.
+//   1. reduce-scatter over the LOCAL ring (peers of one host): local rank l ends up with the host's sum of chunk (l+1) mod L
+//   2. all-reduce of that chunk over the CROSS ring (the peers with the same local rank, one per host)
+//   3. all-gather over the local ring
+// Every byte crosses the inter-host links 2(B-1)/B times per local-rank lane instead of travelling around one ring of L*B
+// hops, and each inter-host link carries 1/L of the data.  Unquantised only.  `local` / `cross` carry the rank, world and
+// connection pools of the two rings; tag, seq and abort callback are taken from `local`.
+RingResult hierarchical_allreduce(const RingContext &local, const RingContext &cross, const ReduceArgs &args, std::vector<uint8_t> *backup);
+
 // chunk i of `count` elements split over `world` owners: [begin, end)
 inline void chunk_bounds(uint64_t count, uint32_t world, uint32_t i, uint64_t &begin, uint64_t &end) {
     const uint64_t base = count / world, rem = count % world;

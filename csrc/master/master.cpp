@@ -772,7 +772,7 @@ void Master::handle_collective_initiate(Client &c, const C2MCollectiveInitiate &
         // same tag right away; the vote takes effect when the current one is finished
         if (it->second != CollectiveState::VoteComplete || c.queued_initiate.count(p.tag))
             return kick(c.link, "collective tag already in flight");
-        c.queued_initiate[p.tag] = static_cast<uint8_t>(p.op) & 0xf0u;
+        c.queued_initiate[p.tag] = static_cast<uint8_t>(p.op) & 0xf8u;
         return;
     }
     // A vote for a tag the group runs under a lease: this peer cannot (or will not) take the lease path for this
@@ -784,7 +784,7 @@ void Master::handle_collective_initiate(Client &c, const C2MCollectiveInitiate &
     // extension: top bit of the operator byte = "I can run this one on the device plane"
     // bit 6: "... and over NVSwitch multicast", bit 5: "I would run later operations on this tag under a lease",
     // bit 4: "the multicast view of the ring exists here" (independent of this operation)
-    c.device_capable[p.tag] = static_cast<uint8_t>(p.op) & 0xf0u;
+    c.device_capable[p.tag] = static_cast<uint8_t>(p.op) & 0xf8u;
     eval_collective_initiate(c.group, p.tag);
 }
 
@@ -799,7 +799,7 @@ void Master::eval_collective_initiate(uint32_t group, uint64_t tag) {
     if (voting == 0 || voting != accepted) return;
     uint64_t seq = next_seq_nr_++;
     // the device plane is used only if every single peer of the group offered it
-    uint8_t common = 0xf0u;
+    uint8_t common = 0xf8u;
     for (auto &[u, c] : clients_) {
         if (c.group != group || c.phase != Phase::Accepted) continue;
         const auto it = c.device_capable.find(tag);
@@ -808,6 +808,7 @@ void Master::eval_collective_initiate(uint32_t group, uint64_t tag) {
     }
     if (common & 0x80u) seq |= 1ull << 63;
     if ((common & 0xc0u) == 0xc0u) seq |= 1ull << 62;
+    if (common & 0x08u) seq |= 1ull << 59; // every peer has the two-level layout of a multi-host ring wired
     // Lease: every peer ran this operation on the device plane and offers to run the following operations on this
     // tag without voting.  From the next operation on, the group orders its collectives on this tag among itself
     // (same-box sequencer) and the master only hears of them when something goes wrong.

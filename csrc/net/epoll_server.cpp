@@ -62,7 +62,9 @@ bool EpollServer::listen() {
 }
 
 bool EpollServer::run_async() {
-    if (!listening_ || running_.exchange(true)) return false;
+    // a stopped server stays stopped (reference: tinysockets/tests/test_server_socket.cpp test_run_async_after_interrupt): its
+    // listening socket is gone, and re-assigning a thread that was never joined would terminate the process
+    if (!listening_ || stop_ || running_.exchange(true)) return false;
     loop_thread_ = std::thread([this] { loop(); });
     return true;
 }

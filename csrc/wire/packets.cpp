@@ -330,6 +330,32 @@ bool M2CLeaseRevoked::read(Reader &r) {
     return r.ok();
 }
 
+void P2PDirectory::write(Writer &w) const {
+    w.put<uint64_t>(entries.size());
+    for (const auto &e : entries) {
+        put_uuid(w, e.uuid);
+        w.put<uint64_t>(e.host_id);
+        w.put<bool>(e.has_host);
+        w.put<bool>(e.has_endpoint);
+        put_sockaddr(w, e.endpoint);
+    }
+}
+bool P2PDirectory::read(Reader &r) {
+    const uint64_t n = r.get<uint64_t>();
+    if (n > 4096) return false;
+    entries.clear();
+    for (uint64_t i = 0; i < n && r.ok(); ++i) {
+        DirectoryEntry e;
+        e.uuid = get_uuid(r);
+        e.host_id = r.get<uint64_t>();
+        e.has_host = r.get<bool>();
+        e.has_endpoint = r.get<bool>();
+        e.endpoint = get_sockaddr(r);
+        entries.push_back(e);
+    }
+    return r.ok();
+}
+
 // ---- P2P
 void P2PHello::write(Writer &w) const {
     put_uuid(w, uuid);

@@ -202,6 +202,21 @@ struct P2PDequantMeta {
     size_t wire_size() const;
 };
 
+// Extension (never sent unless the hierarchy is switched on, see Client::build_hierarchy): peers of one ring tell each other
+// which host they run on and where they can be dialled, travelling around the ring like an all-gather.  A peer contributes its
+// own host identity and the endpoint of its ring SUCCESSOR (the only endpoints a peer learns from the master are its
+// neighbours'), so after world-1 hops everybody knows everybody's host and address.
+struct DirectoryEntry {
+    Uuid uuid;
+    uint64_t host_id = 0;      // valid when has_host
+    bool has_host = false, has_endpoint = false;
+    ccoip_socket_address_t endpoint{}; // valid when has_endpoint
+};
+struct P2PDirectory {
+    PCCL_PACKET(5)
+    std::vector<DirectoryEntry> entries;
+};
+
 // ---------------------------------------------------------------- shared-state server
 struct C2SRequestSharedState {
     PCCL_PACKET(1)

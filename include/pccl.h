@@ -326,7 +326,8 @@ typedef enum pcclExtDataPlane_t {
     pcclExtPlaneTcpRing = 1,     /* CCoIP ring over sockets (host memory, staged for device buffers) */
     pcclExtPlaneP2POneShot = 2,  /* every GPU reads every peer, latency regime */
     pcclExtPlaneP2PTwoShot = 3,  /* reduce-scatter + all-gather with direct peer loads */
-    pcclExtPlaneNvls = 4         /* NVSwitch multicast ld_reduce / st */
+    pcclExtPlaneNvls = 4,        /* NVSwitch multicast ld_reduce / st */
+    pcclExtPlaneTcpHierarchical = 5 /* two-level ring for groups that span hosts: local reduce-scatter, cross-host ring, local all-gather */
 } pcclExtDataPlane_t;
 
 typedef struct pcclExtReduceStats_t {

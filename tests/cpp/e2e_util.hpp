@@ -42,11 +42,14 @@ struct TestMaster {
 
 // Connects `n` clients.  Already connected peers keep calling update_topology() until the
 // newcomer is in, the way an application's training loop would.
-inline std::vector<std::unique_ptr<pccl::client::Client>> connect_peers(const TestMaster &tm, int n,
-                                                                        const std::vector<uint32_t> &groups = {}) {
+// `hosts` (one id per client) turns the two-level ring on and pretends the clients run on that many machines.
+inline std::vector<std::unique_ptr<pccl::client::Client>> connect_peers(const TestMaster &tm, int n, const std::vector<uint32_t> &groups = {},
+                                                                        const std::vector<uint64_t> &hosts = {}) {
     std::vector<std::unique_ptr<pccl::client::Client>> peers;
     for (int i = 0; i < n; ++i) {
-        auto c = std::make_unique<pccl::client::Client>(tm.config(groups.empty() ? 0 : groups[i]));
+        auto cfg = tm.config(groups.empty() ? 0 : groups[i]);
+        if (!hosts.empty()) cfg.host_id = hosts[i], cfg.hierarchy = 1;
+        auto c = std::make_unique<pccl::client::Client>(cfg);
         std::atomic<bool> joined{false};
         std::thread joiner([&] {
             CHECK(c->connect());

@@ -203,6 +203,56 @@ TEST(peer_loss_during_reduce_then_retry) {
     for (auto &t : again) t.join();
 }
 
+// The same on a two-level ring: a peer of a 2x2 group vanishes in the middle of a hierarchical reduction.  The survivors'
+// attempt fails with the input intact; three peers cannot be split evenly over two hosts, so the retry runs on the flat ring.
+TEST(peer_loss_on_a_two_level_ring) {
+    TestMaster tm;
+    auto peers = connect_peers(tm, 4, {}, {1, 2, 1, 2});
+    for (auto &p : peers) CHECK(p->hierarchy_shape() == std::make_pair(2u, 2u));
+    const size_t n = 6'000'000;
+    std::vector<std::thread> ts;
+    std::atomic<int> survivors_ok{0};
+    for (int r = 0; r < 3; ++r)
+        ts.emplace_back([&, r] {
+            std::vector<float> buf(n, static_cast<float>(r + 1));
+            int attempts = 0;
+            for (;;) {
+                ++attempts;
+                ReduceRequest q;
+                q.send = q.recv = buf.data();
+                q.count = n, q.op = wire::RedOp::Sum, q.tag = 1;
+                CHECK(peers[r]->all_reduce_async(q) == client::Client::Launch::Ok);
+                ReduceOutcome o;
+                if (peers[r]->await_reduce(1, o)) {
+                    const float want = o.world == 4 ? 10.0f : 6.0f;
+                    for (size_t i = 0; i < n; i += 997) CHECK(buf[i] == want);
+                    CHECK(o.world == 3 || o.world == 4);
+                    CHECK_EQ(static_cast<int>(o.stats.plane), static_cast<int>(o.world == 4 ? pcclExtPlaneTcpHierarchical : pcclExtPlaneTcpRing));
+                    break;
+                }
+                for (size_t i = 0; i < n; i += 997) CHECK(buf[i] == static_cast<float>(r + 1)); // rolled back
+                CHECK(attempts < 10);
+            }
+            survivors_ok++;
+        });
+    std::thread victim([&] {
+        std::vector<float> buf(n, 4.0f);
+        ReduceRequest q;
+        q.send = q.recv = buf.data();
+        q.count = n, q.tag = 1;
+        CHECK(peers[3]->all_reduce_async(q) == client::Client::Launch::Ok);
+        std::this_thread::sleep_for(3ms);
+        peers[3]->interrupt();
+        ReduceOutcome o;
+        peers[3]->await_reduce(1, o);
+    });
+    victim.join();
+    for (auto &t : ts) t.join();
+    CHECK_EQ(survivors_ok.load(), 3);
+    CHECK_EQ(peers[0]->local_world(), 3u);
+    for (int r = 0; r < 3; ++r) CHECK(peers[r]->hierarchy_shape() == std::make_pair(0u, 0u));
+}
+
 // pcclAllReduceMultipleWithRetry keeps going when a peer vanishes
 TEST(multiple_with_retry_survives_peer_loss) {
     CHECK_EQ(pcclInit(), pcclSuccess);

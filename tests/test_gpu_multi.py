@@ -14,14 +14,16 @@ pytestmark = [pytest.mark.gpu, pytest.mark.multigpu]
 HERE = Path(__file__).resolve().parent
 
 
-def run_peers(world: int, scenario: str, devices=None, timeout=600, env=None):
+def run_peers(world: int, scenario: str, devices=None, timeout=600, env=None, rank_env=None):
+    """`env` goes to every peer, `rank_env` (a list of dicts) to one peer each."""
     import os
     with pccl.MasterNode("127.0.0.1:0") as master:  # leaving the block interrupts the master, also when a check fails
         master.run()
         port = master.port
         devices = devices or [f"cuda:{i}" for i in range(world)]
         procs = [subprocess.Popen([sys.executable, str(HERE / "peer_worker.py"), str(port), str(r), str(world), devices[r], scenario],
-                                  stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True, env=dict(os.environ, **(env or {})))
+                                  stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True,
+                                  env=dict(os.environ, **(env or {}), **(rank_env[r] if rank_env else {})))
                  for r in range(world)]
         outs = []
         for p in procs:

@@ -199,6 +199,25 @@ def test_multi_process_peers_on_cpu(scenario):
         assert r["ok"], r
 
 
+def test_two_level_ring_between_pretended_hosts():
+    """PCCL_HOST_ID tells peers which machine they are on; two "hosts" of two peers reduce over a local ring and a ring
+    between hosts.  Quantised operations stay on the flat ring (their codes are made for one hop pattern)."""
+    hosts = [{"PCCL_HOST_ID": h} for h in ("left", "right", "left", "right")]
+    results = run_peers(4, "allreduce", devices=["cpu"] * 4, rank_env=hosts)
+    by_case = {}
+    planes = set()
+    for r in results:
+        assert r["ok"], r
+        for c in r["cases"]:
+            by_case.setdefault(c["id"], set()).add(c["hash"])
+            planes.add(c["plane"])
+    assert planes == {"tcp_hierarchical", "tcp_ring"}, planes
+    assert all(len(h) == 1 for h in by_case.values()), "peers disagree bit-wise"
+    # the same peers without host ids on loopback: one flat ring
+    flat = run_peers(4, "allreduce", devices=["cpu"] * 4, env={"PCCL_HIERARCHY": "0"}, rank_env=hosts)
+    assert {c["plane"] for r in flat for c in r["cases"]} == {"tcp_ring"}
+
+
 @pytest.mark.parametrize("hash_type", ["mset", "crc32"])
 def test_shared_state_with_the_other_hash_types(hash_type):
     """PCCL_SHARED_STATE_HASH switches the content hash of the whole run: mset64 (the order-independent hash the collective
