@@ -28,3 +28,22 @@ def test_outer_step_two_peers_one_gpu():
         assert r["ok"], r
         assert all(c["plane"] == "tcp_ring" for c in r["cases"]), r
     assert len({c["hash"] for r in results for c in r["cases"] if c["id"] == "outer_step_1"}) == 1
+
+
+def test_two_level_ring_with_device_tensors():
+    """Four peers on this GPU pretend to be two hosts of two (PCCL_HOST_ID): device tensors are staged and reduced over the
+    local ring, the ring between hosts and the local ring again; quantised operations keep the flat ring."""
+    hosts = [{"PCCL_HOST_ID": h} for h in ("north", "south", "north", "south")]
+    small = {"PCCL_ARENA_SLOT_MB": "64", "PCCL_SYMMETRIC_MB": "128"}
+    results = run_peers(4, "allreduce", devices=["cuda:0"] * 4, env=small, rank_env=hosts)
+    by_case = {}
+    for r in results:
+        for c in r["cases"]:
+            assert c["ok"], c
+            by_case.setdefault(c["id"], set()).add(c["hash"])
+    assert {c["plane"] for r in results for c in r["cases"]} == {"tcp_hierarchical", "tcp_ring"}
+    assert all(len(h) == 1 for h in by_case.values()), "peers disagree bit-wise"
+    stepped = run_peers(4, "outer_step", devices=["cuda:0"] * 4, env=small, rank_env=hosts)
+    assert all(r["ok"] for r in stepped), stepped
+    assert {c["plane"] for r in stepped for c in r["cases"]} == {"tcp_hierarchical"}
+    assert len({c["hash"] for r in stepped for c in r["cases"] if c["id"] == "outer_step_1"}) == 1

@@ -213,6 +213,11 @@ def test_two_level_ring_between_pretended_hosts():
             planes.add(c["plane"])
     assert planes == {"tcp_hierarchical", "tcp_ring"}, planes
     assert all(len(h) == 1 for h in by_case.values()), "peers disagree bit-wise"
+    # the DiLoCo outer step of host tensors reduces its pseudo-gradients the same way
+    stepped = run_peers(4, "outer_step", devices=["cpu"] * 4, rank_env=hosts)
+    assert all(r["ok"] for r in stepped), stepped
+    assert {c["plane"] for r in stepped for c in r["cases"]} == {"tcp_hierarchical"}
+    assert len({c["hash"] for r in stepped for c in r["cases"] if c["id"] == "outer_step_1"}) == 1
     # the same peers without host ids on loopback: one flat ring
     flat = run_peers(4, "allreduce", devices=["cpu"] * 4, env={"PCCL_HIERARCHY": "0"}, rank_env=hosts)
     assert {c["plane"] for r in flat for c in r["cases"]} == {"tcp_ring"}
