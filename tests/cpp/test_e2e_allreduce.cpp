@@ -209,8 +209,15 @@ TEST(concurrent_tags) {
             q2.send = b.data(), q2.recv = rb.data(), q2.count = n, q2.op = wire::RedOp::Max, q2.tag = 2;
             CHECK(peers[r]->all_reduce_async(q1) == client::Client::Launch::Ok);
             CHECK(peers[r]->all_reduce_async(q2) == client::Client::Launch::Ok);
-            // joint calls are refused while reductions are in flight
+            // joint calls are refused while reductions are in flight (reference test_all_reduce.cpp:449-524, :527-618)
             CHECK(!peers[r]->update_topology());
+            CHECK(!peers[r]->optimize_topology());
+            client::SharedStateArgs state;
+            client::SharedEntry entry;
+            entry.key = "w", entry.data = a.data(), entry.count = n, entry.dtype = wire::DType::F32;
+            state.entries.push_back(entry);
+            uint64_t tx = 0, rx = 0;
+            CHECK(!peers[r]->sync_shared_state(state, tx, rx));
             ReduceOutcome o;
             CHECK(peers[r]->await_reduce(1, o));
             CHECK(peers[r]->await_reduce(2, o));

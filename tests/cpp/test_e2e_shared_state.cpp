@@ -349,6 +349,158 @@ TEST(late_joiner_participates) {
     CHECK(st[2].buffers[0] == st[0].buffers[0]);
 }
 
+// Two leaders advance content and revision in lock step, a follower never touches its copy: every step the follower is
+// outdated, receives the whole tensor from exactly one of the leaders and adopts their revision
+// (reference test_shared_state_distribution.cpp:1318-1472)
+TEST(follower_is_dragged_along_every_step) {
+    TestMaster tm;
+    auto peers = connect_peers(tm, 3);
+    std::vector<PeerState> st(3);
+    for (auto &s : st) s.add("w", 1500, 0, wire::DType::I16);
+    for (int step = 0; step < 6; ++step) {
+        for (int leader = 0; leader < 2; ++leader) {
+            std::fill(st[leader].buffers[0].begin(), st[leader].buffers[0].end(), static_cast<uint8_t>(100 + step));
+            st[leader].args.revision = 7 + step;
+        }
+        sync_all(peers, st);
+        for (auto &s : st) CHECK(s.ok);
+        CHECK_EQ(st[2].rx, 3000u);
+        CHECK_EQ(st[2].tx, 0u);
+        CHECK_EQ(st[0].rx + st[1].rx, 0u);
+        CHECK((st[0].tx == 3000 && st[1].tx == 0) || (st[0].tx == 0 && st[1].tx == 3000));
+        CHECK(st[2].buffers[0] == st[0].buffers[0]);
+        CHECK_EQ(st[2].args.revision, uint64_t(7 + step));
+    }
+}
+
+// The first revision a group ever sees may be anything (a run that resumes from a checkpoint); from then on the rule holds
+// (reference :1582-1672)
+TEST(first_revision_is_free_later_ones_are_not) {
+    TestMaster tm;
+    auto peers = connect_peers(tm, 2);
+    std::vector<PeerState> st(2);
+    for (auto &s : st) s.add("w", 64, 1);
+    st[0].args.revision = st[1].args.revision = 13;
+    sync_all(peers, st);
+    CHECK(st[0].ok && st[1].ok);
+    st[0].args.revision = st[1].args.revision = 14;
+    sync_all(peers, st);
+    CHECK(st[0].ok && st[1].ok);
+    st[0].args.revision = st[1].args.revision = 16; // both skip one: both are kicked
+    sync_all(peers, st);
+    CHECK(!st[0].ok && !st[1].ok);
+}
+
+// Groups loop at their own pace on their own threads: ten steps each, one group twice as fast as the other; nothing moves,
+// nobody waits for the other group (reference :1791-1934)
+TEST(groups_advance_concurrently_at_their_own_pace) {
+    TestMaster tm;
+    auto peers = connect_peers(tm, 4, {0, 0, 1, 1});
+    std::vector<PeerState> st(4);
+    for (auto &s : st) s.add("w", 4096, 0);
+    std::atomic<int> bad{0};
+    auto run_group = [&](int a, int b, int delay_ms, uint8_t base) {
+        for (int step = 0; step < 10; ++step) {
+            for (int p : {a, b}) {
+                std::fill(st[p].buffers[0].begin(), st[p].buffers[0].end(), static_cast<uint8_t>(base + step));
+                st[p].args.revision = 1 + step;
+            }
+            std::thread other([&] { st[b].ok = peers[b]->sync_shared_state(st[b].args, st[b].tx, st[b].rx); });
+            st[a].ok = peers[a]->sync_shared_state(st[a].args, st[a].tx, st[a].rx);
+            other.join();
+            for (int p : {a, b})
+                if (!st[p].ok || st[p].tx || st[p].rx) bad++;
+            std::this_thread::sleep_for(std::chrono::milliseconds(delay_ms));
+        }
+    };
+    const auto t0 = std::chrono::steady_clock::now();
+    std::chrono::steady_clock::duration fast_took{};
+    std::thread g0([&] {
+        run_group(0, 1, 5, 10);
+        fast_took = std::chrono::steady_clock::now() - t0;
+    });
+    std::thread g1([&] { run_group(2, 3, 60, 200); });
+    g0.join();
+    g1.join();
+    CHECK_EQ(bad.load(), 0);
+    CHECK(st[0].buffers[0] == st[1].buffers[0] && st[2].buffers[0] == st[3].buffers[0]);
+    CHECK(st[0].buffers[0] != st[2].buffers[0]);
+    CHECK(fast_took < std::chrono::milliseconds(550)); // the slow group needs >= 600 ms for its sleeps alone
+}
+
+// Drag-along in three groups at once, each with two leaders and a follower and its own content (reference :1936-2080)
+TEST(drag_along_in_several_groups_at_once) {
+    TestMaster tm;
+    auto peers = connect_peers(tm, 9, {0, 0, 0, 1, 1, 1, 2, 2, 2});
+    std::vector<PeerState> st(9);
+    for (auto &s : st) s.add("w", 2000, 0);
+    std::atomic<int> bad{0};
+    std::vector<std::thread> groups;
+    for (int g = 0; g < 3; ++g)
+        groups.emplace_back([&, g] {
+            const int l0 = 3 * g, l1 = 3 * g + 1, f = 3 * g + 2;
+            for (int step = 0; step < 4; ++step) {
+                for (int p : {l0, l1}) {
+                    std::fill(st[p].buffers[0].begin(), st[p].buffers[0].end(), static_cast<uint8_t>(50 * g + step + 1));
+                    st[p].args.revision = 1 + step;
+                }
+                std::vector<std::thread> ts;
+                for (int p : {l0, l1, f}) ts.emplace_back([&, p] { st[p].ok = peers[p]->sync_shared_state(st[p].args, st[p].tx, st[p].rx); });
+                for (auto &t : ts) t.join();
+                if (!(st[l0].ok && st[l1].ok && st[f].ok)) bad++;
+                if (st[f].rx != 2000 || st[f].tx != 0 || st[l0].rx + st[l1].rx != 0 || st[l0].tx + st[l1].tx != 2000) bad++;
+                if (st[f].buffers[0] != st[l0].buffers[0] || st[f].args.revision != uint64_t(1 + step)) bad++;
+            }
+        });
+    for (auto &t : groups) t.join();
+    CHECK_EQ(bad.load(), 0);
+}
+
+// A peer admitted between two synchronisation steps that already holds the right content and revision (it loaded the same
+// checkpoint) takes part in the next step like everybody else: nothing moves (reference :2218-2378)
+TEST(newcomer_between_steps_with_matching_state) {
+    TestMaster tm;
+    auto peers = connect_peers(tm, 2);
+    std::vector<PeerState> st(3);
+    for (auto &s : st) s.add("w", 999, 0);
+    auto content = [&](int p, int step) {
+        std::fill(st[p].buffers[0].begin(), st[p].buffers[0].end(), static_cast<uint8_t>(160 + step));
+        st[p].args.revision = step;
+    };
+    for (int step = 0; step < 3; ++step) {
+        content(0, step), content(1, step);
+        sync_all(peers, st, {0, 1});
+        CHECK(st[0].ok && st[1].ok && st[0].tx + st[1].tx + st[0].rx + st[1].rx == 0);
+    }
+    auto late = std::make_unique<client::Client>(tm.config());
+    std::thread joiner([&] { CHECK(late->connect()); });
+    while (peers[0]->global_world() < 3) {
+        std::vector<std::thread> ts;
+        for (auto &p : peers) ts.emplace_back([&p] { CHECK(p->update_topology()); });
+        for (auto &t : ts) t.join();
+    }
+    joiner.join();
+    peers.push_back(std::move(late));
+    for (int step = 3; step < 6; ++step) {
+        for (int p = 0; p < 3; ++p) content(p, step);
+        sync_all(peers, st);
+        for (auto &s : st) CHECK(s.ok && s.tx == 0 && s.rx == 0);
+    }
+}
+
+// RECEIVE_ONLY everywhere with DIFFERENT content: still nobody to receive from, still everybody out (reference :2569-2664)
+TEST(all_receive_only_with_different_content) {
+    TestMaster tm;
+    auto peers = connect_peers(tm, 2);
+    std::vector<PeerState> st(2);
+    st[0].add("w", 64, 1);
+    st[1].add("w", 64, 2);
+    st[0].args.strategy = st[1].args.strategy = SyncStrategy::RxOnly;
+    sync_all(peers, st);
+    CHECK(!st[0].ok && !st[1].ok);
+    CHECK(st[0].buffers[0] == std::vector<uint8_t>(64, 1) && st[1].buffers[0] == std::vector<uint8_t>(64, 2)); // untouched
+}
+
 // tensors with allow_content_inequality are never hashed or transferred
 TEST(content_inequality_allowed) {
     TestMaster tm;
