@@ -73,6 +73,7 @@ def main():
     ap.add_argument("--eval-interval", dest="eval_interval", type=int, default=None)
     ap.add_argument("--checkpoint-dir", dest="checkpoint_dir", default=None)
     ap.add_argument("--quant", default=None, choices=["none", "u8", "fp8"])
+    ap.add_argument("--timeline", default="", help="write the section timeline here (.png/.svg) and a Chrome trace next to it")
     args = ap.parse_args()
     cfg = load_config(args)
 
@@ -180,6 +181,9 @@ def main():
         algo.flush()
     save_checkpoint()
     print(prof.report())
+    if args.timeline:  # reference: profiler.export_timeline(), sync_diloco.py:538
+        prof.export_timeline(args.timeline)
+        prof.export_chrome_trace(str(Path(args.timeline).with_suffix(".trace.json")))
     comm.destroy()
     if master:
         master.interrupt()

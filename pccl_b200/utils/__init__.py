@@ -1,4 +1,4 @@
 from .numa import bind_to_device, device_numa_node
-from .profiler import Profiler
+from .profiler import Profiler, ProfilerCollection
 
-__all__ = ["Profiler", "bind_to_device", "device_numa_node"]
+__all__ = ["Profiler", "ProfilerCollection", "bind_to_device", "device_numa_node"]

@@ -50,14 +50,18 @@ def test_fsdp_islands_share_shards_through_peer_groups(master):
 
 
 @pytest.mark.parametrize("mode", ["sync", "async"])
-def test_diloco_example_two_peers_cpu(master, mode):
+def test_diloco_example_two_peers_cpu(master, mode, tmp_path):
     procs = [subprocess.Popen([sys.executable, str(REPO / "examples" / "diloco.py"), "--master", f"127.0.0.1:{master.port}", "--device", "cpu",
-                               "--outer-steps", "2", "--inner-steps", "2", "--min-peers", "2", "--mode", mode],
-                              stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, env=_env()) for _ in range(2)]
+                               "--outer-steps", "2", "--inner-steps", "2", "--min-peers", "2", "--mode", mode,
+                               "--timeline", str(tmp_path / f"peer{i}.svg")],
+                              stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, env=_env()) for i in range(2)]
     for p in procs:
         out, _ = p.communicate(timeout=300)
         assert p.returncode == 0, out[-4000:]
         assert "outer step 1" in out and "world 2" in out, out[-2000:]
+    for i in range(2):  # the section timeline and its trace (reference: profiler.export_timeline)
+        assert "inner" in (tmp_path / f"peer{i}.svg").read_text()
+        assert '"traceEvents"' in (tmp_path / f"peer{i}.trace.json").read_text()
 
 
 def test_ddp_examples_cpu(master):
