@@ -20,13 +20,13 @@ sys.path.insert(0, str(HERE.parent.parent))
 import pccl_b200 as pccl  # noqa: E402
 
 
-def run(seconds: float, max_peers: int, stall: float, device: str, seed: int = 0) -> dict:
+def run(seconds: float, max_peers: int, stall: float, device: str, seed: int = 0, mode: str = "basic") -> dict:
     with pccl.MasterNode("127.0.0.1:0") as master:  # leaving the block interrupts the master
         master.run()
-        return _run(master, seconds, max_peers, stall, device, seed)
+        return _run(master, seconds, max_peers, stall, device, seed, mode)
 
 
-def _run(master, seconds: float, max_peers: int, stall: float, device: str, seed: int) -> dict:
+def _run(master, seconds: float, max_peers: int, stall: float, device: str, seed: int, mode: str = "basic") -> dict:
     rng = random.Random(seed)
     port = master.port
     peers = []
@@ -59,7 +59,7 @@ def _run(master, seconds: float, max_peers: int, stall: float, device: str, seed
             if not free:
                 return
             dev = f"cuda:{free[0]}"
-        p = subprocess.Popen([sys.executable, str(HERE / "chaos_peer.py"), str(port), dev], stdout=subprocess.PIPE,
+        p = subprocess.Popen([sys.executable, str(HERE / "chaos_peer.py"), str(port), dev, mode], stdout=subprocess.PIPE,
                              stderr=subprocess.DEVNULL, text=True)
         if device == "cuda":
             gpu_of[p.pid] = int(dev.split(":")[1])
@@ -98,7 +98,8 @@ if __name__ == "__main__":
     ap.add_argument("--max-peers", type=int, default=5)
     ap.add_argument("--stall", type=float, default=20)
     ap.add_argument("--device", default="cpu")
+    ap.add_argument("--mode", default="basic", choices=["basic", "cross_step"])
     a = ap.parse_args()
-    out = run(a.seconds, a.max_peers, a.stall, a.device)
+    out = run(a.seconds, a.max_peers, a.stall, a.device, mode=a.mode)
     print(out)
     sys.exit(1 if out["stalled"] or out.get("fatal") else 0)
