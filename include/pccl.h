@@ -351,7 +351,8 @@ PCCL_EXPORT pcclResult_t pcclExtGetLastReduceStats(const pcclComm_t *communicato
 PCCL_EXPORT pcclResult_t pcclExtMasterGetPort(const pcclMasterInstance_t *master_instance, uint16_t *port_out);
 
 /* Hash of a host or device buffer with the hash the shared-state protocol uses.
- * hash_type: 0 = simplehash (reference-compatible value), 1 = CRC32C. */
+ * hash_type: 0 = simplehash (reference-compatible value), 1 = CRC32C, 2 = mset64 (order-independent sum of mixed
+ * 16-byte packets; the one the collective kernels can produce as a by-product). */
 PCCL_EXPORT pcclResult_t pcclExtHashBuffer(const void *data, size_t n_bytes, pcclDeviceType_t device_type,
                                            int hash_type, uint64_t *hash_out);
 
@@ -364,18 +365,6 @@ PCCL_EXPORT pcclResult_t pcclExtSymmetricFree(pcclComm_t *communicator, void *pt
 /* Size of one element of a data type in bytes, 0 for unknown values. */
 PCCL_EXPORT size_t pcclExtDataTypeSize(pcclDataType_t datatype);
 
-/* DiLoCo outer step as one collective operation (no counterpart in the reference, whose example performs the
- * three stages with torch ops on the host around pcclAllReduce: python/examples/nanogpt_diloco/sync_diloco.py:480-530):
- *     g        = average over all peers of (params - inner)
- *     momentum = first_step ? g : mu * momentum + g
- *     params  -= lr * (g + mu * momentum)            (torch.optim.SGD with nesterov=True)
- *     inner    = params
- * All three tensors are float32[count], all on the host or all on one CUDA device.  Between GPUs of one NVLink
- * domain the whole step is a single kernel per peer (pseudo-gradient while staging, reduction over NVLink /
- * NVSwitch, update while writing out); otherwise -- TCP ring, or more elements than one staging slot holds --
- * the library computes the pseudo-gradient into a scratch buffer, reduces that, and applies the update.
- * Either way the tensors are untouched when the call fails (pcclRankConnectionLost: retry after
- * pcclUpdateTopology, like pcclAllReduce).  Synchronous; one tag like any reduction. */
 /* Stream-ordered all-reduce on device buffers (no counterpart in the reference, whose all-reduce takes host memory and
  * blocks: src/pccl.cpp:301-313).  The operation is ordered after everything already queued on `cuda_stream`
  * (a cudaStream_t; NULL = the legacy default stream) and that stream waits for the result, so the caller needs no
@@ -401,6 +390,18 @@ PCCL_EXPORT pcclResult_t pcclExtWaitStreamOps(const pcclComm_t *communicator, ui
 PCCL_EXPORT pcclResult_t pcclExtTrustContentHashes(pcclComm_t *communicator, int on);
 PCCL_EXPORT pcclResult_t pcclExtHashKernelsSkipped(const pcclComm_t *communicator, uint64_t *count_out);
 
+/* DiLoCo outer step as one collective operation (no counterpart in the reference, whose example performs the
+ * three stages with torch ops on the host around pcclAllReduce: python/examples/nanogpt_diloco/sync_diloco.py:480-530):
+ *     g        = average over all peers of (params - inner)
+ *     momentum = first_step ? g : mu * momentum + g
+ *     params  -= lr * (g + mu * momentum)            (torch.optim.SGD with nesterov=True)
+ *     inner    = params
+ * All three tensors are float32[count], all on the host or all on one CUDA device.  Between GPUs of one NVLink
+ * domain the whole step is a single kernel per peer (pseudo-gradient while staging, reduction over NVLink /
+ * NVSwitch, update while writing out); otherwise -- TCP ring, or more elements than one staging slot holds --
+ * the library computes the pseudo-gradient into a scratch buffer, reduces that, and applies the update.
+ * Either way the tensors are untouched when the call fails (pcclRankConnectionLost: retry after
+ * pcclUpdateTopology, like pcclAllReduce).  Synchronous; one tag like any reduction. */
 typedef struct pcclExtOuterStepDescriptor_t {
     void *params;
     void *inner;

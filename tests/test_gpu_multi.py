@@ -208,3 +208,34 @@ def test_outer_step_hashes_make_the_next_shared_state_check_free(world):
     writes them; the following shared-state synchronisation launches no hash kernel for them and moves nothing."""
     for r in run_peers(world, "trusted_hashes", timeout=200, env={"PCCL_SHARED_STATE_HASH": "mset"}):
         assert r["ok"], r
+
+
+@pytest.mark.skipif(gpu_count() < 2, reason="needs >= 2 GPUs")
+def test_cuda_example_program_on_two_gpus(tmp_path):
+    """examples/cuda/stream_allreduce.cu, built with nvcc and run as one process per GPU: symmetric buffers, stream-ordered
+    enqueued all-reduces between two kernels, no host synchronisation inside the loop.  The weights it prints follow from the
+    arithmetic of its two kernels."""
+    import re
+    from test_native_examples import build_cuda_example
+    exe = build_cuda_example(tmp_path)
+    steps = 12
+    with pccl.MasterNode("127.0.0.1:0") as master:
+        master.run()
+        procs = [subprocess.Popen([str(exe), f"127.0.0.1:{master.port}", str(g), str(steps), "2"], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+                 for g in range(2)]
+        outs = []
+        for p in procs:
+            try:
+                outs.append(p.communicate(timeout=150)[0])
+            except subprocess.TimeoutExpired:
+                for q in procs:
+                    q.kill()
+                raise
+    assert all(p.returncode == 0 for p in procs), outs
+    want = [-0.01 * sum((i + s) % 5 + 0.5 for s in range(steps)) for i in range(4)]  # average of the seeds 0 and 1 is 0.5
+    for o in outs:
+        m = re.search(r"with 2 peers, ([\d.]+) ms per step .* plane (\d), leased (\d), weights\[0..3\] = (.*)", o)
+        assert m, o
+        assert int(m.group(2)) in (2, 3, 4) and int(m.group(3)) == 1, o  # an NVLink plane, under a lease
+        got = [float(x) for x in m.group(4).split()]
+        assert all(abs(a - b) < 2e-3 for a, b in zip(got, want)), (got, want)
