@@ -10,7 +10,7 @@ BUILD    := build
 LIBDIR   := pccl_b200/lib
 BINDIR   := pccl_b200/bin
 
-CXXFLAGS := -std=c++20 -O3 -g1 -fPIC -fvisibility=hidden -Wall -Wextra -Wpedantic -Wshadow=local -Iinclude -Icsrc -pthread
+CXXFLAGS := -std=c++20 -O3 -g1 -ffp-contract=off -fPIC -fvisibility=hidden -Wall -Wextra -Wpedantic -Wshadow=local -Iinclude -Icsrc -pthread
 NVFLAGS  := -std=c++20 -O3 -lineinfo -gencode arch=compute_100a,code=sm_100a -Xcompiler -fPIC,-fvisibility=hidden \
             -Iinclude -Icsrc --expt-relaxed-constexpr -Xptxas -v
 LDFLAGS  := -pthread -Wl,--no-undefined

@@ -1,9 +1,14 @@
 #include "ring_reduce.hpp"
 
+#include <algorithm>
 #include <cstring>
+#include <future>
+#include <thread>
 
 #include "../kernels/cpu/reduce.hpp"
+#include "../util/env.hpp"
 #include "../util/log.hpp"
+#include "../util/threadpool.hpp"
 
 namespace pccl::client {
 
@@ -14,6 +19,19 @@ using wire::RedOp;
 namespace {
 
 constexpr int kPollMs = 2;
+constexpr size_t kOffloadBytes = 256u << 10; // smaller code buffers are quantised inline: a hand-over costs more than it hides
+
+// Helpers that run the sending half of a quantised ring step beside the receiving half.  Shared by all operations of the
+// process, never destroyed (its threads sleep on a condition variable when the process exits).  A job only computes and
+// enqueues sends; it never waits for another job, so a busy pool delays an operation but cannot block it for good.
+ThreadPool &host_kernel_pool() {
+    static ThreadPool *pool = [] {
+        const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
+        const size_t n = static_cast<size_t>(env_u64("PCCL_HOST_KERNEL_THREADS", std::clamp(hw / 4, 1u, 4u)));
+        return new ThreadPool(std::max<size_t>(1, n), 1024);
+    }();
+    return *pool;
+}
 
 struct Stage {
     const RingContext &ctx;
@@ -59,6 +77,31 @@ struct Stage {
             part_bounds(bytes, n, i, b, e);
             const size_t sock = n == 1 ? lane : i;
             tickets.push_back(ctx.tx[sock]->send_bytes(ctx.tag, ctx.seq, data + b, e - b, ctx.frame_bytes));
+        }
+        res.tx_bytes += bytes;
+        return tickets;
+    }
+
+    // Like send(), but the bytes do not exist yet: `produce(b, e)` fills codes[b, e) (quantises that range) right before it
+    // is handed to the socket, in pieces, so the first piece is on the wire while the second is being produced.  Same byte
+    // stream and the same cuts across the pool as send(): the receiver cannot tell the difference.
+    template <typename Produce> Tickets send_pieces(const uint8_t *codes, size_t bytes, Produce produce) {
+        constexpr size_t kPiece = 512u << 10;
+        Tickets tickets;
+        const size_t n = parts(bytes);
+        for (size_t i = 0; i < n; ++i) {
+            size_t b, e;
+            part_bounds(bytes, n, i, b, e);
+            net::MuxSocket &sock = *ctx.tx[n == 1 ? lane : i];
+            if (b == e) {
+                tickets.push_back(sock.send_bytes(ctx.tag, ctx.seq, codes + b, 0, ctx.frame_bytes));
+                continue;
+            }
+            for (size_t p = b; p < e; p += kPiece) {
+                const size_t q = std::min(e, p + kPiece);
+                produce(p, q);
+                tickets.push_back(sock.send_bytes(ctx.tag, ctx.seq, codes + p, q - p, ctx.frame_bytes));
+            }
         }
         res.tx_bytes += bytes;
         return tickets;
@@ -205,12 +248,26 @@ RingResult ring_allreduce(const RingContext &ctx, const ReduceArgs &a, std::vect
             continue;
         }
 
+        // The sending half (quantise piece by piece, hand each piece to the sockets) runs beside the receiving half
+        // (decode and reduce every frame as it arrives): the two touch different chunks of dst.
         cpu::QuantParams mine = qp, theirs = qp;
         cpu::quant_analyze(dst + tb * esz, tx_n, mine);
-        tx_codes.resize(cpu::quantized_size(mine, tx_n));
-        cpu::quantize(dst + tb * esz, tx_codes.data(), tx_n, mine);
         if (!st.exchange_meta(mine, theirs)) return fail();
-        const auto tickets = st.send(tx_codes.data(), tx_codes.size());
+        tx_codes.resize(cpu::quantized_size(mine, tx_n));
+        Stage::Tickets tickets;
+        auto tx_half = [&] {
+            if (block_format) { // records first, codes after them: produced as a whole
+                cpu::quantize(dst + tb * esz, tx_codes.data(), tx_n, mine);
+                tickets = st.send(tx_codes.data(), tx_codes.size());
+            } else {
+                tickets = st.send_pieces(tx_codes.data(), tx_codes.size(), [&](size_t b, size_t e) {
+                    cpu::quantize(dst + (tb + b / qsz) * esz, tx_codes.data() + b, (e - b) / qsz, mine);
+                });
+            }
+        };
+        std::future<void> tx_job;
+        if (tx_codes.size() >= kOffloadBytes) tx_job = host_kernel_pool().submit(tx_half);
+        else tx_half();
         const size_t rx_bytes = cpu::quantized_size(theirs, rx_n);
         bool rx_ok;
         if (block_format) {
@@ -222,6 +279,7 @@ RingResult ring_allreduce(const RingContext &ctx, const ReduceArgs &a, std::vect
                 cpu::dequantize_reduce(dst + (rb + off / qsz) * esz, data, n / qsz, theirs, a.op);
             });
         }
+        if (tx_job.valid()) tx_job.get(); // before anything else: it works on this frame's variables
         const bool tx_ok = st.finish_send(tickets);
         if (!rx_ok || !tx_ok) return fail();
     }
@@ -245,25 +303,44 @@ RingResult ring_allreduce(const RingContext &ctx, const ReduceArgs &a, std::vect
             continue;
         }
 
-        if (step == 0) {
-            // Quantise the chunk this peer owns exactly once and adopt the decoded values, so
-            // the owner holds what everybody else will decode.
+        const bool own = step == 0;
+        if (own) {
+            // The chunk this peer owns is quantised exactly once, and the owner adopts the decoded values, so it holds what
+            // everybody else will decode.  Later steps forward received codes and metadata unchanged.
             forwarded = qp;
             cpu::quant_analyze(dst + tb * esz, tx_n, forwarded);
             tx_codes.resize(cpu::quantized_size(forwarded, tx_n));
-            cpu::quantize(dst + tb * esz, tx_codes.data(), tx_n, forwarded);
-            cpu::dequantize_reduce(dst + tb * esz, tx_codes.data(), tx_n, forwarded, RedOp::Set);
         }
         cpu::QuantParams theirs = qp;
         if (!st.exchange_meta(forwarded, theirs)) return fail();
-        const auto tickets = st.send(tx_codes.data(), tx_codes.size());
+        Stage::Tickets tickets;
+        auto tx_half = [&] {
+            if (!own) {
+                tickets = st.send(tx_codes.data(), tx_codes.size());
+            } else if (block_format) {
+                cpu::quantize(dst + tb * esz, tx_codes.data(), tx_n, forwarded);
+                tickets = st.send(tx_codes.data(), tx_codes.size());
+                cpu::dequantize_reduce(dst + tb * esz, tx_codes.data(), tx_n, forwarded, RedOp::Set);
+            } else {
+                tickets = st.send_pieces(tx_codes.data(), tx_codes.size(), [&](size_t b, size_t e) {
+                    cpu::quantize(dst + (tb + b / qsz) * esz, tx_codes.data() + b, (e - b) / qsz, forwarded);
+                    cpu::dequantize_reduce(dst + (tb + b / qsz) * esz, tx_codes.data() + b, (e - b) / qsz, forwarded, RedOp::Set);
+                });
+            }
+        };
+        std::future<void> tx_job;
+        if (own && tx_codes.size() >= kOffloadBytes) tx_job = host_kernel_pool().submit(tx_half);
+        else tx_half();
         const size_t rx_bytes = cpu::quantized_size(theirs, rx_n);
         rx_codes.resize(rx_bytes);
-        const bool rx_ok =
-            st.receive(rx_bytes, [&](size_t off, const uint8_t *data, size_t n) { std::memcpy(rx_codes.data() + off, data, n); });
+        const bool rx_ok = st.receive(rx_bytes, [&](size_t off, const uint8_t *data, size_t n) {
+            std::memcpy(rx_codes.data() + off, data, n);
+            if (!block_format) cpu::dequantize_reduce(dst + (rb + off / qsz) * esz, data, n / qsz, theirs, RedOp::Set); // while it is in cache
+        });
+        if (tx_job.valid()) tx_job.get();
         const bool tx_ok = st.finish_send(tickets);
         if (!rx_ok || !tx_ok) return fail();
-        cpu::dequantize_reduce(dst + rb * esz, rx_codes.data(), rx_n, theirs, RedOp::Set);
+        if (block_format) cpu::dequantize_reduce(dst + rb * esz, rx_codes.data(), rx_n, theirs, RedOp::Set);
         // next step forwards the received codes and metadata unchanged (no second quantisation)
         tx_codes.swap(rx_codes);
         forwarded = theirs;

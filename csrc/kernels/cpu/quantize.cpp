@@ -1,6 +1,10 @@
 #include "quantize.hpp"
 
+#include "../../util/env.hpp"
+#include "quantize_fast.hpp"
+
 #include <algorithm>
+#include <atomic>
 #include <bit>
 #include <cmath>
 #include <cstring>
@@ -205,6 +209,23 @@ bool is_unsigned_code(DType t) { return t == DType::U8 || t == DType::U16 || t =
 
 } // namespace
 
+namespace {
+std::atomic<int> g_generic{-1};
+bool generic_forced() {
+    int g = g_generic.load(std::memory_order_relaxed);
+    if (g < 0) {
+        g = env_flag("PCCL_QUANT_GENERIC", false) ? 1 : 0;
+        g_generic.store(g, std::memory_order_relaxed);
+    }
+    return g == 1;
+}
+bool use_fast(const QuantParams &p) {
+    return !generic_forced() && p.value_dtype == DType::F32 && (p.code_dtype == DType::U8 || p.code_dtype == DType::F8E4M3);
+}
+} // namespace
+
+void quant_force_generic(bool on) { g_generic.store(on ? 1 : 0, std::memory_order_relaxed); }
+
 bool quant_supported(QuantAlgo algo, DType value_dtype, DType code_dtype) {
     if (value_dtype != DType::F32 && value_dtype != DType::F64) return false;
     switch (algo) {
@@ -229,7 +250,11 @@ size_t quantized_size(const QuantParams &p, size_t count) {
 void quant_analyze(const void *src, size_t count, QuantParams &p) {
     if (p.algo != QuantAlgo::MinMax && p.algo != QuantAlgo::ZeroPointScale) return;
     double mn = 0, mx = 0;
-    if (p.value_dtype == DType::F32)
+    if (p.value_dtype == DType::F32 && !generic_forced()) {
+        float lo, hi;
+        fast::extrema_f32(static_cast<const float *>(src), count, lo, hi);
+        mn = lo, mx = hi;
+    } else if (p.value_dtype == DType::F32)
         minmax_scan(static_cast<const float *>(src), count, mn, mx);
     else
         minmax_scan(static_cast<const double *>(src), count, mn, mx);
@@ -257,6 +282,17 @@ void quant_analyze(const void *src, size_t count, QuantParams &p) {
 
 void quantize(const void *src, void *dst, size_t count, const QuantParams &p) {
     const bool f32 = p.value_dtype == DType::F32;
+    if (use_fast(p)) {
+        const auto *x = static_cast<const float *>(src);
+        auto *q = static_cast<uint8_t *>(dst);
+        switch (p.algo) {
+        case QuantAlgo::MinMax: fast::minmax_quant_u8(x, q, count, static_cast<float>(p.min), static_cast<float>(p.max)); return;
+        case QuantAlgo::ZeroPointScale: fast::zps_quant_u8(x, q, count, p.scale, p.zero_point); return;
+        case QuantAlgo::BlockMinMax: fast::block_minmax_quant(x, q, count); return;
+        case QuantAlgo::BlockFp8: fast::block_fp8_quant(x, q, count); return;
+        default: break;
+        }
+    }
     switch (p.algo) {
     case QuantAlgo::None: std::memcpy(dst, src, count * wire::dtype_size(p.value_dtype)); break;
     case QuantAlgo::MinMax:
@@ -291,6 +327,25 @@ void quantize(const void *src, void *dst, size_t count, const QuantParams &p) {
 
 void dequantize_reduce(void *dst, const void *q, size_t count, const QuantParams &p, RedOp op) {
     const bool f32 = p.value_dtype == DType::F32;
+    const bool add = op == RedOp::Sum || op == RedOp::Avg, set = op == RedOp::Set;
+    if (use_fast(p) && (add || set)) { // the other operators are rare with quantisation and keep the generic loops
+        auto *d = static_cast<float *>(dst);
+        const auto *c = static_cast<const uint8_t *>(q);
+        switch (p.algo) {
+        case QuantAlgo::MinMax:
+            (set ? fast::minmax_dequant_u8_set : fast::minmax_dequant_u8_add)(d, c, count, static_cast<float>(p.min), static_cast<float>(p.max));
+            return;
+        case QuantAlgo::ZeroPointScale: (set ? fast::zps_dequant_u8_set : fast::zps_dequant_u8_add)(d, c, count, p.scale, p.zero_point); return;
+        case QuantAlgo::BlockMinMax:
+            if (fast::cpu_has_fma()) {
+                (set ? fast::block_minmax_dequant_set_fma : fast::block_minmax_dequant_add_fma)(d, c, count);
+                return;
+            }
+            break;
+        case QuantAlgo::BlockFp8: (set ? fast::block_fp8_dequant_set : fast::block_fp8_dequant_add)(d, c, count); return;
+        default: break;
+        }
+    }
     switch (p.algo) {
     case QuantAlgo::None: break;
     case QuantAlgo::MinMax:

@@ -44,6 +44,10 @@ void dequantize_reduce(void *dst, const void *q, size_t count, const QuantParams
 wire::P2PDequantMeta to_wire(const QuantParams &p, uint64_t tag);
 bool from_wire(const wire::P2PDequantMeta &m, QuantParams &p); // fills the numeric fields only
 
+// Tests only: true routes everything through the generic (scalar, branchy) templates, which define the arithmetic; the
+// vectorised float32 / 8-bit paths must reproduce them bit for bit.  Also settable with PCCL_QUANT_GENERIC=1.
+void quant_force_generic(bool on);
+
 float fp8e4m3_to_f32(uint8_t v);
 uint8_t f32_to_fp8e4m3(float f); // round to nearest even, saturating at +-448
 

@@ -160,6 +160,59 @@ TEST(quantised_minmax_bit_identical) {
     }
 }
 
+// Large quantised operands: the sending half of every ring step (quantise in pieces, send each piece) runs on a helper beside
+// the receiving half, over a striped connection pool.  Whatever the interleaving, the result is a function of the inputs
+// alone: all peers agree bit for bit, and a second run gives the same bits as the first.
+TEST(large_quantised_operands_are_deterministic) {
+    TestMaster tm;
+    const int world = 3;
+    std::vector<std::unique_ptr<client::Client>> peers;
+    {
+        auto built = connect_peers(tm, world);
+        peers = std::move(built);
+    }
+    const size_t n = 3'000'017;
+    std::vector<std::vector<float>> in(world, std::vector<float>(n));
+    for (int r = 0; r < world; ++r)
+        for (size_t i = 0; i < n; ++i) in[r][i] = std::sin(0.0007f * static_cast<float>(i % 100'000) + r) * (1.0f + static_cast<float>(i % 7));
+    struct Case {
+        wire::QuantAlgo algo;
+        wire::DType code;
+        float tol;
+    };
+    for (const Case c : {Case{wire::QuantAlgo::MinMax, wire::DType::U8, 0.25f}, Case{wire::QuantAlgo::ZeroPointScale, wire::DType::U8, 0.25f},
+                         Case{wire::QuantAlgo::MinMax, wire::DType::U16, 0.002f}, Case{wire::QuantAlgo::BlockMinMax, wire::DType::U8, 0.25f},
+                         Case{wire::QuantAlgo::BlockFp8, wire::DType::F8E4M3, 1.2f}}) {
+        std::vector<std::vector<float>> first;
+        for (int run = 0; run < 2; ++run) {
+            std::vector<std::vector<float>> out(world);
+            std::vector<std::thread> ts;
+            for (int r = 0; r < world; ++r)
+                ts.emplace_back([&, r] {
+                    out[r] = in[r]; // in place
+                    ReduceRequest req;
+                    req.send = req.recv = out[r].data();
+                    req.count = n;
+                    req.op = wire::RedOp::Avg;
+                    req.quant = c.algo;
+                    req.quant_dtype = c.code;
+                    req.tag = 11;
+                    ReduceOutcome o;
+                    CHECK(peers[r]->all_reduce_sync(req, o) == client::Client::Launch::Ok);
+                    CHECK(o.ok);
+                });
+            for (auto &t : ts) t.join();
+            for (int r = 1; r < world; ++r) CHECK(std::memcmp(out[0].data(), out[r].data(), n * sizeof(float)) == 0);
+            for (size_t i = 0; i < n; i += 13) {
+                const float truth = (in[0][i] + in[1][i] + in[2][i]) / 3.0f;
+                CHECK(std::fabs(out[0][i] - truth) < c.tol);
+            }
+            if (run == 0) first = out;
+            else CHECK(std::memcmp(first[0].data(), out[0].data(), n * sizeof(float)) == 0);
+        }
+    }
+}
+
 TEST(quantised_block_formats) {
     for (auto algo : {wire::QuantAlgo::BlockMinMax, wire::QuantAlgo::BlockFp8}) {
         TestMaster tm;

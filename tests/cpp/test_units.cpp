@@ -21,6 +21,7 @@
 #include "kernels/cpu/half.hpp"
 #include "kernels/cpu/hash.hpp"
 #include "kernels/cpu/quantize.hpp"
+#include "kernels/cpu/quantize_fast.hpp"
 #include "kernels/cpu/reduce.hpp"
 #include "topo/atsp.hpp"
 #include "topo/bandwidth_store.hpp"
@@ -340,6 +341,132 @@ TEST(minmax_quantiser_matches_reference_formula) {
     back.min = back.max = 0;
     CHECK(cpu::from_wire(cpu::to_wire(p, 1), back));
     CHECK(back.min == p.min && back.max == p.max);
+}
+
+// The vectorised float32 / 8-bit paths against the generic templates that define the arithmetic: identical codes, identical
+// metadata, identical decoded values -- on ordinary data, on ragged lengths, and on the values where rounding decides.
+TEST(fast_quantisers_equal_the_generic_ones_bit_for_bit) {
+    std::mt19937_64 rng(99);
+    std::vector<std::vector<float>> inputs;
+    for (size_t n : {size_t(0), size_t(1), size_t(3), size_t(127), size_t(128), size_t(129), size_t(1000), size_t(65536 + 77)}) {
+        std::vector<float> x(n);
+        std::normal_distribution<float> normal(0.5f, 3.0f);
+        for (auto &v : x) v = normal(rng);
+        inputs.push_back(x);
+    }
+    { // values of very different magnitudes, exact ties, zeros of both signs, subnormals, huge values, a constant block
+        std::vector<float> x;
+        for (int e = -30; e <= 30; ++e)
+            for (float m : {1.0f, 1.0625f, 1.125f, 1.1875f, 1.5f, 1.9375f, 1.99999f}) x.push_back(std::ldexp(m, e)), x.push_back(-std::ldexp(m, e));
+        for (float v : {0.0f, -0.0f, 1e-40f, -1e-42f, 3.4e38f, -3.4e38f, 448.0f, 447.9f, 464.0f, 0.0009765625f, 0.00146484375f}) x.push_back(v);
+        x.resize(((x.size() + 127) / 128 + 1) * 128, 7.25f); // last block constant
+        inputs.push_back(x);
+        std::vector<float> same(300, -2.5f);
+        inputs.push_back(same);
+        std::vector<float> broken = inputs[6]; // a gradient that has gone wrong in places: same garbage out of both
+        broken[5] = std::numeric_limits<float>::quiet_NaN(), broken[200] = std::numeric_limits<float>::infinity(),
+        broken[700] = -std::numeric_limits<float>::infinity(), broken[701] = std::numeric_limits<float>::quiet_NaN();
+        inputs.push_back(broken);
+    }
+    struct Case {
+        QuantAlgo algo;
+        DType code;
+    };
+    for (const Case c : {Case{QuantAlgo::MinMax, DType::U8}, Case{QuantAlgo::ZeroPointScale, DType::U8}, Case{QuantAlgo::BlockMinMax, DType::U8},
+                         Case{QuantAlgo::BlockFp8, DType::F8E4M3}})
+        for (const auto &x : inputs) {
+            cpu::QuantParams pf, pg;
+            pf.algo = pg.algo = c.algo;
+            pf.code_dtype = pg.code_dtype = c.code;
+            std::vector<uint8_t> qf(cpu::quantized_size(pf, x.size()) + 1, 0xAB), qg(qf.size(), 0xAB);
+            std::vector<float> acc(x.size());
+            for (size_t i = 0; i < acc.size(); ++i) acc[i] = 0.1f * static_cast<float>(i % 17) - 0.5f;
+            std::vector<float> set_f(x.size(), 1.0f), set_g(x.size(), 1.0f), add_f = acc, add_g = acc, avg_f = acc, avg_g = acc;
+            cpu::quant_force_generic(false);
+            cpu::quant_analyze(x.data(), x.size(), pf);
+            cpu::quantize(x.data(), qf.data(), x.size(), pf);
+            cpu::dequantize_reduce(set_f.data(), qf.data(), x.size(), pf, RedOp::Set);
+            cpu::dequantize_reduce(add_f.data(), qf.data(), x.size(), pf, RedOp::Sum);
+            cpu::dequantize_reduce(avg_f.data(), qf.data(), x.size(), pf, RedOp::Avg);
+            cpu::quant_force_generic(true);
+            cpu::quant_analyze(x.data(), x.size(), pg);
+            cpu::quantize(x.data(), qg.data(), x.size(), pg);
+            cpu::dequantize_reduce(set_g.data(), qg.data(), x.size(), pg, RedOp::Set);
+            cpu::dequantize_reduce(add_g.data(), qg.data(), x.size(), pg, RedOp::Sum);
+            cpu::dequantize_reduce(avg_g.data(), qg.data(), x.size(), pg, RedOp::Avg);
+            cpu::quant_force_generic(false);
+            CHECK(pf.min == pg.min && pf.max == pg.max && pf.scale == pg.scale && pf.zero_point == pg.zero_point);
+            CHECK(qf == qg);
+            CHECK_EQ(qf.back(), uint8_t(0xAB)); // nothing written past the end
+            CHECK(std::memcmp(set_f.data(), set_g.data(), x.size() * 4) == 0);
+            CHECK(std::memcmp(add_f.data(), add_g.data(), x.size() * 4) == 0);
+            CHECK(std::memcmp(avg_f.data(), avg_g.data(), x.size() * 4) == 0);
+        }
+    // the fp8 conversions themselves: every code, and a few hundred million floats spread over all exponents (every 13th
+    // bit pattern would take a minute; a stride of 4099 covers each binade with thousands of mantissas, ties included)
+    for (int c = 0; c < 256; ++c) {
+        const float a = cpu::fp8e4m3_to_f32(static_cast<uint8_t>(c)), b = cpu::fast::fp8e4m3_to_f32_branchless(static_cast<uint8_t>(c));
+        CHECK(std::memcmp(&a, &b, 4) == 0);
+    }
+    uint64_t mismatches = 0;
+    for (uint64_t u = 0; u <= 0xffffffffull; u += 4099) {
+        const float f = std::bit_cast<float>(static_cast<uint32_t>(u));
+        mismatches += cpu::f32_to_fp8e4m3(f) != cpu::fast::f32_to_fp8e4m3_branchless(f);
+    }
+    for (int c = 0; c < 256; ++c) // exact code points and the midpoints between neighbours
+        for (int d = 0; d < 2; ++d) {
+            const float lo = cpu::fp8e4m3_to_f32(static_cast<uint8_t>(c)), hi = cpu::fp8e4m3_to_f32(static_cast<uint8_t>((c & 0x7f) == 0x7e ? c : c + 1));
+            const float f = d ? 0.5f * (lo + hi) : lo;
+            if (f == f) mismatches += cpu::f32_to_fp8e4m3(f) != cpu::fast::f32_to_fp8e4m3_branchless(f);
+        }
+    CHECK_EQ(mismatches, uint64_t(0));
+}
+
+// The 16-bit float loops (F16C instructions, branch-free bfloat16 rounding) against the conversions of half.hpp that define
+// them: every operator, the averaging division, every bit pattern on one side and awkward partners on the other.
+TEST(half_precision_reductions_equal_their_definition) {
+    std::vector<uint16_t> all(65536 + 5); // + a ragged tail
+    for (size_t i = 0; i < all.size(); ++i) all[i] = static_cast<uint16_t>(i);
+    std::mt19937 rng(5);
+    std::vector<uint16_t> partner(all.size());
+    for (auto &v : partner) v = static_cast<uint16_t>(rng());
+    const uint16_t special[] = {0x0000, 0x8000, 0x0001, 0x83ff, 0x0400, 0x3c00, 0xbc00, 0x7bff, 0xfbff, 0x7c00, 0xfc00, 0x7e00, 0x7c01, 0x7f80, 0xff80, 0x7fc0, 0x3f80};
+    for (size_t i = 0; i < partner.size(); i += 97) partner[i] = special[(i / 97) % (sizeof special / 2)];
+    struct Fmt {
+        DType dtype;
+        float (*load)(uint16_t);
+        uint16_t (*store)(float);
+    };
+    for (const Fmt f : {Fmt{DType::F16, cpu::f16_to_f32, cpu::f32_to_f16}, Fmt{DType::BF16, cpu::bf16_to_f32, cpu::f32_to_bf16}}) {
+        for (RedOp op : {RedOp::Sum, RedOp::Prod, RedOp::Max, RedOp::Min, RedOp::Set}) {
+            std::vector<uint16_t> got = all;
+            cpu::reduce_inplace(got.data(), partner.data(), got.size(), f.dtype, op);
+            size_t bad = 0;
+            for (size_t i = 0; i < all.size(); ++i) {
+                const float a = f.load(all[i]), b = f.load(partner[i]);
+                uint16_t want;
+                switch (op) {
+                case RedOp::Sum: want = f.store(a + b); break;
+                case RedOp::Prod: want = f.store(a * b); break;
+                case RedOp::Max: want = f.store(a > b ? a : b); break;
+                case RedOp::Min: want = f.store(a < b ? a : b); break;
+                default: want = partner[i]; break;
+                }
+                // two NaN operands: which of the two payloads (and signs) survives an x86 addition depends on the order the
+                // compiler hands them to the instruction, in the definition as much as in the fast loops; any NaN will do
+                if (a != a && b != b && op != RedOp::Set) want = f.store(f.load(got[i])) == got[i] && f.load(got[i]) != f.load(got[i]) ? got[i] : want;
+                bad += got[i] != want;
+            }
+            CHECK_EQ(bad, size_t(0));
+        }
+        for (uint64_t world : {uint64_t(2), uint64_t(3), uint64_t(7)}) {
+            std::vector<uint16_t> got = all;
+            cpu::finalize_avg(got.data(), got.size(), f.dtype, world);
+            size_t bad = 0;
+            for (size_t i = 0; i < all.size(); ++i) bad += got[i] != f.store(f.load(all[i]) / static_cast<float>(world));
+            CHECK_EQ(bad, size_t(0));
+        }
+    }
 }
 
 TEST(zero_point_scale_quantiser) {
