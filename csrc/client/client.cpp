@@ -439,8 +439,13 @@ void Client::build_hierarchy(const std::vector<Uuid> &ring) {
     h.cross_next = members[hosts[(h.box + 1) % B]][h.local_rank];
     h.cross_prev = members[hosts[(h.box + B - 1) % B]][h.local_rank];
     for (const Uuid *target : {&h.local_next, &h.cross_next}) {
-        bool have;
-        {
+        // A link to a ring neighbour is shared with the flat ring and was just confirmed by the establishment round.  Any
+        // other link left over from an earlier layout is dialled afresh: the far end may have dropped its half in a round
+        // in which this peer's neighbours did not change (so nothing was pruned here), and a sending socket does not notice
+        // that nobody is listening until it writes.
+        const bool ring_neighbour = std::any_of(last_neighbours_.begin(), last_neighbours_.end(), [&](const PeerEndpoint &p) { return p.uuid == *target; });
+        bool have = false;
+        if (ring_neighbour) {
             std::lock_guard<std::mutex> lock(tx_mu_);
             const auto it = tx_pools_.find(*target);
             have = it != tx_pools_.end() && !it->second.empty() &&
