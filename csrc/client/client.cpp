@@ -337,7 +337,8 @@ Client::Establish Client::establish_round() {
 // same number L >= 2 of peers each, links to the local successor and to the peer of equal local rank on the next host are
 // dialled.  Whether an operation then uses the hierarchy is agreed through the vote (bit 3 of the operator byte), so a peer
 // on which any of this failed -- or a reference peer, which does not forward the directory -- simply keeps the ring flat
-// for everybody.  The flat ring remains wired and is what quantised operations use.
+// for everybody.  The flat ring remains wired.  Quantised operations use the hierarchy too: plain values inside a host, codes
+// between hosts.
 void Client::build_hierarchy(const std::vector<Uuid> &ring) {
     {
         std::unique_lock<std::shared_mutex> lock(ring_mu_);
@@ -1485,7 +1486,7 @@ ReduceOutcome Client::run_reduce_impl(const ReduceRequest &req, uint64_t) {
         std::shared_lock<std::shared_mutex> lock(ring_mu_);
         hier = hier_;
     }
-    const bool offer_hierarchy = hier.ready && req.quant == QuantAlgo::None && hier.L * hier.B == world;
+    const bool offer_hierarchy = hier.ready && hier.L * hier.B == world;
     vote.op = static_cast<RedOp>(static_cast<uint8_t>(req.op) | (device_capable ? 0x80u : 0u) |
                                  ((caps & device::Plane::kCapNvls) ? 0x40u : 0u) | (offer_lease ? 0x20u : 0u) |
                                  (offer_lease && plane_->multicast_ready() ? 0x10u : 0u) | (offer_hierarchy ? 0x08u : 0u));

@@ -357,7 +357,7 @@ RingResult hierarchical_allreduce(const RingContext &local, const RingContext &c
     auto *dst = static_cast<uint8_t *>(a.dst);
     const bool in_place = a.src == a.dst;
     if (backup) backup->clear();
-    if (a.quant != QuantAlgo::None || local.world < 1 || cross.world < 1) return res;
+    if (local.world < 1 || cross.world < 1) return res;
     const uint32_t L = local.world, B = cross.world, l = local.rank;
     if ((L > 1 && (local.tx.empty() || local.tx.size() != local.rx.size())) || (B > 1 && (cross.tx.empty() || cross.tx.size() != cross.rx.size())))
         return res;
@@ -389,7 +389,10 @@ RingResult hierarchical_allreduce(const RingContext &local, const RingContext &c
         if (!rx_ok || !tx_ok) return fail();
     }
 
-    // ---- 2. the chunk this peer now owns, (l+1) mod L, is summed over the hosts by the peers of equal local rank
+    // ---- 2. the chunk this peer now owns, (l+1) mod L, is summed over the hosts by the peers of equal local rank.  A wire
+    //         quantisation applies here and only here: between hosts is where bytes are expensive.  The owner of every piece
+    //         adopts what the others decode (ring_allreduce), the local all-gather then copies exact bytes, so all L*B peers
+    //         end with identical bits.
     {
         uint64_t ob, oe;
         chunk_bounds(a.count, L, (l + 1) % L, ob, oe);

@@ -57,7 +57,8 @@ RingResult ring_allreduce(const RingContext &ctx, const ReduceArgs &args, std::v
 //   2. all-reduce of that chunk over the CROSS ring (the peers with the same local rank, one per host)
 //   3. all-gather over the local ring
 // Every byte crosses the inter-host links 2(B-1)/B times per local-rank lane instead of travelling around one ring of L*B
-// hops, and each inter-host link carries 1/L of the data.  Unquantised only.  `local` / `cross` carry the rank, world and
+// hops, and each inter-host link carries 1/L of the data.  A wire quantisation applies to step 2 only (codes between hosts, plain
+// values inside a host).  `local` / `cross` carry the rank, world and
 // connection pools of the two rings; tag, seq and abort callback are taken from `local`.
 RingResult hierarchical_allreduce(const RingContext &local, const RingContext &cross, const ReduceArgs &args, std::vector<uint8_t> *backup);
 

@@ -525,39 +525,78 @@ TEST(two_level_ring_three_hosts_of_two_and_two_hosts_of_three) {
     }
 }
 
-TEST(uneven_hosts_and_quantised_operations_keep_the_flat_ring) {
+TEST(uneven_hosts_keep_the_flat_ring) {
     TestMaster tm;
     auto peers = connect_on_hosts(tm, {1, 1, 1, 2});
     for (auto &p : peers) CHECK(p->hierarchy_shape() == std::make_pair(0u, 0u));
     reduce_everywhere<float>(peers, 4097, wire::RedOp::Sum, false, pcclExtPlaneTcpRing);
+}
 
-    // a quantised operation on a group that HAS a hierarchy is not offered to it: the codes go around the flat ring
-    TestMaster tm2;
-    auto even = connect_on_hosts(tm2, {1, 2, 1, 2});
-    for (auto &p : even) CHECK(p->hierarchy_shape() == std::make_pair(2u, 2u));
+// Quantised operations on a two-level ring: plain values inside a host, codes between hosts.  Every peer ends with the same
+// bits; the traffic of a peer is the local exchange in full precision plus the quantised exchange of its 1/L share.
+TEST(two_level_ring_quantises_between_hosts_only) {
+    TestMaster tm;
+    auto peers = connect_on_hosts(tm, {1, 2, 1, 2, 2, 1}); // 2 hosts x 3 peers
+    for (auto &p : peers) CHECK(p->hierarchy_shape() == std::make_pair(2u, 3u));
+    const int world = 6;
+    const size_t n = 600'011;
+    std::vector<std::vector<float>> in(world, std::vector<float>(n));
+    for (int r = 0; r < world; ++r)
+        for (size_t i = 0; i < n; ++i) in[r][i] = std::cos(0.001f * static_cast<float>(i % 50'000) + 0.5f * r) * 2.0f;
+    struct Case {
+        wire::QuantAlgo algo;
+        wire::DType code;
+        wire::RedOp op;
+        float tol;
+    };
+    for (const Case c : {Case{wire::QuantAlgo::ZeroPointScale, wire::DType::U8, wire::RedOp::Sum, 0.2f}, Case{wire::QuantAlgo::MinMax, wire::DType::U8, wire::RedOp::Avg, 0.05f},
+                         Case{wire::QuantAlgo::BlockFp8, wire::DType::F8E4M3, wire::RedOp::Avg, 0.2f}}) {
+        std::vector<std::vector<float>> out(world, std::vector<float>(n));
+        std::vector<uint64_t> tx(world);
+        std::vector<std::thread> ts;
+        for (int r = 0; r < world; ++r)
+            ts.emplace_back([&, r] {
+                ReduceRequest req;
+                req.send = in[r].data();
+                req.recv = out[r].data();
+                req.count = n;
+                req.op = c.op;
+                req.quant = c.algo;
+                req.quant_dtype = c.code;
+                req.tag = 6;
+                ReduceOutcome o;
+                CHECK(peers[r]->all_reduce_sync(req, o) == client::Client::Launch::Ok);
+                CHECK(o.ok);
+                CHECK_EQ(static_cast<int>(o.stats.plane), static_cast<int>(pcclExtPlaneTcpHierarchical));
+                tx[r] = o.tx_bytes;
+            });
+        for (auto &t : ts) t.join();
+        for (int r = 1; r < world; ++r) CHECK(std::memcmp(out[0].data(), out[r].data(), n * sizeof(float)) == 0);
+        for (size_t i = 0; i < n; i += 7) {
+            float truth = 0;
+            for (int r = 0; r < world; ++r) truth += in[r][i];
+            if (c.op == wire::RedOp::Avg) truth /= world;
+            CHECK(std::fabs(out[0][i] - truth) < c.tol);
+        }
+        // local ring of 3: 2 x 2/3 of the tensor in fp32; cross ring of 2: 2 x 1/2 of the owned third in 8-bit codes
+        const double local_bytes = 2.0 * (2.0 / 3.0) * n * 4, cross_bytes = 2.0 * 0.5 * (n / 3.0) * 1.07;
+        for (int r = 0; r < world; ++r) CHECK(std::fabs(static_cast<double>(tx[r]) - (local_bytes + cross_bytes)) < 0.05 * (local_bytes + cross_bytes));
+    }
+    // the constants of the reference's anchor test come out exact through both levels: 6 peers x 42 = 252
+    std::vector<std::vector<float>> out(world, std::vector<float>(2048));
     std::vector<std::thread> ts;
-    std::vector<std::vector<float>> out(4, std::vector<float>(2048));
-    for (int r = 0; r < 4; ++r)
+    for (int r = 0; r < world; ++r)
         ts.emplace_back([&, r] {
-            std::vector<float> in(2048, 42.0f + static_cast<float>(r));
+            std::vector<float> x(2048, 42.0f);
             ReduceRequest req;
-            req.send = in.data();
-            req.recv = out[r].data();
-            req.count = in.size();
-            req.dtype = wire::DType::F32;
-            req.op = wire::RedOp::Sum;
-            req.quant = wire::QuantAlgo::ZeroPointScale;
-            req.quant_dtype = wire::DType::U8;
-            req.tag = 6;
+            req.send = x.data(), req.recv = out[r].data(), req.count = x.size(), req.op = wire::RedOp::Sum;
+            req.quant = wire::QuantAlgo::ZeroPointScale, req.quant_dtype = wire::DType::U8, req.tag = 7;
             ReduceOutcome o;
-            CHECK(even[r]->all_reduce_sync(req, o) == client::Client::Launch::Ok);
-            CHECK(o.ok);
-            CHECK_EQ(static_cast<int>(o.stats.plane), static_cast<int>(pcclExtPlaneTcpRing));
+            CHECK(peers[r]->all_reduce_sync(req, o) == client::Client::Launch::Ok && o.ok);
         });
     for (auto &t : ts) t.join();
-    for (int r = 0; r < 4; ++r)
-        for (float v : out[r]) CHECK(std::fabs(v - 174.0f) < 1e-3f);
-    reduce_everywhere<float>(even, 4097, wire::RedOp::Sum, false, pcclExtPlaneTcpHierarchical); // and the next plain one uses it again
+    for (int r = 0; r < world; ++r)
+        for (float v : out[r]) CHECK(v == 252.0f);
 }
 
 // ---- lease extension of the collective vote, spoken by hand: two scripted peers on raw sockets (a real peer only offers a

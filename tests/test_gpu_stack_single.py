@@ -32,7 +32,7 @@ def test_outer_step_two_peers_one_gpu():
 
 def test_two_level_ring_with_device_tensors():
     """Four peers on this GPU pretend to be two hosts of two (PCCL_HOST_ID): device tensors are staged and reduced over the
-    local ring, the ring between hosts and the local ring again; quantised operations keep the flat ring."""
+    local ring, the ring between hosts and the local ring again."""
     hosts = [{"PCCL_HOST_ID": h} for h in ("north", "south", "north", "south")]
     small = {"PCCL_ARENA_SLOT_MB": "64", "PCCL_SYMMETRIC_MB": "128"}
     results = run_peers(4, "allreduce", devices=["cuda:0"] * 4, env=small, rank_env=hosts)
@@ -41,7 +41,7 @@ def test_two_level_ring_with_device_tensors():
         for c in r["cases"]:
             assert c["ok"], c
             by_case.setdefault(c["id"], set()).add(c["hash"])
-    assert {c["plane"] for r in results for c in r["cases"]} == {"tcp_hierarchical", "tcp_ring"}
+    assert {c["plane"] for r in results for c in r["cases"]} == {"tcp_hierarchical"}
     assert all(len(h) == 1 for h in by_case.values()), "peers disagree bit-wise"
     stepped = run_peers(4, "outer_step", devices=["cuda:0"] * 4, env=small, rank_env=hosts)
     assert all(r["ok"] for r in stepped), stepped

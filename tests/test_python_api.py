@@ -201,7 +201,7 @@ def test_multi_process_peers_on_cpu(scenario):
 
 def test_two_level_ring_between_pretended_hosts():
     """PCCL_HOST_ID tells peers which machine they are on; two "hosts" of two peers reduce over a local ring and a ring
-    between hosts.  Quantised operations stay on the flat ring (their codes are made for one hop pattern)."""
+    between hosts; quantised operations too (codes travel between the hosts only)."""
     hosts = [{"PCCL_HOST_ID": h} for h in ("left", "right", "left", "right")]
     results = run_peers(4, "allreduce", devices=["cpu"] * 4, rank_env=hosts)
     by_case = {}
@@ -211,7 +211,7 @@ def test_two_level_ring_between_pretended_hosts():
         for c in r["cases"]:
             by_case.setdefault(c["id"], set()).add(c["hash"])
             planes.add(c["plane"])
-    assert planes == {"tcp_hierarchical", "tcp_ring"}, planes
+    assert planes == {"tcp_hierarchical"}, planes
     assert all(len(h) == 1 for h in by_case.values()), "peers disagree bit-wise"
     # the DiLoCo outer step of host tensors reduces its pseudo-gradients the same way
     stepped = run_peers(4, "outer_step", devices=["cpu"] * 4, rank_env=hosts)
