@@ -6,6 +6,8 @@
 #include <cstdlib>
 #include <random>
 
+#include <numeric>
+
 #include "e2e_util.hpp"
 #include "pccl.h"
 
@@ -251,6 +253,51 @@ TEST(peer_loss_on_a_two_level_ring) {
     CHECK_EQ(survivors_ok.load(), 3);
     CHECK_EQ(peers[0]->local_world(), 3u);
     for (int r = 0; r < 3; ++r) CHECK(peers[r]->hierarchy_shape() == std::make_pair(0u, 0u));
+}
+
+// Two dozen peers in one run, three groups of eight: admission one by one (every admission is a vote of everybody already
+// in), ring per group, concurrent reductions in all groups, then a third of the peers leave at once and the rest carry on.
+TEST(two_dozen_peers_three_groups) {
+    TestMaster tm;
+    const int n_peers = std::getenv("PCCL_TEST_MANY_PEERS") ? 3 * (std::atoi(std::getenv("PCCL_TEST_MANY_PEERS")) / 3) : 24;
+    const uint32_t per_group = static_cast<uint32_t>(n_peers / 3);
+    std::vector<uint32_t> groups(n_peers);
+    for (int i = 0; i < n_peers; ++i) groups[i] = static_cast<uint32_t>(i % 3);
+    auto peers = connect_peers(tm, n_peers, groups);
+    CHECK_EQ(peers[0]->global_world(), uint64_t(n_peers));
+    CHECK_EQ(peers[0]->local_world(), per_group);
+    CHECK_EQ(peers[0]->num_groups(), 3u);
+    auto reduce_all = [&](const std::vector<int> &who, uint32_t want_world, uint64_t tag) {
+        std::vector<std::thread> ts;
+        std::atomic<int> good{0};
+        for (int r : who)
+            ts.emplace_back([&, r] {
+                std::vector<int32_t> in(50'000, r % 3 + 1), out(50'000);
+                ReduceRequest q;
+                q.send = in.data(), q.recv = out.data(), q.count = in.size(), q.dtype = wire::DType::I32, q.op = wire::RedOp::Sum, q.tag = tag;
+                ReduceOutcome o;
+                if (peers[r]->all_reduce_sync(q, o) != client::Client::Launch::Ok || !o.ok) return;
+                if (o.world == want_world && out[0] == static_cast<int32_t>(want_world) * (r % 3 + 1) && out.back() == out[0]) good++;
+            });
+        for (auto &t : ts) t.join();
+        return good.load();
+    };
+    std::vector<int> everybody(n_peers);
+    std::iota(everybody.begin(), everybody.end(), 0);
+    CHECK_EQ(reduce_all(everybody, per_group, 1), n_peers);
+    // peers 0..8 vanish (three from every group); the others notice at their next joint call
+    for (int r = 0; r < 9; ++r) peers[r]->interrupt();
+    std::vector<int> rest;
+    for (int r = 9; r < n_peers; ++r) rest.push_back(r);
+    bool settled = false;
+    for (int attempt = 0; attempt < 20 && !settled; ++attempt) {
+        std::vector<std::thread> ts;
+        for (int r : rest) ts.emplace_back([&, r] { peers[r]->update_topology(); });
+        for (auto &t : ts) t.join();
+        settled = peers[9]->global_world() == uint64_t(n_peers - 9) && peers[9]->local_world() == per_group - 3;
+    }
+    CHECK(settled);
+    CHECK_EQ(reduce_all(rest, per_group - 3, 2), n_peers - 9);
 }
 
 // pcclAllReduceMultipleWithRetry keeps going when a peer vanishes
