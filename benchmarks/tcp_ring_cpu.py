@@ -65,19 +65,40 @@ def peer(args) -> None:
                 if i >= 2:
                     times.append(time.perf_counter() - t0)
             rows.append({"bytes": n * 4, "quant": quant or "none", "median_s": statistics.median(times), "min_s": min(times), "reps": reps})
+    # shared state: rank 0 holds the content everybody must end up with (two peers of the majority would be needed for an
+    # election; SEND_ONLY / RECEIVE_ONLY states it directly), then a second synchronisation in which nothing differs
+    revision = 0  # one counter for the whole run: the master expects every synchronisation to carry the next number
+    for size in args.state_sizes:
+        n = max(1, size // 4)
+        w = np.full(n, 1.0 + (0 if args.rank == 0 else args.rank), dtype=np.float32)
+        state = pccl.SharedState([pccl.TensorInfo.from_numpy(w, "w")])
+        state.revision = revision
+        strategy = pccl.SharedStateSyncStrategy.SEND_ONLY if args.rank == 0 else pccl.SharedStateSyncStrategy.RECEIVE_ONLY
+        t0 = time.perf_counter()
+        info = comm.sync_shared_state(state, strategy)
+        t_move = time.perf_counter() - t0
+        assert float(w[0]) == 1.0 and float(w[-1]) == 1.0
+        state.revision = revision + 1
+        t0 = time.perf_counter()
+        info2 = comm.sync_shared_state(state)
+        t_check = time.perf_counter() - t0
+        revision += 2
+        assert info2.tx_bytes == 0 and info2.rx_bytes == 0
+        rows.append({"bytes": n * 4, "quant": "shared_state", "median_s": t_move, "min_s": t_check, "reps": 1,
+                     "moved": int(info.tx_bytes + info.rx_bytes)})
     print("ROWS " + json.dumps(rows), flush=True)
     if hasattr(comm, "destroy"):
         comm.destroy()
 
 
-def run(impl: str, world: int, sizes, pool: int):
+def run(impl: str, world: int, sizes, pool: int, state_sizes=()):
     pccl = load(impl)
     port = 48700 + world + (50 if impl == "reference" else 0)
     master = pccl.MasterNode(f"127.0.0.1:{port}")
     master.run()
     env = dict(os.environ, OMP_NUM_THREADS="2")
     procs = [subprocess.Popen([sys.executable, __file__, "--as-peer", "--impl", impl, "--rank", str(r), "--world", str(world), "--port", str(port),
-                               "--pool", str(pool), "--sizes", *map(str, sizes)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True, env=env)
+                               "--pool", str(pool), "--state-sizes", *map(str, state_sizes), "--sizes", *map(str, sizes)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True, env=env)
              for r in range(world)]
     per_peer = []
     for p in procs:
@@ -88,6 +109,10 @@ def run(impl: str, world: int, sizes, pool: int):
     master.interrupt()
     for i, row in enumerate(per_peer[0]):
         t = max(pp[i]["median_s"] for pp in per_peer)
+        if row["quant"] == "shared_state":
+            print(json.dumps({"impl": impl, "peers": world, "bytes": row["bytes"], "what": "shared_state", "sync_ms": round(t * 1e3, 3),
+                              "GBps": round(row["bytes"] / t / 1e9, 3), "recheck_ms": round(max(pp[i]["min_s"] for pp in per_peer) * 1e3, 3)}), flush=True)
+            continue
         print(json.dumps({"impl": impl, "peers": world, "bytes": row["bytes"], "quant": row["quant"], "ms": round(t * 1e3, 4),
                           "bus_GBps": round(row["bytes"] * 2 * (world - 1) / world / t / 1e9, 3), "reps": row["reps"], "pool": pool}), flush=True)
 
@@ -97,6 +122,7 @@ def main():
     ap.add_argument("--impl", nargs="+", default=["ours", "reference"])
     ap.add_argument("--peers", nargs="+", type=int, default=[2, 4])
     ap.add_argument("--sizes", nargs="+", type=int, default=[1 << 10, 1 << 16, 1 << 20, 1 << 24, 1 << 26, 1 << 28])
+    ap.add_argument("--state-sizes", nargs="*", type=int, default=[])
     ap.add_argument("--pool", type=int, default=4)
     ap.add_argument("--as-peer", action="store_true")
     ap.add_argument("--rank", type=int, default=0)
@@ -112,7 +138,7 @@ def main():
             print(json.dumps({"impl": "reference", "unavailable": "baseline/_ref is not installed (python baseline/install_reference.py)"}))
             continue
         for world in args.peers:
-            run(impl, world, args.sizes, args.pool)
+            run(impl, world, args.sizes, args.pool, args.state_sizes)
 
 
 if __name__ == "__main__":

@@ -2,6 +2,10 @@
 #include <cstring>
 
 #include "../crc_gf.hpp"
+#include <algorithm>
+#include <thread>
+#include <vector>
+
 #include "hash.hpp"
 
 #if defined(__x86_64__)
@@ -137,12 +141,37 @@ uint32_t crc32c_generic(const void *data, size_t n_bytes) {
     return ~raw_generic(0xFFFFFFFFu, static_cast<const uint8_t *>(data), n_bytes);
 }
 
-uint32_t crc32c(const void *data, size_t n_bytes) {
+namespace {
+uint32_t crc32c_one_thread(const void *data, size_t n_bytes) {
 #if defined(__x86_64__)
     if (!g_force_generic && crc32c_hardware_available())
         return ~raw_sse42(0xFFFFFFFFu, static_cast<const uint8_t *>(data), n_bytes);
 #endif
     return crc32c_generic(data, n_bytes);
+}
+} // namespace
+
+// Large buffers are cut into one piece per thread; crc(A||B) follows from crc(A), crc(B) and the length of B (the same
+// algebra the device kernel uses to combine its lanes), so the pieces are hashed independently.
+uint32_t crc32c(const void *data, size_t n_bytes) {
+    const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
+    const size_t n_threads = std::min<size_t>(std::min(8u, std::max(1u, hw / 2)), n_bytes / (4u << 20));
+    if (n_threads <= 1) return crc32c_one_thread(data, n_bytes);
+    const auto *bytes = static_cast<const uint8_t *>(data);
+    const size_t per = ((n_bytes + n_threads - 1) / n_threads + 63) / 64 * 64;
+    std::vector<uint32_t> part(n_threads, 0);
+    std::vector<size_t> len(n_threads, 0);
+    std::vector<std::thread> pool;
+    for (size_t t = 0; t < n_threads; ++t) {
+        const size_t lo = std::min(n_bytes, t * per), hi = std::min(n_bytes, lo + per);
+        len[t] = hi - lo;
+        pool.emplace_back([&, t, lo] { part[t] = crc32c_one_thread(bytes + lo, len[t]); });
+    }
+    for (auto &th : pool) th.join();
+    uint32_t crc = part[0];
+    for (size_t t = 1; t < n_threads; ++t)
+        if (len[t]) crc = crc32c_combine(crc, part[t], len[t]);
+    return crc;
 }
 
 uint32_t crc32c_combine(uint32_t crc_a, uint32_t crc_b, uint64_t len_b) {

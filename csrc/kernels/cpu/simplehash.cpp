@@ -22,20 +22,37 @@ uint32_t warp_fold(const uint32_t *lanes) {
     return v[0];
 }
 
+// The slab of one virtual block: virtual thread t folds packets t, t+256, t+512, ...  Walking the slab row by row (256
+// consecutive packets, one per virtual thread) keeps 256 independent chains going, which the compiler turns into vector
+// code (interleaved loads, packed multiply and rotate): several times the speed of following one chain at a time, same value.
+#if defined(__x86_64__) && defined(__GNUC__) && !defined(__clang__) && !defined(__SANITIZE_ADDRESS__) && !defined(__SANITIZE_THREAD__)
+__attribute__((target_clones("arch=x86-64-v4", "arch=x86-64-v3", "default")))
+#endif
 uint32_t block_partial(const uint32_t *words, uint64_t vec_begin, uint64_t vec_end) {
-    uint32_t per_thread[kSimpleHashThreads];
-    for (uint32_t t = 0; t < kSimpleHashThreads; ++t) {
-        uint32_t h = 0;
-        for (uint64_t i = vec_begin + t; i < vec_end; i += kSimpleHashThreads) {
-            const uint32_t *w = words + i * 4;
-            h = hash_combine(h, w[0]);
-            h = hash_combine(h, w[1]);
-            h = hash_combine(h, w[2]);
-            h = hash_combine(h, w[3]);
+    uint32_t h[kSimpleHashThreads];
+    for (uint32_t t = 0; t < kSimpleHashThreads; ++t) h[t] = 0;
+    uint64_t i = vec_begin;
+    for (; i + kSimpleHashThreads <= vec_end; i += kSimpleHashThreads) {
+        const uint32_t *w = words + i * 4;
+        for (uint32_t t = 0; t < kSimpleHashThreads; ++t) {
+            uint32_t x = h[t];
+            x = hash_combine(x, w[4 * t]);
+            x = hash_combine(x, w[4 * t + 1]);
+            x = hash_combine(x, w[4 * t + 2]);
+            x = hash_combine(x, w[4 * t + 3]);
+            h[t] = x;
         }
-        per_thread[t] = h;
     }
-    return simplehash_block_fold(per_thread);
+    const uint32_t *w = words + i * 4;
+    for (uint32_t t = 0; i + t < vec_end; ++t) {
+        uint32_t x = h[t];
+        x = hash_combine(x, w[4 * t]);
+        x = hash_combine(x, w[4 * t + 1]);
+        x = hash_combine(x, w[4 * t + 2]);
+        x = hash_combine(x, w[4 * t + 3]);
+        h[t] = x;
+    }
+    return simplehash_block_fold(h);
 }
 
 } // namespace
