@@ -396,7 +396,8 @@ void Client::build_hierarchy(const std::vector<Uuid> &ring) {
     }
     for (const auto &e : mine.entries) merge(e);
     P2PDirectory cur = mine;
-    const auto deadline = clock_type::now() + std::chrono::seconds(3);
+    // the packet makes W-1 hops, each of them a one-way trip between two peers that may be an ocean apart
+    const auto deadline = clock_type::now() + std::chrono::seconds(3) + std::chrono::milliseconds(150) * W;
     for (uint32_t step = 0; step + 1 < W; ++step) {
         if (!tx[0]->send_packet(kDirectoryTag, seq, cur)) return;
         std::optional<P2PDirectory> got;
