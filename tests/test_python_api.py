@@ -415,3 +415,51 @@ print("NUMPY ONLY OK")
 '''
     proc = subprocess.run([sys.executable, "-c", code, str(REPO)], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=180)
     assert proc.returncode == 0 and "NUMPY ONLY OK" in proc.stdout, proc.stdout[-3000:]
+
+
+def test_package_works_without_numpy():
+    """torch-only installation (reference: python/tests/pytorch_only_tests/pytorch_only_test.py): the same with `numpy`
+    made unimportable and torch tensors as operands and shared state."""
+    code = r'''
+import sys, threading, warnings
+warnings.filterwarnings("ignore")
+sys.modules["numpy"] = None
+sys.path.insert(0, sys.argv[1])
+import torch
+import pccl_b200 as pccl
+with pccl.MasterNode("127.0.0.1:0") as m:
+    m.run()
+    lone = pccl.Communicator(f"127.0.0.1:{m.port}")
+    lone.connect()
+    arr = torch.rand(27)
+    try:
+        lone.all_reduce_async(arr, arr, op=pccl.ReduceOp.SUM)
+        raise SystemExit("a single peer must not be able to reduce")
+    except pccl.PCCLError:
+        pass
+    out = {}
+    def second():
+        c = pccl.Communicator(f"127.0.0.1:{m.port}")
+        c.connect(n_attempts=10)
+        w = torch.zeros(100)
+        info = c.sync_shared_state(pccl.SharedState([pccl.TensorInfo.from_torch(w, "w")]))
+        x = torch.full((1000,), 2.0)
+        c.all_reduce(x, x, op=pccl.ReduceOp.AVG)
+        out[1] = (float(x[0]), float(w[7]), info.rx_bytes)
+        c.destroy()
+    t = threading.Thread(target=second); t.start()
+    while lone.get_attribute(pccl.Attribute.GLOBAL_WORLD_SIZE) < 2:
+        lone.update_topology()
+    w = torch.full((100,), 5.0)
+    state = pccl.SharedState([pccl.TensorInfo.from_torch(w, "w")])
+    state.revision = 1                       # ahead of the newcomer: this content is what the group holds
+    lone.sync_shared_state(state)
+    x = torch.full((1000,), 1.0)
+    lone.all_reduce(x, x, op=pccl.ReduceOp.AVG)
+    t.join(timeout=60)
+    assert float(x[0]) == 1.5 and out[1] == (1.5, 5.0, 400), (x[0], out)
+    lone.destroy()
+print("TORCH ONLY OK")
+'''
+    proc = subprocess.run([sys.executable, "-c", code, str(REPO)], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=180)
+    assert proc.returncode == 0 and "TORCH ONLY OK" in proc.stdout, proc.stdout[-3000:]
