@@ -22,6 +22,7 @@ from pathlib import Path
 
 REPO = Path(__file__).resolve().parent.parent
 REF = REPO / "baseline" / "_ref"
+STATE_TENSORS = 1
 
 
 def load(impl: str):
@@ -71,7 +72,8 @@ def peer(args) -> None:
     for size in args.state_sizes:
         n = max(1, size // 4)
         w = np.full(n, 1.0 + (0 if args.rank == 0 else args.rank), dtype=np.float32)
-        state = pccl.SharedState([pccl.TensorInfo.from_numpy(w, "w")])
+        parts = np.array_split(w, args.state_tensors)  # views: a model is many tensors, not one
+        state = pccl.SharedState([pccl.TensorInfo.from_numpy(p, f"w{i}") for i, p in enumerate(parts)])
         state.revision = revision
         strategy = pccl.SharedStateSyncStrategy.SEND_ONLY if args.rank == 0 else pccl.SharedStateSyncStrategy.RECEIVE_ONLY
         t0 = time.perf_counter()
@@ -98,7 +100,7 @@ def run(impl: str, world: int, sizes, pool: int, state_sizes=()):
     master.run()
     env = dict(os.environ, OMP_NUM_THREADS="2")
     procs = [subprocess.Popen([sys.executable, __file__, "--as-peer", "--impl", impl, "--rank", str(r), "--world", str(world), "--port", str(port),
-                               "--pool", str(pool), "--state-sizes", *map(str, state_sizes), "--sizes", *map(str, sizes)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True, env=env)
+                               "--pool", str(pool), "--state-tensors", str(STATE_TENSORS), "--state-sizes", *map(str, state_sizes), "--sizes", *map(str, sizes)], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True, env=env)
              for r in range(world)]
     per_peer = []
     for p in procs:
@@ -123,12 +125,15 @@ def main():
     ap.add_argument("--peers", nargs="+", type=int, default=[2, 4])
     ap.add_argument("--sizes", nargs="+", type=int, default=[1 << 10, 1 << 16, 1 << 20, 1 << 24, 1 << 26, 1 << 28])
     ap.add_argument("--state-sizes", nargs="*", type=int, default=[])
+    ap.add_argument("--state-tensors", type=int, default=1)
     ap.add_argument("--pool", type=int, default=4)
     ap.add_argument("--as-peer", action="store_true")
     ap.add_argument("--rank", type=int, default=0)
     ap.add_argument("--world", type=int, default=2)
     ap.add_argument("--port", type=int, default=0)
     args = ap.parse_args()
+    global STATE_TENSORS
+    STATE_TENSORS = args.state_tensors
     if args.as_peer:
         args.impl = args.impl[0]
         peer(args)

@@ -36,7 +36,7 @@ Client::Client(const ClientConfig &cfg)
     if (cfg_.pool_size == 0) cfg_.pool_size = 1;
     const size_t n_workers = static_cast<size_t>(env_u64("PCCL_MAX_CONCURRENT_COLLECTIVE_OPS", 16));
     workers_ = std::make_unique<ThreadPool>(std::max<size_t>(1, n_workers), 64);
-    ss_workers_ = std::make_unique<ThreadPool>(2, 64);
+    ss_workers_ = std::make_unique<ThreadPool>(4, 64); // a requester may fetch over several connections at once
     bm_workers_ = std::make_unique<ThreadPool>(static_cast<size_t>(env_u64("PCCL_NUM_BENCHMARK_CONNECTIONS", 16)) + 1, 64);
     lease_enabled_ = env_flag("PCCL_LEASE", true);
     // which host this peer runs on, for the two-level all-reduce of groups that span hosts
@@ -627,6 +627,17 @@ bool Client::optimize_topology() {
 namespace {
 constexpr size_t kStageBytes = 8u << 20;
 
+// Whether the peer of a connected socket is this machine (the kernel picked the same address for both ends).
+bool same_host(int fd) {
+    sockaddr_storage a{}, b{};
+    socklen_t la = sizeof a, lb = sizeof b;
+    if (getsockname(fd, reinterpret_cast<sockaddr *>(&a), &la) != 0 || getpeername(fd, reinterpret_cast<sockaddr *>(&b), &lb) != 0) return true;
+    if (a.ss_family != b.ss_family) return false;
+    if (a.ss_family == AF_INET)
+        return reinterpret_cast<sockaddr_in *>(&a)->sin_addr.s_addr == reinterpret_cast<sockaddr_in *>(&b)->sin_addr.s_addr;
+    return std::memcmp(&reinterpret_cast<sockaddr_in6 *>(&a)->sin6_addr, &reinterpret_cast<sockaddr_in6 *>(&b)->sin6_addr, 16) == 0;
+}
+
 // two page-locked staging buffers for the socket <-> GPU pipelines of the shared-state transfer
 class PinnedPair {
 public:
@@ -809,6 +820,20 @@ bool Client::sync_shared_state(SharedStateArgs &state, uint64_t &tx_bytes, uint6
             job_entry.push_back(i);
         }
     }
+    { // host tensors that still need a hash: several at a time
+        std::vector<const void *> ptrs;
+        std::vector<size_t> sizes, idx;
+        for (size_t i = 0; i < state.entries.size(); ++i) {
+            const auto &e = state.entries[i];
+            if (e.allow_content_inequality || e.on_device || have[i]) continue;
+            ptrs.push_back(e.data), sizes.push_back(e.bytes()), idx.push_back(i);
+        }
+        if (ptrs.size() > 1) {
+            std::vector<uint64_t> out(ptrs.size(), 0);
+            cpu::hash_many(ptrs.data(), sizes.data(), ptrs.size(), static_cast<int>(hash_type), out.data());
+            for (size_t k = 0; k < idx.size(); ++k) hashes[idx[k]] = out[k], have[idx[k]] = true;
+        }
+    }
     if (!jobs.empty()) {
         if (plane_->hash_device_many(jobs, hash_type)) {
             for (size_t j = 0; j < jobs.size(); ++j) {
@@ -865,9 +890,108 @@ bool Client::sync_shared_state(SharedStateArgs &state, uint64_t &tx_bytes, uint6
             PLOG(ERR) << "cannot reach shared-state distributor " << net::to_string(verdict->distributor);
             return false;
         }
+        // One tensor of the plain stream: straight into host memory, or socket -> page-locked buffer -> GPU with the copy of
+        // chunk k overlapping the receive of chunk k+1.
+        auto receive_tensor = [&](net::BlockingSocket &from, PinnedPair &stage, const SharedEntry &e, size_t bytes) {
+            if (!e.on_device) return from.recv_raw(e.data, bytes);
+            if (!stage.ok()) return false;
+            auto *dst = static_cast<uint8_t *>(e.data);
+            std::future<bool> pending;
+            size_t k = 0;
+            for (size_t off = 0; off < bytes; off += kStageBytes, ++k) {
+                const size_t n = std::min<size_t>(kStageBytes, bytes - off);
+                const bool got = from.recv_raw(stage.buf(k & 1), n);
+                if (pending.valid() && !pending.get()) return false; // the buffer received into next is free again
+                if (!got) return false;
+                pending = std::async(std::launch::async, [&, k, off, n] { return plane_->copy_to_device(dst + off, stage.buf(k & 1), n); });
+            }
+            return !pending.valid() || pending.get();
+        };
+        auto entry_of = [&](const std::string &key) -> const SharedEntry * {
+            const auto it = std::find_if(state.entries.begin(), state.entries.end(), [&](const SharedEntry &e) { return e.key == key; });
+            return it == state.entries.end() ? nullptr : &*it;
+        };
+
         // Ask with the extended request when this peer has a device plane that could take the data
-        // over NVLink; the distributor answers whether it can.
-        const bool try_p2p = plane_->exchange_bytes() > 0;
+        // over NVLink; the distributor answers whether it can.  A distributor on another machine cannot.  A large transfer
+        // that has to go through sockets is split over several connections: one TCP stream rarely fills a long fat pipe.  Every
+        // connection asks for a contiguous run of the outdated tensors with the reference's plain request, so any distributor
+        // can serve it.
+        const bool remote = !same_host(sock.fd());
+        const bool try_p2p = plane_->exchange_bytes() > 0 && !remote;
+        uint64_t want_bytes = 0;
+        for (const auto &key : verdict->outdated_keys)
+            if (const SharedEntry *e = entry_of(key)) want_bytes += e->bytes();
+        size_t n_streams = static_cast<size_t>(env_u64("PCCL_SHARED_STATE_CONNECTIONS", 4));
+        n_streams = std::min<size_t>({std::max<size_t>(n_streams, 1), verdict->outdated_keys.size(), 16});
+        if (want_bytes < (32u << 20)) n_streams = 1;
+        if (!try_p2p && n_streams > 1) {
+            // contiguous runs of about equal size
+            std::vector<std::pair<size_t, size_t>> runs; // [first, last) into outdated_keys
+            {
+                const uint64_t per = (want_bytes + n_streams - 1) / n_streams;
+                size_t first = 0;
+                uint64_t acc = 0;
+                for (size_t i = 0; i < verdict->outdated_keys.size(); ++i) {
+                    const SharedEntry *e = entry_of(verdict->outdated_keys[i]);
+                    if (!e) return false;
+                    acc += e->bytes();
+                    if (acc >= per && runs.size() + 1 < n_streams) {
+                        runs.push_back({first, i + 1});
+                        first = i + 1;
+                        acc = 0;
+                    }
+                }
+                if (first < verdict->outdated_keys.size()) runs.push_back({first, verdict->outdated_keys.size()});
+            }
+            PLOG(DEBUG) << "fetching " << want_bytes << " bytes of shared state over " << runs.size() << " connections";
+            std::vector<uint64_t> revisions(runs.size(), 0), moved(runs.size(), 0);
+            std::vector<char> good(runs.size(), 0);
+            std::vector<std::thread> streams;
+            for (size_t g = 0; g < runs.size(); ++g)
+                streams.emplace_back([&, g] {
+                    std::unique_ptr<net::BlockingSocket> own;
+                    net::BlockingSocket *link = &sock;
+                    if (g > 0) {
+                        own = std::make_unique<net::BlockingSocket>(verdict->distributor);
+                        if (!own->connect(10000)) return;
+                        link = own.get();
+                    }
+                    C2SRequestSharedState req;
+                    req.keys.assign(verdict->outdated_keys.begin() + runs[g].first, verdict->outdated_keys.begin() + runs[g].second);
+                    if (!link->send_packet(req)) return;
+                    const auto resp = link->recv_packet<S2CSharedStateResponse>(60000);
+                    if (!resp || resp->status != SharedStateStatus::Success || resp->entries.size() != req.keys.size()) return;
+                    revisions[g] = resp->revision;
+                    PinnedPair stage(*plane_);
+                    for (const auto &slice : resp->entries) {
+                        const SharedEntry *e = entry_of(slice.key);
+                        if (!e || e->bytes() != slice.size_bytes) return;
+                        if (!receive_tensor(*link, stage, *e, slice.size_bytes)) return;
+                        moved[g] += slice.size_bytes;
+                    }
+                    good[g] = 1;
+                });
+            for (auto &t : streams) t.join();
+            for (size_t g = 0; g < runs.size(); ++g)
+                if (!good[g] || revisions[g] != revisions[0]) {
+                    PLOG(ERR) << "shared-state transfer over " << runs.size() << " connections failed on connection " << g;
+                    return false;
+                }
+            state.revision = revisions[0];
+            std::vector<std::pair<const SharedEntry *, uint64_t>> arrived;
+            for (size_t i = 0; i < verdict->outdated_keys.size(); ++i) {
+                const SharedEntry *e = entry_of(verdict->outdated_keys[i]);
+                rx_bytes += e->bytes();
+                forget_hashes(e->data, e->bytes());
+                if (!e->allow_content_inequality && i < verdict->expected_hashes.size()) arrived.push_back({e, verdict->expected_hashes[i]});
+            }
+            if (!verify_received(arrived, hash_type)) return false;
+            if (!master_.send_packet(C2MDistSharedStateComplete{})) return false;
+            if (!master_.recv_packet<M2CSyncSharedStateComplete>()) return false;
+            tx_bytes = ss_tx_bytes_;
+            return true;
+        }
         bool p2p = false;
         Uuid distributor;
         uint64_t chunk = 0;
@@ -938,22 +1062,8 @@ bool Client::sync_shared_state(SharedStateArgs &state, uint64_t &tx_bytes, uint6
                     if (slice.size_bytes == 0) break;
                 }
 
-            } else if (!it->on_device) {
-                if (!sock.recv_raw(it->data, slice.size_bytes)) return false;
-            } else {
-                // socket -> page-locked buffer -> GPU, the copy of chunk k overlapping the receive of chunk k+1
-                if (!stage.ok()) return false;
-                auto *dst = static_cast<uint8_t *>(it->data);
-                std::future<bool> pending;
-                size_t k = 0;
-                for (size_t off = 0; off < slice.size_bytes; off += kStageBytes, ++k) {
-                    const size_t n = std::min<size_t>(kStageBytes, slice.size_bytes - off);
-                    const bool got = sock.recv_raw(stage.buf(k & 1), n);
-                    if (pending.valid() && !pending.get()) return false; // the buffer received into next is free again
-                    if (!got) return false;
-                    pending = std::async(std::launch::async, [&, k, off, n] { return plane_->copy_to_device(dst + off, stage.buf(k & 1), n); });
-                }
-                if (pending.valid() && !pending.get()) return false;
+            } else if (!receive_tensor(sock, stage, *it, slice.size_bytes)) {
+                return false;
             }
             rx_bytes += slice.size_bytes;
             forget_hashes(it->data, it->bytes());
@@ -967,7 +1077,25 @@ bool Client::sync_shared_state(SharedStateArgs &state, uint64_t &tx_bytes, uint6
         }
         for (; acks_owed; --acks_owed)
             if (!sock.send_packet(C2SChunkAck{})) return false;
-        // verify what arrived against what the master elected: device tensors in one batch
+        if (!verify_received(to_verify, hash_type)) return false;
+    }
+
+    if (!master_.send_packet(C2MDistSharedStateComplete{})) return false;
+    if (!master_.recv_packet<M2CSyncSharedStateComplete>()) return false;
+    tx_bytes = ss_tx_bytes_;
+    return true;
+}
+
+// What arrived is checked against what the master elected: device tensors in one batch of hash kernels.
+bool Client::verify_received(const std::vector<std::pair<const SharedEntry *, uint64_t>> &to_verify, wire::HashType hash_type) {
+    auto hash_of = [&](const SharedEntry &e, uint64_t &out) { // nothing to recall here: whatever was known about these tensors is stale
+        if (e.on_device) return plane_->hash_device(e.data, e.bytes(), hash_type, out);
+        out = hash_type == HashType::Simple  ? cpu::simplehash(e.data, e.bytes())
+              : hash_type == HashType::Crc32 ? cpu::crc32c(e.data, e.bytes())
+                                             : cpu::mset64(e.data, e.bytes());
+        return true;
+    };
+    {
         std::vector<device::Plane::HashJob> vjobs;
         std::vector<size_t> vidx;
         for (size_t k = 0; k < to_verify.size(); ++k)
@@ -982,6 +1110,17 @@ bool Client::sync_shared_state(SharedStateArgs &state, uint64_t &tx_bytes, uint6
                 got[vidx[j]] = vjobs[j].result;
                 hashed[vidx[j]] = true;
             }
+        {
+            std::vector<const void *> ptrs;
+            std::vector<size_t> sizes, idx;
+            for (size_t k = 0; k < to_verify.size(); ++k)
+                if (!hashed[k] && !to_verify[k].first->on_device) ptrs.push_back(to_verify[k].first->data), sizes.push_back(to_verify[k].first->bytes()), idx.push_back(k);
+            if (ptrs.size() > 1) {
+                std::vector<uint64_t> out(ptrs.size(), 0);
+                cpu::hash_many(ptrs.data(), sizes.data(), ptrs.size(), static_cast<int>(hash_type), out.data());
+                for (size_t j = 0; j < idx.size(); ++j) got[idx[j]] = out[j], hashed[idx[j]] = true;
+            }
+        }
         for (size_t k = 0; k < to_verify.size(); ++k) {
             const SharedEntry &e = *to_verify[k].first;
             if (!hashed[k] && !hash_of(e, got[k])) return false;
@@ -992,10 +1131,6 @@ bool Client::sync_shared_state(SharedStateArgs &state, uint64_t &tx_bytes, uint6
             if (hash_type == HashType::Mset64) remember_hash(e.data, e.bytes(), got[k]);
         }
     }
-
-    if (!master_.send_packet(C2MDistSharedStateComplete{})) return false;
-    if (!master_.recv_packet<M2CSyncSharedStateComplete>()) return false;
-    tx_bytes = ss_tx_bytes_;
     return true;
 }
 

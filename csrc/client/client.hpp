@@ -119,6 +119,7 @@ public:
     Launch all_reduce_on_stream(const ReduceRequest &req, ReduceOutcome &out);
     // Takes the verdict of the enqueued operation on `tag` (all tags when `all`).  False when one of them failed.
     bool wait_stream_ops(uint64_t tag, bool all, ReduceOutcome &last);
+    bool verify_received(const std::vector<std::pair<const SharedEntry *, uint64_t>> &to_verify, wire::HashType hash_type);
     bool any_reduce_running();
     bool last_stats(uint64_t tag, pcclExtReduceStats_t &out);
 

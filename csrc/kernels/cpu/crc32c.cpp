@@ -155,7 +155,8 @@ uint32_t crc32c_one_thread(const void *data, size_t n_bytes) {
 // algebra the device kernel uses to combine its lanes), so the pieces are hashed independently.
 uint32_t crc32c(const void *data, size_t n_bytes) {
     const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
-    const size_t n_threads = std::min<size_t>(std::min(8u, std::max(1u, hw / 2)), n_bytes / (4u << 20));
+    size_t n_threads = std::min<size_t>(std::min(8u, std::max(1u, hw / 2)), n_bytes / (4u << 20));
+    if (hash_thread_cap()) n_threads = std::min<size_t>(n_threads, hash_thread_cap());
     if (n_threads <= 1) return crc32c_one_thread(data, n_bytes);
     const auto *bytes = static_cast<const uint8_t *>(data);
     const size_t per = ((n_bytes + n_threads - 1) / n_threads + 63) / 64 * 64;

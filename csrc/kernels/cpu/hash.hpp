@@ -23,6 +23,15 @@ inline uint32_t hash_combine(uint32_t a, uint32_t b) {
     return a;
 }
 
+// Upper bound on the threads one hash call of THIS thread may use (0 = no bound).  A caller that hashes many tensors at once,
+// one per thread, sets 1 so that the calls do not each start a crew of their own.
+void hash_thread_cap(unsigned max_threads);
+unsigned hash_thread_cap();
+
+// Hashes `n` host buffers with the given hash type (0 simplehash, 1 CRC32C, 2 mset64), several buffers at a time when there
+// are several: results in out[i].
+void hash_many(const void *const *data, const size_t *n_bytes, size_t n, int hash_type, uint64_t *out);
+
 uint64_t simplehash(const void *data, size_t n_bytes);
 
 // Folds 256 per-thread values the way the device block reduction does (8 warp trees, then one

@@ -24,7 +24,8 @@ uint64_t mset64_raw(const void *data, size_t n_bytes, uint64_t first_packet) {
     };
     uint64_t raw = 0;
     const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
-    const size_t n_threads = std::min<size_t>(hw > 16 ? 16 : hw, full / (1u << 16)); // below 1 MiB per thread it is not worth it
+    size_t n_threads = std::min<size_t>(hw > 16 ? 16 : hw, full / (1u << 16)); // below 1 MiB per thread it is not worth it
+    if (hash_thread_cap()) n_threads = std::min<size_t>(n_threads, hash_thread_cap());
     if (n_threads <= 1) {
         raw = span(0, full);
     } else {

@@ -1,4 +1,5 @@
 #include <algorithm>
+#include <atomic>
 #include <cstring>
 #include <thread>
 #include <vector>
@@ -8,17 +9,43 @@
 namespace pccl::cpu {
 
 namespace {
+thread_local unsigned t_thread_cap = 0;
+} // namespace
 
-// One shuffle tree over 32 lanes: lane i takes lane i+offset, lanes without a partner combine
-// with themselves (that is what __shfl_down_sync hands back); only lane 0 is read afterwards.
+void hash_thread_cap(unsigned max_threads) { t_thread_cap = max_threads; }
+unsigned hash_thread_cap() { return t_thread_cap; }
+
+void hash_many(const void *const *data, const size_t *n_bytes, size_t n, int hash_type, uint64_t *out) {
+    auto one = [&](size_t i) {
+        out[i] = hash_type == 0 ? simplehash(data[i], n_bytes[i]) : hash_type == 1 ? crc32c(data[i], n_bytes[i]) : mset64(data[i], n_bytes[i]);
+    };
+    size_t total = 0;
+    for (size_t i = 0; i < n; ++i) total += n_bytes[i];
+    const unsigned crew = std::min<unsigned>({8u, std::max(1u, std::thread::hardware_concurrency() / 2), static_cast<unsigned>(n)});
+    if (n < 2 || crew < 2 || total < (8u << 20)) { // one buffer, or little data: the calls thread themselves where it pays
+        for (size_t i = 0; i < n; ++i) one(i);
+        return;
+    }
+    std::atomic<size_t> next{0};
+    std::vector<std::thread> pool;
+    for (unsigned t = 0; t < crew; ++t)
+        pool.emplace_back([&] {
+            hash_thread_cap(1);
+            for (size_t i = next++; i < n; i = next++) one(i);
+        });
+    for (auto &th : pool) th.join();
+}
+
+namespace {
+
+// One shuffle tree over 32 lanes: at every level lane i takes lane i+offset (lanes without a partner combine with
+// themselves -- that is what __shfl_down_sync hands back), and only lane 0 is read afterwards.  Lane 0 at the end depends on
+// lanes 0..offset-1 of each level only, and those always have a partner, so the tree is computed on a shrinking prefix.
 uint32_t warp_fold(const uint32_t *lanes) {
     uint32_t v[32];
     std::memcpy(v, lanes, sizeof v);
-    for (int offset = 16; offset > 0; offset >>= 1) {
-        uint32_t next[32];
-        for (int i = 0; i < 32; ++i) next[i] = hash_combine(v[i], i + offset < 32 ? v[i + offset] : v[i]);
-        std::memcpy(v, next, sizeof v);
-    }
+    for (int offset = 16; offset > 0; offset >>= 1)
+        for (int i = 0; i < offset; ++i) v[i] = hash_combine(v[i], v[i + offset]);
     return v[0];
 }
 
@@ -94,6 +121,7 @@ uint64_t simplehash(const void *data, size_t n_bytes) {
         };
         unsigned n_threads = 1;
         if (n_bytes >= (8u << 20)) n_threads = std::max(1u, std::min(16u, std::thread::hardware_concurrency() / 2));
+        if (hash_thread_cap()) n_threads = std::min(n_threads, hash_thread_cap());
         if (n_threads <= 1 || grid < n_threads) {
             run_blocks(0, grid);
         } else {

@@ -501,6 +501,36 @@ TEST(all_receive_only_with_different_content) {
     CHECK(st[0].buffers[0] == std::vector<uint8_t>(64, 1) && st[1].buffers[0] == std::vector<uint8_t>(64, 2)); // untouched
 }
 
+// A large state over sockets: every receiver fetches contiguous runs of the tensors over several connections at once, with the
+// reference's plain request on each.  Sizes are uneven on purpose, one tensor is empty, one is larger than a run.
+TEST(large_state_over_several_connections) {
+    TestMaster tm;
+    auto peers = connect_peers(tm, 3);
+    std::vector<PeerState> st(3);
+    const size_t sizes[] = {3u << 20, 1, 7u << 20, 0, 5u << 20, 30u << 20, 123457, 2u << 20, 9u << 20, 4u << 20, 64, 6u << 20};
+    uint64_t total = 0;
+    for (int p = 0; p < 3; ++p) {
+        int k = 0;
+        for (size_t n : sizes) st[p].add("tensor" + std::to_string(k++), n, static_cast<uint8_t>(p == 0 ? 0 : 200 + p));
+    }
+    for (size_t n : sizes) total += n;
+    for (size_t k = 0; k < st[0].buffers.size(); ++k) // the sender's content: different in every tensor and along it
+        for (size_t i = 0; i < st[0].buffers[k].size(); ++i) st[0].buffers[k][i] = static_cast<uint8_t>(i * 31 + k * 7 + (i >> 13));
+    st[0].args.strategy = SyncStrategy::TxOnly;
+    st[1].args.strategy = st[2].args.strategy = SyncStrategy::RxOnly;
+    sync_all(peers, st);
+    for (auto &s : st) CHECK(s.ok);
+    CHECK_EQ(st[0].tx, 2 * total);
+    CHECK_EQ(st[1].rx, total);
+    CHECK_EQ(st[2].rx, total);
+    for (int p = 1; p < 3; ++p)
+        for (size_t k = 0; k < st[0].buffers.size(); ++k) CHECK(st[p].buffers[k] == st[0].buffers[k]);
+    // the next synchronisation finds nothing to do
+    for (auto &s : st) s.args.revision += 1, s.args.strategy = SyncStrategy::EnforcePopular;
+    sync_all(peers, st);
+    for (auto &s : st) CHECK(s.ok && s.tx == 0 && s.rx == 0);
+}
+
 // tensors with allow_content_inequality are never hashed or transferred
 TEST(content_inequality_allowed) {
     TestMaster tm;

@@ -74,6 +74,17 @@ assert (info.rx_bytes == 0) == (rank == 0), (rank, info.tx_bytes, info.rx_bytes)
 state.revision = 2
 info = comm.sync_shared_state(state, pccl.SharedStateSyncStrategy.ENFORCE_POPULAR)
 assert info.rx_bytes == 0 and info.tx_bytes == 0, (info.tx_bytes, info.rx_bytes)
+# 4b. (optional) a state large enough for this implementation to fetch it over several connections at once -- from a
+#     distributor of either implementation, which sees nothing but independent plain requests
+if len(sys.argv) > 6 and sys.argv[6] == "bigstate":
+    tensors = [torch.full((1_500_000 + 1000 * k,), float(k) if rank == 0 else -7.0) for k in range(12)]  # 72 MB
+    big = pccl.SharedState([pccl.TensorInfo.from_torch(t, f"layer{k}") for k, t in enumerate(tensors)])
+    big.revision = 3
+    info = comm.sync_shared_state(big, pccl.SharedStateSyncStrategy.SEND_ONLY if rank == 0 else pccl.SharedStateSyncStrategy.RECEIVE_ONLY)
+    for k, t in enumerate(tensors):
+        assert float(t[0]) == float(k) and float(t[-1]) == float(k) and float(t[len(t) // 2]) == float(k), (k, t[:3])
+    total = sum(t.numel() * 4 for t in tensors)
+    assert info.rx_bytes == (0 if rank == 0 else total), (rank, info.rx_bytes, total)
 # 5. (optional) topology optimisation: every peer measures its bandwidth to the others with the benchmark protocol
 if len(sys.argv) > 6 and sys.argv[6] == "topology":
     comm.optimize_topology()

@@ -107,3 +107,10 @@ print(json.dumps(problems))
     import json
     problems = json.loads(proc.stdout.strip().splitlines()[-1])
     assert problems == [], problems
+
+
+@pytest.mark.parametrize("peer_impls", [["ref", "ours", "ours"], ["ours", "ref", "ours"]], ids=["ref-distributes", "ours-distributes"])
+def test_large_shared_state_between_the_implementations(peer_impls):
+    """72 MB in twelve tensors: our receivers fetch contiguous runs over several connections, each with the reference's plain
+    request, so a reference distributor serves them without knowing; a reference receiver fetches from ours over one."""
+    run_mix("ours", peer_impls, extra=("bigstate",))
