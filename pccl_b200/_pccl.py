@@ -247,6 +247,11 @@ class ReduceOpDescriptor:
 
     from_numpy = from_torch
 
+    def to_c(self) -> _lib.ReduceOpDescriptorC:
+        c_desc = _lib.ReduceOpDescriptorC()
+        self.to_c_inpl(c_desc)
+        return c_desc
+
     def to_c_inpl(self, c_desc: _lib.ReduceOpDescriptorC) -> None:
         c_desc.sendbuf = self.sendbuf_ptr
         c_desc.recvbuf = self.recvbuf_ptr
