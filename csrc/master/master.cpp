@@ -622,9 +622,16 @@ Master::Verdict Master::eval_sync_votes(uint32_t group) {
         size_t votes;
         int priority;
     };
+    // Peers that mix another strategy into a group with an ENFORCE_POPULAR member are kicked further down; their content
+    // does not stand for election either.  (The reference lets it: with one enforcer and one SEND_ONLY peer holding
+    // different content the outcome -- enforcer served, or enforcer left without a distributor -- depends on whose vote
+    // arrives first, ccoip_master_handler.cpp:616-735.)
+    bool enforcer_present = false;
+    for (const auto &v : g.sync_votes) enforcer_present = enforcer_present || v.strategy == SyncStrategy::EnforcePopular;
     std::vector<Tally> tallies;
     for (const auto &v : g.sync_votes) {
         if (v.strategy == SyncStrategy::RxOnly) continue;
+        if (enforcer_present && v.strategy != SyncStrategy::EnforcePopular) continue;
         const int prio = v.rev_status == RevisionStatus::Match ? 1 : -2;
         auto it = std::find_if(tallies.begin(), tallies.end(), [&](const Tally &t) { return same_candidate(*t.entries, v.entries); });
         if (it == tallies.end())
@@ -634,9 +641,17 @@ Master::Verdict Master::eval_sync_votes(uint32_t group) {
             it->priority = std::max(it->priority, prio);
         }
     }
+    // a tie in class and votes is broken by content (smaller hash sequence first), never by the order the votes came in
+    auto content_less = [](const std::vector<SharedStateEntry> &a, const std::vector<SharedStateEntry> &b) {
+        if (a.size() != b.size()) return a.size() < b.size();
+        for (size_t i = 0; i < a.size(); ++i)
+            if (a[i].hash != b[i].hash) return a[i].hash < b[i].hash;
+        return false;
+    };
     const Tally *winner = nullptr;
     for (const auto &t : tallies) {
-        if (!winner || t.priority > winner->priority || (t.priority == winner->priority && t.votes > winner->votes))
+        if (!winner || t.priority > winner->priority || (t.priority == winner->priority && t.votes > winner->votes) ||
+            (t.priority == winner->priority && t.votes == winner->votes && content_less(*t.entries, *winner->entries)))
             winner = &t;
     }
     if (!winner) return Verdict::Failed; // nobody offered content

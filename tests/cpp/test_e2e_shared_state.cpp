@@ -293,6 +293,47 @@ TEST(enforce_popular_three_peers_mixed_others) {
     CHECK_EQ(tx + rx, 0u);
 }
 
+// The outcome of an election does not depend on the order in which the votes reach the master: the same three peers
+// (an enforcer, a SEND_ONLY peer and a RECEIVE_ONLY peer, all with different content) vote in every order, and two
+// enforcers with different content always settle on the same one of the two.
+TEST(elections_do_not_depend_on_vote_order) {
+    const int orders[6][3] = {{0, 1, 2}, {0, 2, 1}, {1, 0, 2}, {1, 2, 0}, {2, 0, 1}, {2, 1, 0}};
+    for (const auto &order : orders) {
+        TestMaster tm;
+        auto peers = connect_peers(tm, 3);
+        std::vector<PeerState> st(3);
+        for (int i = 0; i < 3; ++i) st[i].add("w", 32, static_cast<uint8_t>(10 + i));
+        st[0].args.strategy = SyncStrategy::EnforcePopular;
+        st[1].args.strategy = SyncStrategy::TxOnly;
+        st[2].args.strategy = SyncStrategy::RxOnly;
+        std::vector<std::thread> ts;
+        for (int k = 0; k < 3; ++k) {
+            const int p = order[k];
+            ts.emplace_back([&, p] { st[p].ok = peers[p]->sync_shared_state(st[p].args, st[p].tx, st[p].rx); });
+            std::this_thread::sleep_for(std::chrono::milliseconds(60));
+        }
+        for (auto &t : ts) t.join();
+        CHECK(st[0].ok);
+        CHECK(!st[1].ok && !st[2].ok);
+        CHECK(st[0].buffers[0] == std::vector<uint8_t>(32, 10)); // the enforcer kept its own content
+    }
+    std::vector<uint8_t> settled;
+    for (int first = 0; first < 2; ++first) {
+        TestMaster tm;
+        auto peers = connect_peers(tm, 2);
+        std::vector<PeerState> st(2);
+        st[0].add("w", 48, 77);
+        st[1].add("w", 48, 99);
+        std::thread early([&] { st[first].ok = peers[first]->sync_shared_state(st[first].args, st[first].tx, st[first].rx); });
+        std::this_thread::sleep_for(std::chrono::milliseconds(80));
+        st[1 - first].ok = peers[1 - first]->sync_shared_state(st[1 - first].args, st[1 - first].tx, st[1 - first].rx);
+        early.join();
+        CHECK(st[0].ok && st[1].ok && st[0].buffers[0] == st[1].buffers[0]);
+        if (first == 0) settled = st[0].buffers[0];
+        else CHECK(settled == st[0].buffers[0]); // one vote each: the tie is broken by content, not by arrival
+    }
+}
+
 // SEND_ONLY towards two receivers: one distributor serves both, each receiver gets the full state exactly once
 TEST(one_sender_two_receivers) {
     TestMaster tm;
