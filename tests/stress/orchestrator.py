@@ -20,13 +20,13 @@ sys.path.insert(0, str(HERE.parent.parent))
 import pccl_b200 as pccl  # noqa: E402
 
 
-def run(seconds: float, max_peers: int, stall: float, device: str, seed: int = 0, mode: str = "basic") -> dict:
+def run(seconds: float, max_peers: int, stall: float, device: str, seed: int = 0, mode: str = "basic", min_kills: int = 0) -> dict:
     with pccl.MasterNode("127.0.0.1:0") as master:  # leaving the block interrupts the master
         master.run()
-        return _run(master, seconds, max_peers, stall, device, seed, mode)
+        return _run(master, seconds, max_peers, stall, device, seed, mode, min_kills)
 
 
-def _run(master, seconds: float, max_peers: int, stall: float, device: str, seed: int, mode: str = "basic") -> dict:
+def _run(master, seconds: float, max_peers: int, stall: float, device: str, seed: int, mode: str = "basic", min_kills: int = 0) -> dict:
     rng = random.Random(seed)
     port = master.port
     peers = []
@@ -34,12 +34,19 @@ def _run(master, seconds: float, max_peers: int, stall: float, device: str, seed
     counts = {"reductions": 0, "spawned": 0, "killed": 0}
     lock = threading.Lock()
 
+    joined = set()  # pids of peers that are in the run (a process spends seconds importing torch before that)
+
     def watch(p):
         for line in p.stdout:
             if line.startswith("REDUCE"):
                 with lock:
                     counts["reductions"] += 1
                     last_progress[0] = time.time()
+            elif line.startswith("JOINED"):
+                with lock:
+                    joined.add(p.pid)
+                    if len(joined) == 2:
+                        last_progress[0] = time.time()  # only now can anything be reduced: the stall clock starts here
             elif line.startswith("FATAL"):
                 counts.setdefault("fatal", []).append(line.strip())
 
@@ -69,20 +76,35 @@ def _run(master, seconds: float, max_peers: int, stall: float, device: str, seed
 
     spawn()
     spawn()
+    # the run proper starts when two peers are in (at most 90 s later: then the stall check below reports it)
+    t_wait = time.time() + 90
+    while time.time() < t_wait:
+        with lock:
+            if len(joined) >= 2:
+                break
+        time.sleep(0.05)
     t_end = time.time() + seconds
     stalled = False
-    while time.time() < t_end:
+    # (a short run on a slow machine is extended, by a minute at most, until it has seen the kills it was asked to see)
+    while time.time() < t_end or (counts["killed"] < min_kills and time.time() < t_end + 60):
         time.sleep(rng.uniform(0.3, 1.2))
         peers[:] = [p for p in peers if p.poll() is None]
         if rng.random() < 0.6:
             if len(peers) < max_peers:
                 spawn()
-        elif len(peers) > 2:
-            victim = rng.choice(peers)
-            os.kill(victim.pid, signal.SIGKILL)
-            peers.remove(victim)
-            counts["killed"] += 1
-        if time.time() - last_progress[0] > stall:
+        else:
+            # victims are peers that made it into the run, and two of those are left alone: on a loaded machine a process
+            # needs longer to start than the pause between two kills, and killing what has not joined yet proves nothing
+            with lock:
+                in_run = [p for p in peers if p.pid in joined]
+            if len(in_run) > 2:
+                victim = rng.choice(in_run)
+                os.kill(victim.pid, signal.SIGKILL)
+                peers.remove(victim)
+                counts["killed"] += 1
+        with lock:
+            started = len(joined) >= 2
+        if (started and time.time() - last_progress[0] > stall) or (not started and time.time() > t_wait):
             stalled = True
             break
     for p in peers:
