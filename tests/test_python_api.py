@@ -219,8 +219,11 @@ def test_two_level_ring_between_pretended_hosts():
     assert {c["plane"] for r in stepped for c in r["cases"]} == {"tcp_hierarchical"}
     assert len({c["hash"] for r in stepped for c in r["cases"] if c["id"] == "outer_step_1"}) == 1
     # the same peers without host ids on loopback: one flat ring
-    flat = run_peers(4, "allreduce", devices=["cpu"] * 4, env={"PCCL_HIERARCHY": "0"}, rank_env=hosts)
-    assert {c["plane"] for r in flat for c in r["cases"]} == {"tcp_ring"}
+    flat = run_peers(4, "concurrent", devices=["cpu"] * 4, env={"PCCL_HIERARCHY": "0"}, rank_env=hosts)
+    assert all(r["ok"] for r in flat) and {c["plane"] for r in flat for c in r["cases"]} == {"tcp_ring"}
+    # ... and two operations in flight at once share the two extra links of the hierarchy
+    both = run_peers(4, "concurrent", devices=["cpu"] * 4, rank_env=hosts)
+    assert all(r["ok"] for r in both) and {c["plane"] for r in both for c in r["cases"]} == {"tcp_hierarchical"}
 
 
 @pytest.mark.parametrize("hash_type", ["mset", "crc32"])
