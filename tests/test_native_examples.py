@@ -2,6 +2,7 @@
 (counterparts of the reference's docs/md hello-world and concurrent all-reduce tutorials)."""
 import os
 import re
+import shutil
 import subprocess
 import time
 from pathlib import Path
@@ -72,6 +73,7 @@ def test_cpp_concurrent_allreduce_program(tmp_path):
         stop(master)
 
 
+@pytest.mark.skipif(shutil.which("nvcc") is None, reason="no CUDA toolkit on this machine")
 def test_cuda_example_compiles_for_sm_100a(tmp_path):
     """Cross-compiles on the CPU box; it runs in tests/test_gpu_multi.py where there are two GPUs."""
     build_cuda_example(tmp_path)
