@@ -718,20 +718,41 @@ Master::Verdict Master::eval_sync_votes(uint32_t group) {
     g.next_revision++;
     g.revision_initialised = true;
 
-    // ---- tell everybody
-    const Client *distributor = nullptr;
+    // ---- tell everybody.  Whoever needs content is pointed at a peer that has it: one on the same machine when there is
+    // one (NVLink or loopback instead of the network), and among equally good ones the one with the fewest takers so far, so
+    // that several newcomers do not all queue at the same peer.  (The reference always names the first distributor;
+    // ccoip_master_handler.cpp:567-593 carries a "should be topology aware" note.)
+    struct Source {
+        const Client *peer;
+        size_t takers = 0;
+    };
+    std::vector<Source> sources;
     for (Client *c : ordered_clients())
-        if (c->group == group && c->phase == Phase::Accepted && c->state == State::DistributeSharedState &&
-            !kicked.count(c->uuid)) {
-            distributor = c;
-            break;
+        if (c->group == group && c->phase == Phase::Accepted && c->state == State::DistributeSharedState && !kicked.count(c->uuid))
+            sources.push_back({c, 0});
+    auto same_machine = [](const Client &a, const Client &b) {
+        const auto &x = a.ss_addr.inet, &y = b.ss_addr.inet;
+        if (x.protocol != y.protocol) return false;
+        return x.protocol == inetIPv4 ? std::memcmp(x.ipv4.data, y.ipv4.data, 4) == 0 : std::memcmp(x.ipv6.data, y.ipv6.data, 16) == 0;
+    };
+    auto pick_source = [&](const Client &taker) -> const Client * {
+        Source *best = nullptr;
+        bool best_local = false;
+        for (auto &src : sources) {
+            const bool local = same_machine(*src.peer, taker);
+            if (!best || (local && !best_local) || (local == best_local && src.takers < best->takers)) best = &src, best_local = local;
         }
+        if (!best) return nullptr;
+        best->takers++;
+        return best->peer;
+    };
     for (Client *c : ordered_clients()) {
         if (c->group != group || c->phase != Phase::Accepted) continue;
         if (c->state != State::DistributeSharedState && c->state != State::RequestSharedState) continue;
         M2CSyncSharedState out;
         out.is_outdated = c->state == State::RequestSharedState;
         if (out.is_outdated) {
+            const Client *distributor = kicked.count(c->uuid) ? nullptr : pick_source(*c);
             if (distributor) {
                 out.distributor = distributor->ss_addr;
                 for (size_t i : outcomes[c->uuid].dirty) {
@@ -739,7 +760,7 @@ Master::Verdict Master::eval_sync_votes(uint32_t group) {
                     out.expected_hashes.push_back(mask[i].hash);
                     out.expected_hash_types.push_back(mask[i].hash_type);
                 }
-            } else {
+            } else if (!kicked.count(c->uuid)) {
                 PLOG(WARN) << "no peer can distribute shared state to " << c->uuid.str();
             }
         }

@@ -334,6 +334,22 @@ TEST(elections_do_not_depend_on_vote_order) {
     }
 }
 
+// Several newcomers at once and several peers that hold the content: the master spreads the takers over the sources instead of
+// sending everybody to the first one (the reference does the latter and says so in a comment, ccoip_master_handler.cpp:575).
+TEST(takers_are_spread_over_the_sources) {
+    TestMaster tm;
+    auto peers = connect_peers(tm, 6);
+    std::vector<PeerState> st(6);
+    for (int p = 0; p < 6; ++p) st[p].add("w", 40'000, static_cast<uint8_t>(p < 3 ? 5 : 100 + p)); // three agree, three differ
+    sync_all(peers, st);
+    for (auto &s : st) CHECK(s.ok);
+    for (int p = 3; p < 6; ++p) {
+        CHECK_EQ(st[p].rx, 40'000u);
+        CHECK(st[p].buffers[0] == st[0].buffers[0]);
+    }
+    for (int p = 0; p < 3; ++p) CHECK_EQ(st[p].tx, 40'000u); // one taker each
+}
+
 // SEND_ONLY towards two receivers: one distributor serves both, each receiver gets the full state exactly once
 TEST(one_sender_two_receivers) {
     TestMaster tm;
