@@ -73,6 +73,8 @@ def main():
     ap.add_argument("--eval-interval", dest="eval_interval", type=int, default=None)
     ap.add_argument("--checkpoint-dir", dest="checkpoint_dir", default=None)
     ap.add_argument("--quant", default=None, choices=["none", "u8", "fp8"])
+    ap.add_argument("--count-from-world", dest="count_from_world", type=int, default=0,
+                    help="keep training, but start counting the outer steps only once the run has had this many peers")
     ap.add_argument("--timeline", default="", help="write the section timeline here (.png/.svg) and a Chrome trace next to it")
     args = ap.parse_args()
     cfg = load_config(args)
@@ -143,7 +145,9 @@ def main():
         state.push_revision()
         return info
 
-    for it in range(cfg["outer_steps"]):
+    it, counted, crowd_seen = -1, 0, args.count_from_world <= 0
+    while counted < cfg["outer_steps"]:
+        it += 1
         with prof.section("membership"):
             if args.mode == "async":
                 # shared state is only synchronised when the topology changed (reference: async_diloco.py:419-431,448-451)
@@ -175,6 +179,8 @@ def main():
                 algo.outer_step(inner_flat)
             step_t += 1
         world = comm.get_attribute(pccl.Attribute.PEER_GROUP_WORLD_SIZE)
+        crowd_seen = crowd_seen or world >= args.count_from_world
+        counted += 1 if crowd_seen else 0
         plane = comm.ext_last_reduce_stats(0)["plane"] if world > 1 and args.mode == "sync" else "-"
         print(f"outer step {it}: loss {loss.item():.4f} world {world} plane {plane} run step {int(step_t)}", flush=True)
     if args.mode == "async":

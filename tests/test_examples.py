@@ -110,44 +110,57 @@ def test_diloco_example_checkpoint_and_resume(master, tmp_path):
         assert "run step 6" in o and "world 2" in o, o[-2000:]
 
 
-def test_sync_diloco_late_joiner(master):
-    """A peer that joins a synchronous run mid-way takes part from the next outer step with the run's parameters."""
+def _run_with_a_late_joiner(base, tmp_path, timeout):
+    """Two peers train; a third is started once the run is demonstrably under way (the first peer has printed its third
+    outer step) and does 12 outer steps.  The old peers start counting their 15 steps when they first see three peers
+    (--count-from-world), so nothing here depends on how fast this machine trains or starts a Python process.  The old peers
+    write to files: nobody reads their pipes while the test waits for the newcomer."""
     import time
+    logs = [tmp_path / f"old{i}.log" for i in range(2)]
+    old = [subprocess.Popen(base + ["--outer-steps", "15", "--min-peers", "2", "--count-from-world", "3"], stdout=open(log, "w"),
+                            stderr=subprocess.STDOUT, env=_env()) for log in logs]
+    deadline = time.time() + 120
+    while "outer step 2:" not in logs[0].read_text():
+        assert old[0].poll() is None and time.time() < deadline, logs[0].read_text()[-3000:]
+        time.sleep(0.1)
+    new = subprocess.Popen(base + ["--outer-steps", "12", "--min-peers", "3"], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, env=_env())
+    try:
+        out_new, _ = new.communicate(timeout=timeout)
+        for p in old:
+            p.wait(timeout=timeout)
+    finally:
+        for p in old + [new]:
+            if p.poll() is None:
+                p.kill()
+    return new.returncode, out_new, [(p.returncode, log.read_text()) for p, log in zip(old, logs)]
+
+
+def test_sync_diloco_late_joiner(master, tmp_path):
+    """A peer that joins a synchronous run mid-way takes part from the next outer step with the run's parameters."""
     base = [sys.executable, str(REPO / "examples" / "diloco.py"), "--master", f"127.0.0.1:{master.port}", "--device", "cpu", "--mode", "sync",
             "--inner-steps", "2", "--batch", "2"]
-    old = [subprocess.Popen(base + ["--outer-steps", "40", "--min-peers", "2"], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, env=_env())
-           for _ in range(2)]
-    time.sleep(6)
-    new = subprocess.Popen(base + ["--outer-steps", "12", "--min-peers", "3"], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, env=_env())
-    out_new, _ = new.communicate(timeout=300)
-    assert new.returncode == 0, out_new[-4000:]
+    rc, out_new, olds = _run_with_a_late_joiner(base, tmp_path, 300)
+    assert rc == 0, out_new[-4000:]
     assert "world 3" in out_new, out_new[-3000:]
     first = re.search(r"outer step 0: .* run step (\d+)", out_new)
     assert first and int(first.group(1)) > 1, out_new[:2000]
-    for p in old:
-        out, _ = p.communicate(timeout=300)
-        assert p.returncode == 0, out[-4000:]
+    for rc_old, out in olds:
+        assert rc_old == 0, out[-4000:]
         assert "world 3" in out, out[-3000:]
 
 
-def test_async_diloco_late_joiner_is_inserted_into_the_pipeline(master):
+def test_async_diloco_late_joiner_is_inserted_into_the_pipeline(master, tmp_path):
     """Two peers train in the one-step-delayed mode; a third joins mid-run.  The members apply the reduction the joiner
     missed and re-send the shared state (SEND_ONLY), the joiner receives it (RECEIVE_ONLY) -- reference:
     python/examples/nanogpt_diloco/async_diloco.py:551-580 -- and all three go on together."""
-    import time
     base = [sys.executable, str(REPO / "examples" / "diloco.py"), "--master", f"127.0.0.1:{master.port}", "--device", "cpu", "--mode", "async",
             "--inner-steps", "2", "--batch", "2"]
-    old = [subprocess.Popen(base + ["--outer-steps", "40", "--min-peers", "2"], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, env=_env())
-           for _ in range(2)]
-    time.sleep(6)
-    new = subprocess.Popen(base + ["--outer-steps", "12", "--min-peers", "3"], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, env=_env())
-    out_new, _ = new.communicate(timeout=400)
-    assert new.returncode == 0, out_new[-4000:]
+    rc, out_new, olds = _run_with_a_late_joiner(base, tmp_path, 400)
+    assert rc == 0, out_new[-4000:]
     assert "world 3" in out_new, out_new[-3000:]
     # the joiner adopted the run's step counter: its first line is not "run step 1"
     first = re.search(r"outer step 0: .* run step (\d+)", out_new)
     assert first and int(first.group(1)) > 1, out_new[:2000]
-    for p in old:
-        out, _ = p.communicate(timeout=400)
-        assert p.returncode == 0, out[-4000:]
+    for rc_old, out in olds:
+        assert rc_old == 0, out[-4000:]
         assert "world 3" in out, out[-3000:]
