@@ -42,7 +42,7 @@ def test_c_peer_program_with_a_late_joiner(tmp_path):
     _, master, port = start_master(tmp_path)
     env = dict(os.environ, PCCL_EXAMPLE_MASTER_PORT=str(port))
     try:
-        args = [str(peer), "127.0.0.1", "40", "2", "40"]  # 40 steps of 40 ms
+        args = [str(peer), "127.0.0.1", "60", "2", "50"]  # 60 steps of at least 50 ms: three seconds for the newcomer to arrive
         procs = [subprocess.Popen(args, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, env=env) for _ in range(2)]
         time.sleep(0.6)
         procs.append(subprocess.Popen(args, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, env=env))
