@@ -22,6 +22,11 @@ using namespace pccl;
 struct pcclComm_t {
     pcclCommCreateParams_t params{};
     std::unique_ptr<client::Client> client;
+    // scratch of the fused form of pcclAllReduceMultipleWithRetry on host tensors: kept between calls (a training loop makes
+    // the same call every step; a fresh half-gigabyte vector would be zero-filled and page-faulted in every time)
+    std::mutex fuse_mu;
+    std::unique_ptr<uint8_t[]> fuse_buf;
+    size_t fuse_bytes = 0;
 };
 
 struct pcclMasterInstanceState_t {
@@ -383,12 +388,24 @@ static pcclResult_t try_fused_multiple(const pcclReduceOpDescriptor_t *descripto
         fused = static_cast<uint8_t *>(plane.fuse_buffer(total_bytes));
         if (!fused || !plane.gather(in_parts, fused, true)) return pcclInternalError;
     } else {
-        host_fused.resize(total_bytes);
-        fused = host_fused.data();
+        auto *comm = const_cast<pcclComm_t *>(c);
+        scratch_guard = std::unique_lock<std::mutex>(comm->fuse_mu, std::try_to_lock);
+        if (scratch_guard.owns_lock()) {
+            if (comm->fuse_bytes < total_bytes) {
+                comm->fuse_buf.reset(new uint8_t[total_bytes]); // not value-initialised: every byte that matters is copied in below
+                comm->fuse_bytes = total_bytes;
+            }
+            fused = comm->fuse_buf.get();
+        } else { // a second list in flight on the same communicator: its own buffer
+            host_fused.resize(total_bytes);
+            fused = host_fused.data();
+        }
         size_t off = 0;
         for (const auto &p : in_parts) {
             std::memcpy(fused + off, p.ptr, p.bytes);
-            off += (p.bytes + 15) / 16 * 16;
+            const size_t padded = (p.bytes + 15) / 16 * 16;
+            std::memset(fused + off + p.bytes, 0, padded - p.bytes);
+            off += padded;
         }
     }
     // padding between the parts is reduced too; its contents are irrelevant but must be defined
@@ -396,6 +413,7 @@ static pcclResult_t try_fused_multiple(const pcclReduceOpDescriptor_t *descripto
     desc.count = total_bytes / esz;
     client::ReduceRequest req;
     if (const pcclResult_t rc = build_request(fused, fused, &desc, req); rc != pcclSuccess) return rc;
+    req.input_is_scratch = !any_device; // a failed attempt is followed by a fresh gather below, no rollback copy needed
     client::ReduceOutcome out;
     for (;;) {
         if (c->client->local_world() < 2) {

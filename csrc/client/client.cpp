@@ -1786,7 +1786,7 @@ ReduceOutcome Client::run_reduce_impl(const ReduceRequest &req, uint64_t) {
                 a.dst = recv;
             }
             if (staged_ok) {
-                std::vector<uint8_t> *backup = stage || outer_two_pass ? nullptr : &host_backup;
+                std::vector<uint8_t> *backup = stage || outer_two_pass || req.input_is_scratch ? nullptr : &host_backup;
                 const RingResult r = use_hierarchy ? hierarchical_allreduce(ctx, cross_ctx, a, backup) : ring_allreduce(ctx, a, backup);
                 local_ok = r.ok;
                 out.tx_bytes = r.tx_bytes;

@@ -78,6 +78,8 @@ struct ReduceRequest {
     void *user_stream = nullptr;
     bool enqueue = false;
     bool want_hash = false; // also produce the mset64 content hash(es) of the result (device plane, one launch)
+    // the operand is a scratch copy the caller can make again: an in-place host reduction then keeps no backup to roll back to
+    bool input_is_scratch = false;
 };
 
 struct ReduceOutcome {
