@@ -1699,7 +1699,23 @@ ReduceOutcome Client::run_reduce_impl(const ReduceRequest &req, uint64_t) {
     };
 
     bool local_ok = false;
-    std::vector<uint8_t> host_backup; // in-place rollback for host buffers
+    // in-place rollback for host buffers: the tag's cached vector when the cache has room (a tag is in flight once, so nobody
+    // else touches it meanwhile), otherwise one that lives as long as this call
+    std::vector<uint8_t> uncached_backup;
+    std::vector<uint8_t> *cached = nullptr;
+    if (send == recv && !send_info.is_device && !req.input_is_scratch) {
+        constexpr uint64_t kCacheLimit = 4ull << 30;
+        const uint64_t bytes = req.count * esz;
+        std::lock_guard<std::mutex> lock(stage_mu_);
+        auto it = backup_cache_.find(req.tag);
+        if (it == backup_cache_.end() && backup_cache_bytes_ + bytes <= kCacheLimit) {
+            it = backup_cache_.emplace(req.tag, std::vector<uint8_t>()).first;
+            backup_cache_bytes_ += bytes;
+        }
+        if (it != backup_cache_.end() && (it->second.capacity() >= bytes || backup_cache_bytes_ + bytes <= kCacheLimit)) cached = &it->second;
+    }
+    std::vector<uint8_t> &host_backup = cached ? *cached : uncached_backup;
+    host_backup.clear(); // a left-over of the previous operation on this tag must not pass for this one's backup
     uint8_t *stage = nullptr;         // host staging for device buffers on the TCP plane
     const bool in_place = send == recv && !outer_fused;
 

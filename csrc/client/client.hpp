@@ -225,6 +225,10 @@ private:
     };
     std::mutex stage_mu_;
     std::map<uint64_t, StageBuf> stage_cache_;
+    // rollback copies of in-place host operands, one per tag, kept between calls: a training loop reduces the same buffers
+    // every step, and a fresh vector of that size costs more in page faults than the copy itself
+    std::map<uint64_t, std::vector<uint8_t>> backup_cache_;
+    uint64_t backup_cache_bytes_ = 0;
     std::mutex deferred_mu_;
     std::map<uint64_t, Deferred> deferred_;
     std::atomic<bool> ring_stale_{false};       // a peer vanished after an operation had finished here: rewire before the next one
