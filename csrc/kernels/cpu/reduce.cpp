@@ -3,6 +3,8 @@
 #include <algorithm>
 #include <bit>
 #include <cstring>
+#include <thread>
+#include <vector>
 
 #include "half.hpp"
 
@@ -171,8 +173,29 @@ void reduce_inplace(void *dst, const void *src, size_t count, DType dtype, RedOp
     }
 }
 
+namespace {
+void finalize_avg_serial(void *dst, size_t count, DType dtype, uint64_t world);
+} // namespace
+
+// The division is one more pass over the whole result; large results are cut into a few ranges that are divided at once.
 void finalize_avg(void *dst, size_t count, DType dtype, uint64_t world) {
     if (world <= 1) return;
+    const size_t esz = wire::dtype_size(dtype);
+    const unsigned hw = std::max(1u, std::thread::hardware_concurrency());
+    const size_t crew = std::min<size_t>({4, hw / 2, count * esz / (16u << 20)});
+    if (crew < 2) return finalize_avg_serial(dst, count, dtype, world);
+    const size_t per = ((count + crew - 1) / crew + 63) / 64 * 64;
+    std::vector<std::thread> helpers;
+    for (size_t t = 1; t < crew; ++t) {
+        const size_t lo = std::min(count, t * per), hi = std::min(count, lo + per);
+        if (lo < hi) helpers.emplace_back([=] { finalize_avg_serial(static_cast<uint8_t *>(dst) + lo * esz, hi - lo, dtype, world); });
+    }
+    finalize_avg_serial(dst, std::min(count, per), dtype, world);
+    for (auto &h : helpers) h.join();
+}
+
+namespace {
+void finalize_avg_serial(void *dst, size_t count, DType dtype, uint64_t world) {
     switch (dtype) {
     case DType::U8: avg_typed<uint8_t>(dst, count, world); break;
     case DType::I8: avg_typed<int8_t>(dst, count, world); break;
@@ -189,5 +212,6 @@ void finalize_avg(void *dst, size_t count, DType dtype, uint64_t world) {
     case DType::F8E4M3: break;
     }
 }
+} // namespace
 
 } // namespace pccl::cpu

@@ -602,6 +602,27 @@ TEST(half_precision_reductions_equal_their_definition) {
     }
 }
 
+// The averaging division on a buffer large enough to be cut into ranges for several threads: every element divided exactly
+// once, ragged length, the two types whose division is not a plain float divide included.
+TEST(average_of_a_large_buffer_is_divided_once_everywhere) {
+    const size_t n = (48u << 20) / 4 + 13;
+    std::vector<float> f(n);
+    std::vector<int32_t> k(n);
+    for (size_t i = 0; i < n; ++i) f[i] = static_cast<float>(i % 1000) * 3.0f, k[i] = static_cast<int32_t>(i % 1000) * 7 - 3000;
+    cpu::finalize_avg(f.data(), n, DType::F32, 3);
+    cpu::finalize_avg(k.data(), n, DType::I32, 7);
+    size_t bad = 0;
+    for (size_t i = 0; i < n; ++i) {
+        bad += f[i] != static_cast<float>(i % 1000) * 3.0f / 3.0f;
+        bad += k[i] != (static_cast<int32_t>(i % 1000) * 7 - 3000) / 7;
+    }
+    CHECK_EQ(bad, size_t(0));
+    std::vector<uint16_t> h((40u << 20) / 2 + 5, cpu::f32_to_bf16(6.0f));
+    cpu::finalize_avg(h.data(), h.size(), DType::BF16, 4);
+    for (size_t i = 0; i < h.size(); i += 4099) CHECK_EQ(h[i], cpu::f32_to_bf16(1.5f));
+    CHECK_EQ(h.back(), cpu::f32_to_bf16(1.5f));
+}
+
 TEST(zero_point_scale_quantiser) {
     std::vector<float> x(512);
     for (size_t i = 0; i < x.size(); ++i) x[i] = std::sin(0.05f * static_cast<float>(i)) * 4.0f + 1.0f;
