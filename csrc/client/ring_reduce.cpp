@@ -205,12 +205,12 @@ RingResult ring_allreduce(const RingContext &ctx, const ReduceArgs &a, std::vect
     }
     if (ctx.tx.empty() || ctx.rx.empty() || ctx.tx.size() != ctx.rx.size()) return res;
 
-    // In-place operation destroys the input while it runs; keep a copy to roll back to.
-    if (in_place) {
-        if (backup) backup->assign(dst, dst + a.count * esz);
-    } else {
-        std::memcpy(dst, a.src, a.count * esz);
-    }
+    // In-place operation destroys the input while it runs; keep a copy to roll back to.  Out of place nothing is copied up
+    // front: in the reduce-scatter every chunk but the own one is received exactly once, so the input is brought over piece
+    // by piece right before the incoming frame is folded into it (cache-warm, and while the network is busy anyway); the
+    // first chunk sent is read from the input, and the all-gather overwrites whatever was not reduced here.
+    const auto *src = static_cast<const uint8_t *>(a.src);
+    if (in_place && backup) backup->assign(dst, dst + a.count * esz);
     auto fail = [&]() {
         PLOG(DEBUG) << "ring all-reduce tag " << ctx.tag << " seq " << ctx.seq << " failed locally (aborted_by_master=" << res.aborted_by_master << ")";
         if (in_place && backup && !backup->empty()) std::memcpy(dst, backup->data(), backup->size());
@@ -238,9 +238,12 @@ RingResult ring_allreduce(const RingContext &ctx, const ReduceArgs &a, std::vect
         chunk_bounds(a.count, W, rx_chunk, rb, re);
         const uint64_t tx_n = te - tb, rx_n = re - rb;
 
+        // what this peer sends first is its own, still untouched chunk; later it forwards what it reduced into dst
+        const uint8_t *tx_from = (in_place || step > 0 ? dst : src) + tb * esz;
         if (!quantised) {
-            const auto tickets = st.send(dst + tb * esz, tx_n * esz);
+            const auto tickets = st.send(tx_from, tx_n * esz);
             const bool rx_ok = st.receive(rx_n * esz, [&](size_t off, const uint8_t *data, size_t n) {
+                if (!in_place) std::memcpy(dst + rb * esz + off, src + rb * esz + off, n);
                 cpu::reduce_inplace(dst + rb * esz + off, data, n / esz, a.dtype, a.op);
             });
             const bool tx_ok = st.finish_send(tickets);
@@ -251,17 +254,17 @@ RingResult ring_allreduce(const RingContext &ctx, const ReduceArgs &a, std::vect
         // The sending half (quantise piece by piece, hand each piece to the sockets) runs beside the receiving half
         // (decode and reduce every frame as it arrives): the two touch different chunks of dst.
         cpu::QuantParams mine = qp, theirs = qp;
-        cpu::quant_analyze(dst + tb * esz, tx_n, mine);
+        cpu::quant_analyze(tx_from, tx_n, mine);
         if (!st.exchange_meta(mine, theirs)) return fail();
         tx_codes.resize(cpu::quantized_size(mine, tx_n));
         Stage::Tickets tickets;
         auto tx_half = [&] {
             if (block_format) { // records first, codes after them: produced as a whole
-                cpu::quantize(dst + tb * esz, tx_codes.data(), tx_n, mine);
+                cpu::quantize(tx_from, tx_codes.data(), tx_n, mine);
                 tickets = st.send(tx_codes.data(), tx_codes.size());
             } else {
                 tickets = st.send_pieces(tx_codes.data(), tx_codes.size(), [&](size_t b, size_t e) {
-                    cpu::quantize(dst + (tb + b / qsz) * esz, tx_codes.data() + b, (e - b) / qsz, mine);
+                    cpu::quantize(tx_from + (b / qsz) * esz, tx_codes.data() + b, (e - b) / qsz, mine);
                 });
             }
         };
@@ -273,9 +276,11 @@ RingResult ring_allreduce(const RingContext &ctx, const ReduceArgs &a, std::vect
         if (block_format) {
             rx_codes.resize(rx_bytes);
             rx_ok = st.receive(rx_bytes, [&](size_t off, const uint8_t *data, size_t n) { std::memcpy(rx_codes.data() + off, data, n); });
+            if (rx_ok && !in_place) std::memcpy(dst + rb * esz, src + rb * esz, rx_n * esz);
             if (rx_ok) cpu::dequantize_reduce(dst + rb * esz, rx_codes.data(), rx_n, theirs, a.op);
         } else {
             rx_ok = st.receive(rx_bytes, [&](size_t off, const uint8_t *data, size_t n) {
+                if (!in_place) std::memcpy(dst + (rb + off / qsz) * esz, src + (rb + off / qsz) * esz, n / qsz * esz);
                 cpu::dequantize_reduce(dst + (rb + off / qsz) * esz, data, n / qsz, theirs, a.op);
             });
         }
