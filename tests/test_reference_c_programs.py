@@ -37,10 +37,21 @@ def test_c99_program(tmp_path):
                                                 ("basic_reduce_test", "All reduce finished", 1)])
 def test_reduce_program_runs_as_two_peers(tmp_path, name, marker, wanted):
     exe = build(tmp_path, name)
-    master = subprocess.Popen([str(REPO / "pccl_b200" / "bin" / "ccoip_master")], stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+    master = subprocess.Popen([str(REPO / "pccl_b200" / "bin" / "ccoip_master")], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
     peers = []
     try:
-        time.sleep(0.5)
+        # the programs connect exactly once, to the default port: wait until the master really listens there (and say why
+        # when it does not -- a stray process on 48148 is the usual reason)
+        import socket
+        deadline = time.time() + 30
+        while True:
+            assert master.poll() is None, f"ccoip_master exited with {master.returncode}: {master.stdout.read()[-2000:]}"
+            try:
+                socket.create_connection(("127.0.0.1", 48148), timeout=0.5).close()
+                break
+            except OSError:
+                assert time.time() < deadline, "ccoip_master does not listen on 48148"
+                time.sleep(0.05)
         peers = [subprocess.Popen([str(exe)], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True) for _ in range(2)]
         for p in peers:
             os.set_blocking(p.stdout.fileno(), False)
