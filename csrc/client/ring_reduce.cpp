@@ -356,6 +356,9 @@ RingResult ring_allreduce(const RingContext &ctx, const ReduceArgs &a, std::vect
     return res;
 }
 
+// a "local ring" of one peer reduces nothing: the input then has to be in place before the ring between hosts starts
+static bool L_is_one(const RingContext &local) { return local.world <= 1; }
+
 RingResult hierarchical_allreduce(const RingContext &local, const RingContext &cross, const ReduceArgs &a, std::vector<uint8_t> *backup) {
     RingResult res;
     const size_t esz = wire::dtype_size(a.dtype);
@@ -366,11 +369,11 @@ RingResult hierarchical_allreduce(const RingContext &local, const RingContext &c
     const uint32_t L = local.world, B = cross.world, l = local.rank;
     if ((L > 1 && (local.tx.empty() || local.tx.size() != local.rx.size())) || (B > 1 && (cross.tx.empty() || cross.tx.size() != cross.rx.size())))
         return res;
-    if (in_place) {
-        if (backup) backup->assign(dst, dst + a.count * esz);
-    } else {
-        std::memcpy(dst, a.src, a.count * esz);
-    }
+    // (out of place the input is brought over piece by piece as the frames of the local reduce-scatter arrive, as in the
+    // flat ring: every chunk but the own one is received exactly once there, and the all-gather overwrites the rest)
+    const auto *src = static_cast<const uint8_t *>(a.src);
+    if (in_place && backup) backup->assign(dst, dst + a.count * esz);
+    if (!in_place && L_is_one(local)) std::memcpy(dst, a.src, a.count * esz);
     auto fail = [&]() {
         if (in_place && backup && !backup->empty()) std::memcpy(dst, backup->data(), backup->size());
         res.ok = false;
@@ -386,8 +389,9 @@ RingResult hierarchical_allreduce(const RingContext &local, const RingContext &c
         uint64_t tb, te, rb, re;
         chunk_bounds(a.count, L, tx_chunk, tb, te);
         chunk_bounds(a.count, L, rx_chunk, rb, re);
-        const auto tickets = st.send(dst + tb * esz, (te - tb) * esz);
+        const auto tickets = st.send((in_place || step > 0 ? dst : src) + tb * esz, (te - tb) * esz);
         const bool rx_ok = st.receive((re - rb) * esz, [&](size_t off, const uint8_t *data, size_t n) {
+            if (!in_place) std::memcpy(dst + rb * esz + off, src + rb * esz + off, n);
             cpu::reduce_inplace(dst + rb * esz + off, data, n / esz, a.dtype, op);
         });
         const bool tx_ok = st.finish_send(tickets);
